@@ -1,0 +1,79 @@
+/* nds_b200.h - C ABI of the B200-native NDS query engine (libndsb200.so).
+ *
+ * The reference (bilalbari/spark-rapids-benchmarks) has no FFI of its own: its hot path is the
+ * py4j hand-off to Apache Spark.  Each entry point below cites the reference call it stands in
+ * for.  All functions return 0 on success and a non-zero code on failure; the message is
+ * available from nds_engine_last_error() (or nds_last_error() when no engine exists yet).
+ * Plain pointers and sizes only; results travel through the Arrow C Data Interface.
+ * There is no CPU fallback: without a CUDA device nds_engine_create() fails.
+ */
+#ifndef NDS_B200_H
+#define NDS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define NDS_API __attribute__((visibility("default")))
+#else
+#define NDS_API
+#endif
+
+struct ArrowSchema;
+struct ArrowArray;
+typedef struct nds_engine nds_engine;
+
+/* Library / ABI version string. */
+NDS_API const char* nds_version(void);
+
+/* Message of the last failure that happened without an engine handle (e.g. in nds_engine_create). */
+NDS_API const char* nds_last_error(void);
+
+/* Create an engine bound to one GPU.  cfg_json: {"device":0, "resident":true, "keep_host":false,
+ * "rank":0, "world":1}.  resident: encoded column chunks are kept in HBM; keep_host: a pinned host
+ * copy is kept as well so that a plan can run with {"options":{"source":"host"}} (host->device copy
+ * of the needed chunks inside the query).  rank/world: hive-partitioned (fact) tables are sharded by
+ * file across `world` engines, dimension tables are replicated.
+ * Replaces: SparkSession.builder...getOrCreate()   /root/reference/nds/nds_power.py:224-240 */
+NDS_API int nds_engine_create(const char* cfg_json, nds_engine** out);
+
+/* Replaces: sparkContext.stop()                      /root/reference/nds/nds_power.py:279-280 */
+NDS_API void nds_engine_destroy(nds_engine* e);
+
+NDS_API const char* nds_engine_last_error(nds_engine* e);
+
+/* Register `path` (a directory of uncompressed parquet files, optionally one level of
+ * <col>=<value> hive partition directories) under `name`.  Parses footers and page headers and stages
+ * the encoded pages in HBM.  format must be "parquet"; anything else fails.
+ * Replaces: spark.read.format(fmt).load(path).createOrReplaceTempView(name)
+ *                                                    /root/reference/nds/nds_power.py:97-100 */
+NDS_API int nds_engine_register_table(nds_engine* e, const char* name, const char* path, const char* format);
+
+/* Register an in-memory record batch (Arrow C Data Interface, struct array) as a table; the engine
+ * copies the buffers to the GPU and does not take ownership of the Arrow structures.  Used for
+ * operator-level tests and for the gathered partial aggregates of a multi-GPU run.
+ * Replaces: spark.createDataFrame(...).createOrReplaceTempView(name) (no call site on the hot path) */
+NDS_API int nds_engine_register_arrow(nds_engine* e, const char* name, struct ArrowSchema* schema, struct ArrowArray* array);
+
+NDS_API int nds_engine_drop_table(nds_engine* e, const char* name);
+
+/* JSON description of a registered table (rows, files, encoded bytes, columns) into buf. */
+NDS_API int nds_engine_table_info(nds_engine* e, const char* name, char* buf, int64_t buflen);
+
+/* Execute one physical plan (JSON plan IR, DESIGN.md "Plan IR") and return the result as one record
+ * batch.  The caller owns out_schema/out_array and must call their release callbacks.
+ * An unsupported node or expression fails with a message; nothing is computed on the CPU.
+ * Replaces: df = spark.sql(query); df.collect()     /root/reference/nds/nds_power.py:130-132 */
+NDS_API int nds_engine_execute(nds_engine* e, const char* plan_json, struct ArrowSchema* out_schema, struct ArrowArray* out_array);
+
+/* JSON statistics of the last nds_engine_execute: kernel launches, device ms, h2d/d2h bytes and
+ * per-operator {op, ms, bytes, rows}. */
+NDS_API int nds_engine_last_stats(nds_engine* e, char* buf, int64_t buflen);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NDS_B200_H */

@@ -1,0 +1,112 @@
+// extern "C" surface of libndsb200.so (declared in include/nds_b200.h).
+#include <mutex>
+#include "engine.h"
+#include "../../include/nds_b200.h"
+
+namespace nds {
+static std::mutex g_mu;
+static std::string g_error;
+void set_global_error(const std::string& s) {
+  std::lock_guard<std::mutex> l(g_mu);
+  g_error = s;
+}
+}  // namespace nds
+
+struct nds_engine {
+  nds::Engine* impl;
+};
+
+#define NDS_API_BEGIN try {
+#define NDS_API_END(e)                                                  \
+  }                                                                     \
+  catch (const std::exception& ex) {                                    \
+    if (e) (e)->impl->last_error = ex.what();                           \
+    else nds::set_global_error(ex.what());                              \
+    cudaGetLastError();                                                 \
+    return 1;                                                           \
+  }                                                                     \
+  return 0;
+
+static int copy_out(const std::string& s, char* buf, int64_t buflen) {
+  if (!buf || buflen <= 0) return 2;
+  if ((int64_t)s.size() + 1 > buflen) return 3;
+  memcpy(buf, s.c_str(), s.size() + 1);
+  return 0;
+}
+
+extern "C" {
+
+NDS_API const char* nds_version(void) { return "nds_b200 0.1 (sm_100a)"; }
+
+NDS_API const char* nds_last_error(void) {
+  static thread_local std::string copy;
+  std::lock_guard<std::mutex> l(nds::g_mu);
+  copy = nds::g_error;
+  return copy.c_str();
+}
+
+NDS_API int nds_engine_create(const char* cfg_json, nds_engine** out) {
+  nds_engine* none = nullptr;
+  NDS_API_BEGIN
+  if (!out) nds::fail("nds_engine_create: out is null");
+  nds::Json cfg = nds::JsonParser(cfg_json && *cfg_json ? cfg_json : "{}").parse();
+  nds::Engine* impl = new nds::Engine(cfg);
+  *out = new nds_engine{impl};
+  NDS_API_END(none)
+}
+
+NDS_API void nds_engine_destroy(nds_engine* e) {
+  if (!e) return;
+  delete e->impl;
+  delete e;
+}
+
+NDS_API const char* nds_engine_last_error(nds_engine* e) { return e ? e->impl->last_error.c_str() : nds_last_error(); }
+
+NDS_API int nds_engine_register_table(nds_engine* e, const char* name, const char* path, const char* format) {
+  if (!e) return 2;
+  NDS_API_BEGIN
+  e->impl->register_table(name, path, format ? format : "parquet");
+  NDS_API_END(e)
+}
+
+NDS_API int nds_engine_register_arrow(nds_engine* e, const char* name, struct ArrowSchema* schema, struct ArrowArray* array) {
+  if (!e) return 2;
+  NDS_API_BEGIN
+  e->impl->register_arrow(name, schema, array);
+  NDS_API_END(e)
+}
+
+NDS_API int nds_engine_drop_table(nds_engine* e, const char* name) {
+  if (!e) return 2;
+  NDS_API_BEGIN
+  e->impl->drop_table(name);
+  NDS_API_END(e)
+}
+
+NDS_API int nds_engine_table_info(nds_engine* e, const char* name, char* buf, int64_t buflen) {
+  if (!e) return 2;
+  NDS_API_BEGIN
+  int rc = copy_out(e->impl->table_info_json(name), buf, buflen);
+  if (rc) nds::fail("nds_engine_table_info: buffer too small");
+  NDS_API_END(e)
+}
+
+NDS_API int nds_engine_execute(nds_engine* e, const char* plan_json, struct ArrowSchema* out_schema, struct ArrowArray* out_array) {
+  if (!e) return 2;
+  NDS_API_BEGIN
+  if (!plan_json || !out_schema || !out_array) nds::fail("nds_engine_execute: null argument");
+  nds::Json plan = nds::JsonParser(plan_json).parse();
+  e->impl->execute(plan, out_schema, out_array);
+  NDS_API_END(e)
+}
+
+NDS_API int nds_engine_last_stats(nds_engine* e, char* buf, int64_t buflen) {
+  if (!e) return 2;
+  NDS_API_BEGIN
+  int rc = copy_out(e->impl->stats_json(), buf, buflen);
+  if (rc) nds::fail("nds_engine_last_stats: buffer too small");
+  NDS_API_END(e)
+}
+
+}  // extern "C"

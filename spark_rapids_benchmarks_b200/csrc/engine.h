@@ -1,0 +1,169 @@
+// Engine internals: table registry (encoded Parquet column chunks staged in HBM), plan executor.
+#pragma once
+#include <map>
+#include <memory>
+#include <set>
+#include "common.h"
+#include "json.h"
+#include "ops.cuh"
+#include "parquet_meta.h"
+
+// Arrow C Data Interface (https://arrow.apache.org/docs/format/CDataInterface.html)
+extern "C" {
+#ifndef ARROW_C_DATA_INTERFACE
+#define ARROW_C_DATA_INTERFACE
+struct ArrowSchema {
+  const char* format;
+  const char* name;
+  const char* metadata;
+  int64_t flags;
+  int64_t n_children;
+  struct ArrowSchema** children;
+  struct ArrowSchema* dictionary;
+  void (*release)(struct ArrowSchema*);
+  void* private_data;
+};
+struct ArrowArray {
+  int64_t length;
+  int64_t null_count;
+  int64_t offset;
+  int64_t n_buffers;
+  int64_t n_children;
+  const void** buffers;
+  struct ArrowArray** children;
+  struct ArrowArray* dictionary;
+  void (*release)(struct ArrowArray*);
+  void* private_data;
+};
+#endif
+}
+
+namespace nds {
+
+struct LType {                 // logical type of a column / expression
+  enum Kind { INT = 0, DATE = 1, DECIMAL = 2, F64 = 3, STR = 4, BOOL = 5 } kind = INT;
+  int precision = 0, scale = 0;
+  bool is32 = false;           // stored as int32 on the device
+  DType dtype() const { return kind == STR ? DT_STR : (kind == F64 ? DT_F64 : (is32 ? DT_I32 : DT_I64)); }
+  std::string str() const;
+};
+
+struct PageInfo {
+  int32_t file, dict;          // dict: index into TableColumn::dicts or -1
+  int64_t off;                 // payload offset in the column's staged byte buffer
+  uint32_t size, num_values, def_len;
+  int64_t row_in_file;
+  uint8_t enc;                 // 0 PLAIN, 1 dictionary
+};
+struct DictInfo {
+  int64_t off;                 // fixed width: values; BYTE_ARRAY: StrView table (chars follow)
+  uint32_t count;
+};
+struct FileInfo {
+  std::string path;
+  int64_t rows = 0;
+  bool part_null = false;
+  int64_t part_val = 0;
+};
+struct TableColumn {
+  std::string name;
+  int phys = -1;
+  LType lt;
+  bool nullable = false;
+  bool supported = true;
+  std::string why_unsupported;
+  std::vector<uint8_t> stage;          // host copy of the encoded pages (kept when keep_host)
+  bool pinned = false;
+  uint8_t* d_enc = nullptr;            // resident copy in HBM
+  int64_t enc_bytes = 0;
+  std::vector<PageInfo> pages;
+  std::vector<DictInfo> dicts;
+  std::vector<int64_t> file_page_begin;  // per file: first page index (size nfiles + 1)
+  std::vector<int64_t> file_byte_begin;  // per file: first staged byte (16 B aligned), size nfiles + 1
+};
+struct MemColumn {                      // table registered from Arrow buffers
+  std::string name;
+  LType lt;
+  void* d_data = nullptr;
+  uint32_t* d_valid = nullptr;
+  uint8_t* d_chars = nullptr;
+};
+struct Table {
+  std::string name, path;
+  std::vector<FileInfo> files;
+  std::vector<TableColumn> cols;
+  std::map<std::string, int> col_index;
+  std::string part_col;                 // hive partition column ("" if none)
+  int64_t rows = 0;
+  int64_t encoded_bytes = 0;
+  bool is_mem = false;
+  std::vector<MemColumn> mem_cols;
+};
+
+struct Column {
+  std::string name;
+  LType lt;
+  const void* data = nullptr;
+  const uint32_t* valid = nullptr;
+  const uint32_t* rowmap = nullptr;
+  const uint8_t* strbase = nullptr;
+  ColRef ref() const {
+    ColRef r;
+    r.data = data; r.valid = valid; r.rowmap = rowmap; r.strbase = strbase; r.dtype = lt.dtype(); r.pad = 0;
+    return r;
+  }
+};
+
+struct Batch {
+  int64_t n_max = 0;            // upper bound (exact when n_dev == nullptr)
+  int* n_dev = nullptr;
+  int64_t n_exact = -1;         // cached after a sync
+  std::vector<Column> cols;
+  RowCount rc() const { return RowCount{n_dev, n_exact >= 0 ? n_exact : n_max}; }
+  int find(const std::string& name) const {
+    for (size_t i = 0; i < cols.size(); ++i)
+      if (cols[i].name == name) return (int)i;
+    return -1;
+  }
+};
+
+struct OpStat {
+  std::string op;
+  double ms = 0;
+  int64_t bytes = 0;            // algorithmic bytes
+  int64_t rows = 0;
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+};
+
+typedef int (*nds_allgather_fn)(void* ctx, const void* send_dev, int64_t send_bytes, void* recv_dev,
+                                int64_t max_bytes_per_rank, int64_t* recv_bytes);
+
+class Engine {
+ public:
+  explicit Engine(const Json& cfg);
+  ~Engine();
+  void register_table(const std::string& name, const std::string& path, const std::string& format);
+  void register_arrow(const std::string& name, ArrowSchema* schema, ArrowArray* array);
+  void drop_table(const std::string& name);
+  void execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_array);
+  std::string stats_json() const;
+  std::string table_info_json(const std::string& name) const;
+
+  std::string last_error;
+  int device = 0;
+  int rank = 0, world = 1;
+
+ private:
+  friend struct Exec;
+  cudaStream_t stream_ = nullptr;
+  bool resident_ = true, keep_host_ = false;
+  std::map<std::string, Table> tables_;
+  std::vector<OpStat> stats_;
+  int64_t launches_ = 0;
+  int64_t h2d_bytes_ = 0, d2h_bytes_ = 0;
+  double exec_ms_ = 0;
+};
+
+void set_global_error(const std::string& s);
+
+}  // namespace nds

@@ -1,0 +1,1123 @@
+// Plan executor: walks the JSON physical-plan IR (scan / filter / project / join / aggregate / sort)
+// and drives the kernels in decode.cu and ops.cu.  Replaces the engine behind the reference's
+// `spark_session.sql(query)` + `collect()` / `write...save()` hand-off
+// (/root/reference/nds/nds_power.py:125-135).  An unknown node or expression raises; there is no CPU path.
+#include <algorithm>
+#include <cmath>
+#include <unordered_set>
+#include "engine.h"
+
+namespace nds {
+
+namespace {
+
+struct Arena {
+  cudaStream_t s;
+  std::vector<void*> ptrs;
+  explicit Arena(cudaStream_t st) : s(st) {}
+  void* alloc(int64_t bytes) {
+    void* p = nullptr;
+    if (bytes < 16) bytes = 16;
+    NDS_CUDA(cudaMallocAsync(&p, (size_t)bytes + 64, s));
+    ptrs.push_back(p);
+    return p;
+  }
+  template <typename T>
+  T* alloc_n(int64_t n) { return reinterpret_cast<T*>(alloc(n * (int64_t)sizeof(T))); }
+  template <typename T>
+  T* zeros(int64_t n) {
+    T* p = alloc_n<T>(n);
+    NDS_CUDA(cudaMemsetAsync(p, 0, (size_t)(n < 1 ? 16 : n * (int64_t)sizeof(T)), s));
+    return p;
+  }
+  ~Arena() {
+    for (void* p : ptrs) cudaFreeAsync(p, s);
+  }
+};
+
+int64_t pow10i(int k) {
+  int64_t v = 1;
+  for (int i = 0; i < k; ++i) v *= 10;
+  return v;
+}
+
+uint32_t next_pow2(int64_t v) {
+  uint32_t c = 64;
+  while ((int64_t)c < v) c <<= 1;
+  return c;
+}
+
+LType parse_type(const std::string& s) {
+  LType t;
+  if (s == "int" || s == "int64" || s == "long" || s == "bigint") { t.kind = LType::INT; return t; }
+  if (s == "int32") { t.kind = LType::INT; t.is32 = true; return t; }
+  if (s == "double") { t.kind = LType::F64; return t; }
+  if (s == "string") { t.kind = LType::STR; return t; }
+  if (s == "bool") { t.kind = LType::BOOL; return t; }
+  if (s == "date") { t.kind = LType::DATE; t.is32 = true; return t; }
+  int p, sc;
+  if (sscanf(s.c_str(), "decimal(%d,%d)", &p, &sc) == 2) { t.kind = LType::DECIMAL; t.precision = p; t.scale = sc; return t; }
+  fail("plan: unknown type '" + s + "'");
+}
+
+// Collects the column slots, literal pool and programs of one operator and uploads them in one copy.
+struct Blob {
+  std::vector<ColRef> cols;
+  std::vector<int> col_src;
+  std::string lit;
+  std::vector<std::vector<Instr>> progs;
+  std::vector<int> kinds;
+
+  int slot(const Batch& b, int ci) {
+    for (size_t i = 0; i < col_src.size(); ++i)
+      if (col_src[i] == ci) return (int)i;
+    col_src.push_back(ci);
+    cols.push_back(b.cols[ci].ref());
+    return (int)cols.size() - 1;
+  }
+  int add_prog(std::vector<Instr> code, const LType& t) {
+    progs.push_back(std::move(code));
+    kinds.push_back(t.kind == LType::STR ? 2 : (t.kind == LType::F64 ? 1 : 0));
+    return (int)progs.size() - 1;
+  }
+  struct Dev {
+    OpCtx ctx;
+    std::vector<Prog> host_progs;
+    const Prog* progs = nullptr;
+    const uint8_t* extra = nullptr;   // caller-provided POD block (AggSpec / SortKey arrays)
+  };
+  Dev upload(Arena& ar, cudaStream_t s, const void* extra = nullptr, int64_t extra_bytes = 0) {
+    int64_t off_cols = 0;
+    int64_t off_lit = align_up(off_cols + (int64_t)cols.size() * sizeof(ColRef), 16);
+    int64_t off_code = align_up(off_lit + (int64_t)lit.size() + 1, 16);
+    int64_t ninstr = 0;
+    for (auto& p : progs) ninstr += (int64_t)p.size();
+    int64_t off_progs = align_up(off_code + ninstr * (int64_t)sizeof(Instr), 16);
+    int64_t off_extra = align_up(off_progs + (int64_t)progs.size() * sizeof(Prog), 16);
+    int64_t total = off_extra + extra_bytes + 16;
+    std::vector<uint8_t> h(total, 0);
+    uint8_t* d = (uint8_t*)ar.alloc(total);
+    if (!cols.empty()) memcpy(h.data() + off_cols, cols.data(), cols.size() * sizeof(ColRef));
+    if (!lit.empty()) memcpy(h.data() + off_lit, lit.data(), lit.size());
+    Dev dev;
+    int64_t ci = 0;
+    for (size_t k = 0; k < progs.size(); ++k) {
+      if (!progs[k].empty()) memcpy(h.data() + off_code + ci * sizeof(Instr), progs[k].data(), progs[k].size() * sizeof(Instr));
+      Prog p;
+      p.code = reinterpret_cast<const Instr*>(d + off_code + ci * sizeof(Instr));
+      p.n = (int32_t)progs[k].size();
+      p.kind = kinds[k];
+      dev.host_progs.push_back(p);
+      ci += (int64_t)progs[k].size();
+    }
+    if (!progs.empty()) memcpy(h.data() + off_progs, dev.host_progs.data(), progs.size() * sizeof(Prog));
+    if (extra_bytes) memcpy(h.data() + off_extra, extra, extra_bytes);
+    NDS_CUDA(cudaMemcpyAsync(d, h.data(), total, cudaMemcpyHostToDevice, s));
+    NDS_CUDA(cudaStreamSynchronize(s));   // h goes out of scope; pageable copy is already staged, this is cheap
+    dev.ctx.cols = reinterpret_cast<const ColRef*>(d + off_cols);
+    dev.ctx.lit = d + off_lit;
+    dev.progs = reinterpret_cast<const Prog*>(d + off_progs);
+    dev.extra = d + off_extra;
+    return dev;
+  }
+};
+
+struct RuntimeFilter {           // dynamic partition pruning: build-side join keys
+  std::string column;
+  std::unordered_set<int64_t> keys;
+};
+
+}  // namespace
+
+struct Exec {
+  Engine& e;
+  Arena ar;
+  cudaStream_t s;
+  int* err = nullptr;            // err[0]: kernel error code, err[1]: join flags
+  bool source_host = false;
+  bool profile = false;
+  std::vector<OpStat> stats;
+  int64_t launches = 0;
+  int64_t h2d = 0, d2h = 0;
+
+  Exec(Engine& en, const Json* options) : e(en), ar(en.stream_), s(en.stream_) {
+    err = ar.zeros<int>(4);
+    if (options) {
+      source_host = options->str_or("source", "hbm") == "host";
+      profile = options->bool_or("profile", false);
+    }
+  }
+
+  // ---------------------------------------------------------------- op timing
+  size_t begin_stat(const std::string& op, bool always = false) {
+    OpStat st;
+    st.op = op;
+    if (profile || always) {
+      NDS_CUDA(cudaEventCreate(&st.e0));
+      NDS_CUDA(cudaEventCreate(&st.e1));
+      NDS_CUDA(cudaEventRecord(st.e0, s));
+    }
+    stats.push_back(st);
+    return stats.size() - 1;
+  }
+  void end_stat(size_t i, int64_t bytes, int64_t rows) {
+    stats[i].bytes = bytes;
+    stats[i].rows = rows;
+    if (stats[i].e1) NDS_CUDA(cudaEventRecord(stats[i].e1, s));
+  }
+
+  void check_err() {
+    int h[4];
+    NDS_CUDA(cudaMemcpyAsync(h, err, sizeof h, cudaMemcpyDeviceToHost, s));
+    NDS_CUDA(cudaStreamSynchronize(s));
+    if (h[0]) fail("device kernel reported error code " + std::to_string(h[0]) +
+                   " (3-6: malformed parquet page, 11: string projection outside its column buffer, 12: sort key overflow)");
+    if (h[1] & 1) fail("hash join: duplicate keys on the build side (only unique build keys are supported)");
+    if (h[1] & 2) fail("hash join: key equals the reserved empty marker");
+  }
+
+  int64_t count(Batch& b) {
+    if (b.n_exact >= 0) return b.n_exact;
+    if (!b.n_dev) { b.n_exact = b.n_max; return b.n_exact; }
+    int v = 0;
+    NDS_CUDA(cudaMemcpyAsync(&v, b.n_dev, 4, cudaMemcpyDeviceToHost, s));
+    NDS_CUDA(cudaStreamSynchronize(s));
+    d2h += 4;
+    b.n_exact = std::min<int64_t>(v, b.n_max);
+    return b.n_exact;
+  }
+
+  // ---------------------------------------------------------------- expressions
+  static bool is_intlike(const LType& t) { return t.kind == LType::INT || t.kind == LType::DATE || t.kind == LType::DECIMAL || t.kind == LType::BOOL; }
+
+  void to_double(std::vector<Instr>& code, const LType& t) {
+    if (t.kind == LType::F64) return;
+    code.push_back(Instr{OP_I2F, 0, 0});
+    if (t.kind == LType::DECIMAL && t.scale > 0) {
+      double d = std::pow(10.0, t.scale);
+      int64_t bits;
+      memcpy(&bits, &d, 8);
+      code.push_back(Instr{OP_LIT_F, 0, bits});
+      code.push_back(Instr{OP_DIV_F, 0, 0});
+    }
+  }
+  void scale_up(std::vector<Instr>& code, int k) {
+    if (k <= 0) return;
+    code.push_back(Instr{OP_LIT_I, 0, pow10i(k)});
+    code.push_back(Instr{OP_MUL_I, 0, 0});
+  }
+
+  // str_origin: batch column whose byte buffer a string result points into (-1: none / literal, -2: mixed)
+  LType compile(const Json& x, const Batch& b, Blob& bb, std::vector<Instr>& code, int* str_origin = nullptr) {
+    if (str_origin) *str_origin = -1;
+    if (x.kind != Json::Obj) fail("plan: expression must be an object");
+    if (x.has("col")) {
+      const std::string& name = x.str("col");
+      int ci = b.find(name);
+      if (ci < 0) fail("plan: unknown column '" + name + "'");
+      code.push_back(Instr{OP_COL, bb.slot(b, ci), 0});
+      if (str_origin && b.cols[ci].lt.kind == LType::STR) *str_origin = ci;
+      return b.cols[ci].lt;
+    }
+    if (x.has("lit")) {
+      const Json& v = x.at("lit");
+      if (v.kind == Json::Null) { code.push_back(Instr{OP_LIT_NULL, 0, 0}); return x.has("type") ? parse_type(x.str("type")) : LType(); }
+      LType t = parse_type(x.str_or("type", v.kind == Json::Str ? "string" : (v.is_int ? "int" : "double")));
+      if (t.kind == LType::STR) {
+        if (v.kind != Json::Str) fail("plan: string literal expected");
+        int64_t off = (int64_t)bb.lit.size();
+        bb.lit += v.s;
+        code.push_back(Instr{OP_LIT_S, 0, (int64_t)(((uint64_t)v.s.size() << 32) | (uint64_t)off)});
+      } else if (t.kind == LType::F64) {
+        double d = v.d;
+        int64_t bits;
+        memcpy(&bits, &d, 8);
+        code.push_back(Instr{OP_LIT_F, 0, bits});
+      } else {
+        if (v.kind != Json::Num || !v.is_int) fail("plan: integer literal expected (decimals are passed unscaled)");
+        code.push_back(Instr{OP_LIT_I, 0, v.i});
+      }
+      return t;
+    }
+    const std::string& fn = x.str("fn");
+    const Json& args = x.at("args");
+    auto arg = [&](size_t i) -> const Json& {
+      if (i >= args.a.size()) fail("plan: function '" + fn + "' is missing argument " + std::to_string(i));
+      return args.a[i];
+    };
+    LType out;
+    static const std::map<std::string, int> cmp = {{"eq", 0}, {"ne", 1}, {"lt", 2}, {"le", 3}, {"gt", 4}, {"ge", 5}};
+    auto cit = cmp.find(fn);
+    if (cit != cmp.end()) {
+      std::vector<Instr> ca, cb;
+      LType ta = compile(arg(0), b, bb, ca), tb = compile(arg(1), b, bb, cb);
+      int base;
+      if (ta.kind == LType::STR || tb.kind == LType::STR) {
+        if (ta.kind != tb.kind) fail("plan: comparison between string and non-string");
+        base = OP_EQ_S;
+      } else if (ta.kind == LType::F64 || tb.kind == LType::F64) {
+        to_double(ca, ta);
+        to_double(cb, tb);
+        base = OP_EQ_F;
+      } else {
+        int sa = ta.kind == LType::DECIMAL ? ta.scale : 0, sb = tb.kind == LType::DECIMAL ? tb.scale : 0;
+        scale_up(ca, sb - sa);
+        scale_up(cb, sa - sb);
+        base = OP_EQ_I;
+      }
+      code.insert(code.end(), ca.begin(), ca.end());
+      code.insert(code.end(), cb.begin(), cb.end());
+      code.push_back(Instr{base + cit->second, 0, 0});
+      out.kind = LType::BOOL;
+    } else if (fn == "and" || fn == "or") {
+      if (args.a.empty()) fail("plan: empty " + fn);
+      for (size_t i = 0; i < args.a.size(); ++i) {
+        LType t = compile(args.a[i], b, bb, code);
+        if (t.kind != LType::BOOL) fail("plan: " + fn + " over a non-boolean");
+        if (i) code.push_back(Instr{fn == "and" ? OP_AND : OP_OR, 0, 0});
+      }
+      out.kind = LType::BOOL;
+    } else if (fn == "not") {
+      compile(arg(0), b, bb, code);
+      code.push_back(Instr{OP_NOT, 0, 0});
+      out.kind = LType::BOOL;
+    } else if (fn == "isnull" || fn == "isnotnull") {
+      compile(arg(0), b, bb, code);
+      code.push_back(Instr{fn == "isnull" ? OP_ISNULL : OP_ISNOTNULL, 0, 0});
+      out.kind = LType::BOOL;
+    } else if (fn == "add" || fn == "sub" || fn == "mul") {
+      std::vector<Instr> ca, cb;
+      LType ta = compile(arg(0), b, bb, ca), tb = compile(arg(1), b, bb, cb);
+      if (ta.kind == LType::STR || tb.kind == LType::STR) fail("plan: arithmetic on strings");
+      if (ta.kind == LType::F64 || tb.kind == LType::F64) {
+        to_double(ca, ta);
+        to_double(cb, tb);
+        code.insert(code.end(), ca.begin(), ca.end());
+        code.insert(code.end(), cb.begin(), cb.end());
+        code.push_back(Instr{fn == "add" ? OP_ADD_F : (fn == "sub" ? OP_SUB_F : OP_MUL_F), 0, 0});
+        out.kind = LType::F64;
+      } else {
+        int sa = ta.kind == LType::DECIMAL ? ta.scale : 0, sb = tb.kind == LType::DECIMAL ? tb.scale : 0;
+        bool dec = ta.kind == LType::DECIMAL || tb.kind == LType::DECIMAL;
+        int pa = ta.kind == LType::DECIMAL ? ta.precision : (ta.is32 ? 10 : 20), pb = tb.kind == LType::DECIMAL ? tb.precision : (tb.is32 ? 10 : 20);
+        if (fn != "mul") { scale_up(ca, sb - sa); scale_up(cb, sa - sb); }
+        code.insert(code.end(), ca.begin(), ca.end());
+        code.insert(code.end(), cb.begin(), cb.end());
+        code.push_back(Instr{fn == "add" ? OP_ADD_I : (fn == "sub" ? OP_SUB_I : OP_MUL_I), 0, 0});
+        if (dec) {
+          out.kind = LType::DECIMAL;
+          if (fn == "mul") { out.scale = sa + sb; out.precision = std::min(38, pa + pb + 1); }
+          else { out.scale = std::max(sa, sb); out.precision = std::min(38, std::max(pa - sa, pb - sb) + out.scale + 1); }
+        } else out.kind = LType::INT;
+      }
+    } else if (fn == "neg") {
+      LType t = compile(arg(0), b, bb, code);
+      code.push_back(Instr{t.kind == LType::F64 ? OP_NEG_F : OP_NEG_I, 0, 0});
+      out = t;
+      out.is32 = false;
+    } else if (fn == "substr") {
+      int origin = -1;
+      LType t = compile(arg(0), b, bb, code, &origin);
+      if (t.kind != LType::STR) fail("plan: substr over a non-string");
+      code.push_back(Instr{OP_SUBSTR, (int32_t)x.int_or("start", 1), x.int_or("len", 1 << 30)});
+      if (str_origin) *str_origin = origin;
+      out.kind = LType::STR;
+    } else if (fn == "if") {
+      LType tc = compile(arg(0), b, bb, code);
+      if (tc.kind != LType::BOOL) fail("plan: if() condition must be boolean");
+      LType tt = compile(arg(1), b, bb, code), te = compile(arg(2), b, bb, code);
+      if ((tt.kind == LType::STR) != (te.kind == LType::STR) || (tt.kind == LType::F64) != (te.kind == LType::F64))
+        fail("plan: if() branches of different type families");
+      code.push_back(Instr{OP_IF, 0, 0});
+      if (str_origin) *str_origin = -2;
+      out = tt;
+      out.is32 = false;
+    } else if (fn == "decavg") {
+      LType ts = compile(arg(0), b, bb, code);
+      compile(arg(1), b, bb, code);
+      int up = (int)x.int_or("up", 4);
+      code.push_back(Instr{OP_DECAVG, up, 0});
+      out.kind = LType::DECIMAL;
+      out.scale = (ts.kind == LType::DECIMAL ? ts.scale : 0) + up;
+      out.precision = std::min(38, (ts.kind == LType::DECIMAL ? ts.precision : 20) - 10 + up);
+    } else if (fn == "divi2f") {
+      compile(arg(0), b, bb, code);
+      compile(arg(1), b, bb, code);
+      code.push_back(Instr{OP_DIVI2F, 0, 0});
+      out.kind = LType::F64;
+    } else if (fn == "cast_double") {
+      LType t = compile(arg(0), b, bb, code);
+      if (t.kind == LType::STR) fail("plan: cast string -> double is not supported");
+      to_double(code, t);
+      out.kind = LType::F64;
+    } else {
+      fail("plan: unsupported expression function '" + fn + "'");
+    }
+    if (x.has("type")) {
+      LType forced = parse_type(x.str("type"));
+      if ((forced.kind == LType::STR) != (out.kind == LType::STR) || (forced.kind == LType::F64) != (out.kind == LType::F64))
+        fail("plan: type annotation '" + x.str("type") + "' contradicts the expression");
+      out = forced;
+      out.is32 = false;
+    }
+    if ((int)code.size() > 200) fail("plan: expression too large");
+    return out;
+  }
+
+  // rowmap composition with per-operator caching (columns that share a rowmap share the result)
+  struct MapCache {
+    std::map<const uint32_t*, const uint32_t*> m;
+  };
+  const uint32_t* remap(const uint32_t* old_map, const uint32_t* sel, RowCount n, MapCache& mc) {
+    if (!old_map) return sel;
+    auto it = mc.m.find(old_map);
+    if (it != mc.m.end()) return it->second;
+    uint32_t* out = ar.alloc_n<uint32_t>(n.host);
+    launch_compose(old_map, sel, n, out, s);
+    ++launches;
+    mc.m[old_map] = out;
+    return out;
+  }
+
+  // ---------------------------------------------------------------- scan
+  Batch scan(const Json& node, std::vector<RuntimeFilter>& filters) {
+    const std::string& tname = node.str("table");
+    auto it = e.tables_.find(tname);
+    if (it == e.tables_.end()) fail("plan: table '" + tname + "' is not registered");
+    Table& t = it->second;
+    const Json& jc = node.at("columns");
+    Batch out;
+    if (t.is_mem) {
+      out.n_max = t.rows;
+      for (const Json& c : jc.a) {
+        auto ci = t.col_index.find(c.s);
+        if (ci == t.col_index.end()) fail("plan: table '" + tname + "' has no column '" + c.s + "'");
+        const MemColumn& mc = t.mem_cols[ci->second];
+        Column col;
+        col.name = mc.name; col.lt = mc.lt; col.data = mc.d_data; col.valid = mc.d_valid; col.strbase = mc.d_chars;
+        out.cols.push_back(col);
+      }
+      return out;
+    }
+    // ---- partition pruning (Spark: dynamic partition pruning on the broadcast side's keys)
+    const RuntimeFilter* rf = nullptr;
+    for (const RuntimeFilter& f : filters)
+      if (f.column == t.part_col && !t.part_col.empty()) rf = &f;
+    std::vector<int> sel;
+    std::vector<int64_t> row_start;
+    int64_t N = 0;
+    for (size_t f = 0; f < t.files.size(); ++f) {
+      const FileInfo& fi = t.files[f];
+      if (rf && (fi.part_null || !rf->keys.count(fi.part_val))) continue;
+      sel.push_back((int)f);
+      row_start.push_back(N);
+      N += fi.rows;
+    }
+    row_start.push_back(N);
+    if (N >= (int64_t(1) << 31)) fail("scan of '" + tname + "' selects 2^31 or more rows; shard the table across GPUs");
+    out.n_max = N;
+    size_t st = begin_stat("decode:" + tname, true);
+    std::vector<PageTask> tasks;
+    int64_t bytes_in = 0, bytes_out = 0;
+    for (const Json& c : jc.a) {
+      const std::string& cname = c.s;
+      Column col;
+      col.name = cname;
+      if (cname == t.part_col) {
+        col.lt.kind = LType::INT;
+        col.lt.is32 = true;
+        int32_t* d = ar.alloc_n<int32_t>(N);
+        uint32_t* valid = nullptr;
+        std::vector<int64_t> seg(2 * sel.size() + 1);
+        bool any_null = false;
+        for (size_t k = 0; k < sel.size(); ++k) any_null |= t.files[sel[k]].part_null;
+        if (any_null) {
+          // validity: whole files are null; build on host (tiny) and upload
+          std::vector<uint32_t> hv((N + 31) / 32 + 1, 0);
+          for (size_t k = 0; k < sel.size(); ++k) {
+            if (t.files[sel[k]].part_null) continue;
+            for (int64_t r = row_start[k]; r < row_start[k + 1];) {
+              if ((r & 31) == 0 && r + 32 <= row_start[k + 1]) { hv[r >> 5] = 0xFFFFFFFFu; r += 32; }
+              else { hv[r >> 5] |= 1u << (r & 31); ++r; }
+            }
+          }
+          valid = ar.alloc_n<uint32_t>((int64_t)hv.size());
+          NDS_CUDA(cudaMemcpyAsync(valid, hv.data(), hv.size() * 4, cudaMemcpyHostToDevice, s));
+          NDS_CUDA(cudaStreamSynchronize(s));
+          h2d += (int64_t)hv.size() * 4;
+        }
+        if (!sel.empty()) {
+          std::vector<int64_t> hs(sel.size() + 1), hvv(sel.size());
+          for (size_t k = 0; k < sel.size(); ++k) { hs[k] = row_start[k]; hvv[k] = t.files[sel[k]].part_null ? 0 : t.files[sel[k]].part_val; }
+          hs[sel.size()] = N;
+          int64_t* dseg = ar.alloc_n<int64_t>((int64_t)hs.size() + (int64_t)hvv.size());
+          NDS_CUDA(cudaMemcpyAsync(dseg, hs.data(), hs.size() * 8, cudaMemcpyHostToDevice, s));
+          NDS_CUDA(cudaMemcpyAsync(dseg + hs.size(), hvv.data(), hvv.size() * 8, cudaMemcpyHostToDevice, s));
+          NDS_CUDA(cudaStreamSynchronize(s));
+          launch_fill_segments(dseg, dseg + hs.size(), (int)sel.size(), d, s);
+          ++launches;
+          bytes_out += N * 4;
+        }
+        col.data = d;
+        col.valid = valid;
+        out.cols.push_back(col);
+        continue;
+      }
+      auto ci = t.col_index.find(cname);
+      if (ci == t.col_index.end()) fail("plan: table '" + tname + "' has no column '" + cname + "'");
+      TableColumn& tc = t.cols[ci->second];
+      if (!tc.supported) fail("column '" + cname + "' of '" + tname + "' cannot be decoded: " + tc.why_unsupported);
+      col.lt = tc.lt;
+      const int width = tc.lt.dtype() == DT_I32 ? 4 : 8;
+      void* d_out = ar.alloc(N * width);
+      uint32_t* d_valid = tc.nullable ? ar.zeros<uint32_t>((N + 31) / 32 + 1) : nullptr;
+      col.data = d_out;
+      col.valid = d_valid;
+      // ---- where do the encoded bytes come from
+      const uint8_t* src_base = nullptr;   // address of staged byte 0
+      if (!sel.empty()) {
+        if (source_host) {
+          if (tc.stage.empty()) fail("engine was created without keep_host; source=host is unavailable");
+          int64_t span_b = tc.file_byte_begin[sel.front()], span_e = tc.file_byte_begin[sel.back() + 1];
+          uint8_t* tr = (uint8_t*)ar.alloc(span_e - span_b + 256);
+          // copy only the selected files' byte ranges, adjacent ranges coalesced
+          size_t k = 0;
+          while (k < sel.size()) {
+            size_t k2 = k;
+            while (k2 + 1 < sel.size() && sel[k2 + 1] == sel[k2] + 1) ++k2;
+            int64_t b0 = tc.file_byte_begin[sel[k]], b1 = tc.file_byte_begin[sel[k2] + 1];
+            NDS_CUDA(cudaMemcpyAsync(tr + (b0 - span_b), tc.stage.data() + b0, b1 - b0, cudaMemcpyHostToDevice, s));
+            h2d += b1 - b0;
+            k = k2 + 1;
+          }
+          src_base = tr - span_b;
+        } else {
+          if (!tc.d_enc) fail("engine was created with resident=false; use source=host");
+          src_base = tc.d_enc;
+        }
+      }
+      col.strbase = src_base;
+      for (size_t k = 0; k < sel.size(); ++k) {
+        int f = sel[k];
+        for (int64_t p = tc.file_page_begin[f]; p < tc.file_page_begin[f + 1]; ++p) {
+          const PageInfo& pi = tc.pages[p];
+          PageTask task;
+          memset(&task, 0, sizeof task);
+          task.src = src_base + pi.off;
+          task.out = d_out;
+          task.valid = d_valid;
+          task.out_row = row_start[k] + pi.row_in_file;
+          task.size = pi.size;
+          task.num_values = pi.num_values;
+          task.def_len = pi.def_len;
+          task.src_off = (uint32_t)pi.off;
+          task.enc = pi.enc;
+          task.width = (uint8_t)width;
+          task.phys = tc.phys == pq::BYTE_ARRAY ? 1 : 0;
+          if (pi.dict >= 0) {
+            task.dict = src_base + tc.dicts[pi.dict].off;
+            task.dict_count = tc.dicts[pi.dict].count;
+          }
+          tasks.push_back(task);
+          bytes_in += pi.size;
+        }
+      }
+      bytes_out += N * width + (tc.nullable ? N / 8 : 0);
+      out.cols.push_back(col);
+    }
+    if (!tasks.empty()) {
+      PageTask* d_tasks = ar.alloc_n<PageTask>((int64_t)tasks.size());
+      NDS_CUDA(cudaMemcpyAsync(d_tasks, tasks.data(), tasks.size() * sizeof(PageTask), cudaMemcpyHostToDevice, s));
+      NDS_CUDA(cudaStreamSynchronize(s));
+      // a dedicated pair of events brackets only the decode launch (roofline.achieved in bench.py)
+      size_t ks = begin_stat("decode_kernel", true);
+      launch_decode_pages(d_tasks, (int)tasks.size(), err, s);
+      ++launches;
+      end_stat(ks, bytes_in + bytes_out, N);
+    }
+    end_stat(st, bytes_in + bytes_out, N);
+    return out;
+  }
+
+  // ---------------------------------------------------------------- filter
+  Batch filter(const Json& node, std::vector<RuntimeFilter>& filters) {
+    Batch in = exec(node.at("child"), filters);
+    size_t st = begin_stat("filter");
+    Blob bb;
+    std::vector<Instr> code;
+    LType t = compile(node.at("cond"), in, bb, code);
+    if (t.kind != LType::BOOL) fail("plan: filter condition is not boolean");
+    bb.add_prog(code, t);
+    Blob::Dev dev = bb.upload(ar, s);
+    RowCount n = in.rc();
+    uint32_t* sel = ar.alloc_n<uint32_t>(n.host);
+    int* cnt = ar.zeros<int>(1);
+    launch_filter(dev.host_progs[0], dev.ctx, n, sel, cnt, s);
+    ++launches;
+    Batch out;
+    out.n_max = n.host;
+    out.n_dev = cnt;
+    MapCache mc;
+    RowCount nout{cnt, n.host};
+    for (const Column& c : in.cols) {
+      Column o = c;
+      o.rowmap = remap(c.rowmap, sel, nout, mc);
+      out.cols.push_back(o);
+    }
+    end_stat(st, 0, n.host);
+    return out;
+  }
+
+  // ---------------------------------------------------------------- project
+  Column eval_to_column(const Json& expr, const std::string& name, Batch& in, const uint32_t* rows, RowCount n) {
+    Blob bb;
+    std::vector<Instr> code;
+    int origin = -1;
+    LType t = compile(expr, in, bb, code, &origin);
+    bb.add_prog(code, t);
+    Blob::Dev dev = bb.upload(ar, s);
+    Column o;
+    o.name = name;
+    o.lt = t;
+    if (t.kind == LType::BOOL) { o.lt.kind = LType::INT; o.lt.is32 = false; }
+    const DType dt = o.lt.dtype();
+    const uint8_t* sbase = nullptr;
+    if (dt == DT_STR) {
+      if (origin < 0) fail("plan: a string-valued projection must be a column or substr(column)");
+      sbase = in.cols[origin].strbase;
+      o.strbase = sbase;
+    }
+    void* d = ar.alloc(n.host * (dt == DT_I32 ? 4 : 8));
+    uint32_t* v = ar.alloc_n<uint32_t>((n.host + 31) / 32 + 1);
+    launch_project(dev.host_progs[0], dev.ctx, n, rows, d, v, dt, sbase, err, s);
+    ++launches;
+    o.data = d;
+    o.valid = v;
+    return o;
+  }
+
+  Batch project(const Json& node, std::vector<RuntimeFilter>& filters) {
+    Batch in = exec(node.at("child"), filters);
+    size_t st = begin_stat("project");
+    Batch out;
+    out.n_max = in.n_max;
+    out.n_dev = in.n_dev;
+    out.n_exact = in.n_exact;
+    for (const Json& pe : node.at("exprs").a) {
+      const std::string& name = pe.str("name");
+      const Json& ex = pe.at("expr");
+      if (ex.has("col")) {
+        int ci = in.find(ex.str("col"));
+        if (ci < 0) fail("plan: unknown column '" + ex.str("col") + "'");
+        Column o = in.cols[ci];
+        o.name = name;
+        out.cols.push_back(o);
+      } else {
+        out.cols.push_back(eval_to_column(ex, name, in, nullptr, in.rc()));
+      }
+    }
+    end_stat(st, 0, in.n_max);
+    return out;
+  }
+
+  // ---------------------------------------------------------------- join
+  Batch join(const Json& node, std::vector<RuntimeFilter>& filters) {
+    const std::string type = node.str_or("type", "inner");
+    if (type != "inner") fail("plan: join type '" + type + "' is not supported yet");
+    std::vector<RuntimeFilter> none;
+    Batch build = exec(node.at("build"), none);
+    const std::string& bk = node.str("build_key");
+    const std::string& pk = node.str("probe_key");
+    int kb = build.find(bk);
+    if (kb < 0) fail("plan: build key '" + bk + "' not found");
+    if (!is_intlike(build.cols[kb].lt)) fail("plan: join keys must be integer columns");
+    int64_t nb = count(build);
+    size_t stb = begin_stat("join_build");
+    HashTable ht;
+    uint32_t cap = next_pow2(2 * nb);
+    ht.mask = cap - 1;
+    ht.keys = ar.alloc_n<int64_t>(cap);
+    ht.vals = ar.alloc_n<uint32_t>(cap);
+    launch_fill_i64(ht.keys, kEmptyKey, cap, s);
+    launch_join_build(build.cols[kb].ref(), build.rc(), ht, err + 1, s);
+    launches += 2;
+    end_stat(stb, nb * 8 + (int64_t)cap * 12, nb);
+    // dynamic partition pruning: ship the (small) build key set to the host and let the scan skip files
+    std::vector<RuntimeFilter> down = filters;
+    if (node.bool_or("prune_partitions", false)) {
+      Json kexpr;
+      kexpr.kind = Json::Obj;
+      Json cn; cn.kind = Json::Str; cn.s = bk;
+      kexpr.o.emplace_back("col", cn);
+      Column flat = eval_to_column(kexpr, bk, build, nullptr, build.rc());
+      RuntimeFilter rf;
+      rf.column = pk;
+      if (nb > 0) {
+        const bool is32 = flat.lt.dtype() == DT_I32;
+        std::vector<uint8_t> hk(nb * (is32 ? 4 : 8));
+        std::vector<uint32_t> hv((nb + 31) / 32);
+        NDS_CUDA(cudaMemcpyAsync(hk.data(), flat.data, hk.size(), cudaMemcpyDeviceToHost, s));
+        NDS_CUDA(cudaMemcpyAsync(hv.data(), flat.valid, hv.size() * 4, cudaMemcpyDeviceToHost, s));
+        NDS_CUDA(cudaStreamSynchronize(s));
+        d2h += (int64_t)hk.size() + (int64_t)hv.size() * 4;
+        for (int64_t i = 0; i < nb; ++i)
+          if ((hv[i >> 5] >> (i & 31)) & 1u)
+            rf.keys.insert(is32 ? (int64_t) reinterpret_cast<int32_t*>(hk.data())[i] : reinterpret_cast<int64_t*>(hk.data())[i]);
+      }
+      down.push_back(std::move(rf));
+    }
+    Batch probe = exec(node.at("probe"), down);
+    int kp = probe.find(pk);
+    if (kp < 0) fail("plan: probe key '" + pk + "' not found");
+    if (!is_intlike(probe.cols[kp].lt)) fail("plan: join keys must be integer columns");
+    size_t stp = begin_stat("join_probe");
+    RowCount np = probe.rc();
+    uint32_t* out_p = ar.alloc_n<uint32_t>(np.host);
+    uint32_t* out_b = ar.alloc_n<uint32_t>(np.host);
+    int* cnt = ar.zeros<int>(1);
+    launch_join_probe(probe.cols[kp].ref(), np, ht, out_p, out_b, cnt, s);
+    ++launches;
+    Batch out;
+    out.n_max = np.host;
+    out.n_dev = cnt;
+    RowCount nout{cnt, np.host};
+    MapCache mp, mb;
+    for (const Column& c : probe.cols) {
+      Column o = c;
+      o.rowmap = remap(c.rowmap, out_p, nout, mp);
+      out.cols.push_back(o);
+    }
+    for (const Column& c : build.cols) {
+      if (out.find(c.name) >= 0) continue;
+      Column o = c;
+      o.rowmap = remap(c.rowmap, out_b, nout, mb);
+      out.cols.push_back(o);
+    }
+    end_stat(stp, np.host * (probe.cols[kp].lt.dtype() == DT_I32 ? 4 : 8), np.host);
+    return out;
+  }
+
+  // ---------------------------------------------------------------- aggregate
+  Batch aggregate(const Json& node, std::vector<RuntimeFilter>& filters) {
+    Batch in = exec(node.at("child"), filters);
+    const Json& jkeys = node.at("keys");
+    const Json& jaggs = node.at("aggs");
+    const int nkeys = (int)jkeys.a.size(), naggs = (int)jaggs.a.size();
+    if (nkeys > kMaxGroupKeys) fail("plan: more than " + std::to_string(kMaxGroupKeys) + " group-by keys");
+    if (nkeys == 0) fail("plan: aggregation without group-by keys is not supported yet");
+    int64_t n = count(in);
+    size_t st = begin_stat("aggregate");
+    Blob bb;
+    std::vector<LType> ktypes, atypes;
+    std::vector<int> korigin;
+    for (const Json& k : jkeys.a) {
+      std::vector<Instr> code;
+      int origin = -1;
+      LType t = compile(k.at("expr"), in, bb, code, &origin);
+      bb.add_prog(code, t);
+      ktypes.push_back(t);
+      korigin.push_back(origin);
+    }
+    std::vector<AggSpec> specs;
+    for (const Json& a : jaggs.a) {
+      const std::string& fn = a.str("fn");
+      AggSpec sp;
+      LType ot;
+      if (fn == "count_star") { sp.fn = AGG_COUNT_STAR; sp.prog = -1; ot.kind = LType::INT; }
+      else {
+        std::vector<Instr> code;
+        LType t = compile(a.at("expr"), in, bb, code);
+        sp.prog = bb.add_prog(code, t);
+        if (fn == "count") { sp.fn = AGG_COUNT; ot.kind = LType::INT; }
+        else if (t.kind == LType::STR) fail("plan: " + fn + " over strings is not supported");
+        else if (fn == "sum") {
+          if (t.kind == LType::F64) { sp.fn = AGG_SUM_F; ot.kind = LType::F64; }
+          else {
+            sp.fn = AGG_SUM_I;
+            ot = t;
+            ot.is32 = false;
+            if (t.kind == LType::DECIMAL) ot.precision = std::min(38, t.precision + 10);   // Spark: sum(dec(p,s)) -> dec(p+10,s)
+            else ot.kind = LType::INT;
+          }
+        } else if (fn == "min" || fn == "max") {
+          if (t.kind == LType::F64) fail("plan: min/max over doubles is not supported yet");
+          sp.fn = fn == "min" ? AGG_MIN_I : AGG_MAX_I;
+          ot = t;
+          ot.is32 = false;
+        } else fail("plan: unsupported aggregate function '" + fn + "'");
+      }
+      specs.push_back(sp);
+      atypes.push_back(ot);
+    }
+    Batch out;
+    if (n == 0) {
+      out.n_max = 0;
+      out.n_exact = 0;
+      for (int k = 0; k < nkeys; ++k) { Column c; c.name = jkeys.a[k].str("name"); c.lt = ktypes[k]; if (c.lt.kind == LType::BOOL) c.lt.kind = LType::INT; c.data = ar.alloc(16); out.cols.push_back(c); }
+      for (int a = 0; a < naggs; ++a) { Column c; c.name = jaggs.a[a].str("name"); c.lt = atypes[a]; c.data = ar.alloc(16); out.cols.push_back(c); }
+      end_stat(st, 0, 0);
+      return out;
+    }
+    Blob::Dev dev = bb.upload(ar, s, specs.data(), (int64_t)specs.size() * sizeof(AggSpec));
+    const AggSpec* d_specs = reinterpret_cast<const AggSpec*>(dev.extra);
+    const uint32_t cap = next_pow2(2 * n);
+    uint32_t* slots = ar.zeros<uint32_t>(cap);
+    int64_t* acc = ar.zeros<int64_t>((int64_t)cap * std::max(naggs, 1));
+    int64_t* cnt = ar.zeros<int64_t>((int64_t)cap * std::max(naggs, 1));
+    for (int a = 0; a < naggs; ++a) {
+      if (specs[a].fn == AGG_MIN_I) { launch_fill_i64(acc + (int64_t)a * cap, INT64_MAX, cap, s); ++launches; }
+      if (specs[a].fn == AGG_MAX_I) { launch_fill_i64(acc + (int64_t)a * cap, INT64_MIN, cap, s); ++launches; }
+    }
+    launch_agg_insert(dev.progs, nkeys, d_specs, naggs, dev.ctx, in.rc(), slots, cap - 1, acc, cnt, s);
+    const int64_t vwords = (n + 31) / 32 + 1;
+    uint32_t* rep = ar.alloc_n<uint32_t>(n);
+    int64_t* ovals = ar.alloc_n<int64_t>(n * std::max(naggs, 1));
+    uint32_t* ovalid = ar.zeros<uint32_t>(vwords * std::max(naggs, 1));
+    int* ng = ar.zeros<int>(1);
+    launch_agg_finalize(d_specs, naggs, slots, cap, acc, cnt, rep, ovals, ovalid, n, vwords, ng, s);
+    launches += 2;
+    out.n_max = n;
+    out.n_dev = ng;
+    RowCount nout{ng, n};
+    for (int k = 0; k < nkeys; ++k) out.cols.push_back(eval_to_column(jkeys.a[k].at("expr"), jkeys.a[k].str("name"), in, rep, nout));
+    for (int a = 0; a < naggs; ++a) {
+      Column c;
+      c.name = jaggs.a[a].str("name");
+      c.lt = atypes[a];
+      c.data = ovals + (int64_t)a * n;
+      c.valid = ovalid + (int64_t)a * vwords;
+      out.cols.push_back(c);
+    }
+    end_stat(st, 0, n);
+    return out;
+  }
+
+  // ---------------------------------------------------------------- sort / top-k
+  Batch sort(const Json& node, std::vector<RuntimeFilter>& filters) {
+    Batch in = exec(node.at("child"), filters);
+    const int64_t limit = node.int_or("limit", -1);
+    int64_t n = count(in);
+    size_t st = begin_stat("sort");
+    Batch out;
+    const int64_t m = (limit >= 0 && limit < n) ? limit : n;
+    out.n_max = m;
+    out.n_exact = m;
+    uint32_t* rows = ar.alloc_n<uint32_t>(std::max<int64_t>(m, 1));
+    if (n > 0) {
+      Blob bb;
+      std::vector<SortKey> keys;
+      int B = 0;
+      RowCount rc{nullptr, n};
+      for (const Json& k : node.at("keys").a) {
+        std::vector<Instr> code;
+        LType t = compile(k.at("expr"), in, bb, code);
+        SortKey sk;
+        sk.prog = bb.add_prog(code, t);
+        sk.kind = t.kind == LType::STR ? 2 : (t.kind == LType::F64 ? 1 : 0);
+        sk.desc = k.bool_or("desc", false) ? 1 : 0;
+        sk.nulls_first = k.bool_or("nulls_first", !sk.desc) ? 1 : 0;   // Spark default null ordering
+        sk.width = 8;
+        sk.offset = 0;
+        keys.push_back(sk);
+      }
+      // string keys: padded to the longest value present (one small reduction + sync per string key)
+      bool any_str = false;
+      for (const SortKey& sk : keys) any_str |= sk.kind == 2;
+      if (any_str) {
+        Blob::Dev dev0 = bb.upload(ar, s);
+        int* dmax = ar.zeros<int>((int64_t)keys.size());
+        for (size_t k = 0; k < keys.size(); ++k)
+          if (keys[k].kind == 2) { launch_str_maxlen(dev0.host_progs[keys[k].prog], dev0.ctx, rc, dmax + k, s); ++launches; }
+        std::vector<int> hmax(keys.size());
+        NDS_CUDA(cudaMemcpyAsync(hmax.data(), dmax, keys.size() * 4, cudaMemcpyDeviceToHost, s));
+        NDS_CUDA(cudaStreamSynchronize(s));
+        d2h += (int64_t)keys.size() * 4;
+        for (size_t k = 0; k < keys.size(); ++k)
+          if (keys[k].kind == 2) keys[k].width = hmax[k];
+      }
+      for (SortKey& sk : keys) { sk.offset = B; B += 1 + sk.width; }
+      Blob::Dev dev = bb.upload(ar, s, keys.data(), (int64_t)keys.size() * sizeof(SortKey));
+      uint8_t* keybuf = (uint8_t*)ar.alloc(n * B);
+      launch_encode_keys(dev.progs, reinterpret_cast<const SortKey*>(dev.extra), (int)keys.size(), dev.ctx, rc, keybuf, B, err, s);
+      ++launches;
+      uint32_t* pa = ar.alloc_n<uint32_t>(n);
+      uint32_t* pb = ar.alloc_n<uint32_t>(n);
+      int* which = ar.zeros<int>(B + 2);
+      uint32_t* scratch = ar.alloc_n<uint32_t>((int64_t)radix_sort_grid(n) * 256 + B + 16);
+      int l = 0;
+      launch_radix_sort(keybuf, B, rc, pa, pb, which, scratch, s, &l);
+      launches += l;
+      int* dummy = ar.zeros<int>(1);
+      launch_take_perm(pa, pb, which, B, rc, limit, rows, dummy, s);
+      ++launches;
+    }
+    RowCount rm{nullptr, m};
+    for (size_t c = 0; c < in.cols.size(); ++c) {
+      Json ce;
+      ce.kind = Json::Obj;
+      Json cn; cn.kind = Json::Str; cn.s = in.cols[c].name;
+      ce.o.emplace_back("col", cn);
+      if (m > 0) out.cols.push_back(eval_to_column(ce, in.cols[c].name, in, rows, rm));
+      else { Column e0 = in.cols[c]; e0.rowmap = nullptr; e0.valid = nullptr; e0.data = ar.alloc(16); out.cols.push_back(e0); }
+    }
+    end_stat(st, 0, n);
+    return out;
+  }
+
+  Batch exec(const Json& node, std::vector<RuntimeFilter>& filters) {
+    const std::string& op = node.str("op");
+    if (op == "scan") return scan(node, filters);
+    if (op == "filter") return filter(node, filters);
+    if (op == "project") return project(node, filters);
+    if (op == "join") return join(node, filters);
+    if (op == "aggregate") return aggregate(node, filters);
+    if (op == "sort") return sort(node, filters);
+    fail("plan: unsupported plan node '" + op + "' (no CPU fallback exists)");
+  }
+};
+
+// ------------------------------------------------------------------------------------------ result export
+namespace {
+
+struct ExportPriv {
+  std::vector<void*> bufs;           // malloc'd buffers
+  std::vector<std::string> strings;  // format / name storage
+  std::vector<ArrowSchema*> schema_children;
+  std::vector<ArrowArray*> array_children;
+  std::vector<const void*> bufptrs;
+  std::vector<ArrowSchema> schema_store;
+  std::vector<ArrowArray> array_store;
+  std::vector<std::vector<const void*>> child_bufptrs;
+};
+
+void release_schema(ArrowSchema* s) {
+  if (!s || !s->release) return;
+  for (int64_t i = 0; i < s->n_children; ++i)
+    if (s->children[i] && s->children[i]->release) s->children[i]->release(s->children[i]);
+  if (s->private_data) delete reinterpret_cast<ExportPriv*>(s->private_data);
+  s->release = nullptr;
+}
+void release_schema_child(ArrowSchema* s) { if (s) s->release = nullptr; }
+void release_array(ArrowArray* a) {
+  if (!a || !a->release) return;
+  for (int64_t i = 0; i < a->n_children; ++i)
+    if (a->children[i] && a->children[i]->release) a->children[i]->release(a->children[i]);
+  if (a->private_data) {
+    ExportPriv* p = reinterpret_cast<ExportPriv*>(a->private_data);
+    for (void* b : p->bufs) free(b);
+    delete p;
+  }
+  a->release = nullptr;
+}
+void release_array_child(ArrowArray* a) { if (a) a->release = nullptr; }
+
+}  // namespace
+
+void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_array) {
+  NDS_CUDA(cudaSetDevice(device));
+  const Json* options = plan.find("options");
+  const Json& root = plan.has("root") ? plan.at("root") : plan;
+  cudaEvent_t ev0, ev1;
+  NDS_CUDA(cudaEventCreate(&ev0));
+  NDS_CUDA(cudaEventCreate(&ev1));
+  NDS_CUDA(cudaEventRecord(ev0, stream_));
+  std::vector<OpStat> op_stats;
+  {
+    Exec ex(*this, options);
+    std::vector<RuntimeFilter> none;
+    Batch res = ex.exec(root, none);
+    int64_t n = ex.count(res);
+    // flatten every result column
+    std::vector<Column> flat;
+    RowCount rn{nullptr, n};
+    for (size_t c = 0; c < res.cols.size(); ++c) {
+      if (!res.cols[c].rowmap || n == 0) { flat.push_back(res.cols[c]); continue; }
+      Json ce;
+      ce.kind = Json::Obj;
+      Json cn; cn.kind = Json::Str; cn.s = res.cols[c].name;
+      ce.o.emplace_back("col", cn);
+      flat.push_back(ex.eval_to_column(ce, res.cols[c].name, res, nullptr, rn));
+    }
+    ex.check_err();
+    // ---- device -> host, as Arrow C data
+    ExportPriv* sp = new ExportPriv();
+    ExportPriv* apv = new ExportPriv();
+    const size_t nc = flat.size();
+    sp->schema_store.resize(nc);
+    apv->array_store.resize(nc);
+    apv->child_bufptrs.resize(nc);
+    sp->strings.reserve(2 * nc + 2);
+    for (size_t c = 0; c < nc; ++c) {
+      const Column& col = flat[c];
+      const DType dt = col.lt.dtype();
+      std::string fmt;
+      switch (col.lt.kind) {
+        case LType::INT: case LType::BOOL: fmt = dt == DT_I32 ? "i" : "l"; break;
+        case LType::DATE: fmt = "tdD"; break;
+        case LType::DECIMAL: fmt = "d:" + std::to_string(col.lt.precision) + "," + std::to_string(col.lt.scale); break;
+        case LType::F64: fmt = "g"; break;
+        case LType::STR: fmt = "u"; break;
+      }
+      sp->strings.push_back(fmt);
+      const char* fmt_c = sp->strings.back().c_str();
+      sp->strings.push_back(col.name);
+      const char* name_c = sp->strings.back().c_str();
+      ArrowSchema& cs = sp->schema_store[c];
+      memset(&cs, 0, sizeof cs);
+      cs.format = fmt_c;
+      cs.name = name_c;
+      cs.flags = 2;  // nullable
+      cs.release = release_schema_child;
+      sp->schema_children.push_back(&cs);
+
+      const int64_t vbytes = ((n + 31) / 32) * 4;
+      uint8_t* hvalid = nullptr;
+      int64_t null_count = 0;
+      if (col.valid && n > 0) {
+        hvalid = (uint8_t*)malloc(vbytes + 8);
+        apv->bufs.push_back(hvalid);
+        NDS_CUDA(cudaMemcpyAsync(hvalid, col.valid, vbytes, cudaMemcpyDeviceToHost, stream_));
+        ex.d2h += vbytes;
+      }
+      const int w = dt == DT_I32 ? 4 : 8;
+      uint8_t* hdata = (uint8_t*)malloc(std::max<int64_t>(n * w, 8));
+      apv->bufs.push_back(hdata);
+      if (n > 0) { NDS_CUDA(cudaMemcpyAsync(hdata, col.data, n * w, cudaMemcpyDeviceToHost, stream_)); ex.d2h += n * w; }
+      NDS_CUDA(cudaStreamSynchronize(stream_));
+      if (hvalid) {
+        // clear padding bits, count nulls
+        int64_t valid_cnt = 0;
+        for (int64_t i = 0; i < n; ++i) valid_cnt += (hvalid[i >> 3] >> (i & 7)) & 1;
+        null_count = n - valid_cnt;
+        if (n & 7) hvalid[n >> 3] &= (uint8_t)((1u << (n & 7)) - 1u);
+      }
+      std::vector<const void*>& bp = apv->child_bufptrs[c];
+      ArrowArray& ca = apv->array_store[c];
+      memset(&ca, 0, sizeof ca);
+      ca.length = n;
+      ca.null_count = null_count;
+      ca.release = release_array_child;
+      if (col.lt.kind == LType::DECIMAL) {
+        int64_t* wide = (int64_t*)malloc(std::max<int64_t>(n * 16, 16));
+        apv->bufs.push_back(wide);
+        for (int64_t i = 0; i < n; ++i) {
+          int64_t v = dt == DT_I32 ? (int64_t) reinterpret_cast<int32_t*>(hdata)[i] : reinterpret_cast<int64_t*>(hdata)[i];
+          wide[2 * i] = v;
+          wide[2 * i + 1] = v >> 63;
+        }
+        bp = {hvalid, wide};
+      } else if (col.lt.kind == LType::STR) {
+        const StrView* views = reinterpret_cast<const StrView*>(hdata);
+        int32_t* offs = (int32_t*)malloc((n + 1) * 4 + 8);
+        apv->bufs.push_back(offs);
+        std::vector<int64_t> offs64(n + 1, 0);
+        for (int64_t i = 0; i < n; ++i) {
+          bool ok = !hvalid || ((hvalid[i >> 3] >> (i & 7)) & 1);
+          offs64[i + 1] = offs64[i] + (ok ? (int64_t)(views[i] >> 32) : 0);
+        }
+        if (offs64[n] > 0x7FFFFFFFll) fail("result string column exceeds 2 GiB");
+        for (int64_t i = 0; i <= n; ++i) offs[i] = (int32_t)offs64[i];
+        uint8_t* chars = (uint8_t*)malloc(std::max<int64_t>(offs64[n], 8));
+        apv->bufs.push_back(chars);
+        if (offs64[n] > 0) {
+          Arena& ar = ex.ar;
+          int64_t* doffs = ar.alloc_n<int64_t>(n + 1);
+          uint8_t* dchars = (uint8_t*)ar.alloc(offs64[n]);
+          NDS_CUDA(cudaMemcpyAsync(doffs, offs64.data(), (n + 1) * 8, cudaMemcpyHostToDevice, stream_));
+          launch_copy_str_bytes(reinterpret_cast<const StrView*>(col.data), col.strbase, doffs, n, dchars, stream_);
+          ++ex.launches;
+          NDS_CUDA(cudaMemcpyAsync(chars, dchars, offs64[n], cudaMemcpyDeviceToHost, stream_));
+          NDS_CUDA(cudaStreamSynchronize(stream_));
+          ex.d2h += offs64[n];
+        }
+        bp = {hvalid, offs, chars};
+      } else {
+        bp = {hvalid, hdata};
+      }
+      ca.n_buffers = (int64_t)bp.size();
+      ca.buffers = bp.data();
+      apv->array_children.push_back(&ca);
+    }
+    memset(out_schema, 0, sizeof *out_schema);
+    out_schema->format = "+s";
+    out_schema->name = "";
+    out_schema->n_children = (int64_t)nc;
+    out_schema->children = sp->schema_children.data();
+    out_schema->release = release_schema;
+    out_schema->private_data = sp;
+    memset(out_array, 0, sizeof *out_array);
+    apv->bufptrs = {nullptr};
+    out_array->length = n;
+    out_array->n_buffers = 1;
+    out_array->buffers = apv->bufptrs.data();
+    out_array->n_children = (int64_t)nc;
+    out_array->children = apv->array_children.data();
+    out_array->release = release_array;
+    out_array->private_data = apv;
+
+    NDS_CUDA(cudaEventRecord(ev1, stream_));
+    NDS_CUDA(cudaStreamSynchronize(stream_));
+    launches_ = ex.launches;
+    h2d_bytes_ = ex.h2d;
+    d2h_bytes_ = ex.d2h;
+    op_stats = std::move(ex.stats);
+  }
+  float ms = 0;
+  cudaEventElapsedTime(&ms, ev0, ev1);
+  exec_ms_ = ms;
+  cudaEventDestroy(ev0);
+  cudaEventDestroy(ev1);
+  for (OpStat& st : op_stats) {
+    if (st.e0 && st.e1) {
+      float t = 0;
+      if (cudaEventElapsedTime(&t, st.e0, st.e1) == cudaSuccess) st.ms = t;
+      else cudaGetLastError();
+    }
+    if (st.e0) cudaEventDestroy(st.e0);
+    if (st.e1) cudaEventDestroy(st.e1);
+    st.e0 = st.e1 = nullptr;
+  }
+  stats_ = std::move(op_stats);
+}
+
+std::string Engine::stats_json() const {
+  std::string s = "{\"launches\":" + std::to_string(launches_) + ",\"device_ms\":" + std::to_string(exec_ms_) +
+                  ",\"h2d_bytes\":" + std::to_string(h2d_bytes_) + ",\"d2h_bytes\":" + std::to_string(d2h_bytes_) + ",\"ops\":[";
+  for (size_t i = 0; i < stats_.size(); ++i) {
+    if (i) s += ",";
+    s += "{\"op\":\"" + json_escape(stats_[i].op) + "\",\"ms\":" + std::to_string(stats_[i].ms) + ",\"bytes\":" +
+         std::to_string(stats_[i].bytes) + ",\"rows\":" + std::to_string(stats_[i].rows) + "}";
+  }
+  s += "]}";
+  return s;
+}
+
+Engine::Engine(const Json& cfg) {
+  device = (int)cfg.int_or("device", 0);
+  resident_ = cfg.bool_or("resident", true);
+  keep_host_ = cfg.bool_or("keep_host", false);
+  rank = (int)cfg.int_or("rank", 0);
+  world = (int)cfg.int_or("world", 1);
+  if (world < 1 || rank < 0 || rank >= world) fail("engine config: bad rank/world");
+  int ndev = 0;
+  cudaError_t ce = cudaGetDeviceCount(&ndev);
+  if (ce != cudaSuccess || ndev == 0)
+    fail(std::string("no CUDA device is available (") + cudaGetErrorString(ce) + "); the NDS B200 engine has no CPU path");
+  if (device >= ndev) fail("engine config: device " + std::to_string(device) + " does not exist");
+  NDS_CUDA(cudaSetDevice(device));
+  NDS_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+  cudaMemPool_t pool;
+  NDS_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
+  uint64_t thr = UINT64_MAX;
+  NDS_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+}
+
+Engine::~Engine() {
+  cudaSetDevice(device);
+  std::vector<std::string> names;
+  for (auto& kv : tables_) names.push_back(kv.first);
+  for (auto& n : names) drop_table(n);
+  if (stream_) cudaStreamDestroy(stream_);
+}
+
+}  // namespace nds

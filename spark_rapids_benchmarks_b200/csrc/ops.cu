@@ -1,0 +1,481 @@
+// Operator kernels: fused filter/project, hash-join build/probe, hash group-by, key encoding and
+// LSD radix sort.  All are HBM-bound integer/byte kernels (no tensor-core work on this path).
+// Row counts may live on the device (RowCount::dev) so that a chain of operators needs no host sync.
+//
+// Spark operators these replace (none of them is in /root/reference; the reference hands SQL text to
+// Spark at /root/reference/nds/nds_power.py:130): FilterExec/ProjectExec, BroadcastHashJoinExec,
+// HashAggregateExec, TakeOrderedAndProjectExec.
+#include "ops.cuh"
+#include "common.h"
+
+namespace nds {
+
+namespace {
+
+constexpr int kThreads = 256;
+
+inline int grid_for(int64_t n, int per_block = kThreads, int max_blocks = 148 * 8) {
+  int64_t g = (n + per_block - 1) / per_block;
+  if (g < 1) g = 1;
+  if (g > max_blocks) g = max_blocks;
+  return (int)g;
+}
+
+__device__ __forceinline__ int64_t row_count(const int* dev, int64_t host) {
+  if (dev) { int64_t d = *dev; return d < host ? d : host; }
+  return host;
+}
+
+__device__ __forceinline__ uint32_t lanemask_lt() {
+  uint32_t m;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+  return m;
+}
+
+// warp-aggregated append: returns the output position for lanes with keep == true
+__device__ __forceinline__ int warp_append(bool keep, int* counter) {
+  uint32_t m = __ballot_sync(0xFFFFFFFFu, keep);
+  int base = 0;
+  int lane = threadIdx.x & 31;
+  if (m) {
+    if (lane == (__ffs(m) - 1)) base = atomicAdd(counter, __popc(m));
+    base = __shfl_sync(0xFFFFFFFFu, base, __ffs(m) - 1);
+  }
+  return base + __popc(m & lanemask_lt());
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ filter
+__global__ void __launch_bounds__(kThreads)
+filter_kernel(Prog p, OpCtx c, const int* n_dev, int64_t n_host, uint32_t* __restrict__ out_sel, int* out_count) {
+  const int64_t n = row_count(n_dev, n_host);
+  const int64_t nround = (n + 31) & ~int64_t(31);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nround; i += (int64_t)gridDim.x * blockDim.x) {
+    bool keep = false;
+    if (i < n) {
+      Val v = eval_program(p.code, p.n, c.cols, c.lit, i);
+      keep = v.ok && v.v != 0;
+    }
+    int pos = warp_append(keep, out_count);
+    if (keep) out_sel[pos] = (uint32_t)i;
+  }
+}
+
+void launch_filter(Prog p, OpCtx c, RowCount n, uint32_t* out_sel, int* out_count, cudaStream_t s) {
+  filter_kernel<<<grid_for(n.host), kThreads, 0, s>>>(p, c, n.dev, n.host, out_sel, out_count);
+  NDS_CUDA(cudaGetLastError());
+}
+
+// ------------------------------------------------------------------ project
+// Evaluates one expression for every row (or for rows[i] when given) into a flat column.
+__global__ void __launch_bounds__(kThreads)
+project_kernel(Prog p, OpCtx c, const int* n_dev, int64_t n_host, const uint32_t* __restrict__ rows, void* out,
+               uint32_t* __restrict__ out_valid, int out_dtype, const uint8_t* str_out_base, int* err) {
+  const int64_t n = row_count(n_dev, n_host);
+  const int64_t nround = (n + 31) & ~int64_t(31);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nround; i += (int64_t)gridDim.x * blockDim.x) {
+    Val v;
+    v.ok = false; v.v = 0; v.len = 0;
+    if (i < n) v = eval_program(p.code, p.n, c.cols, c.lit, rows ? (int64_t)rows[i] : i);
+    uint32_t m = __ballot_sync(0xFFFFFFFFu, v.ok);
+    if (out_valid && (threadIdx.x & 31) == 0) out_valid[i >> 5] = m;
+    if (i < n) {
+      if (out_dtype == DT_I32) reinterpret_cast<int32_t*>(out)[i] = v.ok ? (int32_t)v.v : 0;
+      else if (out_dtype == DT_STR) {
+        StrView sv = 0;
+        if (v.ok) {
+          int64_t off = (int64_t)((const uint8_t*)(uintptr_t)v.v - str_out_base);
+          if (off < 0 || off > 0xFFFFFFFFll) { if (err) atomicExch(err, 11); off = 0; }
+          sv = ((uint64_t)v.len << 32) | (uint64_t)(uint32_t)off;
+        }
+        reinterpret_cast<StrView*>(out)[i] = sv;
+      } else reinterpret_cast<int64_t*>(out)[i] = v.ok ? v.v : 0;
+    }
+  }
+}
+
+void launch_project(Prog p, OpCtx c, RowCount n, const uint32_t* rows, void* out, uint32_t* out_valid, int out_dtype,
+                    const uint8_t* str_out_base, int* err, cudaStream_t s) {
+  project_kernel<<<grid_for(n.host), kThreads, 0, s>>>(p, c, n.dev, n.host, rows, out, out_valid, out_dtype, str_out_base, err);
+  NDS_CUDA(cudaGetLastError());
+}
+
+// ------------------------------------------------------------------ small utilities
+__global__ void compose_kernel(const uint32_t* __restrict__ inner, const uint32_t* __restrict__ idx, const int* n_dev,
+                               int64_t n_host, uint32_t* __restrict__ out) {
+  const int64_t n = row_count(n_dev, n_host);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = inner[idx[i]];
+}
+void launch_compose(const uint32_t* inner, const uint32_t* idx, RowCount n, uint32_t* out, cudaStream_t s) {
+  compose_kernel<<<grid_for(n.host), kThreads, 0, s>>>(inner, idx, n.dev, n.host, out);
+  NDS_CUDA(cudaGetLastError());
+}
+
+__global__ void fill_i64_kernel(int64_t* p, int64_t v, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
+}
+void launch_fill_i64(int64_t* p, int64_t v, int64_t n, cudaStream_t s) {
+  if (n <= 0) return;
+  fill_i64_kernel<<<grid_for(n), kThreads, 0, s>>>(p, v, n);
+  NDS_CUDA(cudaGetLastError());
+}
+
+// ------------------------------------------------------------------ hash join
+// Open addressing, linear probing, 64-bit keys + 32-bit payload (the build-side batch row).
+// Build keys must be unique (FK -> PK joins); a duplicate raises flag bit 0.
+__global__ void __launch_bounds__(kThreads)
+join_build_kernel(ColRef key, const int* n_dev, int64_t n_host, HashTable ht, int* flags) {
+  const int64_t n = row_count(n_dev, n_host);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    Val k = load_col(key, i);
+    if (!k.ok) continue;                       // NULL keys never match an equi-join
+    if (k.v == kEmptyKey) { atomicOr(flags, 2); continue; }
+    uint32_t s = (uint32_t)mix64((uint64_t)k.v) & ht.mask;
+    for (;;) {
+      unsigned long long prev = atomicCAS(reinterpret_cast<unsigned long long*>(&ht.keys[s]),
+                                          (unsigned long long)kEmptyKey, (unsigned long long)k.v);
+      if ((int64_t)prev == kEmptyKey) { ht.vals[s] = (uint32_t)i; break; }
+      if ((int64_t)prev == k.v) { atomicOr(flags, 1); break; }
+      s = (s + 1) & ht.mask;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+join_probe_kernel(ColRef key, const int* n_dev, int64_t n_host, HashTable ht, uint32_t* __restrict__ out_probe,
+                  uint32_t* __restrict__ out_build, int* out_count) {
+  const int64_t n = row_count(n_dev, n_host);
+  const int64_t nround = (n + 31) & ~int64_t(31);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nround; i += (int64_t)gridDim.x * blockDim.x) {
+    bool hit = false;
+    uint32_t b = 0;
+    if (i < n) {
+      Val k = load_col(key, i);
+      if (k.ok && k.v != kEmptyKey) {
+        uint32_t s = (uint32_t)mix64((uint64_t)k.v) & ht.mask;
+        for (;;) {
+          int64_t cur = ht.keys[s];
+          if (cur == k.v) { hit = true; b = ht.vals[s]; break; }
+          if (cur == kEmptyKey) break;
+          s = (s + 1) & ht.mask;
+        }
+      }
+    }
+    int pos = warp_append(hit, out_count);
+    if (hit) { out_probe[pos] = (uint32_t)i; out_build[pos] = b; }
+  }
+}
+
+void launch_join_build(ColRef key, RowCount n, HashTable ht, int* flags, cudaStream_t s) {
+  join_build_kernel<<<grid_for(n.host), kThreads, 0, s>>>(key, n.dev, n.host, ht, flags);
+  NDS_CUDA(cudaGetLastError());
+}
+void launch_join_probe(ColRef key, RowCount n, HashTable ht, uint32_t* out_probe, uint32_t* out_build, int* out_count,
+                       cudaStream_t s) {
+  join_probe_kernel<<<grid_for(n.host), kThreads, 0, s>>>(key, n.dev, n.host, ht, out_probe, out_build, out_count);
+  NDS_CUDA(cudaGetLastError());
+}
+
+// ------------------------------------------------------------------ hash group-by
+// slots[s] = representative batch row + 1 (0 = empty). Key equality is decided by re-evaluating the key
+// expressions at the representative row, so no key columns are stored in the table.
+__device__ __forceinline__ bool val_equal(const Val& a, const Val& b, int kind) {
+  if (a.ok != b.ok) return false;
+  if (!a.ok) return true;
+  if (kind == 2) {
+    if (a.len != b.len) return false;
+    const uint8_t* x = (const uint8_t*)(uintptr_t)a.v;
+    const uint8_t* y = (const uint8_t*)(uintptr_t)b.v;
+    for (uint32_t i = 0; i < a.len; ++i)
+      if (x[i] != y[i]) return false;
+    return true;
+  }
+  return a.v == b.v;
+}
+
+__global__ void __launch_bounds__(kThreads)
+agg_insert_kernel(const Prog* __restrict__ progs, int nkeys, const AggSpec* __restrict__ aggs, int naggs, OpCtx c,
+                  const int* n_dev, int64_t n_host, uint32_t* slots, uint32_t mask, int64_t* acc, int64_t* cnt) {
+  const int64_t n = row_count(n_dev, n_host);
+  const uint64_t cap = (uint64_t)mask + 1;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    Val mine[kMaxGroupKeys];
+    uint64_t h = 0x9E3779B97F4A7C15ULL;
+    for (int k = 0; k < nkeys; ++k) {
+      mine[k] = eval_program(progs[k].code, progs[k].n, c.cols, c.lit, i);
+      uint64_t hv = !mine[k].ok ? 0x7F4A7C15ULL
+                    : (progs[k].kind == 2 ? hash_bytes((const uint8_t*)(uintptr_t)mine[k].v, mine[k].len) : (uint64_t)mine[k].v);
+      h = mix64(h ^ hv) + 0x9E3779B97F4A7C15ULL * (k + 1);
+    }
+    uint32_t s = (uint32_t)mix64(h) & mask;
+    for (;;) {
+      uint32_t prev = atomicCAS(&slots[s], 0u, (uint32_t)i + 1u);
+      if (prev == 0) break;
+      const int64_t rep = (int64_t)prev - 1;
+      bool same = true;
+      for (int k = 0; k < nkeys && same; ++k) {
+        Val o = eval_program(progs[k].code, progs[k].n, c.cols, c.lit, rep);
+        same = val_equal(mine[k], o, progs[k].kind);
+      }
+      if (same) break;
+      s = (s + 1) & mask;
+    }
+    for (int a = 0; a < naggs; ++a) {
+      const AggSpec sp = aggs[a];
+      if (sp.fn == AGG_COUNT_STAR) { atomicAdd(reinterpret_cast<unsigned long long*>(&cnt[a * cap + s]), 1ull); continue; }
+      Val v = eval_program(progs[sp.prog].code, progs[sp.prog].n, c.cols, c.lit, i);
+      if (!v.ok) continue;
+      atomicAdd(reinterpret_cast<unsigned long long*>(&cnt[a * cap + s]), 1ull);
+      if (sp.fn == AGG_SUM_I) atomicAdd(reinterpret_cast<unsigned long long*>(&acc[a * cap + s]), (unsigned long long)v.v);
+      else if (sp.fn == AGG_MIN_I) atomicMin(reinterpret_cast<long long*>(&acc[a * cap + s]), (long long)v.v);
+      else if (sp.fn == AGG_MAX_I) atomicMax(reinterpret_cast<long long*>(&acc[a * cap + s]), (long long)v.v);
+      else if (sp.fn == AGG_SUM_F) atomicAdd(reinterpret_cast<double*>(&acc[a * cap + s]), __longlong_as_double(v.v));
+    }
+  }
+}
+
+// Compacts occupied slots into group rows. out_vals[a * out_stride + g], out_valid[a * valid_stride_words + g/32].
+__global__ void __launch_bounds__(kThreads)
+agg_finalize_kernel(const AggSpec* __restrict__ aggs, int naggs, const uint32_t* __restrict__ slots, uint32_t cap,
+                    const int64_t* __restrict__ acc, const int64_t* __restrict__ cnt, uint32_t* __restrict__ rep_out,
+                    int64_t* __restrict__ out_vals, uint32_t* out_valid, int64_t out_stride, int64_t valid_stride_words,
+                    int* ngroups) {
+  const uint32_t capround = (cap + 31u) & ~31u;
+  for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < capround; s += gridDim.x * blockDim.x) {
+    uint32_t rep = s < cap ? slots[s] : 0u;
+    int g = warp_append(rep != 0, ngroups);
+    if (!rep) continue;
+    rep_out[g] = rep - 1;
+    for (int a = 0; a < naggs; ++a) {
+      const int fn = aggs[a].fn;
+      int64_t c = cnt[(uint64_t)a * cap + s];
+      int64_t v = (fn == AGG_COUNT || fn == AGG_COUNT_STAR) ? c : acc[(uint64_t)a * cap + s];
+      bool ok = (fn == AGG_COUNT || fn == AGG_COUNT_STAR) ? true : c > 0;
+      out_vals[a * out_stride + g] = ok ? v : 0;
+      if (ok) atomicOr(&out_valid[a * valid_stride_words + (g >> 5)], 1u << (g & 31));
+    }
+  }
+}
+
+void launch_agg_insert(const Prog* progs, int nkeys, const AggSpec* aggs, int naggs, OpCtx c, RowCount n, uint32_t* slots,
+                       uint32_t mask, int64_t* acc, int64_t* cnt, cudaStream_t s) {
+  agg_insert_kernel<<<grid_for(n.host), kThreads, 0, s>>>(progs, nkeys, aggs, naggs, c, n.dev, n.host, slots, mask, acc, cnt);
+  NDS_CUDA(cudaGetLastError());
+}
+void launch_agg_finalize(const AggSpec* aggs, int naggs, const uint32_t* slots, uint32_t cap, const int64_t* acc,
+                         const int64_t* cnt, uint32_t* rep_out, int64_t* out_vals, uint32_t* out_valid, int64_t out_stride,
+                         int64_t valid_stride_words, int* ngroups, cudaStream_t s) {
+  agg_finalize_kernel<<<grid_for(cap), kThreads, 0, s>>>(aggs, naggs, slots, cap, acc, cnt, rep_out, out_vals, out_valid,
+                                                         out_stride, valid_stride_words, ngroups);
+  NDS_CUDA(cudaGetLastError());
+}
+
+// ------------------------------------------------------------------ sort: key encoding
+__global__ void str_maxlen_kernel(Prog p, OpCtx c, const int* n_dev, int64_t n_host, int* out_max) {
+  const int64_t n = row_count(n_dev, n_host);
+  int m = 0;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    Val v = eval_program(p.code, p.n, c.cols, c.lit, i);
+    if (v.ok && (int)v.len > m) m = (int)v.len;
+  }
+  for (int d = 16; d; d >>= 1) m = max(m, __shfl_xor_sync(0xFFFFFFFFu, m, d));
+  if ((threadIdx.x & 31) == 0 && m) atomicMax(out_max, m);
+}
+void launch_str_maxlen(Prog p, OpCtx c, RowCount n, int* out_max, cudaStream_t s) {
+  str_maxlen_kernel<<<grid_for(n.host), kThreads, 0, s>>>(p, c, n.dev, n.host, out_max);
+  NDS_CUDA(cudaGetLastError());
+}
+
+// Order-preserving big-endian byte strings: per key [flag][payload]. Spark's default null ordering
+// (NULLS FIRST ascending, NULLS LAST descending) arrives as nulls_first; desc inverts the payload.
+__global__ void __launch_bounds__(kThreads)
+encode_keys_kernel(const Prog* __restrict__ progs, const SortKey* __restrict__ keys, int nk, OpCtx c, const int* n_dev,
+                   int64_t n_host, uint8_t* __restrict__ keybuf, int B, int* err) {
+  const int64_t n = row_count(n_dev, n_host);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    uint8_t* row = keybuf + i * B;
+    for (int k = 0; k < nk; ++k) {
+      const SortKey sk = keys[k];
+      Val v = eval_program(progs[sk.prog].code, progs[sk.prog].n, c.cols, c.lit, i);
+      uint8_t* o = row + sk.offset;
+      o[0] = sk.nulls_first ? (v.ok ? 1 : 0) : (v.ok ? 0 : 1);
+      const uint8_t inv = sk.desc ? 0xFF : 0x00;
+      if (!v.ok) {
+        for (int b = 0; b < sk.width; ++b) o[1 + b] = 0;
+      } else if (sk.kind == 2) {
+        const uint8_t* p = (const uint8_t*)(uintptr_t)v.v;
+        if ((int)v.len > sk.width) { if (err) atomicExch(err, 12); }
+        for (int b = 0; b < sk.width; ++b) o[1 + b] = (b < (int)v.len ? p[b] : 0) ^ inv;
+      } else {
+        uint64_t u = (uint64_t)v.v;
+        if (sk.kind == 1) u = (u >> 63) ? ~u : (u | 0x8000000000000000ULL);
+        else u ^= 0x8000000000000000ULL;
+        for (int b = 0; b < 8; ++b) o[1 + b] = (uint8_t)(u >> (56 - 8 * b)) ^ inv;
+      }
+    }
+  }
+}
+void launch_encode_keys(const Prog* progs, const SortKey* keys, int nk, OpCtx c, RowCount n, uint8_t* keybuf, int B, int* err,
+                        cudaStream_t s) {
+  encode_keys_kernel<<<grid_for(n.host), kThreads, 0, s>>>(progs, keys, nk, c, n.dev, n.host, keybuf, B, err);
+  NDS_CUDA(cudaGetLastError());
+}
+
+// ------------------------------------------------------------------ sort: LSD radix, 8-bit digits
+// Pass p (p = 0 is the least significant byte B-1) reads the live permutation buffer which[p], and, unless all rows
+// share the digit (skip), scatters into the other buffer; which[p+1] records the result. Three kernels per
+// pass: per-block histograms, one-block scan, stable scatter.
+constexpr int kSortThreads = 256;
+constexpr int kSortTile = 4096;     // rows per block
+
+int radix_sort_grid(int64_t n_max) {
+  int64_t g = (n_max + kSortTile - 1) / kSortTile;
+  return (int)(g < 1 ? 1 : g);
+}
+
+__global__ void radix_init_kernel(const int* n_dev, int64_t n_host, uint32_t* perm_a, int* which) {
+  const int64_t n = row_count(n_dev, n_host);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) perm_a[i] = (uint32_t)i;
+  if (blockIdx.x == 0 && threadIdx.x == 0) which[0] = 0;
+}
+
+__global__ void __launch_bounds__(kSortThreads)
+radix_hist_kernel(const uint8_t* __restrict__ keybuf, int B, int byte, const int* n_dev, int64_t n_host,
+                  const uint32_t* perm_a, const uint32_t* perm_b, const int* which, int pass, uint32_t* __restrict__ block_hist) {
+  __shared__ uint32_t h[256];
+  const int64_t n = row_count(n_dev, n_host);
+  const uint32_t* perm = which[pass] ? perm_b : perm_a;
+  h[threadIdx.x] = 0;
+  __syncthreads();
+  const int64_t lo = (int64_t)blockIdx.x * kSortTile;
+  const int64_t hi = min(lo + (int64_t)kSortTile, n);
+  for (int64_t i = lo + threadIdx.x; i < hi; i += kSortThreads) atomicAdd(&h[keybuf[(int64_t)perm[i] * B + byte]], 1u);
+  __syncthreads();
+  block_hist[(int64_t)blockIdx.x * 256 + threadIdx.x] = h[threadIdx.x];
+}
+
+// one block of 256 threads: thread d owns digit d
+__global__ void __launch_bounds__(256)
+radix_scan_kernel(uint32_t* block_hist, int nblocks, const int* n_dev, int64_t n_host, int* which, int pass, uint32_t* skip_flag) {
+  __shared__ uint32_t tot[256];
+  __shared__ int s_skip;
+  const int64_t n = row_count(n_dev, n_host);
+  const int d = threadIdx.x;
+  if (d == 0) s_skip = 0;
+  __syncthreads();
+  uint32_t sum = 0;
+  for (int g = 0; g < nblocks; ++g) sum += block_hist[(int64_t)g * 256 + d];
+  tot[d] = sum;
+  if ((int64_t)sum == n) s_skip = 1;      // every row has this digit (covers n == 0 via d == any)
+  __syncthreads();
+  // exclusive scan over digits (256 values, serial per thread is fine: 256 adds)
+  uint32_t base = 0;
+  for (int k = 0; k < d; ++k) base += tot[k];
+  uint32_t run = base;
+  for (int g = 0; g < nblocks; ++g) {
+    uint32_t c = block_hist[(int64_t)g * 256 + d];
+    block_hist[(int64_t)g * 256 + d] = run;
+    run += c;
+  }
+  if (d == 0) {
+    int skip = s_skip || n <= 1;
+    skip_flag[pass] = skip;
+    which[pass + 1] = which[pass] ^ (skip ? 0 : 1);
+  }
+}
+
+__global__ void __launch_bounds__(kSortThreads)
+radix_scatter_kernel(const uint8_t* __restrict__ keybuf, int B, int byte, const int* n_dev, int64_t n_host, uint32_t* perm_a,
+                     uint32_t* perm_b, const int* which, int pass, const uint32_t* __restrict__ block_off,
+                     const uint32_t* __restrict__ skip_flag) {
+  if (skip_flag[pass]) return;
+  __shared__ uint32_t base[256];
+  __shared__ uint16_t wcnt[kSortThreads / 32][256];
+  const int64_t n = row_count(n_dev, n_host);
+  const uint32_t* src = which[pass] ? perm_b : perm_a;
+  uint32_t* dst = which[pass] ? perm_a : perm_b;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  base[tid] = block_off[(int64_t)blockIdx.x * 256 + tid];
+  const int64_t lo = (int64_t)blockIdx.x * kSortTile;
+  const int64_t hi = min(lo + (int64_t)kSortTile, n);
+  for (int64_t c0 = lo; c0 < hi; c0 += kSortThreads) {
+    for (int k = tid; k < (kSortThreads / 32) * 256; k += kSortThreads) (&wcnt[0][0])[k] = 0;
+    __syncthreads();
+    const int64_t i = c0 + tid;
+    const bool act = i < hi;
+    uint32_t row = act ? src[i] : 0u;
+    int d = act ? keybuf[(int64_t)row * B + byte] : 256 + (tid & 31);   // inactive lanes get unique pseudo-digits
+    uint32_t m = __match_any_sync(0xFFFFFFFFu, d);
+    uint32_t rank = __popc(m & lanemask_lt());
+    if (act && rank == 0) wcnt[warp][d] = (uint16_t)__popc(m);
+    __syncthreads();
+    if (act) {
+      uint32_t pos = base[d] + rank;
+      for (int w = 0; w < warp; ++w) pos += wcnt[w][d];
+      dst[pos] = row;
+    }
+    __syncthreads();
+    uint32_t add = 0;
+    for (int w = 0; w < kSortThreads / 32; ++w) add += wcnt[w][tid];
+    base[tid] += add;
+    __syncthreads();
+  }
+}
+
+void launch_radix_sort(const uint8_t* keybuf, int B, RowCount n, uint32_t* perm_a, uint32_t* perm_b, int* which,
+                       uint32_t* scratch, cudaStream_t s, int* launches) {
+  const int G = radix_sort_grid(n.host);
+  uint32_t* block_hist = scratch;
+  uint32_t* skip_flag = scratch + (int64_t)G * 256;
+  radix_init_kernel<<<grid_for(n.host), kThreads, 0, s>>>(n.dev, n.host, perm_a, which);
+  NDS_CUDA(cudaGetLastError());
+  *launches += 1;
+  for (int pass = 0; pass < B; ++pass) {
+    const int byte = B - 1 - pass;
+    radix_hist_kernel<<<G, kSortThreads, 0, s>>>(keybuf, B, byte, n.dev, n.host, perm_a, perm_b, which, pass, block_hist);
+    radix_scan_kernel<<<1, 256, 0, s>>>(block_hist, G, n.dev, n.host, which, pass, skip_flag);
+    radix_scatter_kernel<<<G, kSortThreads, 0, s>>>(keybuf, B, byte, n.dev, n.host, perm_a, perm_b, which, pass, block_hist,
+                                                    skip_flag);
+    *launches += 3;
+  }
+  NDS_CUDA(cudaGetLastError());
+}
+
+__global__ void take_perm_kernel(const uint32_t* perm_a, const uint32_t* perm_b, const int* which, int B, const int* n_dev,
+                                 int64_t n_host, int64_t limit, uint32_t* out_rows, int* out_count) {
+  const int64_t n = row_count(n_dev, n_host);
+  const int64_t m = (limit >= 0 && limit < n) ? limit : n;
+  const uint32_t* perm = which[B] ? perm_b : perm_a;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < m; i += (int64_t)gridDim.x * blockDim.x) out_rows[i] = perm[i];
+  if (blockIdx.x == 0 && threadIdx.x == 0) *out_count = (int)m;
+}
+void launch_take_perm(const uint32_t* perm_a, const uint32_t* perm_b, const int* which, int B, RowCount n, int64_t limit,
+                      uint32_t* out_rows, int* out_count, cudaStream_t s) {
+  int64_t m = (limit >= 0 && limit < n.host) ? limit : n.host;
+  take_perm_kernel<<<grid_for(m), kThreads, 0, s>>>(perm_a, perm_b, which, B, n.dev, n.host, limit, out_rows, out_count);
+  NDS_CUDA(cudaGetLastError());
+}
+
+// ------------------------------------------------------------------ result strings
+__global__ void copy_str_bytes_kernel(const StrView* __restrict__ views, const uint8_t* __restrict__ base,
+                                      const int64_t* __restrict__ offsets, int64_t n, uint8_t* __restrict__ out) {
+  // one warp per string
+  const int lane = threadIdx.x & 31;
+  for (int64_t i = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5; i < n; i += ((int64_t)gridDim.x * blockDim.x) >> 5) {
+    StrView v = views[i];
+    const uint8_t* p = base + (uint32_t)v;
+    uint32_t len = (uint32_t)(v >> 32);
+    if ((int64_t)len != offsets[i + 1] - offsets[i]) continue;   // null rows have length 0 in offsets
+    for (uint32_t b = lane; b < len; b += 32) out[offsets[i] + b] = p[b];
+  }
+}
+void launch_copy_str_bytes(const StrView* views, const uint8_t* base, const int64_t* offsets, int64_t n, uint8_t* out,
+                           cudaStream_t s) {
+  if (n <= 0) return;
+  copy_str_bytes_kernel<<<grid_for(n * 32), kThreads, 0, s>>>(views, base, offsets, n, out);
+  NDS_CUDA(cudaGetLastError());
+}
+
+}  // namespace nds

@@ -1,0 +1,81 @@
+// Launcher declarations for the operator kernels (ops.cu, decode.cu).
+#pragma once
+#include "device_types.h"
+#include "expr.cuh"
+#include <cuda_runtime.h>
+
+namespace nds {
+
+struct Prog {            // one compiled expression, resident in device memory
+  const Instr* code;
+  int32_t n;
+  int32_t kind;          // 0 integer-like, 1 double, 2 string
+};
+
+struct OpCtx {
+  const ColRef* cols;
+  const uint8_t* lit;
+};
+
+struct RowCount {        // rows of a batch: device-side count if known only there
+  const int* dev;        // may be null
+  int64_t host;          // exact count when dev == null, else an upper bound
+};
+
+constexpr int64_t kEmptyKey = INT64_MIN;
+
+struct HashTable {
+  int64_t* keys;
+  uint32_t* vals;
+  uint32_t mask;
+};
+
+enum AggFn : int32_t { AGG_SUM_I = 0, AGG_COUNT = 1, AGG_COUNT_STAR = 2, AGG_MIN_I = 3, AGG_MAX_I = 4, AGG_SUM_F = 5 };
+struct AggSpec {
+  int32_t fn;
+  int32_t prog;          // index into the program array, -1 for count(*)
+};
+constexpr int kMaxGroupKeys = 8;
+
+struct SortKey {
+  int32_t prog;
+  int32_t kind;          // 0 int, 1 double, 2 string
+  int32_t desc;
+  int32_t nulls_first;
+  int32_t width;         // payload bytes (8 for numbers, padded length for strings)
+  int32_t offset;        // byte offset of this key (flag byte first) inside the encoded row
+};
+
+// decode.cu
+void launch_decode_pages(const PageTask* d_tasks, int npages, int* d_err, cudaStream_t s);
+void launch_fill_segments(const int64_t* d_seg_start, const int64_t* d_seg_val, int nseg, int32_t* out, cudaStream_t s);
+
+// ops.cu
+void launch_filter(Prog p, OpCtx c, RowCount n, uint32_t* out_sel, int* out_count, cudaStream_t s);
+void launch_project(Prog p, OpCtx c, RowCount n, const uint32_t* rows, void* out, uint32_t* out_valid, int out_dtype,
+                    const uint8_t* str_out_base, int* err, cudaStream_t s);
+void launch_compose(const uint32_t* inner, const uint32_t* idx, RowCount n, uint32_t* out, cudaStream_t s);
+void launch_fill_i64(int64_t* p, int64_t v, int64_t n, cudaStream_t s);
+void launch_join_build(ColRef key, RowCount n, HashTable ht, int* flags, cudaStream_t s);
+void launch_join_probe(ColRef key, RowCount n, HashTable ht, uint32_t* out_probe, uint32_t* out_build, int* out_count,
+                       cudaStream_t s);
+void launch_agg_insert(const Prog* progs, int nkeys, const AggSpec* aggs, int naggs, OpCtx c, RowCount n, uint32_t* slots,
+                       uint32_t mask, int64_t* acc, int64_t* cnt, cudaStream_t s);
+void launch_agg_finalize(const AggSpec* aggs, int naggs, const uint32_t* slots, uint32_t cap, const int64_t* acc,
+                         const int64_t* cnt, uint32_t* rep_out, int64_t* out_vals, uint32_t* out_valid, int64_t out_stride,
+                         int64_t valid_stride_words, int* ngroups, cudaStream_t s);
+void launch_str_maxlen(Prog p, OpCtx c, RowCount n, int* out_max, cudaStream_t s);
+void launch_encode_keys(const Prog* progs, const SortKey* keys, int nk, OpCtx c, RowCount n, uint8_t* keybuf, int B, int* err,
+                        cudaStream_t s);
+// Stable LSD radix sort of row ids by B-byte big-endian keys. perm_a/perm_b: ping-pong buffers of n_max
+// entries; *which (device int array of B+1 entries, which[0] = 0) tracks the live buffer; on return the sorted
+// permutation is in (which[B] ? perm_b : perm_a). scratch: (grid*256 + 512) uint32.
+int radix_sort_grid(int64_t n_max);
+void launch_radix_sort(const uint8_t* keybuf, int B, RowCount n, uint32_t* perm_a, uint32_t* perm_b, int* which,
+                       uint32_t* scratch, cudaStream_t s, int* launches);
+void launch_take_perm(const uint32_t* perm_a, const uint32_t* perm_b, const int* which, int B, RowCount n, int64_t limit,
+                      uint32_t* out_rows, int* out_count, cudaStream_t s);
+void launch_copy_str_bytes(const StrView* views, const uint8_t* base, const int64_t* offsets, int64_t n, uint8_t* out,
+                           cudaStream_t s);
+
+}  // namespace nds

@@ -1,0 +1,410 @@
+// Table registration: directory walk (hive partitions), footer + page-header parse, staging of the
+// encoded column chunks, upload to HBM.
+//
+// Mirrors what `setup_tables` makes Spark do per table (/root/reference/nds/nds_power.py:79-106:
+// read.format(fmt).load(prefix/table).createOrReplaceTempView(table)) for the layout written by
+// `store()` (/root/reference/nds/nds_transcode.py:131-150): fact tables as <col>=<value>/ directories with
+// the partition column only in the directory name, dimension tables as one file.
+#include <algorithm>
+#include <dirent.h>
+#include <fcntl.h>
+#include <sys/stat.h>
+#include <unistd.h>
+#include "engine.h"
+
+namespace nds {
+
+std::string LType::str() const {
+  switch (kind) {
+    case INT: return is32 ? "int32" : "int64";
+    case DATE: return "date";
+    case DECIMAL: return "decimal(" + std::to_string(precision) + "," + std::to_string(scale) + ")";
+    case F64: return "double";
+    case STR: return "string";
+    case BOOL: return "bool";
+  }
+  return "?";
+}
+
+namespace {
+
+const char* kHiveNull = "__HIVE_DEFAULT_PARTITION__";
+
+bool ends_with(const std::string& s, const std::string& suf) {
+  return s.size() >= suf.size() && !s.compare(s.size() - suf.size(), suf.size(), suf);
+}
+
+std::vector<std::string> list_dir(const std::string& path) {
+  std::vector<std::string> out;
+  DIR* d = opendir(path.c_str());
+  if (!d) fail("cannot open directory '" + path + "'");
+  while (dirent* e = readdir(d)) {
+    std::string n = e->d_name;
+    if (n == "." || n == "..") continue;
+    out.push_back(n);
+  }
+  closedir(d);
+  std::sort(out.begin(), out.end());
+  return out;
+}
+
+bool is_dir(const std::string& p) {
+  struct stat st;
+  return stat(p.c_str(), &st) == 0 && S_ISDIR(st.st_mode);
+}
+
+void read_file(const std::string& path, std::vector<uint8_t>& buf) {
+  int fd = open(path.c_str(), O_RDONLY);
+  if (fd < 0) fail("cannot open '" + path + "'");
+  struct stat st;
+  fstat(fd, &st);
+  buf.resize(st.st_size);
+  int64_t got = 0;
+  while (got < st.st_size) {
+    ssize_t r = read(fd, buf.data() + got, st.st_size - got);
+    if (r <= 0) { close(fd); fail("short read on '" + path + "'"); }
+    got += r;
+  }
+  close(fd);
+}
+
+LType logical_of(const pq::SchemaElement& e, bool& supported, std::string& why) {
+  LType t;
+  supported = true;
+  bool dec = e.converted == pq::CT_DECIMAL || e.logical_decimal;
+  switch (e.type) {
+    case pq::INT32:
+      t.is32 = true;
+      if (dec) { t.kind = LType::DECIMAL; t.precision = e.precision; t.scale = e.scale; }
+      else if (e.converted == pq::CT_DATE || e.logical_date) t.kind = LType::DATE;
+      else t.kind = LType::INT;
+      break;
+    case pq::INT64:
+      if (dec) { t.kind = LType::DECIMAL; t.precision = e.precision; t.scale = e.scale; }
+      else t.kind = LType::INT;
+      break;
+    case pq::DOUBLE: t.kind = LType::F64; break;
+    case pq::BYTE_ARRAY:
+      if (dec) { supported = false; why = "decimal stored as BYTE_ARRAY"; }
+      t.kind = LType::STR;
+      break;
+    default:
+      supported = false;
+      why = "parquet physical type " + std::to_string(e.type) + " has no device decoder";
+  }
+  return t;
+}
+
+void stage_align(std::vector<uint8_t>& s, int64_t a) { s.resize(align_up((int64_t)s.size(), a), 0); }
+
+}  // namespace
+
+void Engine::register_table(const std::string& name, const std::string& path, const std::string& format) {
+  if (format != "parquet")
+    fail("input format '" + format + "' is not supported by the B200 engine (only uncompressed parquet)");
+  if (!is_dir(path)) fail("table path '" + path + "' is not a directory");
+  Table t;
+  t.name = name;
+  t.path = path;
+
+  // ---- enumerate files (one level of hive partition directories) ---------------------------------
+  std::vector<FileInfo> all;
+  for (const std::string& e : list_dir(path)) {
+    std::string p = path + "/" + e;
+    if (e[0] == '_' || e[0] == '.') continue;  // _SUCCESS, _b200gen.json, .crc
+    if (is_dir(p)) {
+      size_t eq = e.find('=');
+      if (eq == std::string::npos) fail("unexpected directory '" + p + "' (not <col>=<value>)");
+      std::string col = e.substr(0, eq), val = e.substr(eq + 1);
+      if (t.part_col.empty()) t.part_col = col;
+      else if (t.part_col != col) fail("mixed partition columns under '" + path + "'");
+      for (const std::string& f : list_dir(p)) {
+        if (!ends_with(f, ".parquet")) continue;
+        FileInfo fi;
+        fi.path = p + "/" + f;
+        if (val == kHiveNull) fi.part_null = true;
+        else {
+          char* endp = nullptr;
+          fi.part_val = strtoll(val.c_str(), &endp, 10);
+          if (!endp || *endp) fail("non-integer partition value '" + val + "' under '" + path + "'");
+        }
+        all.push_back(fi);
+      }
+    } else if (ends_with(e, ".parquet")) {
+      FileInfo fi;
+      fi.path = p;
+      all.push_back(fi);
+    }
+  }
+  if (all.empty()) fail("no parquet files under '" + path + "'");
+  // multi-GPU: partitioned (fact) tables are sharded by file, dimension tables replicated
+  for (size_t i = 0; i < all.size(); ++i)
+    if (t.part_col.empty() || world <= 1 || (int)(i % world) == rank) t.files.push_back(all[i]);
+
+  // ---- parse + stage -----------------------------------------------------------------------------------
+  std::vector<uint8_t> buf;
+  bool first = true;
+  std::vector<int> max_def;
+  for (size_t fidx = 0; fidx < t.files.size(); ++fidx) {
+    FileInfo& fi = t.files[fidx];
+    read_file(fi.path, buf);
+    pq::FileMeta fm = pq::parse_footer(buf.data(), (int64_t)buf.size());
+    if (fm.schema.empty()) fail("empty schema in '" + fi.path + "'");
+    const int ncol = (int)fm.schema.size() - 1;
+    if ((int)fm.schema[0].num_children != ncol) fail("nested schema in '" + fi.path + "' is not supported");
+    if (first) {
+      for (int c = 0; c < ncol; ++c) {
+        const pq::SchemaElement& e = fm.schema[c + 1];
+        TableColumn tc;
+        tc.name = e.name;
+        tc.phys = e.type;
+        tc.lt = logical_of(e, tc.supported, tc.why_unsupported);
+        if (e.repetition == 2) { tc.supported = false; tc.why_unsupported = "repeated field"; }
+        t.col_index[tc.name] = (int)t.cols.size();
+        t.cols.push_back(std::move(tc));
+      }
+      first = false;
+    } else if (ncol != (int)t.cols.size()) {
+      fail("schema mismatch between files of table '" + name + "'");
+    }
+    max_def.assign(ncol, 0);
+    for (int c = 0; c < ncol; ++c) {
+      const pq::SchemaElement& e = fm.schema[c + 1];
+      if (e.name != t.cols[c].name || e.type != t.cols[c].phys) fail("schema mismatch in '" + fi.path + "'");
+      max_def[c] = e.repetition == 1 ? 1 : 0;
+      if (max_def[c]) t.cols[c].nullable = true;
+    }
+    fi.rows = fm.num_rows;
+    for (int c = 0; c < ncol; ++c) {
+      TableColumn& tc = t.cols[c];
+      stage_align(tc.stage, 16);
+      tc.file_page_begin.push_back((int64_t)tc.pages.size());
+      tc.file_byte_begin.push_back((int64_t)tc.stage.size());
+    }
+    int64_t row_base = 0;
+    for (const pq::RowGroup& rg : fm.row_groups) {
+      if ((int)rg.columns.size() != ncol) fail("row group column count mismatch in '" + fi.path + "'");
+      for (int c = 0; c < ncol; ++c) {
+        TableColumn& tc = t.cols[c];
+        if (!tc.supported) continue;
+        const pq::ColumnChunk& cc = rg.columns[c];
+        if (cc.codec != 0)
+          fail("column '" + tc.name + "' in '" + fi.path + "' is compressed (codec " + std::to_string(cc.codec) +
+               "); this engine reads uncompressed parquet only (nds_transcode --compression none)");
+        int64_t pos = cc.data_page_offset;
+        if (cc.dictionary_page_offset > 0 && cc.dictionary_page_offset < pos) pos = cc.dictionary_page_offset;
+        int64_t seen = 0, row_in_file = row_base;
+        int cur_dict = -1;
+        while (seen < cc.num_values) {
+          pq::PageHeader ph = pq::parse_page_header(buf.data(), pos, (int64_t)buf.size());
+          const uint8_t* payload = buf.data() + pos + ph.header_len;
+          const int64_t psize = ph.compressed_size;
+          if (ph.compressed_size != ph.uncompressed_size) fail("compressed page in '" + fi.path + "'");
+          if (pos + ph.header_len + psize > (int64_t)buf.size()) fail("page overruns file '" + fi.path + "'");
+          if (ph.type == pq::DICTIONARY_PAGE) {
+            if (ph.encoding != pq::PLAIN && ph.encoding != pq::PLAIN_DICTIONARY) fail("unsupported dictionary encoding");
+            DictInfo di;
+            di.count = (uint32_t)ph.num_values;
+            stage_align(tc.stage, 16);
+            if (tc.phys == pq::BYTE_ARRAY) {
+              // index the dictionary entries once at load time: StrView table, then the raw page
+              int64_t views_off = (int64_t)tc.stage.size();
+              tc.stage.resize(views_off + 8 * (int64_t)di.count);
+              int64_t chars_off = (int64_t)tc.stage.size();
+              tc.stage.insert(tc.stage.end(), payload, payload + psize);
+              int64_t p = 0;
+              for (uint32_t k = 0; k < di.count; ++k) {
+                if (p + 4 > psize) fail("truncated string dictionary in '" + fi.path + "'");
+                uint32_t len;
+                memcpy(&len, payload + p, 4);
+                int64_t abs_off = chars_off + p + 4;
+                if (abs_off + len > 0xFFFFFFFFll) fail("string column '" + tc.name + "' exceeds 4 GiB of encoded bytes");
+                uint64_t v = ((uint64_t)len << 32) | (uint64_t)abs_off;
+                memcpy(tc.stage.data() + views_off + 8 * (int64_t)k, &v, 8);
+                p += 4 + len;
+              }
+              di.off = views_off;
+            } else {
+              di.off = (int64_t)tc.stage.size();
+              tc.stage.insert(tc.stage.end(), payload, payload + psize);
+            }
+            tc.stage.resize(tc.stage.size() + kPagePad, 0);
+            cur_dict = (int)tc.dicts.size();
+            tc.dicts.push_back(di);
+          } else if (ph.type == pq::DATA_PAGE) {
+            PageInfo pi;
+            pi.file = (int32_t)fidx;
+            pi.num_values = (uint32_t)ph.num_values;
+            pi.size = (uint32_t)psize;
+            pi.row_in_file = row_in_file;
+            pi.def_len = 0;
+            if (ph.num_values > kMaxPageValues)
+              fail("data page with " + std::to_string(ph.num_values) + " values in '" + fi.path +
+                   "' exceeds the decode kernel limit of " + std::to_string(kMaxPageValues));
+            int64_t values_off = 0;
+            if (max_def[c] > 0) {
+              if (ph.def_encoding != pq::RLE) fail("definition levels not RLE-encoded in '" + fi.path + "'");
+              uint32_t dl;
+              memcpy(&dl, payload, 4);
+              pi.def_len = dl;
+              values_off = 4 + (int64_t)dl;
+              if (values_off > psize) fail("bad definition level length in '" + fi.path + "'");
+              if (dl == 0) fail("empty definition level stream in '" + fi.path + "'");
+            }
+            if (ph.encoding == pq::PLAIN) { pi.enc = 0; pi.dict = -1; }
+            else if (ph.encoding == pq::RLE_DICTIONARY || ph.encoding == pq::PLAIN_DICTIONARY) {
+              pi.enc = 1;
+              pi.dict = cur_dict;
+              if (cur_dict < 0) fail("dictionary-encoded page without dictionary in '" + fi.path + "'");
+            } else fail("unsupported data page encoding " + std::to_string(ph.encoding) + " in '" + fi.path + "'");
+            // place the payload so that its values section is 16 B aligned
+            int64_t cur = (int64_t)tc.stage.size();
+            int64_t off = align_up(cur + values_off, 16) - values_off;
+            tc.stage.resize(off, 0);
+            tc.stage.insert(tc.stage.end(), payload, payload + psize);
+            tc.stage.resize(tc.stage.size() + kPagePad, 0);
+            pi.off = off;
+            tc.pages.push_back(pi);
+            seen += ph.num_values;
+            row_in_file += ph.num_values;
+          } else if (ph.type == pq::DATA_PAGE_V2) {
+            fail("data page v2 in '" + fi.path + "' is not supported (write with data page version 1.0)");
+          }  // index pages are skipped
+          pos += ph.header_len + psize;
+        }
+      }
+      row_base += rg.num_rows;
+    }
+    if (row_base != fi.rows) fail("row group rows do not add up in '" + fi.path + "'");
+    t.rows += fi.rows;
+  }
+  for (TableColumn& tc : t.cols) {
+    stage_align(tc.stage, 16);
+    tc.file_page_begin.push_back((int64_t)tc.pages.size());
+    tc.file_byte_begin.push_back((int64_t)tc.stage.size());
+    tc.enc_bytes = (int64_t)tc.stage.size();
+    t.encoded_bytes += tc.enc_bytes;
+    if (tc.phys == pq::BYTE_ARRAY && tc.enc_bytes > 0xFFFFFFFFll)
+      fail("string column '" + tc.name + "' exceeds 4 GiB of encoded bytes");
+  }
+  if (t.part_col.size() && t.col_index.count(t.part_col))
+    fail("partition column '" + t.part_col + "' is also stored in the files of '" + name + "'");
+
+  // ---- upload -------------------------------------------------------------------------------------------
+  NDS_CUDA(cudaSetDevice(device));
+  for (TableColumn& tc : t.cols) {
+    if (!tc.supported || tc.enc_bytes == 0) { tc.stage.clear(); tc.stage.shrink_to_fit(); continue; }
+    if (resident_) {
+      NDS_CUDA(cudaMalloc(&tc.d_enc, tc.enc_bytes + 256));
+      NDS_CUDA(cudaMemcpyAsync(tc.d_enc, tc.stage.data(), tc.enc_bytes, cudaMemcpyHostToDevice, stream_));
+      NDS_CUDA(cudaStreamSynchronize(stream_));
+    }
+    if (keep_host_) {
+      if (cudaHostRegister(tc.stage.data(), tc.stage.size(), cudaHostRegisterDefault) == cudaSuccess) tc.pinned = true;
+      else cudaGetLastError();
+    } else {
+      tc.stage.clear();
+      tc.stage.shrink_to_fit();
+    }
+  }
+  drop_table(name);
+  tables_[name] = std::move(t);
+}
+
+void Engine::drop_table(const std::string& name) {
+  auto it = tables_.find(name);
+  if (it == tables_.end()) return;
+  for (TableColumn& tc : it->second.cols) {
+    if (tc.d_enc) cudaFree(tc.d_enc);
+    if (tc.pinned) cudaHostUnregister(tc.stage.data());
+  }
+  for (MemColumn& mc : it->second.mem_cols) {
+    if (mc.d_data) cudaFree(mc.d_data);
+    if (mc.d_valid) cudaFree(mc.d_valid);
+    if (mc.d_chars) cudaFree(mc.d_chars);
+  }
+  tables_.erase(it);
+}
+
+// ---- tables from Arrow buffers (operator-level tests, gathered partial aggregates) ----------------------
+void Engine::register_arrow(const std::string& name, ArrowSchema* schema, ArrowArray* array) {
+  NDS_REQUIRE(schema && array, "register_arrow: null schema/array");
+  NDS_REQUIRE(std::string(schema->format) == "+s", "register_arrow: expected a struct (record batch)");
+  NDS_REQUIRE(array->offset == 0, "register_arrow: sliced record batches are not supported");
+  NDS_CUDA(cudaSetDevice(device));
+  Table t;
+  t.name = name;
+  t.is_mem = true;
+  t.rows = array->length;
+  const int64_t n = array->length;
+  for (int64_t c = 0; c < schema->n_children; ++c) {
+    ArrowSchema* cs = schema->children[c];
+    ArrowArray* ca = array->children[c];
+    NDS_REQUIRE(ca->offset == 0, "register_arrow: sliced columns are not supported");
+    MemColumn mc;
+    mc.name = cs->name ? cs->name : "";
+    std::string f = cs->format;
+    const uint8_t* validity = (const uint8_t*)ca->buffers[0];
+    int64_t vwords = (n + 31) / 32 + 1;
+    if (validity && ca->null_count != 0) {
+      std::vector<uint32_t> v(vwords, 0);
+      memcpy(v.data(), validity, (n + 7) / 8);
+      NDS_CUDA(cudaMalloc(&mc.d_valid, vwords * 4));
+      NDS_CUDA(cudaMemcpy(mc.d_valid, v.data(), vwords * 4, cudaMemcpyHostToDevice));
+    }
+    auto upload = [&](const void* src, int64_t bytes) {
+      void* d = nullptr;
+      NDS_CUDA(cudaMalloc(&d, bytes + 256));
+      if (bytes) NDS_CUDA(cudaMemcpy(d, src, bytes, cudaMemcpyHostToDevice));
+      return d;
+    };
+    if (f == "i") { mc.lt.kind = LType::INT; mc.lt.is32 = true; mc.d_data = upload(ca->buffers[1], n * 4); }
+    else if (f == "tdD") { mc.lt.kind = LType::DATE; mc.lt.is32 = true; mc.d_data = upload(ca->buffers[1], n * 4); }
+    else if (f == "l") { mc.lt.kind = LType::INT; mc.d_data = upload(ca->buffers[1], n * 8); }
+    else if (f == "g") { mc.lt.kind = LType::F64; mc.d_data = upload(ca->buffers[1], n * 8); }
+    else if (f.rfind("d:", 0) == 0) {
+      int p = 0, s = 0, bits = 128;
+      int got = sscanf(f.c_str(), "d:%d,%d,%d", &p, &s, &bits);
+      NDS_REQUIRE(got >= 2 && bits == 128 && p <= 18, "register_arrow: only decimal128 with precision <= 18 is supported");
+      mc.lt.kind = LType::DECIMAL; mc.lt.precision = p; mc.lt.scale = s;
+      std::vector<int64_t> lo(n);
+      const int64_t* src = (const int64_t*)ca->buffers[1];
+      for (int64_t i = 0; i < n; ++i) lo[i] = src[2 * i];
+      mc.d_data = upload(lo.data(), n * 8);
+    } else if (f == "u") {
+      mc.lt.kind = LType::STR;
+      const int32_t* offs = (const int32_t*)ca->buffers[1];
+      std::vector<uint64_t> views(n);
+      for (int64_t i = 0; i < n; ++i) views[i] = ((uint64_t)(uint32_t)(offs[i + 1] - offs[i]) << 32) | (uint32_t)offs[i];
+      mc.d_data = upload(views.data(), n * 8);
+      mc.d_chars = (uint8_t*)upload(ca->buffers[2], n ? offs[n] : 0);
+    } else fail("register_arrow: unsupported column format '" + f + "' for column '" + mc.name + "'");
+    t.col_index[mc.name] = (int)t.mem_cols.size();
+    t.mem_cols.push_back(mc);
+  }
+  drop_table(name);
+  tables_[name] = std::move(t);
+}
+
+std::string Engine::table_info_json(const std::string& name) const {
+  auto it = tables_.find(name);
+  if (it == tables_.end()) fail("unknown table '" + name + "'");
+  const Table& t = it->second;
+  std::string s = "{\"name\":\"" + json_escape(name) + "\",\"rows\":" + std::to_string(t.rows) + ",\"files\":" +
+                  std::to_string(t.files.size()) + ",\"encoded_bytes\":" + std::to_string(t.encoded_bytes) +
+                  ",\"partition_column\":\"" + json_escape(t.part_col) + "\",\"columns\":[";
+  bool firstc = true;
+  auto add = [&](const std::string& n, const LType& lt, bool nullable, int64_t pages, int64_t bytes, bool ok) {
+    if (!firstc) s += ",";
+    firstc = false;
+    s += "{\"name\":\"" + json_escape(n) + "\",\"type\":\"" + lt.str() + "\",\"nullable\":" + (nullable ? "true" : "false") +
+         ",\"pages\":" + std::to_string(pages) + ",\"encoded_bytes\":" + std::to_string(bytes) + ",\"supported\":" +
+         (ok ? "true" : "false") + "}";
+  };
+  for (const TableColumn& c : t.cols) add(c.name, c.lt, c.nullable, (int64_t)c.pages.size(), c.enc_bytes, c.supported);
+  for (const MemColumn& c : t.mem_cols) add(c.name, c.lt, c.d_valid != nullptr, 0, 0, true);
+  s += "]}";
+  return s;
+}
+
+}  // namespace nds

@@ -1,0 +1,209 @@
+"""GPU parity for the operator kernels on in-memory tables: fused filter/project with SQL null
+semantics, hash join, hash group-by (sum/count/min/max, decimal avg), radix sort + limit.
+Checked against pyarrow.compute / plain Python - bit exact for integers, strings, decimals."""
+import decimal
+
+import numpy as np
+import pyarrow as pa
+import pyarrow.compute as pc
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def col(n):
+    return {'col': n}
+
+
+def lit(v, t=None):
+    d = {'lit': v}
+    if t:
+        d['type'] = t
+    return d
+
+
+def fn(name, *args, **kw):
+    d = {'fn': name, 'args': list(args)}
+    d.update(kw)
+    return d
+
+
+def _mk(n, seed=7):
+    rng = np.random.default_rng(seed)
+    a = pa.array(rng.integers(-50, 50, n).astype(np.int32), mask=rng.random(n) < 0.1)
+    b = pa.array(rng.integers(-10**12, 10**12, n), mask=rng.random(n) < 0.1)
+    words = ['alpha', 'beta', 'gamma', 'delta', '', 'epsilon-longer-string', 'b', 'beta2']
+    s = pa.array([None if rng.random() < 0.1 else words[i] for i in rng.integers(0, len(words), n)], type=pa.string())
+    d = pa.array([None if rng.random() < 0.1 else decimal.Decimal(int(v)).scaleb(-2) for v in rng.integers(-10**6, 10**6, n)],
+                 type=pa.decimal128(7, 2))
+    g = pa.array(rng.integers(0, 13, n), mask=rng.random(n) < 0.05)
+    return pa.table({'a': a, 'b': b, 's': s, 'd': d, 'g': g})
+
+
+@pytest.fixture(scope='module')
+def tbl(gpu_engine):
+    t = _mk(10007)
+    gpu_engine.register_arrow('t', t)
+    return t
+
+
+def test_roundtrip_arrow(gpu_engine, tbl):
+    got = gpu_engine.execute({'op': 'scan', 'table': 't', 'columns': tbl.schema.names})
+    assert pa.Table.from_batches([got]).equals(tbl.combine_chunks())
+
+
+def test_filter_three_valued_logic(gpu_engine, tbl):
+    # (a > 3 and s <> 'beta') or b is null or d >= 12.34
+    cond = fn('or', fn('and', fn('gt', col('a'), lit(3)), fn('ne', col('s'), lit('beta'))),
+              fn('isnull', col('b')), fn('ge', col('d'), lit(1234, 'decimal(7,2)')))
+    got = gpu_engine.execute({'op': 'sort', 'keys': [{'expr': col('rid')}],
+                              'child': {'op': 'filter', 'cond': cond,
+                                        'child': {'op': 'scan', 'table': 't2', 'columns': ['rid', 'a', 'b', 's', 'd']}}}) \
+        if False else None
+    t = tbl.append_column('rid', pa.array(np.arange(tbl.num_rows)))
+    gpu_engine.register_arrow('t2', t)
+    got = gpu_engine.execute({'op': 'sort', 'keys': [{'expr': col('rid')}],
+                              'child': {'op': 'filter', 'cond': cond,
+                                        'child': {'op': 'scan', 'table': 't2', 'columns': ['rid', 'a', 'b', 's', 'd']}}})
+    m = pc.or_kleene(pc.or_kleene(pc.and_kleene(pc.greater(t['a'], 3), pc.not_equal(t['s'], 'beta')), pc.is_null(t['b'])),
+                     pc.greater_equal(t['d'], pa.scalar(decimal.Decimal('12.34'), pa.decimal128(7, 2))))
+    exp = t.filter(m.combine_chunks().fill_null(False)).select(['rid', 'a', 'b', 's', 'd']).combine_chunks()
+    assert pa.Table.from_batches([got]).equals(exp)
+
+
+def test_project_arithmetic_substr(gpu_engine, tbl):
+    t = tbl.append_column('rid', pa.array(np.arange(tbl.num_rows)))
+    gpu_engine.register_arrow('t2', t)
+    plan = {'op': 'project', 'child': {'op': 'scan', 'table': 't2', 'columns': ['rid', 'a', 'b', 's']},
+            'exprs': [{'name': 'rid', 'expr': col('rid')},
+                      {'name': 'x', 'expr': fn('add', fn('mul', col('a'), lit(3)), col('b'))},
+                      {'name': 'p', 'expr': fn('substr', col('s'), start=2, len=3)},
+                      {'name': 'c', 'expr': fn('if', fn('lt', col('a'), lit(0)), lit(-1), col('a'))}]}
+    got = pa.Table.from_batches([gpu_engine.execute(plan)])
+    x = pc.add(pc.multiply(t['a'].cast(pa.int64()), 3), t['b'])
+    p = pc.utf8_slice_codeunits(t['s'], 1, 4)
+    a64 = t['a'].cast(pa.int64())
+    c = pc.if_else(pc.less(a64, 0).fill_null(False), pa.scalar(-1, pa.int64()), a64)
+    assert got['x'].combine_chunks().equals(x.combine_chunks())
+    assert got['p'].combine_chunks().equals(p.combine_chunks())
+    assert got['c'].combine_chunks().equals(c.combine_chunks())
+
+
+def test_join_inner_unique_build(gpu_engine, tbl):
+    n = 5000
+    rng = np.random.default_rng(3)
+    dim = pa.table({'k': pa.array(np.arange(100, 100 + 300, dtype=np.int32)),
+                    'name': pa.array(['n%03d' % (i % 37) for i in range(300)]),
+                    'w': pa.array(rng.integers(0, 1000, 300))})
+    fact = pa.table({'fk': pa.array(rng.integers(0, 600, n).astype(np.int32), mask=rng.random(n) < 0.05),
+                     'v': pa.array(rng.integers(0, 10**6, n)), 'rid': pa.array(np.arange(n))})
+    gpu_engine.register_arrow('dim', dim)
+    gpu_engine.register_arrow('fact', fact)
+    plan = {'op': 'sort', 'keys': [{'expr': col('rid')}],
+            'child': {'op': 'join', 'probe': {'op': 'scan', 'table': 'fact', 'columns': ['fk', 'v', 'rid']},
+                      'build': {'op': 'filter', 'cond': fn('lt', col('w'), lit(700)),
+                                'child': {'op': 'scan', 'table': 'dim', 'columns': ['k', 'name', 'w']}},
+                      'probe_key': 'fk', 'build_key': 'k'}}
+    got = pa.Table.from_batches([gpu_engine.execute(plan)])
+    d2 = dim.filter(pc.less(dim['w'], 700))
+    exp = fact.join(d2, keys='fk', right_keys='k', join_type='inner').sort_by('rid')
+    assert got.num_rows == exp.num_rows
+    for c in ['fk', 'v', 'rid', 'name', 'w']:
+        assert got[c].combine_chunks().equals(exp[c].combine_chunks()), c
+
+
+def test_join_duplicate_build_keys_fail(gpu_engine):
+    from spark_rapids_benchmarks_b200.engine import EngineError
+    gpu_engine.register_arrow('dup', pa.table({'k': pa.array([1, 2, 2], type=pa.int32())}))
+    gpu_engine.register_arrow('pr', pa.table({'fk': pa.array([1, 2, 3], type=pa.int32())}))
+    with pytest.raises(EngineError):
+        gpu_engine.execute({'op': 'join', 'probe': {'op': 'scan', 'table': 'pr', 'columns': ['fk']},
+                            'build': {'op': 'scan', 'table': 'dup', 'columns': ['k']}, 'probe_key': 'fk', 'build_key': 'k'})
+
+
+def test_group_by_sum_count_min_max_avg(gpu_engine, tbl):
+    plan = {'op': 'sort',
+            'keys': [{'expr': col('g')}, {'expr': col('s')}],
+            'child': {'op': 'project',
+                      'exprs': [{'name': 'g', 'expr': col('g')}, {'name': 's', 'expr': col('s')},
+                                {'name': 'sd', 'expr': col('sd')}, {'name': 'cb', 'expr': col('cb')},
+                                {'name': 'n', 'expr': col('n')}, {'name': 'mn', 'expr': col('mn')}, {'name': 'mx', 'expr': col('mx')},
+                                {'name': 'avg_d', 'expr': fn('decavg', col('sd'), col('cd'), up=4, type='decimal(11,6)')},
+                                {'name': 'avg_a', 'expr': fn('divi2f', col('sa'), col('ca'))}],
+                      'child': {'op': 'aggregate',
+                                'keys': [{'name': 'g', 'expr': col('g')}, {'name': 's', 'expr': col('s')}],
+                                'aggs': [{'name': 'sd', 'fn': 'sum', 'expr': col('d')}, {'name': 'cd', 'fn': 'count', 'expr': col('d')},
+                                         {'name': 'cb', 'fn': 'count', 'expr': col('b')}, {'name': 'n', 'fn': 'count_star'},
+                                         {'name': 'mn', 'fn': 'min', 'expr': col('b')}, {'name': 'mx', 'fn': 'max', 'expr': col('a')},
+                                         {'name': 'sa', 'fn': 'sum', 'expr': col('a')}, {'name': 'ca', 'fn': 'count', 'expr': col('a')}],
+                                'child': {'op': 'scan', 'table': 't', 'columns': ['a', 'b', 's', 'd', 'g']}}}}
+    got = pa.Table.from_batches([gpu_engine.execute(plan)]).to_pylist()
+    # plain-Python oracle
+    groups = {}
+    for r in tbl.to_pylist():
+        groups.setdefault((r['g'], r['s']), []).append(r)
+
+    def keyf(k):   # NULLS FIRST ascending
+        return tuple((0, 0) if v is None else (1, v if not isinstance(v, str) else v.encode()) for v in k)
+    exp = []
+    for k in sorted(groups, key=keyf):
+        rows = groups[k]
+        ds = [r['d'] for r in rows if r['d'] is not None]
+        bs = [r['b'] for r in rows if r['b'] is not None]
+        as_ = [r['a'] for r in rows if r['a'] is not None]
+        sd = sum(ds) if ds else None
+        avg_d = None
+        if ds:
+            avg_d = (sd / decimal.Decimal(len(ds))).quantize(decimal.Decimal('0.000001'), rounding=decimal.ROUND_HALF_UP)
+        exp.append({'g': k[0], 's': k[1], 'sd': sd, 'cb': len(bs), 'n': len(rows), 'mn': min(bs) if bs else None,
+                    'mx': max(as_) if as_ else None, 'avg_d': avg_d, 'avg_a': (sum(as_) / len(as_)) if as_ else None})
+    assert len(got) == len(exp)
+    for g, e in zip(got, exp):
+        assert g == e, (g, e)
+
+
+def test_sort_multi_key_desc_nulls_limit(gpu_engine, tbl):
+    t = tbl.append_column('rid', pa.array(np.arange(tbl.num_rows)))
+    gpu_engine.register_arrow('t2', t)
+    plan = {'op': 'sort', 'limit': 250,
+            'keys': [{'expr': col('s'), 'desc': True}, {'expr': col('d')}, {'expr': col('b'), 'desc': True}, {'expr': col('rid')}],
+            'child': {'op': 'scan', 'table': 't2', 'columns': ['rid', 's', 'd', 'b']}}
+    got = pa.Table.from_batches([gpu_engine.execute(plan)]).to_pylist()
+    rows = t.select(['rid', 's', 'd', 'b']).to_pylist()
+
+    def key(r):
+        s, d, b = r['s'], r['d'], r['b']
+        ks = (1, b'') if s is None else (0, bytes(255 - c for c in s.encode()) + b'\xff')   # desc, nulls last
+        kd = (0, 0) if d is None else (1, d)                                                # asc, nulls first
+        kb = (1, 0) if b is None else (0, -b)                                               # desc, nulls last
+        return (ks, kd, kb, r['rid'])
+    # descending byte order with prefix rule: a longer string sorts BEFORE its prefix when descending
+    import functools
+
+    def cmp(x, y):
+        for kx, ky, desc in ((x['s'], y['s'], True), (x['d'], y['d'], False), (x['b'], y['b'], True), (x['rid'], y['rid'], False)):
+            if kx is None and ky is None:
+                continue
+            if kx is None:
+                return 1 if desc else -1
+            if ky is None:
+                return -1 if desc else 1
+            if isinstance(kx, str):
+                kx, ky = kx.encode(), ky.encode()
+            if kx == ky:
+                continue
+            r = -1 if kx < ky else 1
+            return -r if desc else r
+        return 0
+    exp = sorted(rows, key=functools.cmp_to_key(cmp))[:250]
+    assert got == exp
+
+
+def test_empty_inputs(gpu_engine):
+    gpu_engine.register_arrow('e', pa.table({'k': pa.array([], type=pa.int32()), 'v': pa.array([], type=pa.int64())}))
+    got = gpu_engine.execute({'op': 'sort', 'keys': [{'expr': col('k')}], 'limit': 10,
+                              'child': {'op': 'aggregate', 'keys': [{'name': 'k', 'expr': col('k')}],
+                                        'aggs': [{'name': 'sv', 'fn': 'sum', 'expr': col('v')}],
+                                        'child': {'op': 'filter', 'cond': fn('gt', col('v'), lit(0)),
+                                                  'child': {'op': 'scan', 'table': 'e', 'columns': ['k', 'v']}}}})
+    assert got.num_rows == 0 and got.schema.names == ['k', 'sv']
