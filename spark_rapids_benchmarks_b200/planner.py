@@ -1,0 +1,536 @@
+"""SQL AST -> physical plan IR for the B200 engine (star / snowflake join + aggregate + top-k).
+
+Stands in for Catalyst, which the reference reaches through `spark_session.sql(query)`
+(/root/reference/nds/nds_power.py:130).  The produced IR is the JSON the C ABI's
+`nds_engine_execute` takes (DESIGN.md "Plan IR").  Shapes outside the supported subset raise
+PlanError: an unsupported query fails loudly, it is never run elsewhere.
+
+Planning rules (all result-preserving for inner equi-joins):
+  * single-table conjuncts are pushed below the joins; col = col conjuncts between two tables
+    become hash joins; other multi-table conjuncts run after the joins;
+  * the hive-partitioned fact table is the probe side; every dimension (with its own
+    snowflake children joined in first) is a unique-key build side;
+  * joins are ordered most-selective first by a static estimate; the join on the fact table's
+    partition column is marked `prune_partitions` (Spark's dynamic partition pruning) and goes last;
+  * AVG is planned as SUM and COUNT plus a final divide (decimal: scale + 4, HALF_UP - Spark's
+    Average for DecimalType; integer: double);
+  * ORDER BY keys are followed by every remaining output column as tie-breakers so that the
+    LIMIT cut is deterministic.
+"""
+import datetime
+import decimal
+import json
+import re
+
+from . import nds_schema
+from .sql import parse, SqlError
+
+
+class PlanError(ValueError):
+    pass
+
+
+AGG_FUNCS = ('sum', 'avg', 'count', 'min', 'max')
+_DEC = re.compile(r'decimal\((\d+),(\d+)\)')
+
+
+def _col(n):
+    return {'col': n}
+
+
+def _fn(name, *args, **kw):
+    d = {'fn': name, 'args': list(args)}
+    d.update(kw)
+    return d
+
+
+def _engine_type(t):
+    """schema type-string -> engine type-string"""
+    if t in ('int32', 'int64', 'date', 'double', 'string', 'bool'):
+        return t
+    if _DEC.match(t):
+        return t
+    if t.startswith('char(') or t.startswith('varchar('):
+        return 'string'
+    raise PlanError('unsupported column type %r' % t)
+
+
+def _is_num(t):
+    return t in ('int32', 'int64') or bool(_DEC.match(t))
+
+
+class Planner:
+    def __init__(self, ast, catalog=None):
+        self.q = ast
+        self.col_types = catalog or nds_schema.column_types()
+        self.col_table = nds_schema.column_table()
+        self.alias = {}
+        for name, alias in ast['from']:
+            if name not in nds_schema.SOURCE_TABLES:
+                raise PlanError('unknown table %r' % name)
+            if alias in self.alias:
+                raise PlanError('duplicate table alias %r (self joins are not supported yet)' % alias)
+            self.alias[alias] = name
+        self.tables = [t for t, _ in ast['from']]
+        if len(set(self.tables)) != len(self.tables):
+            raise PlanError('a table appears twice in FROM (self joins are not supported yet)')
+
+    # ---- name resolution ----------------------------------------------------------------------------
+    def resolve(self, node):
+        _, qual, name = node
+        if qual is not None:
+            if qual not in self.alias:
+                raise PlanError('unknown table alias %r' % qual)
+            tbl = self.alias[qual]
+            if self.col_table.get(name) != tbl:
+                raise PlanError('column %r is not in table %r' % (name, tbl))
+            return name
+        tbl = self.col_table.get(name)
+        if tbl is None or tbl not in self.tables:
+            raise PlanError('unknown column %r' % name)
+        return name
+
+    def tables_of(self, ast, out=None):
+        out = set() if out is None else out
+        if not isinstance(ast, tuple):
+            return out
+        if ast[0] == 'col':
+            out.add(self.col_table[self.resolve(ast)])
+            return out
+        for x in ast[1:]:
+            if isinstance(x, tuple):
+                self.tables_of(x, out)
+            elif isinstance(x, list):
+                for y in x:
+                    if isinstance(y, tuple) and y and isinstance(y[0], str):
+                        self.tables_of(y, out)
+                    elif isinstance(y, tuple):
+                        for z in y:
+                            self.tables_of(z, out)
+        return out
+
+    def columns_of(self, ast, out=None):
+        out = set() if out is None else out
+        if not isinstance(ast, tuple):
+            return out
+        if ast[0] == 'col':
+            out.add(self.resolve(ast))
+            return out
+        for x in ast[1:]:
+            if isinstance(x, tuple):
+                self.columns_of(x, out)
+            elif isinstance(x, list):
+                for y in x:
+                    if isinstance(y, tuple) and y and isinstance(y[0], str):
+                        self.columns_of(y, out)
+                    elif isinstance(y, tuple):
+                        for z in y:
+                            self.columns_of(z, out)
+        return out
+
+    # ---- expression translation ------------------------------------------------------------------------
+    def expr(self, ast, agg_map=None, key_map=None):
+        """AST -> (IR, type-string). agg_map/key_map: replace aggregate calls / group expressions by
+        references to aggregate output columns."""
+        if key_map is not None:
+            k = self.ast_key(ast)
+            if k in key_map:
+                name, t = key_map[k]
+                return _col(name), t
+        kind = ast[0]
+        if kind == 'col':
+            name = self.resolve(ast)
+            if key_map is not None:
+                raise PlanError('column %r must appear in GROUP BY or inside an aggregate' % name)
+            return _col(name), _engine_type(self.col_types[name])
+        if kind == 'num':
+            txt = ast[1]
+            if '.' in txt:
+                d = decimal.Decimal(txt)
+                scale = -d.as_tuple().exponent
+                unscaled = int(d.scaleb(scale))
+                t = 'decimal(%d,%d)' % (max(len(str(abs(unscaled))), scale, 1), scale)
+                return {'lit': unscaled, 'type': t}, t
+            return {'lit': int(txt), 'type': 'int64'}, 'int64'
+        if kind == 'str':
+            return {'lit': ast[1], 'type': 'string'}, 'string'
+        if kind == 'null':
+            return {'lit': None, 'type': 'int64'}, 'int64'
+        if kind == 'neg':
+            x, t = self.expr(ast[1], agg_map, key_map)
+            if 'lit' in x and isinstance(x['lit'], int):
+                return {'lit': -x['lit'], 'type': x['type']}, t
+            return _fn('neg', x), t
+        if kind == 'not':
+            x, _ = self.expr(ast[1], agg_map, key_map)
+            return _fn('not', x), 'bool'
+        if kind == 'isnull':
+            x, _ = self.expr(ast[1], agg_map, key_map)
+            return _fn('isnotnull' if ast[2] else 'isnull', x), 'bool'
+        if kind == 'between':
+            x, _ = self.expr(ast[1], agg_map, key_map)
+            lo, _ = self.expr(ast[2], agg_map, key_map)
+            hi, _ = self.expr(ast[3], agg_map, key_map)
+            r = _fn('and', _fn('ge', x, lo), _fn('le', x, hi))
+            return (_fn('not', r) if ast[4] else r), 'bool'
+        if kind == 'in':
+            x, _ = self.expr(ast[1], agg_map, key_map)
+            items = [self.expr(i, agg_map, key_map)[0] for i in ast[2]]
+            r = _fn('or', *[_fn('eq', x, i) for i in items]) if len(items) > 1 else _fn('eq', x, items[0])
+            return (_fn('not', r) if ast[3] else r), 'bool'
+        if kind == 'case':
+            other = self.expr(ast[2], agg_map, key_map) if ast[2] is not None else ({'lit': None, 'type': 'int64'}, 'int64')
+            res, t = other
+            for cond, val in reversed(ast[1]):
+                c, _ = self.expr(cond, agg_map, key_map)
+                v, tv = self.expr(val, agg_map, key_map)
+                res, t = _fn('if', c, v, res), tv
+            return res, t
+        if kind == 'cast':
+            tname = ast[2].lower()
+            if tname == 'date' and ast[1][0] == 'str':
+                d = datetime.date.fromisoformat(ast[1][1])
+                return {'lit': (d - datetime.date(1970, 1, 1)).days, 'type': 'date'}, 'date'
+            x, t = self.expr(ast[1], agg_map, key_map)
+            if tname in ('double', 'float'):
+                return _fn('cast_double', x), 'double'
+            raise PlanError('CAST to %r is not supported yet' % tname)
+        if kind == 'bin':
+            op = ast[1]
+            if op in ('and', 'or'):
+                l, _ = self.expr(ast[2], agg_map, key_map)
+                r, _ = self.expr(ast[3], agg_map, key_map)
+                return _fn(op, l, r), 'bool'
+            l, tl = self.expr(ast[2], agg_map, key_map)
+            r, tr = self.expr(ast[3], agg_map, key_map)
+            if op in ('eq', 'ne', 'lt', 'le', 'gt', 'ge'):
+                if (tl == 'string') != (tr == 'string'):
+                    raise PlanError('comparison between string and non-string')
+                return _fn(op, l, r), 'bool'
+            if op in ('add', 'sub', 'mul'):
+                if tl == 'string' or tr == 'string':
+                    raise PlanError('arithmetic on strings')
+                if tl == 'double' or tr == 'double':
+                    return _fn(op, l, r), 'double'
+                ml, mr = _DEC.match(tl), _DEC.match(tr)
+                if ml or mr:
+                    pl, sl = (int(ml.group(1)), int(ml.group(2))) if ml else (20, 0)
+                    pr, sr = (int(mr.group(1)), int(mr.group(2))) if mr else (20, 0)
+                    if op == 'mul':
+                        return _fn(op, l, r), 'decimal(%d,%d)' % (min(38, pl + pr + 1), sl + sr)
+                    s = max(sl, sr)
+                    return _fn(op, l, r), 'decimal(%d,%d)' % (min(38, max(pl - sl, pr - sr) + s + 1), s)
+                return _fn(op, l, r), 'int64'
+            if op == 'div':
+                return _fn('div', l, r), 'double'
+            raise PlanError('operator %r' % op)
+        if kind == 'call':
+            fname = ast[1]
+            if fname in AGG_FUNCS:
+                if agg_map is None:
+                    raise PlanError('aggregate %s() is not allowed here' % fname)
+                return self.agg_ref(ast, agg_map)
+            if fname in ('substr', 'substring'):
+                x, t = self.expr(ast[2][0], agg_map, key_map)
+                if t != 'string':
+                    raise PlanError('substr over a non-string')
+                start = self.const_int(ast[2][1])
+                ln = self.const_int(ast[2][2]) if len(ast[2]) > 2 else (1 << 30)
+                return _fn('substr', x, start=start, len=ln), 'string'
+            raise PlanError('function %s() is not supported yet' % fname)
+        raise PlanError('unsupported expression %r' % (kind,))
+
+    def const_int(self, ast):
+        if ast[0] == 'num' and '.' not in ast[1]:
+            return int(ast[1])
+        raise PlanError('expected an integer constant')
+
+    def ast_key(self, ast):
+        """structural key with resolved column names (dt.d_year == d_year)"""
+        if isinstance(ast, tuple):
+            if ast and ast[0] == 'col':
+                return ('col', self.resolve(ast))
+            return tuple(self.ast_key(x) for x in ast)
+        if isinstance(ast, list):
+            return tuple(self.ast_key(x) for x in ast)
+        return ast
+
+    # ---- aggregates ----------------------------------------------------------------------------------------
+    def agg_ref(self, ast, agg_map):
+        fname, args, distinct = ast[1], ast[2], ast[3]
+        if distinct:
+            raise PlanError('%s(DISTINCT ...) is not supported yet' % fname)
+        if fname == 'count' and (not args or args[0] == ('star',)):
+            name = agg_map.add('count_star', None, 'int64')
+            return _col(name), 'int64'
+        if len(args) != 1:
+            raise PlanError('%s() takes one argument' % fname)
+        x, t = self.expr(args[0])
+        if fname == 'count':
+            return _col(agg_map.add('count', x, 'int64')), 'int64'
+        if not _is_num(t) and t != 'double':
+            raise PlanError('%s() over %s is not supported' % (fname, t))
+        m = _DEC.match(t)
+        if fname in ('min', 'max'):
+            rt = t if t != 'int32' else 'int64'
+            return _col(agg_map.add(fname, x, rt)), rt
+        sum_t = 'decimal(%d,%s)' % (min(38, int(m.group(1)) + 10), m.group(2)) if m else ('double' if t == 'double' else 'int64')
+        sname = agg_map.add('sum', x, sum_t)
+        if fname == 'sum':
+            return _col(sname), sum_t
+        cname = agg_map.add('count', x, 'int64')
+        if m:   # Spark Average(DecimalType(p,s)) -> DecimalType(p+4, s+4)
+            rt = 'decimal(%d,%d)' % (min(38, int(m.group(1)) + 4), int(m.group(2)) + 4)
+            return _fn('decavg', _col(sname), _col(cname), up=4, type=rt), rt
+        if t == 'double':
+            return _fn('div', _col(sname), _col(cname)), 'double'
+        return _fn('divi2f', _col(sname), _col(cname)), 'double'
+
+    # ---- SQL text of an expression, for unaliased output names (Spark style) ----------------------------
+    def text(self, ast):
+        k = ast[0]
+        if k == 'col':
+            return self.resolve(ast)
+        if k == 'num':
+            return ast[1]
+        if k == 'str':
+            return ast[1]
+        if k == 'call':
+            return '%s(%s)' % (ast[1], ', '.join('*' if a == ('star',) else self.text(a) for a in ast[2]))
+        if k == 'bin':
+            sym = {'add': '+', 'sub': '-', 'mul': '*', 'div': '/', 'eq': '=', 'ne': '<>', 'lt': '<', 'le': '<=', 'gt': '>',
+                   'ge': '>=', 'and': 'AND', 'or': 'OR'}[ast[1]]
+            return '(%s %s %s)' % (self.text(ast[2]), sym, self.text(ast[3]))
+        if k == 'neg':
+            return '(- %s)' % self.text(ast[1])
+        return k
+
+    # ---- the plan ---------------------------------------------------------------------------------------------
+    def plan(self, distributed=False):
+        q = self.q
+        conj = []
+
+        def split(e):
+            if e is None:
+                return
+            if e[0] == 'bin' and e[1] == 'and':
+                split(e[2])
+                split(e[3])
+            else:
+                conj.append(e)
+        split(q['where'])
+        edges, table_filters, post = [], {}, []
+        for c in conj:
+            tabs = self.tables_of(c)
+            if (c[0] == 'bin' and c[1] == 'eq' and c[2][0] == 'col' and c[3][0] == 'col' and len(tabs) == 2):
+                a, b = self.resolve(c[2]), self.resolve(c[3])
+                edges.append((self.col_table[a], a, self.col_table[b], b))
+            elif len(tabs) == 1:
+                table_filters.setdefault(next(iter(tabs)), []).append(c)
+            elif len(tabs) == 0:
+                raise PlanError('constant predicates are not supported')
+            else:
+                post.append(c)
+        # ---- root (fact) table
+        facts = [t for t in self.tables if t in nds_schema.TABLE_PARTITIONING]
+        if len(facts) > 1:
+            raise PlanError('joins between fact tables (%s) are not supported yet' % ', '.join(facts))
+        root = facts[0] if facts else self.tables[0]
+        # ---- columns each table must produce
+        need = {t: set() for t in self.tables}
+        used = set()
+        for e, _ in q['select']:
+            self.columns_of(e, used)
+        for e in q['group']:
+            self.columns_of(e, used)
+        select_aliases = {a for _, a in q['select'] if a}
+        for e, _, _ in q['order']:
+            if e[0] == 'col' and e[1] is None and e[2] in select_aliases:
+                continue
+            self.columns_of(e, used)
+        for c in conj:
+            self.columns_of(c, used)
+        for c in used:
+            need[self.col_table[c]].add(c)
+        # ---- join tree
+        children = {t: [] for t in self.tables}
+        visited = {root}
+        frontier = [root]
+        remaining = list(edges)
+        while frontier:
+            cur = frontier.pop(0)
+            for e in list(remaining):
+                ta, ca, tb, cb = e
+                if ta == cur and tb not in visited:
+                    children[cur].append((ca, tb, cb))
+                elif tb == cur and ta not in visited:
+                    children[cur].append((cb, ta, ca))
+                else:
+                    continue
+                nxt = children[cur][-1][1]
+                visited.add(nxt)
+                frontier.append(nxt)
+                remaining.remove(e)
+        for t in self.tables:
+            if t not in visited:
+                raise PlanError('table %r is not connected by an equi-join (cross joins are not supported)' % t)
+        for ta, ca, tb, cb in remaining:       # extra equalities between already-joined tables
+            post.append(('bin', 'eq', ('col', None, ca), ('col', None, cb)))
+
+        def selectivity(t):
+            s = 1.0
+            for c in table_filters.get(t, []):
+                s *= self.pred_selectivity(c)
+            for _, ct, _ in children[t]:
+                s *= min(1.0, selectivity(ct) * 1.5)
+            return s
+
+        def subtree(t):
+            cols = sorted(need[t], key=lambda c: [n for n, _, _ in nds_schema.SOURCE_TABLES[t]].index(c))
+            node = {'op': 'scan', 'table': t, 'columns': cols}
+            flt = table_filters.get(t, [])
+            if flt:
+                irs = [self.expr(c)[0] for c in flt]
+                node = {'op': 'filter', 'cond': irs[0] if len(irs) == 1 else _fn('and', *irs), 'child': node}
+            pcol = nds_schema.TABLE_PARTITIONING.get(t)
+            joins = []
+            for pk, ct, ck in children[t]:
+                prune = pk == pcol
+                joins.append((2.0 if prune else selectivity(ct), pk, ct, ck, prune))
+            joins.sort(key=lambda j: j[0])
+            for _, pk, ct, ck, prune in joins:
+                node = {'op': 'join', 'type': 'inner', 'probe': node, 'build': subtree(ct), 'probe_key': pk, 'build_key': ck}
+                if prune:
+                    node['prune_partitions'] = True
+            return node
+        node = subtree(root)
+        if post:
+            irs = [self.expr(c)[0] for c in post]
+            node = {'op': 'filter', 'cond': irs[0] if len(irs) == 1 else _fn('and', *irs), 'child': node}
+
+        # ---- aggregation
+        def has_agg(a):
+            if not isinstance(a, tuple):
+                return False
+            if a[0] == 'call' and a[1] in AGG_FUNCS:
+                return True
+            return any(has_agg(x) if isinstance(x, tuple) else any(has_agg(y) for y in x if isinstance(y, tuple))
+                       for x in a[1:] if isinstance(x, (tuple, list)))
+        is_agg = bool(q['group']) or any(has_agg(e) for e, _ in q['select'])
+        out_cols = []          # [(name, ir, type)]
+        names = []
+        for e, alias in q['select']:
+            names.append(alias if alias else self.text(e))
+        final_partial = None
+        if is_agg:
+            key_map, keys = {}, []
+            for i, g in enumerate(q['group']):
+                ir, t = self.expr(g)
+                name = ir['col'] if 'col' in ir else '_gk%d' % i
+                key_map[self.ast_key(g)] = (name, t)
+                keys.append({'name': name, 'expr': ir, '_type': t})
+            agg_map = _AggMap()
+            sel_ir = [self.expr(e, agg_map, key_map) for e, _ in q['select']]
+            order_extra = []
+            for e, desc, nf in q['order']:
+                order_extra.append(None if (e[0] == 'col' and e[1] is None and e[2] in select_aliases)
+                                   else self.expr(e, agg_map, key_map))
+            agg_node = {'op': 'aggregate', 'keys': [{'name': k['name'], 'expr': k['expr']} for k in keys],
+                        'aggs': agg_map.specs(), 'child': node}
+            if distributed:
+                final_partial = agg_node
+                merge = {'op': 'aggregate',
+                         'keys': [{'name': k['name'], 'expr': _col(k['name'])} for k in keys],
+                         'aggs': [{'name': a['name'], 'fn': {'count': 'sum', 'count_star': 'sum'}.get(a['fn'], a['fn']),
+                                   'expr': _col(a['name'])} for a in agg_map.specs()],
+                         'child': {'op': 'scan', 'table': '__partial__',
+                                   'columns': [k['name'] for k in keys] + [a['name'] for a in agg_map.specs()]}}
+                node = merge
+            else:
+                node = agg_node
+            for (ir, t), name in zip(sel_ir, names):
+                out_cols.append((name, ir, t))
+        else:
+            for (e, _), name in zip(q['select'], names):
+                ir, t = self.expr(e)
+                out_cols.append((name, ir, t))
+            order_extra = [None if (e[0] == 'col' and e[1] is None and e[2] in select_aliases) else self.expr(e)
+                           for e, _, _ in q['order']]
+        node = {'op': 'project', 'exprs': [{'name': n, 'expr': ir} for n, ir, _ in out_cols], 'child': node}
+
+        # ---- order by / limit
+        if q['order'] or q['limit'] is not None:
+            keys = []
+            used_names = []
+            for (e, desc, nf), extra in zip(q['order'], order_extra):
+                if extra is None:
+                    name = e[2]
+                else:
+                    ir, _ = extra
+                    match = [n for n, oir, _ in out_cols if json.dumps(oir, sort_keys=True) == json.dumps(ir, sort_keys=True)]
+                    if not match:
+                        raise PlanError('ORDER BY expression %s is not in the select list (not supported yet)' % self.text(e))
+                    name = match[0]
+                k = {'expr': _col(name), 'desc': bool(desc)}
+                if nf is not None:
+                    k['nulls_first'] = bool(nf)
+                keys.append(k)
+                used_names.append(name)
+            for n, _, _ in out_cols:                       # deterministic tie-break
+                if n not in used_names:
+                    keys.append({'expr': _col(n), 'desc': False})
+            node = {'op': 'sort', 'keys': keys, 'limit': -1 if q['limit'] is None else q['limit'], 'child': node}
+        out = {'root': node, 'output': [{'name': n, 'type': t} for n, _, t in out_cols]}
+        if distributed:
+            if final_partial is None:
+                raise PlanError('distributed execution needs an aggregating query')
+            out['partial'] = final_partial
+        return out
+
+    def pred_selectivity(self, c):
+        k = c[0]
+        if k == 'bin':
+            if c[1] == 'eq':
+                return 0.02
+            if c[1] == 'ne':
+                return 0.9
+            if c[1] == 'or':
+                return min(1.0, self.pred_selectivity(c[2]) + self.pred_selectivity(c[3]) + 0.3)
+            if c[1] == 'and':
+                return self.pred_selectivity(c[2]) * self.pred_selectivity(c[3])
+            return 0.3
+        if k == 'between':
+            return 0.25
+        if k == 'in':
+            return min(1.0, 0.02 * len(c[2]))
+        return 0.5
+
+
+class _AggMap:
+    def __init__(self):
+        self.items = {}
+        self.order = []
+
+    def add(self, fn, ir, rtype):
+        key = (fn, json.dumps(ir, sort_keys=True))
+        if key not in self.items:
+            name = '_agg%d' % len(self.order)
+            self.items[key] = name
+            spec = {'name': name, 'fn': fn}
+            if ir is not None:
+                spec['expr'] = ir
+            self.order.append(spec)
+        return self.items[key]
+
+    def specs(self):
+        return [dict(s) for s in self.order]
+
+
+def plan_sql(sql_text, distributed=False):
+    """SQL text -> plan dict ({'root': ..., 'output': [...]} [+ 'partial'])."""
+    body = '\n'.join(l for l in sql_text.split('\n') if not l.strip().startswith('--'))
+    try:
+        ast = parse(body)
+    except SqlError as e:
+        raise PlanError(str(e))
+    return Planner(ast).plan(distributed=distributed)

@@ -1,0 +1,307 @@
+"""A small SQL front-end for the NDS star-join/aggregate query shape.
+
+In the reference, `spark_session.sql(query)` (/root/reference/nds/nds_power.py:130) parses and
+plans the statement inside Spark (Catalyst).  No JVM exists on the build or GPU boxes, so the host
+side carries its own parser for the subset of Spark SQL the supported templates use:
+
+    SELECT <exprs [AS alias]> FROM <t [alias], ...> [WHERE <expr>] [GROUP BY ...]
+    [ORDER BY <expr [ASC|DESC] [NULLS FIRST|LAST]>, ...] [LIMIT n]
+
+Anything outside the subset raises SqlError - the statement is never silently approximated.
+The AST is plain tuples:  ('col', qualifier|None, name) | ('num', text) | ('str', value) | ('null',)
+ | ('call', fname, [args], distinct) | ('bin', op, l, r) | ('not', x) | ('neg', x)
+ | ('isnull', x, negated) | ('between', x, lo, hi, negated) | ('in', x, [items], negated)
+ | ('case', [(cond, value)...], else|None) | ('cast', x, typename) | ('star',)
+"""
+import re
+
+
+class SqlError(ValueError):
+    pass
+
+
+_TOKEN = re.compile(r"""
+    \s+ | --[^\n]* |
+    (?P<num>\d+\.\d*|\.\d+|\d+) |
+    (?P<str>'(?:[^']|'')*') |
+    (?P<bq>`[^`]*`) |
+    (?P<id>[A-Za-z_][A-Za-z_0-9]*) |
+    (?P<op><>|!=|<=|>=|\|\||[=<>+\-*/(),.;])
+""", re.X)
+
+KEYWORDS = {'select', 'from', 'where', 'group', 'by', 'order', 'limit', 'as', 'and', 'or', 'not', 'is', 'null',
+            'between', 'in', 'asc', 'desc', 'nulls', 'first', 'last', 'case', 'when', 'then', 'else', 'end',
+            'cast', 'distinct', 'having', 'union', 'intersect', 'except', 'join', 'on', 'inner', 'left',
+            'right', 'full', 'outer', 'with', 'over', 'partition', 'rollup', 'exists', 'interval', 'like'}
+
+
+def tokenize(text):
+    out = []
+    pos = 0
+    while pos < len(text):
+        m = _TOKEN.match(text, pos)
+        if not m:
+            raise SqlError('cannot tokenize SQL at: %r' % text[pos:pos + 30])
+        pos = m.end()
+        if m.lastgroup is None:
+            continue
+        v = m.group(m.lastgroup)
+        if m.lastgroup == 'id':
+            lv = v.lower()
+            out.append(('kw', lv) if lv in KEYWORDS else ('id', lv))
+        elif m.lastgroup == 'bq':
+            out.append(('id', v[1:-1]))
+        elif m.lastgroup == 'str':
+            out.append(('str', v[1:-1].replace("''", "'")))
+        else:
+            out.append((m.lastgroup, v))
+    out.append(('eof', ''))
+    return out
+
+
+class Parser:
+    def __init__(self, text):
+        self.t = tokenize(text)
+        self.i = 0
+
+    def peek(self, k=0):
+        return self.t[min(self.i + k, len(self.t) - 1)]
+
+    def next(self):
+        tok = self.t[self.i]
+        self.i += 1
+        return tok
+
+    def accept(self, kind, val=None):
+        tok = self.peek()
+        if tok[0] == kind and (val is None or tok[1] == val):
+            self.i += 1
+            return tok
+        return None
+
+    def expect(self, kind, val=None):
+        tok = self.accept(kind, val)
+        if not tok:
+            raise SqlError('expected %s %s, found %r' % (kind, val or '', self.peek()[1]))
+        return tok
+
+    def kw(self, word):
+        return self.accept('kw', word)
+
+    # ---- statement -----------------------------------------------------------------------------
+    def parse_query(self):
+        if self.peek() == ('kw', 'with'):
+            raise SqlError('WITH (common table expressions) is not supported by the B200 planner yet')
+        self.expect('kw', 'select')
+        if self.kw('distinct'):
+            raise SqlError('SELECT DISTINCT is not supported by the B200 planner yet')
+        select = [self.select_item()]
+        while self.accept('op', ','):
+            select.append(self.select_item())
+        self.expect('kw', 'from')
+        tables = [self.table_ref()]
+        while self.accept('op', ','):
+            tables.append(self.table_ref())
+        if self.peek()[0] == 'kw' and self.peek()[1] in ('join', 'inner', 'left', 'right', 'full'):
+            raise SqlError('explicit JOIN syntax is not supported by the B200 planner yet')
+        where = self.expr() if self.kw('where') else None
+        group = []
+        if self.kw('group'):
+            self.expect('kw', 'by')
+            if self.peek() == ('kw', 'rollup'):
+                raise SqlError('GROUP BY ROLLUP is not supported by the B200 planner yet')
+            group.append(self.expr())
+            while self.accept('op', ','):
+                group.append(self.expr())
+        if self.kw('having'):
+            raise SqlError('HAVING is not supported by the B200 planner yet')
+        order = []
+        if self.kw('order'):
+            self.expect('kw', 'by')
+            order.append(self.order_item())
+            while self.accept('op', ','):
+                order.append(self.order_item())
+        limit = None
+        if self.kw('limit'):
+            limit = int(self.expect('num')[1])
+        self.accept('op', ';')
+        if self.peek()[0] != 'eof':
+            raise SqlError('unsupported trailing SQL: %r' % self.peek()[1])
+        return {'select': select, 'from': tables, 'where': where, 'group': group, 'order': order, 'limit': limit}
+
+    def select_item(self):
+        if self.accept('op', '*'):
+            raise SqlError('SELECT * is not supported by the B200 planner yet')
+        e = self.expr()
+        alias = None
+        if self.kw('as'):
+            alias = self.expect('id')[1]
+        elif self.peek()[0] == 'id':
+            alias = self.next()[1]
+        return (e, alias)
+
+    def table_ref(self):
+        if self.peek() == ('op', '('):
+            raise SqlError('derived tables (subqueries in FROM) are not supported by the B200 planner yet')
+        name = self.expect('id')[1]
+        alias = None
+        if self.kw('as'):
+            alias = self.expect('id')[1]
+        elif self.peek()[0] == 'id':
+            alias = self.next()[1]
+        return (name, alias or name)
+
+    def order_item(self):
+        e = self.expr()
+        desc = False
+        if self.kw('desc'):
+            desc = True
+        else:
+            self.kw('asc')
+        nulls_first = None
+        if self.kw('nulls'):
+            if self.kw('first'):
+                nulls_first = True
+            else:
+                self.expect('kw', 'last')
+                nulls_first = False
+        return (e, desc, nulls_first)
+
+    # ---- expressions -------------------------------------------------------------------------------
+    def expr(self):
+        e = self.and_expr()
+        while self.kw('or'):
+            e = ('bin', 'or', e, self.and_expr())
+        return e
+
+    def and_expr(self):
+        e = self.not_expr()
+        while self.kw('and'):
+            e = ('bin', 'and', e, self.not_expr())
+        return e
+
+    def not_expr(self):
+        if self.kw('not'):
+            return ('not', self.not_expr())
+        return self.predicate()
+
+    def predicate(self):
+        e = self.additive()
+        tok = self.peek()
+        if tok[0] == 'op' and tok[1] in ('=', '<>', '!=', '<', '<=', '>', '>='):
+            self.next()
+            op = {'=': 'eq', '<>': 'ne', '!=': 'ne', '<': 'lt', '<=': 'le', '>': 'gt', '>=': 'ge'}[tok[1]]
+            return ('bin', op, e, self.additive())
+        if self.kw('is'):
+            neg = bool(self.kw('not'))
+            self.expect('kw', 'null')
+            return ('isnull', e, neg)
+        neg = False
+        if self.peek() == ('kw', 'not') and self.peek(1)[0] == 'kw' and self.peek(1)[1] in ('between', 'in', 'like'):
+            self.next()
+            neg = True
+        if self.kw('between'):
+            lo = self.additive()
+            self.expect('kw', 'and')
+            hi = self.additive()
+            return ('between', e, lo, hi, neg)
+        if self.kw('in'):
+            self.expect('op', '(')
+            if self.peek() == ('kw', 'select'):
+                raise SqlError('IN (subquery) is not supported by the B200 planner yet')
+            items = [self.expr()]
+            while self.accept('op', ','):
+                items.append(self.expr())
+            self.expect('op', ')')
+            return ('in', e, items, neg)
+        if self.kw('like'):
+            raise SqlError('LIKE is not supported by the B200 planner yet')
+        return e
+
+    def additive(self):
+        e = self.mult()
+        while True:
+            if self.accept('op', '+'):
+                e = ('bin', 'add', e, self.mult())
+            elif self.accept('op', '-'):
+                e = ('bin', 'sub', e, self.mult())
+            else:
+                return e
+
+    def mult(self):
+        e = self.unary()
+        while True:
+            if self.accept('op', '*'):
+                e = ('bin', 'mul', e, self.unary())
+            elif self.accept('op', '/'):
+                e = ('bin', 'div', e, self.unary())
+            else:
+                return e
+
+    def unary(self):
+        if self.accept('op', '-'):
+            return ('neg', self.unary())
+        if self.accept('op', '+'):
+            return self.unary()
+        return self.primary()
+
+    def primary(self):
+        tok = self.next()
+        if tok[0] == 'num':
+            return ('num', tok[1])
+        if tok[0] == 'str':
+            return ('str', tok[1])
+        if tok == ('kw', 'null'):
+            return ('null',)
+        if tok == ('op', '('):
+            if self.peek() == ('kw', 'select'):
+                raise SqlError('scalar subqueries are not supported by the B200 planner yet')
+            e = self.expr()
+            self.expect('op', ')')
+            return e
+        if tok == ('kw', 'case'):
+            whens = []
+            if self.peek() != ('kw', 'when'):
+                raise SqlError('CASE <expr> WHEN is not supported; use CASE WHEN <cond>')
+            while self.kw('when'):
+                c = self.expr()
+                self.expect('kw', 'then')
+                whens.append((c, self.expr()))
+            other = self.expr() if self.kw('else') else None
+            self.expect('kw', 'end')
+            return ('case', whens, other)
+        if tok == ('kw', 'cast'):
+            self.expect('op', '(')
+            e = self.expr()
+            self.expect('kw', 'as')
+            tname = self.expect('id')[1]
+            if self.accept('op', '('):
+                args = [self.expect('num')[1]]
+                while self.accept('op', ','):
+                    args.append(self.expect('num')[1])
+                self.expect('op', ')')
+                tname += '(%s)' % ','.join(args)
+            self.expect('op', ')')
+            return ('cast', e, tname)
+        if tok[0] == 'id':
+            if self.accept('op', '('):
+                distinct = bool(self.kw('distinct'))
+                args = []
+                if self.accept('op', '*'):
+                    args.append(('star',))
+                elif self.peek() != ('op', ')'):
+                    args.append(self.expr())
+                    while self.accept('op', ','):
+                        args.append(self.expr())
+                self.expect('op', ')')
+                if self.peek() == ('kw', 'over'):
+                    raise SqlError('window functions are not supported by the B200 planner yet')
+                return ('call', tok[1], args, distinct)
+            if self.accept('op', '.'):
+                return ('col', tok[1], self.expect('id')[1])
+            return ('col', None, tok[1])
+        raise SqlError('unexpected token %r' % (tok[1],))
+
+
+def parse(text):
+    return Parser(text).parse_query()

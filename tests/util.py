@@ -23,12 +23,12 @@ def read_table_like_engine(warehouse, table, columns=None):
             for f in sorted(os.listdir(p)):
                 if not f.endswith('.parquet'):
                     continue
-                t = pq.read_table(os.path.join(p, f))
+                t = pq.ParquetFile(os.path.join(p, f)).read()
                 v = None if val == HIVE_NULL else int(val)
                 t = t.append_column(pcol, pa.array([v] * t.num_rows, type=pa.int32()))
                 parts.append(t)
         elif e.endswith('.parquet'):
-            parts.append(pq.read_table(p))
+            parts.append(pq.ParquetFile(p).read())
     t = pa.concat_tables(parts)
     if columns:
         t = t.select(columns)
