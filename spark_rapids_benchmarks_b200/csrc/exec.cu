@@ -345,6 +345,16 @@ struct Exec {
       compile(arg(1), b, bb, code);
       code.push_back(Instr{OP_DIVI2F, 0, 0});
       out.kind = LType::F64;
+    } else if (fn == "div") {     // Spark: `/` on integers and doubles yields double, x / 0 = NULL
+      std::vector<Instr> ca, cb;
+      LType ta = compile(arg(0), b, bb, ca), tb = compile(arg(1), b, bb, cb);
+      if (ta.kind == LType::STR || tb.kind == LType::STR) fail("plan: division on strings");
+      to_double(ca, ta);
+      to_double(cb, tb);
+      code.insert(code.end(), ca.begin(), ca.end());
+      code.insert(code.end(), cb.begin(), cb.end());
+      code.push_back(Instr{OP_DIV_F, 0, 0});
+      out.kind = LType::F64;
     } else if (fn == "cast_double") {
       LType t = compile(arg(0), b, bb, code);
       if (t.kind == LType::STR) fail("plan: cast string -> double is not supported");

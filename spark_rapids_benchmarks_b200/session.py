@@ -1,0 +1,117 @@
+"""Engine session: the object that takes the place of the SparkSession in the harness
+(`spark_session.sql(query)` -> `.collect()` / `.write.format(f).mode('overwrite').save(path)`,
+/root/reference/nds/nds_power.py:125-135; `read.format(f).load(p).createOrReplaceTempView(t)`,
+:97-100).  SQL text is planned on the host (planner.py) and executed on the GPU through the
+C ABI (engine.py).  Unsupported statements raise."""
+import os
+import shutil
+import time
+
+import pyarrow as pa
+import pyarrow.csv as pacsv
+import pyarrow.parquet as pq
+
+from . import __version__
+from . import planner
+from .engine import Engine, EngineError
+
+
+class Row(tuple):
+    pass
+
+
+class DataFrame:
+    """The small slice of pyspark.sql.DataFrame the harness touches."""
+
+    def __init__(self, table):
+        self._t = table
+
+    @property
+    def columns(self):
+        return list(self._t.schema.names)
+
+    def toDF(self, *names):
+        return DataFrame(self._t.rename_columns(list(names)))
+
+    def collect(self):
+        cols = [c.to_pylist() for c in self._t.columns]
+        return [Row(r) for r in zip(*cols)] if cols else []
+
+    def count(self):
+        return self._t.num_rows
+
+    def toArrow(self):
+        return self._t
+
+    @property
+    def write(self):
+        return _Writer(self._t)
+
+
+class _Writer:
+    def __init__(self, table):
+        self._t, self._fmt, self._mode = table, 'parquet', 'errorifexists'
+
+    def format(self, fmt):
+        self._fmt = fmt
+        return self
+
+    def mode(self, mode):
+        self._mode = mode
+        return self
+
+    def save(self, path):
+        if os.path.exists(path):
+            if self._mode != 'overwrite':
+                raise EngineError('path %s already exists' % path)
+            shutil.rmtree(path)
+        os.makedirs(path)
+        if self._fmt == 'parquet':
+            pq.write_table(self._t, os.path.join(path, 'part-00000-b200.parquet'), compression='NONE')
+        elif self._fmt == 'csv':
+            pacsv.write_csv(self._t, os.path.join(path, 'part-00000-b200.csv'))
+        else:
+            raise EngineError("output format '%s' is not supported by the B200 engine (parquet, csv)" % self._fmt)
+        open(os.path.join(path, '_SUCCESS'), 'w').close()
+
+
+class Session:
+    def __init__(self, app_name='NDS', conf=None, device=None, rank=0, world=1, comm=None, keep_host=False):
+        self.conf = dict(conf or {})
+        self.app_name = app_name
+        self.version = 'nds_b200 ' + __version__
+        self.application_id = 'b200-%d' % int(time.time() * 1000)
+        self.rank, self.world, self.comm = rank, world, comm
+        if device is None:
+            device = int(self.conf.get('b200.device', os.environ.get('LOCAL_RANK', 0)))
+        self.source = self.conf.get('b200.source', 'hbm')
+        self.engine = Engine(device=device, resident=True, keep_host=keep_host or self.source == 'host',
+                             rank=rank, world=world)
+        self.last_stats = None
+
+    def conf_items(self):
+        d = dict(self.conf)
+        d.update({'b200.rank': str(self.rank), 'b200.world': str(self.world), 'spark.app.name': self.app_name})
+        return d.items()
+
+    def register_table(self, name, path, fmt='parquet'):
+        self.engine.register_table(name, path, fmt)
+
+    def plan(self, query):
+        return planner.plan_sql(query, distributed=self.world > 1)
+
+    def sql(self, query):
+        plan = self.plan(query)
+        return DataFrame(self.execute_plan(plan))
+
+    def execute_plan(self, plan):
+        if self.world > 1:
+            from . import dist
+            batch = dist.execute_distributed(self, plan)
+        else:
+            batch = self.engine.execute({'root': plan['root']}, source=self.source if self.source != 'hbm' else None)
+        self.last_stats = self.engine.last_stats()
+        return pa.Table.from_batches([batch]) if isinstance(batch, pa.RecordBatch) else batch
+
+    def stop(self):
+        self.engine.close()

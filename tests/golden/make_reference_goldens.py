@@ -1,0 +1,264 @@
+"""Generates tests/golden/reference_harness.json by IMPORTING THE REFERENCE'S OWN PYTHON
+(/root/reference/nds/*.py) in the build container and recording what its pure-Python functions
+return on fixed inputs.  pyspark is not installed, so the modules are imported under a stub
+`pyspark` package; only functions that never touch Spark are exercised:
+
+    nds_power.gen_sql_from_stream / ensure_valid_column_names / load_properties / get_query_subset
+    nds_gen_query_stream.split_special_query
+    nds_validate.compare / rowEqual / check_nth_col_problematic_q78 / update_summary
+    PysparkBenchReport.report_on / write_summary / is_success   (with a fake session object)
+    nds_bench.get_power_time / get_start_end_time               (parsing a time log written by THIS repo)
+
+Run:  python tests/golden/make_reference_goldens.py      (needs /root/reference; not run on the GPU box)
+"""
+import decimal
+import glob
+import io
+import json
+import math
+import os
+import sys
+import tempfile
+import types
+import contextlib
+
+REF = '/root/reference/nds'
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+
+
+def install_stub_pyspark():
+    def mod(name):
+        m = types.ModuleType(name)
+        sys.modules[name] = m
+        return m
+    ps = mod('pyspark')
+    sql = mod('pyspark.sql')
+    typ = mod('pyspark.sql.types')
+    fun = mod('pyspark.sql.functions')
+    jg = mod('pyspark.java_gateway')
+    ps.sql = sql
+    sql.types = typ
+    sql.functions = fun
+
+    class _T:
+        def __init__(self, *a, **k):
+            self.a = a
+
+        @classmethod
+        def typeName(cls):
+            return cls.__name__.replace('Type', '').lower()
+    for n in ['StructType', 'StructField', 'IntegerType', 'LongType', 'DoubleType', 'FloatType', 'StringType', 'DateType',
+              'DecimalType', 'VarcharType', 'CharType', 'TimestampType', 'ShortType', 'ByteType', 'BooleanType']:
+        setattr(typ, n, type(n, (_T,), {}))
+    typ.__all__ = [n for n in dir(typ) if n.endswith('Type') or n == 'StructField']
+    sql.SparkSession = type('SparkSession', (), {})
+    sql.DataFrame = type('DataFrame', (), {})
+    ps.SparkContext = type('SparkContext', (), {})
+    fun.col = lambda n: n
+    jg.ensure_callback_server_started = lambda gw=None: None
+
+
+class FakeDF:
+    def __init__(self, columns):
+        self.columns = list(columns)
+
+    def toDF(self, *names):
+        return FakeDF(names)
+
+
+STREAM = """-- start query 1 in stream 0 using template query3.tpl
+select a, b from t where x = 1
+ LIMIT 100;
+
+-- end query 1 in stream 0 using template query3.tpl
+-- start query 2 in stream 0 using template query14.tpl
+with cs as (select 1) select * from cs limit 100;
+ select k, sum(v) from u group by k
+ limit 100;
+
+-- end query 2 in stream 0 using template query14.tpl
+-- start query 3 in stream 0 using template query98.tpl
+select 'x;y' from w order by 1;
+
+-- end query 3 in stream 0 using template query98.tpl
+"""
+
+PROPS = """#
+# comment line = with equals
+spark.sql.adaptive.enabled=true
+spark.executor.memory = 16g
+b200.source=host
+novalue
+k=a=b
+"""
+
+Q78 = """-- start query 78 in stream 0 using template query78.tpl
+with ws as (select 1 from web_sales), ss as (select 2 from store_sales)
+select ss_sold_year, ss_item_sk, ss_customer_sk,
+round(ss_qty/(coalesce(ws_qty,0)+coalesce(cs_qty,0)),2) ratio,
+ss_qty store_qty
+from ss limit 100;
+"""
+
+
+def main():
+    install_stub_pyspark()
+    sys.path.insert(0, REF)
+    import nds_power as ref_power
+    import nds_validate as ref_validate
+    import nds_gen_query_stream as ref_stream
+    import PysparkBenchReport as ref_report
+    import nds_bench as ref_bench
+    out = {'_generated_by': 'tests/golden/make_reference_goldens.py', '_reference': 'bilalbari/spark-rapids-benchmarks @ /root/reference'}
+
+    with tempfile.TemporaryDirectory() as tmp:
+        # ---- gen_sql_from_stream / split_special_query
+        sp = os.path.join(tmp, 'query_0.sql')
+        open(sp, 'w').write(STREAM)
+        d = ref_power.gen_sql_from_stream(sp)
+        out['stream_text'] = STREAM
+        out['gen_sql_from_stream'] = list(d.items())
+        block = STREAM.split('-- start')[2]
+        out['split_special_query'] = {'input': block, 'output': list(ref_stream.split_special_query(block))}
+        # ---- get_query_subset
+        out['get_query_subset'] = {'subset': ['query98', 'query14_part2'],
+                                   'keys': list(ref_power.get_query_subset(d, ['query98', 'query14_part2']).keys())}
+        try:
+            ref_power.get_query_subset(d, ['query1'])
+            out['get_query_subset']['missing_error'] = None
+        except Exception as e:
+            out['get_query_subset']['missing_error'] = str(e)
+        # ---- ensure_valid_column_names
+        cases = [['d_year', 'brand_id', 'sum(ss_ext_sales_price)'], ['a', 'a', 'b', 'a'], ['1abc', 'x-y', '_ok', 'c d e'],
+                 ['count(1)', 'count(1)', 'avg(x)'], ['ünï', 'col#1', 'col#1'], ['a', 'a0', 'a']]
+        out['ensure_valid_column_names'] = [{'in': c, 'out': ref_power.ensure_valid_column_names(FakeDF(c)).columns} for c in cases]
+        # ---- load_properties
+        pp = os.path.join(tmp, 'x.properties')
+        open(pp, 'w').write(PROPS)
+        out['load_properties'] = {'text': PROPS, 'out': ref_power.load_properties(pp)}
+        # ---- compare
+        D = decimal.Decimal
+        vals = [1, 2, 1.0, 1.000001, 1.1, float('nan'), float('inf'), 0.0, -0.0, 1e-12, 'a', 'b', '', None, D('1.00'), D('1.000009'),
+                D('1.01'), D('0'), D('100000.00'), D('100000.99'), True, False]
+
+        def enc(v):
+            if isinstance(v, D):
+                return {'dec': str(v)}
+            if isinstance(v, float):
+                return {'f': repr(v)}
+            return v
+        cmp_rows = []
+        for a in vals:
+            for b in vals:
+                for eps in (0.00001, 0.01):
+                    try:
+                        r = bool(ref_validate.compare(a, b, eps))
+                    except Exception as e:   # the reference raises on Decimal vs float isclose? record it
+                        r = 'EXC:' + type(e).__name__
+                    cmp_rows.append([enc(a), enc(b), eps, r])
+        out['compare'] = cmp_rows
+        # ---- rowEqual incl. q78
+        rows = [([1, 'a', 2.0], [1, 'a', 2.00001], 0.00001, False, 2),
+                ([1, 'a', 2.0], [1, 'b', 2.0], 0.00001, False, 2),
+                ([1, 0.50, 3, 4.0], [1, 0.505, 3, 4.0], 0.00001, True, 2),
+                ([1, 0.50, 3, 4.0], [1, 0.52, 3, 4.0], 0.00001, True, 2),
+                ([1, None, 3, 4.0], [1, None, 3, 4.0], 0.00001, True, 2),
+                ([1, None, 3, 4.0], [1, 0.1, 3, 4.0], 0.00001, True, 2),
+                ([1, 2, 3, 0.25], [1, 2, 3, 0.2599], 0.00001, True, 4),
+                ([1, 0.0, 3, 4.0], [1, 0.0, 3, 4.0], 0.00001, True, 2)]
+        re_out = []
+        for r1, r2, eps, q78, col in rows:
+            re_out.append({'row1': r1, 'row2': r2, 'epsilon': eps, 'is_q78': q78, 'col': col,
+                           'out': bool(ref_validate.rowEqual(list(r1), list(r2), eps, q78, col))})
+        try:
+            ref_validate.rowEqual([1, 2, 3], [1, 2, 3], 0.00001, True, 3)
+            bad = None
+        except Exception as e:
+            bad = str(e)
+        out['rowEqual'] = {'cases': re_out, 'bad_col_error': bad}
+        out['check_nth_col_problematic_q78'] = {'text': Q78, 'out': ref_validate.check_nth_col_problematic_q78(Q78)}
+        # ---- PysparkBenchReport with a fake session
+        class FakeConf:
+            def getAll(self):
+                return [('spark.app.name', 'x'), ('k', 'v')]
+
+        class FakeSC:
+            _conf = FakeConf()
+
+        class FakeSession:
+            sparkContext = FakeSC()
+            version = '3.1.2-fake'
+        os.environ['TOKEN'] = 'secret-token'
+        os.environ['MY_TOKEN'] = 'kept'
+
+        # python_listener.PythonListener().register() needs a JVM: make it raise TypeError like a missing jar does
+        import python_listener
+        python_listener.PythonListener.register = lambda self: (_ for _ in ()).throw(TypeError("'JavaPackage' object is not callable"))
+        rep = ref_report.PysparkBenchReport(FakeSession(), 'query3')
+        with contextlib.redirect_stdout(io.StringIO()):
+            s = rep.report_on(lambda a, b: None, 1, 2)
+        ok_keys = sorted(s.keys())
+        prefix = os.path.join(tmp, 'aqe-on')
+        rep.write_summary(prefix=prefix)
+        written = json.load(open(glob.glob(prefix + '-query3-*.json')[0]))
+        rep2 = ref_report.PysparkBenchReport(FakeSession(), 'query7')
+        with contextlib.redirect_stdout(io.StringIO()):
+            s2 = rep2.report_on(lambda: (_ for _ in ()).throw(ValueError('boom')))
+        out['bench_report'] = {
+            'summary_keys': ok_keys, 'env_keys': sorted(s['env'].keys()), 'status_ok': s['queryStatus'], 'is_success_ok': rep.is_success(),
+            'token_redacted': 'TOKEN' not in s['env']['envVars'], 'my_token_kept': 'MY_TOKEN' in s['env']['envVars'],
+            'written_keys': sorted(written.keys()), 'filename_pattern_ok': os.path.basename(written['filename']) ==
+            'aqe-on-query3-%d.json' % written['startTime'],
+            'status_fail': s2['queryStatus'], 'exceptions_fail': s2['exceptions'], 'is_success_fail': rep2.is_success(),
+            'times_len': len(s['queryTimes']), 'spark_conf': s['env']['sparkConf'], 'spark_version': s['env']['sparkVersion']}
+        # ---- update_summary
+        jf = os.path.join(tmp, 'json')
+        os.makedirs(jf)
+        for q, st in (('query3', ['Completed']), ('query7', ['Failed']), ('query19', ['CompletedWithTaskFailures']), ('query42', ['Completed'])):
+            json.dump({'query': q, 'queryStatus': st}, open(os.path.join(jf, 'p-%s-123.json' % q), 'w'))
+        ref_validate.query_dict = {'query3': '', 'query7': '', 'query19': '', 'query42': ''}
+        with contextlib.redirect_stdout(io.StringIO()):
+            ref_validate.update_summary(jf, ['query7', 'query19', 'query42'])
+        out['update_summary'] = {q: json.load(open(os.path.join(jf, 'p-%s-123.json' % q)))['queryValidationStatus']
+                                 for q in ('query3', 'query7', 'query19', 'query42')}
+        # ---- the reference's own time-log parsers on a log written by THIS repo's nds_power
+        sys.path.insert(0, ROOT)
+        import pyarrow as pa
+        from spark_rapids_benchmarks_b200 import nds_power as my_power
+        from spark_rapids_benchmarks_b200.session import DataFrame
+
+        class StubSession:
+            application_id = 'b200-test'
+            version = 'stub'
+
+            def conf_items(self):
+                return {}.items()
+
+            def register_table(self, *a):
+                pass
+
+            def sql(self, q):
+                return DataFrame(pa.table({'x': [1]}))
+
+            def stop(self):
+                pass
+        log = os.path.join(tmp, 'time.csv')
+        mine = my_power.gen_sql_from_stream(sp)
+        with contextlib.redirect_stdout(io.StringIO()):
+            my_power.run_query_stream(tmp, None, mine, log, None, None, session=StubSession())
+        text = open(log).read()
+        pt = ref_bench.get_power_time(log)
+        st, en = ref_bench.get_start_end_time(log)
+        assert pt.isdigit() and st.isdigit() and en.isdigit() and int(en) >= int(st)
+        lines = text.strip().split('\n')
+        out['time_log'] = {'header': lines[0], 'labels': [l.split(',')[1] for l in lines[1:]],
+                           'reference_parsers_accept_it': True,
+                           'n_rows': len(lines) - 1}
+    with open(os.path.join(HERE, 'reference_harness.json'), 'w') as f:
+        json.dump(out, f, indent=1, sort_keys=True)
+    print('wrote', os.path.join(HERE, 'reference_harness.json'), len(out['compare']), 'compare cases')
+
+
+if __name__ == '__main__':
+    main()

@@ -1,0 +1,100 @@
+"""GPU parity, end to end: SQL text -> planner -> C ABI -> CUDA kernels, against the CPU oracle on the
+same seeded warehouse.  Bit exact for integers, strings, decimals and row order (ties broken by the
+remaining columns on both sides); AVG(bigint) doubles compared with nds_validate's epsilon 1e-5."""
+import contextlib
+import glob
+import io
+import math
+import os
+
+import pytest
+
+from oracle import nds_queries as oq
+from spark_rapids_benchmarks_b200 import nds_power, nds_validate, streams
+from spark_rapids_benchmarks_b200.session import Session
+
+pytestmark = pytest.mark.gpu
+
+PARAMS = [{'MANUFACT': 606, 'MANAGER': 63, 'MONTH': 1, 'YEAR': 1998},
+          {'MANUFACT': 1, 'MANAGER': 1, 'MONTH': 2, 'YEAR': 1998},
+          {'MANUFACT': 9999, 'MANAGER': 9999, 'MONTH': 1, 'YEAR': 1998},      # empty dimension side
+          {'MONTH': 7, 'YEAR': 2001, 'MANUFACT': 606, 'MANAGER': 63}]         # no partition survives pruning
+
+
+class _Sess(Session):
+    """Session over the shared test engine (tables already registered)."""
+
+    def __init__(self, eng, source='hbm'):
+        self.conf, self.app_name, self.version, self.application_id = {}, 't', 'test', 'b200-test'
+        self.rank, self.world, self.comm, self.source, self.engine, self.last_stats = 0, 1, None, source, eng, None
+
+    def stop(self):
+        pass
+
+
+def rows_equal(got, exp):
+    if len(got) != len(exp):
+        return False
+    for g, e in zip(got, exp):
+        if g.keys() != e.keys():
+            return False
+        for k in g:
+            if isinstance(e[k], float) and e[k] is not None and g[k] is not None:
+                if not math.isclose(g[k], e[k], rel_tol=1e-5):
+                    return False
+            elif g[k] != e[k]:
+                return False
+    return True
+
+
+@pytest.mark.parametrize('query', streams.SUBSET)
+@pytest.mark.parametrize('pi', range(len(PARAMS)))
+def test_query_matches_oracle(gpu_engine, warehouse, query, pi):
+    sql = streams.render(query, overrides=PARAMS[pi])
+    exp = oq.run_query(query, sql, warehouse)
+    for source in ('hbm', 'host'):
+        got = _Sess(gpu_engine, source).sql(sql).toArrow()
+        assert got.schema.names == exp.schema.names
+        assert [str(t) for t in got.schema.types] == [str(t) for t in exp.schema.types], (got.schema, exp.schema)
+        assert rows_equal(got.to_pylist(), exp.to_pylist()), (query, source, got.to_pylist()[:3], exp.to_pylist()[:3])
+
+
+def test_power_run_then_validate_against_oracle(gpu_engine, warehouse, tmp_path):
+    """nds_power-compatible run on the GPU, oracle outputs written beside it, nds_validate-compatible
+    comparison of the two folders - the reference's own correctness procedure."""
+    import pyarrow.parquet as pq
+    stream = str(tmp_path / 'query_0.sql')
+    streams.generate_stream(stream, overrides=PARAMS[0])
+    qd = nds_power.gen_sql_from_stream(stream)
+    out_gpu, out_cpu, js = str(tmp_path / 'gpu'), str(tmp_path / 'cpu'), str(tmp_path / 'json')
+    sess = _Sess(gpu_engine)
+    sess.register_table = lambda *a: None
+    with contextlib.redirect_stdout(io.StringIO()):
+        rows = nds_power.run_query_stream(warehouse, None, qd, str(tmp_path / 'time.csv'), None, None, output_path=out_gpu,
+                                          json_summary_folder=js, session=sess)
+    assert [r[1] for r in rows if r[1].startswith('query')] == streams.SUBSET
+    for q, sql in qd.items():
+        t = oq.run_query(q, sql, warehouse)
+        os.makedirs(os.path.join(out_cpu, q))
+        df = nds_power.ensure_valid_column_names(__import__('spark_rapids_benchmarks_b200.session', fromlist=['DataFrame']).DataFrame(t))
+        pq.write_table(df.toArrow(), os.path.join(out_cpu, q, 'part-0.parquet'))
+    with contextlib.redirect_stdout(io.StringIO()):
+        assert nds_validate.main([out_gpu, out_cpu, stream, '--json_summary_folder', js]) == []
+        assert nds_validate.main([out_gpu, out_cpu, stream, '--ignore_ordering']) == []
+    import json
+    for q in qd:
+        f = glob.glob(os.path.join(js, '*%s-*.json' % q))
+        assert len(f) == 1 and json.load(open(f[0]))['queryValidationStatus'] == ['Pass']
+
+
+def test_unsupported_statement_is_reported_failed(gpu_engine, tmp_path):
+    sess = _Sess(gpu_engine)
+    sess.register_table = lambda *a: None
+    stream = tmp_path / 'q.sql'
+    stream.write_text('-- start query 1 in stream 0 using template query98.tpl\n'
+                      'select i_item_id, rank() over (partition by i_class order by i_item_id) from item\n;\n'
+                      '-- end query 1 in stream 0 using template query98.tpl\n')
+    qd = nds_power.gen_sql_from_stream(str(stream))
+    with contextlib.redirect_stdout(io.StringIO()):
+        with pytest.raises(SystemExit):
+            nds_power.run_query_stream(str(tmp_path), None, qd, str(tmp_path / 't.csv'), None, None, session=sess)

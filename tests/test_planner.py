@@ -1,0 +1,76 @@
+"""CPU: SQL front-end and planner (host logic standing in for Catalyst on this path)."""
+import json
+
+import pytest
+
+from spark_rapids_benchmarks_b200 import planner, sql, streams
+
+
+def _walk(n, f):
+    f(n)
+    for k in ('child', 'probe', 'build'):
+        if k in n:
+            _walk(n[k], f)
+
+
+@pytest.mark.parametrize('query', streams.SUBSET)
+def test_plans_are_star_joins_with_pruning(query):
+    p = planner.plan_sql(streams.render(query))
+    ops, prune, scans = [], [], []
+    _walk(p['root'], lambda n: (ops.append(n['op']), prune.append(n.get('prune_partitions', False)),
+                                scans.append(n.get('table')) if n['op'] == 'scan' else None))
+    assert ops[0] == 'sort' and 'aggregate' in ops and 'join' in ops
+    assert any(prune), 'the date join must carry dynamic partition pruning'
+    assert 'store_sales' in scans
+    json.dumps(p)     # serialisable
+
+
+def test_output_names_and_types():
+    p = planner.plan_sql(streams.render('query42'))
+    assert [o['name'] for o in p['output']] == ['d_year', 'i_category_id', 'i_category', 'sum(ss_ext_sales_price)']
+    assert p['output'][-1]['type'] == 'decimal(17,2)'
+    p7 = planner.plan_sql(streams.render('query7'))
+    assert [o['type'] for o in p7['output']] == ['string', 'double', 'decimal(11,6)', 'decimal(11,6)', 'decimal(11,6)']
+
+
+def test_snowflake_join_goes_through_customer():
+    p = planner.plan_sql(streams.render('query19'))
+    found = []
+    _walk(p['root'], lambda n: found.append((n.get('probe_key'), n.get('build_key'))) if n['op'] == 'join' else None)
+    assert ('c_current_addr_sk', 'ca_address_sk') in found and ('ss_customer_sk', 'c_customer_sk') in found
+
+
+def test_distributed_plan_splits_at_the_aggregate():
+    p = planner.plan_sql(streams.render('query7'), distributed=True)
+    assert p['partial']['op'] == 'aggregate'
+    fns = [a['fn'] for a in p['partial']['aggs']]
+    assert 'avg' not in fns and 'sum' in fns and 'count' in fns
+    scans = []
+    _walk(p['root'], lambda n: scans.append(n['table']) if n['op'] == 'scan' else None)
+    assert scans == ['__partial__']
+
+
+@pytest.mark.parametrize('text', [
+    'select * from item',
+    'select i_item_sk from item where i_item_sk in (select ss_item_sk from store_sales)',
+    'select i_item_sk, rank() over (partition by i_brand order by i_item_sk) from item',
+    'select i_brand, sum(i_item_sk) from item group by rollup(i_brand)',
+    'with x as (select 1) select * from x',
+    'select i_item_sk from item, store',                                     # cross join
+    'select ss_item_sk from store_sales, store_returns where ss_item_sk = sr_item_sk',   # fact-fact join
+    'select distinct i_brand from item',
+    'select i_brand from item where i_brand like \'a%\'',
+    'select i_brand, count(distinct i_item_sk) from item group by i_brand',
+    'select nope from item',
+])
+def test_unsupported_sql_raises(text):
+    with pytest.raises(planner.PlanError):
+        planner.plan_sql(text)
+
+
+def test_parser_details():
+    q = sql.parse("select a.x y, sum(b) from t a where x between 1 and 2 and s not in ('p','q') or z is not null "
+                  "order by y desc nulls first, 2 limit 5")
+    assert q['limit'] == 5 and q['from'] == [('t', 'a')] and q['select'][0][1] == 'y'
+    assert q['order'][0][1] is True and q['order'][0][2] is True
+    assert q['where'][0] == 'bin' and q['where'][1] == 'or'
