@@ -1,0 +1,73 @@
+"""Multi-GPU plumbing: one process (and one engine) per GPU under torchrun; the hive-partitioned fact
+tables are sharded by file (engine cfg rank/world), dimension tables are replicated, every rank
+runs scan -> joins -> PARTIAL aggregate on its shard, the partial group states are all-gathered and
+every rank merges them with the final aggregate + project + sort on its own GPU.
+
+This is the one exchange step the star-join subset has (Spark: HashAggregate(partial) ->
+ShuffleExchange -> HashAggregate(final)).  torch.distributed is the
+transport (NCCL over NVLink on the GPU box, gloo in the CPU tests); group states are a few KB to a
+few MB, so the step is latency-bound, not bandwidth-bound.
+"""
+import io
+
+import pyarrow as pa
+
+
+def serialize_batch(batch):
+    sink = io.BytesIO()
+    with pa.ipc.new_stream(sink, batch.schema) as w:
+        if batch.num_rows:
+            w.write_batch(batch)
+    return sink.getvalue()
+
+
+def deserialize_table(buf):
+    return pa.ipc.open_stream(pa.BufferReader(buf)).read_all()
+
+
+def all_gather_bytes(payload, group=None):
+    """Variable-length all-gather of one bytes object per rank over torch.distributed."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    backend = dist.get_backend(group)
+    dev = torch.device('cuda', torch.cuda.current_device()) if backend == 'nccl' else torch.device('cpu')
+    n = torch.tensor([len(payload)], dtype=torch.int64, device=dev)
+    sizes = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
+    dist.all_gather(sizes, n, group=group)
+    sizes = [int(s.item()) for s in sizes]
+    m = max(max(sizes), 1)
+    send = torch.zeros(m, dtype=torch.uint8)
+    if payload:
+        send[:len(payload)] = torch.frombuffer(bytearray(payload), dtype=torch.uint8)
+    send = send.to(dev)
+    recv = torch.empty(world * m, dtype=torch.uint8, device=dev)
+    dist.all_gather_into_tensor(recv, send, group=group)
+    host = recv.cpu().numpy()
+    return [host[r * m:r * m + sizes[r]].tobytes() for r in range(world)]
+
+
+def all_gather_batches(batch, group=None):
+    """Each rank contributes one record batch; every rank gets the concatenation (rank order)."""
+    parts = [deserialize_table(b) for b in all_gather_bytes(serialize_batch(batch), group)]
+    return pa.concat_tables(parts).combine_chunks()
+
+
+def merge_and_finish(engine, plan, tables, source=None):
+    """Final step shared by the torchrun path and the one-GPU emulation: register the gathered partial
+    states as `__partial__` and run the merge aggregate + projection + sort on the GPU."""
+    merged = pa.concat_tables(tables).combine_chunks() if len(tables) != 1 else tables[0].combine_chunks()
+    engine.register_arrow('__partial__', merged)
+    try:
+        return engine.execute({'root': plan['root']})
+    finally:
+        engine.drop_table('__partial__')
+
+
+def execute_distributed(session, plan):
+    if 'partial' not in plan:
+        raise ValueError('plan was not built with distributed=True')
+    src = session.source if session.source != 'hbm' else None
+    partial = session.engine.execute({'root': plan['partial']}, source=src)
+    gathered = all_gather_batches(partial, session.comm)
+    return merge_and_finish(session.engine, plan, [gathered])

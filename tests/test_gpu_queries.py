@@ -98,3 +98,29 @@ def test_unsupported_statement_is_reported_failed(gpu_engine, tmp_path):
     with contextlib.redirect_stdout(io.StringIO()):
         with pytest.raises(SystemExit):
             nds_power.run_query_stream(str(tmp_path), None, qd, str(tmp_path / 't.csv'), None, None, session=sess)
+
+
+@pytest.mark.parametrize('query', streams.SUBSET)
+def test_two_rank_emulation_on_one_gpu(warehouse, query):
+    """Distributed plan without collectives: two engines (rank 0/2 and 1/2) on the same GPU produce
+    partial states for their file shards; merging them gives the single-GPU answer and the oracle's."""
+    import os
+    from spark_rapids_benchmarks_b200 import dist as ndist, engine, nds_schema, planner
+    import pyarrow as pa
+    sql = streams.render(query, overrides=PARAMS[0])
+    plan = planner.plan_sql(sql, distributed=True)
+    partials, engines = [], []
+    for r in range(2):
+        eng = engine.Engine(device=0, rank=r, world=2)
+        for t in nds_schema.get_schemas(True):
+            eng.register_table(t, os.path.join(warehouse, t))
+        engines.append(eng)
+        partials.append(pa.Table.from_batches([eng.execute({'root': plan['partial']})]))
+    info = [e.table_info('store_sales') for e in engines]
+    assert info[0]['files'] + info[1]['files'] == 41 and abs(info[0]['files'] - info[1]['files']) <= 1
+    assert info[0]['rows'] + info[1]['rows'] == 28804
+    got = pa.Table.from_batches([ndist.merge_and_finish(engines[0], plan, partials)])
+    exp = oq.run_query(query, sql, warehouse)
+    assert rows_equal(got.to_pylist(), exp.to_pylist())
+    for e in engines:
+        e.close()
