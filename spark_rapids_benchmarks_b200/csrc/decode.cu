@@ -1,5 +1,5 @@
 // Parquet page decode: RLE/bit-packed hybrid definition levels -> Arrow validity bitmap,
-// RLE_DICTIONARY indices / PLAIN values -> dense device columns.  One CTA per data page.
+// RLE_DICTIONARY indices / PLAIN values -> dense device columns.  One CTA (512 threads) per data page.
 //
 // Reference boundary: the scan the reference triggers with
 //   spark_session.read.format(input_format).load(table_path)   (/root/reference/nds/nds_power.py:97-100)
@@ -8,6 +8,19 @@
 // (header>>1) groups of 8 values, LSB 0 -> RLE run of (header>>1) copies of a ceil(bw/8)-byte value;
 // data page v1 def levels carry a 4-byte little-endian length prefix; dictionary-encoded values
 // start with a 1-byte bit width.
+//
+// Structure of one page:
+//   1. the def-level bytes (a few KB) are staged in shared memory with one bulk async copy
+//      (cp.async.bulk + mbarrier, SASS UBLKCP);
+//   2. the run headers - a sequential format - are resolved in parallel: every byte position is parsed
+//      speculatively as a header by one thread per 32-byte chunk (phase A: where does a walk entering the
+//      chunk at offset e leave it, and how many values does it emit), one thread hops chunk to chunk
+//      (phase B: 1 shared-memory load per chunk instead of 1 per run), then the chunks expand their own
+//      runs into the validity bitmap (phase C);
+//   3. a block scan of popcounts gives rank(row) = index into the non-null value stream;
+//   4. the index stream's headers are chased by one warp that loads 32 predicted header positions at once
+//      (full 63-group runs are the common case) and verifies them with a ballot;
+//   5. all threads expand rows 4 at a time (independent loads in flight): bits -> dictionary -> store.
 //
 // Roofline: HBM.  Algorithmic bytes per page = payload bytes read + width*num_values written
 // + num_values/8 validity written (DESIGN.md "decode").
@@ -18,8 +31,13 @@ namespace nds {
 
 namespace {
 
-// Read `bw` (<= 32) bits starting `bit` bits after byte pointer p. Reads two aligned words;
-// the staging layout guarantees kPagePad readable bytes after each payload.
+constexpr int kT = kDecodeThreads;
+constexpr int kWords = kMaxPageValues / 32;
+constexpr int kDefStage = 8192;          // def-level bytes staged in shared memory (larger -> sequential fallback)
+constexpr int kDefSeg = 2048;            // byte positions resolved per segment of the parallel header walk
+constexpr int kChunk = 32;               // bytes per chunk of the parallel header walk
+constexpr int kUnroll = 4;
+
 __device__ __forceinline__ uint32_t extract_bits(const uint8_t* p, uint64_t bit, uint32_t bw) {
   const uint8_t* a = p + (bit >> 3);
   uintptr_t ai = reinterpret_cast<uintptr_t>(a);
@@ -27,7 +45,6 @@ __device__ __forceinline__ uint32_t extract_bits(const uint8_t* p, uint64_t bit,
   uint64_t v = (uint64_t)__ldg(w) | ((uint64_t)__ldg(w + 1) << 32);
   uint32_t sh = (uint32_t)(ai & 3) * 8 + (uint32_t)(bit & 7);
   v >>= sh;
-  // sh <= 31, bw <= 32: when sh + bw > 64 is impossible (31 + 32 = 63)
   return bw == 32 ? (uint32_t)v : ((uint32_t)v & ((1u << bw) - 1u));
 }
 
@@ -35,122 +52,275 @@ __device__ __forceinline__ uint32_t load_u32_unaligned(const uint8_t* p) {
   return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
 }
 
-struct Walker {       // sequential hybrid-run header walker state (thread 0 only)
+struct Walker {       // sequential hybrid-run header walker state
   uint32_t pos;       // byte position inside the page payload
   uint32_t end;       // end of the stream
   uint32_t k;         // values covered so far
 };
 
-// Walk up to kRunCap run headers. Writes r_start[j] (first value index of run j) and
-// r_info[j] ((payload byte pos << 1) | 1 for bit-packed, (value << 1) | 0 for RLE).
-// Returns number of runs recorded; r_start[n] holds the end index (sentinel).
-__device__ int walk_runs(const uint8_t* src, Walker& w, uint32_t bw, uint32_t limit,
-                         uint32_t* r_start, uint32_t* r_info) {
-  int n = 0;
+// One header at src[pos]: returns run byte length (header included); cnt = values, info as in the run table.
+__device__ __forceinline__ uint32_t parse_run(const uint8_t* src, uint32_t pos, uint32_t end, uint32_t bw, uint32_t& cnt,
+                                              uint32_t& info) {
+  uint32_t h = 0, s = 0, c, p = pos;
+  do {
+    c = src[p++];
+    h |= (c & 0x7F) << s;
+    s += 7;
+  } while ((c & 0x80) && s < 35 && p < end);
+  if (h & 1) {
+    info = (p << 1) | 1u;
+    cnt = (h >> 1) * 8;
+    return (p - pos) + (h >> 1) * bw;
+  }
   const uint32_t bytew = (bw + 7) >> 3;
+  uint32_t v = 0;
+  for (uint32_t b = 0; b < bytew; ++b) v |= (uint32_t)src[p + b] << (8 * b);
+  info = v << 1;
+  cnt = h >> 1;
+  return (p - pos) + bytew;
+}
+
+// Sequential walk of up to kRunCap headers (fallback for oversized def streams; single thread).
+__device__ int walk_runs_seq(const uint8_t* src, Walker& w, uint32_t bw, uint32_t limit, uint32_t* r_start, uint32_t* r_info) {
+  int n = 0;
   while (n < kRunCap && w.k < limit && w.pos < w.end) {
-    uint32_t h = 0, s = 0, c;
-    do {  // varint
-      c = src[w.pos++];
-      h |= (c & 0x7F) << s;
-      s += 7;
-    } while ((c & 0x80) && s < 35 && w.pos < w.end);
+    uint32_t cnt, info;
+    uint32_t len = parse_run(src, w.pos, w.end, bw, cnt, info);
     r_start[n] = w.k;
-    if (h & 1) {
-      uint32_t groups = h >> 1;
-      r_info[n] = (w.pos << 1) | 1u;
-      w.pos += groups * bw;
-      w.k += groups * 8;
-    } else {
-      uint32_t v = 0;
-      for (uint32_t b = 0; b < bytew; ++b) v |= (uint32_t)src[w.pos + b] << (8 * b);
-      r_info[n] = v << 1;
-      w.pos += bytew;
-      w.k += h >> 1;
-    }
+    r_info[n] = info;
+    w.pos += len;
+    w.k += cnt;
     ++n;
   }
-  if (w.k > limit) w.k = limit;  // padding values of the last bit-packed group
+  if (w.k > limit) w.k = limit;
   r_start[n] = w.k;
   return n;
 }
 
-template <typename T>
-__device__ __forceinline__ void store_val(void* out, int64_t row, T v) {
-  reinterpret_cast<T*>(out)[row] = v;
+// Value-stream headers, one warp: lanes load the 32 positions where the next headers sit if the runs are full
+// 63-group bit-packed runs (what parquet-mr and Arrow emit for long stretches), verify with a ballot, and fall
+// back to a single ordinary parse when the prediction fails.  All lanes return the same run count.
+__device__ int walk_runs_warp(const uint8_t* src, Walker& w, uint32_t bw, uint32_t limit, uint32_t* r_start, uint32_t* r_info) {
+  const int lane = threadIdx.x & 31;
+  const uint32_t S = 1 + 63 * bw;
+  int n = 0;
+  uint32_t pos = w.pos, k = w.k;
+  while (n < kRunCap && k < limit && pos < w.end) {
+    uint32_t cand = pos + (uint32_t)lane * S;
+    bool full = (cand + S <= w.end) && (src[cand] == 0x7F);
+    uint32_t m = __ballot_sync(0xFFFFFFFFu, full);
+    uint32_t lead = (m == 0xFFFFFFFFu) ? 32u : (uint32_t)(__ffs(~m) - 1);
+    uint32_t room = (uint32_t)(kRunCap - n);
+    uint32_t need = (limit - k + 503u) / 504u;
+    lead = min(lead, min(room, need));
+    if (lead > 0) {
+      if ((uint32_t)lane < lead) {
+        r_start[n + lane] = k + (uint32_t)lane * 504u;
+        r_info[n + lane] = ((cand + 1) << 1) | 1u;
+      }
+      n += (int)lead;
+      k += lead * 504u;
+      pos += lead * S;
+    } else {
+      uint32_t cnt = 0, info = 0, len = 0;
+      if (lane == 0) {
+        len = parse_run(src, pos, w.end, bw, cnt, info);
+        r_start[n] = k;
+        r_info[n] = info;
+      }
+      len = __shfl_sync(0xFFFFFFFFu, len, 0);
+      cnt = __shfl_sync(0xFFFFFFFFu, cnt, 0);
+      pos += len;
+      k += cnt;
+      ++n;
+    }
+  }
+  if (k > limit) k = limit;
+  if (lane == 0) r_start[n] = k;
+  w.pos = pos;
+  w.k = k;
+  return n;
+}
+
+__device__ __forceinline__ void set_bits(uint32_t* bm, uint32_t b0, uint32_t b1) {   // [b0, b1) <- 1
+  uint32_t b = b0;
+  while (b < b1) {
+    uint32_t wd = b >> 5, lo = b & 31;
+    uint32_t cnt = min(32u - lo, b1 - b);
+    uint32_t m = (cnt == 32 ? 0xFFFFFFFFu : ((1u << cnt) - 1u)) << lo;
+    atomicOr(&bm[wd], m);
+    b += cnt;
+  }
+}
+
+// bit-packed bw=1 payload bytes p[0..] are validity bits for rows [b0, b1)
+__device__ __forceinline__ void copy_bits(uint32_t* bm, const uint8_t* p, uint32_t b0, uint32_t b1) {
+  for (uint32_t b = b0; b < b1; b += 8) {
+    uint32_t byte = p[(b - b0) >> 3];
+    uint32_t rem = b1 - b;
+    if (rem < 8) byte &= (1u << rem) - 1u;
+    if (!byte) continue;
+    uint32_t lo = b & 31;
+    atomicOr(&bm[b >> 5], byte << lo);
+    if (lo > 24 && (byte >> (32 - lo))) atomicOr(&bm[(b >> 5) + 1], byte >> (32 - lo));
+  }
+}
+
+__device__ __forceinline__ void expand_def_run(uint32_t* bm, const uint8_t* src, uint32_t info, uint32_t b0, uint32_t b1) {
+  if (info & 1) copy_bits(bm, src + (info >> 1), b0, b1);
+  else if (info >> 1) set_bits(bm, b0, b1);
+}
+
+// ---- bulk async copy (TMA 1-D) of a 16 B aligned window into shared memory -----------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void bulk_load_wait(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* mbar, int tid) {
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(mbar)));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (tid == 0) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(mbar)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(mbar))
+                 : "memory");
+  }
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(smem_u32(mbar))
+        : "memory");
+  }
 }
 
 }  // namespace
 
-__global__ void __launch_bounds__(kDecodeThreads)
+__global__ void __launch_bounds__(kT)
 decode_pages_kernel(const PageTask* __restrict__ tasks, int* __restrict__ err) {
-  __shared__ uint32_t s_valid[kMaxPageValues / 32];
-  __shared__ uint32_t s_rank[kMaxPageValues / 32];
+  __shared__ uint32_t s_valid[kWords];
+  __shared__ uint32_t s_rank[kWords];
   __shared__ uint32_t r_start[kRunCap + 1];
   __shared__ uint32_t r_info[kRunCap];
+  __shared__ __align__(16) uint8_t s_def_raw[kDefStage + 48];
+  __shared__ uint32_t s_hop[kDefSeg];                       // phase A: (exit position << 16) | values emitted
+  __shared__ uint32_t s_entry[kDefSeg / kChunk][2];         // phase B: per chunk entry position, first value index
+  __shared__ __align__(8) uint64_t s_mbar;
   __shared__ int s_nruns;
   __shared__ int s_done;
-  __shared__ uint32_t s_warp_tot[kDecodeThreads / 32];
+  __shared__ uint32_t s_warp_tot[kT / 32];
   __shared__ Walker s_walk;
 
   const PageTask t = tasks[blockIdx.x];
   const int tid = threadIdx.x;
   const uint32_t n = t.num_values;
   const uint32_t nw = (n + 31) >> 5;
-  const bool nullable = t.valid != nullptr && t.def_len > 0;
+  const bool has_def = t.valid != nullptr && t.def_len > 0;
   uint32_t values_off = 0;
   uint32_t nn = n;  // non-null count
 
-  if (nullable) {
-    // ---- 1. definition levels (bit width 1) -> s_valid ------------------------------------
-    for (uint32_t w = tid; w < nw; w += kDecodeThreads) s_valid[w] = 0;
-    if (tid == 0) {
-      s_walk.pos = 4;
-      s_walk.end = 4 + t.def_len;
-      s_walk.k = 0;
-      s_done = 0;
-    }
-    __syncthreads();
-    for (;;) {
-      if (tid == 0) {
-        Walker w = s_walk;
-        s_nruns = walk_runs(t.src, w, 1, n, r_start, r_info);
-        s_walk = w;
-        s_done = (w.k >= n || w.pos >= w.end) ? 1 : 0;
-      }
+  if (has_def) {
+    for (uint32_t w = tid; w < nw; w += kT) s_valid[w] = 0;
+    const uint32_t L = t.def_len;
+    if (L <= (uint32_t)kDefStage) {
+      // ---- 1. stage the def-level bytes ------------------------------------------------------------------
+      const uint8_t* g0 = t.src + 4;
+      uintptr_t a0 = reinterpret_cast<uintptr_t>(g0) & ~uintptr_t(15);
+      uintptr_t a1 = (reinterpret_cast<uintptr_t>(g0) + L + 15) & ~uintptr_t(15);
+      bulk_load_wait(s_def_raw, reinterpret_cast<const void*>(a0), (uint32_t)(a1 - a0), &s_mbar, tid);
+      const uint8_t* sd = s_def_raw + (reinterpret_cast<uintptr_t>(g0) - a0);
+      // ---- 2. parallel header walk, kDefSeg byte positions at a time ----------------------------------------
+      if (tid == 0) { s_walk.pos = 0; s_walk.k = 0; s_walk.end = L; }
       __syncthreads();
-      const int nr = s_nruns;
-      for (int j = tid; j < nr; j += kDecodeThreads) {
-        uint32_t b0 = r_start[j], b1 = r_start[j + 1];
-        if (b1 > n) b1 = n;
-        uint32_t info = r_info[j];
-        if (info & 1) {                       // bit-packed: payload bits are validity bits
-          const uint8_t* p = t.src + (info >> 1);
-          for (uint32_t b = b0; b < b1; b += 8) {
-            uint32_t byte = p[(b - b0) >> 3];
-            uint32_t rem = b1 - b;
-            if (rem < 8) byte &= (1u << rem) - 1u;
-            if (byte) atomicOr(&s_valid[b >> 5], byte << (b & 31));
-            if ((b & 31) > 24 && (byte >> (32 - (b & 31)))) atomicOr(&s_valid[(b >> 5) + 1], byte >> (32 - (b & 31)));
-          }
-        } else if (info >> 1) {               // RLE run of 1s
-          uint32_t b = b0;
-          while (b < b1) {
-            uint32_t w = b >> 5, lo = b & 31;
-            uint32_t cnt = min(32u - lo, b1 - b);
-            uint32_t m = (cnt == 32 ? 0xFFFFFFFFu : ((1u << cnt) - 1u)) << lo;
-            atomicOr(&s_valid[w], m);
-            b += cnt;
+      for (;;) {
+        const uint32_t seg0 = s_walk.pos, k0 = s_walk.k;
+        if (seg0 >= L || k0 >= n) break;
+        const uint32_t seg1 = min(seg0 + (uint32_t)kDefSeg, L);
+        const uint32_t nchunks = (seg1 - seg0 + kChunk - 1) / kChunk;
+        // phase A: speculative parse of every byte position of my chunk, last to first
+        if ((uint32_t)tid < nchunks) {
+          const uint32_t cb = seg0 + tid * kChunk, ce = min(cb + (uint32_t)kChunk, seg1);
+          s_entry[tid][0] = 0xFFFFFFFFu;
+          for (uint32_t p = ce; p-- > cb;) {
+            uint32_t b0 = sd[p], h = b0 & 0x7F, hl = 1;
+            if (b0 & 0x80) {
+              uint32_t b1 = p + 1 < L ? sd[p + 1] : 0u;
+              h |= (b1 & 0x7F) << 7;
+              hl = 2;
+              if (b1 & 0x80) {
+                uint32_t b2 = p + 2 < L ? sd[p + 2] : 0u;
+                h |= (b2 & 0x7F) << 14;
+                hl = 3;     // a def-level run never needs more than 3 varint bytes (<= 65536 values)
+              }
+            }
+            uint32_t cnt = (h & 1) ? (h >> 1) * 8 : (h >> 1);
+            uint32_t nxt = p + hl + ((h & 1) ? (h >> 1) : 1u);
+            if (nxt > L) nxt = L;
+            if (nxt < ce) {
+              uint32_t f = s_hop[nxt - seg0];
+              cnt += f & 0xFFFFu;
+              nxt = f >> 16;
+            }
+            if (cnt > 0xFFFFu) cnt = 0xFFFFu;
+            s_hop[p - seg0] = (nxt << 16) | cnt;
           }
         }
+        __syncthreads();
+        // phase B: hop from chunk to chunk
+        if (tid == 0) {
+          uint32_t p = seg0, k = k0;
+          while (p < seg1 && k < n) {
+            uint32_t c = (p - seg0) / kChunk;
+            s_entry[c][0] = p;
+            s_entry[c][1] = k;
+            uint32_t f = s_hop[p - seg0];
+            k += f & 0xFFFFu;
+            p = f >> 16;
+          }
+          s_walk.pos = p;
+          s_walk.k = k > n ? n : k;
+        }
+        __syncthreads();
+        // phase C: every entered chunk expands its own runs
+        if ((uint32_t)tid < nchunks && s_entry[tid][0] != 0xFFFFFFFFu) {
+          const uint32_t ce = min(seg0 + (tid + 1) * (uint32_t)kChunk, seg1);
+          uint32_t p = s_entry[tid][0], k = s_entry[tid][1];
+          while (p < ce && k < n) {
+            uint32_t cnt, info;
+            uint32_t len = parse_run(sd, p, L, 1, cnt, info);
+            expand_def_run(s_valid, sd, info, k, min(k + cnt, n));
+            p += len;
+            k += cnt;
+          }
+        }
+        __syncthreads();
       }
+    } else {
+      // ---- oversized def stream: sequential walk straight from global memory ---------------------------------
+      if (tid == 0) { s_walk.pos = 4; s_walk.end = 4 + L; s_walk.k = 0; s_done = 0; }
       __syncthreads();
-      if (s_done) break;
+      for (;;) {
+        if (tid == 0) {
+          Walker w = s_walk;
+          s_nruns = walk_runs_seq(t.src, w, 1, n, r_start, r_info);
+          s_walk = w;
+          s_done = (w.k >= n || w.pos >= w.end) ? 1 : 0;
+        }
+        __syncthreads();
+        const int nr = s_nruns;
+        for (int j = tid; j < nr; j += kT) expand_def_run(s_valid, t.src, r_info[j], r_start[j], min(r_start[j + 1], n));
+        __syncthreads();
+        if (s_done) break;
+      }
     }
-    // ---- 2. exclusive prefix of popcounts per word -> s_rank ----------------------------------
+    // ---- 3. exclusive prefix of popcounts per word -> s_rank ----------------------------------------------
     {
-      const uint32_t per = (nw + kDecodeThreads - 1) / kDecodeThreads;
-      uint32_t w0 = tid * per, w1 = min(w0 + per, nw);
+      const uint32_t per = (nw + kT - 1) / kT;
+      uint32_t w0 = min((uint32_t)tid * per, nw), w1 = min(w0 + per, nw);
       uint32_t sum = 0;
       for (uint32_t w = w0; w < w1; ++w) sum += __popc(s_valid[w]);
       uint32_t incl = sum;
@@ -168,16 +338,15 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int* __restrict__ err) {
         run += __popc(s_valid[w]);
       }
       nn = 0;
-      for (int wv = 0; wv < kDecodeThreads / 32; ++wv) nn += s_warp_tot[wv];
+      for (int wv = 0; wv < kT / 32; ++wv) nn += s_warp_tot[wv];
     }
     __syncthreads();
-    // ---- 3. validity bitmap out (page may start at any bit of the column bitmap) ---------------
+    // ---- validity bitmap out (the page may start at any bit of the column bitmap) ----------------------------
     {
       const uint32_t sh = (uint32_t)(t.out_row & 31);
       uint32_t* vout = t.valid + (t.out_row >> 5);
-      // output word j (0..nwo) = bits from s_valid[j-1] (high part) and s_valid[j] (low part)
       const uint32_t nwo = (n + sh + 31) >> 5;
-      for (uint32_t j = tid; j < nwo; j += kDecodeThreads) {
+      for (uint32_t j = tid; j < nwo; j += kT) {
         uint32_t lo = j < nw ? s_valid[j] : 0u;
         uint32_t hi = (j > 0 && j - 1 < nw) ? s_valid[j - 1] : 0u;
         uint32_t v = sh ? ((lo << sh) | (hi >> (32 - sh))) : lo;
@@ -191,7 +360,7 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int* __restrict__ err) {
     const uint32_t sh = (uint32_t)(t.out_row & 31);
     uint32_t* vout = t.valid + (t.out_row >> 5);
     const uint32_t nwo = (n + sh + 31) >> 5;
-    for (uint32_t j = tid; j < nwo; j += kDecodeThreads) {
+    for (uint32_t j = tid; j < nwo; j += kT) {
       uint32_t v = 0xFFFFFFFFu;
       if (j == 0) v &= 0xFFFFFFFFu << sh;
       uint32_t endbit = n + sh - j * 32;
@@ -202,55 +371,67 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int* __restrict__ err) {
   }
 
   const uint8_t* vsrc = t.src + values_off;
+  const int64_t orow = t.out_row;
 
-  // ---- 4. values --------------------------------------------------------------------------
-  if (t.enc == 0 && t.phys == 0) {                       // PLAIN fixed width
-    for (uint32_t i = tid; i < n; i += kDecodeThreads) {
-      bool ok = true;
-      uint32_t k = i;
-      if (nullable) {
-        uint32_t wv = s_valid[i >> 5];
-        ok = (wv >> (i & 31)) & 1u;
-        k = s_rank[i >> 5] + __popc(wv & ((1u << (i & 31)) - 1u));
+  // rank / validity of row i
+  auto row_state = [&](uint32_t i, uint32_t& k) -> bool {
+    if (!has_def) { k = i; return true; }
+    uint32_t wv = s_valid[i >> 5];
+    k = s_rank[i >> 5] + __popc(wv & ((1u << (i & 31)) - 1u));
+    return (wv >> (i & 31)) & 1u;
+  };
+
+  // ---- 4a. PLAIN fixed width -------------------------------------------------------------------------------------
+  if (t.enc == 0 && t.phys == 0) {
+    for (uint32_t base = 0; base < n; base += kT * kUnroll) {
+      uint32_t k[kUnroll];
+      bool ok[kUnroll];
+      int64_t v[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        uint32_t i = base + u * kT + tid;
+        ok[u] = i < n && row_state(i, k[u]);
       }
-      if (t.width == 4) {
-        int32_t v = ok ? __ldg(reinterpret_cast<const int32_t*>(vsrc) + k) : 0;
-        store_val<int32_t>(t.out, t.out_row + i, v);
-      } else {
-        int64_t v = ok ? __ldg(reinterpret_cast<const int64_t*>(vsrc) + k) : 0;
-        store_val<int64_t>(t.out, t.out_row + i, v);
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        v[u] = 0;
+        if (ok[u]) v[u] = t.width == 4 ? (int64_t)__ldg(reinterpret_cast<const int32_t*>(vsrc) + k[u])
+                                       : __ldg(reinterpret_cast<const int64_t*>(vsrc) + k[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        uint32_t i = base + u * kT + tid;
+        if (i < n) {
+          if (t.width == 4) reinterpret_cast<int32_t*>(t.out)[orow + i] = (int32_t)v[u];
+          else reinterpret_cast<int64_t*>(t.out)[orow + i] = v[u];
+        }
       }
     }
     return;
   }
 
-  if (t.enc == 0 && t.phys == 1) {                       // PLAIN BYTE_ARRAY -> string views
+  // ---- 4b. PLAIN BYTE_ARRAY -> string views --------------------------------------------------------------------------
+  if (t.enc == 0 && t.phys == 1) {
     // fast path: every value has the same length L (TPC-DS *_id columns are char(16))
     const uint32_t vbytes = t.size - values_off;
     uint32_t L = nn ? load_u32_unaligned(vsrc) : 0;
     bool uniform = nn == 0 || ((uint64_t)(L + 4) * nn == vbytes);
     if (uniform) {
-      for (uint32_t k = tid; k < nn && uniform; k += kDecodeThreads)
-        uniform = load_u32_unaligned(vsrc + (uint64_t)k * (L + 4)) == L;
+      for (uint32_t k = tid; k < nn && uniform; k += kT) uniform = load_u32_unaligned(vsrc + (uint64_t)k * (L + 4)) == L;
     }
     uniform = __syncthreads_and(uniform);
     if (uniform) {
-      for (uint32_t i = tid; i < n; i += kDecodeThreads) {
-        bool ok = true;
-        uint32_t k = i;
-        if (nullable) {
-          uint32_t wv = s_valid[i >> 5];
-          ok = (wv >> (i & 31)) & 1u;
-          k = s_rank[i >> 5] + __popc(wv & ((1u << (i & 31)) - 1u));
-        }
+      for (uint32_t i = tid; i < n; i += kT) {
+        uint32_t k;
+        bool ok = row_state(i, k);
         StrView v = ok ? ((uint64_t)L << 32) | (uint64_t)(t.src_off + values_off + k * (L + 4) + 4) : 0ull;
-        store_val<StrView>(t.out, t.out_row + i, v);
+        reinterpret_cast<StrView*>(t.out)[orow + i] = v;
       }
     } else if (tid == 0) {
       // slow path: one thread follows the length prefixes (variable-length free text)
       uint32_t pos = 0;
       for (uint32_t i = 0; i < n; ++i) {
-        bool ok = !nullable || ((s_valid[i >> 5] >> (i & 31)) & 1u);
+        bool ok = !has_def || ((s_valid[i >> 5] >> (i & 31)) & 1u);
         StrView v = 0;
         if (ok) {
           if (pos + 4 > vbytes) { if (err) atomicExch(err, 4); break; }
@@ -258,63 +439,78 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int* __restrict__ err) {
           v = ((uint64_t)len << 32) | (uint64_t)(t.src_off + values_off + pos + 4);
           pos += 4 + len;
         }
-        store_val<StrView>(t.out, t.out_row + i, v);
+        reinterpret_cast<StrView*>(t.out)[orow + i] = v;
       }
     }
     return;
   }
 
-  // RLE_DICTIONARY: bit width byte, then hybrid runs of dictionary indices over the nn values
+  // ---- 4c. RLE_DICTIONARY: bit width byte, then hybrid runs of dictionary indices over the nn values ------------
   const uint32_t bw = vsrc[0];
   if (bw > 32) { if (tid == 0 && err) atomicExch(err, 5); return; }
-  if (tid == 0) {
-    s_walk.pos = values_off + 1;
-    s_walk.end = t.size;
-    s_walk.k = 0;
-    s_done = 0;
-  }
+  if (tid == 0) { s_walk.pos = values_off + 1; s_walk.end = t.size; s_walk.k = 0; s_done = 0; }
   __syncthreads();
   for (;;) {
-    if (tid == 0) {
+    if (tid < 32) {
       Walker w = s_walk;
-      s_nruns = bw ? walk_runs(t.src, w, bw, nn, r_start, r_info) : 0;
-      if (!bw) { r_start[0] = 0; w.k = nn; }
-      s_walk = w;
-      s_done = (w.k >= nn || w.pos >= w.end) ? 1 : 0;
+      int nr = 0;
+      if (bw) nr = walk_runs_warp(t.src, w, bw, nn, r_start, r_info);
+      else { if (tid == 0) r_start[0] = 0; w.k = nn; }
+      __syncwarp();
+      if (tid == 0) {
+        s_nruns = nr;
+        s_walk = w;
+        s_done = (w.k >= nn || w.pos >= w.end) ? 1 : 0;
+      }
     }
     __syncthreads();
     const int nr = s_nruns;
     const uint32_t k_lo = r_start[0], k_hi = bw ? r_start[nr] : nn;
-    for (uint32_t i = tid; i < n; i += kDecodeThreads) {
-      bool ok = true;
-      uint32_t k = i;
-      if (nullable) {
-        uint32_t wv = s_valid[i >> 5];
-        ok = (wv >> (i & 31)) & 1u;
-        k = s_rank[i >> 5] + __popc(wv & ((1u << (i & 31)) - 1u));
-      }
-      if (!ok) {
-        if (k_lo == 0) {  // nulls are written once, in the first batch
-          if (t.width == 4) store_val<int32_t>(t.out, t.out_row + i, 0);
-          else store_val<int64_t>(t.out, t.out_row + i, 0);
+    for (uint32_t base = 0; base < n; base += kT * kUnroll) {
+      uint32_t k[kUnroll], idx[kUnroll];
+      int st[kUnroll];      // 0 skip, 1 write null, 2 write value
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        uint32_t i = base + u * kT + tid;
+        st[u] = 0;
+        idx[u] = 0;
+        if (i < n) {
+          bool ok = row_state(i, k[u]);
+          if (!ok) st[u] = k_lo == 0 ? 1 : 0;        // nulls are written once, with the first batch
+          else if (k[u] >= k_lo && k[u] < k_hi) st[u] = 2;
         }
-        continue;
       }
-      if (k < k_lo || k >= k_hi) continue;
-      uint32_t idx = 0;
       if (bw) {
-        int lo = 0, hi = nr - 1;          // last run with r_start <= k
-        while (lo < hi) {
-          int mid = (lo + hi + 1) >> 1;
-          if (r_start[mid] <= k) lo = mid; else hi = mid - 1;
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          if (st[u] != 2) continue;
+          int lo = 0, hi = nr - 1;          // last run with r_start <= k
+          while (lo < hi) {
+            int mid = (lo + hi + 1) >> 1;
+            if (r_start[mid] <= k[u]) lo = mid; else hi = mid - 1;
+          }
+          uint32_t info = r_info[lo];
+          idx[u] = (info & 1) ? extract_bits(t.src + (info >> 1), (uint64_t)(k[u] - r_start[lo]) * bw, bw) : (info >> 1);
         }
-        uint32_t info = r_info[lo];
-        idx = (info & 1) ? extract_bits(t.src + (info >> 1), (uint64_t)(k - r_start[lo]) * bw, bw)
-                         : (info >> 1);
       }
-      if (idx >= t.dict_count) { if (err) atomicExch(err, 6); idx = 0; if (!t.dict_count) continue; }
-      if (t.width == 4) store_val<int32_t>(t.out, t.out_row + i, __ldg(reinterpret_cast<const int32_t*>(t.dict) + idx));
-      else store_val<int64_t>(t.out, t.out_row + i, __ldg(reinterpret_cast<const int64_t*>(t.dict) + idx));
+      int64_t v[kUnroll];
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        v[u] = 0;
+        if (st[u] == 2) {
+          if (idx[u] >= t.dict_count) { if (err) atomicExch(err, 6); st[u] = 1; continue; }
+          v[u] = t.width == 4 ? (int64_t)__ldg(reinterpret_cast<const int32_t*>(t.dict) + idx[u])
+                              : __ldg(reinterpret_cast<const int64_t*>(t.dict) + idx[u]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        uint32_t i = base + u * kT + tid;
+        if (st[u]) {
+          if (t.width == 4) reinterpret_cast<int32_t*>(t.out)[orow + i] = (int32_t)v[u];
+          else reinterpret_cast<int64_t*>(t.out)[orow + i] = v[u];
+        }
+      }
     }
     __syncthreads();
     if (s_done) break;

@@ -162,6 +162,8 @@ class Engine {
   int64_t launches_ = 0;
   int64_t h2d_bytes_ = 0, d2h_bytes_ = 0;
   double exec_ms_ = 0;
+  uint8_t* pin_ = nullptr;      // pinned host ring for small host->device uploads (plan blobs, page tasks)
+  int64_t pin_cap_ = 0;
 };
 
 void set_global_error(const std::string& s);

@@ -14,7 +14,22 @@ namespace {
 struct Arena {
   cudaStream_t s;
   std::vector<void*> ptrs;
+  uint8_t* pin = nullptr;       // pinned staging ring owned by the engine (reset per query)
+  int64_t pin_cap = 0, pin_off = 0;
   explicit Arena(cudaStream_t st) : s(st) {}
+  // host -> device copy that does not need a stream sync when the bytes fit the pinned ring
+  void upload(void* dst, const void* src, int64_t bytes) {
+    if (bytes <= 0) return;
+    int64_t need = align_up(bytes, 64);
+    if (pin && pin_off + need <= pin_cap) {
+      memcpy(pin + pin_off, src, (size_t)bytes);
+      NDS_CUDA(cudaMemcpyAsync(dst, pin + pin_off, (size_t)bytes, cudaMemcpyHostToDevice, s));
+      pin_off += need;
+    } else {
+      NDS_CUDA(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyHostToDevice, s));
+      NDS_CUDA(cudaStreamSynchronize(s));
+    }
+  }
   void* alloc(int64_t bytes) {
     void* p = nullptr;
     if (bytes < 16) bytes = 16;
@@ -112,8 +127,7 @@ struct Blob {
     }
     if (!progs.empty()) memcpy(h.data() + off_progs, dev.host_progs.data(), progs.size() * sizeof(Prog));
     if (extra_bytes) memcpy(h.data() + off_extra, extra, extra_bytes);
-    NDS_CUDA(cudaMemcpyAsync(d, h.data(), total, cudaMemcpyHostToDevice, s));
-    NDS_CUDA(cudaStreamSynchronize(s));   // h goes out of scope; pageable copy is already staged, this is cheap
+    ar.upload(d, h.data(), total);
     dev.ctx.cols = reinterpret_cast<const ColRef*>(d + off_cols);
     dev.ctx.lit = d + off_lit;
     dev.progs = reinterpret_cast<const Prog*>(d + off_progs);
@@ -141,6 +155,8 @@ struct Exec {
   int64_t h2d = 0, d2h = 0;
 
   Exec(Engine& en, const Json* options) : e(en), ar(en.stream_), s(en.stream_) {
+    ar.pin = en.pin_;
+    ar.pin_cap = en.pin_cap_;
     err = ar.zeros<int>(4);
     if (options) {
       source_host = options->str_or("source", "hbm") == "host";
@@ -452,8 +468,7 @@ struct Exec {
             }
           }
           valid = ar.alloc_n<uint32_t>((int64_t)hv.size());
-          NDS_CUDA(cudaMemcpyAsync(valid, hv.data(), hv.size() * 4, cudaMemcpyHostToDevice, s));
-          NDS_CUDA(cudaStreamSynchronize(s));
+          ar.upload(valid, hv.data(), (int64_t)hv.size() * 4);
           h2d += (int64_t)hv.size() * 4;
         }
         if (!sel.empty()) {
@@ -461,9 +476,8 @@ struct Exec {
           for (size_t k = 0; k < sel.size(); ++k) { hs[k] = row_start[k]; hvv[k] = t.files[sel[k]].part_null ? 0 : t.files[sel[k]].part_val; }
           hs[sel.size()] = N;
           int64_t* dseg = ar.alloc_n<int64_t>((int64_t)hs.size() + (int64_t)hvv.size());
-          NDS_CUDA(cudaMemcpyAsync(dseg, hs.data(), hs.size() * 8, cudaMemcpyHostToDevice, s));
-          NDS_CUDA(cudaMemcpyAsync(dseg + hs.size(), hvv.data(), hvv.size() * 8, cudaMemcpyHostToDevice, s));
-          NDS_CUDA(cudaStreamSynchronize(s));
+          ar.upload(dseg, hs.data(), (int64_t)hs.size() * 8);
+          ar.upload(dseg + hs.size(), hvv.data(), (int64_t)hvv.size() * 8);
           launch_fill_segments(dseg, dseg + hs.size(), (int)sel.size(), d, s);
           ++launches;
           bytes_out += N * 4;
@@ -537,8 +551,7 @@ struct Exec {
     }
     if (!tasks.empty()) {
       PageTask* d_tasks = ar.alloc_n<PageTask>((int64_t)tasks.size());
-      NDS_CUDA(cudaMemcpyAsync(d_tasks, tasks.data(), tasks.size() * sizeof(PageTask), cudaMemcpyHostToDevice, s));
-      NDS_CUDA(cudaStreamSynchronize(s));
+      ar.upload(d_tasks, tasks.data(), (int64_t)(tasks.size() * sizeof(PageTask)));
       // a dedicated pair of events brackets only the decode launch (roofline.achieved in bench.py)
       size_t ks = begin_stat("decode_kernel", true);
       launch_decode_pages(d_tasks, (int)tasks.size(), err, s);
@@ -848,18 +861,35 @@ struct Exec {
       for (SortKey& sk : keys) { sk.offset = B; B += 1 + sk.width; }
       Blob::Dev dev = bb.upload(ar, s, keys.data(), (int64_t)keys.size() * sizeof(SortKey));
       uint8_t* keybuf = (uint8_t*)ar.alloc(n * B);
-      launch_encode_keys(dev.progs, reinterpret_cast<const SortKey*>(dev.extra), (int)keys.size(), dev.ctx, rc, keybuf, B, err, s);
+      int* active = ar.zeros<int>(B + 1);
+      launch_encode_keys(dev.progs, reinterpret_cast<const SortKey*>(dev.extra), (int)keys.size(), dev.ctx, rc, keybuf, B, active, err, s);
       ++launches;
       uint32_t* pa = ar.alloc_n<uint32_t>(n);
       uint32_t* pb = ar.alloc_n<uint32_t>(n);
-      int* which = ar.zeros<int>(B + 2);
-      uint32_t* scratch = ar.alloc_n<uint32_t>((int64_t)radix_sort_grid(n) * 256 + B + 16);
-      int l = 0;
-      launch_radix_sort(keybuf, B, rc, pa, pb, which, scratch, s, &l);
-      launches += l;
       int* dummy = ar.zeros<int>(1);
-      launch_take_perm(pa, pb, which, B, rc, limit, rows, dummy, s);
-      ++launches;
+      if (n <= kSmallSortMax) {
+        int* which = ar.zeros<int>(2);
+        launch_radix_sort_small(keybuf, B, active, rc, pa, pb, which, s);
+        launch_take_perm(pa, pb, which, 0, rc, limit, rows, dummy, s);
+        launches += 2;
+      } else {
+        // which key bytes differ between rows decides the passes (one small read-back)
+        std::vector<int> hact(B);
+        NDS_CUDA(cudaMemcpyAsync(hact.data(), active, B * sizeof(int), cudaMemcpyDeviceToHost, s));
+        NDS_CUDA(cudaStreamSynchronize(s));
+        d2h += B * 4;
+        std::vector<int> passes;
+        for (int b = B - 1; b >= 0; --b)
+          if (hact[b]) passes.push_back(b);
+        const int np = (int)passes.size();
+        int* which = ar.zeros<int>(np + 2);
+        uint32_t* scratch = ar.alloc_n<uint32_t>((int64_t)radix_sort_grid(n) * 256 + np + 16);
+        int l = 0;
+        launch_radix_sort(keybuf, B, passes.data(), np, rc, pa, pb, which, scratch, s, &l);
+        launches += l;
+        launch_take_perm(pa, pb, which, np, rc, limit, rows, dummy, s);
+        ++launches;
+      }
     }
     RowCount rm{nullptr, m};
     for (size_t c = 0; c < in.cols.size(); ++c) {
@@ -1033,7 +1063,7 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
           Arena& ar = ex.ar;
           int64_t* doffs = ar.alloc_n<int64_t>(n + 1);
           uint8_t* dchars = (uint8_t*)ar.alloc(offs64[n]);
-          NDS_CUDA(cudaMemcpyAsync(doffs, offs64.data(), (n + 1) * 8, cudaMemcpyHostToDevice, stream_));
+          ar.upload(doffs, offs64.data(), (n + 1) * 8);
           launch_copy_str_bytes(reinterpret_cast<const StrView*>(col.data), col.strbase, doffs, n, dchars, stream_);
           ++ex.launches;
           NDS_CUDA(cudaMemcpyAsync(chars, dchars, offs64[n], cudaMemcpyDeviceToHost, stream_));
@@ -1120,6 +1150,12 @@ Engine::Engine(const Json& cfg) {
   NDS_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
   uint64_t thr = UINT64_MAX;
   NDS_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+  pin_cap_ = 8 << 20;
+  if (cudaHostAlloc(reinterpret_cast<void**>(&pin_), (size_t)pin_cap_, cudaHostAllocDefault) != cudaSuccess) {
+    cudaGetLastError();
+    pin_ = nullptr;
+    pin_cap_ = 0;
+  }
 }
 
 Engine::~Engine() {
@@ -1128,6 +1164,7 @@ Engine::~Engine() {
   for (auto& kv : tables_) names.push_back(kv.first);
   for (auto& n : names) drop_table(n);
   if (stream_) cudaStreamDestroy(stream_);
+  if (pin_) cudaFreeHost(pin_);
 }
 
 }  // namespace nds

@@ -290,36 +290,55 @@ void launch_str_maxlen(Prog p, OpCtx c, RowCount n, int* out_max, cudaStream_t s
 
 // Order-preserving big-endian byte strings: per key [flag][payload]. Spark's default null ordering
 // (NULLS FIRST ascending, NULLS LAST descending) arrives as nulls_first; desc inverts the payload.
-__global__ void __launch_bounds__(kThreads)
-encode_keys_kernel(const Prog* __restrict__ progs, const SortKey* __restrict__ keys, int nk, OpCtx c, const int* n_dev,
-                   int64_t n_host, uint8_t* __restrict__ keybuf, int B, int* err) {
-  const int64_t n = row_count(n_dev, n_host);
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    uint8_t* row = keybuf + i * B;
-    for (int k = 0; k < nk; ++k) {
-      const SortKey sk = keys[k];
-      Val v = eval_program(progs[sk.prog].code, progs[sk.prog].n, c.cols, c.lit, i);
-      uint8_t* o = row + sk.offset;
-      o[0] = sk.nulls_first ? (v.ok ? 1 : 0) : (v.ok ? 0 : 1);
-      const uint8_t inv = sk.desc ? 0xFF : 0x00;
-      if (!v.ok) {
-        for (int b = 0; b < sk.width; ++b) o[1 + b] = 0;
-      } else if (sk.kind == 2) {
-        const uint8_t* p = (const uint8_t*)(uintptr_t)v.v;
-        if ((int)v.len > sk.width) { if (err) atomicExch(err, 12); }
-        for (int b = 0; b < sk.width; ++b) o[1 + b] = (b < (int)v.len ? p[b] : 0) ^ inv;
-      } else {
-        uint64_t u = (uint64_t)v.v;
-        if (sk.kind == 1) u = (u >> 63) ? ~u : (u | 0x8000000000000000ULL);
-        else u ^= 0x8000000000000000ULL;
-        for (int b = 0; b < 8; ++b) o[1 + b] = (uint8_t)(u >> (56 - 8 * b)) ^ inv;
-      }
+// While encoding, every byte is compared with row 0's: active[b] != 0 afterwards means byte b differs between
+// rows, so the radix sort only needs passes over those bytes.
+__device__ __forceinline__ void encode_row(const Prog* __restrict__ progs, const SortKey* __restrict__ keys, int nk, const OpCtx& c,
+                                           int64_t i, uint8_t* row, const uint8_t* first, uint8_t* flag, int* err) {
+  for (int k = 0; k < nk; ++k) {
+    const SortKey sk = keys[k];
+    Val v = eval_program(progs[sk.prog].code, progs[sk.prog].n, c.cols, c.lit, i);
+    const int o = sk.offset;
+    const uint8_t inv = sk.desc ? 0xFF : 0x00;
+    auto put = [&](int j, uint8_t b) {
+      row[o + j] = b;
+      if (first && b != first[o + j]) flag[o + j] = 1;
+    };
+    put(0, sk.nulls_first ? (v.ok ? 1 : 0) : (v.ok ? 0 : 1));
+    if (!v.ok) {
+      for (int b = 0; b < sk.width; ++b) put(1 + b, 0);
+    } else if (sk.kind == 2) {
+      const uint8_t* p = (const uint8_t*)(uintptr_t)v.v;
+      if ((int)v.len > sk.width) { if (err) atomicExch(err, 12); }
+      for (int b = 0; b < sk.width; ++b) put(1 + b, (uint8_t)((b < (int)v.len ? p[b] : 0) ^ inv));
+    } else {
+      uint64_t u = (uint64_t)v.v;
+      if (sk.kind == 1) u = (u >> 63) ? ~u : (u | 0x8000000000000000ULL);
+      else u ^= 0x8000000000000000ULL;
+      for (int b = 0; b < 8; ++b) put(1 + b, (uint8_t)((uint8_t)(u >> (56 - 8 * b)) ^ inv));
     }
   }
 }
-void launch_encode_keys(const Prog* progs, const SortKey* keys, int nk, OpCtx c, RowCount n, uint8_t* keybuf, int B, int* err,
-                        cudaStream_t s) {
-  encode_keys_kernel<<<grid_for(n.host), kThreads, 0, s>>>(progs, keys, nk, c, n.dev, n.host, keybuf, B, err);
+
+__global__ void __launch_bounds__(kThreads)
+encode_keys_kernel(const Prog* __restrict__ progs, const SortKey* __restrict__ keys, int nk, OpCtx c, const int* n_dev,
+                   int64_t n_host, uint8_t* __restrict__ keybuf, int B, int* active, int* err) {
+  extern __shared__ uint8_t sm_keys[];
+  uint8_t* first = sm_keys;
+  uint8_t* flag = sm_keys + B;
+  const int64_t n = row_count(n_dev, n_host);
+  if (n <= 0) return;
+  for (int b = threadIdx.x; b < B; b += blockDim.x) flag[b] = 0;
+  if (threadIdx.x == 0) encode_row(progs, keys, nk, c, 0, first, nullptr, nullptr, nullptr);
+  __syncthreads();
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    encode_row(progs, keys, nk, c, i, keybuf + i * B, first, flag, err);
+  __syncthreads();
+  for (int b = threadIdx.x; b < B; b += blockDim.x)
+    if (flag[b]) atomicOr(&active[b], 1);
+}
+void launch_encode_keys(const Prog* progs, const SortKey* keys, int nk, OpCtx c, RowCount n, uint8_t* keybuf, int B, int* active,
+                        int* err, cudaStream_t s) {
+  encode_keys_kernel<<<grid_for(n.host), kThreads, 2 * B, s>>>(progs, keys, nk, c, n.dev, n.host, keybuf, B, active, err);
   NDS_CUDA(cudaGetLastError());
 }
 
@@ -424,16 +443,16 @@ radix_scatter_kernel(const uint8_t* __restrict__ keybuf, int B, int byte, const 
   }
 }
 
-void launch_radix_sort(const uint8_t* keybuf, int B, RowCount n, uint32_t* perm_a, uint32_t* perm_b, int* which,
-                       uint32_t* scratch, cudaStream_t s, int* launches) {
+void launch_radix_sort(const uint8_t* keybuf, int B, const int* passes, int npasses, RowCount n, uint32_t* perm_a,
+                       uint32_t* perm_b, int* which, uint32_t* scratch, cudaStream_t s, int* launches) {
   const int G = radix_sort_grid(n.host);
   uint32_t* block_hist = scratch;
   uint32_t* skip_flag = scratch + (int64_t)G * 256;
   radix_init_kernel<<<grid_for(n.host), kThreads, 0, s>>>(n.dev, n.host, perm_a, which);
   NDS_CUDA(cudaGetLastError());
   *launches += 1;
-  for (int pass = 0; pass < B; ++pass) {
-    const int byte = B - 1 - pass;
+  for (int pass = 0; pass < npasses; ++pass) {
+    const int byte = passes[pass];
     radix_hist_kernel<<<G, kSortThreads, 0, s>>>(keybuf, B, byte, n.dev, n.host, perm_a, perm_b, which, pass, block_hist);
     radix_scan_kernel<<<1, 256, 0, s>>>(block_hist, G, n.dev, n.host, which, pass, skip_flag);
     radix_scatter_kernel<<<G, kSortThreads, 0, s>>>(keybuf, B, byte, n.dev, n.host, perm_a, perm_b, which, pass, block_hist,
@@ -443,18 +462,82 @@ void launch_radix_sort(const uint8_t* keybuf, int B, RowCount n, uint32_t* perm_
   NDS_CUDA(cudaGetLastError());
 }
 
-__global__ void take_perm_kernel(const uint32_t* perm_a, const uint32_t* perm_b, const int* which, int B, const int* n_dev,
+// One CTA sorts up to kSmallSortMax rows: all passes in one launch, bytes whose active flag is 0 are skipped.
+// which[0] receives the index of the buffer holding the result.
+constexpr int kSmallThreads = 1024;
+__global__ void __launch_bounds__(kSmallThreads)
+radix_sort_small_kernel(const uint8_t* __restrict__ keybuf, int B, const int* __restrict__ active, const int* n_dev, int64_t n_host,
+                        uint32_t* perm_a, uint32_t* perm_b, int* which) {
+  __shared__ uint32_t hist[256];
+  __shared__ uint32_t base[256];
+  __shared__ uint16_t wcnt[kSmallThreads / 32][256];
+  const int n = (int)row_count(n_dev, n_host);
+  const int tid = threadIdx.x, warp = tid >> 5;
+  for (int i = tid; i < n; i += kSmallThreads) perm_a[i] = (uint32_t)i;
+  int cur = 0;
+  __syncthreads();
+  for (int byte = B - 1; byte >= 0; --byte) {
+    if (!active[byte]) continue;
+    const uint32_t* src = cur ? perm_b : perm_a;
+    uint32_t* dst = cur ? perm_a : perm_b;
+    if (tid < 256) hist[tid] = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += kSmallThreads) atomicAdd(&hist[keybuf[(int64_t)src[i] * B + byte]], 1u);
+    __syncthreads();
+    if (tid < 256) {
+      uint32_t b = 0;
+      for (int k = 0; k < tid; ++k) b += hist[k];
+      base[tid] = b;
+    }
+    __syncthreads();
+    for (int c0 = 0; c0 < n; c0 += kSmallThreads) {
+      for (int k = tid; k < (kSmallThreads / 32) * 256; k += kSmallThreads) (&wcnt[0][0])[k] = 0;
+      __syncthreads();
+      const int i = c0 + tid;
+      const bool act = i < n;
+      uint32_t row = act ? src[i] : 0u;
+      int d = act ? keybuf[(int64_t)row * B + byte] : 256 + (tid & 31);
+      uint32_t m = __match_any_sync(0xFFFFFFFFu, d);
+      uint32_t rank = __popc(m & lanemask_lt());
+      if (act && rank == 0) wcnt[warp][d] = (uint16_t)__popc(m);
+      __syncthreads();
+      if (act) {
+        uint32_t pos = base[d] + rank;
+        for (int w = 0; w < warp; ++w) pos += wcnt[w][d];
+        dst[pos] = row;
+      }
+      __syncthreads();
+      if (tid < 256) {
+        uint32_t add = 0;
+        for (int w = 0; w < kSmallThreads / 32; ++w) add += wcnt[w][tid];
+        base[tid] += add;
+      }
+      __syncthreads();
+    }
+    cur ^= 1;
+    __syncthreads();
+  }
+  if (tid == 0) which[0] = cur;
+}
+
+void launch_radix_sort_small(const uint8_t* keybuf, int B, const int* active, RowCount n, uint32_t* perm_a, uint32_t* perm_b,
+                             int* which, cudaStream_t s) {
+  radix_sort_small_kernel<<<1, kSmallThreads, 0, s>>>(keybuf, B, active, n.dev, n.host, perm_a, perm_b, which);
+  NDS_CUDA(cudaGetLastError());
+}
+
+__global__ void take_perm_kernel(const uint32_t* perm_a, const uint32_t* perm_b, const int* which, int widx, const int* n_dev,
                                  int64_t n_host, int64_t limit, uint32_t* out_rows, int* out_count) {
   const int64_t n = row_count(n_dev, n_host);
   const int64_t m = (limit >= 0 && limit < n) ? limit : n;
-  const uint32_t* perm = which[B] ? perm_b : perm_a;
+  const uint32_t* perm = which[widx] ? perm_b : perm_a;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < m; i += (int64_t)gridDim.x * blockDim.x) out_rows[i] = perm[i];
   if (blockIdx.x == 0 && threadIdx.x == 0) *out_count = (int)m;
 }
-void launch_take_perm(const uint32_t* perm_a, const uint32_t* perm_b, const int* which, int B, RowCount n, int64_t limit,
+void launch_take_perm(const uint32_t* perm_a, const uint32_t* perm_b, const int* which, int widx, RowCount n, int64_t limit,
                       uint32_t* out_rows, int* out_count, cudaStream_t s) {
   int64_t m = (limit >= 0 && limit < n.host) ? limit : n.host;
-  take_perm_kernel<<<grid_for(m), kThreads, 0, s>>>(perm_a, perm_b, which, B, n.dev, n.host, limit, out_rows, out_count);
+  take_perm_kernel<<<grid_for(m), kThreads, 0, s>>>(perm_a, perm_b, which, widx, n.dev, n.host, limit, out_rows, out_count);
   NDS_CUDA(cudaGetLastError());
 }
 

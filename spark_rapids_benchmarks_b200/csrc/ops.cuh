@@ -65,15 +65,20 @@ void launch_agg_finalize(const AggSpec* aggs, int naggs, const uint32_t* slots, 
                          const int64_t* cnt, uint32_t* rep_out, int64_t* out_vals, uint32_t* out_valid, int64_t out_stride,
                          int64_t valid_stride_words, int* ngroups, cudaStream_t s);
 void launch_str_maxlen(Prog p, OpCtx c, RowCount n, int* out_max, cudaStream_t s);
-void launch_encode_keys(const Prog* progs, const SortKey* keys, int nk, OpCtx c, RowCount n, uint8_t* keybuf, int B, int* err,
-                        cudaStream_t s);
-// Stable LSD radix sort of row ids by B-byte big-endian keys. perm_a/perm_b: ping-pong buffers of n_max
-// entries; *which (device int array of B+1 entries, which[0] = 0) tracks the live buffer; on return the sorted
-// permutation is in (which[B] ? perm_b : perm_a). scratch: (grid*256 + 512) uint32.
+void launch_encode_keys(const Prog* progs, const SortKey* keys, int nk, OpCtx c, RowCount n, uint8_t* keybuf, int B, int* active,
+                        int* err, cudaStream_t s);
+// Stable LSD radix sort of row ids by B-byte big-endian keys (8-bit digits).
+//  * launch_radix_sort_small: one CTA, rows <= kSmallSortMax, skips bytes whose active[] flag is 0; the index of
+//    the result buffer (0: perm_a, 1: perm_b) is written to which[0].
+//  * launch_radix_sort: multi-CTA, one hist/scan/scatter triple per listed byte (passes[] in LSD order);
+//    which[] must hold npasses + 1 ints; result buffer index is which[npasses]. scratch: grid*256 + npasses + 16 uint32.
+constexpr int kSmallSortMax = 8192;
 int radix_sort_grid(int64_t n_max);
-void launch_radix_sort(const uint8_t* keybuf, int B, RowCount n, uint32_t* perm_a, uint32_t* perm_b, int* which,
-                       uint32_t* scratch, cudaStream_t s, int* launches);
-void launch_take_perm(const uint32_t* perm_a, const uint32_t* perm_b, const int* which, int B, RowCount n, int64_t limit,
+void launch_radix_sort_small(const uint8_t* keybuf, int B, const int* active, RowCount n, uint32_t* perm_a, uint32_t* perm_b,
+                             int* which, cudaStream_t s);
+void launch_radix_sort(const uint8_t* keybuf, int B, const int* passes, int npasses, RowCount n, uint32_t* perm_a,
+                       uint32_t* perm_b, int* which, uint32_t* scratch, cudaStream_t s, int* launches);
+void launch_take_perm(const uint32_t* perm_a, const uint32_t* perm_b, const int* which, int widx, RowCount n, int64_t limit,
                       uint32_t* out_rows, int* out_count, cudaStream_t s);
 void launch_copy_str_bytes(const StrView* views, const uint8_t* base, const int64_t* offsets, int64_t n, uint8_t* out,
                            cudaStream_t s);

@@ -476,8 +476,16 @@ class Planner:
                     k['nulls_first'] = bool(nf)
                 keys.append(k)
                 used_names.append(name)
-            for n, _, _ in out_cols:                       # deterministic tie-break
-                if n not in used_names:
+            # deterministic tie-break: the remaining output columns - unless the ORDER BY keys already contain
+            # every GROUP BY key, in which case no two result rows can tie
+            total = False
+            if is_agg and q['group']:
+                key_outs = []
+                for kname, _ in key_map.values():
+                    key_outs.append([n for n, oir, _ in out_cols if oir == _col(kname)])
+                total = all(any(n in used_names for n in outs) for outs in key_outs)
+            for n, _, _ in out_cols:
+                if n not in used_names and not total:
                     keys.append({'expr': _col(n), 'desc': False})
             node = {'op': 'sort', 'keys': keys, 'limit': -1 if q['limit'] is None else q['limit'], 'child': node}
         out = {'root': node, 'output': [{'name': n, 'type': t} for n, _, t in out_cols]}

@@ -1,0 +1,53 @@
+"""Per-query, per-operator CUDA-event timings on the bench warehouse (development aid).
+usage: python tools/profile_queries.py [--sf 10] [--reps 3] [--source hbm|host] [--queries query3,query7]"""
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--sf', type=float, default=10)
+    ap.add_argument('--sales_days', type=int, default=1823)
+    ap.add_argument('--reps', type=int, default=3)
+    ap.add_argument('--source', default='hbm')
+    ap.add_argument('--queries', default='')
+    ap.add_argument('--no_profile', action='store_true')
+    a = ap.parse_args()
+    import bench
+    import __graft_entry__ as entry
+    entry.build()
+    from spark_rapids_benchmarks_b200 import nds_schema, planner
+    from spark_rapids_benchmarks_b200.session import Session
+
+    class A:
+        pass
+    args = A()
+    args.sf, args.sales_days, args.data_dir = a.sf, a.sales_days, ''
+    bench.ensure_data(args, print)
+    qd = bench.make_stream(args)
+    wh = bench.data_dir(args)
+    sess = Session('profile', device=0, keep_host=True)
+    for t in nds_schema.get_schemas(True):
+        sess.register_table(t, os.path.join(wh, t))
+    names = [q for q in qd if not a.queries or q in a.queries.split(',')]
+    for name in names:
+        plan = planner.plan_sql(qd[name])
+        for rep in range(a.reps):
+            t0 = time.perf_counter()
+            sess.engine.execute({'root': plan['root']}, source=None if a.source == 'hbm' else a.source, profile=not a.no_profile)
+            wall = (time.perf_counter() - t0) * 1e3
+            st = sess.engine.last_stats()
+        print('== %s: wall %.3f ms, device %.3f ms, launches %d, h2d %d' % (name, wall, st['device_ms'], st['launches'], st['h2d_bytes']))
+        for o in st['ops']:
+            gbs = (o['bytes'] / (o['ms'] * 1e-3) / 1e9) if o['ms'] > 0 and o['bytes'] else 0
+            print('   %-28s %9.3f ms  %12d B  %10d rows  %8.1f GB/s' % (o['op'], o['ms'], o['bytes'], o['rows'], gbs))
+
+
+if __name__ == '__main__':
+    main()
