@@ -33,7 +33,8 @@ namespace {
 
 constexpr int kT = kDecodeThreads;
 constexpr int kWords = kMaxPageValues / 32;
-constexpr int kDefStage = 8192;          // def-level bytes staged in shared memory (larger -> sequential fallback)
+constexpr int kStage = 16384;            // bytes of one hybrid stream staged in shared memory
+constexpr int kEntCap = 1024;            // header entries (position, first value index) per batch
 constexpr int kDefSeg = 2048;            // byte positions resolved per segment of the parallel header walk
 constexpr int kChunk = 32;               // bytes per chunk of the parallel header walk
 constexpr int kUnroll = 4;
@@ -83,7 +84,7 @@ __device__ __forceinline__ uint32_t parse_run(const uint8_t* src, uint32_t pos, 
 // Sequential walk of up to kRunCap headers (fallback for oversized def streams; single thread).
 __device__ int walk_runs_seq(const uint8_t* src, Walker& w, uint32_t bw, uint32_t limit, uint32_t* r_start, uint32_t* r_info) {
   int n = 0;
-  while (n < kRunCap && w.k < limit && w.pos < w.end) {
+  while (n < kEntCap && w.k < limit && w.pos < w.end) {
     uint32_t cnt, info;
     uint32_t len = parse_run(src, w.pos, w.end, bw, cnt, info);
     r_start[n] = w.k;
@@ -105,12 +106,12 @@ __device__ int walk_runs_warp(const uint8_t* src, Walker& w, uint32_t bw, uint32
   const uint32_t S = 1 + 63 * bw;
   int n = 0;
   uint32_t pos = w.pos, k = w.k;
-  while (n < kRunCap && k < limit && pos < w.end) {
+  while (n < kEntCap && k < limit && pos < w.end) {
     uint32_t cand = pos + (uint32_t)lane * S;
     bool full = (cand + S <= w.end) && (src[cand] == 0x7F);
     uint32_t m = __ballot_sync(0xFFFFFFFFu, full);
     uint32_t lead = (m == 0xFFFFFFFFu) ? 32u : (uint32_t)(__ffs(~m) - 1);
-    uint32_t room = (uint32_t)(kRunCap - n);
+    uint32_t room = (uint32_t)(kEntCap - n);
     uint32_t need = (limit - k + 503u) / 504u;
     lead = min(lead, min(room, need));
     if (lead > 0) {
@@ -174,13 +175,10 @@ __device__ __forceinline__ void expand_def_run(uint32_t* bm, const uint8_t* src,
 // ---- bulk async copy (TMA 1-D) of a 16 B aligned window into shared memory -----------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
-__device__ __forceinline__ void bulk_load_wait(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* mbar, int tid) {
+__device__ __forceinline__ void bulk_load_wait(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* mbar, uint32_t parity,
+                                               int tid) {
   if (tid == 0) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(mbar)));
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
-  __syncthreads();
-  if (tid == 0) {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // earlier generic-proxy accesses to smem_dst are ordered first
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(mbar)), "r"(bytes) : "memory");
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
                  "l"(gsrc), "r"(bytes), "r"(smem_u32(mbar))
@@ -190,111 +188,159 @@ __device__ __forceinline__ void bulk_load_wait(void* smem_dst, const void* gsrc,
   while (!done) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
         "selp.u32 %0, 1, 0, p;\n\t}"
         : "=r"(done)
-        : "r"(smem_u32(mbar))
+        : "r"(smem_u32(mbar)), "r"(parity)
         : "memory");
   }
 }
 
 }  // namespace
 
+// ---- parallel resolution of a hybrid stream's run headers ----------------------------------------------------
+// sd[0..L): the stream (shared or global memory). Starting at header position w.pos with w.k values already
+// covered, resolves up to kDefSeg byte positions: appends (position, first value index) of the first header of
+// every entered kChunk-byte chunk to ent_pos/ent_k (at most kDefSeg/kChunk new entries) and advances w.
+// Must be called by all threads of the CTA; s_hop is kDefSeg words of scratch.
+__device__ __forceinline__ void resolve_segment(const uint8_t* sd, uint32_t L, uint32_t bw, uint32_t limit, Walker* w, uint32_t* s_hop,
+                                                uint32_t* ent_pos, uint32_t* ent_k, int* n_ent, int tid) {
+  const uint32_t seg0 = w->pos, k0 = w->k;
+  const uint32_t seg1 = min(seg0 + (uint32_t)kDefSeg, L);
+  const uint32_t nchunks = (seg1 - seg0 + kChunk - 1) / kChunk;
+  const uint32_t bytew = (bw + 7) >> 3;
+  __syncthreads();
+  // phase A: speculative parse of every byte position of my chunk, last to first
+  if ((uint32_t)tid < nchunks) {
+    const uint32_t cb = seg0 + tid * kChunk, ce = min(cb + (uint32_t)kChunk, seg1);
+    for (uint32_t p = ce; p-- > cb;) {
+      uint32_t b0 = sd[p], h = b0 & 0x7F, hl = 1;
+      if (b0 & 0x80) {
+        uint32_t b1 = p + 1 < L ? sd[p + 1] : 0u;
+        h |= (b1 & 0x7F) << 7;
+        hl = 2;
+        if (b1 & 0x80) {
+          uint32_t b2 = p + 2 < L ? sd[p + 2] : 0u;
+          h |= (b2 & 0x7F) << 14;
+          hl = 3;     // a run of one page never needs more than 3 varint bytes (<= 32768 values)
+        }
+      }
+      uint32_t cnt = (h & 1) ? (h >> 1) * 8 : (h >> 1);
+      uint32_t nxt = p + hl + ((h & 1) ? (h >> 1) * bw : bytew);
+      if (nxt > L || nxt <= p) nxt = L;
+      if (nxt < ce) {
+        uint32_t f = s_hop[nxt - seg0];
+        cnt += f & 0xFFFFu;
+        nxt = f >> 16;
+      }
+      if (cnt > 0xFFFFu) cnt = 0xFFFFu;
+      s_hop[p - seg0] = (nxt << 16) | cnt;
+    }
+  }
+  __syncthreads();
+  // phase B: hop from chunk to chunk, one shared-memory load per chunk
+  if (tid == 0) {
+    uint32_t p = seg0, k = k0;
+    int ne = *n_ent;
+    while (p < seg1 && k < limit) {
+      ent_pos[ne] = p;
+      ent_k[ne] = k;
+      ++ne;
+      uint32_t f = s_hop[p - seg0];
+      k += f & 0xFFFFu;
+      p = f >> 16;
+    }
+    *n_ent = ne;
+    w->pos = p;
+    w->k = k > limit ? limit : k;
+  }
+  __syncthreads();
+}
+
 __global__ void __launch_bounds__(kT)
-decode_pages_kernel(const PageTask* __restrict__ tasks, int* __restrict__ err) {
+decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __restrict__ err, long long* __restrict__ dbg) {
   __shared__ uint32_t s_valid[kWords];
   __shared__ uint32_t s_rank[kWords];
-  __shared__ uint32_t r_start[kRunCap + 1];
-  __shared__ uint32_t r_info[kRunCap];
-  __shared__ __align__(16) uint8_t s_def_raw[kDefStage + 48];
-  __shared__ uint32_t s_hop[kDefSeg];                       // phase A: (exit position << 16) | values emitted
-  __shared__ uint32_t s_entry[kDefSeg / kChunk][2];         // phase B: per chunk entry position, first value index
+  __shared__ uint32_t ent_pos[kEntCap + 1];
+  __shared__ uint32_t ent_k[kEntCap + 1];
+  __shared__ __align__(16) uint8_t s_stage[kStage + 48];
+  __shared__ uint32_t s_hop[kDefSeg];                       // (exit position << 16) | values emitted
   __shared__ __align__(8) uint64_t s_mbar;
-  __shared__ int s_nruns;
+  __shared__ int s_nent;
   __shared__ int s_done;
   __shared__ uint32_t s_warp_tot[kT / 32];
   __shared__ Walker s_walk;
 
-  const PageTask t = tasks[blockIdx.x];
+  // a page may be shared by `nslices` CTAs when a launch has too few pages to fill the GPU: every slice resolves
+  // the page's run headers, then expands only its own share of the rows; slice 0 writes the validity bitmap
+#define NDS_CKPT(j) do { if (dbg && threadIdx.x == 0) dbg[(int64_t)blockIdx.x * 8 + (j)] = clock64(); } while (0)
+  NDS_CKPT(0);
+  const PageTask t = tasks[blockIdx.x / nslices];
+  const int slice = blockIdx.x % nslices;
   const int tid = threadIdx.x;
   const uint32_t n = t.num_values;
   const uint32_t nw = (n + 31) >> 5;
+  __shared__ uint32_t s_long[64][2];       // long RLE runs of 1s, filled cooperatively
+  __shared__ int s_nlong;
   const bool has_def = t.valid != nullptr && t.def_len > 0;
   uint32_t values_off = 0;
   uint32_t nn = n;  // non-null count
+  uint32_t mbar_phase = 0;
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_mbar)));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
 
   if (has_def) {
     for (uint32_t w = tid; w < nw; w += kT) s_valid[w] = 0;
     const uint32_t L = t.def_len;
-    if (L <= (uint32_t)kDefStage) {
-      // ---- 1. stage the def-level bytes ------------------------------------------------------------------
+    if (L <= (uint32_t)kStage) {
+      // ---- 1. stage the def-level bytes, 2. resolve their run headers in parallel -----------------------------
       const uint8_t* g0 = t.src + 4;
       uintptr_t a0 = reinterpret_cast<uintptr_t>(g0) & ~uintptr_t(15);
       uintptr_t a1 = (reinterpret_cast<uintptr_t>(g0) + L + 15) & ~uintptr_t(15);
-      bulk_load_wait(s_def_raw, reinterpret_cast<const void*>(a0), (uint32_t)(a1 - a0), &s_mbar, tid);
-      const uint8_t* sd = s_def_raw + (reinterpret_cast<uintptr_t>(g0) - a0);
-      // ---- 2. parallel header walk, kDefSeg byte positions at a time ----------------------------------------
+      bulk_load_wait(s_stage, reinterpret_cast<const void*>(a0), (uint32_t)(a1 - a0), &s_mbar, mbar_phase, tid);
+      mbar_phase ^= 1;
+      const uint8_t* sd = s_stage + (reinterpret_cast<uintptr_t>(g0) - a0);
+      NDS_CKPT(1);
       if (tid == 0) { s_walk.pos = 0; s_walk.k = 0; s_walk.end = L; }
       __syncthreads();
       for (;;) {
-        const uint32_t seg0 = s_walk.pos, k0 = s_walk.k;
-        if (seg0 >= L || k0 >= n) break;
-        const uint32_t seg1 = min(seg0 + (uint32_t)kDefSeg, L);
-        const uint32_t nchunks = (seg1 - seg0 + kChunk - 1) / kChunk;
-        // phase A: speculative parse of every byte position of my chunk, last to first
-        if ((uint32_t)tid < nchunks) {
-          const uint32_t cb = seg0 + tid * kChunk, ce = min(cb + (uint32_t)kChunk, seg1);
-          s_entry[tid][0] = 0xFFFFFFFFu;
-          for (uint32_t p = ce; p-- > cb;) {
-            uint32_t b0 = sd[p], h = b0 & 0x7F, hl = 1;
-            if (b0 & 0x80) {
-              uint32_t b1 = p + 1 < L ? sd[p + 1] : 0u;
-              h |= (b1 & 0x7F) << 7;
-              hl = 2;
-              if (b1 & 0x80) {
-                uint32_t b2 = p + 2 < L ? sd[p + 2] : 0u;
-                h |= (b2 & 0x7F) << 14;
-                hl = 3;     // a def-level run never needs more than 3 varint bytes (<= 65536 values)
-              }
-            }
-            uint32_t cnt = (h & 1) ? (h >> 1) * 8 : (h >> 1);
-            uint32_t nxt = p + hl + ((h & 1) ? (h >> 1) : 1u);
-            if (nxt > L) nxt = L;
-            if (nxt < ce) {
-              uint32_t f = s_hop[nxt - seg0];
-              cnt += f & 0xFFFFu;
-              nxt = f >> 16;
-            }
-            if (cnt > 0xFFFFu) cnt = 0xFFFFu;
-            s_hop[p - seg0] = (nxt << 16) | cnt;
-          }
-        }
+        if (s_walk.pos >= L || s_walk.k >= n) break;
+        if (tid == 0) s_nent = 0;
+        resolve_segment(sd, L, 1, n, &s_walk, s_hop, ent_pos, ent_k, &s_nent, tid);
+        // phase C: every entry expands the runs up to the next entry into the validity bitmap; long runs of
+        // valid rows (a column without NULLs is one run) are queued and filled by the whole CTA
+        const int ne = s_nent;
+        const uint32_t seg_end = s_walk.pos;
+        if (tid == 0) s_nlong = 0;
         __syncthreads();
-        // phase B: hop from chunk to chunk
-        if (tid == 0) {
-          uint32_t p = seg0, k = k0;
-          while (p < seg1 && k < n) {
-            uint32_t c = (p - seg0) / kChunk;
-            s_entry[c][0] = p;
-            s_entry[c][1] = k;
-            uint32_t f = s_hop[p - seg0];
-            k += f & 0xFFFFu;
-            p = f >> 16;
-          }
-          s_walk.pos = p;
-          s_walk.k = k > n ? n : k;
-        }
-        __syncthreads();
-        // phase C: every entered chunk expands its own runs
-        if ((uint32_t)tid < nchunks && s_entry[tid][0] != 0xFFFFFFFFu) {
-          const uint32_t ce = min(seg0 + (tid + 1) * (uint32_t)kChunk, seg1);
-          uint32_t p = s_entry[tid][0], k = s_entry[tid][1];
-          while (p < ce && k < n) {
+        if (tid < ne) {
+          const uint32_t pe = tid + 1 < ne ? ent_pos[tid + 1] : seg_end;
+          uint32_t p = ent_pos[tid], k = ent_k[tid];
+          while (p < pe && k < n) {
             uint32_t cnt, info;
             uint32_t len = parse_run(sd, p, L, 1, cnt, info);
-            expand_def_run(s_valid, sd, info, k, min(k + cnt, n));
+            const uint32_t k1 = min(k + cnt, n);
+            if (!(info & 1) && (info >> 1) && k1 - k >= 256) {
+              int j = atomicAdd(&s_nlong, 1);
+              if (j < 64) { s_long[j][0] = k; s_long[j][1] = k1; }
+              else set_bits(s_valid, k, k1);
+            } else expand_def_run(s_valid, sd, info, k, k1);
             p += len;
             k += cnt;
+          }
+        }
+        __syncthreads();
+        const int nl = min(s_nlong, 64);
+        for (int j = 0; j < nl; ++j) {
+          const uint32_t b0 = s_long[j][0], b1 = s_long[j][1];
+          for (uint32_t w = (b0 >> 5) + tid; w <= ((b1 - 1) >> 5); w += kT) {
+            uint32_t lo = max(b0, w << 5), hi = min(b1, (w + 1) << 5);
+            uint32_t cntb = hi - lo;
+            uint32_t m = (cntb == 32 ? 0xFFFFFFFFu : ((1u << cntb) - 1u)) << (lo & 31);
+            atomicOr(&s_valid[w], m);
           }
         }
         __syncthreads();
@@ -306,17 +352,18 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int* __restrict__ err) {
       for (;;) {
         if (tid == 0) {
           Walker w = s_walk;
-          s_nruns = walk_runs_seq(t.src, w, 1, n, r_start, r_info);
+          s_nent = walk_runs_seq(t.src, w, 1, n, ent_k, ent_pos);
           s_walk = w;
           s_done = (w.k >= n || w.pos >= w.end) ? 1 : 0;
         }
         __syncthreads();
-        const int nr = s_nruns;
-        for (int j = tid; j < nr; j += kT) expand_def_run(s_valid, t.src, r_info[j], r_start[j], min(r_start[j + 1], n));
+        const int nr = s_nent;
+        for (int j = tid; j < nr; j += kT) expand_def_run(s_valid, t.src, ent_pos[j], ent_k[j], min(ent_k[j + 1], n));
         __syncthreads();
         if (s_done) break;
       }
     }
+    NDS_CKPT(2);
     // ---- 3. exclusive prefix of popcounts per word -> s_rank ----------------------------------------------
     {
       const uint32_t per = (nw + kT - 1) / kT;
@@ -345,7 +392,7 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int* __restrict__ err) {
     {
       const uint32_t sh = (uint32_t)(t.out_row & 31);
       uint32_t* vout = t.valid + (t.out_row >> 5);
-      const uint32_t nwo = (n + sh + 31) >> 5;
+      const uint32_t nwo = slice == 0 ? (n + sh + 31) >> 5 : 0u;
       for (uint32_t j = tid; j < nwo; j += kT) {
         uint32_t lo = j < nw ? s_valid[j] : 0u;
         uint32_t hi = (j > 0 && j - 1 < nw) ? s_valid[j - 1] : 0u;
@@ -359,7 +406,7 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int* __restrict__ err) {
     // page without def levels (REQUIRED in this file) of a column that is nullable elsewhere
     const uint32_t sh = (uint32_t)(t.out_row & 31);
     uint32_t* vout = t.valid + (t.out_row >> 5);
-    const uint32_t nwo = (n + sh + 31) >> 5;
+    const uint32_t nwo = slice == 0 ? (n + sh + 31) >> 5 : 0u;
     for (uint32_t j = tid; j < nwo; j += kT) {
       uint32_t v = 0xFFFFFFFFu;
       if (j == 0) v &= 0xFFFFFFFFu << sh;
@@ -370,6 +417,7 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int* __restrict__ err) {
     }
   }
 
+  NDS_CKPT(3);
   const uint8_t* vsrc = t.src + values_off;
   const int64_t orow = t.out_row;
 
@@ -381,16 +429,22 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int* __restrict__ err) {
     return (wv >> (i & 31)) & 1u;
   };
 
+  // this slice's share of the page, in 32-row tiles
+  const uint32_t ntiles = (n + 31) >> 5;
+  const uint32_t tiles_per_slice = (ntiles + nslices - 1) / nslices;
+  const uint32_t stile0 = min((uint32_t)slice * tiles_per_slice, ntiles), stile1 = min(stile0 + tiles_per_slice, ntiles);
+  const uint32_t row0 = stile0 * 32, row1 = min(stile1 * 32, n);
+
   // ---- 4a. PLAIN fixed width -------------------------------------------------------------------------------------
   if (t.enc == 0 && t.phys == 0) {
-    for (uint32_t base = 0; base < n; base += kT * kUnroll) {
+    for (uint32_t base = row0; base < row1; base += kT * kUnroll) {
       uint32_t k[kUnroll];
       bool ok[kUnroll];
       int64_t v[kUnroll];
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
         uint32_t i = base + u * kT + tid;
-        ok[u] = i < n && row_state(i, k[u]);
+        ok[u] = i < row1 && row_state(i, k[u]);
       }
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
@@ -401,7 +455,7 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int* __restrict__ err) {
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
         uint32_t i = base + u * kT + tid;
-        if (i < n) {
+        if (i < row1) {
           if (t.width == 4) reinterpret_cast<int32_t*>(t.out)[orow + i] = (int32_t)v[u];
           else reinterpret_cast<int64_t*>(t.out)[orow + i] = v[u];
         }
@@ -421,13 +475,13 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int* __restrict__ err) {
     }
     uniform = __syncthreads_and(uniform);
     if (uniform) {
-      for (uint32_t i = tid; i < n; i += kT) {
+      for (uint32_t i = row0 + tid; i < row1; i += kT) {
         uint32_t k;
         bool ok = row_state(i, k);
         StrView v = ok ? ((uint64_t)L << 32) | (uint64_t)(t.src_off + values_off + k * (L + 4) + 4) : 0ull;
         reinterpret_cast<StrView*>(t.out)[orow + i] = v;
       }
-    } else if (tid == 0) {
+    } else if (tid == 0 && slice == 0) {
       // slow path: one thread follows the length prefixes (variable-length free text)
       uint32_t pos = 0;
       for (uint32_t i = 0; i < n; ++i) {
@@ -448,33 +502,63 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int* __restrict__ err) {
   // ---- 4c. RLE_DICTIONARY: bit width byte, then hybrid runs of dictionary indices over the nn values ------------
   const uint32_t bw = vsrc[0];
   if (bw > 32) { if (tid == 0 && err) atomicExch(err, 5); return; }
-  if (tid == 0) { s_walk.pos = values_off + 1; s_walk.end = t.size; s_walk.k = 0; s_done = 0; }
+  const uint32_t L = t.size - (values_off + 1);        // index stream bytes
+  const uint8_t* sd = vsrc + 1;                        // stream base (global, or shared once staged)
+  const bool staged = bw > 0 && L <= (uint32_t)kStage;
+  if (staged) {
+    uintptr_t a0 = reinterpret_cast<uintptr_t>(sd) & ~uintptr_t(15);
+    uintptr_t a1 = (reinterpret_cast<uintptr_t>(sd) + L + 15) & ~uintptr_t(15);
+    __syncthreads();    // everyone is done with the def bytes in s_stage
+    bulk_load_wait(s_stage, reinterpret_cast<const void*>(a0), (uint32_t)(a1 - a0), &s_mbar, mbar_phase, tid);
+    mbar_phase ^= 1;
+    sd = s_stage + (reinterpret_cast<uintptr_t>(sd) - a0);
+  }
+  if (tid == 0) { s_walk.pos = 0; s_walk.end = L; s_walk.k = 0; s_done = 0; }
   __syncthreads();
+  const int warp = tid >> 5, lane = tid & 31;
+  // contiguous block of 32-row tiles per warp, so that a warp's run cursor only moves forward
+  const uint32_t tiles_per_warp = (stile1 - stile0 + kT / 32 - 1) / (kT / 32);
+  const uint32_t tile0 = min(stile0 + (uint32_t)warp * tiles_per_warp, stile1), tile1 = min(tile0 + tiles_per_warp, stile1);
   for (;;) {
-    if (tid < 32) {
-      Walker w = s_walk;
-      int nr = 0;
-      if (bw) nr = walk_runs_warp(t.src, w, bw, nn, r_start, r_info);
-      else { if (tid == 0) r_start[0] = 0; w.k = nn; }
-      __syncwarp();
-      if (tid == 0) {
-        s_nruns = nr;
-        s_walk = w;
-        s_done = (w.k >= nn || w.pos >= w.end) ? 1 : 0;
-      }
-    }
+    // ---- entries: (header position, first value index) of some run headers, in stream order -----------------
+    if (tid == 0) s_nent = 0;
     __syncthreads();
-    const int nr = s_nruns;
-    const uint32_t k_lo = r_start[0], k_hi = bw ? r_start[nr] : nn;
-    for (uint32_t base = 0; base < n; base += kT * kUnroll) {
+    if (bw == 0) {
+      if (tid == 0) { s_walk.k = nn; s_walk.pos = L; }
+      __syncthreads();
+    } else if (staged) {
+      // small stream (many short runs fit here): resolve every header in parallel, segment by segment
+      while (s_walk.pos < L && s_walk.k < nn && s_nent + kDefSeg / kChunk <= kEntCap)
+        resolve_segment(sd, L, bw, nn, &s_walk, s_hop, ent_pos, ent_k, &s_nent, tid);
+    } else {
+      // large stream = long bit-packed runs: one warp chases the headers 32 at a time; entries are the runs
+      // themselves and ent_pos holds the run info word instead of a header position
+      if (tid < 32) {
+        Walker w = s_walk;
+        int nr = walk_runs_warp(sd, w, bw, nn, ent_k, ent_pos);
+        __syncwarp();
+        if (tid == 0) { s_nent = nr; s_walk = w; }
+      }
+      __syncthreads();
+    }
+    NDS_CKPT(4);
+    const int ne = s_nent;
+    const uint32_t k_lo = (bw && ne) ? ent_k[0] : 0u, k_hi = s_walk.k;
+    if (tid == 0) s_done = (s_walk.k >= nn || s_walk.pos >= L) ? 1 : 0;
+    // ---- rows: 4 tiles of 32 rows per warp iteration; a warp-uniform cursor tracks the current run --------------
+    int ce = 0;                                   // entry index at or before the cursor
+    uint32_t cp = 0, ck = 0, ccnt = 0, cinfo = 0; // current run: header position (staged), first k, values, info
+    bool cur_ok = false;
+    for (uint32_t tb = tile0; tb < tile1; tb += kUnroll) {
       uint32_t k[kUnroll], idx[kUnroll];
-      int st[kUnroll];      // 0 skip, 1 write null, 2 write value
+      int st[kUnroll];      // 0 skip, 1 write null/zero, 2 write value
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
-        uint32_t i = base + u * kT + tid;
+        uint32_t i = (tb + u) * 32 + lane;
         st[u] = 0;
         idx[u] = 0;
-        if (i < n) {
+        k[u] = 0;
+        if (tb + u < tile1 && i < n) {
           bool ok = row_state(i, k[u]);
           if (!ok) st[u] = k_lo == 0 ? 1 : 0;        // nulls are written once, with the first batch
           else if (k[u] >= k_lo && k[u] < k_hi) st[u] = 2;
@@ -483,14 +567,76 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int* __restrict__ err) {
       if (bw) {
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
-          if (st[u] != 2) continue;
-          int lo = 0, hi = nr - 1;          // last run with r_start <= k
-          while (lo < hi) {
-            int mid = (lo + hi + 1) >> 1;
-            if (r_start[mid] <= k[u]) lo = mid; else hi = mid - 1;
+          uint32_t want = __ballot_sync(0xFFFFFFFFu, st[u] == 2);
+          if (!want) continue;
+          // k grows with the lane: first / last wanted lanes give the tile's k range
+          const uint32_t kmin = __shfl_sync(0xFFFFFFFFu, k[u], __ffs(want) - 1);
+          const uint32_t kmax = __shfl_sync(0xFFFFFFFFu, k[u], 31 - __clz(want));
+          // ---- move the warp cursor to the run containing kmin (uniform) ------------------------------------
+          if (!cur_ok || kmin < ck || kmin >= ck + ccnt) {
+            if (!cur_ok || kmin < ck || (ce + 1 < ne && ent_k[ce + 1] <= kmin)) {
+              int lo = (cur_ok && kmin >= ck) ? ce : 0, hi = ne - 1;     // last entry with ent_k <= kmin
+              while (lo < hi) {
+                int mid = (lo + hi + 1) >> 1;
+                if (ent_k[mid] <= kmin) lo = mid; else hi = mid - 1;
+              }
+              ce = lo;
+              cur_ok = false;
+            }
+            if (!staged) {
+              ck = ent_k[ce];
+              ccnt = ent_k[ce + 1] - ck;
+              cinfo = ent_pos[ce];
+            } else {
+              if (!cur_ok) { cp = ent_pos[ce]; ck = ent_k[ce]; }
+              // walk headers forward from (cp, ck) until the run holds kmin
+              uint32_t len;
+              if (cur_ok) {               // current run is known and too early: step past it first
+                uint32_t c0, i0;
+                len = parse_run(sd, cp, L, bw, c0, i0);
+                cp += len;
+                ck += c0;
+              }
+              for (;;) {
+                len = parse_run(sd, cp, L, bw, ccnt, cinfo);
+                if (ck + ccnt > kmin || cp + len >= L) break;
+                cp += len;
+                ck += ccnt;
+              }
+            }
+            cur_ok = true;
           }
-          uint32_t info = r_info[lo];
-          idx[u] = (info & 1) ? extract_bits(t.src + (info >> 1), (uint64_t)(k[u] - r_start[lo]) * bw, bw) : (info >> 1);
+          if (st[u] != 2) continue;
+          uint32_t rk = ck, info = cinfo;
+          if (kmax >= ck + ccnt && k[u] >= ck + ccnt) {
+            // the tile straddles runs and my value lies in a later one: walk on privately
+            if (!staged) {
+              int e = ce;
+              while (e + 1 < ne && ent_k[e + 1] <= k[u]) ++e;
+              rk = ent_k[e];
+              info = ent_pos[e];
+            } else {
+              uint32_t p = cp, cnt = ccnt;
+              for (;;) {
+                uint32_t len = parse_run(sd, p, L, bw, cnt, info);
+                if (rk + cnt > k[u] || p + len >= L) break;
+                p += len;
+                rk += cnt;
+              }
+            }
+          }
+          if (!(info & 1)) idx[u] = info >> 1;
+          else if (!staged) idx[u] = extract_bits(sd + (info >> 1), (uint64_t)(k[u] - rk) * bw, bw);
+          else {
+            // bit-packed payload in shared memory: byte-wise extraction
+            const uint8_t* q = sd + (info >> 1);
+            uint64_t bit = (uint64_t)(k[u] - rk) * bw;
+            uint32_t by = (uint32_t)(bit >> 3);
+            uint64_t v = 0;
+            for (int b = 0; b < 5; ++b) v |= (uint64_t)q[by + b] << (8 * b);
+            v >>= (bit & 7);
+            idx[u] = bw == 32 ? (uint32_t)v : ((uint32_t)v & ((1u << bw) - 1u));
+          }
         }
       }
       int64_t v[kUnroll];
@@ -505,7 +651,7 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int* __restrict__ err) {
       }
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
-        uint32_t i = base + u * kT + tid;
+        uint32_t i = (tb + u) * 32 + lane;
         if (st[u]) {
           if (t.width == 4) reinterpret_cast<int32_t*>(t.out)[orow + i] = (int32_t)v[u];
           else reinterpret_cast<int64_t*>(t.out)[orow + i] = v[u];
@@ -513,6 +659,7 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int* __restrict__ err) {
       }
     }
     __syncthreads();
+    NDS_CKPT(5);
     if (s_done) break;
   }
 }
@@ -527,9 +674,20 @@ __global__ void fill_segments_kernel(const int64_t* __restrict__ seg_start, cons
   }
 }
 
-void launch_decode_pages(const PageTask* d_tasks, int npages, int* d_err, cudaStream_t stream) {
+int decode_slices(int npages) {
+  int nslices = 1;
+  if (npages > 0 && npages < 2 * 148) {
+    nslices = (2 * 148 + npages - 1) / npages;
+    if (nslices > 8) nslices = 8;
+  }
+  return nslices;
+}
+
+void launch_decode_pages(const PageTask* d_tasks, int npages, int* d_err, cudaStream_t stream, long long* dbg) {
   if (npages <= 0) return;
-  decode_pages_kernel<<<npages, kDecodeThreads, 0, stream>>>(d_tasks, d_err);
+  // few pages: share each page between several CTAs so that the launch still covers the 148 SMs twice
+  const int nslices = decode_slices(npages);
+  decode_pages_kernel<<<npages * nslices, kDecodeThreads, 0, stream>>>(d_tasks, nslices, d_err, dbg);
   NDS_CUDA(cudaGetLastError());
 }
 

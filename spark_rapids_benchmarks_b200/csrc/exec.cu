@@ -150,6 +150,7 @@ struct Exec {
   int* err = nullptr;            // err[0]: kernel error code, err[1]: join flags
   bool source_host = false;
   bool profile = false;
+  bool decode_timing = false;
   std::vector<OpStat> stats;
   int64_t launches = 0;
   int64_t h2d = 0, d2h = 0;
@@ -161,6 +162,7 @@ struct Exec {
     if (options) {
       source_host = options->str_or("source", "hbm") == "host";
       profile = options->bool_or("profile", false);
+      decode_timing = options->bool_or("decode_timing", false);
     }
   }
 
@@ -554,9 +556,33 @@ struct Exec {
       ar.upload(d_tasks, tasks.data(), (int64_t)(tasks.size() * sizeof(PageTask)));
       // a dedicated pair of events brackets only the decode launch (roofline.achieved in bench.py)
       size_t ks = begin_stat("decode_kernel", true);
-      launch_decode_pages(d_tasks, (int)tasks.size(), err, s);
+      long long* dbg = nullptr;
+      const int nctas = (int)tasks.size() * decode_slices((int)tasks.size());
+      if (decode_timing) dbg = ar.zeros<long long>((int64_t)nctas * 8);
+      launch_decode_pages(d_tasks, (int)tasks.size(), err, s, dbg);
       ++launches;
       end_stat(ks, bytes_in + bytes_out, N);
+      if (dbg) {
+        std::vector<long long> h((size_t)nctas * 8);
+        NDS_CUDA(cudaMemcpyAsync(h.data(), dbg, h.size() * 8, cudaMemcpyDeviceToHost, s));
+        NDS_CUDA(cudaStreamSynchronize(s));
+        double acc[6] = {0, 0, 0, 0, 0, 0};
+        long long tmin = h[0], tmax = 0;
+        for (int c = 0; c < nctas; ++c) {
+          long long prev = h[c * 8];
+          tmin = std::min(tmin, prev);
+          for (int j = 1; j < 6; ++j) {
+            long long v = h[c * 8 + j];
+            if (v) { acc[j] += (double)(v - prev); prev = v; }
+          }
+          tmax = std::max(tmax, prev);
+        }
+        char buf[256];
+        snprintf(buf, sizeof buf, "decode_phases(avg cycles/CTA over %d CTAs): stage=%.0f def=%.0f scan+valid=%.0f headers=%.0f rows=%.0f span=%lld",
+                 nctas, acc[1] / nctas, acc[2] / nctas, acc[3] / nctas, acc[4] / nctas, acc[5] / nctas, tmax - tmin);
+        size_t di = begin_stat(buf);
+        end_stat(di, 0, 0);
+      }
     }
     end_stat(st, bytes_in + bytes_out, N);
     return out;

@@ -47,7 +47,9 @@ struct SortKey {
 };
 
 // decode.cu
-void launch_decode_pages(const PageTask* d_tasks, int npages, int* d_err, cudaStream_t s);
+int decode_slices(int npages);
+// dbg (optional): 8 clock64 checkpoints per CTA, development aid
+void launch_decode_pages(const PageTask* d_tasks, int npages, int* d_err, cudaStream_t s, long long* dbg = nullptr);
 void launch_fill_segments(const int64_t* d_seg_start, const int64_t* d_seg_val, int nseg, int32_t* out, cudaStream_t s);
 
 // ops.cu

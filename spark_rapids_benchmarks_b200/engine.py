@@ -129,19 +129,21 @@ class Engine:
         self._check(self._lib.nds_engine_table_info(self._h, name.encode(), buf, len(buf)))
         return json.loads(buf.value.decode())
 
-    def execute(self, plan, source=None, profile=False):
+    def execute(self, plan, source=None, profile=False, decode_timing=False):
         """Run a plan (dict or JSON string) and return a pyarrow.RecordBatch."""
         if isinstance(plan, str):
             plan = json.loads(plan)
         if 'root' not in plan:
             plan = {'root': plan}
-        if source or profile:
+        if source or profile or decode_timing:
             plan = dict(plan)
             opts = dict(plan.get('options', {}))
             if source:
                 opts['source'] = source
             if profile:
                 opts['profile'] = True
+            if decode_timing:
+                opts['decode_timing'] = True
             plan['options'] = opts
         cs = ctypes.create_string_buffer(_SCHEMA_BYTES)
         ca = ctypes.create_string_buffer(_ARRAY_BYTES)

@@ -18,6 +18,7 @@ def main():
     ap.add_argument('--source', default='hbm')
     ap.add_argument('--queries', default='')
     ap.add_argument('--no_profile', action='store_true')
+    ap.add_argument('--decode_timing', action='store_true')
     a = ap.parse_args()
     import bench
     import __graft_entry__ as entry
@@ -40,7 +41,7 @@ def main():
         plan = planner.plan_sql(qd[name])
         for rep in range(a.reps):
             t0 = time.perf_counter()
-            sess.engine.execute({'root': plan['root']}, source=None if a.source == 'hbm' else a.source, profile=not a.no_profile)
+            sess.engine.execute({'root': plan['root']}, source=None if a.source == 'hbm' else a.source, profile=not a.no_profile, decode_timing=a.decode_timing)
             wall = (time.perf_counter() - t0) * 1e3
             st = sess.engine.last_stats()
         print('== %s: wall %.3f ms, device %.3f ms, launches %d, h2d %d' % (name, wall, st['device_ms'], st['launches'], st['h2d_bytes']))
