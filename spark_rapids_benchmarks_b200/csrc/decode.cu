@@ -1,5 +1,6 @@
 // Parquet page decode: RLE/bit-packed hybrid definition levels -> Arrow validity bitmap,
-// RLE_DICTIONARY indices / PLAIN values -> dense device columns.  One CTA (512 threads) per data page.
+// RLE_DICTIONARY indices / PLAIN values -> dense device columns.  One CTA (512 threads) per data page,
+// or several CTAs per page when a launch has too few pages to fill the GPU.
 //
 // Reference boundary: the scan the reference triggers with
 //   spark_session.read.format(input_format).load(table_path)   (/root/reference/nds/nds_power.py:97-100)
@@ -9,22 +10,25 @@
 // data page v1 def levels carry a 4-byte little-endian length prefix; dictionary-encoded values
 // start with a 1-byte bit width.
 //
-// Structure of one page:
-//   1. the def-level bytes (a few KB) are staged in shared memory with one bulk async copy
-//      (cp.async.bulk + mbarrier, SASS UBLKCP);
-//   2. the run headers - a sequential format - are resolved in parallel: every byte position is parsed
-//      speculatively as a header by one thread per 32-byte chunk (phase A: where does a walk entering the
-//      chunk at offset e leave it, and how many values does it emit), one thread hops chunk to chunk
-//      (phase B: 1 shared-memory load per chunk instead of 1 per run), then the chunks expand their own
-//      runs into the validity bitmap (phase C);
+// Structure of one page (DESIGN.md 3.1):
+//   0. one warp starts chasing the dictionary-index run headers (32 predicted header positions per
+//      round, verified with a ballot) while
+//   1. the def-level bytes are staged in shared memory by a bulk async copy (cp.async.bulk + mbarrier,
+//      SASS UBLKCP);
+//   2. the def-level run headers - a sequential format - are resolved in parallel: every byte position is
+//      parsed speculatively as a header by one thread per 32-byte chunk (phase A: where does a walk that
+//      enters the chunk at this offset leave it, and how many values does it emit), one thread hops chunk
+//      to chunk (phase B), the entered chunks expand their runs into the validity bitmap (phase C);
 //   3. a block scan of popcounts gives rank(row) = index into the non-null value stream;
-//   4. the index stream's headers are chased by one warp that loads 32 predicted header positions at once
-//      (full 63-group runs are the common case) and verifies them with a ballot;
-//   5. all threads expand rows 4 at a time (independent loads in flight): bits -> dictionary -> store.
+//   4. small index streams (<= 16 KB, where thousands of short runs can hide) are staged and resolved like
+//      the def levels;
+//   5. each warp expands a contiguous block of 32-row tiles with a warp-uniform run cursor, four tiles per
+//      iteration with the loads of all four issued before the first use: bits -> dictionary -> store.
 //
 // Roofline: HBM.  Algorithmic bytes per page = payload bytes read + width*num_values written
-// + num_values/8 validity written (DESIGN.md "decode").
+// + num_values/8 validity written.
 #include "device_types.h"
+#include "ops.cuh"
 #include "common.h"
 
 namespace nds {
@@ -38,30 +42,40 @@ constexpr int kEntCap = 1024;            // header entries (position, first valu
 constexpr int kDefSeg = 2048;            // byte positions resolved per segment of the parallel header walk
 constexpr int kChunk = 32;               // bytes per chunk of the parallel header walk
 constexpr int kUnroll = 4;
+constexpr int kEarlyCap = 80;            // runs the early index-header chase may record (32768 / 504 = 65 full runs)
 
-__device__ __forceinline__ uint32_t extract_bits(const uint8_t* p, uint64_t bit, uint32_t bw) {
-  const uint8_t* a = p + (bit >> 3);
-  uintptr_t ai = reinterpret_cast<uintptr_t>(a);
-  const uint32_t* w = reinterpret_cast<const uint32_t*>(ai & ~uintptr_t(3));
-  uint64_t v = (uint64_t)__ldg(w) | ((uint64_t)__ldg(w + 1) << 32);
-  uint32_t sh = (uint32_t)(ai & 3) * 8 + (uint32_t)(bit & 7);
-  v >>= sh;
-  return bw == 32 ? (uint32_t)v : ((uint32_t)v & ((1u << bw) - 1u));
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ uint32_t lds8(uint32_t a) {
+  uint32_t v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+
+__device__ __forceinline__ uint32_t lds32(uint32_t a) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+// bw bits starting `bit` bits after the 4 B aligned shared address base (two aligned word loads + funnel shift)
+__device__ __forceinline__ uint32_t smem_bits(uint32_t base_al, uint32_t bit, uint32_t mask) {
+  const uint32_t a = base_al + ((bit >> 5) << 2);
+  return __funnelshift_r(lds32(a), lds32(a + 4), bit & 31) & mask;
 }
 
 __device__ __forceinline__ uint32_t load_u32_unaligned(const uint8_t* p) {
   return (uint32_t)p[0] | ((uint32_t)p[1] << 8) | ((uint32_t)p[2] << 16) | ((uint32_t)p[3] << 24);
 }
 
-struct Walker {       // sequential hybrid-run header walker state
-  uint32_t pos;       // byte position inside the page payload
+struct Walker {       // header walker state
+  uint32_t pos;       // byte position inside the stream
   uint32_t end;       // end of the stream
   uint32_t k;         // values covered so far
 };
 
-// One header at src[pos]: returns run byte length (header included); cnt = values, info as in the run table.
-__device__ __forceinline__ uint32_t parse_run(const uint8_t* src, uint32_t pos, uint32_t end, uint32_t bw, uint32_t& cnt,
-                                              uint32_t& info) {
+// One header at global src[pos]: returns the run's byte length (header included); cnt = values,
+// info = (payload position << 1) | 1 for bit-packed, (value << 1) for RLE.
+__device__ __forceinline__ uint32_t parse_run_g(const uint8_t* src, uint32_t pos, uint32_t end, uint32_t bw, uint32_t& cnt,
+                                                uint32_t& info) {
   uint32_t h = 0, s = 0, c, p = pos;
   do {
     c = src[p++];
@@ -81,12 +95,34 @@ __device__ __forceinline__ uint32_t parse_run(const uint8_t* src, uint32_t pos, 
   return (p - pos) + bytew;
 }
 
-// Sequential walk of up to kRunCap headers (fallback for oversized def streams; single thread).
+// Same, for a stream staged in shared memory (sd = shared-window address of stream byte 0).
+__device__ __forceinline__ uint32_t parse_run_s(uint32_t sd, uint32_t pos, uint32_t end, uint32_t bw, uint32_t& cnt, uint32_t& info) {
+  uint32_t h = 0, s = 0, c, p = pos;
+  do {
+    c = lds8(sd + p);
+    ++p;
+    h |= (c & 0x7F) << s;
+    s += 7;
+  } while ((c & 0x80) && s < 35 && p < end);
+  if (h & 1) {
+    info = (p << 1) | 1u;
+    cnt = (h >> 1) * 8;
+    return (p - pos) + (h >> 1) * bw;
+  }
+  const uint32_t bytew = (bw + 7) >> 3;
+  uint32_t v = 0;
+  for (uint32_t b = 0; b < bytew; ++b) v |= lds8(sd + p + b) << (8 * b);
+  info = v << 1;
+  cnt = h >> 1;
+  return (p - pos) + bytew;
+}
+
+// Sequential walk of up to kEntCap headers from global memory (fallback for oversized def streams; one thread).
 __device__ int walk_runs_seq(const uint8_t* src, Walker& w, uint32_t bw, uint32_t limit, uint32_t* r_start, uint32_t* r_info) {
   int n = 0;
   while (n < kEntCap && w.k < limit && w.pos < w.end) {
     uint32_t cnt, info;
-    uint32_t len = parse_run(src, w.pos, w.end, bw, cnt, info);
+    uint32_t len = parse_run_g(src, w.pos, w.end, bw, cnt, info);
     r_start[n] = w.k;
     r_info[n] = info;
     w.pos += len;
@@ -98,22 +134,23 @@ __device__ int walk_runs_seq(const uint8_t* src, Walker& w, uint32_t bw, uint32_
   return n;
 }
 
-// Value-stream headers, one warp: lanes load the 32 positions where the next headers sit if the runs are full
-// 63-group bit-packed runs (what parquet-mr and Arrow emit for long stretches), verify with a ballot, and fall
-// back to a single ordinary parse when the prediction fails.  All lanes return the same run count.
-__device__ int walk_runs_warp(const uint8_t* src, Walker& w, uint32_t bw, uint32_t limit, uint32_t* r_start, uint32_t* r_info) {
+// Index-stream headers, one warp: lanes load the 32 positions where the next headers sit if the runs are full
+// 63-group bit-packed runs (what parquet-mr and Arrow emit for long stretches) and verify them with a ballot;
+// the run after the verified ones is parsed from the byte its lane already holds when it is a short bit-packed
+// run, otherwise by one ordinary parse.  All lanes return the same run count; r_start[n] is the end sentinel.
+__device__ int walk_runs_warp(const uint8_t* src, Walker& w, uint32_t bw, uint32_t limit, int cap, int max_single,
+                              uint32_t* r_start, uint32_t* r_info) {
   const int lane = threadIdx.x & 31;
   const uint32_t S = 1 + 63 * bw;
-  int n = 0;
+  int n = 0, singles = 0;
   uint32_t pos = w.pos, k = w.k;
-  while (n < kEntCap && k < limit && pos < w.end) {
-    uint32_t cand = pos + (uint32_t)lane * S;
-    bool full = (cand + S <= w.end) && (src[cand] == 0x7F);
-    uint32_t m = __ballot_sync(0xFFFFFFFFu, full);
+  while (n < cap && k < limit && pos < w.end && singles <= max_single) {
+    const uint32_t cand = pos + (uint32_t)lane * S;
+    const uint32_t byte = cand < w.end ? (uint32_t)src[cand] : 0x100u;
+    const bool full = byte == 0x7Fu && cand + S <= w.end;
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, full);
     uint32_t lead = (m == 0xFFFFFFFFu) ? 32u : (uint32_t)(__ffs(~m) - 1);
-    uint32_t room = (uint32_t)(kEntCap - n);
-    uint32_t need = (limit - k + 503u) / 504u;
-    lead = min(lead, min(room, need));
+    lead = min(lead, min((uint32_t)(cap - n), (limit - k + 503u) / 504u));
     if (lead > 0) {
       if ((uint32_t)lane < lead) {
         r_start[n + lane] = k + (uint32_t)lane * 504u;
@@ -122,10 +159,23 @@ __device__ int walk_runs_warp(const uint8_t* src, Walker& w, uint32_t bw, uint32
       n += (int)lead;
       k += lead * 504u;
       pos += lead * S;
+      if (n >= cap || k >= limit || pos >= w.end || lead >= 32) continue;
+      // the lane after the verified runs already holds the next header byte: short bit-packed run?
+      const uint32_t nb = __shfl_sync(0xFFFFFFFFu, byte, (int)lead);
+      if (nb < 0x80u && (nb & 1u)) {
+        const uint32_t groups = nb >> 1;
+        if (lane == 0) {
+          r_start[n] = k;
+          r_info[n] = ((pos + 1) << 1) | 1u;
+        }
+        ++n;
+        k += groups * 8;
+        pos += 1 + groups * bw;
+      }
     } else {
       uint32_t cnt = 0, info = 0, len = 0;
       if (lane == 0) {
-        len = parse_run(src, pos, w.end, bw, cnt, info);
+        len = parse_run_g(src, pos, w.end, bw, cnt, info);
         r_start[n] = k;
         r_info[n] = info;
       }
@@ -134,6 +184,7 @@ __device__ int walk_runs_warp(const uint8_t* src, Walker& w, uint32_t bw, uint32
       pos += len;
       k += cnt;
       ++n;
+      ++singles;     // each of these costs dependent global loads: a stream of short runs is given up on early
     }
   }
   if (k > limit) k = limit;
@@ -154,10 +205,10 @@ __device__ __forceinline__ void set_bits(uint32_t* bm, uint32_t b0, uint32_t b1)
   }
 }
 
-// bit-packed bw=1 payload bytes p[0..] are validity bits for rows [b0, b1)
-__device__ __forceinline__ void copy_bits(uint32_t* bm, const uint8_t* p, uint32_t b0, uint32_t b1) {
+// bit-packed bw=1 payload bytes are validity bits for rows [b0, b1); payload in shared (sp) or global (gp) memory
+__device__ __forceinline__ void copy_bits(uint32_t* bm, uint32_t sp, const uint8_t* gp, uint32_t b0, uint32_t b1) {
   for (uint32_t b = b0; b < b1; b += 8) {
-    uint32_t byte = p[(b - b0) >> 3];
+    uint32_t byte = gp ? (uint32_t)gp[(b - b0) >> 3] : lds8(sp + ((b - b0) >> 3));
     uint32_t rem = b1 - b;
     if (rem < 8) byte &= (1u << rem) - 1u;
     if (!byte) continue;
@@ -167,23 +218,15 @@ __device__ __forceinline__ void copy_bits(uint32_t* bm, const uint8_t* p, uint32
   }
 }
 
-__device__ __forceinline__ void expand_def_run(uint32_t* bm, const uint8_t* src, uint32_t info, uint32_t b0, uint32_t b1) {
-  if (info & 1) copy_bits(bm, src + (info >> 1), b0, b1);
-  else if (info >> 1) set_bits(bm, b0, b1);
-}
-
 // ---- bulk async copy (TMA 1-D) of a 16 B aligned window into shared memory -----------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void bulk_load_wait(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* mbar, uint32_t parity,
-                                               int tid) {
-  if (tid == 0) {
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // earlier generic-proxy accesses to smem_dst are ordered first
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(mbar)), "r"(bytes) : "memory");
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
-                 "l"(gsrc), "r"(bytes), "r"(smem_u32(mbar))
-                 : "memory");
-  }
+__device__ __forceinline__ void bulk_load_issue(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* mbar) {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // order earlier generic accesses to smem_dst first
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(mbar)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+               "l"(gsrc), "r"(bytes), "r"(smem_u32(mbar))
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* mbar, uint32_t parity) {
   uint32_t done = 0;
   while (!done) {
     asm volatile(
@@ -196,31 +239,29 @@ __device__ __forceinline__ void bulk_load_wait(void* smem_dst, const void* gsrc,
   }
 }
 
-}  // namespace
-
-// ---- parallel resolution of a hybrid stream's run headers ----------------------------------------------------
-// sd[0..L): the stream (shared or global memory). Starting at header position w.pos with w.k values already
-// covered, resolves up to kDefSeg byte positions: appends (position, first value index) of the first header of
-// every entered kChunk-byte chunk to ent_pos/ent_k (at most kDefSeg/kChunk new entries) and advances w.
-// Must be called by all threads of the CTA; s_hop is kDefSeg words of scratch.
-__device__ __forceinline__ void resolve_segment(const uint8_t* sd, uint32_t L, uint32_t bw, uint32_t limit, Walker* w, uint32_t* s_hop,
+// ---- parallel resolution of a staged hybrid stream's run headers -------------------------------------------------
+// sd: shared-window address of stream byte 0, L bytes long. Starting at header position w->pos with w->k values
+// covered, resolves up to kDefSeg byte positions: appends (position, first value index) of the first header of every
+// entered kChunk-byte chunk to ent_pos/ent_k (at most kDefSeg/kChunk new entries) and advances *w.
+// Called by all threads of the CTA; s_hop is kDefSeg words of scratch.
+__device__ __forceinline__ void resolve_segment(uint32_t sd, uint32_t L, uint32_t bw, uint32_t limit, Walker* w, uint32_t* s_hop,
                                                 uint32_t* ent_pos, uint32_t* ent_k, int* n_ent, int tid) {
   const uint32_t seg0 = w->pos, k0 = w->k;
   const uint32_t seg1 = min(seg0 + (uint32_t)kDefSeg, L);
   const uint32_t nchunks = (seg1 - seg0 + kChunk - 1) / kChunk;
   const uint32_t bytew = (bw + 7) >> 3;
   __syncthreads();
-  // phase A: speculative parse of every byte position of my chunk, last to first
+  // phase A: speculative parse of every byte position of my chunk, last to first (one shared load per position)
   if ((uint32_t)tid < nchunks) {
     const uint32_t cb = seg0 + tid * kChunk, ce = min(cb + (uint32_t)kChunk, seg1);
+    uint32_t b1 = ce < L ? lds8(sd + ce) : 0u, b2 = ce + 1 < L ? lds8(sd + ce + 1) : 0u;
     for (uint32_t p = ce; p-- > cb;) {
-      uint32_t b0 = sd[p], h = b0 & 0x7F, hl = 1;
+      const uint32_t b0 = lds8(sd + p);
+      uint32_t h = b0 & 0x7F, hl = 1;
       if (b0 & 0x80) {
-        uint32_t b1 = p + 1 < L ? sd[p + 1] : 0u;
         h |= (b1 & 0x7F) << 7;
         hl = 2;
         if (b1 & 0x80) {
-          uint32_t b2 = p + 2 < L ? sd[p + 2] : 0u;
           h |= (b2 & 0x7F) << 14;
           hl = 3;     // a run of one page never needs more than 3 varint bytes (<= 32768 values)
         }
@@ -235,6 +276,8 @@ __device__ __forceinline__ void resolve_segment(const uint8_t* sd, uint32_t L, u
       }
       if (cnt > 0xFFFFu) cnt = 0xFFFFu;
       s_hop[p - seg0] = (nxt << 16) | cnt;
+      b2 = b1;
+      b1 = b0;
     }
   }
   __syncthreads();
@@ -257,77 +300,108 @@ __device__ __forceinline__ void resolve_segment(const uint8_t* sd, uint32_t L, u
   __syncthreads();
 }
 
-__global__ void __launch_bounds__(kT)
+}  // namespace
+
+#define NDS_CKPT(j) do { if (dbg && threadIdx.x == 0) dbg[(int64_t)blockIdx.x * 8 + (j)] = clock64(); } while (0)
+
+__global__ void __launch_bounds__(kT, 4)
 decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __restrict__ err, long long* __restrict__ dbg) {
   __shared__ uint32_t s_valid[kWords];
   __shared__ uint32_t s_rank[kWords];
   __shared__ uint32_t ent_pos[kEntCap + 1];
   __shared__ uint32_t ent_k[kEntCap + 1];
+  __shared__ uint32_t early_k[kEarlyCap + 1];
+  __shared__ uint32_t early_info[kEarlyCap];
   __shared__ __align__(16) uint8_t s_stage[kStage + 48];
   __shared__ uint32_t s_hop[kDefSeg];                       // (exit position << 16) | values emitted
+  __shared__ uint32_t s_long[64][2];                        // long RLE runs of 1s, filled cooperatively
   __shared__ __align__(8) uint64_t s_mbar;
+  __shared__ int s_nlong;
   __shared__ int s_nent;
   __shared__ int s_done;
+  __shared__ int s_early_n;                                 // -1: early chase not done / did not finish
   __shared__ uint32_t s_warp_tot[kT / 32];
   __shared__ Walker s_walk;
 
+  NDS_CKPT(0);
   // a page may be shared by `nslices` CTAs when a launch has too few pages to fill the GPU: every slice resolves
   // the page's run headers, then expands only its own share of the rows; slice 0 writes the validity bitmap
-#define NDS_CKPT(j) do { if (dbg && threadIdx.x == 0) dbg[(int64_t)blockIdx.x * 8 + (j)] = clock64(); } while (0)
-  NDS_CKPT(0);
   const PageTask t = tasks[blockIdx.x / nslices];
   const int slice = blockIdx.x % nslices;
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t n = t.num_values;
   const uint32_t nw = (n + 31) >> 5;
-  __shared__ uint32_t s_long[64][2];       // long RLE runs of 1s, filled cooperatively
-  __shared__ int s_nlong;
   const bool has_def = t.valid != nullptr && t.def_len > 0;
-  uint32_t values_off = 0;
-  uint32_t nn = n;  // non-null count
+  const uint32_t values_off = has_def ? 4 + t.def_len : 0;
+  const bool def_staged = has_def && t.def_len <= (uint32_t)kStage;
+  const bool is_dict = t.enc == 1;
+  const uint32_t bw = t.bw;
+  const uint32_t VL = is_dict ? t.size - (values_off + 1) : 0;     // index stream bytes
+  const uint8_t* vstream = t.src + values_off + 1;                 // index stream in global memory
+  const bool v_small = is_dict && bw > 0 && VL <= (uint32_t)kStage;   // may be staged if it has many short runs
+  uint32_t nn = n;          // non-null count
   uint32_t mbar_phase = 0;
+
   if (tid == 0) {
+    s_early_n = -1;
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_mbar)));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
 
+  // ---- 1. def-level bytes -> shared memory (async) ---------------------------------------------------------------
+  uint32_t def_sd = 0;
+  if (def_staged) {
+    const uint8_t* g0 = t.src + 4;
+    const uintptr_t a0 = reinterpret_cast<uintptr_t>(g0) & ~uintptr_t(15);
+    const uintptr_t a1 = (reinterpret_cast<uintptr_t>(g0) + t.def_len + 15) & ~uintptr_t(15);
+    if (tid == 0) bulk_load_issue(s_stage, reinterpret_cast<const void*>(a0), (uint32_t)(a1 - a0), &s_mbar);
+    def_sd = smem_u32(s_stage) + (uint32_t)(reinterpret_cast<uintptr_t>(g0) - a0);
+  }
+  // ---- 0. meanwhile the last warp chases the index stream's headers (large streams = long bit-packed runs) ----------
+  if (is_dict && bw > 0 && bw <= 32 && warp == kT / 32 - 1) {
+    Walker w;
+    w.pos = 0;
+    w.end = VL;
+    w.k = 0;
+    int nr = walk_runs_warp(vstream, w, bw, n, kEarlyCap, 4, early_k, early_info);
+    __syncwarp();
+    if (lane == 0 && (w.pos >= VL || w.k >= n)) s_early_n = nr;     // finished: the runs cover every value
+  }
+  for (uint32_t w = tid; w < nw; w += kT) s_valid[w] = 0;
+
   if (has_def) {
-    for (uint32_t w = tid; w < nw; w += kT) s_valid[w] = 0;
     const uint32_t L = t.def_len;
-    if (L <= (uint32_t)kStage) {
-      // ---- 1. stage the def-level bytes, 2. resolve their run headers in parallel -----------------------------
-      const uint8_t* g0 = t.src + 4;
-      uintptr_t a0 = reinterpret_cast<uintptr_t>(g0) & ~uintptr_t(15);
-      uintptr_t a1 = (reinterpret_cast<uintptr_t>(g0) + L + 15) & ~uintptr_t(15);
-      bulk_load_wait(s_stage, reinterpret_cast<const void*>(a0), (uint32_t)(a1 - a0), &s_mbar, mbar_phase, tid);
+    if (def_staged) {
+      mbar_wait(&s_mbar, mbar_phase);
       mbar_phase ^= 1;
-      const uint8_t* sd = s_stage + (reinterpret_cast<uintptr_t>(g0) - a0);
       NDS_CKPT(1);
       if (tid == 0) { s_walk.pos = 0; s_walk.k = 0; s_walk.end = L; }
       __syncthreads();
+      // ---- 2. resolve the def-level run headers in parallel, segment by segment --------------------------------
       for (;;) {
         if (s_walk.pos >= L || s_walk.k >= n) break;
-        if (tid == 0) s_nent = 0;
-        resolve_segment(sd, L, 1, n, &s_walk, s_hop, ent_pos, ent_k, &s_nent, tid);
+        if (tid == 0) { s_nent = 0; s_nlong = 0; }
+        resolve_segment(def_sd, L, 1, n, &s_walk, s_hop, ent_pos, ent_k, &s_nent, tid);
         // phase C: every entry expands the runs up to the next entry into the validity bitmap; long runs of
         // valid rows (a column without NULLs is one run) are queued and filled by the whole CTA
         const int ne = s_nent;
         const uint32_t seg_end = s_walk.pos;
-        if (tid == 0) s_nlong = 0;
-        __syncthreads();
         if (tid < ne) {
           const uint32_t pe = tid + 1 < ne ? ent_pos[tid + 1] : seg_end;
           uint32_t p = ent_pos[tid], k = ent_k[tid];
           while (p < pe && k < n) {
             uint32_t cnt, info;
-            uint32_t len = parse_run(sd, p, L, 1, cnt, info);
+            const uint32_t len = parse_run_s(def_sd, p, L, 1, cnt, info);
             const uint32_t k1 = min(k + cnt, n);
-            if (!(info & 1) && (info >> 1) && k1 - k >= 256) {
-              int j = atomicAdd(&s_nlong, 1);
-              if (j < 64) { s_long[j][0] = k; s_long[j][1] = k1; }
-              else set_bits(s_valid, k, k1);
-            } else expand_def_run(s_valid, sd, info, k, k1);
+            if (info & 1) copy_bits(s_valid, def_sd + (info >> 1), nullptr, k, k1);
+            else if (info >> 1) {
+              if (k1 - k >= 256) {
+                int j = atomicAdd(&s_nlong, 1);
+                if (j < 64) { s_long[j][0] = k; s_long[j][1] = k1; }
+                else set_bits(s_valid, k, k1);
+              } else set_bits(s_valid, k, k1);
+            }
             p += len;
             k += cnt;
           }
@@ -337,10 +411,9 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __rest
         for (int j = 0; j < nl; ++j) {
           const uint32_t b0 = s_long[j][0], b1 = s_long[j][1];
           for (uint32_t w = (b0 >> 5) + tid; w <= ((b1 - 1) >> 5); w += kT) {
-            uint32_t lo = max(b0, w << 5), hi = min(b1, (w + 1) << 5);
-            uint32_t cntb = hi - lo;
-            uint32_t m = (cntb == 32 ? 0xFFFFFFFFu : ((1u << cntb) - 1u)) << (lo & 31);
-            atomicOr(&s_valid[w], m);
+            const uint32_t lo = max(b0, w << 5), hi = min(b1, (w + 1) << 5);
+            const uint32_t cntb = hi - lo;
+            atomicOr(&s_valid[w], (cntb == 32 ? 0xFFFFFFFFu : ((1u << cntb) - 1u)) << (lo & 31));
           }
         }
         __syncthreads();
@@ -358,7 +431,11 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __rest
         }
         __syncthreads();
         const int nr = s_nent;
-        for (int j = tid; j < nr; j += kT) expand_def_run(s_valid, t.src, ent_pos[j], ent_k[j], min(ent_k[j + 1], n));
+        for (int j = tid; j < nr; j += kT) {
+          const uint32_t info = ent_pos[j], k = ent_k[j], k1 = min(ent_k[j + 1], n);
+          if (info & 1) copy_bits(s_valid, 0, t.src + (info >> 1), k, k1);
+          else if (info >> 1) set_bits(s_valid, k, k1);
+        }
         __syncthreads();
         if (s_done) break;
       }
@@ -367,18 +444,18 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __rest
     // ---- 3. exclusive prefix of popcounts per word -> s_rank ----------------------------------------------
     {
       const uint32_t per = (nw + kT - 1) / kT;
-      uint32_t w0 = min((uint32_t)tid * per, nw), w1 = min(w0 + per, nw);
+      const uint32_t w0 = min((uint32_t)tid * per, nw), w1 = min(w0 + per, nw);
       uint32_t sum = 0;
       for (uint32_t w = w0; w < w1; ++w) sum += __popc(s_valid[w]);
       uint32_t incl = sum;
       for (int d = 1; d < 32; d <<= 1) {
         uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-        if ((tid & 31) >= d) incl += v;
+        if (lane >= d) incl += v;
       }
-      if ((tid & 31) == 31) s_warp_tot[tid >> 5] = incl;
+      if (lane == 31) s_warp_tot[warp] = incl;
       __syncthreads();
       uint32_t base = 0;
-      for (int wv = 0; wv < (tid >> 5); ++wv) base += s_warp_tot[wv];
+      for (int wv = 0; wv < warp; ++wv) base += s_warp_tot[wv];
       uint32_t run = base + incl - sum;
       for (uint32_t w = w0; w < w1; ++w) {
         s_rank[w] = run;
@@ -389,10 +466,10 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __rest
     }
     __syncthreads();
     // ---- validity bitmap out (the page may start at any bit of the column bitmap) ----------------------------
-    {
+    if (slice == 0) {
       const uint32_t sh = (uint32_t)(t.out_row & 31);
       uint32_t* vout = t.valid + (t.out_row >> 5);
-      const uint32_t nwo = slice == 0 ? (n + sh + 31) >> 5 : 0u;
+      const uint32_t nwo = (n + sh + 31) >> 5;
       for (uint32_t j = tid; j < nwo; j += kT) {
         uint32_t lo = j < nw ? s_valid[j] : 0u;
         uint32_t hi = (j > 0 && j - 1 < nw) ? s_valid[j - 1] : 0u;
@@ -401,12 +478,11 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __rest
         else vout[j] = v;
       }
     }
-    values_off = 4 + t.def_len;
-  } else if (t.valid != nullptr) {
+  } else if (t.valid != nullptr && slice == 0) {
     // page without def levels (REQUIRED in this file) of a column that is nullable elsewhere
     const uint32_t sh = (uint32_t)(t.out_row & 31);
     uint32_t* vout = t.valid + (t.out_row >> 5);
-    const uint32_t nwo = slice == 0 ? (n + sh + 31) >> 5 : 0u;
+    const uint32_t nwo = (n + sh + 31) >> 5;
     for (uint32_t j = tid; j < nwo; j += kT) {
       uint32_t v = 0xFFFFFFFFu;
       if (j == 0) v &= 0xFFFFFFFFu << sh;
@@ -416,8 +492,8 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __rest
       else vout[j] = v;
     }
   }
-
   NDS_CKPT(3);
+
   const uint8_t* vsrc = t.src + values_off;
   const int64_t orow = t.out_row;
 
@@ -499,162 +575,322 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __rest
     return;
   }
 
-  // ---- 4c. RLE_DICTIONARY: bit width byte, then hybrid runs of dictionary indices over the nn values ------------
-  const uint32_t bw = vsrc[0];
+  // ---- 4c. RLE_DICTIONARY -------------------------------------------------------------------------------------------
   if (bw > 32) { if (tid == 0 && err) atomicExch(err, 5); return; }
-  const uint32_t L = t.size - (values_off + 1);        // index stream bytes
-  const uint8_t* sd = vsrc + 1;                        // stream base (global, or shared once staged)
-  const bool staged = bw > 0 && L <= (uint32_t)kStage;
-  if (staged) {
-    uintptr_t a0 = reinterpret_cast<uintptr_t>(sd) & ~uintptr_t(15);
-    uintptr_t a1 = (reinterpret_cast<uintptr_t>(sd) + L + 15) & ~uintptr_t(15);
-    __syncthreads();    // everyone is done with the def bytes in s_stage
-    bulk_load_wait(s_stage, reinterpret_cast<const void*>(a0), (uint32_t)(a1 - a0), &s_mbar, mbar_phase, tid);
+  const uint32_t L = VL;
+  uint32_t vsd = 0;                                     // shared-window address of the staged index stream
+  __syncthreads();                                      // s_early_n is final; everyone is done with the def bytes
+  // long bit-packed runs (the early chase covered the stream in a few runs): read the bits straight from global
+  // memory; otherwise a small stream is staged and its many short runs are resolved in parallel
+  const bool v_staged = v_small && s_early_n < 0;
+  if (v_staged) {
+    const uintptr_t a0 = reinterpret_cast<uintptr_t>(vstream) & ~uintptr_t(15);
+    const uintptr_t a1 = (reinterpret_cast<uintptr_t>(vstream) + L + 15) & ~uintptr_t(15);
+    if (tid == 0) bulk_load_issue(s_stage, reinterpret_cast<const void*>(a0), (uint32_t)(a1 - a0), &s_mbar);
+    mbar_wait(&s_mbar, mbar_phase);
     mbar_phase ^= 1;
-    sd = s_stage + (reinterpret_cast<uintptr_t>(sd) - a0);
+    vsd = smem_u32(s_stage) + (uint32_t)(reinterpret_cast<uintptr_t>(vstream) - a0);
   }
   if (tid == 0) { s_walk.pos = 0; s_walk.end = L; s_walk.k = 0; s_done = 0; }
   __syncthreads();
-  const int warp = tid >> 5, lane = tid & 31;
+  const bool use_early = !v_staged && bw > 0 && s_early_n >= 0;
+  const uint32_t bwmask = bw >= 32 ? 0xFFFFFFFFu : ((1u << bw) - 1u);
+  const uint32_t vsd_al = vsd & ~3u, vsd_mis = (vsd & 3u) * 8u;
   // contiguous block of 32-row tiles per warp, so that a warp's run cursor only moves forward
   const uint32_t tiles_per_warp = (stile1 - stile0 + kT / 32 - 1) / (kT / 32);
   const uint32_t tile0 = min(stile0 + (uint32_t)warp * tiles_per_warp, stile1), tile1 = min(tile0 + tiles_per_warp, stile1);
   for (;;) {
-    // ---- entries: (header position, first value index) of some run headers, in stream order -----------------
-    if (tid == 0) s_nent = 0;
-    __syncthreads();
-    if (bw == 0) {
-      if (tid == 0) { s_walk.k = nn; s_walk.pos = L; }
-      __syncthreads();
-    } else if (staged) {
-      // small stream (many short runs fit here): resolve every header in parallel, segment by segment
-      while (s_walk.pos < L && s_walk.k < nn && s_nent + kDefSeg / kChunk <= kEntCap)
-        resolve_segment(sd, L, bw, nn, &s_walk, s_hop, ent_pos, ent_k, &s_nent, tid);
+    // ---- entries: (header position | run info, first value index) of run headers, in stream order --------------
+    const uint32_t* ek = ent_k;
+    const uint32_t* ep = ent_pos;
+    int ne;
+    uint32_t k_lo, k_hi;
+    if (use_early) {
+      ek = early_k;
+      ep = early_info;
+      ne = s_early_n;
+      k_lo = 0;
+      k_hi = nn;
+      if (tid == 0) s_done = 1;
     } else {
-      // large stream = long bit-packed runs: one warp chases the headers 32 at a time; entries are the runs
-      // themselves and ent_pos holds the run info word instead of a header position
-      if (tid < 32) {
-        Walker w = s_walk;
-        int nr = walk_runs_warp(sd, w, bw, nn, ent_k, ent_pos);
-        __syncwarp();
-        if (tid == 0) { s_nent = nr; s_walk = w; }
-      }
+      if (tid == 0) s_nent = 0;
       __syncthreads();
+      if (bw == 0) {
+        if (tid == 0) { s_walk.k = nn; s_walk.pos = L; }
+        __syncthreads();
+      } else if (v_staged) {
+        // small stream (many short runs fit here): resolve every header in parallel, segment by segment
+        while (s_walk.pos < L && s_walk.k < nn && s_nent + kDefSeg / kChunk <= kEntCap)
+          resolve_segment(vsd, L, bw, nn, &s_walk, s_hop, ent_pos, ent_k, &s_nent, tid);
+      } else {
+        // large stream with more runs than the early chase could record: batches of kEntCap runs
+        if (tid < 32) {
+          Walker w = s_walk;
+          int nr = walk_runs_warp(vstream, w, bw, nn, kEntCap, 1 << 30, ent_k, ent_pos);
+          __syncwarp();
+          if (tid == 0) { s_nent = nr; s_walk = w; }
+        }
+        __syncthreads();
+      }
+      ne = s_nent;
+      k_lo = (bw && ne) ? ent_k[0] : 0u;
+      k_hi = s_walk.k;
+      if (tid == 0) s_done = (s_walk.k >= nn || s_walk.pos >= L) ? 1 : 0;
     }
     NDS_CKPT(4);
-    const int ne = s_nent;
-    const uint32_t k_lo = (bw && ne) ? ent_k[0] : 0u, k_hi = s_walk.k;
-    if (tid == 0) s_done = (s_walk.k >= nn || s_walk.pos >= L) ? 1 : 0;
     // ---- rows: 4 tiles of 32 rows per warp iteration; a warp-uniform cursor tracks the current run --------------
     int ce = 0;                                   // entry index at or before the cursor
     uint32_t cp = 0, ck = 0, ccnt = 0, cinfo = 0; // current run: header position (staged), first k, values, info
     bool cur_ok = false;
-    for (uint32_t tb = tile0; tb < tile1; tb += kUnroll) {
-      uint32_t k[kUnroll], idx[kUnroll];
-      int st[kUnroll];      // 0 skip, 1 write null/zero, 2 write value
-#pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        uint32_t i = (tb + u) * 32 + lane;
-        st[u] = 0;
-        idx[u] = 0;
-        k[u] = 0;
-        if (tb + u < tile1 && i < n) {
-          bool ok = row_state(i, k[u]);
-          if (!ok) st[u] = k_lo == 0 ? 1 : 0;        // nulls are written once, with the first batch
-          else if (k[u] >= k_lo && k[u] < k_hi) st[u] = 2;
+    // rows are expanded in blocks of 8 tiles (256 rows). Block fast path: when all values of the block lie in the
+    // cursor's run or the one after it (runs of 504 values: almost always), the run of a value is a compare+select
+    // and the per-tile cursor bookkeeping below is skipped.
+    const uintptr_t vs_al = reinterpret_cast<uintptr_t>(vstream) & ~uintptr_t(3);
+    const uint32_t vs_mis = (uint32_t)(reinterpret_cast<uintptr_t>(vstream) & 3) * 8;
+    const uint32_t* vwords = reinterpret_cast<const uint32_t*>(vs_al);
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    for (uint32_t bb = tile0; bb < tile1; bb += 8) {
+      const uint32_t be = min(bb + 8u, tile1);
+      const uint32_t kA = has_def ? s_rank[bb] : bb * 32;
+      const uint32_t kB = has_def ? (be < nw ? s_rank[be] : nn) : min(be * 32, n);
+      bool fast = kA >= k_lo && kB <= k_hi;
+      uint32_t rk1 = 0, info1 = 0, rk2 = 0xFFFFFFFFu, info2 = 0;
+      if (fast && bw && kB > kA) {
+        // uniform cursor move to the run holding kA (same rules as the per-tile path below)
+        const uint32_t kmin = kA;
+        if (!cur_ok || kmin < ck || kmin >= ck + ccnt) {
+          if (!cur_ok || kmin < ck || (ce + 1 < ne && ek[ce + 1] <= kmin)) {
+            int lo = (cur_ok && kmin >= ck) ? ce : 0, hi = ne - 1;
+            while (lo < hi) {
+              int mid = (lo + hi + 1) >> 1;
+              if (ek[mid] <= kmin) lo = mid; else hi = mid - 1;
+            }
+            ce = lo;
+            cur_ok = false;
+          }
+          if (!v_staged) {
+            ck = ek[ce];
+            ccnt = ek[ce + 1] - ck;
+            cinfo = ep[ce];
+          } else {
+            uint32_t len;
+            if (!cur_ok) { cp = ep[ce]; ck = ek[ce]; }
+            else {
+              uint32_t c0, i0;
+              len = parse_run_s(vsd, cp, L, bw, c0, i0);
+              cp += len;
+              ck += c0;
+            }
+            for (;;) {
+              len = parse_run_s(vsd, cp, L, bw, ccnt, cinfo);
+              if (ck + ccnt > kmin || cp + len >= L) break;
+              cp += len;
+              ck += ccnt;
+            }
+          }
+          cur_ok = true;
+        }
+        rk1 = ck;
+        info1 = cinfo;
+        uint32_t cnt2 = 0;
+        if (kB > ck + ccnt) {               // the block reaches into the next run
+          if (!v_staged) {
+            if (ce + 1 < ne) { rk2 = ek[ce + 1]; cnt2 = ek[ce + 2] - rk2; info2 = ep[ce + 1]; }
+          } else {
+            uint32_t c1, i1;
+            const uint32_t len1 = parse_run_s(vsd, cp, L, bw, c1, i1);
+            if (cp + len1 < L) { parse_run_s(vsd, cp + len1, L, bw, cnt2, info2); rk2 = ck + ccnt; }
+          }
+          fast = rk2 != 0xFFFFFFFFu && kB <= rk2 + cnt2;
         }
       }
-      if (bw) {
+      if (fast) {
+        uint32_t kk[8], word0[8], word1[8], sh[8];
+        int stt[8];                 // 0 skip, 1 zero, 2 RLE / bw == 0 value in word0, 3 bit-packed
 #pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const uint32_t tcur = bb + u;
+          const uint32_t i = tcur * 32 + lane;
+          stt[u] = 0;
+          word0[u] = 0;
+          word1[u] = 0;
+          sh[u] = 0;
+          kk[u] = 0;
+          if (tcur < be && i < n) {
+            bool ok = true;
+            if (has_def) {
+              const uint32_t wv = s_valid[tcur];
+              kk[u] = s_rank[tcur] + __popc(wv & lt_mask);
+              ok = (wv >> lane) & 1u;
+            } else kk[u] = i;
+            stt[u] = 1;
+            if (ok) {
+              const bool in2 = kk[u] >= rk2;
+              const uint32_t rk = in2 ? rk2 : rk1, info = in2 ? info2 : info1;
+              if (!bw || !(info & 1)) { word0[u] = bw ? (info >> 1) : 0u; stt[u] = 2; }
+              else if (!v_staged) {
+                const uint32_t bit = (info >> 1) * 8u + (kk[u] - rk) * bw + vs_mis;
+                word0[u] = __ldg(vwords + (bit >> 5));
+                word1[u] = __ldg(vwords + (bit >> 5) + 1);
+                sh[u] = bit & 31;
+                stt[u] = 3;
+              } else {
+                word0[u] = smem_bits(vsd_al, vsd_mis + (info >> 1) * 8u + (kk[u] - rk) * bw, bwmask);
+                stt[u] = 2;
+              }
+            }
+          }
+        }
+        int64_t vv[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          vv[u] = 0;
+          if (stt[u] >= 2) {
+            uint32_t ix = stt[u] == 3 ? (__funnelshift_r(word0[u], word1[u], sh[u]) & bwmask) : word0[u];
+            if (ix >= t.dict_count) { if (err) atomicExch(err, 6); continue; }
+            vv[u] = t.width == 4 ? (int64_t)__ldg(reinterpret_cast<const int32_t*>(t.dict) + ix)
+                                 : __ldg(reinterpret_cast<const int64_t*>(t.dict) + ix);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          if (stt[u]) {
+            const uint32_t i = (bb + u) * 32 + lane;
+            if (t.width == 4) reinterpret_cast<int32_t*>(t.out)[orow + i] = (int32_t)vv[u];
+            else reinterpret_cast<int64_t*>(t.out)[orow + i] = vv[u];
+          }
+        }
+        continue;
+      }
+      // ---- general path: per-tile cursor, any mix of runs, batch boundaries ---------------------------------
+      const uint32_t sb = bb, se = be;
+        for (uint32_t tb = sb; tb < se; tb += kUnroll) {
+        uint32_t k[kUnroll], idx[kUnroll];
+        uint64_t gbit[kUnroll];                     // global bit offset of a bit-packed value not yet fetched
+        int st[kUnroll];                            // 0 skip, 1 write null/zero, 2 write value, 3 value needs a global fetch
+  #pragma unroll
         for (int u = 0; u < kUnroll; ++u) {
-          uint32_t want = __ballot_sync(0xFFFFFFFFu, st[u] == 2);
-          if (!want) continue;
-          // k grows with the lane: first / last wanted lanes give the tile's k range
-          const uint32_t kmin = __shfl_sync(0xFFFFFFFFu, k[u], __ffs(want) - 1);
-          const uint32_t kmax = __shfl_sync(0xFFFFFFFFu, k[u], 31 - __clz(want));
-          // ---- move the warp cursor to the run containing kmin (uniform) ------------------------------------
-          if (!cur_ok || kmin < ck || kmin >= ck + ccnt) {
-            if (!cur_ok || kmin < ck || (ce + 1 < ne && ent_k[ce + 1] <= kmin)) {
-              int lo = (cur_ok && kmin >= ck) ? ce : 0, hi = ne - 1;     // last entry with ent_k <= kmin
-              while (lo < hi) {
-                int mid = (lo + hi + 1) >> 1;
-                if (ent_k[mid] <= kmin) lo = mid; else hi = mid - 1;
-              }
-              ce = lo;
-              cur_ok = false;
-            }
-            if (!staged) {
-              ck = ent_k[ce];
-              ccnt = ent_k[ce + 1] - ck;
-              cinfo = ent_pos[ce];
-            } else {
-              if (!cur_ok) { cp = ent_pos[ce]; ck = ent_k[ce]; }
-              // walk headers forward from (cp, ck) until the run holds kmin
-              uint32_t len;
-              if (cur_ok) {               // current run is known and too early: step past it first
-                uint32_t c0, i0;
-                len = parse_run(sd, cp, L, bw, c0, i0);
-                cp += len;
-                ck += c0;
-              }
-              for (;;) {
-                len = parse_run(sd, cp, L, bw, ccnt, cinfo);
-                if (ck + ccnt > kmin || cp + len >= L) break;
-                cp += len;
-                ck += ccnt;
-              }
-            }
-            cur_ok = true;
-          }
-          if (st[u] != 2) continue;
-          uint32_t rk = ck, info = cinfo;
-          if (kmax >= ck + ccnt && k[u] >= ck + ccnt) {
-            // the tile straddles runs and my value lies in a later one: walk on privately
-            if (!staged) {
-              int e = ce;
-              while (e + 1 < ne && ent_k[e + 1] <= k[u]) ++e;
-              rk = ent_k[e];
-              info = ent_pos[e];
-            } else {
-              uint32_t p = cp, cnt = ccnt;
-              for (;;) {
-                uint32_t len = parse_run(sd, p, L, bw, cnt, info);
-                if (rk + cnt > k[u] || p + len >= L) break;
-                p += len;
-                rk += cnt;
-              }
-            }
-          }
-          if (!(info & 1)) idx[u] = info >> 1;
-          else if (!staged) idx[u] = extract_bits(sd + (info >> 1), (uint64_t)(k[u] - rk) * bw, bw);
-          else {
-            // bit-packed payload in shared memory: byte-wise extraction
-            const uint8_t* q = sd + (info >> 1);
-            uint64_t bit = (uint64_t)(k[u] - rk) * bw;
-            uint32_t by = (uint32_t)(bit >> 3);
-            uint64_t v = 0;
-            for (int b = 0; b < 5; ++b) v |= (uint64_t)q[by + b] << (8 * b);
-            v >>= (bit & 7);
-            idx[u] = bw == 32 ? (uint32_t)v : ((uint32_t)v & ((1u << bw) - 1u));
+          uint32_t i = (tb + u) * 32 + lane;
+          st[u] = 0;
+          idx[u] = 0;
+          k[u] = 0;
+          gbit[u] = 0;
+          if (tb + u < se && i < n) {
+            bool ok = row_state(i, k[u]);
+            if (!ok) st[u] = k_lo == 0 ? 1 : 0;        // nulls are written once, with the first batch
+            else if (k[u] >= k_lo && k[u] < k_hi) st[u] = 2;
           }
         }
-      }
-      int64_t v[kUnroll];
-#pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        v[u] = 0;
-        if (st[u] == 2) {
-          if (idx[u] >= t.dict_count) { if (err) atomicExch(err, 6); st[u] = 1; continue; }
-          v[u] = t.width == 4 ? (int64_t)__ldg(reinterpret_cast<const int32_t*>(t.dict) + idx[u])
-                              : __ldg(reinterpret_cast<const int64_t*>(t.dict) + idx[u]);
+        if (bw) {
+          // pass 1: locate every value's run (no global loads for bit-packed values yet)
+  #pragma unroll
+          for (int u = 0; u < kUnroll; ++u) {
+            const uint32_t want = __ballot_sync(0xFFFFFFFFu, st[u] == 2);
+            if (!want) continue;
+            // k grows with the lane: first / last wanted lanes give the tile's k range
+            const uint32_t kmin = __shfl_sync(0xFFFFFFFFu, k[u], __ffs(want) - 1);
+            const uint32_t kmax = __shfl_sync(0xFFFFFFFFu, k[u], 31 - __clz(want));
+            if (!cur_ok || kmin < ck || kmin >= ck + ccnt) {
+              // move the warp cursor to the run containing kmin (uniform across the warp)
+              if (!cur_ok || kmin < ck || (ce + 1 < ne && ek[ce + 1] <= kmin)) {
+                int lo = (cur_ok && kmin >= ck) ? ce : 0, hi = ne - 1;     // last entry with ek <= kmin
+                while (lo < hi) {
+                  int mid = (lo + hi + 1) >> 1;
+                  if (ek[mid] <= kmin) lo = mid; else hi = mid - 1;
+                }
+                ce = lo;
+                cur_ok = false;
+              }
+              if (!v_staged) {
+                ck = ek[ce];
+                ccnt = ek[ce + 1] - ck;
+                cinfo = ep[ce];
+              } else {
+                uint32_t len;
+                if (!cur_ok) { cp = ep[ce]; ck = ek[ce]; }
+                else {                      // current run is known and too early: step past it first
+                  uint32_t c0, i0;
+                  len = parse_run_s(vsd, cp, L, bw, c0, i0);
+                  cp += len;
+                  ck += c0;
+                }
+                for (;;) {
+                  len = parse_run_s(vsd, cp, L, bw, ccnt, cinfo);
+                  if (ck + ccnt > kmin || cp + len >= L) break;
+                  cp += len;
+                  ck += ccnt;
+                }
+              }
+              cur_ok = true;
+            }
+            if (st[u] != 2) continue;
+            uint32_t rk = ck, info = cinfo;
+            if (kmax >= ck + ccnt && k[u] >= ck + ccnt) {
+              // the tile straddles runs and my value lies in a later one: walk on privately
+              if (!v_staged) {
+                int e = ce;
+                while (e + 1 < ne && ek[e + 1] <= k[u]) ++e;
+                rk = ek[e];
+                info = ep[e];
+              } else {
+                uint32_t p = cp, cnt = ccnt;
+                for (;;) {
+                  uint32_t len = parse_run_s(vsd, p, L, bw, cnt, info);
+                  if (rk + cnt > k[u] || p + len >= L) break;
+                  p += len;
+                  rk += cnt;
+                }
+              }
+            }
+            if (!(info & 1)) idx[u] = info >> 1;
+            else if (!v_staged) {
+              gbit[u] = (uint64_t)(info >> 1) * 8u + (uint64_t)(k[u] - rk) * bw;
+              st[u] = 3;
+            } else {
+              idx[u] = smem_bits(vsd_al, vsd_mis + (info >> 1) * 8u + (k[u] - rk) * bw, bwmask);
+            }
+          }
+          // pass 2: all global fetches of the four tiles back to back, pass 3: combine
+          uint32_t w0[kUnroll], w1[kUnroll];
+  #pragma unroll
+          for (int u = 0; u < kUnroll; ++u) {
+            w0[u] = 0;
+            w1[u] = 0;
+            if (st[u] == 3) {
+              const uintptr_t a = reinterpret_cast<uintptr_t>(vstream) + (uintptr_t)(gbit[u] >> 3);
+              const uint32_t* wp = reinterpret_cast<const uint32_t*>(a & ~uintptr_t(3));
+              w0[u] = __ldg(wp);
+              w1[u] = __ldg(wp + 1);
+            }
+          }
+  #pragma unroll
+          for (int u = 0; u < kUnroll; ++u) {
+            if (st[u] == 3) {
+              const uintptr_t a = reinterpret_cast<uintptr_t>(vstream) + (uintptr_t)(gbit[u] >> 3);
+              uint64_t v = ((uint64_t)w1[u] << 32) | w0[u];
+              v >>= (uint32_t)(a & 3) * 8 + (uint32_t)(gbit[u] & 7);
+              idx[u] = bw == 32 ? (uint32_t)v : ((uint32_t)v & ((1u << bw) - 1u));
+              st[u] = 2;
+            }
+          }
         }
-      }
-#pragma unroll
-      for (int u = 0; u < kUnroll; ++u) {
-        uint32_t i = (tb + u) * 32 + lane;
-        if (st[u]) {
-          if (t.width == 4) reinterpret_cast<int32_t*>(t.out)[orow + i] = (int32_t)v[u];
-          else reinterpret_cast<int64_t*>(t.out)[orow + i] = v[u];
+        int64_t v[kUnroll];
+  #pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          v[u] = 0;
+          if (st[u] == 2) {
+            if (idx[u] >= t.dict_count) { if (err) atomicExch(err, 6); st[u] = 1; continue; }
+            v[u] = t.width == 4 ? (int64_t)__ldg(reinterpret_cast<const int32_t*>(t.dict) + idx[u])
+                                : __ldg(reinterpret_cast<const int64_t*>(t.dict) + idx[u]);
+          }
+        }
+  #pragma unroll
+        for (int u = 0; u < kUnroll; ++u) {
+          uint32_t i = (tb + u) * 32 + lane;
+          if (st[u]) {
+            if (t.width == 4) reinterpret_cast<int32_t*>(t.out)[orow + i] = (int32_t)v[u];
+            else reinterpret_cast<int64_t*>(t.out)[orow + i] = v[u];
+          }
         }
       }
     }
@@ -675,6 +911,7 @@ __global__ void fill_segments_kernel(const int64_t* __restrict__ seg_start, cons
 }
 
 int decode_slices(int npages) {
+  // few pages: share each page between several CTAs so that the launch still covers the 148 SMs twice
   int nslices = 1;
   if (npages > 0 && npages < 2 * 148) {
     nslices = (2 * 148 + npages - 1) / npages;
@@ -685,7 +922,6 @@ int decode_slices(int npages) {
 
 void launch_decode_pages(const PageTask* d_tasks, int npages, int* d_err, cudaStream_t stream, long long* dbg) {
   if (npages <= 0) return;
-  // few pages: share each page between several CTAs so that the launch still covers the 148 SMs twice
   const int nslices = decode_slices(npages);
   decode_pages_kernel<<<npages * nslices, kDecodeThreads, 0, stream>>>(d_tasks, nslices, d_err, dbg);
   NDS_CUDA(cudaGetLastError());

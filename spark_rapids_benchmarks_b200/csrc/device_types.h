@@ -11,7 +11,7 @@ enum DType : int { DT_I32 = 0, DT_I64 = 1, DT_F64 = 2, DT_STR = 3 };
 typedef uint64_t StrView;
 
 constexpr int kMaxPageValues = 32768;     // rows per data page the decode kernel accepts (writers default to 20000)
-constexpr int kDecodeThreads = 512;
+constexpr int kDecodeThreads = 256;
 constexpr int kRunCap = 512;              // run-table entries per batch (shared memory)
 constexpr int kPagePad = 16;              // readable slack after every staged page payload
 
@@ -30,7 +30,7 @@ struct PageTask {
   uint8_t enc;           // 0 PLAIN, 1 RLE_DICTIONARY
   uint8_t width;         // 4 or 8 bytes per output value
   uint8_t phys;          // 0 fixed-width, 1 BYTE_ARRAY
-  uint8_t pad;
+  uint8_t bw;            // dictionary index bit width (enc == 1)
 };
 
 // Column reference as kernels see it.

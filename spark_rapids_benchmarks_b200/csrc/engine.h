@@ -54,6 +54,7 @@ struct PageInfo {
   uint32_t size, num_values, def_len;
   int64_t row_in_file;
   uint8_t enc;                 // 0 PLAIN, 1 dictionary
+  uint8_t bw = 0;              // dictionary index bit width (first byte of the values section)
 };
 struct DictInfo {
   int64_t off;                 // fixed width: values; BYTE_ARRAY: StrView table (chars follow)

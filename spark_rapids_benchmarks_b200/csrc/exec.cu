@@ -538,6 +538,7 @@ struct Exec {
           task.def_len = pi.def_len;
           task.src_off = (uint32_t)pi.off;
           task.enc = pi.enc;
+          task.bw = pi.bw;
           task.width = (uint8_t)width;
           task.phys = tc.phys == pq::BYTE_ARRAY ? 1 : 0;
           if (pi.dict >= 0) {

@@ -255,6 +255,9 @@ void Engine::register_table(const std::string& name, const std::string& path, co
             else if (ph.encoding == pq::RLE_DICTIONARY || ph.encoding == pq::PLAIN_DICTIONARY) {
               pi.enc = 1;
               pi.dict = cur_dict;
+              if (values_off >= psize) fail("dictionary-encoded page without index data in '" + fi.path + "'");
+              pi.bw = payload[values_off];
+              if (pi.bw > 32) fail("dictionary index bit width " + std::to_string(pi.bw) + " in '" + fi.path + "'");
               if (cur_dict < 0) fail("dictionary-encoded page without dictionary in '" + fi.path + "'");
             } else fail("unsupported data page encoding " + std::to_string(ph.encoding) + " in '" + fi.path + "'");
             // place the payload so that its values section is 16 B aligned
