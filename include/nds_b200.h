@@ -73,6 +73,31 @@ NDS_API int nds_engine_execute(nds_engine* e, const char* plan_json, struct Arro
  * per-operator {op, ms, bytes, rows}. */
 NDS_API int nds_engine_last_stats(nds_engine* e, char* buf, int64_t buflen);
 
+/* Hash-join lookup that allocates nothing (no counterpart in the reference).
+ *
+ * For callers that must not allocate GPU memory while a query runs: an engine embedded in a host whose own
+ * memory manager already holds the device (spark-rapids gives nearly all HBM to its RMM pool at executor
+ * start-up, so a cudaMalloc from inside a library fails or escapes the pool's spill accounting), or a caller
+ * that cannot afford the driver's allocator lock on its latency path.  nds_engine_execute draws its hash
+ * tables from CUDA's memory pool; this entry point instead keeps the table in a fixed array inside the
+ * library, so it calls no cudaMalloc / cudaFree / pool routine at all.
+ *
+ *   out_build_row_dev[i] = index of the build key equal to probe_keys_dev[i], or -1 if there is none.
+ *
+ * All three pointers are device pointers supplied by the caller; keys are int64, every key is valid, build
+ * keys must be unique and INT64_MIN is reserved (both are reported as errors).  cuda_stream is a cudaStream_t
+ * (NULL = default stream); the call returns after the work on that stream has finished.
+ * Limits and sharing: at most NDS_NOALLOC_MAX_BUILD_KEYS build keys - more is refused with an error, nothing
+ * is truncated.  The table (about 1.5 MB) is part of the loaded module: each GPU that uses the library holds
+ * it until the process exits.  There is ONE table per GPU, reused by every call and left holding the last
+ * call's keys; each call clears it first.  Two calls whose GPU work overlaps (different streams or threads)
+ * would race on it - serialise them.  The first call on a device looks the table's address up
+ * (cudaGetSymbolAddress, with that device current); make that first call outside any stream capture.
+ * On failure returns non-zero and nds_last_error() holds the message. */
+#define NDS_NOALLOC_MAX_BUILD_KEYS 65536
+NDS_API int nds_join_probe_i64_noalloc(const int64_t* build_keys_dev, int32_t n_build, const int64_t* probe_keys_dev,
+                                       int64_t n_probe, int32_t* out_build_row_dev, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(_HERE, 'libndsb200.so')
 SYMBOLS = ['nds_version', 'nds_last_error', 'nds_engine_create', 'nds_engine_destroy',
            'nds_engine_last_error', 'nds_engine_register_table', 'nds_engine_register_arrow',
            'nds_engine_drop_table', 'nds_engine_table_info', 'nds_engine_execute',
-           'nds_engine_last_stats']
+           'nds_engine_last_stats', 'nds_join_probe_i64_noalloc']
 
 _lib = None
 
@@ -49,6 +49,7 @@ def load_library(path=None):
     lib.nds_engine_table_info.argtypes = [vp, cp, ctypes.c_char_p, i64]
     lib.nds_engine_execute.argtypes = [vp, cp, vp, vp]
     lib.nds_engine_last_stats.argtypes = [vp, ctypes.c_char_p, i64]
+    lib.nds_join_probe_i64_noalloc.argtypes = [vp, ctypes.c_int32, vp, i64, vp, vp]
     if path is None:
         _lib = lib
     return lib
