@@ -292,20 +292,25 @@ def main():
     peak = peaks.get('hbm_gbs', 6650.0)
     roof = None
     if dec:
-        byts = sum(o['bytes'] for o in dec)
-        ms = sum(o['ms'] for o in dec)
-        ach = byts / (ms * 1e-3) / 1e9
+        # the dominant launch: the largest decode launch of the stream (query7's store_sales scan), one per step
+        big = max(o['bytes'] for o in dec)
+        top = [o for o in dec if o['bytes'] == big]
+        ach = big / (sum(o['ms'] for o in top) / len(top) * 1e-3) / 1e9
+        all_bytes = sum(o['bytes'] for o in dec)
+        all_ms = sum(o['ms'] for o in dec)
         traffic = None
         tp = os.path.join(ROOT, 'profiles', 'decode_traffic.json')
-        if os.path.exists(tp):
+        if os.path.exists(tp) and world == 1:
             try:
                 traffic = json.load(open(tp)).get('dram_bytes_per_launch')
             except Exception:
                 traffic = None
         roof = {'bound': 'hbm', 'kernel': 'decode_pages_kernel', 'achieved': ach, 'peak': peak, 'unit': 'GB/s', 'frac': ach / peak,
                 'traffic': traffic, 'peak_source': 'MEASURED_PEAKS.json (measured)' if 'hbm_gbs' in peaks else 'fallback 6.65 TB/s',
-                'launches': len(dec), 'algorithmic_bytes_per_launch': byts / len(dec), 'avg_launch_us': ms / len(dec) * 1000.0,
-                'share_of_step': ms / (eng_ms if eng_ms > 0 else 1.0)}
+                'launch': 'largest decode launch of the stream (store_sales scan of query7), %d timed launches' % len(top),
+                'algorithmic_bytes_per_launch': big, 'avg_launch_us': sum(o['ms'] for o in top) / len(top) * 1000.0,
+                'all_decode_launches': {'n': len(dec), 'achieved': all_bytes / (all_ms * 1e-3) / 1e9,
+                                        'share_of_step': all_ms / (eng_ms if eng_ms > 0 else 1.0)}}
 
     if rank != 0:
         if world > 1:

@@ -523,10 +523,15 @@ struct Exec {
         }
       }
       col.strbase = src_base;
+      int last_dict = -1;
       for (size_t k = 0; k < sel.size(); ++k) {
         int f = sel[k];
         for (int64_t p = tc.file_page_begin[f]; p < tc.file_page_begin[f + 1]; ++p) {
           const PageInfo& pi = tc.pages[p];
+          if (pi.dict >= 0 && pi.dict != last_dict) {       // each dictionary page is read once per scan
+            last_dict = pi.dict;
+            bytes_in += (int64_t)tc.dicts[pi.dict].count * (tc.phys == pq::BYTE_ARRAY ? 8 : width);
+          }
           PageTask task;
           memset(&task, 0, sizeof task);
           task.src = src_base + pi.off;

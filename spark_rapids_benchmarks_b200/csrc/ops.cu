@@ -470,24 +470,39 @@ radix_sort_small_kernel(const uint8_t* __restrict__ keybuf, int B, const int* __
                         uint32_t* perm_a, uint32_t* perm_b, int* which) {
   __shared__ uint32_t hist[256];
   __shared__ uint32_t base[256];
+  __shared__ uint32_t wtot[8];
   __shared__ uint16_t wcnt[kSmallThreads / 32][256];
+  __shared__ uint8_t s_active[512];
   const int n = (int)row_count(n_dev, n_host);
-  const int tid = threadIdx.x, warp = tid >> 5;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   for (int i = tid; i < n; i += kSmallThreads) perm_a[i] = (uint32_t)i;
+  for (int b = tid; b < B && b < 512; b += kSmallThreads) s_active[b] = active[b] ? 1 : 0;
   int cur = 0;
   __syncthreads();
   for (int byte = B - 1; byte >= 0; --byte) {
-    if (!active[byte]) continue;
+    if (byte < 512 ? !s_active[byte] : !active[byte]) continue;
     const uint32_t* src = cur ? perm_b : perm_a;
     uint32_t* dst = cur ? perm_a : perm_b;
     if (tid < 256) hist[tid] = 0;
     __syncthreads();
     for (int i = tid; i < n; i += kSmallThreads) atomicAdd(&hist[keybuf[(int64_t)src[i] * B + byte]], 1u);
     __syncthreads();
+    // exclusive scan of the 256 bins: warp shuffles + 8 warp totals
+    uint32_t hv = 0, incl = 0;
+    if (tid < 256) {
+      hv = hist[tid];
+      incl = hv;
+      for (int d = 1; d < 32; d <<= 1) {
+        uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+        if (lane >= d) incl += v;
+      }
+      if (lane == 31) wtot[warp] = incl;
+    }
+    __syncthreads();
     if (tid < 256) {
       uint32_t b = 0;
-      for (int k = 0; k < tid; ++k) b += hist[k];
-      base[tid] = b;
+      for (int w = 0; w < warp; ++w) b += wtot[w];
+      base[tid] = b + incl - hv;
     }
     __syncthreads();
     for (int c0 = 0; c0 < n; c0 += kSmallThreads) {
