@@ -322,9 +322,9 @@ void Engine::drop_table(const std::string& name) {
     if (tc.pinned) cudaHostUnregister(tc.stage.data());
   }
   for (MemColumn& mc : it->second.mem_cols) {
-    if (mc.d_data) cudaFree(mc.d_data);
-    if (mc.d_valid) cudaFree(mc.d_valid);
-    if (mc.d_chars) cudaFree(mc.d_chars);
+    if (mc.d_data) cudaFreeAsync(mc.d_data, stream_);
+    if (mc.d_valid) cudaFreeAsync(mc.d_valid, stream_);
+    if (mc.d_chars) cudaFreeAsync(mc.d_chars, stream_);
   }
   tables_.erase(it);
 }
@@ -349,18 +349,20 @@ void Engine::register_arrow(const std::string& name, ArrowSchema* schema, ArrowA
     std::string f = cs->format;
     const uint8_t* validity = (const uint8_t*)ca->buffers[0];
     int64_t vwords = (n + 31) / 32 + 1;
+    // stream-ordered pool allocations and copies: registering the gathered partial aggregates of a multi-GPU
+    // query sits on the query's critical path, so no cudaMalloc / cudaFree device synchronisation here
+    auto upload = [&](const void* src, int64_t bytes) {
+      void* d = nullptr;
+      NDS_CUDA(cudaMallocAsync(&d, (size_t)bytes + 256, stream_));
+      if (bytes) NDS_CUDA(cudaMemcpyAsync(d, src, (size_t)bytes, cudaMemcpyHostToDevice, stream_));
+      NDS_CUDA(cudaStreamSynchronize(stream_));     // src may be a temporary
+      return d;
+    };
     if (validity && ca->null_count != 0) {
       std::vector<uint32_t> v(vwords, 0);
       memcpy(v.data(), validity, (n + 7) / 8);
-      NDS_CUDA(cudaMalloc(&mc.d_valid, vwords * 4));
-      NDS_CUDA(cudaMemcpy(mc.d_valid, v.data(), vwords * 4, cudaMemcpyHostToDevice));
+      mc.d_valid = (uint32_t*)upload(v.data(), vwords * 4);
     }
-    auto upload = [&](const void* src, int64_t bytes) {
-      void* d = nullptr;
-      NDS_CUDA(cudaMalloc(&d, bytes + 256));
-      if (bytes) NDS_CUDA(cudaMemcpy(d, src, bytes, cudaMemcpyHostToDevice));
-      return d;
-    };
     if (f == "i") { mc.lt.kind = LType::INT; mc.lt.is32 = true; mc.d_data = upload(ca->buffers[1], n * 4); }
     else if (f == "tdD") { mc.lt.kind = LType::DATE; mc.lt.is32 = true; mc.d_data = upload(ca->buffers[1], n * 4); }
     else if (f == "l") { mc.lt.kind = LType::INT; mc.d_data = upload(ca->buffers[1], n * 8); }

@@ -26,16 +26,17 @@ def deserialize_table(buf):
 
 
 def all_gather_bytes(payload, group=None):
-    """Variable-length all-gather of one bytes object per rank over torch.distributed."""
+    """Variable-length all-gather of one bytes object per rank over torch.distributed
+    (one collective for the lengths, one for the padded payloads)."""
     import torch
     import torch.distributed as dist
     world = dist.get_world_size(group)
     backend = dist.get_backend(group)
     dev = torch.device('cuda', torch.cuda.current_device()) if backend == 'nccl' else torch.device('cpu')
     n = torch.tensor([len(payload)], dtype=torch.int64, device=dev)
-    sizes = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
-    dist.all_gather(sizes, n, group=group)
-    sizes = [int(s.item()) for s in sizes]
+    sizes_t = torch.empty(world, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(sizes_t, n, group=group)
+    sizes = sizes_t.tolist()
     m = max(max(sizes), 1)
     send = torch.zeros(m, dtype=torch.uint8)
     if payload:
@@ -64,10 +65,23 @@ def merge_and_finish(engine, plan, tables, source=None):
         engine.drop_table('__partial__')
 
 
+def _add_stats(a, b):
+    out = dict(b)
+    for k in ('launches', 'device_ms', 'h2d_bytes', 'd2h_bytes'):
+        out[k] = a.get(k, 0) + b.get(k, 0)
+    out['ops'] = list(a.get('ops', [])) + list(b.get('ops', []))
+    return out
+
+
 def execute_distributed(session, plan):
+    """Partial plan on this rank's shard -> all-gather of the partial states -> merge on every rank.
+    Leaves the summed statistics of both engine calls in session.dist_stats."""
     if 'partial' not in plan:
         raise ValueError('plan was not built with distributed=True')
     src = session.source if session.source != 'hbm' else None
     partial = session.engine.execute({'root': plan['partial']}, source=src)
+    st = session.engine.last_stats()
     gathered = all_gather_batches(partial, session.comm)
-    return merge_and_finish(session.engine, plan, [gathered])
+    out = merge_and_finish(session.engine, plan, [gathered])
+    session.dist_stats = _add_stats(st, session.engine.last_stats())
+    return out

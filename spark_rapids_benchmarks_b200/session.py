@@ -108,9 +108,10 @@ class Session:
         if self.world > 1:
             from . import dist
             batch = dist.execute_distributed(self, plan)
+            self.last_stats = self.dist_stats
         else:
             batch = self.engine.execute({'root': plan['root']}, source=self.source if self.source != 'hbm' else None)
-        self.last_stats = self.engine.last_stats()
+            self.last_stats = self.engine.last_stats()
         return pa.Table.from_batches([batch]) if isinstance(batch, pa.RecordBatch) else batch
 
     def stop(self):
