@@ -165,6 +165,8 @@ class Engine {
   double exec_ms_ = 0;
   uint8_t* pin_ = nullptr;      // pinned host ring for small host->device uploads (plan blobs, page tasks)
   int64_t pin_cap_ = 0;
+  uint8_t* slab_ = nullptr;     // device slab behind the per-query bump allocator
+  int64_t slab_cap_ = 0;
 };
 
 void set_global_error(const std::string& s);

@@ -11,12 +11,54 @@ namespace nds {
 
 namespace {
 
+// Per-query device memory: a bump allocator over a slab the engine owns (stream-ordered reuse: every query runs on
+// the engine's one stream), with cudaMallocAsync only for what does not fit.  A query makes ~100 small allocations;
+// as driver calls they cost more than the kernels they feed.
 struct Arena {
   cudaStream_t s;
-  std::vector<void*> ptrs;
+  std::vector<void*> ptrs;      // overflow allocations (freed at the end of the query)
+  uint8_t* slab = nullptr;
+  int64_t slab_cap = 0, slab_off = 0;
+  int64_t zero_off = 0, zero_cap = 0;   // pre-zeroed prefix of the slab for counters and flags
   uint8_t* pin = nullptr;       // pinned staging ring owned by the engine (reset per query)
   int64_t pin_cap = 0, pin_off = 0;
   explicit Arena(cudaStream_t st) : s(st) {}
+  void attach_slab(uint8_t* p, int64_t cap) {
+    slab = p;
+    slab_cap = cap;
+    zero_cap = p ? std::min<int64_t>(cap / 4, 256 << 10) : 0;
+    zero_off = 0;
+    slab_off = zero_cap;
+    if (zero_cap) NDS_CUDA(cudaMemsetAsync(slab, 0, (size_t)zero_cap, s));
+  }
+  void* alloc(int64_t bytes) {
+    if (bytes < 16) bytes = 16;
+    const int64_t need = align_up(bytes + 64, 256);
+    if (slab && slab_off + need <= slab_cap) {
+      void* p = slab + slab_off;
+      slab_off += need;
+      return p;
+    }
+    void* p = nullptr;
+    NDS_CUDA(cudaMallocAsync(&p, (size_t)bytes + 64, s));
+    ptrs.push_back(p);
+    return p;
+  }
+  template <typename T>
+  T* alloc_n(int64_t n) { return reinterpret_cast<T*>(alloc(n * (int64_t)sizeof(T))); }
+  template <typename T>
+  T* zeros(int64_t n) {
+    const int64_t bytes = std::max<int64_t>(n, 1) * (int64_t)sizeof(T);
+    const int64_t need = align_up(bytes, 16);
+    if (need <= 4096 && zero_off + need <= zero_cap) {
+      T* p = reinterpret_cast<T*>(slab + zero_off);
+      zero_off += need;
+      return p;
+    }
+    T* p = alloc_n<T>(n);
+    NDS_CUDA(cudaMemsetAsync(p, 0, (size_t)(bytes < 16 ? 16 : bytes), s));
+    return p;
+  }
   // host -> device copy that does not need a stream sync when the bytes fit the pinned ring
   void upload(void* dst, const void* src, int64_t bytes) {
     if (bytes <= 0) return;
@@ -29,21 +71,6 @@ struct Arena {
       NDS_CUDA(cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyHostToDevice, s));
       NDS_CUDA(cudaStreamSynchronize(s));
     }
-  }
-  void* alloc(int64_t bytes) {
-    void* p = nullptr;
-    if (bytes < 16) bytes = 16;
-    NDS_CUDA(cudaMallocAsync(&p, (size_t)bytes + 64, s));
-    ptrs.push_back(p);
-    return p;
-  }
-  template <typename T>
-  T* alloc_n(int64_t n) { return reinterpret_cast<T*>(alloc(n * (int64_t)sizeof(T))); }
-  template <typename T>
-  T* zeros(int64_t n) {
-    T* p = alloc_n<T>(n);
-    NDS_CUDA(cudaMemsetAsync(p, 0, (size_t)(n < 1 ? 16 : n * (int64_t)sizeof(T)), s));
-    return p;
   }
   ~Arena() {
     for (void* p : ptrs) cudaFreeAsync(p, s);
@@ -158,6 +185,7 @@ struct Exec {
   Exec(Engine& en, const Json* options) : e(en), ar(en.stream_), s(en.stream_) {
     ar.pin = en.pin_;
     ar.pin_cap = en.pin_cap_;
+    ar.attach_slab(en.slab_, en.slab_cap_);
     err = ar.zeros<int>(4);
     if (options) {
       source_host = options->str_or("source", "hbm") == "host";
@@ -651,6 +679,58 @@ struct Exec {
     return o;
   }
 
+  // Several expressions -> flat columns with ONE kernel launch (rows: optional gather indices).
+  std::vector<Column> eval_columns(const std::vector<std::pair<std::string, const Json*>>& exprs, Batch& in, const uint32_t* rows,
+                                   RowCount n) {
+    std::vector<Column> outc;
+    if (exprs.empty()) return outc;
+    Blob bb;
+    std::vector<ProjSpec> specs(exprs.size());
+    for (size_t k = 0; k < exprs.size(); ++k) {
+      std::vector<Instr> code;
+      int origin = -1;
+      LType t = compile(*exprs[k].second, in, bb, code, &origin);
+      bb.add_prog(code, t);
+      Column o;
+      o.name = exprs[k].first;
+      o.lt = t;
+      if (t.kind == LType::BOOL) { o.lt.kind = LType::INT; o.lt.is32 = false; }
+      const DType dt = o.lt.dtype();
+      memset(&specs[k], 0, sizeof(ProjSpec));
+      if (dt == DT_STR) {
+        if (origin < 0) fail("plan: a string-valued projection must be a column or substr(column)");
+        o.strbase = in.cols[origin].strbase;
+        specs[k].strbase = o.strbase;
+      }
+      void* d = ar.alloc(n.host * (dt == DT_I32 ? 4 : 8));
+      uint32_t* v = ar.alloc_n<uint32_t>((n.host + 31) / 32 + 1);
+      o.data = d;
+      o.valid = v;
+      specs[k].out = d;
+      specs[k].valid = v;
+      specs[k].dtype = dt;
+      outc.push_back(o);
+    }
+    // program pointers are only known after the upload layout is fixed: upload once to learn them, patch, upload specs
+    Blob::Dev dev = bb.upload(ar, s);
+    for (size_t k = 0; k < exprs.size(); ++k) specs[k].prog = dev.host_progs[k];
+    ProjSpec* d_specs = ar.alloc_n<ProjSpec>((int64_t)specs.size());
+    ar.upload(d_specs, specs.data(), (int64_t)(specs.size() * sizeof(ProjSpec)));
+    launch_project_multi(d_specs, (int)specs.size(), dev.ctx, n, rows, err, s);
+    ++launches;
+    return outc;
+  }
+
+  static Json col_expr(const std::string& name) {
+    Json ce;
+    ce.kind = Json::Obj;
+    Json cn;
+    cn.kind = Json::Str;
+    cn.s = name;
+    ce.o.emplace_back("col", cn);
+    return ce;
+  }
+
   Batch project(const Json& node, std::vector<RuntimeFilter>& filters) {
     Batch in = exec(node.at("child"), filters);
     size_t st = begin_stat("project");
@@ -658,6 +738,8 @@ struct Exec {
     out.n_max = in.n_max;
     out.n_dev = in.n_dev;
     out.n_exact = in.n_exact;
+    std::vector<std::pair<std::string, const Json*>> computed;
+    std::vector<int> slot;       // position in out.cols of each computed column
     for (const Json& pe : node.at("exprs").a) {
       const std::string& name = pe.str("name");
       const Json& ex = pe.at("expr");
@@ -668,8 +750,14 @@ struct Exec {
         o.name = name;
         out.cols.push_back(o);
       } else {
-        out.cols.push_back(eval_to_column(ex, name, in, nullptr, in.rc()));
+        computed.emplace_back(name, &ex);
+        slot.push_back((int)out.cols.size());
+        out.cols.push_back(Column());
       }
+    }
+    if (!computed.empty()) {
+      std::vector<Column> cc = eval_columns(computed, in, nullptr, in.rc());
+      for (size_t k = 0; k < cc.size(); ++k) out.cols[slot[k]] = cc[k];
     }
     end_stat(st, 0, in.n_max);
     return out;
@@ -686,7 +774,9 @@ struct Exec {
     int kb = build.find(bk);
     if (kb < 0) fail("plan: build key '" + bk + "' not found");
     if (!is_intlike(build.cols[kb].lt)) fail("plan: join keys must be integer columns");
-    int64_t nb = count(build);
+    // small build sides (every dimension table): size the table from the upper bound, no host round trip
+    const int64_t nb_bound = build.rc().host;
+    const int64_t nb = nb_bound <= (int64_t(4) << 20) ? nb_bound : count(build);
     size_t stb = begin_stat("join_build");
     HashTable ht;
     uint32_t cap = next_pow2(2 * nb);
@@ -700,22 +790,25 @@ struct Exec {
     // dynamic partition pruning: ship the (small) build key set to the host and let the scan skip files
     std::vector<RuntimeFilter> down = filters;
     if (node.bool_or("prune_partitions", false)) {
-      Json kexpr;
-      kexpr.kind = Json::Obj;
-      Json cn; cn.kind = Json::Str; cn.s = bk;
-      kexpr.o.emplace_back("col", cn);
+      Json kexpr = col_expr(bk);
       Column flat = eval_to_column(kexpr, bk, build, nullptr, build.rc());
       RuntimeFilter rf;
       rf.column = pk;
       if (nb > 0) {
+        // keys of the upper-bound row range and the exact count come back in one synchronisation
         const bool is32 = flat.lt.dtype() == DT_I32;
         std::vector<uint8_t> hk(nb * (is32 ? 4 : 8));
         std::vector<uint32_t> hv((nb + 31) / 32);
+        int hcount = (int)nb;
         NDS_CUDA(cudaMemcpyAsync(hk.data(), flat.data, hk.size(), cudaMemcpyDeviceToHost, s));
         NDS_CUDA(cudaMemcpyAsync(hv.data(), flat.valid, hv.size() * 4, cudaMemcpyDeviceToHost, s));
+        if (build.n_dev && build.n_exact < 0) NDS_CUDA(cudaMemcpyAsync(&hcount, build.n_dev, 4, cudaMemcpyDeviceToHost, s));
         NDS_CUDA(cudaStreamSynchronize(s));
-        d2h += (int64_t)hk.size() + (int64_t)hv.size() * 4;
-        for (int64_t i = 0; i < nb; ++i)
+        d2h += (int64_t)hk.size() + (int64_t)hv.size() * 4 + 4;
+        if (build.n_exact >= 0) hcount = (int)build.n_exact;
+        if (hcount > nb) hcount = (int)nb;
+        build.n_exact = hcount;
+        for (int64_t i = 0; i < hcount; ++i)
           if ((hv[i >> 5] >> (i & 31)) & 1u)
             rf.keys.insert(is32 ? (int64_t) reinterpret_cast<int32_t*>(hk.data())[i] : reinterpret_cast<int64_t*>(hk.data())[i]);
       }
@@ -834,7 +927,11 @@ struct Exec {
     out.n_max = n;
     out.n_dev = ng;
     RowCount nout{ng, n};
-    for (int k = 0; k < nkeys; ++k) out.cols.push_back(eval_to_column(jkeys.a[k].at("expr"), jkeys.a[k].str("name"), in, rep, nout));
+    {
+      std::vector<std::pair<std::string, const Json*>> kx;
+      for (int k = 0; k < nkeys; ++k) kx.emplace_back(jkeys.a[k].str("name"), &jkeys.a[k].at("expr"));
+      for (Column& c : eval_columns(kx, in, rep, nout)) out.cols.push_back(c);
+    }
     for (int a = 0; a < naggs; ++a) {
       Column c;
       c.name = jaggs.a[a].str("name");
@@ -851,45 +948,49 @@ struct Exec {
   Batch sort(const Json& node, std::vector<RuntimeFilter>& filters) {
     Batch in = exec(node.at("child"), filters);
     const int64_t limit = node.int_or("limit", -1);
-    int64_t n = count(in);
     size_t st = begin_stat("sort");
+    // compile the keys first: the string keys' maximum lengths are measured on the device with the row count still
+    // there, so that count and lengths come back in ONE synchronisation
+    Blob bb;
+    std::vector<SortKey> keys;
+    int B = 0;
+    for (const Json& k : node.at("keys").a) {
+      std::vector<Instr> code;
+      LType t = compile(k.at("expr"), in, bb, code);
+      SortKey sk;
+      sk.prog = bb.add_prog(code, t);
+      sk.kind = t.kind == LType::STR ? 2 : (t.kind == LType::F64 ? 1 : 0);
+      sk.desc = k.bool_or("desc", false) ? 1 : 0;
+      sk.nulls_first = k.bool_or("nulls_first", !sk.desc) ? 1 : 0;   // Spark default null ordering
+      sk.width = 8;
+      sk.offset = 0;
+      keys.push_back(sk);
+    }
+    bool any_str = false;
+    for (const SortKey& sk : keys) any_str |= sk.kind == 2;
+    if (any_str && in.rc().host > 0) {
+      Blob::Dev dev0 = bb.upload(ar, s);
+      int* dmax = ar.zeros<int>((int64_t)keys.size());
+      for (size_t k = 0; k < keys.size(); ++k)
+        if (keys[k].kind == 2) { launch_str_maxlen(dev0.host_progs[keys[k].prog], dev0.ctx, in.rc(), dmax + k, s); ++launches; }
+      std::vector<int> hmax(keys.size());
+      int hcount = 0;
+      NDS_CUDA(cudaMemcpyAsync(hmax.data(), dmax, keys.size() * 4, cudaMemcpyDeviceToHost, s));
+      if (in.n_dev && in.n_exact < 0) NDS_CUDA(cudaMemcpyAsync(&hcount, in.n_dev, 4, cudaMemcpyDeviceToHost, s));
+      NDS_CUDA(cudaStreamSynchronize(s));
+      d2h += (int64_t)keys.size() * 4 + 4;
+      if (in.n_dev && in.n_exact < 0) in.n_exact = std::min<int64_t>(hcount, in.n_max);
+      for (size_t k = 0; k < keys.size(); ++k)
+        if (keys[k].kind == 2) keys[k].width = hmax[k];
+    }
+    int64_t n = count(in);
     Batch out;
     const int64_t m = (limit >= 0 && limit < n) ? limit : n;
     out.n_max = m;
     out.n_exact = m;
     uint32_t* rows = ar.alloc_n<uint32_t>(std::max<int64_t>(m, 1));
     if (n > 0) {
-      Blob bb;
-      std::vector<SortKey> keys;
-      int B = 0;
       RowCount rc{nullptr, n};
-      for (const Json& k : node.at("keys").a) {
-        std::vector<Instr> code;
-        LType t = compile(k.at("expr"), in, bb, code);
-        SortKey sk;
-        sk.prog = bb.add_prog(code, t);
-        sk.kind = t.kind == LType::STR ? 2 : (t.kind == LType::F64 ? 1 : 0);
-        sk.desc = k.bool_or("desc", false) ? 1 : 0;
-        sk.nulls_first = k.bool_or("nulls_first", !sk.desc) ? 1 : 0;   // Spark default null ordering
-        sk.width = 8;
-        sk.offset = 0;
-        keys.push_back(sk);
-      }
-      // string keys: padded to the longest value present (one small reduction + sync per string key)
-      bool any_str = false;
-      for (const SortKey& sk : keys) any_str |= sk.kind == 2;
-      if (any_str) {
-        Blob::Dev dev0 = bb.upload(ar, s);
-        int* dmax = ar.zeros<int>((int64_t)keys.size());
-        for (size_t k = 0; k < keys.size(); ++k)
-          if (keys[k].kind == 2) { launch_str_maxlen(dev0.host_progs[keys[k].prog], dev0.ctx, rc, dmax + k, s); ++launches; }
-        std::vector<int> hmax(keys.size());
-        NDS_CUDA(cudaMemcpyAsync(hmax.data(), dmax, keys.size() * 4, cudaMemcpyDeviceToHost, s));
-        NDS_CUDA(cudaStreamSynchronize(s));
-        d2h += (int64_t)keys.size() * 4;
-        for (size_t k = 0; k < keys.size(); ++k)
-          if (keys[k].kind == 2) keys[k].width = hmax[k];
-      }
       for (SortKey& sk : keys) { sk.offset = B; B += 1 + sk.width; }
       Blob::Dev dev = bb.upload(ar, s, keys.data(), (int64_t)keys.size() * sizeof(SortKey));
       uint8_t* keybuf = (uint8_t*)ar.alloc(n * B);
@@ -924,13 +1025,15 @@ struct Exec {
       }
     }
     RowCount rm{nullptr, m};
-    for (size_t c = 0; c < in.cols.size(); ++c) {
-      Json ce;
-      ce.kind = Json::Obj;
-      Json cn; cn.kind = Json::Str; cn.s = in.cols[c].name;
-      ce.o.emplace_back("col", cn);
-      if (m > 0) out.cols.push_back(eval_to_column(ce, in.cols[c].name, in, rows, rm));
-      else { Column e0 = in.cols[c]; e0.rowmap = nullptr; e0.valid = nullptr; e0.data = ar.alloc(16); out.cols.push_back(e0); }
+    if (m > 0) {
+      std::vector<Json> ces;
+      ces.reserve(in.cols.size());
+      for (size_t c = 0; c < in.cols.size(); ++c) ces.push_back(col_expr(in.cols[c].name));
+      std::vector<std::pair<std::string, const Json*>> ex;
+      for (size_t c = 0; c < in.cols.size(); ++c) ex.emplace_back(in.cols[c].name, &ces[c]);
+      out.cols = eval_columns(ex, in, rows, rm);
+    } else {
+      for (size_t c = 0; c < in.cols.size(); ++c) { Column e0 = in.cols[c]; e0.rowmap = nullptr; e0.valid = nullptr; e0.data = ar.alloc(16); out.cols.push_back(e0); }
     }
     end_stat(st, 0, n);
     return out;
@@ -999,16 +1102,18 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
     std::vector<RuntimeFilter> none;
     Batch res = ex.exec(root, none);
     int64_t n = ex.count(res);
-    // flatten every result column
-    std::vector<Column> flat;
+    // flatten every result column that still goes through a row map (one launch for all of them)
+    std::vector<Column> flat = res.cols;
     RowCount rn{nullptr, n};
-    for (size_t c = 0; c < res.cols.size(); ++c) {
-      if (!res.cols[c].rowmap || n == 0) { flat.push_back(res.cols[c]); continue; }
-      Json ce;
-      ce.kind = Json::Obj;
-      Json cn; cn.kind = Json::Str; cn.s = res.cols[c].name;
-      ce.o.emplace_back("col", cn);
-      flat.push_back(ex.eval_to_column(ce, res.cols[c].name, res, nullptr, rn));
+    if (n > 0) {
+      std::vector<Json> ces;
+      std::vector<size_t> which;
+      for (size_t c = 0; c < res.cols.size(); ++c)
+        if (res.cols[c].rowmap) { which.push_back(c); ces.push_back(Exec::col_expr(res.cols[c].name)); }
+      std::vector<std::pair<std::string, const Json*>> exs;
+      for (size_t k = 0; k < which.size(); ++k) exs.emplace_back(res.cols[which[k]].name, &ces[k]);
+      std::vector<Column> fc = ex.eval_columns(exs, res, nullptr, rn);
+      for (size_t k = 0; k < which.size(); ++k) flat[which[k]] = fc[k];
     }
     ex.check_err();
     // ---- device -> host, as Arrow C data
@@ -1019,6 +1124,8 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
     apv->array_store.resize(nc);
     apv->child_bufptrs.resize(nc);
     sp->strings.reserve(2 * nc + 2);
+    // pass 1: schema entries, and every column's validity + values on their way to the host (no sync in between)
+    std::vector<uint8_t*> hvalid_v(nc, nullptr), hdata_v(nc, nullptr);
     for (size_t c = 0; c < nc; ++c) {
       const Column& col = flat[c];
       const DType dt = col.lt.dtype();
@@ -1041,21 +1148,28 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
       cs.flags = 2;  // nullable
       cs.release = release_schema_child;
       sp->schema_children.push_back(&cs);
-
       const int64_t vbytes = ((n + 31) / 32) * 4;
-      uint8_t* hvalid = nullptr;
-      int64_t null_count = 0;
       if (col.valid && n > 0) {
-        hvalid = (uint8_t*)malloc(vbytes + 8);
-        apv->bufs.push_back(hvalid);
-        NDS_CUDA(cudaMemcpyAsync(hvalid, col.valid, vbytes, cudaMemcpyDeviceToHost, stream_));
+        hvalid_v[c] = (uint8_t*)malloc(vbytes + 8);
+        apv->bufs.push_back(hvalid_v[c]);
+        NDS_CUDA(cudaMemcpyAsync(hvalid_v[c], col.valid, vbytes, cudaMemcpyDeviceToHost, stream_));
         ex.d2h += vbytes;
       }
       const int w = dt == DT_I32 ? 4 : 8;
-      uint8_t* hdata = (uint8_t*)malloc(std::max<int64_t>(n * w, 8));
-      apv->bufs.push_back(hdata);
-      if (n > 0) { NDS_CUDA(cudaMemcpyAsync(hdata, col.data, n * w, cudaMemcpyDeviceToHost, stream_)); ex.d2h += n * w; }
-      NDS_CUDA(cudaStreamSynchronize(stream_));
+      hdata_v[c] = (uint8_t*)malloc(std::max<int64_t>(n * w, 8));
+      apv->bufs.push_back(hdata_v[c]);
+      if (n > 0) { NDS_CUDA(cudaMemcpyAsync(hdata_v[c], col.data, n * w, cudaMemcpyDeviceToHost, stream_)); ex.d2h += n * w; }
+    }
+    NDS_CUDA(cudaStreamSynchronize(stream_));
+    // pass 2: Arrow buffers; string characters are gathered on the device for all string columns, one more sync
+    struct PendingStr { size_t c; uint8_t* chars; uint8_t* dchars; int64_t bytes; };
+    std::vector<PendingStr> pending;
+    for (size_t c = 0; c < nc; ++c) {
+      const Column& col = flat[c];
+      const DType dt = col.lt.dtype();
+      uint8_t* hvalid = hvalid_v[c];
+      uint8_t* hdata = hdata_v[c];
+      int64_t null_count = 0;
       if (hvalid) {
         // clear padding bits, count nulls
         int64_t valid_cnt = 0;
@@ -1099,8 +1213,8 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
           launch_copy_str_bytes(reinterpret_cast<const StrView*>(col.data), col.strbase, doffs, n, dchars, stream_);
           ++ex.launches;
           NDS_CUDA(cudaMemcpyAsync(chars, dchars, offs64[n], cudaMemcpyDeviceToHost, stream_));
-          NDS_CUDA(cudaStreamSynchronize(stream_));
           ex.d2h += offs64[n];
+          pending.push_back(PendingStr{c, chars, dchars, offs64[n]});
         }
         bp = {hvalid, offs, chars};
       } else {
@@ -1110,6 +1224,7 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
       ca.buffers = bp.data();
       apv->array_children.push_back(&ca);
     }
+    if (!pending.empty()) NDS_CUDA(cudaStreamSynchronize(stream_));
     memset(out_schema, 0, sizeof *out_schema);
     out_schema->format = "+s";
     out_schema->name = "";
@@ -1182,6 +1297,12 @@ Engine::Engine(const Json& cfg) {
   NDS_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
   uint64_t thr = UINT64_MAX;
   NDS_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+  slab_cap_ = cfg.int_or("slab_mb", 512) << 20;
+  if (slab_cap_ > 0 && cudaMalloc(reinterpret_cast<void**>(&slab_), (size_t)slab_cap_) != cudaSuccess) {
+    cudaGetLastError();
+    slab_ = nullptr;
+    slab_cap_ = 0;
+  }
   pin_cap_ = 8 << 20;
   if (cudaHostAlloc(reinterpret_cast<void**>(&pin_), (size_t)pin_cap_, cudaHostAllocDefault) != cudaSuccess) {
     cudaGetLastError();
@@ -1197,6 +1318,7 @@ Engine::~Engine() {
   for (auto& n : names) drop_table(n);
   if (stream_) cudaStreamDestroy(stream_);
   if (pin_) cudaFreeHost(pin_);
+  if (slab_) cudaFree(slab_);
 }
 
 }  // namespace nds

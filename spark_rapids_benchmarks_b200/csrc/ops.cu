@@ -101,6 +101,43 @@ void launch_project(Prog p, OpCtx c, RowCount n, const uint32_t* rows, void* out
   NDS_CUDA(cudaGetLastError());
 }
 
+// Several expressions in one launch (sort output, group keys, final result columns): every thread evaluates all of
+// them for its row; one launch instead of one per column.
+__global__ void __launch_bounds__(kThreads)
+project_multi_kernel(const ProjSpec* __restrict__ specs, int nspecs, OpCtx c, const int* n_dev, int64_t n_host,
+                     const uint32_t* __restrict__ rows, int* err) {
+  const int64_t n = row_count(n_dev, n_host);
+  const int64_t nround = (n + 31) & ~int64_t(31);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nround; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = (i < n && rows) ? (int64_t)rows[i] : i;
+    for (int sidx = 0; sidx < nspecs; ++sidx) {
+      const ProjSpec sp = specs[sidx];
+      Val v;
+      v.ok = false; v.v = 0; v.len = 0;
+      if (i < n) v = eval_program(sp.prog.code, sp.prog.n, c.cols, c.lit, r);
+      uint32_t m = __ballot_sync(0xFFFFFFFFu, v.ok);
+      if (sp.valid && (threadIdx.x & 31) == 0) sp.valid[i >> 5] = m;
+      if (i < n) {
+        if (sp.dtype == DT_I32) reinterpret_cast<int32_t*>(sp.out)[i] = v.ok ? (int32_t)v.v : 0;
+        else if (sp.dtype == DT_STR) {
+          StrView sv = 0;
+          if (v.ok) {
+            int64_t off = (int64_t)((const uint8_t*)(uintptr_t)v.v - sp.strbase);
+            if (off < 0 || off > 0xFFFFFFFFll) { if (err) atomicExch(err, 11); off = 0; }
+            sv = ((uint64_t)v.len << 32) | (uint64_t)(uint32_t)off;
+          }
+          reinterpret_cast<StrView*>(sp.out)[i] = sv;
+        } else reinterpret_cast<int64_t*>(sp.out)[i] = v.ok ? v.v : 0;
+      }
+    }
+  }
+}
+void launch_project_multi(const ProjSpec* specs, int nspecs, OpCtx c, RowCount n, const uint32_t* rows, int* err, cudaStream_t s) {
+  if (nspecs <= 0) return;
+  project_multi_kernel<<<grid_for(n.host), kThreads, 0, s>>>(specs, nspecs, c, n.dev, n.host, rows, err);
+  NDS_CUDA(cudaGetLastError());
+}
+
 // ------------------------------------------------------------------ small utilities
 __global__ void compose_kernel(const uint32_t* __restrict__ inner, const uint32_t* __restrict__ idx, const int* n_dev,
                                int64_t n_host, uint32_t* __restrict__ out) {

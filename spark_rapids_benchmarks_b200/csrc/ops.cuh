@@ -56,6 +56,15 @@ void launch_fill_segments(const int64_t* d_seg_start, const int64_t* d_seg_val, 
 void launch_filter(Prog p, OpCtx c, RowCount n, uint32_t* out_sel, int* out_count, cudaStream_t s);
 void launch_project(Prog p, OpCtx c, RowCount n, const uint32_t* rows, void* out, uint32_t* out_valid, int out_dtype,
                     const uint8_t* str_out_base, int* err, cudaStream_t s);
+struct ProjSpec {        // one output column of a multi-column projection
+  Prog prog;
+  void* out;
+  uint32_t* valid;
+  const uint8_t* strbase;
+  int32_t dtype;
+  int32_t pad;
+};
+void launch_project_multi(const ProjSpec* specs, int nspecs, OpCtx c, RowCount n, const uint32_t* rows, int* err, cudaStream_t s);
 void launch_compose(const uint32_t* inner, const uint32_t* idx, RowCount n, uint32_t* out, cudaStream_t s);
 void launch_fill_i64(int64_t* p, int64_t v, int64_t n, cudaStream_t s);
 void launch_join_build(ColRef key, RowCount n, HashTable ht, int* flags, cudaStream_t s);
