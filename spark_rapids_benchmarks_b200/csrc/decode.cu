@@ -42,6 +42,7 @@ constexpr int kEntCap = 1024;            // header entries (position, first valu
 constexpr int kDefSeg = 2048;            // byte positions resolved per segment of the parallel header walk
 constexpr int kChunk = 32;               // bytes per chunk of the parallel header walk
 constexpr int kUnroll = 4;
+constexpr int kDictStage = 65536;        // dictionary bytes staged in (dynamic) shared memory; larger ones are gathered from L2
 constexpr int kEarlyCap = 80;            // runs the early index-header chase may record (32768 / 504 = 65 full runs)
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -55,6 +56,11 @@ __device__ __forceinline__ uint32_t lds32(uint32_t a) {
   uint32_t v;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
   return v;
+}
+__device__ __forceinline__ int64_t lds64(uint32_t a) {
+  long long v;
+  asm volatile("ld.shared.s64 %0, [%1];" : "=l"(v) : "r"(a));
+  return (int64_t)v;
 }
 // bw bits starting `bit` bits after the 4 B aligned shared address base (two aligned word loads + funnel shift)
 __device__ __forceinline__ uint32_t smem_bits(uint32_t base_al, uint32_t bit, uint32_t mask) {
@@ -239,48 +245,58 @@ __device__ __forceinline__ void mbar_wait(uint64_t* mbar, uint32_t parity) {
   }
 }
 
+// CTA-wide barrier over the first `nthr` threads (nthr multiple of 32); id 0 with nthr == blockDim is __syncthreads()
+__device__ __forceinline__ void bar_sync(int id, int nthr) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthr) : "memory"); }
+
 // ---- parallel resolution of a staged hybrid stream's run headers -------------------------------------------------
 // sd: shared-window address of stream byte 0, L bytes long. Starting at header position w->pos with w->k values
 // covered, resolves up to kDefSeg byte positions: appends (position, first value index) of the first header of every
 // entered kChunk-byte chunk to ent_pos/ent_k (at most kDefSeg/kChunk new entries) and advances *w.
-// Called by all threads of the CTA; s_hop is kDefSeg words of scratch.
+// Called by the first bar_n threads of the CTA (they synchronise on named barrier bar_id); s_hop is kDefSeg words of scratch.
 __device__ __forceinline__ void resolve_segment(uint32_t sd, uint32_t L, uint32_t bw, uint32_t limit, Walker* w, uint32_t* s_hop,
-                                                uint32_t* ent_pos, uint32_t* ent_k, int* n_ent, int tid) {
+                                                uint32_t* ent_pos, uint32_t* ent_k, int* n_ent, int tid, int bar_id, int bar_n,
+                                                long long* dbg = nullptr) {
   const uint32_t seg0 = w->pos, k0 = w->k;
   const uint32_t seg1 = min(seg0 + (uint32_t)kDefSeg, L);
   const uint32_t nchunks = (seg1 - seg0 + kChunk - 1) / kChunk;
   const uint32_t bytew = (bw + 7) >> 3;
-  __syncthreads();
-  // phase A: speculative parse of every byte position of my chunk, last to first (one shared load per position)
+  bar_sync(bar_id, bar_n);
+  // phase A: speculative parse of every byte position of my chunk, last to first. The chunk's bytes (+2 of look-ahead)
+  // are loaded up front so that the per-position chain is ALU + one hop-table load.
   if ((uint32_t)tid < nchunks) {
     const uint32_t cb = seg0 + tid * kChunk, ce = min(cb + (uint32_t)kChunk, seg1);
-    uint32_t b1 = ce < L ? lds8(sd + ce) : 0u, b2 = ce + 1 < L ? lds8(sd + ce + 1) : 0u;
-    for (uint32_t p = ce; p-- > cb;) {
-      const uint32_t b0 = lds8(sd + p);
-      uint32_t h = b0 & 0x7F, hl = 1;
-      if (b0 & 0x80) {
-        h |= (b1 & 0x7F) << 7;
-        hl = 2;
-        if (b1 & 0x80) {
-          h |= (b2 & 0x7F) << 14;
-          hl = 3;     // a run of one page never needs more than 3 varint bytes (<= 32768 values)
+    uint32_t by[kChunk + 2];
+#pragma unroll
+    for (int j = 0; j < kChunk + 2; ++j) by[j] = cb + j < L ? lds8(sd + cb + j) : 0u;
+#pragma unroll
+    for (int j = kChunk - 1; j >= 0; --j) {
+      const uint32_t p = cb + j;
+      if (p < ce) {
+        const uint32_t b0 = by[j], b1 = by[j + 1], b2 = by[j + 2];
+        uint32_t h = b0 & 0x7F, hl = 1;
+        if (b0 & 0x80) {
+          h |= (b1 & 0x7F) << 7;
+          hl = 2;
+          if (b1 & 0x80) {
+            h |= (b2 & 0x7F) << 14;
+            hl = 3;     // a run of one page never needs more than 3 varint bytes (<= 32768 values)
+          }
         }
+        uint32_t cnt = (h & 1) ? (h >> 1) * 8 : (h >> 1);
+        uint32_t nxt = p + hl + ((h & 1) ? (h >> 1) * bw : bytew);
+        if (nxt > L || nxt <= p) nxt = L;
+        if (nxt < ce) {
+          uint32_t f = s_hop[nxt - seg0];
+          cnt += f & 0xFFFFu;
+          nxt = f >> 16;
+        }
+        if (cnt > 0xFFFFu) cnt = 0xFFFFu;
+        s_hop[p - seg0] = (nxt << 16) | cnt;
       }
-      uint32_t cnt = (h & 1) ? (h >> 1) * 8 : (h >> 1);
-      uint32_t nxt = p + hl + ((h & 1) ? (h >> 1) * bw : bytew);
-      if (nxt > L || nxt <= p) nxt = L;
-      if (nxt < ce) {
-        uint32_t f = s_hop[nxt - seg0];
-        cnt += f & 0xFFFFu;
-        nxt = f >> 16;
-      }
-      if (cnt > 0xFFFFu) cnt = 0xFFFFu;
-      s_hop[p - seg0] = (nxt << 16) | cnt;
-      b2 = b1;
-      b1 = b0;
     }
   }
-  __syncthreads();
+  bar_sync(bar_id, bar_n);
+  if (dbg && tid == 0 && seg0 == 0) dbg[(int64_t)blockIdx.x * 8 + 6] = clock64();
   // phase B: hop from chunk to chunk, one shared-memory load per chunk
   if (tid == 0) {
     uint32_t p = seg0, k = k0;
@@ -296,15 +312,16 @@ __device__ __forceinline__ void resolve_segment(uint32_t sd, uint32_t L, uint32_
     *n_ent = ne;
     w->pos = p;
     w->k = k > limit ? limit : k;
+    if (dbg && seg0 == 0) dbg[(int64_t)blockIdx.x * 8 + 7] = clock64();
   }
-  __syncthreads();
+  bar_sync(bar_id, bar_n);
 }
 
 }  // namespace
 
 #define NDS_CKPT(j) do { if (dbg && threadIdx.x == 0) dbg[(int64_t)blockIdx.x * 8 + (j)] = clock64(); } while (0)
 
-__global__ void __launch_bounds__(kT, 4)
+__global__ void __launch_bounds__(kT, 2)
 decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __restrict__ err, long long* __restrict__ dbg) {
   __shared__ uint32_t s_valid[kWords];
   __shared__ uint32_t s_rank[kWords];
@@ -316,6 +333,8 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __rest
   __shared__ uint32_t s_hop[kDefSeg];                       // (exit position << 16) | values emitted
   __shared__ uint32_t s_long[64][2];                        // long RLE runs of 1s, filled cooperatively
   __shared__ __align__(8) uint64_t s_mbar;
+  __shared__ __align__(8) uint64_t s_mbar_dict;
+  extern __shared__ __align__(16) uint8_t s_dict[];         // kDictStage bytes: the page's dictionary
   __shared__ int s_nlong;
   __shared__ int s_nent;
   __shared__ int s_done;
@@ -342,12 +361,18 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __rest
   uint32_t nn = n;          // non-null count
   uint32_t mbar_phase = 0;
 
+  const uint32_t dict_bytes = is_dict ? t.dict_count * (uint32_t)t.width : 0u;
+  const bool dict_staged = is_dict && dict_bytes > 0 && dict_bytes <= (uint32_t)kDictStage;
   if (tid == 0) {
     s_early_n = -1;
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_mbar)));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_mbar_dict)));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
+  // the dictionary streams into shared memory while the def levels are resolved: the per-value gathers then hit
+  // shared memory instead of 32 different L2 sectors per warp
+  if (dict_staged && tid == 0) bulk_load_issue(s_dict, t.dict, (dict_bytes + 15u) & ~15u, &s_mbar_dict);
 
   // ---- 1. def-level bytes -> shared memory (async) ---------------------------------------------------------------
   uint32_t def_sd = 0;
@@ -368,32 +393,80 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __rest
     __syncwarp();
     if (lane == 0 && (w.pos >= VL || w.k >= n)) s_early_n = nr;     // finished: the runs cover every value
   }
-  for (uint32_t w = tid; w < nw; w += kT) s_valid[w] = 0;
+  // the chase warp stays out of the def-level phases (they synchronise on a named barrier of the other warps)
+  const bool chasing = is_dict && bw > 0 && bw <= 32;
+  const int defN = chasing ? kT - 32 : kT;            // threads taking part in the def-level phases
+  const int defBar = chasing ? 1 : 0;
+  const bool in_def = tid < defN;
+  if (in_def)
+    for (uint32_t w = tid; w < nw; w += defN) s_valid[w] = 0;
 
   if (has_def) {
     const uint32_t L = t.def_len;
     if (def_staged) {
-      mbar_wait(&s_mbar, mbar_phase);
-      mbar_phase ^= 1;
-      NDS_CKPT(1);
-      if (tid == 0) { s_walk.pos = 0; s_walk.k = 0; s_walk.end = L; }
-      __syncthreads();
-      // ---- 2. resolve the def-level run headers in parallel, segment by segment --------------------------------
-      for (;;) {
-        if (s_walk.pos >= L || s_walk.k >= n) break;
-        if (tid == 0) { s_nent = 0; s_nlong = 0; }
-        resolve_segment(def_sd, L, 1, n, &s_walk, s_hop, ent_pos, ent_k, &s_nent, tid);
-        // phase C: every entry expands the runs up to the next entry into the validity bitmap; long runs of
-        // valid rows (a column without NULLs is one run) are queued and filled by the whole CTA
-        const int ne = s_nent;
-        const uint32_t seg_end = s_walk.pos;
-        if (tid < ne) {
-          const uint32_t pe = tid + 1 < ne ? ent_pos[tid + 1] : seg_end;
-          uint32_t p = ent_pos[tid], k = ent_k[tid];
-          while (p < pe && k < n) {
-            uint32_t cnt, info;
-            const uint32_t len = parse_run_s(def_sd, p, L, 1, cnt, info);
-            const uint32_t k1 = min(k + cnt, n);
+      if (in_def) {
+        mbar_wait(&s_mbar, mbar_phase);
+        NDS_CKPT(1);
+        if (tid == 0) { s_walk.pos = 0; s_walk.k = 0; s_walk.end = L; }
+        bar_sync(defBar, defN);
+        // ---- 2. resolve the def-level run headers in parallel, segment by segment --------------------------------
+        for (;;) {
+          if (s_walk.pos >= L || s_walk.k >= n) break;
+          if (tid == 0) { s_nent = 0; s_nlong = 0; }
+          resolve_segment(def_sd, L, 1, n, &s_walk, s_hop, ent_pos, ent_k, &s_nent, tid, defBar, defN, dbg);
+          // phase C: the entered chunks list their runs (count, scan, write - the hop table is free again and holds
+          // the list), then every run is expanded into the bitmap by its own thread; long runs of valid rows (a
+          // column without NULLs is one run) go to the whole CTA.
+          const int ne = s_nent;
+          const uint32_t seg_end = s_walk.pos;
+          uint32_t my_runs = 0;
+          if (tid < ne) {
+            const uint32_t pe = tid + 1 < ne ? ent_pos[tid + 1] : seg_end;
+            uint32_t p = ent_pos[tid], k = ent_k[tid];
+            while (p < pe && k < n) {
+              uint32_t cnt, info;
+              p += parse_run_s(def_sd, p, L, 1, cnt, info);
+              k += cnt;
+              ++my_runs;
+            }
+          }
+          // exclusive scan of my_runs over the (<= kDefSeg / kChunk = 64) entry threads: warps 0 and 1
+          uint32_t run0 = 0;
+          if (tid < 64) {
+            uint32_t incl = my_runs;
+            for (int d = 1; d < 32; d <<= 1) {
+              uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+              if (lane >= d) incl += v;
+            }
+            if (lane == 31) s_warp_tot[warp] = incl;
+            run0 = incl - my_runs;
+          }
+          bar_sync(defBar, defN);
+          const uint32_t nruns = min(s_warp_tot[0] + s_warp_tot[1], (uint32_t)kDefSeg / 2);
+          if (tid < ne) {
+            if (warp == 1) run0 += s_warp_tot[0];
+            const uint32_t pe = tid + 1 < ne ? ent_pos[tid + 1] : seg_end;
+            uint32_t p = ent_pos[tid], k = ent_k[tid], r = run0;
+            while (p < pe && k < n) {
+              uint32_t cnt, info;
+              p += parse_run_s(def_sd, p, L, 1, cnt, info);
+              if (r < (uint32_t)kDefSeg / 2) {
+                s_hop[2 * r] = k;
+                s_hop[2 * r + 1] = (min(cnt, 0xFFFFu) << 16) | (info & 0xFFFFu);
+              } else {            // more runs than the list holds (degenerate zero-length runs): expand in place
+                const uint32_t k1 = min(k + cnt, n);
+                if (info & 1) copy_bits(s_valid, def_sd + (info >> 1), nullptr, k, k1);
+                else if (info >> 1) set_bits(s_valid, k, k1);
+              }
+              k += cnt;
+              ++r;
+            }
+          }
+          bar_sync(defBar, defN);
+          for (uint32_t r = tid; r < nruns; r += defN) {
+            const uint32_t k = s_hop[2 * r], ci = s_hop[2 * r + 1];
+            const uint32_t info = ci & 0xFFFFu;
+            const uint32_t k1 = min(k + (ci >> 16), n);
             if (info & 1) copy_bits(s_valid, def_sd + (info >> 1), nullptr, k, k1);
             else if (info >> 1) {
               if (k1 - k >= 256) {
@@ -402,22 +475,21 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __rest
                 else set_bits(s_valid, k, k1);
               } else set_bits(s_valid, k, k1);
             }
-            p += len;
-            k += cnt;
           }
-        }
-        __syncthreads();
-        const int nl = min(s_nlong, 64);
-        for (int j = 0; j < nl; ++j) {
-          const uint32_t b0 = s_long[j][0], b1 = s_long[j][1];
-          for (uint32_t w = (b0 >> 5) + tid; w <= ((b1 - 1) >> 5); w += kT) {
-            const uint32_t lo = max(b0, w << 5), hi = min(b1, (w + 1) << 5);
-            const uint32_t cntb = hi - lo;
-            atomicOr(&s_valid[w], (cntb == 32 ? 0xFFFFFFFFu : ((1u << cntb) - 1u)) << (lo & 31));
+          bar_sync(defBar, defN);
+          const int nl = min(s_nlong, 64);
+          for (int j = 0; j < nl; ++j) {
+            const uint32_t b0 = s_long[j][0], b1 = s_long[j][1];
+            for (uint32_t w = (b0 >> 5) + tid; w <= ((b1 - 1) >> 5); w += defN) {
+              const uint32_t lo = max(b0, w << 5), hi = min(b1, (w + 1) << 5);
+              const uint32_t cntb = hi - lo;
+              atomicOr(&s_valid[w], (cntb == 32 ? 0xFFFFFFFFu : ((1u << cntb) - 1u)) << (lo & 31));
+            }
           }
+          bar_sync(defBar, defN);
         }
-        __syncthreads();
       }
+      mbar_phase ^= 1;
     } else {
       // ---- oversized def stream: sequential walk straight from global memory ---------------------------------
       if (tid == 0) { s_walk.pos = 4; s_walk.end = 4 + L; s_walk.k = 0; s_done = 0; }
@@ -440,6 +512,7 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __rest
         if (s_done) break;
       }
     }
+    __syncthreads();          // the chase warp rejoins; s_valid is complete
     NDS_CKPT(2);
     // ---- 3. exclusive prefix of popcounts per word -> s_rank ----------------------------------------------
     {
@@ -576,6 +649,7 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __rest
   }
 
   // ---- 4c. RLE_DICTIONARY -------------------------------------------------------------------------------------------
+  if (dict_staged) mbar_wait(&s_mbar_dict, 0);       // the dictionary has landed in shared memory
   if (bw > 32) { if (tid == 0 && err) atomicExch(err, 5); return; }
   const uint32_t L = VL;
   uint32_t vsd = 0;                                     // shared-window address of the staged index stream
@@ -594,6 +668,7 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __rest
   if (tid == 0) { s_walk.pos = 0; s_walk.end = L; s_walk.k = 0; s_done = 0; }
   __syncthreads();
   const bool use_early = !v_staged && bw > 0 && s_early_n >= 0;
+  const uint32_t dict_s = smem_u32(s_dict);
   const uint32_t bwmask = bw >= 32 ? 0xFFFFFFFFu : ((1u << bw) - 1u);
   const uint32_t vsd_al = vsd & ~3u, vsd_mis = (vsd & 3u) * 8u;
   // contiguous block of 32-row tiles per warp, so that a warp's run cursor only moves forward
@@ -621,7 +696,7 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __rest
       } else if (v_staged) {
         // small stream (many short runs fit here): resolve every header in parallel, segment by segment
         while (s_walk.pos < L && s_walk.k < nn && s_nent + kDefSeg / kChunk <= kEntCap)
-          resolve_segment(vsd, L, bw, nn, &s_walk, s_hop, ent_pos, ent_k, &s_nent, tid);
+          resolve_segment(vsd, L, bw, nn, &s_walk, s_hop, ent_pos, ent_k, &s_nent, tid, 0, kT);
       } else {
         // large stream with more runs than the early chase could record: batches of kEntCap runs
         if (tid < 32) {
@@ -748,8 +823,9 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __rest
           if (stt[u] >= 2) {
             uint32_t ix = stt[u] == 3 ? (__funnelshift_r(word0[u], word1[u], sh[u]) & bwmask) : word0[u];
             if (ix >= t.dict_count) { if (err) atomicExch(err, 6); continue; }
-            vv[u] = t.width == 4 ? (int64_t)__ldg(reinterpret_cast<const int32_t*>(t.dict) + ix)
-                                 : __ldg(reinterpret_cast<const int64_t*>(t.dict) + ix);
+            if (dict_staged) vv[u] = t.width == 4 ? (int64_t)(int32_t)lds32(dict_s + ix * 4u) : lds64(dict_s + ix * 8u);
+            else vv[u] = t.width == 4 ? (int64_t)__ldg(reinterpret_cast<const int32_t*>(t.dict) + ix)
+                                      : __ldg(reinterpret_cast<const int64_t*>(t.dict) + ix);
           }
         }
 #pragma unroll
@@ -880,8 +956,9 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, int nslices, int* __rest
           v[u] = 0;
           if (st[u] == 2) {
             if (idx[u] >= t.dict_count) { if (err) atomicExch(err, 6); st[u] = 1; continue; }
-            v[u] = t.width == 4 ? (int64_t)__ldg(reinterpret_cast<const int32_t*>(t.dict) + idx[u])
-                                : __ldg(reinterpret_cast<const int64_t*>(t.dict) + idx[u]);
+            if (dict_staged) v[u] = t.width == 4 ? (int64_t)(int32_t)lds32(dict_s + idx[u] * 4u) : lds64(dict_s + idx[u] * 8u);
+            else v[u] = t.width == 4 ? (int64_t)__ldg(reinterpret_cast<const int32_t*>(t.dict) + idx[u])
+                                     : __ldg(reinterpret_cast<const int64_t*>(t.dict) + idx[u]);
           }
         }
   #pragma unroll
@@ -923,7 +1000,14 @@ int decode_slices(int npages) {
 void launch_decode_pages(const PageTask* d_tasks, int npages, int* d_err, cudaStream_t stream, long long* dbg) {
   if (npages <= 0) return;
   const int nslices = decode_slices(npages);
-  decode_pages_kernel<<<npages * nslices, kDecodeThreads, 0, stream>>>(d_tasks, nslices, d_err, dbg);
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  NDS_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    NDS_CUDA(cudaFuncSetAttribute(decode_pages_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kDictStage));
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
+  }
+  decode_pages_kernel<<<npages * nslices, kDecodeThreads, kDictStage, stream>>>(d_tasks, nslices, d_err, dbg);
   NDS_CUDA(cudaGetLastError());
 }
 

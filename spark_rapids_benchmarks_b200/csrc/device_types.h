@@ -11,7 +11,7 @@ enum DType : int { DT_I32 = 0, DT_I64 = 1, DT_F64 = 2, DT_STR = 3 };
 typedef uint64_t StrView;
 
 constexpr int kMaxPageValues = 32768;     // rows per data page the decode kernel accepts (writers default to 20000)
-constexpr int kDecodeThreads = 256;
+constexpr int kDecodeThreads = 512;
 constexpr int kRunCap = 512;              // run-table entries per batch (shared memory)
 constexpr int kPagePad = 16;              // readable slack after every staged page payload
 

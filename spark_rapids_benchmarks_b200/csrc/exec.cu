@@ -601,6 +601,7 @@ struct Exec {
         NDS_CUDA(cudaMemcpyAsync(h.data(), dbg, h.size() * 8, cudaMemcpyDeviceToHost, s));
         NDS_CUDA(cudaStreamSynchronize(s));
         double acc[6] = {0, 0, 0, 0, 0, 0};
+        double defA = 0, defB = 0, defC = 0;
         long long tmin = h[0], tmax = 0;
         for (int c = 0; c < nctas; ++c) {
           long long prev = h[c * 8];
@@ -610,10 +611,15 @@ struct Exec {
             if (v) { acc[j] += (double)(v - prev); prev = v; }
           }
           tmax = std::max(tmax, prev);
+          if (h[c * 8 + 6] && h[c * 8 + 7] && h[c * 8 + 1] && h[c * 8 + 2]) {
+            defA += (double)(h[c * 8 + 6] - h[c * 8 + 1]);
+            defB += (double)(h[c * 8 + 7] - h[c * 8 + 6]);
+            defC += (double)(h[c * 8 + 2] - h[c * 8 + 7]);
+          }
         }
-        char buf[256];
-        snprintf(buf, sizeof buf, "decode_phases(avg cycles/CTA over %d CTAs): stage=%.0f def=%.0f scan+valid=%.0f headers=%.0f rows=%.0f span=%lld",
-                 nctas, acc[1] / nctas, acc[2] / nctas, acc[3] / nctas, acc[4] / nctas, acc[5] / nctas, tmax - tmin);
+        char buf[320];
+        snprintf(buf, sizeof buf, "decode_phases(avg cycles/CTA over %d CTAs): stage=%.0f def=%.0f [A=%.0f B=%.0f C+=%.0f] scan+valid=%.0f headers=%.0f rows=%.0f",
+                 nctas, acc[1] / nctas, acc[2] / nctas, defA / nctas, defB / nctas, defC / nctas, acc[3] / nctas, acc[4] / nctas, acc[5] / nctas);
         size_t di = begin_stat(buf);
         end_stat(di, 0, 0);
       }
