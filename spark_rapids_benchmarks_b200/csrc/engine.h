@@ -167,6 +167,9 @@ class Engine {
   int64_t pin_cap_ = 0;
   uint8_t* slab_ = nullptr;     // device slab behind the per-query bump allocator
   int64_t slab_cap_ = 0;
+  std::vector<cudaEvent_t> event_pool_;
+  cudaEvent_t get_event();
+  void put_event(cudaEvent_t e);
 };
 
 void set_global_error(const std::string& s);

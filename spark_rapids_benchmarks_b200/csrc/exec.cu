@@ -194,13 +194,20 @@ struct Exec {
     }
   }
 
+  ~Exec() {     // a failed query still returns its timing events to the pool
+    for (OpStat& st : stats) {
+      if (st.e0) e.put_event(st.e0);
+      if (st.e1) e.put_event(st.e1);
+    }
+  }
+
   // ---------------------------------------------------------------- op timing
   size_t begin_stat(const std::string& op, bool always = false) {
     OpStat st;
     st.op = op;
     if (profile || always) {
-      NDS_CUDA(cudaEventCreate(&st.e0));
-      NDS_CUDA(cudaEventCreate(&st.e1));
+      st.e0 = e.get_event();
+      st.e1 = e.get_event();
       NDS_CUDA(cudaEventRecord(st.e0, s));
     }
     stats.push_back(st);
@@ -216,6 +223,9 @@ struct Exec {
     int h[4];
     NDS_CUDA(cudaMemcpyAsync(h, err, sizeof h, cudaMemcpyDeviceToHost, s));
     NDS_CUDA(cudaStreamSynchronize(s));
+    check_err_values(h);
+  }
+  void check_err_values(const int* h) {
     if (h[0]) fail("device kernel reported error code " + std::to_string(h[0]) +
                    " (3-6: malformed parquet page, 11: string projection outside its column buffer, 12: sort key overflow)");
     if (h[1] & 1) fail("hash join: duplicate keys on the build side (only unique build keys are supported)");
@@ -770,13 +780,24 @@ struct Exec {
   }
 
   // ---------------------------------------------------------------- join
-  Batch join(const Json& node, std::vector<RuntimeFilter>& filters) {
+  struct BuiltSide {
+    Batch build;
+    HashTable ht;
+    std::string pk, bk;
+  };
+
+  // Executes the build child of a join node, builds its hash table and, for a partition-pruning join, turns the build
+  // keys into a runtime filter for the scan below.
+  BuiltSide build_side(const Json& node, std::vector<RuntimeFilter>& down) {
     const std::string type = node.str_or("type", "inner");
     if (type != "inner") fail("plan: join type '" + type + "' is not supported yet");
+    BuiltSide bs;
     std::vector<RuntimeFilter> none;
-    Batch build = exec(node.at("build"), none);
-    const std::string& bk = node.str("build_key");
-    const std::string& pk = node.str("probe_key");
+    bs.build = exec(node.at("build"), none);
+    Batch& build = bs.build;
+    bs.bk = node.str("build_key");
+    bs.pk = node.str("probe_key");
+    const std::string& bk = bs.bk;
     int kb = build.find(bk);
     if (kb < 0) fail("plan: build key '" + bk + "' not found");
     if (!is_intlike(build.cols[kb].lt)) fail("plan: join keys must be integer columns");
@@ -784,7 +805,7 @@ struct Exec {
     const int64_t nb_bound = build.rc().host;
     const int64_t nb = nb_bound <= (int64_t(4) << 20) ? nb_bound : count(build);
     size_t stb = begin_stat("join_build");
-    HashTable ht;
+    HashTable& ht = bs.ht;
     uint32_t cap = next_pow2(2 * nb);
     ht.mask = cap - 1;
     ht.keys = ar.alloc_n<int64_t>(cap);
@@ -794,12 +815,11 @@ struct Exec {
     launches += 2;
     end_stat(stb, nb * 8 + (int64_t)cap * 12, nb);
     // dynamic partition pruning: ship the (small) build key set to the host and let the scan skip files
-    std::vector<RuntimeFilter> down = filters;
     if (node.bool_or("prune_partitions", false)) {
       Json kexpr = col_expr(bk);
       Column flat = eval_to_column(kexpr, bk, build, nullptr, build.rc());
       RuntimeFilter rf;
-      rf.column = pk;
+      rf.column = bs.pk;
       if (nb > 0) {
         // keys of the upper-bound row range and the exact count come back in one synchronisation
         const bool is32 = flat.lt.dtype() == DT_I32;
@@ -820,34 +840,120 @@ struct Exec {
       }
       down.push_back(std::move(rf));
     }
-    Batch probe = exec(node.at("probe"), down);
-    int kp = probe.find(pk);
-    if (kp < 0) fail("plan: probe key '" + pk + "' not found");
-    if (!is_intlike(probe.cols[kp].lt)) fail("plan: join keys must be integer columns");
-    size_t stp = begin_stat("join_probe");
-    RowCount np = probe.rc();
+    return bs;
+  }
+
+  // column names a plan subtree produces (static; used to decide whether a join chain can be fused)
+  static void plan_columns(const Json& node, std::set<std::string>& out) {
+    const std::string& op = node.str("op");
+    if (op == "scan") { for (const Json& c : node.at("columns").a) out.insert(c.s); }
+    else if (op == "filter" || op == "sort") plan_columns(node.at("child"), out);
+    else if (op == "join") { plan_columns(node.at("probe"), out); plan_columns(node.at("build"), out); }
+    else if (op == "project") { for (const Json& e : node.at("exprs").a) out.insert(e.str("name")); }
+    else if (op == "aggregate") {
+      for (const Json& k : node.at("keys").a) out.insert(k.str("name"));
+      for (const Json& a : node.at("aggs").a) out.insert(a.str("name"));
+    }
+  }
+
+  Batch join(const Json& node, std::vector<RuntimeFilter>& filters) {
+    // ---- a left-deep chain of inner joins whose probe keys all come from the innermost probe side is probed in ONE pass
+    std::vector<const Json*> chain;          // outermost first
+    const Json* cur = &node;
+    while (cur->str("op") == "join" && (int)chain.size() < kMaxChain) {
+      chain.push_back(cur);
+      cur = &cur->at("probe");
+    }
+    const Json& base_node = *cur;
+    bool fuse = chain.size() >= 2 && base_node.str("op") != "join";
+    if (fuse) {
+      std::set<std::string> base_cols;
+      plan_columns(base_node, base_cols);
+      for (const Json* j : chain)
+        if (!base_cols.count(j->str("probe_key")) || j->str_or("type", "inner") != "inner") fuse = false;
+    }
+    if (!fuse) {
+      std::vector<RuntimeFilter> down = filters;
+      BuiltSide bs = build_side(node, down);
+      Batch probe = exec(node.at("probe"), down);
+      int kp = probe.find(bs.pk);
+      if (kp < 0) fail("plan: probe key '" + bs.pk + "' not found");
+      if (!is_intlike(probe.cols[kp].lt)) fail("plan: join keys must be integer columns");
+      size_t stp = begin_stat("join_probe");
+      RowCount np = probe.rc();
+      uint32_t* out_p = ar.alloc_n<uint32_t>(np.host);
+      uint32_t* out_b = ar.alloc_n<uint32_t>(np.host);
+      int* cnt = ar.zeros<int>(1);
+      launch_join_probe(probe.cols[kp].ref(), np, bs.ht, out_p, out_b, cnt, s);
+      ++launches;
+      Batch out;
+      out.n_max = np.host;
+      out.n_dev = cnt;
+      RowCount nout{cnt, np.host};
+      MapCache mp, mb;
+      for (const Column& c : probe.cols) {
+        Column o = c;
+        o.rowmap = remap(c.rowmap, out_p, nout, mp);
+        out.cols.push_back(o);
+      }
+      for (const Column& c : bs.build.cols) {
+        if (out.find(c.name) >= 0) continue;
+        Column o = c;
+        o.rowmap = remap(c.rowmap, out_b, nout, mb);
+        out.cols.push_back(o);
+      }
+      end_stat(stp, np.host * (probe.cols[kp].lt.dtype() == DT_I32 ? 4 : 8), np.host);
+      return out;
+    }
+    // ---- fused: all build sides first (their partition filters reach the base scan), then one probe pass
+    std::vector<RuntimeFilter> down = filters;
+    std::vector<BuiltSide> sides;
+    sides.reserve(chain.size());
+    for (const Json* j : chain) sides.push_back(build_side(*j, down));
+    Batch base = exec(base_node, down);
+    size_t stp = begin_stat("join_probe_chain");
+    RowCount np = base.rc();
+    ProbeChain pc;
+    memset(&pc, 0, sizeof pc);
+    pc.n = (int32_t)chain.size();
+    int64_t key_bytes = 0;
+    // probe order: innermost join first (the planner put the most selective join there)
+    for (size_t q = 0; q < chain.size(); ++q) {
+      const BuiltSide& bs = sides[chain.size() - 1 - q];
+      int kp = base.find(bs.pk);
+      if (kp < 0) fail("plan: probe key '" + bs.pk + "' not found");
+      if (!is_intlike(base.cols[kp].lt)) fail("plan: join keys must be integer columns");
+      pc.key[q] = base.cols[kp].ref();
+      pc.ht[q] = bs.ht;
+      pc.out_build[q] = ar.alloc_n<uint32_t>(np.host);
+      key_bytes += np.host * (base.cols[kp].lt.dtype() == DT_I32 ? 4 : 8);
+    }
     uint32_t* out_p = ar.alloc_n<uint32_t>(np.host);
-    uint32_t* out_b = ar.alloc_n<uint32_t>(np.host);
     int* cnt = ar.zeros<int>(1);
-    launch_join_probe(probe.cols[kp].ref(), np, ht, out_p, out_b, cnt, s);
+    launch_join_probe_chain(pc, np, out_p, cnt, s);
     ++launches;
     Batch out;
     out.n_max = np.host;
     out.n_dev = cnt;
     RowCount nout{cnt, np.host};
-    MapCache mp, mb;
-    for (const Column& c : probe.cols) {
+    MapCache mp;
+    for (const Column& c : base.cols) {
       Column o = c;
       o.rowmap = remap(c.rowmap, out_p, nout, mp);
       out.cols.push_back(o);
     }
-    for (const Column& c : build.cols) {
-      if (out.find(c.name) >= 0) continue;
-      Column o = c;
-      o.rowmap = remap(c.rowmap, out_b, nout, mb);
-      out.cols.push_back(o);
+    // build-side columns in the order the unfused plan would produce them (innermost join first)
+    for (size_t q = 0; q < chain.size(); ++q) {
+      const BuiltSide& bs = sides[chain.size() - 1 - q];
+      MapCache mb;
+      for (const Column& c : bs.build.cols) {
+        if (out.find(c.name) >= 0) continue;
+        Column o = c;
+        o.rowmap = remap(c.rowmap, pc.out_build[q], nout, mb);
+        out.cols.push_back(o);
+      }
     }
-    end_stat(stp, np.host * (probe.cols[kp].lt.dtype() == DT_I32 ? 4 : 8), np.host);
+    end_stat(stp, key_bytes, np.host);
     return out;
   }
 
@@ -1098,9 +1204,7 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
   NDS_CUDA(cudaSetDevice(device));
   const Json* options = plan.find("options");
   const Json& root = plan.has("root") ? plan.at("root") : plan;
-  cudaEvent_t ev0, ev1;
-  NDS_CUDA(cudaEventCreate(&ev0));
-  NDS_CUDA(cudaEventCreate(&ev1));
+  cudaEvent_t ev0 = get_event(), ev1 = get_event();
   NDS_CUDA(cudaEventRecord(ev0, stream_));
   std::vector<OpStat> op_stats;
   {
@@ -1121,7 +1225,8 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
       std::vector<Column> fc = ex.eval_columns(exs, res, nullptr, rn);
       for (size_t k = 0; k < which.size(); ++k) flat[which[k]] = fc[k];
     }
-    ex.check_err();
+    int h_err[4] = {0, 0, 0, 0};
+    NDS_CUDA(cudaMemcpyAsync(h_err, ex.err, sizeof h_err, cudaMemcpyDeviceToHost, stream_));   // checked after the export sync
     // ---- device -> host, as Arrow C data
     ExportPriv* sp = new ExportPriv();
     ExportPriv* apv = new ExportPriv();
@@ -1167,6 +1272,14 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
       if (n > 0) { NDS_CUDA(cudaMemcpyAsync(hdata_v[c], col.data, n * w, cudaMemcpyDeviceToHost, stream_)); ex.d2h += n * w; }
     }
     NDS_CUDA(cudaStreamSynchronize(stream_));
+    try {
+      ex.check_err_values(h_err);
+    } catch (...) {
+      for (void* b : apv->bufs) free(b);
+      delete apv;
+      delete sp;
+      throw;
+    }
     // pass 2: Arrow buffers; string characters are gathered on the device for all string columns, one more sync
     struct PendingStr { size_t c; uint8_t* chars; uint8_t* dchars; int64_t bytes; };
     std::vector<PendingStr> pending;
@@ -1258,16 +1371,16 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
   float ms = 0;
   cudaEventElapsedTime(&ms, ev0, ev1);
   exec_ms_ = ms;
-  cudaEventDestroy(ev0);
-  cudaEventDestroy(ev1);
+  put_event(ev0);
+  put_event(ev1);
   for (OpStat& st : op_stats) {
     if (st.e0 && st.e1) {
       float t = 0;
       if (cudaEventElapsedTime(&t, st.e0, st.e1) == cudaSuccess) st.ms = t;
       else cudaGetLastError();
     }
-    if (st.e0) cudaEventDestroy(st.e0);
-    if (st.e1) cudaEventDestroy(st.e1);
+    if (st.e0) put_event(st.e0);
+    if (st.e1) put_event(st.e1);
     st.e0 = st.e1 = nullptr;
   }
   stats_ = std::move(op_stats);
@@ -1317,8 +1430,21 @@ Engine::Engine(const Json& cfg) {
   }
 }
 
+cudaEvent_t Engine::get_event() {
+  if (!event_pool_.empty()) {
+    cudaEvent_t e = event_pool_.back();
+    event_pool_.pop_back();
+    return e;
+  }
+  cudaEvent_t e;
+  NDS_CUDA(cudaEventCreate(&e));
+  return e;
+}
+void Engine::put_event(cudaEvent_t e) { event_pool_.push_back(e); }
+
 Engine::~Engine() {
   cudaSetDevice(device);
+  for (cudaEvent_t e : event_pool_) cudaEventDestroy(e);
   std::vector<std::string> names;
   for (auto& kv : tables_) names.push_back(kv.first);
   for (auto& n : names) drop_table(n);

@@ -205,6 +205,47 @@ join_probe_kernel(ColRef key, const int* n_dev, int64_t n_host, HashTable ht, ui
   }
 }
 
+// Fused star-join probe: every base row walks the chain of hash tables (most selective first) and leaves at its first
+// miss; survivors are appended once with the matched build row of every join. One kernel instead of one probe plus
+// the row-map compositions per join, and no intermediate selection vectors.
+__global__ void __launch_bounds__(kThreads)
+join_probe_chain_kernel(const ProbeChain c, const int* n_dev, int64_t n_host, uint32_t* __restrict__ out_probe, int* out_count) {
+  const int64_t n = row_count(n_dev, n_host);
+  const int64_t nround = (n + 31) & ~int64_t(31);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nround; i += (int64_t)gridDim.x * blockDim.x) {
+    bool hit = i < n;
+    uint32_t b[kMaxChain];
+#pragma unroll
+    for (int j = 0; j < kMaxChain; ++j) {
+      b[j] = 0;
+      if (j < c.n && hit) {
+        Val k = load_col(c.key[j], i);
+        hit = false;
+        if (k.ok && k.v != kEmptyKey) {
+          uint32_t s = (uint32_t)mix64((uint64_t)k.v) & c.ht[j].mask;
+          for (;;) {
+            int64_t cur = c.ht[j].keys[s];
+            if (cur == k.v) { hit = true; b[j] = c.ht[j].vals[s]; break; }
+            if (cur == kEmptyKey) break;
+            s = (s + 1) & c.ht[j].mask;
+          }
+        }
+      }
+    }
+    int pos = warp_append(hit, out_count);
+    if (hit) {
+      out_probe[pos] = (uint32_t)i;
+#pragma unroll
+      for (int j = 0; j < kMaxChain; ++j)
+        if (j < c.n) c.out_build[j][pos] = b[j];
+    }
+  }
+}
+void launch_join_probe_chain(const ProbeChain& chain, RowCount n, uint32_t* out_probe, int* out_count, cudaStream_t s) {
+  join_probe_chain_kernel<<<grid_for(n.host), kThreads, 0, s>>>(chain, n.dev, n.host, out_probe, out_count);
+  NDS_CUDA(cudaGetLastError());
+}
+
 void launch_join_build(ColRef key, RowCount n, HashTable ht, int* flags, cudaStream_t s) {
   join_build_kernel<<<grid_for(n.host), kThreads, 0, s>>>(key, n.dev, n.host, ht, flags);
   NDS_CUDA(cudaGetLastError());

@@ -70,6 +70,15 @@ void launch_fill_i64(int64_t* p, int64_t v, int64_t n, cudaStream_t s);
 void launch_join_build(ColRef key, RowCount n, HashTable ht, int* flags, cudaStream_t s);
 void launch_join_probe(ColRef key, RowCount n, HashTable ht, uint32_t* out_probe, uint32_t* out_build, int* out_count,
                        cudaStream_t s);
+constexpr int kMaxChain = 8;
+struct ProbeChain {            // a left-deep chain of inner hash joins probed in one pass over the base rows
+  ColRef key[kMaxChain];
+  HashTable ht[kMaxChain];
+  uint32_t* out_build[kMaxChain];
+  int32_t n;
+  int32_t pad;
+};
+void launch_join_probe_chain(const ProbeChain& chain, RowCount n, uint32_t* out_probe, int* out_count, cudaStream_t s);
 void launch_agg_insert(const Prog* progs, int nkeys, const AggSpec* aggs, int naggs, OpCtx c, RowCount n, uint32_t* slots,
                        uint32_t mask, int64_t* acc, int64_t* cnt, cudaStream_t s);
 void launch_agg_finalize(const AggSpec* aggs, int naggs, const uint32_t* slots, uint32_t cap, const int64_t* acc,

@@ -130,14 +130,17 @@ class Engine:
         self._check(self._lib.nds_engine_table_info(self._h, name.encode(), buf, len(buf)))
         return json.loads(buf.value.decode())
 
-    def execute(self, plan, source=None, profile=False, decode_timing=False):
-        """Run a plan (dict or JSON string) and return a pyarrow.RecordBatch."""
+    def encode_plan(self, plan, source=None, profile=False, decode_timing=False):
+        """Plan dict -> the JSON bytes nds_engine_execute takes (cache these when a plan is run repeatedly)."""
+        if isinstance(plan, (bytes, bytearray)):
+            return bytes(plan)
         if isinstance(plan, str):
             plan = json.loads(plan)
         if 'root' not in plan:
             plan = {'root': plan}
+        else:
+            plan = {'root': plan['root'], **({'options': plan['options']} if 'options' in plan else {})}
         if source or profile or decode_timing:
-            plan = dict(plan)
             opts = dict(plan.get('options', {}))
             if source:
                 opts['source'] = source
@@ -146,10 +149,14 @@ class Engine:
             if decode_timing:
                 opts['decode_timing'] = True
             plan['options'] = opts
+        return json.dumps(plan, separators=(',', ':')).encode()
+
+    def execute(self, plan, source=None, profile=False, decode_timing=False):
+        """Run a plan (dict, JSON string, or bytes from encode_plan) and return a pyarrow.RecordBatch."""
+        payload = self.encode_plan(plan, source, profile, decode_timing)
         cs = ctypes.create_string_buffer(_SCHEMA_BYTES)
         ca = ctypes.create_string_buffer(_ARRAY_BYTES)
-        self._check(self._lib.nds_engine_execute(self._h, json.dumps(plan).encode(), ctypes.addressof(cs),
-                                                 ctypes.addressof(ca)))
+        self._check(self._lib.nds_engine_execute(self._h, payload, ctypes.addressof(cs), ctypes.addressof(ca)))
         return pa.RecordBatch._import_from_c(ctypes.addressof(ca), ctypes.addressof(cs))
 
     def last_stats(self):

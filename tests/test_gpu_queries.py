@@ -26,7 +26,7 @@ class _Sess(Session):
 
     def __init__(self, eng, source='hbm'):
         self.conf, self.app_name, self.version, self.application_id = {}, 't', 'test', 'b200-test'
-        self.rank, self.world, self.comm, self.source, self.engine, self.last_stats = 0, 1, None, source, eng, None
+        self.rank, self.world, self.comm, self.source, self.engine, self._stats = 0, 1, None, source, eng, None
 
     def stop(self):
         pass
