@@ -31,6 +31,7 @@ struct PageTask {
   uint8_t width;         // 4 or 8 bytes per output value
   uint8_t phys;          // 0 fixed-width, 1 BYTE_ARRAY
   uint8_t bw;            // dictionary index bit width (enc == 1)
+  uint32_t* vr;          // split decode only: page-local scratch [nw validity words][nw + 1 rank words] (nw = ceil(n/32))
 };
 
 // Column reference as kernels see it.

@@ -55,6 +55,7 @@ struct PageInfo {
   int64_t row_in_file;
   uint8_t enc;                 // 0 PLAIN, 1 dictionary
   uint8_t bw = 0;              // dictionary index bit width (first byte of the values section)
+  uint8_t fast = 0;            // 1: eligible for the split def/rows kernels (PLAIN fixed width, or few long index runs)
 };
 struct DictInfo {
   int64_t off;                 // fixed width: values; BYTE_ARRAY: StrView table (chars follow)

@@ -178,6 +178,7 @@ struct Exec {
   bool source_host = false;
   bool profile = false;
   bool decode_timing = false;
+  bool split_decode = true;      // options.split_decode=false forces every page through the general kernel
   std::vector<OpStat> stats;
   int64_t launches = 0;
   int64_t h2d = 0, d2h = 0;
@@ -191,6 +192,7 @@ struct Exec {
       source_host = options->str_or("source", "hbm") == "host";
       profile = options->bool_or("profile", false);
       decode_timing = options->bool_or("decode_timing", false);
+      split_decode = options->bool_or("split_decode", true);
     }
   }
 
@@ -484,6 +486,9 @@ struct Exec {
     out.n_max = N;
     size_t st = begin_stat("decode:" + tname, true);
     std::vector<PageTask> tasks;
+    std::vector<int> def_idx, rows_idx, gen_idx;     // routes: split def/rows kernels vs the general kernel
+    std::vector<int64_t> vr_off;                      // per task: offset of its validity/rank scratch (words) or -1
+    int64_t vr_words = 0;
     int64_t bytes_in = 0, bytes_out = 0;
     for (const Json& c : jc.a) {
       const std::string& cname = c.s;
@@ -582,6 +587,17 @@ struct Exec {
           task.src_off = (uint32_t)pi.off;
           task.enc = pi.enc;
           task.bw = pi.bw;
+          if (pi.fast && split_decode) {
+            rows_idx.push_back((int)tasks.size());
+            if (d_valid) {
+              def_idx.push_back((int)tasks.size());
+              vr_off.push_back(vr_words);
+              vr_words += 2 * (((int64_t)pi.num_values + 31) / 32) + 1;
+            } else vr_off.push_back(-1);
+          } else {
+            gen_idx.push_back((int)tasks.size());
+            vr_off.push_back(-1);
+          }
           task.width = (uint8_t)width;
           task.phys = tc.phys == pq::BYTE_ARRAY ? 1 : 0;
           if (pi.dict >= 0) {
@@ -596,15 +612,31 @@ struct Exec {
       out.cols.push_back(col);
     }
     if (!tasks.empty()) {
+      // scratch of the split route: per nullable page its validity words and their rank prefix
+      uint32_t* d_vr = vr_words ? ar.alloc_n<uint32_t>(vr_words) : nullptr;
+      for (size_t k = 0; k < tasks.size(); ++k) tasks[k].vr = vr_off[k] >= 0 ? d_vr + vr_off[k] : nullptr;
       PageTask* d_tasks = ar.alloc_n<PageTask>((int64_t)tasks.size());
       ar.upload(d_tasks, tasks.data(), (int64_t)(tasks.size() * sizeof(PageTask)));
-      // a dedicated pair of events brackets only the decode launch (roofline.achieved in bench.py)
+      std::vector<int> idx_all;
+      idx_all.reserve(def_idx.size() + rows_idx.size() + gen_idx.size());
+      idx_all.insert(idx_all.end(), def_idx.begin(), def_idx.end());
+      idx_all.insert(idx_all.end(), rows_idx.begin(), rows_idx.end());
+      idx_all.insert(idx_all.end(), gen_idx.begin(), gen_idx.end());
+      int* d_idx = ar.alloc_n<int>((int64_t)idx_all.size());
+      ar.upload(d_idx, idx_all.data(), (int64_t)(idx_all.size() * sizeof(int)));
+      // a dedicated pair of events brackets only the decode launches (roofline.achieved in bench.py)
       size_t ks = begin_stat("decode_kernel", true);
+      int l = 0;
+      launch_decode_split(d_tasks, d_idx, (int)def_idx.size(), d_idx + def_idx.size(), (int)rows_idx.size(), err, s, &l);
+      launches += l;
       long long* dbg = nullptr;
-      const int nctas = (int)tasks.size() * decode_slices((int)tasks.size());
-      if (decode_timing) dbg = ar.zeros<long long>((int64_t)nctas * 8);
-      launch_decode_pages(d_tasks, (int)tasks.size(), err, s, dbg);
-      ++launches;
+      const int ngen = (int)gen_idx.size();
+      const int nctas = ngen * decode_slices(ngen);
+      if (decode_timing && ngen) dbg = ar.zeros<long long>((int64_t)nctas * 8);
+      if (ngen) {
+        launch_decode_pages(d_tasks, d_idx + def_idx.size() + rows_idx.size(), ngen, err, s, dbg);
+        ++launches;
+      }
       end_stat(ks, bytes_in + bytes_out, N);
       if (dbg) {
         std::vector<long long> h((size_t)nctas * 8);
@@ -612,15 +644,12 @@ struct Exec {
         NDS_CUDA(cudaStreamSynchronize(s));
         double acc[6] = {0, 0, 0, 0, 0, 0};
         double defA = 0, defB = 0, defC = 0;
-        long long tmin = h[0], tmax = 0;
         for (int c = 0; c < nctas; ++c) {
           long long prev = h[c * 8];
-          tmin = std::min(tmin, prev);
           for (int j = 1; j < 6; ++j) {
             long long v = h[c * 8 + j];
             if (v) { acc[j] += (double)(v - prev); prev = v; }
           }
-          tmax = std::max(tmax, prev);
           if (h[c * 8 + 6] && h[c * 8 + 7] && h[c * 8 + 1] && h[c * 8 + 2]) {
             defA += (double)(h[c * 8 + 6] - h[c * 8 + 1]);
             defB += (double)(h[c * 8 + 7] - h[c * 8 + 6]);
@@ -628,8 +657,14 @@ struct Exec {
           }
         }
         char buf[320];
-        snprintf(buf, sizeof buf, "decode_phases(avg cycles/CTA over %d CTAs): stage=%.0f def=%.0f [A=%.0f B=%.0f C+=%.0f] scan+valid=%.0f headers=%.0f rows=%.0f",
+        snprintf(buf, sizeof buf, "decode_phases(general kernel, avg cycles/CTA over %d CTAs): stage=%.0f def=%.0f [A=%.0f B=%.0f C+=%.0f] scan+valid=%.0f headers=%.0f rows=%.0f",
                  nctas, acc[1] / nctas, acc[2] / nctas, defA / nctas, defB / nctas, defC / nctas, acc[3] / nctas, acc[4] / nctas, acc[5] / nctas);
+        size_t di = begin_stat(buf);
+        end_stat(di, 0, 0);
+      }
+      {
+        char buf[160];
+        snprintf(buf, sizeof buf, "decode_routes: def=%zu rows=%zu general=%zu pages", def_idx.size(), rows_idx.size(), gen_idx.size());
         size_t di = begin_stat(buf);
         end_stat(di, 0, 0);
       }

@@ -260,6 +260,26 @@ void Engine::register_table(const std::string& name, const std::string& path, co
               if (pi.bw > 32) fail("dictionary index bit width " + std::to_string(pi.bw) + " in '" + fi.path + "'");
               if (cur_dict < 0) fail("dictionary-encoded page without dictionary in '" + fi.path + "'");
             } else fail("unsupported data page encoding " + std::to_string(ph.encoding) + " in '" + fi.path + "'");
+            // route: the split def/rows kernels take PLAIN fixed-width pages and dictionary pages whose index stream
+            // is a few long runs (counted here, up to 64); everything else goes to the general kernel
+            pi.fast = 0;
+            if (pi.def_len <= 8192 && ph.num_values > 0) {
+              if (pi.enc == 0) pi.fast = tc.phys != pq::BYTE_ARRAY;
+              else if (pi.bw == 0) pi.fast = 1;
+              else {
+                int64_t p = values_off + 1, runs = 0;
+                const uint32_t bytew = (pi.bw + 7) / 8;
+                while (p < psize && runs <= 64) {
+                  uint64_t h = 0;
+                  int sft = 0;
+                  uint8_t c;
+                  do { c = payload[p++]; h |= (uint64_t)(c & 0x7F) << sft; sft += 7; } while ((c & 0x80) && p < psize && sft < 35);
+                  p += (h & 1) ? (int64_t)(h >> 1) * pi.bw : bytew;
+                  ++runs;
+                }
+                pi.fast = runs <= 64;
+              }
+            }
             // place the payload so that its values section is 16 B aligned
             int64_t cur = (int64_t)tc.stage.size();
             int64_t off = align_up(cur + values_off, 16) - values_off;

@@ -130,7 +130,7 @@ class Engine:
         self._check(self._lib.nds_engine_table_info(self._h, name.encode(), buf, len(buf)))
         return json.loads(buf.value.decode())
 
-    def encode_plan(self, plan, source=None, profile=False, decode_timing=False):
+    def encode_plan(self, plan, source=None, profile=False, decode_timing=False, options=None):
         """Plan dict -> the JSON bytes nds_engine_execute takes (cache these when a plan is run repeatedly)."""
         if isinstance(plan, (bytes, bytearray)):
             return bytes(plan)
@@ -140,8 +140,10 @@ class Engine:
             plan = {'root': plan}
         else:
             plan = {'root': plan['root'], **({'options': plan['options']} if 'options' in plan else {})}
-        if source or profile or decode_timing:
+        if source or profile or decode_timing or options:
             opts = dict(plan.get('options', {}))
+            if options:
+                opts.update(options)
             if source:
                 opts['source'] = source
             if profile:
@@ -151,9 +153,9 @@ class Engine:
             plan['options'] = opts
         return json.dumps(plan, separators=(',', ':')).encode()
 
-    def execute(self, plan, source=None, profile=False, decode_timing=False):
+    def execute(self, plan, source=None, profile=False, decode_timing=False, options=None):
         """Run a plan (dict, JSON string, or bytes from encode_plan) and return a pyarrow.RecordBatch."""
-        payload = self.encode_plan(plan, source, profile, decode_timing)
+        payload = self.encode_plan(plan, source, profile, decode_timing, options)
         cs = ctypes.create_string_buffer(_SCHEMA_BYTES)
         ca = ctypes.create_string_buffer(_ARRAY_BYTES)
         self._check(self._lib.nds_engine_execute(self._h, payload, ctypes.addressof(cs), ctypes.addressof(ca)))

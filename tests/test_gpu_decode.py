@@ -33,6 +33,18 @@ def test_decode_matches_pyarrow(gpu_engine, warehouse, table, source):
     assert st['launches'] >= 1
 
 
+@pytest.mark.parametrize('table', ['store_sales', 'item', 'date_dim', 'customer_demographics', 'customer'])
+def test_general_kernel_alone_matches_pyarrow(gpu_engine, warehouse, table):
+    """split_decode=false sends every page through decode_pages_kernel (the route RLE-heavy pages always take)."""
+    expected = read_table_like_engine(warehouse, table)
+    cols = expected.schema.names
+    got = gpu_engine.execute(scan_plan(table, cols), options={'split_decode': False})
+    for name in cols:
+        assert got.column(got.schema.get_field_index(name)).equals(_normalize(expected.column(name))), name
+    routes = [o['op'] for o in gpu_engine.last_stats()['ops'] if o['op'].startswith('decode_routes')]
+    assert routes and all('def=0 rows=0' in r for r in routes)
+
+
 def test_decode_column_subset_and_order(gpu_engine, warehouse):
     cols = ['ss_ext_sales_price', 'ss_sold_date_sk', 'ss_item_sk']
     expected = read_table_like_engine(warehouse, 'store_sales', cols)

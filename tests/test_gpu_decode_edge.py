@@ -25,6 +25,8 @@ def _roundtrip(eng, tmp_path, name, table, files=1, **kw):
         pq.write_table(part, d / ('part-%05d.parquet' % f), **args)
     eng.register_table(name, str(d))
     got = eng.execute({'op': 'scan', 'table': name, 'columns': table.schema.names})
+    got_general = eng.execute({'op': 'scan', 'table': name, 'columns': table.schema.names}, options={'split_decode': False})
+    assert got_general.equals(got), name + ': the general kernel and the split def/rows kernels disagree'
     exp = pa.concat_tables([pq.ParquetFile(str(d / ('part-%05d.parquet' % f))).read() for f in range(files)]).combine_chunks()
     got_t = pa.Table.from_batches([got])
     assert got_t.num_rows == exp.num_rows
