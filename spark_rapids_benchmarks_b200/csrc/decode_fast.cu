@@ -88,51 +88,43 @@ def_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ tas
     if (s_walk.pos >= L || s_walk.k >= n) break;
     if (tid == 0) { s_nent = 0; s_nlong = 0; }
     resolve_segment(def_sd, L, 1, n, &s_walk, s_hop, ent_pos, ent_k, &s_nent, tid, 0, kTD);
-    // the entered chunks list their runs (count, scan, write into the now free hop table), then one thread per run
+    // the entered chunks list the runs that start in them into their own 16 slots of the (now free) hop table -
+    // a 32-byte chunk holds at most 16 runs of 2+ bytes - then the listed runs are expanded one thread per run
     const int ne = s_nent;
     const uint32_t seg_end = s_walk.pos;
-    uint32_t my_runs = 0;
     if (tid < ne) {
       const uint32_t pe = tid + 1 < ne ? ent_pos[tid + 1] : seg_end;
-      uint32_t p = ent_pos[tid], k = ent_k[tid];
+      uint32_t p = ent_pos[tid], k = ent_k[tid], r = 0;
       while (p < pe && k < n) {
-        uint32_t cnt, info;
-        p += parse_run_s(def_sd, p, L, 1, cnt, info);
-        k += cnt;
-        ++my_runs;
-      }
-    }
-    uint32_t incl = my_runs;
-    for (int d = 1; d < 32; d <<= 1) {
-      uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-      if (lane >= d) incl += v;
-    }
-    if (lane == 31) s_warp_tot[warp] = incl;
-    uint32_t run0 = incl - my_runs;
-    __syncthreads();
-    const uint32_t nruns = min(s_warp_tot[0] + s_warp_tot[1], (uint32_t)kDefSeg / 2);
-    if (tid < ne) {
-      if (warp == 1) run0 += s_warp_tot[0];
-      const uint32_t pe = tid + 1 < ne ? ent_pos[tid + 1] : seg_end;
-      uint32_t p = ent_pos[tid], k = ent_k[tid], r = run0;
-      while (p < pe && k < n) {
-        uint32_t cnt, info;
-        p += parse_run_s(def_sd, p, L, 1, cnt, info);
-        if (r < (uint32_t)kDefSeg / 2) {
-          s_hop[2 * r] = k;
-          s_hop[2 * r + 1] = (min(cnt, 0xFFFFu) << 16) | (info & 0xFFFFu);
-        } else {
+        // def-level header: one varint byte unless the run is longer than 63 values / groups
+        uint32_t b0 = lds8(def_sd + p), h = b0 & 0x7F, hl = 1;
+        if (b0 & 0x80) {
+          const uint32_t b1 = lds8(def_sd + p + 1);
+          h |= (b1 & 0x7F) << 7;
+          hl = 2;
+          if (b1 & 0x80) { h |= (lds8(def_sd + p + 2) & 0x7F) << 14; hl = 3; }
+        }
+        const bool packed = h & 1;
+        const uint32_t cnt = packed ? (h >> 1) * 8 : (h >> 1);
+        const uint32_t info = packed ? (((p + hl) << 1) | 1u) : ((lds8(def_sd + p + hl) & 1u) << 1);
+        if (r < 16) {
+          s_hop[(tid * 16 + r) * 2] = k;
+          s_hop[(tid * 16 + r) * 2 + 1] = (min(cnt, 0xFFFFu) << 16) | (info & 0xFFFFu);
+        } else {              // degenerate zero-length runs overflowed the chunk's slots: expand in place
           const uint32_t k1 = min(k + cnt, n);
           if (info & 1) copy_bits(s_valid, def_sd + (info >> 1), nullptr, k, k1);
           else if (info >> 1) set_bits(s_valid, k, k1);
         }
+        p += hl + (packed ? (h >> 1) : 1u);
         k += cnt;
         ++r;
       }
+      ent_k[tid] = min(r, 16u);       // ent_k is free after phase B: number of listed runs of this entry
     }
     __syncthreads();
-    for (uint32_t r = tid; r < nruns; r += kTD) {
-      const uint32_t k = s_hop[2 * r], ci = s_hop[2 * r + 1];
+    for (uint32_t idx = tid; idx < (uint32_t)ne * 16; idx += kTD) {
+      if ((idx & 15) >= ent_k[idx >> 4]) continue;
+      const uint32_t k = s_hop[idx * 2], ci = s_hop[idx * 2 + 1];
       const uint32_t info = ci & 0xFFFFu;
       const uint32_t k1 = min(k + (ci >> 16), n);
       if (info & 1) copy_bits(s_valid, def_sd + (info >> 1), nullptr, k, k1);
@@ -233,6 +225,39 @@ __device__ __forceinline__ void expand_dict(const RowsCtx& c, uint32_t tile0, ui
     }
     uint32_t w0[8], w1[8], shv[8];
     int stt[8];          // 0 skip, 1 zero, 2 index in w0, 3 bit-packed words in w0/w1
+    const uint32_t kB = DEF ? c.s_r[be] : min(be * 32, c.n);
+    const bool two_packed = c.bw && c.ne && (info1 & 1) && (next1 == 0xFFFFFFFFu || (info2 & 1)) && kB <= next2;
+    if (two_packed) {
+      // every value of the block sits in one of two bit-packed runs: bit position = base(run) + k * bw
+      const uint32_t base1 = (info1 >> 1) * 8u + c.vs_mis - rk1 * c.bw;
+      const uint32_t base2 = (info2 >> 1) * 8u + c.vs_mis - next1 * c.bw;
+      const bool full = be == bb + 8 && be * 32 <= c.n;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const uint32_t tcur = bb + u;
+        stt[u] = 0;
+        w0[u] = 0;
+        w1[u] = 0;
+        shv[u] = 0;
+        if (full || (tcur < be && tcur * 32 + lane < c.n)) {
+          uint32_t k = tcur * 32 + lane;
+          bool ok = true;
+          if (DEF) {
+            const uint32_t wv = c.s_v[tcur];
+            k = c.s_r[tcur] + __popc(wv & lt_mask);
+            ok = (wv >> lane) & 1u;
+          }
+          stt[u] = 1;
+          if (ok) {
+            const uint32_t bit = (k >= next1 ? base2 : base1) + k * c.bw;
+            w0[u] = __ldg(c.vwords + (bit >> 5));
+            w1[u] = __ldg(c.vwords + (bit >> 5) + 1);
+            shv[u] = bit & 31;
+            stt[u] = 3;
+          }
+        }
+      }
+    } else {
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
       const uint32_t tcur = bb + u;
@@ -273,6 +298,7 @@ __device__ __forceinline__ void expand_dict(const RowsCtx& c, uint32_t tile0, ui
         }
       }
     }
+    }
     int64_t vv[8];
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
@@ -284,9 +310,10 @@ __device__ __forceinline__ void expand_dict(const RowsCtx& c, uint32_t tile0, ui
         else vv[u] = W == 4 ? (int64_t)__ldg(reinterpret_cast<const int32_t*>(c.dict) + ix) : __ldg(reinterpret_cast<const int64_t*>(c.dict) + ix);
       }
     }
+    const int64_t row_base = c.orow + (int64_t)bb * 32 + lane;
 #pragma unroll
     for (int u = 0; u < 8; ++u)
-      if (stt[u]) store_out<W>(c.out, c.orow + (bb + u) * 32 + lane, vv[u]);
+      if (stt[u]) store_out<W>(c.out, row_base + u * 32, vv[u]);
   }
 }
 
