@@ -217,6 +217,14 @@ __device__ __forceinline__ void expand_dict(const RowsCtx& c, uint32_t tile0, ui
     uint32_t rk1 = 0, info1 = 0, next1 = 0xFFFFFFFFu, info2 = 0, next2 = 0xFFFFFFFFu;
     if (c.bw && c.ne) {
       const uint32_t kA = DEF ? c.s_r[bb] : bb * 32;
+      if (bb == tile0) {                 // first block of this warp: binary search, afterwards the cursor creeps forward
+        int lo = 0, hi = c.ne - 1;
+        while (lo < hi) {
+          const int mid = (lo + hi + 1) >> 1;
+          if (c.ek[mid] <= kA) lo = mid; else hi = mid - 1;
+        }
+        ce = lo;
+      }
       while (ce + 1 < c.ne && c.ek[ce + 1] <= kA) ++ce;
       rk1 = c.ek[ce];
       info1 = c.ep[ce];

@@ -134,6 +134,8 @@ struct OpStat {
   double ms = 0;
   int64_t bytes = 0;            // algorithmic bytes
   int64_t rows = 0;
+  double host_ms = 0;           // wall-clock time the host spent inside this operator (launch + bookkeeping)
+  double t0 = 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
 };
 
@@ -164,6 +166,7 @@ class Engine {
   int64_t launches_ = 0;
   int64_t h2d_bytes_ = 0, d2h_bytes_ = 0;
   double exec_ms_ = 0;
+  double host_ms_ = 0;
   uint8_t* pin_ = nullptr;      // pinned host ring for small host->device uploads (plan blobs, page tasks)
   int64_t pin_cap_ = 0;
   uint8_t* slab_ = nullptr;     // device slab behind the per-query bump allocator

@@ -3,6 +3,7 @@
 // `spark_session.sql(query)` + `collect()` / `write...save()` hand-off
 // (/root/reference/nds/nds_power.py:125-135).  An unknown node or expression raises; there is no CPU path.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <unordered_set>
 #include "engine.h"
@@ -204,9 +205,13 @@ struct Exec {
   }
 
   // ---------------------------------------------------------------- op timing
+  static double now_ms() {
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+  }
   size_t begin_stat(const std::string& op, bool always = false) {
     OpStat st;
     st.op = op;
+    st.t0 = now_ms();
     if (profile || always) {
       st.e0 = e.get_event();
       st.e1 = e.get_event();
@@ -218,6 +223,7 @@ struct Exec {
   void end_stat(size_t i, int64_t bytes, int64_t rows) {
     stats[i].bytes = bytes;
     stats[i].rows = rows;
+    stats[i].host_ms = now_ms() - stats[i].t0;
     if (stats[i].e1) NDS_CUDA(cudaEventRecord(stats[i].e1, s));
   }
 
@@ -1236,6 +1242,7 @@ void release_array_child(ArrowArray* a) { if (a) a->release = nullptr; }
 }  // namespace
 
 void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_array) {
+  const double t_exec0 = Exec::now_ms();
   NDS_CUDA(cudaSetDevice(device));
   const Json* options = plan.find("options");
   const Json& root = plan.has("root") ? plan.at("root") : plan;
@@ -1419,15 +1426,17 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
     st.e0 = st.e1 = nullptr;
   }
   stats_ = std::move(op_stats);
+  host_ms_ = Exec::now_ms() - t_exec0;
 }
 
 std::string Engine::stats_json() const {
-  std::string s = "{\"launches\":" + std::to_string(launches_) + ",\"device_ms\":" + std::to_string(exec_ms_) +
+  std::string s = "{\"launches\":" + std::to_string(launches_) + ",\"device_ms\":" + std::to_string(exec_ms_) + ",\"host_ms\":" + std::to_string(host_ms_) +
                   ",\"h2d_bytes\":" + std::to_string(h2d_bytes_) + ",\"d2h_bytes\":" + std::to_string(d2h_bytes_) + ",\"ops\":[";
   for (size_t i = 0; i < stats_.size(); ++i) {
     if (i) s += ",";
     s += "{\"op\":\"" + json_escape(stats_[i].op) + "\",\"ms\":" + std::to_string(stats_[i].ms) + ",\"bytes\":" +
-         std::to_string(stats_[i].bytes) + ",\"rows\":" + std::to_string(stats_[i].rows) + "}";
+         std::to_string(stats_[i].bytes) + ",\"rows\":" + std::to_string(stats_[i].rows) + ",\"host_ms\":" +
+         std::to_string(stats_[i].host_ms) + "}";
   }
   s += "]}";
   return s;

@@ -44,10 +44,10 @@ def main():
             sess.engine.execute({'root': plan['root']}, source=None if a.source == 'hbm' else a.source, profile=not a.no_profile, decode_timing=a.decode_timing)
             wall = (time.perf_counter() - t0) * 1e3
             st = sess.engine.last_stats()
-        print('== %s: wall %.3f ms, device %.3f ms, launches %d, h2d %d' % (name, wall, st['device_ms'], st['launches'], st['h2d_bytes']))
+        print('== %s: wall %.3f ms, device %.3f ms, host(execute) %.3f ms, launches %d, h2d %d' % (name, wall, st['device_ms'], st.get('host_ms', 0), st['launches'], st['h2d_bytes']))
         for o in st['ops']:
             gbs = (o['bytes'] / (o['ms'] * 1e-3) / 1e9) if o['ms'] > 0 and o['bytes'] else 0
-            print('   %-28s %9.3f ms  %12d B  %10d rows  %8.1f GB/s' % (o['op'], o['ms'], o['bytes'], o['rows'], gbs))
+            print('   %-28s %9.3f ms (host %6.3f)  %12d B  %10d rows  %8.1f GB/s' % (o['op'][:28], o['ms'], o.get('host_ms', 0), o['bytes'], o['rows'], gbs))
 
 
 if __name__ == '__main__':
