@@ -124,6 +124,15 @@ def make_stream(args):
     return nds_power.gen_sql_from_stream(path)
 
 
+def use_all_host_threads():
+    """torchrun exports OMP_NUM_THREADS=1, which pyarrow takes as its pool size: undo that for the CPU arm."""
+    import pyarrow as pa
+    n = os.cpu_count() or 1
+    pa.set_cpu_count(n)
+    pa.set_io_thread_count(max(n, 8))
+    return n
+
+
 def cpu_power_run(query_dict, wh):
     from oracle import nds_queries as oq
     t0 = time.perf_counter()
@@ -135,6 +144,7 @@ def cpu_power_run(query_dict, wh):
 
 def measure_cpu(query_dict, wh, warmup, steps):
     import pyarrow as pa
+    use_all_host_threads()
     for _ in range(warmup):
         cpu_power_run(query_dict, wh)
     times = [cpu_power_run(query_dict, wh)[0] for _ in range(steps)]
@@ -149,6 +159,7 @@ def run_reference(args, rank, world):
     ensure_data(args, log)
     qd = make_stream(args)
     import pyarrow as pa
+    use_all_host_threads()
     wh = data_dir(args)
     for _ in range(args.warmup):
         cpu_power_run(qd, wh)

@@ -25,27 +25,47 @@ def deserialize_table(buf):
     return pa.ipc.open_stream(pa.BufferReader(buf)).read_all()
 
 
+INLINE_BYTES = 512 << 10     # payloads up to this size travel with the length in ONE collective
+
+
 def all_gather_bytes(payload, group=None):
-    """Variable-length all-gather of one bytes object per rank over torch.distributed
-    (one collective for the lengths, one for the padded payloads)."""
+    """Variable-length all-gather of one bytes object per rank over torch.distributed.
+
+    One collective in the common case: every rank sends an 8-byte length followed by the first
+    INLINE_BYTES of its payload; only if some payload is longer does a second collective carry the
+    remainders (padded to the longest)."""
+    import numpy as np
     import torch
     import torch.distributed as dist
     world = dist.get_world_size(group)
     backend = dist.get_backend(group)
     dev = torch.device('cuda', torch.cuda.current_device()) if backend == 'nccl' else torch.device('cpu')
-    n = torch.tensor([len(payload)], dtype=torch.int64, device=dev)
-    sizes_t = torch.empty(world, dtype=torch.int64, device=dev)
-    dist.all_gather_into_tensor(sizes_t, n, group=group)
-    sizes = sizes_t.tolist()
-    m = max(max(sizes), 1)
-    send = torch.zeros(m, dtype=torch.uint8)
-    if payload:
-        send[:len(payload)] = torch.frombuffer(bytearray(payload), dtype=torch.uint8)
-    send = send.to(dev)
-    recv = torch.empty(world * m, dtype=torch.uint8, device=dev)
+    n = len(payload)
+    head = np.zeros(8 + INLINE_BYTES, dtype=np.uint8)
+    head[:8] = np.frombuffer(np.int64(n).tobytes(), dtype=np.uint8)
+    k = min(n, INLINE_BYTES)
+    if k:
+        head[8:8 + k] = np.frombuffer(payload, dtype=np.uint8, count=k)
+    send = torch.from_numpy(head).to(dev)
+    recv = torch.empty(world * head.size, dtype=torch.uint8, device=dev)
     dist.all_gather_into_tensor(recv, send, group=group)
-    host = recv.cpu().numpy()
-    return [host[r * m:r * m + sizes[r]].tobytes() for r in range(world)]
+    host = recv.cpu().numpy().reshape(world, head.size)
+    sizes = [int(np.frombuffer(host[r, :8].tobytes(), dtype=np.int64)[0]) for r in range(world)]
+    parts = [host[r, 8:8 + min(sizes[r], INLINE_BYTES)].tobytes() for r in range(world)]
+    longest = max(sizes)
+    if longest > INLINE_BYTES:
+        m = longest - INLINE_BYTES
+        rest = np.zeros(m, dtype=np.uint8)
+        if n > INLINE_BYTES:
+            rest[:n - INLINE_BYTES] = np.frombuffer(payload, dtype=np.uint8, count=n - INLINE_BYTES, offset=INLINE_BYTES)
+        send2 = torch.from_numpy(rest).to(dev)
+        recv2 = torch.empty(world * m, dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(recv2, send2, group=group)
+        host2 = recv2.cpu().numpy().reshape(world, m)
+        for r in range(world):
+            if sizes[r] > INLINE_BYTES:
+                parts[r] += host2[r, :sizes[r] - INLINE_BYTES].tobytes()
+    return parts
 
 
 def all_gather_batches(batch, group=None):

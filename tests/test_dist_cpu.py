@@ -24,6 +24,11 @@ def _worker(rank, world, port, out_dir):
     b2 = pa.record_batch({'x': pa.array(list(range(rank * 1000, rank * 1000 + 500 * (rank + 1))), type=pa.int64())})
     t2 = ndist.all_gather_batches(b2)
     assert t2['x'].to_pylist() == list(range(0, 500)) + list(range(1000, 2000))
+    # payloads beyond the inline size take the second collective (only rank 1 is long here)
+    big = bytes(range(256)) * (3 * ndist.INLINE_BYTES // 256) if rank == 1 else b'short-%d' % rank
+    parts = ndist.all_gather_bytes(big)
+    assert parts[0] == b'short-0' and len(parts[1]) == 3 * ndist.INLINE_BYTES and parts[1][:256] == bytes(range(256))
+    assert parts[1][-1] == 255
     open(os.path.join(out_dir, 'ok%d' % rank), 'w').close()
     dist.destroy_process_group()
 

@@ -124,3 +124,42 @@ def test_two_rank_emulation_on_one_gpu(warehouse, query):
     assert rows_equal(got.to_pylist(), exp.to_pylist())
     for e in engines:
         e.close()
+
+
+def test_power_and_validate_cli_as_subprocesses(warehouse, tmp_path):
+    """The drop-in surface itself: `nds_power.py <input_prefix> <stream> <time_log> ...` and
+    `nds_validate.py <input1> <input2> <stream> ...` run as scripts, like the reference's spark-submit templates do."""
+    import json
+    import subprocess
+    import sys
+    import pyarrow.parquet as pq
+    from spark_rapids_benchmarks_b200.session import DataFrame
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    stream = str(tmp_path / 'query_0.sql')
+    streams.generate_stream(stream, overrides=PARAMS[0])
+    props = tmp_path / 'b200.properties'
+    props.write_text('b200.source=host\nspark.sql.adaptive.enabled=true\n')
+    out_gpu, out_cpu, js, log = str(tmp_path / 'gpu'), str(tmp_path / 'cpu'), str(tmp_path / 'json'), str(tmp_path / 'time.csv')
+    r = subprocess.run([sys.executable, os.path.join(root, 'spark_rapids_benchmarks_b200', 'nds_power.py'), warehouse, stream, log,
+                        '--output_prefix', out_gpu, '--json_summary_folder', js, '--property_file', str(props),
+                        '--sub_queries', 'query3,query7,query19'], capture_output=True, text=True, cwd=str(tmp_path))
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    lines = open(log).read().strip().split('\n')
+    assert lines[0] == 'application_id,query,time/milliseconds'
+    assert [l.split(',')[1] for l in lines[-7:]] == ['query3', 'query7', 'query19', 'Power Start Time', 'Power End Time',
+                                                    'Power Test Time', 'Total Time']
+    summaries = sorted(os.listdir(js))
+    assert len(summaries) == 3 and all(s.startswith('b200-query') for s in summaries)     # '<property file stem>-<query>-<start>.json'
+    summ = json.load(open(os.path.join(js, summaries[0])))
+    assert summ['queryStatus'] == ['Completed'] and summ['env']['sparkConf']['b200.source'] == 'host'
+    qd = nds_power.gen_sql_from_stream(stream)
+    for q in ('query3', 'query7', 'query19'):
+        t = oq.run_query(q, qd[q], warehouse)
+        os.makedirs(os.path.join(out_cpu, q))
+        pq.write_table(nds_power.ensure_valid_column_names(DataFrame(t)).toArrow(), os.path.join(out_cpu, q, 'part-0.parquet'))
+    v = subprocess.run([sys.executable, os.path.join(root, 'spark_rapids_benchmarks_b200', 'nds_validate.py'), out_gpu, out_cpu, stream,
+                        '--sub_queries', 'query3,query7,query19', '--json_summary_folder', js], capture_output=True, text=True,
+                       cwd=str(tmp_path))
+    assert v.returncode == 0, v.stdout[-2000:] + v.stderr[-2000:]
+    assert 'Unmatch Queries' not in v.stdout and v.stdout.count('Results match') == 3
+    assert json.load(open(os.path.join(js, summaries[0])))['queryValidationStatus'] == ['Pass']
