@@ -74,7 +74,8 @@ struct TableColumn {
   bool nullable = false;
   bool supported = true;
   std::string why_unsupported;
-  std::vector<uint8_t> stage;          // host copy of the encoded pages (kept when keep_host)
+  std::vector<uint8_t> stage;          // host copy of the encoded pages while registering
+  uint8_t* h_enc = nullptr;            // pinned (cudaHostAlloc) host copy kept when keep_host: source of source=host scans
   bool pinned = false;
   uint8_t* d_enc = nullptr;            // resident copy in HBM
   int64_t enc_bytes = 0;

@@ -552,7 +552,7 @@ struct Exec {
       const uint8_t* src_base = nullptr;   // address of staged byte 0
       if (!sel.empty()) {
         if (source_host) {
-          if (tc.stage.empty()) fail("engine was created without keep_host; source=host is unavailable");
+          if (!tc.h_enc) fail("engine was created without keep_host; source=host is unavailable");
           int64_t span_b = tc.file_byte_begin[sel.front()], span_e = tc.file_byte_begin[sel.back() + 1];
           uint8_t* tr = (uint8_t*)ar.alloc(span_e - span_b + 256);
           // copy only the selected files' byte ranges, adjacent ranges coalesced
@@ -561,7 +561,7 @@ struct Exec {
             size_t k2 = k;
             while (k2 + 1 < sel.size() && sel[k2 + 1] == sel[k2] + 1) ++k2;
             int64_t b0 = tc.file_byte_begin[sel[k]], b1 = tc.file_byte_begin[sel[k2] + 1];
-            NDS_CUDA(cudaMemcpyAsync(tr + (b0 - span_b), tc.stage.data() + b0, b1 - b0, cudaMemcpyHostToDevice, s));
+            NDS_CUDA(cudaMemcpyAsync(tr + (b0 - span_b), tc.h_enc + b0, b1 - b0, cudaMemcpyHostToDevice, s));
             h2d += b1 - b0;
             k = k2 + 1;
           }
@@ -618,6 +618,15 @@ struct Exec {
       out.cols.push_back(col);
     }
     if (!tasks.empty()) {
+      // a scan of a few pages is latency-bound: one general launch beats a def + rows (+ general) sequence
+      if (rows_idx.size() < 64) {
+        gen_idx.clear();
+        for (size_t k = 0; k < tasks.size(); ++k) gen_idx.push_back((int)k);
+        def_idx.clear();
+        rows_idx.clear();
+        vr_words = 0;
+        std::fill(vr_off.begin(), vr_off.end(), (int64_t)-1);
+      }
       // scratch of the split route: per nullable page its validity words and their rank prefix
       uint32_t* d_vr = vr_words ? ar.alloc_n<uint32_t>(vr_words) : nullptr;
       for (size_t k = 0; k < tasks.size(); ++k) tasks[k].vr = vr_off[k] >= 0 ? d_vr + vr_off[k] : nullptr;

@@ -323,12 +323,14 @@ void Engine::register_table(const std::string& name, const std::string& path, co
       NDS_CUDA(cudaStreamSynchronize(stream_));
     }
     if (keep_host_) {
-      if (cudaHostRegister(tc.stage.data(), tc.stage.size(), cudaHostRegisterDefault) == cudaSuccess) tc.pinned = true;
-      else cudaGetLastError();
-    } else {
-      tc.stage.clear();
-      tc.stage.shrink_to_fit();
+      // page-locked memory from the driver (not a registered std::vector): host->device copies out of it run at the
+      // full PCIe rate
+      NDS_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&tc.h_enc), (size_t)tc.enc_bytes + 256, cudaHostAllocDefault));
+      memcpy(tc.h_enc, tc.stage.data(), (size_t)tc.enc_bytes);
+      tc.pinned = true;
     }
+    tc.stage.clear();
+    tc.stage.shrink_to_fit();
   }
   drop_table(name);
   tables_[name] = std::move(t);
@@ -339,7 +341,7 @@ void Engine::drop_table(const std::string& name) {
   if (it == tables_.end()) return;
   for (TableColumn& tc : it->second.cols) {
     if (tc.d_enc) cudaFree(tc.d_enc);
-    if (tc.pinned) cudaHostUnregister(tc.stage.data());
+    if (tc.h_enc) cudaFreeHost(tc.h_enc);
   }
   for (MemColumn& mc : it->second.mem_cols) {
     if (mc.d_data) cudaFreeAsync(mc.d_data, stream_);

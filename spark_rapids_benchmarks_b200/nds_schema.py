@@ -76,9 +76,14 @@ def column_spec(table):
     return SOURCE_TABLES[table]
 
 
+_CACHE = {}
+
+
 def column_types():
     """{column_name: type-string} over all source tables (TPC-DS column names are unique)."""
-    out = {}
+    if 'types' in _CACHE:
+        return _CACHE['types']
+    out = _CACHE['types'] = {}
     for cols in SOURCE_TABLES.values():
         for n, t, _ in cols:
             out[n] = t
@@ -86,7 +91,9 @@ def column_types():
 
 
 def column_table():
-    out = {}
+    if 'table' in _CACHE:
+        return _CACHE['table']
+    out = _CACHE['table'] = {}
     for tbl, cols in SOURCE_TABLES.items():
         for n, _, _ in cols:
             out[n] = tbl

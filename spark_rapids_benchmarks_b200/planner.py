@@ -467,7 +467,7 @@ class Planner:
                     name = e[2]
                 else:
                     ir, _ = extra
-                    match = [n for n, oir, _ in out_cols if json.dumps(oir, sort_keys=True) == json.dumps(ir, sort_keys=True)]
+                    match = [n for n, oir, _ in out_cols if oir == ir]
                     if not match:
                         raise PlanError('ORDER BY expression %s is not in the select list (not supported yet)' % self.text(e))
                     name = match[0]
@@ -520,7 +520,7 @@ class _AggMap:
         self.order = []
 
     def add(self, fn, ir, rtype):
-        key = (fn, json.dumps(ir, sort_keys=True))
+        key = (fn, repr(ir))
         if key not in self.items:
             name = '_agg%d' % len(self.order)
             self.items[key] = name

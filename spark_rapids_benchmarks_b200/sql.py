@@ -38,24 +38,26 @@ KEYWORDS = {'select', 'from', 'where', 'group', 'by', 'order', 'limit', 'as', 'a
 def tokenize(text):
     out = []
     pos = 0
-    while pos < len(text):
-        m = _TOKEN.match(text, pos)
-        if not m:
-            raise SqlError('cannot tokenize SQL at: %r' % text[pos:pos + 30])
+    for m in _TOKEN.finditer(text):
+        if m.start() != pos:
+            break
         pos = m.end()
-        if m.lastgroup is None:
+        kind = m.lastgroup
+        if kind is None:
             continue
-        v = m.group(m.lastgroup)
-        if m.lastgroup == 'id':
+        v = m.group(kind)
+        if kind == 'id':
             lv = v.lower()
             out.append(('kw', lv) if lv in KEYWORDS else ('id', lv))
-        elif m.lastgroup == 'bq':
+        elif kind == 'bq':
             out.append(('id', v[1:-1]))
-        elif m.lastgroup == 'str':
+        elif kind == 'str':
             out.append(('str', v[1:-1].replace("''", "'")))
         else:
-            out.append((m.lastgroup, v))
-    out.append(('eof', ''))
+            out.append((kind, v))
+    if pos != len(text):
+        raise SqlError('cannot tokenize SQL at: %r' % text[pos:pos + 30])
+    out.extend([('eof', '')] * 4)      # look-ahead never runs off the end
     return out
 
 
@@ -65,17 +67,19 @@ class Parser:
         self.i = 0
 
     def peek(self, k=0):
-        return self.t[min(self.i + k, len(self.t) - 1)]
+        return self.t[self.i + k]
 
     def next(self):
         tok = self.t[self.i]
-        self.i += 1
+        if tok[0] != 'eof':
+            self.i += 1
         return tok
 
     def accept(self, kind, val=None):
-        tok = self.peek()
+        tok = self.t[self.i]
         if tok[0] == kind and (val is None or tok[1] == val):
-            self.i += 1
+            if kind != 'eof':
+                self.i += 1
             return tok
         return None
 
@@ -86,7 +90,11 @@ class Parser:
         return tok
 
     def kw(self, word):
-        return self.accept('kw', word)
+        tok = self.t[self.i]
+        if tok[0] == 'kw' and tok[1] == word:
+            self.i += 1
+            return tok
+        return None
 
     # ---- statement -----------------------------------------------------------------------------
     def parse_query(self):
