@@ -44,6 +44,7 @@ struct LType {                 // logical type of a column / expression
   enum Kind { INT = 0, DATE = 1, DECIMAL = 2, F64 = 3, STR = 4, BOOL = 5 } kind = INT;
   int precision = 0, scale = 0;
   bool is32 = false;           // stored as int32 on the device
+  int maxlen = 0;              // strings: upper bound of the byte length when known (0 = unknown)
   DType dtype() const { return kind == STR ? DT_STR : (kind == F64 ? DT_F64 : (is32 ? DT_I32 : DT_I64)); }
   std::string str() const;
 };
@@ -168,6 +169,7 @@ class Engine {
   int64_t h2d_bytes_ = 0, d2h_bytes_ = 0;
   double exec_ms_ = 0;
   double host_ms_ = 0;
+  std::string trace_;             // options.trace: host timeline of the last execute
   uint8_t* pin_ = nullptr;      // pinned host ring for small host->device uploads (plan blobs, page tasks)
   int64_t pin_cap_ = 0;
   uint8_t* slab_ = nullptr;     // device slab behind the per-query bump allocator

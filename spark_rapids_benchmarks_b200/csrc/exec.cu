@@ -73,6 +73,14 @@ struct Arena {
       NDS_CUDA(cudaStreamSynchronize(s));
     }
   }
+  // pinned bytes for a device -> host read-back (nullptr when the ring is full: the caller falls back to pageable memory)
+  uint8_t* pin_take(int64_t bytes) {
+    int64_t need = align_up(std::max<int64_t>(bytes, 1), 64);
+    if (!pin || pin_off + need > pin_cap) return nullptr;
+    uint8_t* p = pin + pin_off;
+    pin_off += need;
+    return p;
+  }
   ~Arena() {
     for (void* p : ptrs) cudaFreeAsync(p, s);
   }
@@ -166,7 +174,27 @@ struct Blob {
 
 struct RuntimeFilter {           // dynamic partition pruning: build-side join keys
   std::string column;
-  std::unordered_set<int64_t> keys;
+  // a bitmap over [lo, hi] when the key range is small (surrogate keys are dense), else a sorted list
+  int64_t lo = 0, hi = -1;
+  std::vector<uint64_t> bits;
+  std::vector<int64_t> sorted;
+  void assign(std::vector<int64_t>& k) {
+    if (k.empty()) return;
+    lo = hi = k[0];
+    for (int64_t v : k) { lo = std::min(lo, v); hi = std::max(hi, v); }
+    if (hi - lo < (int64_t(1) << 26)) {
+      bits.assign((size_t)((hi - lo) / 64 + 1), 0);
+      for (int64_t v : k) bits[(size_t)((v - lo) >> 6)] |= uint64_t(1) << ((v - lo) & 63);
+    } else {
+      std::sort(k.begin(), k.end());
+      sorted.swap(k);
+    }
+  }
+  bool contains(int64_t v) const {
+    if (v < lo || v > hi) return false;
+    if (!bits.empty()) return (bits[(size_t)((v - lo) >> 6)] >> ((v - lo) & 63)) & 1;
+    return std::binary_search(sorted.begin(), sorted.end(), v);
+  }
 };
 
 }  // namespace
@@ -180,6 +208,9 @@ struct Exec {
   bool profile = false;
   bool decode_timing = false;
   bool split_decode = true;      // options.split_decode=false forces every page through the general kernel
+  bool trace = false;            // options.trace: host timeline marks + time spent waiting in each stream sync
+  double t_base = 0;
+  std::string trace_out;
   std::vector<OpStat> stats;
   int64_t launches = 0;
   int64_t h2d = 0, d2h = 0;
@@ -194,7 +225,23 @@ struct Exec {
       profile = options->bool_or("profile", false);
       decode_timing = options->bool_or("decode_timing", false);
       split_decode = options->bool_or("split_decode", true);
+      trace = options->bool_or("trace", false);
     }
+    t_base = now_ms();
+  }
+
+  void mark(const char* label, double wait_ms = -1) {
+    if (!trace) return;
+    char buf[160];
+    snprintf(buf, sizeof buf, "%s[\"%s\",%.4f,%.4f]", trace_out.empty() ? "" : ",", label, now_ms() - t_base, wait_ms);
+    trace_out += buf;
+  }
+  void sync(const char* label) {
+    if (!trace) { NDS_CUDA(cudaStreamSynchronize(s)); return; }
+    mark(label);
+    const double t0 = now_ms();
+    NDS_CUDA(cudaStreamSynchronize(s));
+    mark("sync_done", now_ms() - t0);
   }
 
   ~Exec() {     // a failed query still returns its timing events to the pool
@@ -212,6 +259,7 @@ struct Exec {
     OpStat st;
     st.op = op;
     st.t0 = now_ms();
+    if (trace) mark(op.c_str());
     if (profile || always) {
       st.e0 = e.get_event();
       st.e1 = e.get_event();
@@ -224,18 +272,20 @@ struct Exec {
     stats[i].bytes = bytes;
     stats[i].rows = rows;
     stats[i].host_ms = now_ms() - stats[i].t0;
+    if (trace) mark("end");
     if (stats[i].e1) NDS_CUDA(cudaEventRecord(stats[i].e1, s));
   }
 
   void check_err() {
     int h[4];
     NDS_CUDA(cudaMemcpyAsync(h, err, sizeof h, cudaMemcpyDeviceToHost, s));
-    NDS_CUDA(cudaStreamSynchronize(s));
+    sync("sync:check_err");
     check_err_values(h);
   }
   void check_err_values(const int* h) {
     if (h[0]) fail("device kernel reported error code " + std::to_string(h[0]) +
-                   " (3-6: malformed parquet page, 11: string projection outside its column buffer, 12: sort key overflow)");
+                   " (3-6: malformed parquet page, 11: string projection outside its column buffer, 12: sort key wider than its declared maximum, 13: result string "
+                   "longer than its column's known maximum)");
     if (h[1] & 1) fail("hash join: duplicate keys on the build side (only unique build keys are supported)");
     if (h[1] & 2) fail("hash join: key equals the reserved empty marker");
   }
@@ -245,7 +295,7 @@ struct Exec {
     if (!b.n_dev) { b.n_exact = b.n_max; return b.n_exact; }
     int v = 0;
     NDS_CUDA(cudaMemcpyAsync(&v, b.n_dev, 4, cudaMemcpyDeviceToHost, s));
-    NDS_CUDA(cudaStreamSynchronize(s));
+    sync("sync:count");
     d2h += 4;
     b.n_exact = std::min<int64_t>(v, b.n_max);
     return b.n_exact;
@@ -291,6 +341,7 @@ struct Exec {
         if (v.kind != Json::Str) fail("plan: string literal expected");
         int64_t off = (int64_t)bb.lit.size();
         bb.lit += v.s;
+        t.maxlen = std::max<int>(1, (int)v.s.size());
         code.push_back(Instr{OP_LIT_S, 0, (int64_t)(((uint64_t)v.s.size() << 32) | (uint64_t)off)});
       } else if (t.kind == LType::F64) {
         double d = v.d;
@@ -386,6 +437,10 @@ struct Exec {
       code.push_back(Instr{OP_SUBSTR, (int32_t)x.int_or("start", 1), x.int_or("len", 1 << 30)});
       if (str_origin) *str_origin = origin;
       out.kind = LType::STR;
+      {
+        const int64_t want = std::max<int64_t>(1, x.int_or("len", 1 << 30));
+        out.maxlen = (int)std::min<int64_t>(want, t.maxlen > 0 ? t.maxlen : (want < (1 << 20) ? want : 0));
+      }
     } else if (fn == "if") {
       LType tc = compile(arg(0), b, bb, code);
       if (tc.kind != LType::BOOL) fail("plan: if() condition must be boolean");
@@ -396,6 +451,7 @@ struct Exec {
       if (str_origin) *str_origin = -2;
       out = tt;
       out.is32 = false;
+      out.maxlen = (tt.maxlen > 0 && te.maxlen > 0) ? std::max(tt.maxlen, te.maxlen) : 0;
     } else if (fn == "decavg") {
       LType ts = compile(arg(0), b, bb, code);
       compile(arg(1), b, bb, code);
@@ -431,8 +487,10 @@ struct Exec {
       LType forced = parse_type(x.str("type"));
       if ((forced.kind == LType::STR) != (out.kind == LType::STR) || (forced.kind == LType::F64) != (out.kind == LType::F64))
         fail("plan: type annotation '" + x.str("type") + "' contradicts the expression");
+      const int keep_len = out.maxlen;
       out = forced;
       out.is32 = false;
+      out.maxlen = keep_len;
     }
     if ((int)code.size() > 200) fail("plan: expression too large");
     return out;
@@ -482,7 +540,7 @@ struct Exec {
     int64_t N = 0;
     for (size_t f = 0; f < t.files.size(); ++f) {
       const FileInfo& fi = t.files[f];
-      if (rf && (fi.part_null || !rf->keys.count(fi.part_val))) continue;
+      if (rf && (fi.part_null || !rf->contains(fi.part_val))) continue;
       sel.push_back((int)f);
       row_start.push_back(N);
       N += fi.rows;
@@ -873,20 +931,30 @@ struct Exec {
       if (nb > 0) {
         // keys of the upper-bound row range and the exact count come back in one synchronisation
         const bool is32 = flat.lt.dtype() == DT_I32;
-        std::vector<uint8_t> hk(nb * (is32 ? 4 : 8));
-        std::vector<uint32_t> hv((nb + 31) / 32);
-        int hcount = (int)nb;
-        NDS_CUDA(cudaMemcpyAsync(hk.data(), flat.data, hk.size(), cudaMemcpyDeviceToHost, s));
-        NDS_CUDA(cudaMemcpyAsync(hv.data(), flat.valid, hv.size() * 4, cudaMemcpyDeviceToHost, s));
-        if (build.n_dev && build.n_exact < 0) NDS_CUDA(cudaMemcpyAsync(&hcount, build.n_dev, 4, cudaMemcpyDeviceToHost, s));
-        NDS_CUDA(cudaStreamSynchronize(s));
-        d2h += (int64_t)hk.size() + (int64_t)hv.size() * 4 + 4;
+        const int64_t kbytes = nb * (is32 ? 4 : 8), vbytes = ((nb + 31) / 32) * 4;
+        std::vector<uint8_t> pageable;
+        uint8_t* hbuf = ar.pin_take(kbytes + vbytes + 16);
+        if (!hbuf) { pageable.resize((size_t)(kbytes + vbytes + 16)); hbuf = pageable.data(); }
+        const int64_t off_v = align_up(kbytes, 8), off_c = off_v + vbytes;
+        const uint8_t* hk = hbuf;
+        const uint32_t* hv = reinterpret_cast<const uint32_t*>(hbuf + off_v);
+        int* hcount_p = reinterpret_cast<int*>(hbuf + align_up(off_c, 4));
+        *hcount_p = (int)nb;
+        NDS_CUDA(cudaMemcpyAsync(hbuf, flat.data, (size_t)kbytes, cudaMemcpyDeviceToHost, s));
+        NDS_CUDA(cudaMemcpyAsync(hbuf + off_v, flat.valid, (size_t)vbytes, cudaMemcpyDeviceToHost, s));
+        if (build.n_dev && build.n_exact < 0) NDS_CUDA(cudaMemcpyAsync(hcount_p, build.n_dev, 4, cudaMemcpyDeviceToHost, s));
+        sync("sync:build_keys");
+        d2h += kbytes + vbytes + 4;
+        int hcount = *hcount_p;
         if (build.n_exact >= 0) hcount = (int)build.n_exact;
         if (hcount > nb) hcount = (int)nb;
         build.n_exact = hcount;
+        std::vector<int64_t> keys;
+        keys.reserve((size_t)hcount);
         for (int64_t i = 0; i < hcount; ++i)
           if ((hv[i >> 5] >> (i & 31)) & 1u)
-            rf.keys.insert(is32 ? (int64_t) reinterpret_cast<int32_t*>(hk.data())[i] : reinterpret_cast<int64_t*>(hk.data())[i]);
+            keys.push_back(is32 ? (int64_t) reinterpret_cast<const int32_t*>(hk)[i] : reinterpret_cast<const int64_t*>(hk)[i]);
+        rf.assign(keys);
       }
       down.push_back(std::move(rf));
     }
@@ -1115,10 +1183,12 @@ struct Exec {
     // there, so that count and lengths come back in ONE synchronisation
     Blob bb;
     std::vector<SortKey> keys;
+    std::vector<LType> key_types;
     int B = 0;
     for (const Json& k : node.at("keys").a) {
       std::vector<Instr> code;
       LType t = compile(k.at("expr"), in, bb, code);
+      key_types.push_back(t);
       SortKey sk;
       sk.prog = bb.add_prog(code, t);
       sk.kind = t.kind == LType::STR ? 2 : (t.kind == LType::F64 ? 1 : 0);
@@ -1128,9 +1198,15 @@ struct Exec {
       sk.offset = 0;
       keys.push_back(sk);
     }
-    bool any_str = false;
-    for (const SortKey& sk : keys) any_str |= sk.kind == 2;
-    if (any_str && in.rc().host > 0) {
+    // string key widths: the column's known maximum length (dictionary / page scan at registration, substr length),
+    // else measured on the device - with the row count still there, so that both come back in ONE synchronisation
+    bool need_measure = false;
+    for (SortKey& sk : keys)
+      if (sk.kind == 2) {
+        const int ml = key_types[&sk - keys.data()].maxlen;
+        if (ml > 0) sk.width = ml; else need_measure = true;
+      }
+    if (need_measure && in.rc().host > 0) {
       Blob::Dev dev0 = bb.upload(ar, s);
       int* dmax = ar.zeros<int>((int64_t)keys.size());
       for (size_t k = 0; k < keys.size(); ++k)
@@ -1139,54 +1215,107 @@ struct Exec {
       int hcount = 0;
       NDS_CUDA(cudaMemcpyAsync(hmax.data(), dmax, keys.size() * 4, cudaMemcpyDeviceToHost, s));
       if (in.n_dev && in.n_exact < 0) NDS_CUDA(cudaMemcpyAsync(&hcount, in.n_dev, 4, cudaMemcpyDeviceToHost, s));
-      NDS_CUDA(cudaStreamSynchronize(s));
+      sync("sync:sort_widths");
       d2h += (int64_t)keys.size() * 4 + 4;
       if (in.n_dev && in.n_exact < 0) in.n_exact = std::min<int64_t>(hcount, in.n_max);
       for (size_t k = 0; k < keys.size(); ++k)
-        if (keys[k].kind == 2) keys[k].width = hmax[k];
+        if (keys[k].kind == 2) keys[k].width = std::max(hmax[k], 1);
     }
-    int64_t n = count(in);
+    for (SortKey& sk : keys) { sk.offset = B; B += 1 + sk.width; }
+    const int64_t nb = in.rc().host;                   // exact when known, else the upper bound
     Batch out;
-    const int64_t m = (limit >= 0 && limit < n) ? limit : n;
-    out.n_max = m;
-    out.n_exact = m;
+    int64_t m = (limit >= 0 && limit < nb) ? limit : nb;
     uint32_t* rows = ar.alloc_n<uint32_t>(std::max<int64_t>(m, 1));
-    if (n > 0) {
-      RowCount rc{nullptr, n};
-      for (SortKey& sk : keys) { sk.offset = B; B += 1 + sk.width; }
+    int* out_count = nullptr;
+    if (nb > 0) {
+      RowCount rc = in.rc();
       Blob::Dev dev = bb.upload(ar, s, keys.data(), (int64_t)keys.size() * sizeof(SortKey));
-      uint8_t* keybuf = (uint8_t*)ar.alloc(n * B);
+      uint8_t* keybuf = (uint8_t*)ar.alloc(nb * B);
       int* active = ar.zeros<int>(B + 1);
       launch_encode_keys(dev.progs, reinterpret_cast<const SortKey*>(dev.extra), (int)keys.size(), dev.ctx, rc, keybuf, B, active, err, s);
       ++launches;
-      uint32_t* pa = ar.alloc_n<uint32_t>(n);
-      uint32_t* pb = ar.alloc_n<uint32_t>(n);
-      int* dummy = ar.zeros<int>(1);
-      if (n <= kSmallSortMax) {
-        int* which = ar.zeros<int>(2);
-        launch_radix_sort_small(keybuf, B, active, rc, pa, pb, which, s);
-        launch_take_perm(pa, pb, which, 0, rc, limit, rows, dummy, s);
-        launches += 2;
-      } else {
-        // which key bytes differ between rows decides the passes (one small read-back)
-        std::vector<int> hact(B);
-        NDS_CUDA(cudaMemcpyAsync(hact.data(), active, B * sizeof(int), cudaMemcpyDeviceToHost, s));
-        NDS_CUDA(cudaStreamSynchronize(s));
-        d2h += B * 4;
-        std::vector<int> passes;
-        for (int b = B - 1; b >= 0; --b)
-          if (hact[b]) passes.push_back(b);
-        const int np = (int)passes.size();
-        int* which = ar.zeros<int>(np + 2);
-        uint32_t* scratch = ar.alloc_n<uint32_t>((int64_t)radix_sort_grid(n) * 256 + np + 16);
-        int l = 0;
-        launch_radix_sort(keybuf, B, passes.data(), np, rc, pa, pb, which, scratch, s, &l);
-        launches += l;
-        launch_take_perm(pa, pb, which, np, rc, limit, rows, dummy, s);
+      out_count = ar.zeros<int>(1);
+      bool done = false;
+      const bool compact_ok = B <= kMaxCompactBytes;
+      const bool topk = limit >= 1 && limit <= kRankSortMax / 8;
+      if (compact_ok && (nb <= kRankSortMax || topk)) {
+        const int W = (B + 7) / 8;
+        uint64_t* ckeys = ar.alloc_n<uint64_t>(nb * W);
+        int* wact = ar.zeros<int>(1);
+        const bool direct = nb <= kRankSortMax;
+        uint32_t* rank_tmp = direct ? ar.alloc_n<uint32_t>(nb) : nullptr;
+        int* tile_done = direct ? ar.alloc_n<int>((nb + 127) / 128 + 1) : nullptr;
+        launch_compact_keys(keybuf, B, active, rc, ckeys, W, wact, rank_tmp, tile_done, direct ? nb : 0, s);
         ++launches;
+        if (direct) {
+          // no host round trip at all: the row count stays on the device
+          launch_rank_sort(ckeys, W, wact, nullptr, nullptr, 0, rc, nb, limit, rank_tmp, tile_done, rows, out_count, s);
+          ++launches;
+          done = true;
+        } else {
+          uint32_t* cand = ar.alloc_n<uint32_t>(kRankSortMax);
+          int* nc_dev = ar.zeros<int>(1);
+          uint32_t* hist = ar.zeros<uint32_t>(kSelectPasses * 256);
+          int l = 0;
+          launch_topk_select(ckeys, W, rc, limit, cand, kRankSortMax, hist, nc_dev, s, &l);
+          launches += l;
+          int hv[2] = {0, (int)nb};
+          NDS_CUDA(cudaMemcpyAsync(&hv[0], nc_dev, 4, cudaMemcpyDeviceToHost, s));
+          if (in.n_dev && in.n_exact < 0) NDS_CUDA(cudaMemcpyAsync(&hv[1], in.n_dev, 4, cudaMemcpyDeviceToHost, s));
+          sync("sync:sort_topk");
+          d2h += 8;
+          if (in.n_exact < 0) in.n_exact = std::min<int64_t>(hv[1], in.n_max);
+          if (hv[0] <= kRankSortMax) {
+            const int64_t ncand = std::max(hv[0], 1);
+            uint32_t* rt = ar.zeros<uint32_t>(ncand);
+            int* td = ar.zeros<int>((ncand + 127) / 128);
+            launch_rank_sort(ckeys, W, wact, cand, nc_dev, kRankSortMax, in.rc(), ncand, limit, rt, td, rows, out_count, s);
+            ++launches;
+            done = true;
+          }
+        }
+      }
+      if (!done) {
+        // LSD radix sort over the key bytes that differ between rows (one small read-back decides the passes)
+        const int64_t n = count(in);
+        RowCount rn{nullptr, n};
+        uint32_t* pa = ar.alloc_n<uint32_t>(std::max<int64_t>(n, 1));
+        uint32_t* pb = ar.alloc_n<uint32_t>(std::max<int64_t>(n, 1));
+        if (n > 0 && n <= kSmallSortMax) {
+          int* which = ar.zeros<int>(2);
+          launch_radix_sort_small(keybuf, B, active, rn, pa, pb, which, s);
+          launch_take_perm(pa, pb, which, 0, rn, limit, rows, out_count, s);
+          launches += 2;
+        } else if (n > 0) {
+          std::vector<int> hact(B);
+          NDS_CUDA(cudaMemcpyAsync(hact.data(), active, B * sizeof(int), cudaMemcpyDeviceToHost, s));
+          sync("sync:sort_active");
+          d2h += B * 4;
+          std::vector<int> passes;
+          for (int b = B - 1; b >= 0; --b)
+            if (hact[b]) passes.push_back(b);
+          const int np = (int)passes.size();
+          int* which = ar.zeros<int>(np + 2);
+          uint32_t* scratch = ar.alloc_n<uint32_t>((int64_t)radix_sort_grid(n) * 256 + np + 16);
+          int l = 0;
+          launch_radix_sort(keybuf, B, passes.data(), np, rn, pa, pb, which, scratch, s, &l);
+          launches += l;
+          launch_take_perm(pa, pb, which, np, rn, limit, rows, out_count, s);
+          ++launches;
+        }
       }
     }
-    RowCount rm{nullptr, m};
+    if (in.n_exact >= 0 || !in.n_dev) {
+      const int64_t n = in.n_exact >= 0 ? in.n_exact : in.n_max;
+      m = (limit >= 0 && limit < n) ? limit : n;
+      out.n_max = m;
+      out.n_exact = m;
+    } else {
+      out.n_max = m;              // upper bound; the exact min(limit, n) is on the device
+      out.n_dev = out_count;
+    }
+    const int64_t n = nb;
+    RowCount rm = out.rc();
     if (m > 0) {
       std::vector<Json> ces;
       ces.reserve(in.cols.size());
@@ -1262,38 +1391,51 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
     Exec ex(*this, options);
     std::vector<RuntimeFilter> none;
     Batch res = ex.exec(root, none);
-    int64_t n = ex.count(res);
+    ex.mark("plan_issued");
+    const size_t nc = res.cols.size();
+    // Small results (every NDS top-k) leave the device in one packed buffer, row count included: one copy, one
+    // synchronisation.  Anything larger takes the column-at-a-time route below.
+    constexpr int64_t kSmallRows = 8192, kSmallBytes = 2 << 20;
+    int64_t pack_bytes = 64;
+    bool small = res.rc().host <= kSmallRows && ex.ar.pin != nullptr;
+    for (size_t c = 0; c < nc && small; ++c) {
+      const Column& col = res.cols[c];
+      const int64_t nb = std::max<int64_t>(res.rc().host, 1);
+      pack_bytes += ((nb + 31) / 32) * 4 + 64;
+      if (col.lt.kind == LType::STR) {
+        if (col.lt.maxlen <= 0) small = false;
+        pack_bytes += (nb + 1) * 4 + nb * (int64_t)col.lt.maxlen + 128;
+      } else {
+        pack_bytes += nb * 8 + 64;
+      }
+      if (pack_bytes > kSmallBytes) small = false;
+    }
+    int64_t n = small ? -1 : ex.count(res);
     // flatten every result column that still goes through a row map (one launch for all of them)
     std::vector<Column> flat = res.cols;
-    RowCount rn{nullptr, n};
-    if (n > 0) {
+    const RowCount rn = small ? res.rc() : RowCount{nullptr, n};
+    if (rn.host > 0) {
       std::vector<Json> ces;
       std::vector<size_t> which;
-      for (size_t c = 0; c < res.cols.size(); ++c)
+      for (size_t c = 0; c < nc; ++c)
         if (res.cols[c].rowmap) { which.push_back(c); ces.push_back(Exec::col_expr(res.cols[c].name)); }
       std::vector<std::pair<std::string, const Json*>> exs;
       for (size_t k = 0; k < which.size(); ++k) exs.emplace_back(res.cols[which[k]].name, &ces[k]);
       std::vector<Column> fc = ex.eval_columns(exs, res, nullptr, rn);
       for (size_t k = 0; k < which.size(); ++k) flat[which[k]] = fc[k];
     }
-    int h_err[4] = {0, 0, 0, 0};
-    NDS_CUDA(cudaMemcpyAsync(h_err, ex.err, sizeof h_err, cudaMemcpyDeviceToHost, stream_));   // checked after the export sync
-    // ---- device -> host, as Arrow C data
+    // ---- schema
     ExportPriv* sp = new ExportPriv();
     ExportPriv* apv = new ExportPriv();
-    const size_t nc = flat.size();
     sp->schema_store.resize(nc);
     apv->array_store.resize(nc);
     apv->child_bufptrs.resize(nc);
     sp->strings.reserve(2 * nc + 2);
-    // pass 1: schema entries, and every column's validity + values on their way to the host (no sync in between)
-    std::vector<uint8_t*> hvalid_v(nc, nullptr), hdata_v(nc, nullptr);
     for (size_t c = 0; c < nc; ++c) {
       const Column& col = flat[c];
-      const DType dt = col.lt.dtype();
       std::string fmt;
       switch (col.lt.kind) {
-        case LType::INT: case LType::BOOL: fmt = dt == DT_I32 ? "i" : "l"; break;
+        case LType::INT: case LType::BOOL: fmt = col.lt.dtype() == DT_I32 ? "i" : "l"; break;
         case LType::DATE: fmt = "tdD"; break;
         case LType::DECIMAL: fmt = "d:" + std::to_string(col.lt.precision) + "," + std::to_string(col.lt.scale); break;
         case LType::F64: fmt = "g"; break;
@@ -1310,30 +1452,143 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
       cs.flags = 2;  // nullable
       cs.release = release_schema_child;
       sp->schema_children.push_back(&cs);
-      const int64_t vbytes = ((n + 31) / 32) * 4;
-      if (col.valid && n > 0) {
-        hvalid_v[c] = (uint8_t*)malloc(vbytes + 8);
-        apv->bufs.push_back(hvalid_v[c]);
-        NDS_CUDA(cudaMemcpyAsync(hvalid_v[c], col.valid, vbytes, cudaMemcpyDeviceToHost, stream_));
-        ex.d2h += vbytes;
-      }
-      const int w = dt == DT_I32 ? 4 : 8;
-      hdata_v[c] = (uint8_t*)malloc(std::max<int64_t>(n * w, 8));
-      apv->bufs.push_back(hdata_v[c]);
-      if (n > 0) { NDS_CUDA(cudaMemcpyAsync(hdata_v[c], col.data, n * w, cudaMemcpyDeviceToHost, stream_)); ex.d2h += n * w; }
     }
-    NDS_CUDA(cudaStreamSynchronize(stream_));
-    try {
-      ex.check_err_values(h_err);
-    } catch (...) {
+    auto drop_export = [&]() {
       for (void* b : apv->bufs) free(b);
       delete apv;
       delete sp;
+    };
+    // ---- device -> host.  Per column afterwards: hvalid (or null), hdata (fixed width values or StrViews),
+    // and for strings either (offs32, chars) already final (small route) or pending a device gather (large route).
+    std::vector<uint8_t*> hvalid_v(nc, nullptr), hdata_v(nc, nullptr), hchars_v(nc, nullptr);
+    std::vector<int32_t*> hoffs_v(nc, nullptr);
+    int h_err[4] = {0, 0, 0, 0};
+    try {
+      if (small) {
+        const int64_t nb = std::max<int64_t>(rn.host, 1);
+        const int64_t vbytes_b = ((nb + 31) / 32) * 4;
+        std::vector<ExportSeg> segs;
+        struct Place { int64_t valid = -1, data = -1, offs = -1, chars = -1; };
+        std::vector<Place> place(nc);
+        int64_t off = 0;
+        auto take = [&](int64_t bytes) { int64_t o = off; off = align_up(off + bytes, 16); return o; };
+        const int64_t off_count = take(4), off_err = take(16);
+        segs.push_back(ExportSeg{nullptr, nullptr, nullptr, off_count, 4, 0, 0, 2, 0});
+        for (size_t c = 0; c < nc; ++c) {
+          const Column& col = flat[c];
+          if (col.valid) {
+            place[c].valid = take(vbytes_b);
+            segs.push_back(ExportSeg{col.valid, nullptr, nullptr, place[c].valid, vbytes_b, 0, 0, 0, 0});
+          }
+          if (col.lt.kind == LType::STR) {
+            const int64_t cap = nb * (int64_t)col.lt.maxlen;
+            place[c].offs = take((nb + 1) * 4);
+            place[c].chars = take(cap);
+            segs.push_back(ExportSeg{col.data, col.valid, col.strbase, place[c].offs, 0, place[c].chars, cap, 1, 0});
+          } else {
+            const int64_t w = col.lt.dtype() == DT_I32 ? 4 : 8;
+            place[c].data = take(nb * w);
+            segs.push_back(ExportSeg{col.data, nullptr, nullptr, place[c].data, nb * w, 0, 0, 0, 0});
+          }
+        }
+        const int64_t total = off;
+        uint8_t* hpack = ex.ar.pin_take(total);
+        std::vector<uint8_t> pageable;
+        if (!hpack) { pageable.resize((size_t)total); hpack = pageable.data(); }
+        uint8_t* dpack = (uint8_t*)ex.ar.alloc(total);
+        ExportSeg* dsegs = ex.ar.alloc_n<ExportSeg>((int64_t)segs.size());
+        ex.ar.upload(dsegs, segs.data(), (int64_t)segs.size() * (int64_t)sizeof(ExportSeg));
+        launch_export_pack(dsegs, (int)segs.size(), rn, dpack, ex.err, stream_);
+        ++ex.launches;
+        NDS_CUDA(cudaMemcpyAsync(dpack + off_err, ex.err, sizeof h_err, cudaMemcpyDeviceToDevice, stream_));
+        NDS_CUDA(cudaMemcpyAsync(hpack, dpack, (size_t)total, cudaMemcpyDeviceToHost, stream_));
+        ex.sync("sync:export");
+        ex.d2h += total;
+        memcpy(h_err, hpack + off_err, sizeof h_err);
+        ex.check_err_values(h_err);
+        n = std::min<int64_t>(*reinterpret_cast<const int*>(hpack + off_count), rn.host);
+        if (n < 0) n = 0;
+        const int64_t vbytes = ((n + 31) / 32) * 4;
+        for (size_t c = 0; c < nc; ++c) {
+          const Column& col = flat[c];
+          if (place[c].valid >= 0 && n > 0) {
+            hvalid_v[c] = (uint8_t*)malloc(vbytes + 8);
+            apv->bufs.push_back(hvalid_v[c]);
+            memcpy(hvalid_v[c], hpack + place[c].valid, (size_t)vbytes);
+          }
+          if (col.lt.kind == LType::STR) {
+            const int32_t* po = reinterpret_cast<const int32_t*>(hpack + place[c].offs);
+            hoffs_v[c] = (int32_t*)malloc((n + 1) * 4 + 8);
+            apv->bufs.push_back(hoffs_v[c]);
+            if (n > 0) memcpy(hoffs_v[c], po, (size_t)(n + 1) * 4); else hoffs_v[c][0] = 0;
+            const int64_t cb = n > 0 ? po[n] : 0;
+            hchars_v[c] = (uint8_t*)malloc(std::max<int64_t>(cb, 8));
+            apv->bufs.push_back(hchars_v[c]);
+            if (cb > 0) memcpy(hchars_v[c], hpack + place[c].chars, (size_t)cb);
+          } else {
+            const int64_t w = col.lt.dtype() == DT_I32 ? 4 : 8;
+            hdata_v[c] = (uint8_t*)malloc(std::max<int64_t>(n * w, 8));
+            apv->bufs.push_back(hdata_v[c]);
+            if (n > 0) memcpy(hdata_v[c], hpack + place[c].data, (size_t)(n * w));
+          }
+        }
+      } else {
+        NDS_CUDA(cudaMemcpyAsync(h_err, ex.err, sizeof h_err, cudaMemcpyDeviceToHost, stream_));   // checked after the export sync
+        for (size_t c = 0; c < nc; ++c) {
+          const Column& col = flat[c];
+          const int64_t vbytes = ((n + 31) / 32) * 4;
+          if (col.valid && n > 0) {
+            hvalid_v[c] = (uint8_t*)malloc(vbytes + 8);
+            apv->bufs.push_back(hvalid_v[c]);
+            NDS_CUDA(cudaMemcpyAsync(hvalid_v[c], col.valid, vbytes, cudaMemcpyDeviceToHost, stream_));
+            ex.d2h += vbytes;
+          }
+          const int w = col.lt.dtype() == DT_I32 ? 4 : 8;
+          hdata_v[c] = (uint8_t*)malloc(std::max<int64_t>(n * w, 8));
+          apv->bufs.push_back(hdata_v[c]);
+          if (n > 0) { NDS_CUDA(cudaMemcpyAsync(hdata_v[c], col.data, n * w, cudaMemcpyDeviceToHost, stream_)); ex.d2h += n * w; }
+        }
+        ex.sync("sync:export");
+        ex.check_err_values(h_err);
+        // string characters are gathered on the device for all string columns, one more sync
+        bool pending = false;
+        for (size_t c = 0; c < nc; ++c) {
+          const Column& col = flat[c];
+          if (col.lt.kind != LType::STR) continue;
+          const uint8_t* hvalid = hvalid_v[c];
+          const StrView* views = reinterpret_cast<const StrView*>(hdata_v[c]);
+          int32_t* offs = (int32_t*)malloc((n + 1) * 4 + 8);
+          apv->bufs.push_back(offs);
+          hoffs_v[c] = offs;
+          std::vector<int64_t> offs64(n + 1, 0);
+          for (int64_t i = 0; i < n; ++i) {
+            bool ok = !hvalid || ((hvalid[i >> 3] >> (i & 7)) & 1);
+            offs64[i + 1] = offs64[i] + (ok ? (int64_t)(views[i] >> 32) : 0);
+          }
+          if (offs64[n] > 0x7FFFFFFFll) fail("result string column exceeds 2 GiB");
+          for (int64_t i = 0; i <= n; ++i) offs[i] = (int32_t)offs64[i];
+          uint8_t* chars = (uint8_t*)malloc(std::max<int64_t>(offs64[n], 8));
+          apv->bufs.push_back(chars);
+          hchars_v[c] = chars;
+          if (offs64[n] > 0) {
+            Arena& ar = ex.ar;
+            int64_t* doffs = ar.alloc_n<int64_t>(n + 1);
+            uint8_t* dchars = (uint8_t*)ar.alloc(offs64[n]);
+            ar.upload(doffs, offs64.data(), (n + 1) * 8);
+            launch_copy_str_bytes(reinterpret_cast<const StrView*>(col.data), col.strbase, doffs, n, dchars, stream_);
+            ++ex.launches;
+            NDS_CUDA(cudaMemcpyAsync(chars, dchars, offs64[n], cudaMemcpyDeviceToHost, stream_));
+            ex.d2h += offs64[n];
+            pending = true;
+          }
+        }
+        if (pending) ex.sync("sync:export_strings");
+      }
+    } catch (...) {
+      drop_export();
       throw;
     }
-    // pass 2: Arrow buffers; string characters are gathered on the device for all string columns, one more sync
-    struct PendingStr { size_t c; uint8_t* chars; uint8_t* dchars; int64_t bytes; };
-    std::vector<PendingStr> pending;
+    // ---- Arrow arrays over the host buffers
     for (size_t c = 0; c < nc; ++c) {
       const Column& col = flat[c];
       const DType dt = col.lt.dtype();
@@ -1363,30 +1618,7 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
         }
         bp = {hvalid, wide};
       } else if (col.lt.kind == LType::STR) {
-        const StrView* views = reinterpret_cast<const StrView*>(hdata);
-        int32_t* offs = (int32_t*)malloc((n + 1) * 4 + 8);
-        apv->bufs.push_back(offs);
-        std::vector<int64_t> offs64(n + 1, 0);
-        for (int64_t i = 0; i < n; ++i) {
-          bool ok = !hvalid || ((hvalid[i >> 3] >> (i & 7)) & 1);
-          offs64[i + 1] = offs64[i] + (ok ? (int64_t)(views[i] >> 32) : 0);
-        }
-        if (offs64[n] > 0x7FFFFFFFll) fail("result string column exceeds 2 GiB");
-        for (int64_t i = 0; i <= n; ++i) offs[i] = (int32_t)offs64[i];
-        uint8_t* chars = (uint8_t*)malloc(std::max<int64_t>(offs64[n], 8));
-        apv->bufs.push_back(chars);
-        if (offs64[n] > 0) {
-          Arena& ar = ex.ar;
-          int64_t* doffs = ar.alloc_n<int64_t>(n + 1);
-          uint8_t* dchars = (uint8_t*)ar.alloc(offs64[n]);
-          ar.upload(doffs, offs64.data(), (n + 1) * 8);
-          launch_copy_str_bytes(reinterpret_cast<const StrView*>(col.data), col.strbase, doffs, n, dchars, stream_);
-          ++ex.launches;
-          NDS_CUDA(cudaMemcpyAsync(chars, dchars, offs64[n], cudaMemcpyDeviceToHost, stream_));
-          ex.d2h += offs64[n];
-          pending.push_back(PendingStr{c, chars, dchars, offs64[n]});
-        }
-        bp = {hvalid, offs, chars};
+        bp = {hvalid, hoffs_v[c], hchars_v[c]};
       } else {
         bp = {hvalid, hdata};
       }
@@ -1394,7 +1626,6 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
       ca.buffers = bp.data();
       apv->array_children.push_back(&ca);
     }
-    if (!pending.empty()) NDS_CUDA(cudaStreamSynchronize(stream_));
     memset(out_schema, 0, sizeof *out_schema);
     out_schema->format = "+s";
     out_schema->name = "";
@@ -1413,7 +1644,8 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
     out_array->private_data = apv;
 
     NDS_CUDA(cudaEventRecord(ev1, stream_));
-    NDS_CUDA(cudaStreamSynchronize(stream_));
+    ex.sync("sync:final");
+    trace_ = ex.trace_out;
     launches_ = ex.launches;
     h2d_bytes_ = ex.h2d;
     d2h_bytes_ = ex.d2h;
@@ -1440,7 +1672,8 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
 
 std::string Engine::stats_json() const {
   std::string s = "{\"launches\":" + std::to_string(launches_) + ",\"device_ms\":" + std::to_string(exec_ms_) + ",\"host_ms\":" + std::to_string(host_ms_) +
-                  ",\"h2d_bytes\":" + std::to_string(h2d_bytes_) + ",\"d2h_bytes\":" + std::to_string(d2h_bytes_) + ",\"ops\":[";
+                  ",\"h2d_bytes\":" + std::to_string(h2d_bytes_) + ",\"d2h_bytes\":" + std::to_string(d2h_bytes_) +
+                  ",\"trace\":[" + trace_ + "],\"ops\":[";
   for (size_t i = 0; i < stats_.size(); ++i) {
     if (i) s += ",";
     s += "{\"op\":\"" + json_escape(stats_[i].op) + "\",\"ms\":" + std::to_string(stats_[i].ms) + ",\"bytes\":" +

@@ -619,6 +619,273 @@ void launch_radix_sort_small(const uint8_t* keybuf, int B, const int* active, Ro
   NDS_CUDA(cudaGetLastError());
 }
 
+// ------------------------------------------------------------------ sort: compacted keys, top-k select, rank sort
+// The encoded keys are mostly constant bytes (flags, high bytes of small integers, string padding, shared prefixes).
+// compact_keys_kernel keeps only the bytes that differ between rows (active[]), packed big-endian into 64-bit words,
+// so that an unsigned integer compare of word 0, then word 1, ... is the lexicographic compare of the full key.
+constexpr int kCompactThreads = 256;
+__global__ void __launch_bounds__(kCompactThreads)
+compact_keys_kernel(const uint8_t* __restrict__ keybuf, int B, const int* __restrict__ active, const int* n_dev, int64_t n_host,
+                    uint64_t* __restrict__ ckeys, int W, int* w_out, uint32_t* zero_rank, int* zero_tiles, int64_t zero_n) {
+  __shared__ uint16_t list[kMaxCompactBytes];
+  __shared__ int wsum[kCompactThreads / 32];
+  __shared__ int s_base;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) s_base = 0;
+  __syncthreads();
+  for (int b0 = 0; b0 < B; b0 += kCompactThreads) {
+    const int b = b0 + tid;
+    const bool f = b < B && active[b] != 0;
+    const uint32_t bal = __ballot_sync(0xFFFFFFFFu, f);
+    if (lane == 0) wsum[warp] = __popc(bal);
+    __syncthreads();
+    int pre = s_base;
+    for (int w = 0; w < warp; ++w) pre += wsum[w];
+    if (f) list[pre + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)b;
+    __syncthreads();
+    if (tid == 0) { int t = 0; for (int w = 0; w < kCompactThreads / 32; ++w) t += wsum[w]; s_base += t; }
+    __syncthreads();
+  }
+  const int nact = s_base;
+  const int wact = nact ? (nact + 7) >> 3 : 1;
+  if (blockIdx.x == 0 && tid == 0) w_out[0] = wact;
+  const int64_t n = row_count(n_dev, n_host);
+  if (zero_rank)      // the rank sort that follows accumulates into these
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + tid; i < zero_n; i += (int64_t)gridDim.x * blockDim.x) {
+      zero_rank[i] = 0;
+      if ((i & 127) == 0) zero_tiles[i >> 7] = 0;
+    }
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + tid; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const uint8_t* row = keybuf + i * B;
+    for (int w = 0; w < wact; ++w) {
+      uint64_t v = 0;
+      for (int b = 0; b < 8; ++b) {
+        const int k = 8 * w + b;
+        v = (v << 8) | (k < nact ? (uint64_t)row[list[k]] : 0ull);
+      }
+      ckeys[i * W + w] = v;
+    }
+  }
+}
+void launch_compact_keys(const uint8_t* keybuf, int B, const int* active, RowCount n, uint64_t* ckeys, int W, int* w_out,
+                         uint32_t* zero_rank, int* zero_tiles, int64_t zero_n, cudaStream_t s) {
+  compact_keys_kernel<<<grid_for(n.host), kCompactThreads, 0, s>>>(keybuf, B, active, n.dev, n.host, ckeys, W, w_out, zero_rank,
+                                                                    zero_tiles, zero_n);
+  NDS_CUDA(cudaGetLastError());
+}
+
+// Top-k prefilter (ORDER BY ... LIMIT k over many rows).  Word 0 of the compacted keys is radix-selected most
+// significant byte first: pass q histograms byte q of the rows that match the prefix chosen so far (multi-CTA, one
+// launch per pass, at most kSelectPasses), and every CTA re-derives the prefix from the earlier histograms, so no
+// state other than hist[][] passes between launches.  As soon as (rows below the prefix) + (rows in the chosen
+// bucket) fits the candidate list, later passes are no-ops.  topk_collect_kernel then lists every row whose masked
+// word 0 is <= the prefix: the k smallest keys are all in that list, ties only make it longer.  nc_out[0] = list
+// length; when it exceeds cap only cap entries were stored and the caller must take another route.
+constexpr int kSelectThreads = 256;
+constexpr int kSelectTile = 8192;       // rows per CTA and pass
+__device__ __forceinline__ void topk_state(const uint32_t* __restrict__ hist, int npass, int64_t k, int cap, uint64_t* s_prefix,
+                                           uint64_t* s_mask, int* s_done) {
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    uint64_t prefix = 0, mask = 0;
+    int64_t kk = k, less = 0;
+    int done = 0;
+    for (int q = 0; q < npass && !done; ++q) {
+      uint32_t h[8];
+      uint32_t sum = 0;
+      for (int b = 0; b < 8; ++b) { h[b] = hist[q * 256 + lane * 8 + b]; sum += h[b]; }
+      uint32_t incl = sum;
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+        if (lane >= d) incl += t;
+      }
+      const uint32_t excl = incl - sum;
+      const uint32_t total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+      if (total == 0) { done = 1; break; }
+      const int64_t ke = kk < (int64_t)total ? kk : (int64_t)total;
+      const bool mine = (int64_t)excl < ke && ke <= (int64_t)incl;
+      const uint32_t bal = __ballot_sync(0xFFFFFFFFu, mine);
+      const int src = __ffs(bal) - 1;
+      uint32_t dsel = 0, before = 0, bucket = 0;
+      if (lane == src) {
+        uint32_t c = excl;
+        for (int b = 0; b < 8; ++b) {
+          if ((int64_t)c + h[b] >= ke) { dsel = lane * 8 + b; before = c; bucket = h[b]; break; }
+          c += h[b];
+        }
+      }
+      dsel = __shfl_sync(0xFFFFFFFFu, dsel, src);
+      before = __shfl_sync(0xFFFFFFFFu, before, src);
+      bucket = __shfl_sync(0xFFFFFFFFu, bucket, src);
+      const int shift = 56 - 8 * q;
+      prefix |= (uint64_t)dsel << shift;
+      mask |= 0xFFull << shift;
+      less += before;
+      kk = ke - before;
+      if (less + (int64_t)bucket <= (int64_t)cap) done = 1;
+    }
+    if (lane == 0) { *s_prefix = prefix; *s_mask = mask; *s_done = done; }
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(kSelectThreads)
+topk_hist_kernel(const uint64_t* __restrict__ ckeys, int W, const int* n_dev, int64_t n_host, int64_t k, int cap, uint32_t* hist,
+                 int pass) {
+  __shared__ uint32_t h[256];
+  __shared__ uint64_t s_prefix, s_mask;
+  __shared__ int s_done;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int64_t n = row_count(n_dev, n_host);
+  const int64_t lo = (int64_t)blockIdx.x * kSelectTile, hi = min(n, lo + (int64_t)kSelectTile);
+  if (lo >= n) return;
+  h[tid] = 0;
+  topk_state(hist, pass, k, cap, &s_prefix, &s_mask, &s_done);
+  if (s_done) return;
+  const uint64_t prefix = s_prefix, mask = s_mask;
+  const int shift = 56 - 8 * pass;
+  for (int64_t i0 = lo; i0 < hi; i0 += kSelectThreads) {
+    const int64_t i = i0 + tid;
+    bool in = false;
+    uint32_t d = 256 + lane;
+    if (i < hi) {
+      const uint64_t v = ckeys[i * W];
+      in = (v & mask) == prefix;
+      if (in) d = (uint32_t)(v >> shift) & 255u;
+    }
+    const uint32_t m = __match_any_sync(0xFFFFFFFFu, d);
+    if (in && (m & ((1u << lane) - 1u)) == 0) atomicAdd(&h[d], (uint32_t)__popc(m));
+  }
+  __syncthreads();
+  if (h[tid]) atomicAdd(&hist[pass * 256 + tid], h[tid]);
+}
+
+__global__ void __launch_bounds__(kSelectThreads)
+topk_collect_kernel(const uint64_t* __restrict__ ckeys, int W, const int* n_dev, int64_t n_host, int64_t k, int cap,
+                    const uint32_t* hist, int npass, uint32_t* __restrict__ cand, int* nc_out) {
+  __shared__ uint64_t s_prefix, s_mask;
+  __shared__ int s_done;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int64_t n = row_count(n_dev, n_host);
+  const int64_t lo = (int64_t)blockIdx.x * kSelectTile, hi = min(n, lo + (int64_t)kSelectTile);
+  if (lo >= n) return;
+  topk_state(hist, npass, k, cap, &s_prefix, &s_mask, &s_done);
+  const uint64_t prefix = s_prefix, mask = s_mask;
+  for (int64_t i0 = lo; i0 < hi; i0 += kSelectThreads) {
+    const int64_t i = i0 + tid;
+    const bool take = i < hi && (ckeys[i * W] & mask) <= prefix;
+    const uint32_t bal = __ballot_sync(0xFFFFFFFFu, take);
+    int base = 0;
+    if (lane == 0 && bal) base = atomicAdd(nc_out, __popc(bal));
+    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+    if (take) {
+      const int pos = base + __popc(bal & ((1u << lane) - 1u));
+      if (pos < cap) cand[pos] = (uint32_t)i;
+    }
+  }
+}
+void launch_topk_select(const uint64_t* ckeys, int W, RowCount n, int64_t k, uint32_t* cand, int cap, uint32_t* hist, int* nc_out,
+                        cudaStream_t s, int* launches) {
+  const int G = (int)std::max<int64_t>(1, (n.host + kSelectTile - 1) / kSelectTile);
+  for (int pass = 0; pass < kSelectPasses; ++pass)
+    topk_hist_kernel<<<G, kSelectThreads, 0, s>>>(ckeys, W, n.dev, n.host, k, cap, hist, pass);
+  topk_collect_kernel<<<G, kSelectThreads, 0, s>>>(ckeys, W, n.dev, n.host, k, cap, hist, kSelectPasses, cand, nc_out);
+  NDS_CUDA(cudaGetLastError());
+  *launches += kSelectPasses + 1;
+}
+
+// Rank sort: row i's position is the number of rows that order before it (ties broken by row id, which makes it
+// the same permutation a stable sort yields).  n^2 compares, but they are independent, mostly decided on word 0,
+// and spread over gridDim.x row tiles x gridDim.y slices of the compared range - for the <= kRankSortMax rows an
+// NDS top-k sees, this is a few microseconds where 8-bit LSD passes cost one launch or several block barriers per
+// key byte.  Rows whose rank is below the limit write their id to out_rows[rank]: sort and LIMIT in one step.
+constexpr int kRankThreads = 128;
+__global__ void __launch_bounds__(kRankThreads)
+rank_sort_kernel(const uint64_t* __restrict__ ckeys, int W, const int* __restrict__ w_dev, const uint32_t* __restrict__ cand,
+                 const int* nc_dev, int cand_cap, const int* n_dev, int64_t n_host, int64_t limit, uint32_t* rank_tmp,
+                 int* tile_done, uint32_t* __restrict__ out_rows, int* out_count) {
+  __shared__ uint64_t s_k0[kRankThreads], s_k1[kRankThreads];
+  __shared__ uint32_t s_row[kRankThreads];
+  __shared__ int s_last;
+  const int tid = threadIdx.x;
+  const int64_t n_all = row_count(n_dev, n_host);
+  const int64_t n = cand ? min((int64_t)min(nc_dev[0], cand_cap), n_all) : n_all;
+  const int64_t m = (limit >= 0 && limit < n_all) ? limit : n_all;
+  if (blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) out_count[0] = (int)m;
+  if ((int64_t)blockIdx.x * kRankThreads >= n) return;
+  const int wact = w_dev[0];
+  const int64_t gi = (int64_t)blockIdx.x * kRankThreads + tid;
+  const bool valid = gi < n;
+  const uint32_t ri = valid ? (cand ? cand[gi] : (uint32_t)gi) : 0u;
+  const uint64_t* mine = ckeys + (int64_t)ri * W;
+  const uint64_t k0 = valid ? mine[0] : 0ull;
+  const uint64_t k1 = (valid && wact > 1) ? mine[1] : 0ull;
+  const int J = gridDim.y;
+  int64_t chunk = (n + J - 1) / J;
+  chunk = (chunk + kRankThreads - 1) / kRankThreads * kRankThreads;
+  const int64_t j0 = (int64_t)blockIdx.y * chunk;
+  const int64_t j1 = min(n, j0 + chunk);
+  uint32_t r = 0;
+  for (int64_t t = j0; t < j1; t += kRankThreads) {
+    __syncthreads();
+    const int64_t gj = t + tid;
+    if (gj < j1) {
+      const uint32_t rj = cand ? cand[gj] : (uint32_t)gj;
+      const uint64_t* other = ckeys + (int64_t)rj * W;
+      s_row[tid] = rj;
+      s_k0[tid] = other[0];
+      s_k1[tid] = wact > 1 ? other[1] : 0ull;
+    }
+    __syncthreads();
+    const int cnt = (int)min((int64_t)kRankThreads, j1 - t);
+    if (!valid) continue;
+#pragma unroll 4
+    for (int jj = 0; jj < cnt; ++jj) {
+      const uint64_t a0 = s_k0[jj];
+      if (a0 < k0) { ++r; continue; }
+      if (a0 != k0) continue;
+      const uint64_t a1 = s_k1[jj];
+      if (a1 < k1) { ++r; continue; }
+      if (a1 != k1) continue;
+      const uint32_t rj = s_row[jj];
+      int c = 0;                                   // -1: other < mine, +1: other > mine
+      const uint64_t* other = ckeys + (int64_t)rj * W;
+      for (int w = 2; w < wact && c == 0; ++w) {
+        const uint64_t a = other[w], b = mine[w];
+        c = a < b ? -1 : (a > b ? 1 : 0);
+      }
+      if (c < 0 || (c == 0 && rj < ri)) ++r;
+    }
+  }
+  if (J > 1) {
+    if (valid) atomicAdd(&rank_tmp[gi], r);
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = atomicAdd(&tile_done[blockIdx.x], 1) == J - 1;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    if (valid) r = atomicAdd(&rank_tmp[gi], 0u);
+  }
+  if (valid && (int64_t)r < m) out_rows[r] = ri;
+}
+void launch_rank_sort(const uint64_t* ckeys, int W, const int* w_dev, const uint32_t* cand, const int* nc_dev, int cand_cap,
+                      RowCount n, int64_t rows_bound, int64_t limit, uint32_t* rank_tmp, int* tile_done, uint32_t* out_rows,
+                      int* out_count, cudaStream_t s) {
+  const int tiles = (int)std::max<int64_t>(1, (rows_bound + kRankThreads - 1) / kRankThreads);
+  const int J = rank_sort_slices(rows_bound);
+  rank_sort_kernel<<<dim3(tiles, J), kRankThreads, 0, s>>>(ckeys, W, w_dev, cand, nc_dev, cand_cap, n.dev, n.host, limit, rank_tmp,
+                                                           tile_done, out_rows, out_count);
+  NDS_CUDA(cudaGetLastError());
+}
+int rank_sort_slices(int64_t rows_bound) {
+  const int64_t tiles = std::max<int64_t>(1, (rows_bound + kRankThreads - 1) / kRankThreads);
+  int64_t J = 296 / tiles;                      // about two CTAs per SM in flight
+  if (J > tiles) J = tiles;
+  if (J < 1) J = 1;
+  return (int)J;
+}
+
 __global__ void take_perm_kernel(const uint32_t* perm_a, const uint32_t* perm_b, const int* which, int widx, const int* n_dev,
                                  int64_t n_host, int64_t limit, uint32_t* out_rows, int* out_count) {
   const int64_t n = row_count(n_dev, n_host);
@@ -635,6 +902,67 @@ void launch_take_perm(const uint32_t* perm_a, const uint32_t* perm_b, const int*
 }
 
 // ------------------------------------------------------------------ result strings
+// ------------------------------------------------------------------ result export, small results
+// One launch packs a whole (small) result into one contiguous buffer, so that it reaches the host with ONE copy and
+// ONE synchronisation, row count included: block b handles segment b.
+__global__ void __launch_bounds__(256)
+export_pack_kernel(const ExportSeg* __restrict__ segs, const int* n_dev, int64_t n_host, uint8_t* __restrict__ out, int* err) {
+  const ExportSeg sg = segs[blockIdx.x];
+  const int tid = threadIdx.x;
+  const int64_t n = row_count(n_dev, n_host);
+  if (sg.kind == 2) {
+    if (tid == 0) *reinterpret_cast<int*>(out + sg.dst_off) = (int)n;
+    return;
+  }
+  if (sg.kind == 0) {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(sg.src);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(out + sg.dst_off);
+    for (int64_t i = tid; i < sg.bytes / 4; i += 256) dst[i] = src[i];
+    return;
+  }
+  // strings: Arrow offsets (null rows get length 0) by a block scan, then the bytes
+  __shared__ int wsum[8];
+  __shared__ int s_base;
+  const StrView* views = reinterpret_cast<const StrView*>(sg.src);
+  int32_t* offs = reinterpret_cast<int32_t*>(out + sg.dst_off);
+  uint8_t* chars = out + sg.aux_off;
+  const int warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) s_base = 0;
+  __syncthreads();
+  for (int64_t i0 = 0; i0 < n; i0 += 256) {
+    const int64_t i = i0 + tid;
+    int len = 0;
+    StrView v = 0;
+    if (i < n && (!sg.valid || ((sg.valid[i >> 5] >> (i & 31)) & 1u))) { v = views[i]; len = (int)(v >> 32); }
+    int incl = len;
+    for (int d = 1; d < 32; d <<= 1) {
+      const int t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+      if (lane >= d) incl += t;
+    }
+    if (lane == 31) wsum[warp] = incl;
+    __syncthreads();
+    int pre = s_base;
+    for (int w = 0; w < warp; ++w) pre += wsum[w];
+    const int start = pre + incl - len;
+    if (i < n) {
+      offs[i] = start;
+      if ((int64_t)start + len > sg.cap) { if (len) atomicExch(err, 13); }
+      else {
+        const uint8_t* p = sg.strbase + (uint32_t)v;
+        for (int b = 0; b < len; ++b) chars[start + b] = p[b];
+      }
+    }
+    __syncthreads();
+    if (tid == 255) s_base = pre + incl;
+    __syncthreads();
+  }
+  if (tid == 0) offs[n] = s_base;
+}
+void launch_export_pack(const ExportSeg* segs, int nsegs, RowCount n, uint8_t* out, int* err, cudaStream_t s) {
+  export_pack_kernel<<<nsegs, 256, 0, s>>>(segs, n.dev, n.host, out, err);
+  NDS_CUDA(cudaGetLastError());
+}
+
 __global__ void copy_str_bytes_kernel(const StrView* __restrict__ views, const uint8_t* __restrict__ base,
                                       const int64_t* __restrict__ offsets, int64_t n, uint8_t* __restrict__ out) {
   // one warp per string

@@ -101,8 +101,32 @@ void launch_radix_sort_small(const uint8_t* keybuf, int B, const int* active, Ro
                              int* which, cudaStream_t s);
 void launch_radix_sort(const uint8_t* keybuf, int B, const int* passes, int npasses, RowCount n, uint32_t* perm_a,
                        uint32_t* perm_b, int* which, uint32_t* scratch, cudaStream_t s, int* launches);
+// Sort without byte passes (see ops.cu): compacted keys (W = words per row in ckeys, w_out[0] = words in use),
+// the top-k prefilter, and the rank sort that writes out_rows[0 .. min(limit, n)) and out_count[0] directly.
+// rank_tmp: rows_bound uint32 zeros, tile_done: ceil(rows_bound / 128) int zeros (used when the range is sliced).
+constexpr int kMaxCompactBytes = 512;      // encoded key bytes per row the compact route accepts
+constexpr int kRankSortMax = 8192;         // rows (or top-k candidates) the rank sort is used for
+void launch_compact_keys(const uint8_t* keybuf, int B, const int* active, RowCount n, uint64_t* ckeys, int W, int* w_out,
+                         uint32_t* zero_rank, int* zero_tiles, int64_t zero_n, cudaStream_t s);   // also zeroes rank scratch
+constexpr int kSelectPasses = 4;           // top-k prefilter: leading bytes of word 0 examined; hist = kSelectPasses * 256 zeros
+void launch_topk_select(const uint64_t* ckeys, int W, RowCount n, int64_t k, uint32_t* cand, int cap, uint32_t* hist, int* nc_out,
+                        cudaStream_t s, int* launches);
+int rank_sort_slices(int64_t rows_bound);
+void launch_rank_sort(const uint64_t* ckeys, int W, const int* w_dev, const uint32_t* cand, const int* nc_dev, int cand_cap,
+                      RowCount n, int64_t rows_bound, int64_t limit, uint32_t* rank_tmp, int* tile_done, uint32_t* out_rows,
+                      int* out_count, cudaStream_t s);
 void launch_take_perm(const uint32_t* perm_a, const uint32_t* perm_b, const int* which, int widx, RowCount n, int64_t limit,
                       uint32_t* out_rows, int* out_count, cudaStream_t s);
+// Small-result export: segment kinds 0 = raw bytes (multiple of 4), 1 = string column -> int32 offsets at dst_off
+// and characters at aux_off (cap bytes available; error 13 if exceeded), 2 = the row count as one int.
+struct ExportSeg {
+  const void* src;
+  const uint32_t* valid;
+  const uint8_t* strbase;
+  int64_t dst_off, bytes, aux_off, cap;
+  int32_t kind, pad;
+};
+void launch_export_pack(const ExportSeg* segs, int nsegs, RowCount n, uint8_t* out, int* err, cudaStream_t s);
 void launch_copy_str_bytes(const StrView* views, const uint8_t* base, const int64_t* offsets, int64_t n, uint8_t* out,
                            cudaStream_t s);
 

@@ -221,6 +221,7 @@ void Engine::register_table(const std::string& name, const std::string& path, co
                 if (abs_off + len > 0xFFFFFFFFll) fail("string column '" + tc.name + "' exceeds 4 GiB of encoded bytes");
                 uint64_t v = ((uint64_t)len << 32) | (uint64_t)abs_off;
                 memcpy(tc.stage.data() + views_off + 8 * (int64_t)k, &v, 8);
+                tc.lt.maxlen = std::max<int>(tc.lt.maxlen, (int)std::min<uint32_t>(len, 1u << 30));
                 p += 4 + len;
               }
               di.off = views_off;
@@ -251,8 +252,19 @@ void Engine::register_table(const std::string& name, const std::string& path, co
               if (values_off > psize) fail("bad definition level length in '" + fi.path + "'");
               if (dl == 0) fail("empty definition level stream in '" + fi.path + "'");
             }
-            if (ph.encoding == pq::PLAIN) { pi.enc = 0; pi.dict = -1; }
-            else if (ph.encoding == pq::RLE_DICTIONARY || ph.encoding == pq::PLAIN_DICTIONARY) {
+            if (ph.encoding == pq::PLAIN) {
+              pi.enc = 0;
+              pi.dict = -1;
+              if (tc.phys == pq::BYTE_ARRAY) {       // longest value of the page bounds sort-key widths later
+                int64_t p = values_off;
+                while (p + 4 <= psize) {
+                  uint32_t len;
+                  memcpy(&len, payload + p, 4);
+                  tc.lt.maxlen = std::max<int>(tc.lt.maxlen, (int)std::min<uint32_t>(len, 1u << 30));
+                  p += 4 + (int64_t)len;
+                }
+              }
+            } else if (ph.encoding == pq::RLE_DICTIONARY || ph.encoding == pq::PLAIN_DICTIONARY) {
               pi.enc = 1;
               pi.dict = cur_dict;
               if (values_off >= psize) fail("dictionary-encoded page without index data in '" + fi.path + "'");
@@ -402,7 +414,11 @@ void Engine::register_arrow(const std::string& name, ArrowSchema* schema, ArrowA
       mc.lt.kind = LType::STR;
       const int32_t* offs = (const int32_t*)ca->buffers[1];
       std::vector<uint64_t> views(n);
-      for (int64_t i = 0; i < n; ++i) views[i] = ((uint64_t)(uint32_t)(offs[i + 1] - offs[i]) << 32) | (uint32_t)offs[i];
+      for (int64_t i = 0; i < n; ++i) {
+        views[i] = ((uint64_t)(uint32_t)(offs[i + 1] - offs[i]) << 32) | (uint32_t)offs[i];
+        mc.lt.maxlen = std::max<int>(mc.lt.maxlen, offs[i + 1] - offs[i]);
+      }
+      mc.lt.maxlen = std::max(mc.lt.maxlen, 1);
       mc.d_data = upload(views.data(), n * 8);
       mc.d_chars = (uint8_t*)upload(ca->buffers[2], n ? offs[n] : 0);
     } else fail("register_arrow: unsupported column format '" + f + "' for column '" + mc.name + "'");

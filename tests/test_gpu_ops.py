@@ -207,3 +207,71 @@ def test_empty_inputs(gpu_engine):
                                         'child': {'op': 'filter', 'cond': fn('gt', col('v'), lit(0)),
                                                   'child': {'op': 'scan', 'table': 'e', 'columns': ['k', 'v']}}}})
     assert got.num_rows == 0 and got.schema.names == ['k', 'sv']
+
+
+def _sort_case(gpu_engine, n, limit, pattern, keep_frac, seed):
+    """Every sort route: rank sort (<= 8192 rows, count on the device), top-k prefilter + rank sort over the
+    candidates, candidate overflow -> LSD radix, no LIMIT -> LSD radix; expected order from numpy.lexsort."""
+    rng = np.random.default_rng(seed)
+    if pattern == 'unique':
+        k1 = rng.permutation(n).astype(np.int64) - n // 2
+    elif pattern == 'ties':
+        k1 = rng.integers(0, 5, n).astype(np.int64)
+    else:                                   # 'flat': one value -> every row ties on the first key
+        k1 = np.full(n, 42, dtype=np.int64)
+    k2 = rng.integers(-1000, 1000, n).astype(np.int32)
+    words = np.array(['AAAAAAAA%08d' % v for v in rng.integers(0, 3000, n)])
+    v = rng.integers(0, 100, n).astype(np.int32)
+    rid = np.arange(n, dtype=np.int64)
+    t = pa.table({'k1': k1, 'k2': k2, 'w': pa.array(words.tolist(), type=pa.string()), 'v': v, 'rid': rid})
+    gpu_engine.register_arrow('srt', t)
+    thr = int(100 * (1 - keep_frac))
+    plan = {'op': 'sort',
+            'keys': [{'expr': col('k1')}, {'expr': col('w'), 'desc': True}, {'expr': col('k2'), 'desc': True}, {'expr': col('rid')}],
+            'child': {'op': 'filter', 'cond': fn('ge', col('v'), lit(thr)),
+                      'child': {'op': 'scan', 'table': 'srt', 'columns': ['k1', 'k2', 'w', 'v', 'rid']}}}
+    if limit is not None:
+        plan['limit'] = limit
+    got = gpu_engine.execute(plan)
+    keep = v >= thr
+    kk1, kk2, kw, krid = k1[keep], k2[keep], words[keep], rid[keep]
+    # fixed-width ASCII strings: descending order = ascending order of the negated code points
+    wcodes = np.frombuffer(''.join(kw.tolist()).encode(), dtype=np.uint8).reshape(len(kw), 16).astype(np.int16) if len(kw) else np.zeros((0, 16), np.int16)
+    lex = [krid, -kk2.astype(np.int64)] + [-wcodes[:, c] for c in range(15, -1, -1)] + [kk1]
+    order = np.lexsort(lex)
+    if limit is not None:
+        order = order[:limit]
+    assert got.num_rows == len(order)
+    assert got.column('rid').to_pylist() == krid[order].tolist()
+    assert got.column('w').to_pylist() == kw[order].tolist()
+    assert got.column('k2').to_pylist() == kk2[order].tolist()
+    gpu_engine.drop_table('srt')
+
+
+@pytest.mark.parametrize('n,limit,pattern,keep', [
+    (1, 100, 'unique', 1.0), (100, 100, 'ties', 1.0), (100, None, 'flat', 0.5), (5000, 7, 'ties', 0.5),
+    (8192, 100, 'unique', 1.0), (8192, None, 'ties', 1.0), (8193, 100, 'unique', 1.0), (8193, None, 'flat', 0.7),
+    (40000, 100, 'unique', 0.5), (40000, 100, 'ties', 1.0), (40000, 1, 'flat', 1.0), (40000, 1024, 'ties', 0.3),
+    (40000, 5000, 'unique', 1.0), (40000, None, 'unique', 0.6), (300000, 100, 'flat', 1.0), (300000, 100, 'unique', 0.9),
+    (300000, 1000, 'ties', 0.01), (20000, 100, 'unique', 0.0),
+])
+def test_sort_routes(gpu_engine, n, limit, pattern, keep):
+    _sort_case(gpu_engine, n, limit, pattern, keep, seed=n + (limit or 0))
+
+
+def test_sort_topk_candidate_overflow_falls_back(gpu_engine):
+    """More than 8192 rows tie on everything the prefilter looks at (4 leading bytes of compacted word 0): the
+    candidate list overflows and the sort must take the radix route - same answer."""
+    n = 60000
+    rng = np.random.default_rng(5)
+    hi = np.full(n, 0x0101010100000000, dtype=np.int64)    # the four leading bytes are the same for every row...
+    lo = rng.integers(0, 1 << 20, n).astype(np.int64)      # (differences only in the low 20 bits)
+    k = hi + lo
+    k[0] = 0                                               # ...except one outlier, which makes those bytes "active"
+    rid = np.arange(n, dtype=np.int64)
+    gpu_engine.register_arrow('ovf', pa.table({'k': k, 'rid': rid}))
+    got = gpu_engine.execute({'op': 'sort', 'limit': 50, 'keys': [{'expr': col('k'), 'desc': True}, {'expr': col('rid')}],
+                              'child': {'op': 'scan', 'table': 'ovf', 'columns': ['k', 'rid']}})
+    order = np.lexsort([rid, -k])[:50]
+    assert got.column('rid').to_pylist() == rid[order].tolist()
+    gpu_engine.drop_table('ovf')

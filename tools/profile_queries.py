@@ -19,6 +19,7 @@ def main():
     ap.add_argument('--queries', default='')
     ap.add_argument('--no_profile', action='store_true')
     ap.add_argument('--decode_timing', action='store_true')
+    ap.add_argument('--trace', action='store_true', help='print the host timeline (marks and sync waits) of the last rep')
     a = ap.parse_args()
     import bench
     import __graft_entry__ as entry
@@ -41,13 +42,24 @@ def main():
         plan = planner.plan_sql(qd[name])
         for rep in range(a.reps):
             t0 = time.perf_counter()
-            sess.engine.execute({'root': plan['root']}, source=None if a.source == 'hbm' else a.source, profile=not a.no_profile, decode_timing=a.decode_timing)
+            sess.engine.execute({'root': plan['root']}, source=None if a.source == 'hbm' else a.source, profile=not a.no_profile, decode_timing=a.decode_timing,
+                                options={'trace': True} if a.trace else None)
             wall = (time.perf_counter() - t0) * 1e3
             st = sess.engine.last_stats()
         print('== %s: wall %.3f ms, device %.3f ms, host(execute) %.3f ms, launches %d, h2d %d' % (name, wall, st['device_ms'], st.get('host_ms', 0), st['launches'], st['h2d_bytes']))
         for o in st['ops']:
             gbs = (o['bytes'] / (o['ms'] * 1e-3) / 1e9) if o['ms'] > 0 and o['bytes'] else 0
             print('   %-28s %9.3f ms (host %6.3f)  %12d B  %10d rows  %8.1f GB/s' % (o['op'][:28], o['ms'], o.get('host_ms', 0), o['bytes'], o['rows'], gbs))
+        if a.trace:
+            print_trace(st)
+
+
+def print_trace(st):
+    prev = 0.0
+    for label, t, wait in st.get('trace', []):
+        extra = '   waited %.3f ms' % wait if wait >= 0 else ''
+        print('      t=%8.3f ms (+%.3f)  %s%s' % (t, t - prev, label, extra))
+        prev = t
 
 
 if __name__ == '__main__':
