@@ -225,21 +225,63 @@ __device__ __forceinline__ void expand_dict(const RowsCtx& c, uint32_t tile0, ui
         }
         ce = lo;
       }
-      while (ce + 1 < c.ne && c.ek[ce + 1] <= kA) ++ce;
+      // advance the cursor: all lanes look at the next 32 run starts at once
+      for (;;) {
+        const int e = ce + 1 + lane;
+        const int adv = __popc(__ballot_sync(0xFFFFFFFFu, e < c.ne && c.ek[e] <= kA));
+        ce += adv;
+        if (adv < 32) break;
+      }
       rk1 = c.ek[ce];
       info1 = c.ep[ce];
       if (ce + 1 < c.ne) { next1 = c.ek[ce + 1]; info2 = c.ep[ce + 1]; }
       if (ce + 2 < c.ne) next2 = c.ek[ce + 2];
     }
-    uint32_t w0[8], w1[8], shv[8];
-    int stt[8];          // 0 skip, 1 zero, 2 index in w0, 3 bit-packed words in w0/w1
     const uint32_t kB = DEF ? c.s_r[be] : min(be * 32, c.n);
     const bool two_packed = c.bw && c.ne && (info1 & 1) && (next1 == 0xFFFFFFFFu || (info2 & 1)) && kB <= next2;
-    if (two_packed) {
-      // every value of the block sits in one of two bit-packed runs: bit position = base(run) + k * bw
+    if (two_packed && be == bb + 8 && be * 32 <= c.n && c.dict_count) {
+      // The common block: 256 rows, every value in one of two bit-packed runs (bit position = base(run) + k * bw).
+      // Straight-line code, no per-row state: null lanes fetch the index of the next non-null value (in range, the
+      // page is padded) and store 0.
       const uint32_t base1 = (info1 >> 1) * 8u + c.vs_mis - rk1 * c.bw;
       const uint32_t base2 = (info2 >> 1) * 8u + c.vs_mis - next1 * c.bw;
-      const bool full = be == bb + 8 && be * 32 <= c.n;
+      const uint32_t kmax = (DEF ? c.s_r[c.nw] : c.n) - 1u;      // last value index of the page (block is non-empty)
+      uint32_t ix[8];
+      bool okv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const uint32_t tcur = bb + u;
+        uint32_t k = tcur * 32 + lane;
+        okv[u] = true;
+        if (DEF) {
+          const uint32_t wv = c.s_v[tcur];
+          k = min(c.s_r[tcur] + __popc(wv & lt_mask), kmax);
+          okv[u] = (wv >> lane) & 1u;
+        }
+        const uint32_t bit = (k >= next1 ? base2 : base1) + k * c.bw;
+        const uint32_t* wp = c.vwords + (bit >> 5);
+        ix[u] = __funnelshift_r(__ldg(wp), __ldg(wp + 1), bit & 31) & c.bwmask;
+      }
+      bool bad = false;
+      const int64_t row_base = c.orow + (int64_t)bb * 32 + lane;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        bad |= okv[u] && ix[u] >= c.dict_count;
+        const uint32_t j = min(ix[u], c.dict_count - 1u);
+        int64_t v;
+        if (SDICT) v = W == 4 ? (int64_t)(int32_t)lds32(c.dict_s + j * 4u) : lds64(c.dict_s + j * 8u);
+        else v = W == 4 ? (int64_t)__ldg(reinterpret_cast<const int32_t*>(c.dict) + j) : __ldg(reinterpret_cast<const int64_t*>(c.dict) + j);
+        store_out<W>(c.out, row_base + u * 32, okv[u] ? v : 0);
+      }
+      if (bad && c.err) atomicExch(c.err, 6);
+      continue;
+    }
+    uint32_t w0[8], w1[8], shv[8];
+    int stt[8];          // 0 skip, 1 zero, 2 index in w0, 3 bit-packed words in w0/w1
+    if (two_packed) {
+      // partial block (page tail): same addressing, bounds checked per row
+      const uint32_t base1 = (info1 >> 1) * 8u + c.vs_mis - rk1 * c.bw;
+      const uint32_t base2 = (info2 >> 1) * 8u + c.vs_mis - next1 * c.bw;
 #pragma unroll
       for (int u = 0; u < 8; ++u) {
         const uint32_t tcur = bb + u;
@@ -247,7 +289,7 @@ __device__ __forceinline__ void expand_dict(const RowsCtx& c, uint32_t tile0, ui
         w0[u] = 0;
         w1[u] = 0;
         shv[u] = 0;
-        if (full || (tcur < be && tcur * 32 + lane < c.n)) {
+        if (tcur < be && tcur * 32 + lane < c.n) {
           uint32_t k = tcur * 32 + lane;
           bool ok = true;
           if (DEF) {

@@ -152,6 +152,7 @@ class Engine {
   void register_arrow(const std::string& name, ArrowSchema* schema, ArrowArray* array);
   void drop_table(const std::string& name);
   void execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_array);
+  void execute_once(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_array, bool speculate);
   std::string stats_json() const;
   std::string table_info_json(const std::string& name) const;
 
@@ -162,6 +163,7 @@ class Engine {
  private:
   friend struct Exec;
   cudaStream_t stream_ = nullptr;
+  std::vector<cudaStream_t> side_streams_;   // build sides and base scan of a join chain run side by side (exec.cu: enter_side / leave_side)
   bool resident_ = true, keep_host_ = false;
   std::map<std::string, Table> tables_;
   std::vector<OpStat> stats_;
@@ -174,6 +176,8 @@ class Engine {
   int64_t pin_cap_ = 0;
   uint8_t* slab_ = nullptr;     // device slab behind the per-query bump allocator
   int64_t slab_cap_ = 0;
+  int64_t spec_retries_ = 0;    // queries re-run because a device-side size assumption failed (stats: speculation_retries)
+  int64_t zero_dirty_ = -1;     // bytes of the slab's zeroed prefix the last query used (-1: unknown)
   std::vector<cudaEvent_t> event_pool_;
   cudaEvent_t get_event();
   void put_event(cudaEvent_t e);

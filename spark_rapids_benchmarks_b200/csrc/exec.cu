@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <memory>
 #include <unordered_set>
 #include "engine.h"
 
@@ -24,13 +25,17 @@ struct Arena {
   uint8_t* pin = nullptr;       // pinned staging ring owned by the engine (reset per query)
   int64_t pin_cap = 0, pin_off = 0;
   explicit Arena(cudaStream_t st) : s(st) {}
-  void attach_slab(uint8_t* p, int64_t cap) {
+  // The first zero_cap bytes of the slab are kept zero between queries: a query hands out pieces of it (zeros())
+  // instead of issuing a memset per bitmap / counter / hash table, and the next query re-zeroes only the part the
+  // previous one used (dirty; negative = unknown, clear everything).
+  void attach_slab(uint8_t* p, int64_t cap, int64_t dirty) {
     slab = p;
     slab_cap = cap;
-    zero_cap = p ? std::min<int64_t>(cap / 4, 256 << 10) : 0;
+    zero_cap = p ? std::min<int64_t>(cap / 4, int64_t(32) << 20) : 0;
     zero_off = 0;
     slab_off = zero_cap;
-    if (zero_cap) NDS_CUDA(cudaMemsetAsync(slab, 0, (size_t)zero_cap, s));
+    const int64_t clear = dirty < 0 ? zero_cap : std::min(dirty, zero_cap);
+    if (clear > 0) NDS_CUDA(cudaMemsetAsync(slab, 0, (size_t)clear, s));
   }
   void* alloc(int64_t bytes) {
     if (bytes < 16) bytes = 16;
@@ -51,7 +56,7 @@ struct Arena {
   T* zeros(int64_t n) {
     const int64_t bytes = std::max<int64_t>(n, 1) * (int64_t)sizeof(T);
     const int64_t need = align_up(bytes, 16);
-    if (need <= 4096 && zero_off + need <= zero_cap) {
+    if (need <= (int64_t(4) << 20) && zero_off + need <= zero_cap) {
       T* p = reinterpret_cast<T*>(slab + zero_off);
       zero_off += need;
       return p;
@@ -174,30 +179,47 @@ struct Blob {
 
 struct RuntimeFilter {           // dynamic partition pruning: build-side join keys
   std::string column;
-  // a bitmap over [lo, hi] when the key range is small (surrogate keys are dense), else a sorted list
-  int64_t lo = 0, hi = -1;
-  std::vector<uint64_t> bits;
-  std::vector<int64_t> sorted;
+  // The keys travel to the host asynchronously (pinned memory + an event); the scan that uses the filter waits for
+  // the event, so build sides issued in between keep the GPU busy instead of stalling behind a stream sync.
+  struct State {
+    bool ready = false;
+    cudaEvent_t ev = nullptr;
+    const uint8_t* hk = nullptr;        // keys of the upper-bound row range
+    const uint32_t* hv = nullptr;       // their validity words
+    const int* hcount = nullptr;        // exact row count
+    int64_t nb = 0;
+    bool is32 = false;
+    std::vector<uint8_t> pageable;      // backing store when the pinned ring is full
+    // a bitmap over [lo, hi] when the key range is small (surrogate keys are dense), else a sorted list
+    int64_t lo = 0, hi = -1;
+    std::vector<uint64_t> bits;
+    std::vector<int64_t> sorted;
+  };
+  std::shared_ptr<State> st;
   void assign(std::vector<int64_t>& k) {
+    State& t = *st;
     if (k.empty()) return;
-    lo = hi = k[0];
-    for (int64_t v : k) { lo = std::min(lo, v); hi = std::max(hi, v); }
-    if (hi - lo < (int64_t(1) << 26)) {
-      bits.assign((size_t)((hi - lo) / 64 + 1), 0);
-      for (int64_t v : k) bits[(size_t)((v - lo) >> 6)] |= uint64_t(1) << ((v - lo) & 63);
+    t.lo = t.hi = k[0];
+    for (int64_t v : k) { t.lo = std::min(t.lo, v); t.hi = std::max(t.hi, v); }
+    if (t.hi - t.lo < (int64_t(1) << 26)) {
+      t.bits.assign((size_t)((t.hi - t.lo) / 64 + 1), 0);
+      for (int64_t v : k) t.bits[(size_t)((v - t.lo) >> 6)] |= uint64_t(1) << ((v - t.lo) & 63);
     } else {
       std::sort(k.begin(), k.end());
-      sorted.swap(k);
+      t.sorted.swap(k);
     }
   }
   bool contains(int64_t v) const {
-    if (v < lo || v > hi) return false;
-    if (!bits.empty()) return (bits[(size_t)((v - lo) >> 6)] >> ((v - lo) & 63)) & 1;
-    return std::binary_search(sorted.begin(), sorted.end(), v);
+    const State& t = *st;
+    if (v < t.lo || v > t.hi) return false;
+    if (!t.bits.empty()) return (t.bits[(size_t)((v - t.lo) >> 6)] >> ((v - t.lo) & 63)) & 1;
+    return std::binary_search(t.sorted.begin(), t.sorted.end(), v);
   }
 };
 
 }  // namespace
+
+struct SpeculationFailed {};     // a device-side size assumption did not hold; Engine::execute re-runs the plan without them
 
 struct Exec {
   Engine& e;
@@ -208,6 +230,8 @@ struct Exec {
   bool profile = false;
   bool decode_timing = false;
   bool split_decode = true;      // options.split_decode=false forces every page through the general kernel
+  bool side_stream = true;       // options.side_stream=false keeps every operator on one stream
+  bool speculate = true;         // options.speculate=false: never size a launch on an unverified device-side count
   bool trace = false;            // options.trace: host timeline marks + time spent waiting in each stream sync
   double t_base = 0;
   std::string trace_out;
@@ -218,7 +242,8 @@ struct Exec {
   Exec(Engine& en, const Json* options) : e(en), ar(en.stream_), s(en.stream_) {
     ar.pin = en.pin_;
     ar.pin_cap = en.pin_cap_;
-    ar.attach_slab(en.slab_, en.slab_cap_);
+    ar.attach_slab(en.slab_, en.slab_cap_, en.zero_dirty_);
+    en.zero_dirty_ = -1;          // until this query ends in an orderly way
     err = ar.zeros<int>(4);
     if (options) {
       source_host = options->str_or("source", "hbm") == "host";
@@ -226,8 +251,14 @@ struct Exec {
       decode_timing = options->bool_or("decode_timing", false);
       split_decode = options->bool_or("split_decode", true);
       trace = options->bool_or("trace", false);
+      side_stream = options->bool_or("side_stream", true);
+      speculate = options->bool_or("speculate", true);
     }
     t_base = now_ms();
+    if (!e.side_streams_.empty() && side_stream) {
+      ev_start = e.get_event();
+      NDS_CUDA(cudaEventRecord(ev_start, s));
+    }
   }
 
   void mark(const char* label, double wait_ms = -1) {
@@ -245,6 +276,12 @@ struct Exec {
   }
 
   ~Exec() {     // a failed query still returns its timing events to the pool
+    e.zero_dirty_ = ar.zero_off;
+    if (s_saved) { cudaStreamSynchronize(s); s = s_saved; ar.s = s; }     // failed inside a side-stream section
+    if (ev_start) e.put_event(ev_start);
+    for (cudaEvent_t ev : side_events) e.put_event(ev);
+    for (auto& st : rf_states)
+      if (st->ev) { e.put_event(st->ev); st->ev = nullptr; }     // a filter no scan asked for
     for (OpStat& st : stats) {
       if (st.e0) e.put_event(st.e0);
       if (st.e1) e.put_event(st.e1);
@@ -286,9 +323,59 @@ struct Exec {
     if (h[0]) fail("device kernel reported error code " + std::to_string(h[0]) +
                    " (3-6: malformed parquet page, 11: string projection outside its column buffer, 12: sort key wider than its declared maximum, 13: result string "
                    "longer than its column's known maximum)");
+    if (h[2]) throw SpeculationFailed();
     if (h[1] & 1) fail("hash join: duplicate keys on the build side (only unique build keys are supported)");
     if (h[1] & 2) fail("hash join: key equals the reserved empty marker");
   }
+
+  // ---- dynamic partition pruning: wait for the build keys (usually long since on the host) and index them
+  void resolve(const RuntimeFilter& rf) {
+    RuntimeFilter::State& t = *rf.st;
+    if (t.ready) return;
+    if (t.ev) {
+      mark("wait:prune_keys");
+      const double t0 = now_ms();
+      NDS_CUDA(cudaEventSynchronize(t.ev));
+      mark("wait_done", now_ms() - t0);
+      e.put_event(t.ev);
+      t.ev = nullptr;
+    }
+    int64_t hcount = std::min<int64_t>(*t.hcount, t.nb);
+    std::vector<int64_t> keys;
+    keys.reserve((size_t)std::max<int64_t>(hcount, 0));
+    for (int64_t i = 0; i < hcount; ++i)
+      if ((t.hv[i >> 5] >> (i & 31)) & 1u)
+        keys.push_back(t.is32 ? (int64_t) reinterpret_cast<const int32_t*>(t.hk)[i] : reinterpret_cast<const int64_t*>(t.hk)[i]);
+    const_cast<RuntimeFilter&>(rf).assign(keys);
+    t.ready = true;
+  }
+
+  // ---- second stream: the probe-side scan of a join chain runs beside the build sides
+  cudaStream_t s_saved = nullptr;
+  std::vector<cudaEvent_t> side_events;
+  std::vector<std::shared_ptr<RuntimeFilter::State>> rf_states;
+  void enter_side(int which) {
+    if (e.side_streams_.empty() || s_saved || !ev_start) return;
+    // a subtree made of scans/filters/builds reads registered table bytes and its own allocations only: all it must
+    // wait for is the arena's zeroed prefix (ev_start, recorded when the query began) - not what the main stream
+    // queued since
+    cudaStream_t side = e.side_streams_[(size_t)which % e.side_streams_.size()];
+    NDS_CUDA(cudaStreamWaitEvent(side, ev_start, 0));
+    s_saved = s;
+    s = side;
+    ar.s = s;
+  }
+  void leave_side() {
+    if (!s_saved) return;
+    cudaEvent_t ev = e.get_event();
+    NDS_CUDA(cudaEventRecord(ev, s));
+    side_events.push_back(ev);
+    s = s_saved;
+    ar.s = s;
+    s_saved = nullptr;
+    NDS_CUDA(cudaStreamWaitEvent(s, ev, 0));
+  }
+  cudaEvent_t ev_start = nullptr;
 
   int64_t count(Batch& b) {
     if (b.n_exact >= 0) return b.n_exact;
@@ -535,6 +622,7 @@ struct Exec {
     const RuntimeFilter* rf = nullptr;
     for (const RuntimeFilter& f : filters)
       if (f.column == t.part_col && !t.part_col.empty()) rf = &f;
+    if (rf) resolve(*rf);
     std::vector<int> sel;
     std::vector<int64_t> row_start;
     int64_t N = 0;
@@ -928,37 +1016,42 @@ struct Exec {
       Column flat = eval_to_column(kexpr, bk, build, nullptr, build.rc());
       RuntimeFilter rf;
       rf.column = bs.pk;
+      rf.st = std::make_shared<RuntimeFilter::State>();
+      RuntimeFilter::State& t = *rf.st;
       if (nb > 0) {
-        // keys of the upper-bound row range and the exact count come back in one synchronisation
-        const bool is32 = flat.lt.dtype() == DT_I32;
-        const int64_t kbytes = nb * (is32 ? 4 : 8), vbytes = ((nb + 31) / 32) * 4;
-        std::vector<uint8_t> pageable;
+        // keys of the upper-bound row range and the exact count: copies queued now, read when the scan needs them
+        t.is32 = flat.lt.dtype() == DT_I32;
+        t.nb = nb;
+        const int64_t kbytes = nb * (t.is32 ? 4 : 8), vbytes = ((nb + 31) / 32) * 4;
         uint8_t* hbuf = ar.pin_take(kbytes + vbytes + 16);
-        if (!hbuf) { pageable.resize((size_t)(kbytes + vbytes + 16)); hbuf = pageable.data(); }
-        const int64_t off_v = align_up(kbytes, 8), off_c = off_v + vbytes;
-        const uint8_t* hk = hbuf;
-        const uint32_t* hv = reinterpret_cast<const uint32_t*>(hbuf + off_v);
-        int* hcount_p = reinterpret_cast<int*>(hbuf + align_up(off_c, 4));
-        *hcount_p = (int)nb;
+        if (!hbuf) { t.pageable.resize((size_t)(kbytes + vbytes + 16)); hbuf = t.pageable.data(); }
+        const int64_t off_v = align_up(kbytes, 8), off_c = align_up(off_v + vbytes, 4);
+        t.hk = hbuf;
+        t.hv = reinterpret_cast<const uint32_t*>(hbuf + off_v);
+        int* hcount_p = reinterpret_cast<int*>(hbuf + off_c);
+        *hcount_p = build.n_exact >= 0 ? (int)build.n_exact : (int)nb;
+        t.hcount = hcount_p;
         NDS_CUDA(cudaMemcpyAsync(hbuf, flat.data, (size_t)kbytes, cudaMemcpyDeviceToHost, s));
         NDS_CUDA(cudaMemcpyAsync(hbuf + off_v, flat.valid, (size_t)vbytes, cudaMemcpyDeviceToHost, s));
         if (build.n_dev && build.n_exact < 0) NDS_CUDA(cudaMemcpyAsync(hcount_p, build.n_dev, 4, cudaMemcpyDeviceToHost, s));
-        sync("sync:build_keys");
+        t.ev = e.get_event();
+        NDS_CUDA(cudaEventRecord(t.ev, s));
+        rf_states.push_back(rf.st);
         d2h += kbytes + vbytes + 4;
-        int hcount = *hcount_p;
-        if (build.n_exact >= 0) hcount = (int)build.n_exact;
-        if (hcount > nb) hcount = (int)nb;
-        build.n_exact = hcount;
-        std::vector<int64_t> keys;
-        keys.reserve((size_t)hcount);
-        for (int64_t i = 0; i < hcount; ++i)
-          if ((hv[i >> 5] >> (i & 31)) & 1u)
-            keys.push_back(is32 ? (int64_t) reinterpret_cast<const int32_t*>(hk)[i] : reinterpret_cast<const int64_t*>(hk)[i]);
-        rf.assign(keys);
+      } else {
+        t.ready = true;
       }
       down.push_back(std::move(rf));
     }
     return bs;
+  }
+
+  // scans, filters and projections only: such a subtree reads nothing another operator of the query produces
+  static bool independent_subtree(const Json& node) {
+    const std::string& op = node.str("op");
+    if (op == "scan") return true;
+    if (op == "filter" || op == "project") return independent_subtree(node.at("child"));
+    return false;
   }
 
   // column names a plan subtree produces (static; used to decide whether a join chain can be fused)
@@ -1026,9 +1119,25 @@ struct Exec {
     // ---- fused: all build sides first (their partition filters reach the base scan), then one probe pass
     std::vector<RuntimeFilter> down = filters;
     std::vector<BuiltSide> sides;
-    sides.reserve(chain.size());
-    for (const Json* j : chain) sides.push_back(build_side(*j, down));
+    // build sides that prune the base scan's partitions go first: their keys are on the way to the host while the
+    // other build sides are issued
+    // Neither the build sides nor the base scan depend on one another: each runs on a stream of its own (round
+    // robin over the engine's side streams) and the main stream waits for all of them before the probe pass. Their
+    // kernels are small-grid and latency-bound, so they overlap almost completely.
+    sides.resize(chain.size());
+    int lane_no = 0;
+    for (int pass = 0; pass < 2; ++pass)
+      for (size_t j = 0; j < chain.size(); ++j)
+        if (chain[j]->bool_or("prune_partitions", false) == (pass == 0)) {
+          const bool side = side_stream && independent_subtree(chain[j]->at("build"));
+          if (side) enter_side(lane_no++);
+          sides[j] = build_side(*chain[j], down);
+          if (side) leave_side();
+        }
+    const bool side = side_stream && independent_subtree(base_node);
+    if (side) enter_side(lane_no++);
     Batch base = exec(base_node, down);
+    if (side) leave_side();
     size_t stp = begin_stat("join_probe_chain");
     RowCount np = base.rc();
     ProbeChain pc;
@@ -1083,7 +1192,13 @@ struct Exec {
     const int nkeys = (int)jkeys.a.size(), naggs = (int)jaggs.a.size();
     if (nkeys > kMaxGroupKeys) fail("plan: more than " + std::to_string(kMaxGroupKeys) + " group-by keys");
     if (nkeys == 0) fail("plan: aggregation without group-by keys is not supported yet");
-    int64_t n = count(in);
+    // Row count of the input: exact if already known; otherwise its upper bound, with the table sized on the device
+    // (ops.cu, agg_capacity) - unless that would reserve more than kAggReserveMax bytes, then one host round trip.
+    constexpr int64_t kAggReserveMax = int64_t(6) << 30;
+    int64_t n = in.rc().host;
+    if (in.n_dev && in.n_exact < 0 &&
+        (int64_t)agg_capacity_for(n) * (4 + 16 * (int64_t)std::max(naggs, 1)) + n * 8 * (int64_t)std::max(naggs, 1) > kAggReserveMax)
+      n = count(in);
     size_t st = begin_stat("aggregate");
     Blob bb;
     std::vector<LType> ktypes, atypes;
@@ -1138,22 +1253,19 @@ struct Exec {
     }
     Blob::Dev dev = bb.upload(ar, s, specs.data(), (int64_t)specs.size() * sizeof(AggSpec));
     const AggSpec* d_specs = reinterpret_cast<const AggSpec*>(dev.extra);
-    const uint32_t cap = next_pow2(2 * n);
-    uint32_t* slots = ar.zeros<uint32_t>(cap);
-    int64_t* acc = ar.zeros<int64_t>((int64_t)cap * std::max(naggs, 1));
-    int64_t* cnt = ar.zeros<int64_t>((int64_t)cap * std::max(naggs, 1));
-    for (int a = 0; a < naggs; ++a) {
-      if (specs[a].fn == AGG_MIN_I) { launch_fill_i64(acc + (int64_t)a * cap, INT64_MAX, cap, s); ++launches; }
-      if (specs[a].fn == AGG_MAX_I) { launch_fill_i64(acc + (int64_t)a * cap, INT64_MIN, cap, s); ++launches; }
-    }
-    launch_agg_insert(dev.progs, nkeys, d_specs, naggs, dev.ctx, in.rc(), slots, cap - 1, acc, cnt, s);
+    const uint32_t cap = agg_capacity_for(n);
+    uint32_t* slots = ar.alloc_n<uint32_t>(cap);
+    int64_t* acc = ar.alloc_n<int64_t>((int64_t)cap * std::max(naggs, 1));
+    int64_t* cnt = ar.alloc_n<int64_t>((int64_t)cap * std::max(naggs, 1));
     const int64_t vwords = (n + 31) / 32 + 1;
     uint32_t* rep = ar.alloc_n<uint32_t>(n);
     int64_t* ovals = ar.alloc_n<int64_t>(n * std::max(naggs, 1));
-    uint32_t* ovalid = ar.zeros<uint32_t>(vwords * std::max(naggs, 1));
+    uint32_t* ovalid = ar.alloc_n<uint32_t>(vwords * std::max(naggs, 1));
     int* ng = ar.zeros<int>(1);
-    launch_agg_finalize(d_specs, naggs, slots, cap, acc, cnt, rep, ovals, ovalid, n, vwords, ng, s);
-    launches += 2;
+    launch_agg_init(d_specs, naggs, in.rc(), cap, slots, acc, cnt, ovalid, vwords, s);
+    launch_agg_insert(dev.progs, nkeys, d_specs, naggs, dev.ctx, in.rc(), slots, cap, acc, cnt, s);
+    launch_agg_finalize(d_specs, naggs, slots, cap, in.rc(), acc, cnt, rep, ovals, ovalid, n, vwords, ng, s);
+    launches += 3;
     out.n_max = n;
     out.n_dev = ng;
     RowCount nout{ng, n};
@@ -1249,7 +1361,7 @@ struct Exec {
         ++launches;
         if (direct) {
           // no host round trip at all: the row count stays on the device
-          launch_rank_sort(ckeys, W, wact, nullptr, nullptr, 0, rc, nb, limit, rank_tmp, tile_done, rows, out_count, s);
+          launch_rank_sort(ckeys, W, wact, nullptr, nullptr, 0, rc, nb, limit, rank_tmp, tile_done, rows, out_count, err + 2, s);
           ++launches;
           done = true;
         } else {
@@ -1259,19 +1371,30 @@ struct Exec {
           int l = 0;
           launch_topk_select(ckeys, W, rc, limit, cand, kRankSortMax, hist, nc_dev, s, &l);
           launches += l;
-          int hv[2] = {0, (int)nb};
-          NDS_CUDA(cudaMemcpyAsync(&hv[0], nc_dev, 4, cudaMemcpyDeviceToHost, s));
-          if (in.n_dev && in.n_exact < 0) NDS_CUDA(cudaMemcpyAsync(&hv[1], in.n_dev, 4, cudaMemcpyDeviceToHost, s));
-          sync("sync:sort_topk");
-          d2h += 8;
-          if (in.n_exact < 0) in.n_exact = std::min<int64_t>(hv[1], in.n_max);
-          if (hv[0] <= kRankSortMax) {
-            const int64_t ncand = std::max(hv[0], 1);
-            uint32_t* rt = ar.zeros<uint32_t>(ncand);
-            int* td = ar.zeros<int>((ncand + 127) / 128);
-            launch_rank_sort(ckeys, W, wact, cand, nc_dev, kRankSortMax, in.rc(), ncand, limit, rt, td, rows, out_count, s);
+          if (speculate) {
+            // no host round trip: the rank sort is sized for the candidate list's capacity; should the list overflow
+            // (more than kRankSortMax rows tie on the selected prefix) err[2] is raised and the query runs again
+            // without speculation
+            uint32_t* rt = ar.zeros<uint32_t>(kRankSortMax);
+            int* td = ar.zeros<int>(kRankSortMax / 128);
+            launch_rank_sort(ckeys, W, wact, cand, nc_dev, kRankSortMax, rc, kRankSortMax, limit, rt, td, rows, out_count, err + 2, s);
             ++launches;
             done = true;
+          } else {
+            int hv[2] = {0, (int)nb};
+            NDS_CUDA(cudaMemcpyAsync(&hv[0], nc_dev, 4, cudaMemcpyDeviceToHost, s));
+            if (in.n_dev && in.n_exact < 0) NDS_CUDA(cudaMemcpyAsync(&hv[1], in.n_dev, 4, cudaMemcpyDeviceToHost, s));
+            sync("sync:sort_topk");
+            d2h += 8;
+            if (in.n_exact < 0) in.n_exact = std::min<int64_t>(hv[1], in.n_max);
+            if (hv[0] <= kRankSortMax) {
+              const int64_t ncand = std::max(hv[0], 1);
+              uint32_t* rt = ar.zeros<uint32_t>(ncand);
+              int* td = ar.zeros<int>((ncand + 127) / 128);
+              launch_rank_sort(ckeys, W, wact, cand, nc_dev, kRankSortMax, in.rc(), ncand, limit, rt, td, rows, out_count, nullptr, s);
+              ++launches;
+              done = true;
+            }
           }
         }
       }
@@ -1380,6 +1503,15 @@ void release_array_child(ArrowArray* a) { if (a) a->release = nullptr; }
 }  // namespace
 
 void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_array) {
+  try {
+    execute_once(plan, out_schema, out_array, true);
+  } catch (const SpeculationFailed&) {
+    ++spec_retries_;
+    execute_once(plan, out_schema, out_array, false);
+  }
+}
+
+void Engine::execute_once(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_array, bool speculate) {
   const double t_exec0 = Exec::now_ms();
   NDS_CUDA(cudaSetDevice(device));
   const Json* options = plan.find("options");
@@ -1389,6 +1521,7 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
   std::vector<OpStat> op_stats;
   {
     Exec ex(*this, options);
+    if (!speculate) ex.speculate = false;
     std::vector<RuntimeFilter> none;
     Batch res = ex.exec(root, none);
     ex.mark("plan_issued");
@@ -1673,7 +1806,7 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
 std::string Engine::stats_json() const {
   std::string s = "{\"launches\":" + std::to_string(launches_) + ",\"device_ms\":" + std::to_string(exec_ms_) + ",\"host_ms\":" + std::to_string(host_ms_) +
                   ",\"h2d_bytes\":" + std::to_string(h2d_bytes_) + ",\"d2h_bytes\":" + std::to_string(d2h_bytes_) +
-                  ",\"trace\":[" + trace_ + "],\"ops\":[";
+                  ",\"speculation_retries\":" + std::to_string(spec_retries_) + ",\"trace\":[" + trace_ + "],\"ops\":[";
   for (size_t i = 0; i < stats_.size(); ++i) {
     if (i) s += ",";
     s += "{\"op\":\"" + json_escape(stats_[i].op) + "\",\"ms\":" + std::to_string(stats_[i].ms) + ",\"bytes\":" +
@@ -1698,6 +1831,11 @@ Engine::Engine(const Json& cfg) {
   if (device >= ndev) fail("engine config: device " + std::to_string(device) + " does not exist");
   NDS_CUDA(cudaSetDevice(device));
   NDS_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+  for (int k = 0; k < 6; ++k) {
+    cudaStream_t st;
+    NDS_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    side_streams_.push_back(st);
+  }
   cudaMemPool_t pool;
   NDS_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
   uint64_t thr = UINT64_MAX;
@@ -1734,6 +1872,7 @@ Engine::~Engine() {
   std::vector<std::string> names;
   for (auto& kv : tables_) names.push_back(kv.first);
   for (auto& n : names) drop_table(n);
+  for (cudaStream_t st : side_streams_) cudaStreamDestroy(st);
   if (stream_) cudaStreamDestroy(stream_);
   if (pin_) cudaFreeHost(pin_);
   if (slab_) cudaFree(slab_);

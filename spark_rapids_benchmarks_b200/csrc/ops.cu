@@ -257,6 +257,36 @@ void launch_join_probe(ColRef key, RowCount n, HashTable ht, uint32_t* out_probe
 }
 
 // ------------------------------------------------------------------ hash group-by
+// The table is ALLOCATED for the upper bound of the input rows (cap_max slots) but SIZED on the device from the actual
+// row count: every kernel derives the same power-of-two capacity from n, so only that part is cleared, probed and
+// compacted, and the host never waits for the count of the join below.
+__host__ __device__ __forceinline__ uint32_t agg_capacity(int64_t n, uint32_t cap_max) {
+  uint32_t c = 64;
+  while ((int64_t)c < 2 * n && c < cap_max) c <<= 1;
+  return c < cap_max ? c : cap_max;
+}
+uint32_t agg_capacity_for(int64_t n_bound) {
+  uint32_t c = 64;
+  while ((int64_t)c < 2 * n_bound && c < (1u << 31)) c <<= 1;
+  return c;
+}
+
+__global__ void __launch_bounds__(kThreads)
+agg_init_kernel(const AggSpec* __restrict__ aggs, int naggs, const int* n_dev, int64_t n_host, uint32_t cap_max, uint32_t* slots,
+                int64_t* acc, int64_t* cnt, uint32_t* out_valid, int64_t valid_stride_words) {
+  const int64_t n = row_count(n_dev, n_host);
+  const uint64_t cap = agg_capacity(n, cap_max);
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t t0 = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  for (int64_t i = t0; i < (int64_t)cap; i += stride) slots[i] = 0;
+  for (int a = 0; a < naggs; ++a) {
+    const int fn = aggs[a].fn;
+    const int64_t init = fn == AGG_MIN_I ? INT64_MAX : (fn == AGG_MAX_I ? INT64_MIN : 0);
+    for (int64_t i = t0; i < (int64_t)cap; i += stride) { acc[a * cap + i] = init; cnt[a * cap + i] = 0; }
+    const int64_t vw = min((n + 31) / 32 + 1, valid_stride_words);
+    for (int64_t i = t0; i < vw; i += stride) out_valid[a * valid_stride_words + i] = 0;
+  }
+}
 // slots[s] = representative batch row + 1 (0 = empty). Key equality is decided by re-evaluating the key
 // expressions at the representative row, so no key columns are stored in the table.
 __device__ __forceinline__ bool val_equal(const Val& a, const Val& b, int kind) {
@@ -275,9 +305,10 @@ __device__ __forceinline__ bool val_equal(const Val& a, const Val& b, int kind) 
 
 __global__ void __launch_bounds__(kThreads)
 agg_insert_kernel(const Prog* __restrict__ progs, int nkeys, const AggSpec* __restrict__ aggs, int naggs, OpCtx c,
-                  const int* n_dev, int64_t n_host, uint32_t* slots, uint32_t mask, int64_t* acc, int64_t* cnt) {
+                  const int* n_dev, int64_t n_host, uint32_t* slots, uint32_t cap_max, int64_t* acc, int64_t* cnt) {
   const int64_t n = row_count(n_dev, n_host);
-  const uint64_t cap = (uint64_t)mask + 1;
+  const uint64_t cap = agg_capacity(n, cap_max);
+  const uint32_t mask = (uint32_t)cap - 1u;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     Val mine[kMaxGroupKeys];
     uint64_t h = 0x9E3779B97F4A7C15ULL;
@@ -316,10 +347,11 @@ agg_insert_kernel(const Prog* __restrict__ progs, int nkeys, const AggSpec* __re
 
 // Compacts occupied slots into group rows. out_vals[a * out_stride + g], out_valid[a * valid_stride_words + g/32].
 __global__ void __launch_bounds__(kThreads)
-agg_finalize_kernel(const AggSpec* __restrict__ aggs, int naggs, const uint32_t* __restrict__ slots, uint32_t cap,
-                    const int64_t* __restrict__ acc, const int64_t* __restrict__ cnt, uint32_t* __restrict__ rep_out,
-                    int64_t* __restrict__ out_vals, uint32_t* out_valid, int64_t out_stride, int64_t valid_stride_words,
-                    int* ngroups) {
+agg_finalize_kernel(const AggSpec* __restrict__ aggs, int naggs, const uint32_t* __restrict__ slots, uint32_t cap_max,
+                    const int* n_dev, int64_t n_host, const int64_t* __restrict__ acc, const int64_t* __restrict__ cnt,
+                    uint32_t* __restrict__ rep_out, int64_t* __restrict__ out_vals, uint32_t* out_valid, int64_t out_stride,
+                    int64_t valid_stride_words, int* ngroups) {
+  const uint32_t cap = agg_capacity(row_count(n_dev, n_host), cap_max);
   const uint32_t capround = (cap + 31u) & ~31u;
   for (uint32_t s = blockIdx.x * blockDim.x + threadIdx.x; s < capround; s += gridDim.x * blockDim.x) {
     uint32_t rep = s < cap ? slots[s] : 0u;
@@ -337,16 +369,24 @@ agg_finalize_kernel(const AggSpec* __restrict__ aggs, int naggs, const uint32_t*
   }
 }
 
-void launch_agg_insert(const Prog* progs, int nkeys, const AggSpec* aggs, int naggs, OpCtx c, RowCount n, uint32_t* slots,
-                       uint32_t mask, int64_t* acc, int64_t* cnt, cudaStream_t s) {
-  agg_insert_kernel<<<grid_for(n.host), kThreads, 0, s>>>(progs, nkeys, aggs, naggs, c, n.dev, n.host, slots, mask, acc, cnt);
+void launch_agg_init(const AggSpec* aggs, int naggs, RowCount n, uint32_t cap_max, uint32_t* slots, int64_t* acc, int64_t* cnt,
+                     uint32_t* out_valid, int64_t valid_stride_words, cudaStream_t s) {
+  const int64_t work = (int64_t)agg_capacity(n.host, cap_max) * std::max(naggs, 1);
+  agg_init_kernel<<<grid_for(work), kThreads, 0, s>>>(aggs, naggs, n.dev, n.host, cap_max, slots, acc, cnt, out_valid,
+                                                      valid_stride_words);
   NDS_CUDA(cudaGetLastError());
 }
-void launch_agg_finalize(const AggSpec* aggs, int naggs, const uint32_t* slots, uint32_t cap, const int64_t* acc,
+void launch_agg_insert(const Prog* progs, int nkeys, const AggSpec* aggs, int naggs, OpCtx c, RowCount n, uint32_t* slots,
+                       uint32_t cap_max, int64_t* acc, int64_t* cnt, cudaStream_t s) {
+  agg_insert_kernel<<<grid_for(n.host), kThreads, 0, s>>>(progs, nkeys, aggs, naggs, c, n.dev, n.host, slots, cap_max, acc, cnt);
+  NDS_CUDA(cudaGetLastError());
+}
+void launch_agg_finalize(const AggSpec* aggs, int naggs, const uint32_t* slots, uint32_t cap_max, RowCount n, const int64_t* acc,
                          const int64_t* cnt, uint32_t* rep_out, int64_t* out_vals, uint32_t* out_valid, int64_t out_stride,
                          int64_t valid_stride_words, int* ngroups, cudaStream_t s) {
-  agg_finalize_kernel<<<grid_for(cap), kThreads, 0, s>>>(aggs, naggs, slots, cap, acc, cnt, rep_out, out_vals, out_valid,
-                                                         out_stride, valid_stride_words, ngroups);
+  agg_finalize_kernel<<<grid_for(agg_capacity(n.host, cap_max)), kThreads, 0, s>>>(aggs, naggs, slots, cap_max, n.dev, n.host, acc, cnt,
+                                                                                  rep_out, out_vals, out_valid, out_stride,
+                                                                                  valid_stride_words, ngroups);
   NDS_CUDA(cudaGetLastError());
 }
 
@@ -404,7 +444,7 @@ encode_keys_kernel(const Prog* __restrict__ progs, const SortKey* __restrict__ k
   uint8_t* first = sm_keys;
   uint8_t* flag = sm_keys + B;
   const int64_t n = row_count(n_dev, n_host);
-  if (n <= 0) return;
+  if (blockIdx.x * (int64_t)blockDim.x >= n) return;     // the grid is sized for the upper bound of the row count
   for (int b = threadIdx.x; b < B; b += blockDim.x) flag[b] = 0;
   if (threadIdx.x == 0) encode_row(progs, keys, nk, c, 0, first, nullptr, nullptr, nullptr);
   __syncthreads();
@@ -683,13 +723,13 @@ void launch_compact_keys(const uint8_t* keybuf, int B, const int* active, RowCou
 // length; when it exceeds cap only cap entries were stored and the caller must take another route.
 constexpr int kSelectThreads = 256;
 constexpr int kSelectTile = 8192;       // rows per CTA and pass
-__device__ __forceinline__ void topk_state(const uint32_t* __restrict__ hist, int npass, int64_t k, int cap, uint64_t* s_prefix,
-                                           uint64_t* s_mask, int* s_done) {
+__device__ __forceinline__ void topk_state(const uint32_t* __restrict__ hist, int npass, int64_t k, int cap, int64_t n,
+                                           uint64_t* s_prefix, uint64_t* s_mask, int* s_done) {
   if (threadIdx.x < 32) {
     const int lane = threadIdx.x;
     uint64_t prefix = 0, mask = 0;
     int64_t kk = k, less = 0;
-    int done = 0;
+    int done = n <= (int64_t)cap;        // everything fits the candidate list: empty mask, every row is taken
     for (int q = 0; q < npass && !done; ++q) {
       uint32_t h[8];
       uint32_t sum = 0;
@@ -740,7 +780,7 @@ topk_hist_kernel(const uint64_t* __restrict__ ckeys, int W, const int* n_dev, in
   const int64_t lo = (int64_t)blockIdx.x * kSelectTile, hi = min(n, lo + (int64_t)kSelectTile);
   if (lo >= n) return;
   h[tid] = 0;
-  topk_state(hist, pass, k, cap, &s_prefix, &s_mask, &s_done);
+  topk_state(hist, pass, k, cap, n, &s_prefix, &s_mask, &s_done);
   if (s_done) return;
   const uint64_t prefix = s_prefix, mask = s_mask;
   const int shift = 56 - 8 * pass;
@@ -769,7 +809,7 @@ topk_collect_kernel(const uint64_t* __restrict__ ckeys, int W, const int* n_dev,
   const int64_t n = row_count(n_dev, n_host);
   const int64_t lo = (int64_t)blockIdx.x * kSelectTile, hi = min(n, lo + (int64_t)kSelectTile);
   if (lo >= n) return;
-  topk_state(hist, npass, k, cap, &s_prefix, &s_mask, &s_done);
+  topk_state(hist, npass, k, cap, n, &s_prefix, &s_mask, &s_done);
   const uint64_t prefix = s_prefix, mask = s_mask;
   for (int64_t i0 = lo; i0 < hi; i0 += kSelectThreads) {
     const int64_t i = i0 + tid;
@@ -803,13 +843,23 @@ constexpr int kRankThreads = 128;
 __global__ void __launch_bounds__(kRankThreads)
 rank_sort_kernel(const uint64_t* __restrict__ ckeys, int W, const int* __restrict__ w_dev, const uint32_t* __restrict__ cand,
                  const int* nc_dev, int cand_cap, const int* n_dev, int64_t n_host, int64_t limit, uint32_t* rank_tmp,
-                 int* tile_done, uint32_t* __restrict__ out_rows, int* out_count) {
+                 int* tile_done, uint32_t* __restrict__ out_rows, int* out_count, int* overflow) {
   __shared__ uint64_t s_k0[kRankThreads], s_k1[kRankThreads];
   __shared__ uint32_t s_row[kRankThreads];
   __shared__ int s_last;
   const int tid = threadIdx.x;
   const int64_t n_all = row_count(n_dev, n_host);
-  const int64_t n = cand ? min((int64_t)min(nc_dev[0], cand_cap), n_all) : n_all;
+  if (cand ? nc_dev[0] > cand_cap : n_all > (int64_t)gridDim.x * kRankThreads) {
+    // more candidates / rows than this launch was sized for: tell the host (it re-runs the sort on the radix route)
+    // the rows the caller will gather must still be valid ids: the result is thrown away, but it is computed
+    if (blockIdx.x == 0 && blockIdx.y == 0) {
+      if (tid == 0 && overflow) atomicExch(overflow, 1);
+      const int64_t mo = (limit >= 0 && limit < n_all) ? limit : n_all;
+      for (int64_t i = tid; i < mo; i += kRankThreads) out_rows[i] = 0;
+    }
+    return;
+  }
+  const int64_t n = cand ? min((int64_t)nc_dev[0], n_all) : n_all;
   const int64_t m = (limit >= 0 && limit < n_all) ? limit : n_all;
   if (blockIdx.x == 0 && blockIdx.y == 0 && tid == 0) out_count[0] = (int)m;
   if ((int64_t)blockIdx.x * kRankThreads >= n) return;
@@ -871,11 +921,11 @@ rank_sort_kernel(const uint64_t* __restrict__ ckeys, int W, const int* __restric
 }
 void launch_rank_sort(const uint64_t* ckeys, int W, const int* w_dev, const uint32_t* cand, const int* nc_dev, int cand_cap,
                       RowCount n, int64_t rows_bound, int64_t limit, uint32_t* rank_tmp, int* tile_done, uint32_t* out_rows,
-                      int* out_count, cudaStream_t s) {
+                      int* out_count, int* overflow, cudaStream_t s) {
   const int tiles = (int)std::max<int64_t>(1, (rows_bound + kRankThreads - 1) / kRankThreads);
   const int J = rank_sort_slices(rows_bound);
   rank_sort_kernel<<<dim3(tiles, J), kRankThreads, 0, s>>>(ckeys, W, w_dev, cand, nc_dev, cand_cap, n.dev, n.host, limit, rank_tmp,
-                                                           tile_done, out_rows, out_count);
+                                                           tile_done, out_rows, out_count, overflow);
   NDS_CUDA(cudaGetLastError());
 }
 int rank_sort_slices(int64_t rows_bound) {

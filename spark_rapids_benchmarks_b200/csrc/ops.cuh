@@ -82,9 +82,15 @@ struct ProbeChain {            // a left-deep chain of inner hash joins probed i
   int32_t pad;
 };
 void launch_join_probe_chain(const ProbeChain& chain, RowCount n, uint32_t* out_probe, int* out_count, cudaStream_t s);
+// Hash group-by.  slots / acc / cnt are allocated for cap_max = agg_capacity_for(upper bound of the input rows); the
+// kernels size the table from the row count on the device (<= cap_max), so no host round trip is needed.
+// acc / cnt: naggs * cap_max int64 each; out_valid: naggs * valid_stride_words words (cleared by launch_agg_init).
+uint32_t agg_capacity_for(int64_t n_bound);
+void launch_agg_init(const AggSpec* aggs, int naggs, RowCount n, uint32_t cap_max, uint32_t* slots, int64_t* acc, int64_t* cnt,
+                     uint32_t* out_valid, int64_t valid_stride_words, cudaStream_t s);
 void launch_agg_insert(const Prog* progs, int nkeys, const AggSpec* aggs, int naggs, OpCtx c, RowCount n, uint32_t* slots,
-                       uint32_t mask, int64_t* acc, int64_t* cnt, cudaStream_t s);
-void launch_agg_finalize(const AggSpec* aggs, int naggs, const uint32_t* slots, uint32_t cap, const int64_t* acc,
+                       uint32_t cap_max, int64_t* acc, int64_t* cnt, cudaStream_t s);
+void launch_agg_finalize(const AggSpec* aggs, int naggs, const uint32_t* slots, uint32_t cap_max, RowCount n, const int64_t* acc,
                          const int64_t* cnt, uint32_t* rep_out, int64_t* out_vals, uint32_t* out_valid, int64_t out_stride,
                          int64_t valid_stride_words, int* ngroups, cudaStream_t s);
 void launch_str_maxlen(Prog p, OpCtx c, RowCount n, int* out_max, cudaStream_t s);
@@ -114,7 +120,7 @@ void launch_topk_select(const uint64_t* ckeys, int W, RowCount n, int64_t k, uin
 int rank_sort_slices(int64_t rows_bound);
 void launch_rank_sort(const uint64_t* ckeys, int W, const int* w_dev, const uint32_t* cand, const int* nc_dev, int cand_cap,
                       RowCount n, int64_t rows_bound, int64_t limit, uint32_t* rank_tmp, int* tile_done, uint32_t* out_rows,
-                      int* out_count, cudaStream_t s);
+                      int* out_count, int* overflow, cudaStream_t s);   // *overflow = 1 when rows/candidates exceed rows_bound
 void launch_take_perm(const uint32_t* perm_a, const uint32_t* perm_b, const int* which, int widx, RowCount n, int64_t limit,
                       uint32_t* out_rows, int* out_count, cudaStream_t s);
 // Small-result export: segment kinds 0 = raw bytes (multiple of 4), 1 = string column -> int32 offsets at dst_off

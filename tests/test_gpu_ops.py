@@ -270,8 +270,17 @@ def test_sort_topk_candidate_overflow_falls_back(gpu_engine):
     k[0] = 0                                               # ...except one outlier, which makes those bytes "active"
     rid = np.arange(n, dtype=np.int64)
     gpu_engine.register_arrow('ovf', pa.table({'k': k, 'rid': rid}))
+    gpu_engine.execute({'op': 'scan', 'table': 'ovf', 'columns': ['rid']})
+    retries0 = gpu_engine.last_stats().get('speculation_retries', 0)
     got = gpu_engine.execute({'op': 'sort', 'limit': 50, 'keys': [{'expr': col('k'), 'desc': True}, {'expr': col('rid')}],
                               'child': {'op': 'scan', 'table': 'ovf', 'columns': ['k', 'rid']}})
     order = np.lexsort([rid, -k])[:50]
     assert got.column('rid').to_pylist() == rid[order].tolist()
+    # the device-sized first attempt reported the overflow and the engine ran the plan again without speculation
+    assert gpu_engine.last_stats()['speculation_retries'] == retries0 + 1
+    plan = {'op': 'sort', 'limit': 50, 'keys': [{'expr': col('k'), 'desc': True}, {'expr': col('rid')}],
+            'child': {'op': 'scan', 'table': 'ovf', 'columns': ['k', 'rid']}}
+    again = gpu_engine.execute(plan, options={'speculate': False})
+    assert again.column('rid').to_pylist() == rid[order].tolist()
+    assert gpu_engine.last_stats()['speculation_retries'] == retries0 + 1
     gpu_engine.drop_table('ovf')
