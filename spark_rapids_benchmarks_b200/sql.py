@@ -20,14 +20,8 @@ class SqlError(ValueError):
     pass
 
 
-_TOKEN = re.compile(r"""
-    \s+ | --[^\n]* |
-    (?P<num>\d+\.\d*|\.\d+|\d+) |
-    (?P<str>'(?:[^']|'')*') |
-    (?P<bq>`[^`]*`) |
-    (?P<id>[A-Za-z_][A-Za-z_0-9]*) |
-    (?P<op><>|!=|<=|>=|\|\||[=<>+\-*/(),.;])
-""", re.X)
+# one alternative per token kind; comments match without a group, the last group catches anything unexpected
+_TOKEN = re.compile(r"""--[^\n]*|(\d+\.\d*|\.\d+|\d+)|('(?:[^']|'')*')|(`[^`]*`)|([A-Za-z_][A-Za-z_0-9]*)|(<>|!=|<=|>=|\|\||[=<>+\-*/(),.;])|(\S)""")
 
 KEYWORDS = {'select', 'from', 'where', 'group', 'by', 'order', 'limit', 'as', 'and', 'or', 'not', 'is', 'null',
             'between', 'in', 'asc', 'desc', 'nulls', 'first', 'last', 'case', 'when', 'then', 'else', 'end',
@@ -37,26 +31,21 @@ KEYWORDS = {'select', 'from', 'where', 'group', 'by', 'order', 'limit', 'as', 'a
 
 def tokenize(text):
     out = []
-    pos = 0
-    for m in _TOKEN.finditer(text):
-        if m.start() != pos:
-            break
-        pos = m.end()
-        kind = m.lastgroup
-        if kind is None:
-            continue
-        v = m.group(kind)
-        if kind == 'id':
-            lv = v.lower()
-            out.append(('kw', lv) if lv in KEYWORDS else ('id', lv))
-        elif kind == 'bq':
-            out.append(('id', v[1:-1]))
-        elif kind == 'str':
-            out.append(('str', v[1:-1].replace("''", "'")))
-        else:
-            out.append((kind, v))
-    if pos != len(text):
-        raise SqlError('cannot tokenize SQL at: %r' % text[pos:pos + 30])
+    add = out.append
+    for num, st, bq, ident, op, bad in _TOKEN.findall(text):
+        if ident:
+            lv = ident.lower()
+            add(('kw', lv) if lv in KEYWORDS else ('id', lv))
+        elif op:
+            add(('op', op))
+        elif num:
+            add(('num', num))
+        elif st:
+            add(('str', st[1:-1].replace("''", "'")))
+        elif bq:
+            add(('id', bq[1:-1]))
+        elif bad:
+            raise SqlError('cannot tokenize SQL at: %r' % text[text.index(bad):][:30])
     out.extend([('eof', '')] * 4)      # look-ahead never runs off the end
     return out
 
