@@ -69,6 +69,17 @@ NDS_API int nds_engine_table_info(nds_engine* e, const char* name, char* buf, in
  * Replaces: df = spark.sql(query); df.collect()     /root/reference/nds/nds_power.py:130-132 */
 NDS_API int nds_engine_execute(nds_engine* e, const char* plan_json, struct ArrowSchema* out_schema, struct ArrowArray* out_array);
 
+/* Communicator of the plan IR's "exchange" node (all-gather of partial aggregate states between the per-GPU
+ * processes of one node, NCCL over NVLink; libnccl.so.2 is opened at run time on first use).  Rank 0 obtains an id
+ * with nds_engine_comm_unique_id, the host distributes its NDS_COMM_ID_BYTES bytes to every process (any channel:
+ * torch.distributed, MPI, a file), and every process calls nds_engine_comm_init with its rank - a collective call.
+ * Replaces: the shuffle between HashAggregate(partial) and HashAggregate(final) that Spark inserts for
+ * `spark.sql.shuffle.partitions`   /root/reference/nds/power_run_gpu.template:29, power_run_cpu.template:27
+ * (the reference has no call site of its own - the exchange is inside spark.sql()). */
+#define NDS_COMM_ID_BYTES 128
+NDS_API int nds_engine_comm_unique_id(nds_engine* e, char* out, int64_t out_len);
+NDS_API int nds_engine_comm_init(nds_engine* e, const char* id, int64_t id_len, int rank, int world);
+
 /* JSON statistics of the last nds_engine_execute: kernel launches, device ms, h2d/d2h bytes and
  * per-operator {op, ms, bytes, rows}. */
 NDS_API int nds_engine_last_stats(nds_engine* e, char* buf, int64_t buflen);

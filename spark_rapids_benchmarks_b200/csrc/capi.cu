@@ -101,6 +101,23 @@ NDS_API int nds_engine_execute(nds_engine* e, const char* plan_json, struct Arro
   NDS_API_END(e)
 }
 
+NDS_API int nds_engine_comm_unique_id(nds_engine* e, char* out, int64_t out_len) {
+  if (!e) return 2;
+  NDS_API_BEGIN
+  if (!out || out_len < NDS_COMM_ID_BYTES) nds::fail("nds_engine_comm_unique_id: buffer of NDS_COMM_ID_BYTES needed");
+  std::string id = e->impl->comm_unique_id();
+  memcpy(out, id.data(), NDS_COMM_ID_BYTES);
+  NDS_API_END(e)
+}
+
+NDS_API int nds_engine_comm_init(nds_engine* e, const char* id, int64_t id_len, int rank, int world) {
+  if (!e) return 2;
+  NDS_API_BEGIN
+  if (!id || id_len != NDS_COMM_ID_BYTES) nds::fail("nds_engine_comm_init: id must be the NDS_COMM_ID_BYTES bytes rank 0 obtained");
+  e->impl->comm_init(std::string(id, (size_t)id_len), rank, world);
+  NDS_API_END(e)
+}
+
 NDS_API int nds_engine_last_stats(nds_engine* e, char* buf, int64_t buflen) {
   if (!e) return 2;
   NDS_API_BEGIN

@@ -152,6 +152,8 @@ class Engine {
   void register_arrow(const std::string& name, ArrowSchema* schema, ArrowArray* array);
   void drop_table(const std::string& name);
   void execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_array);
+  std::string comm_unique_id();
+  void comm_init(const std::string& id_bytes, int rank, int world);
   void execute_once(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_array, bool speculate);
   std::string stats_json() const;
   std::string table_info_json(const std::string& name) const;
@@ -176,6 +178,8 @@ class Engine {
   int64_t pin_cap_ = 0;
   uint8_t* slab_ = nullptr;     // device slab behind the per-query bump allocator
   int64_t slab_cap_ = 0;
+  void* comm_ = nullptr;          // ncclComm_t of the exchange operator (nccl_dyn.h); null until comm_init
+  int comm_rank_ = 0, comm_world_ = 1;
   int64_t spec_retries_ = 0;    // queries re-run because a device-side size assumption failed (stats: speculation_retries)
   int64_t zero_dirty_ = -1;     // bytes of the slab's zeroed prefix the last query used (-1: unknown)
   std::vector<cudaEvent_t> event_pool_;

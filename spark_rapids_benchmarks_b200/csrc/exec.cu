@@ -8,6 +8,7 @@
 #include <memory>
 #include <unordered_set>
 #include "engine.h"
+#include "nccl_dyn.h"
 
 namespace nds {
 
@@ -239,7 +240,8 @@ struct Exec {
   int64_t launches = 0;
   int64_t h2d = 0, d2h = 0;
 
-  Exec(Engine& en, const Json* options) : e(en), ar(en.stream_), s(en.stream_) {
+  const Json* opts = nullptr;
+  Exec(Engine& en, const Json* options) : e(en), ar(en.stream_), s(en.stream_), opts(options) {
     ar.pin = en.pin_;
     ar.pin_cap = en.pin_cap_;
     ar.attach_slab(en.slab_, en.slab_cap_, en.zero_dirty_);
@@ -1286,6 +1288,172 @@ struct Exec {
     return out;
   }
 
+  // ---------------------------------------------------------------- exchange (all-gather between the GPUs of a node)
+  // Spark: HashAggregate(partial) -> ShuffleExchange -> HashAggregate(final).  Every rank
+  // contributes the rows of its child (the partial aggregate states of its fact-table shard) and receives the
+  // concatenation in rank order, all in device memory: row counts are all-gathered first (one host read-back, the
+  // only synchronisation), then the packed segments.  With one rank the operator passes its child through;
+  // options.exchange_loopback = k emulates k ranks that all hold this rank's rows (device copies instead of NCCL),
+  // which exercises the pack / layout / unpack path on a single GPU.
+  struct SegLayout { std::vector<int64_t> off_valid, off_data, off_aux; int64_t bytes = 0; };
+  static SegLayout seg_layout(const std::vector<XCol>& proto, int64_t n) {
+    SegLayout L;
+    int64_t off = 0;
+    for (const XCol& x : proto) {
+      L.off_valid.push_back(off);
+      off = align_up(off + n, 16);
+      L.off_data.push_back(off);
+      off = align_up(off + n * (x.kind == 1 ? 8 : 4), 16);
+      L.off_aux.push_back(off);
+      if (x.kind == 2) off = align_up(off + n * (int64_t)x.maxlen, 16);
+    }
+    L.bytes = align_up(std::max<int64_t>(off, 16), 256);
+    return L;
+  }
+
+  Batch exchange(const Json& node, std::vector<RuntimeFilter>& filters) {
+    Batch in = exec(node.at("child"), filters);
+    const int loop = (int)(opts ? opts->int_or("exchange_loopback", 0) : 0);
+    const int world = loop > 0 ? loop : e.comm_world_;
+    if (world <= 1) return in;
+    if (loop <= 0 && !e.comm_) fail("plan: exchange needs a communicator (nds_engine_comm_init) when the engine's world size is > 1");
+    size_t st = begin_stat("exchange");
+    const int ncols = (int)in.cols.size();
+    // flatten the columns (row maps resolved) - one launch
+    std::vector<Column> flat = in.cols;
+    {
+      std::vector<Json> ces;
+      std::vector<size_t> which;
+      for (size_t c = 0; c < in.cols.size(); ++c)
+        if (in.cols[c].rowmap) { which.push_back(c); ces.push_back(col_expr(in.cols[c].name)); }
+      std::vector<std::pair<std::string, const Json*>> exs;
+      for (size_t k = 0; k < which.size(); ++k) exs.emplace_back(in.cols[which[k]].name, &ces[k]);
+      if (!which.empty() && in.rc().host > 0) {
+        std::vector<Column> fc = eval_columns(exs, in, nullptr, in.rc());
+        for (size_t k = 0; k < which.size(); ++k) flat[which[k]] = fc[k];
+      }
+    }
+    // ---- counts (and string slot widths: the widest any rank declares) travel first
+    std::vector<int32_t> meta(1 + ncols, 0);
+    for (int c = 0; c < ncols; ++c) {
+      const LType& t = flat[c].lt;
+      if (t.kind == LType::STR && t.maxlen <= 0) fail("plan: exchange of string column '" + flat[c].name + "' without a known maximum length");
+      meta[1 + c] = t.kind == LType::STR ? t.maxlen : 0;
+    }
+    const int mlen = 1 + ncols;
+    int32_t* d_meta = ar.alloc_n<int32_t>(mlen);
+    int32_t* d_all = ar.alloc_n<int32_t>((int64_t)mlen * world);
+    ar.upload(d_meta, meta.data(), mlen * 4);
+    launch_set_count(in.rc(), d_meta, s);
+    ++launches;
+    if (loop > 0) {
+      for (int r = 0; r < world; ++r)
+        NDS_CUDA(cudaMemcpyAsync(d_all + (int64_t)r * mlen, d_meta, mlen * 4, cudaMemcpyDeviceToDevice, s));
+    } else {
+      nccl_check(nccl_api().AllGather(d_meta, d_all, (size_t)mlen * 4, kNcclChar, e.comm_, s), "ncclAllGather(counts)");
+    }
+    std::vector<int32_t> all((size_t)mlen * world);
+    uint8_t* pin = ar.pin_take((int64_t)all.size() * 4);
+    int32_t* hall = pin ? reinterpret_cast<int32_t*>(pin) : all.data();
+    NDS_CUDA(cudaMemcpyAsync(hall, d_all, all.size() * 4, cudaMemcpyDeviceToHost, s));
+    sync("sync:exchange_counts");
+    d2h += (int64_t)all.size() * 4;
+    std::vector<int64_t> row_begin(world + 1, 0);
+    int64_t max_rows = 0;
+    std::vector<XCol> proto(ncols);
+    for (int c = 0; c < ncols; ++c) {
+      XCol& x = proto[c];
+      memset(&x, 0, sizeof x);
+      const LType& t = flat[c].lt;
+      x.kind = t.kind == LType::STR ? 2 : (t.dtype() == DT_I32 ? 0 : 1);
+      for (int r = 0; r < world; ++r) x.maxlen = std::max(x.maxlen, hall[(int64_t)r * mlen + 1 + c]);
+    }
+    for (int r = 0; r < world; ++r) {
+      const int64_t nr = std::max<int32_t>(hall[(int64_t)r * mlen], 0);
+      row_begin[r + 1] = row_begin[r] + nr;
+      max_rows = std::max(max_rows, nr);
+    }
+    const int my = loop > 0 ? 0 : e.comm_rank_;
+    const int64_t n_mine = row_begin[my + 1] - row_begin[my];
+    in.n_exact = n_mine;
+    const int64_t N = row_begin[world];
+    const int64_t seg_bytes = seg_layout(proto, max_rows).bytes;        // every rank sends this many bytes
+    if (seg_bytes * world >= (int64_t(1) << 32)) fail("exchange: more than 4 GiB of partial state; repartition instead of gathering");
+    // ---- pack my segment
+    uint8_t* d_send = (uint8_t*)ar.alloc(seg_bytes);
+    uint8_t* d_recv = (uint8_t*)ar.alloc(seg_bytes * world);
+    {
+      SegLayout L = seg_layout(proto, n_mine);
+      std::vector<XCol> mine = proto;
+      for (int c = 0; c < ncols; ++c) {
+        mine[c].data = flat[c].data;
+        mine[c].valid = flat[c].valid;
+        mine[c].strbase = flat[c].strbase;
+        mine[c].off_valid = L.off_valid[c];
+        mine[c].off_data = L.off_data[c];
+        mine[c].off_aux = L.off_aux[c];
+      }
+      XCol* d_cols = ar.alloc_n<XCol>(ncols);
+      ar.upload(d_cols, mine.data(), (int64_t)ncols * (int64_t)sizeof(XCol));
+      launch_exchange_pack(d_cols, ncols, n_mine, d_send, err, s);
+      ++launches;
+    }
+    if (loop > 0) {
+      for (int r = 0; r < world; ++r)
+        NDS_CUDA(cudaMemcpyAsync(d_recv + (int64_t)r * seg_bytes, d_send, (size_t)seg_bytes, cudaMemcpyDeviceToDevice, s));
+    } else {
+      nccl_check(nccl_api().AllGather(d_send, d_recv, (size_t)seg_bytes, kNcclChar, e.comm_, s), "ncclAllGather(segments)");
+    }
+    // ---- unpack into concatenated columns
+    Batch out;
+    out.n_max = N;
+    out.n_exact = N;
+    std::vector<XCol> srcs((size_t)world * ncols), dst(ncols);
+    const int64_t vwords = (N + 31) / 32 + 1;
+    for (int c = 0; c < ncols; ++c) {
+      Column oc;
+      oc.name = flat[c].name;
+      oc.lt = flat[c].lt;
+      if (oc.lt.kind == LType::STR) oc.lt.maxlen = proto[c].maxlen;
+      const int w = proto[c].kind == 0 ? 4 : 8;
+      oc.data = ar.alloc(std::max<int64_t>(N, 1) * w);
+      oc.valid = ar.zeros<uint32_t>(vwords);
+      oc.strbase = proto[c].kind == 2 ? d_recv : nullptr;
+      out.cols.push_back(oc);
+      memset(&dst[c], 0, sizeof(XCol));
+      dst[c].data = oc.data;
+      dst[c].valid = oc.valid;
+      dst[c].kind = proto[c].kind;
+    }
+    for (int r = 0; r < world; ++r) {
+      SegLayout L = seg_layout(proto, row_begin[r + 1] - row_begin[r]);
+      for (int c = 0; c < ncols; ++c) {
+        XCol x = proto[c];
+        x.data = d_recv + (int64_t)r * seg_bytes;
+        x.off_valid = L.off_valid[c];
+        x.off_data = L.off_data[c];
+        x.off_aux = L.off_aux[c];
+        srcs[(size_t)r * ncols + c] = x;
+      }
+    }
+    if (N > 0) {
+      const int64_t bytes_desc = (int64_t)(srcs.size() + dst.size()) * (int64_t)sizeof(XCol) + (world + 1) * 8;
+      uint8_t* d_desc = (uint8_t*)ar.alloc(bytes_desc);
+      std::vector<uint8_t> h((size_t)bytes_desc);
+      memcpy(h.data(), srcs.data(), srcs.size() * sizeof(XCol));
+      memcpy(h.data() + srcs.size() * sizeof(XCol), dst.data(), dst.size() * sizeof(XCol));
+      memcpy(h.data() + (srcs.size() + dst.size()) * sizeof(XCol), row_begin.data(), (world + 1) * 8);
+      ar.upload(d_desc, h.data(), bytes_desc);
+      const XCol* d_srcs = reinterpret_cast<const XCol*>(d_desc);
+      const XCol* d_dst = d_srcs + srcs.size();
+      const int64_t* d_rb = reinterpret_cast<const int64_t*>(d_desc + (srcs.size() + dst.size()) * sizeof(XCol));
+      launch_exchange_unpack(d_srcs, d_dst, ncols, d_rb, world, max_rows, d_recv, s);
+      ++launches;
+    }
+    end_stat(st, seg_bytes * (world - 1), N);     // bytes that cross NVLink into this GPU
+    return out;
+  }
+
   // ---------------------------------------------------------------- sort / top-k
   Batch sort(const Json& node, std::vector<RuntimeFilter>& filters) {
     Batch in = exec(node.at("child"), filters);
@@ -1461,6 +1629,7 @@ struct Exec {
     if (op == "join") return join(node, filters);
     if (op == "aggregate") return aggregate(node, filters);
     if (op == "sort") return sort(node, filters);
+    if (op == "exchange") return exchange(node, filters);
     fail("plan: unsupported plan node '" + op + "' (no CPU fallback exists)");
   }
 };
@@ -1866,8 +2035,30 @@ cudaEvent_t Engine::get_event() {
 }
 void Engine::put_event(cudaEvent_t e) { event_pool_.push_back(e); }
 
+// ---- communicator for the exchange operator (one rank per process / GPU, NCCL over NVLink)
+std::string Engine::comm_unique_id() {
+  NcclUniqueId id;
+  memset(&id, 0, sizeof id);
+  nccl_check(nccl_api().GetUniqueId(&id), "ncclGetUniqueId");
+  return std::string(id.internal, sizeof id.internal);
+}
+
+void Engine::comm_init(const std::string& id_bytes, int rank_in, int world_in) {
+  if (id_bytes.size() != sizeof(NcclUniqueId)) fail("comm_init: the unique id must be 128 bytes");
+  if (world_in < 1 || rank_in < 0 || rank_in >= world_in) fail("comm_init: bad rank/world");
+  NDS_CUDA(cudaSetDevice(device));
+  if (comm_) { nccl_api().CommDestroy(comm_); comm_ = nullptr; }
+  comm_rank_ = rank_in;
+  comm_world_ = world_in;
+  if (world_in == 1) return;
+  NcclUniqueId id;
+  memcpy(id.internal, id_bytes.data(), sizeof id.internal);
+  nccl_check(nccl_api().CommInitRank(&comm_, world_in, id, rank_in), "ncclCommInitRank");
+}
+
 Engine::~Engine() {
   cudaSetDevice(device);
+  if (comm_) { nccl_api().CommDestroy(comm_); comm_ = nullptr; }
   for (cudaEvent_t e : event_pool_) cudaEventDestroy(e);
   std::vector<std::string> names;
   for (auto& kv : tables_) names.push_back(kv.first);

@@ -952,6 +952,76 @@ void launch_take_perm(const uint32_t* perm_a, const uint32_t* perm_b, const int*
 }
 
 // ------------------------------------------------------------------ result strings
+// ------------------------------------------------------------------ exchange (all-gather of a batch between GPUs)
+// A rank's rows travel as one segment: per column [validity, one byte per row][values]; string columns send their
+// lengths as the values and their bytes in fixed slots of the column's maximum length (no prefix sum, no second size
+// exchange - NVLink has the bandwidth to spare).  XCol::off_* are byte offsets inside the segment; they depend on
+// the row count only, so every rank can lay out every other rank's segment once the counts are known.
+__global__ void set_count_kernel(const int* n_dev, int64_t n_host, int32_t* out) { out[0] = (int32_t)row_count(n_dev, n_host); }
+void launch_set_count(RowCount n, int32_t* out, cudaStream_t s) {
+  set_count_kernel<<<1, 1, 0, s>>>(n.dev, n.host, out);
+  NDS_CUDA(cudaGetLastError());
+}
+
+__global__ void __launch_bounds__(kThreads)
+exchange_pack_kernel(const XCol* __restrict__ cols, int ncols, int64_t n, uint8_t* __restrict__ out, int* err) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    for (int c = 0; c < ncols; ++c) {
+      const XCol x = cols[c];
+      const bool ok = !x.valid || ((x.valid[i >> 5] >> (i & 31)) & 1u);
+      out[x.off_valid + i] = ok ? 1 : 0;
+      if (x.kind == 0) reinterpret_cast<int32_t*>(out + x.off_data)[i] = ok ? reinterpret_cast<const int32_t*>(x.data)[i] : 0;
+      else if (x.kind == 1) reinterpret_cast<int64_t*>(out + x.off_data)[i] = ok ? reinterpret_cast<const int64_t*>(x.data)[i] : 0;
+      else {
+        const StrView v = ok ? reinterpret_cast<const StrView*>(x.data)[i] : 0;
+        int len = (int)(v >> 32);
+        if (len > x.maxlen) { if (err) atomicExch(err, 14); len = x.maxlen; }
+        reinterpret_cast<int32_t*>(out + x.off_data)[i] = len;
+        const uint8_t* p = x.strbase + (uint32_t)v;
+        uint8_t* q = out + x.off_aux + i * (int64_t)x.maxlen;
+        for (int b = 0; b < len; ++b) q[b] = p[b];
+      }
+    }
+  }
+}
+void launch_exchange_pack(const XCol* cols, int ncols, int64_t n, uint8_t* out, int* err, cudaStream_t s) {
+  if (n <= 0) return;
+  exchange_pack_kernel<<<grid_for(n), kThreads, 0, s>>>(cols, ncols, n, out, err);
+  NDS_CUDA(cudaGetLastError());
+}
+
+// blockIdx.y = source rank; srcs[r * ncols + c] describes column c inside rank r's segment (data = segment base),
+// dst[c] the concatenated output column (data, valid bitmap - pre-zeroed -, strbase = the whole receive buffer).
+__global__ void __launch_bounds__(kThreads)
+exchange_unpack_kernel(const XCol* __restrict__ srcs, const XCol* __restrict__ dst, int ncols, const int64_t* __restrict__ row_begin,
+                       const uint8_t* __restrict__ recv) {
+  const int r = blockIdx.y;
+  const int64_t n = row_begin[r + 1] - row_begin[r];
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t o = row_begin[r] + i;
+    for (int c = 0; c < ncols; ++c) {
+      const XCol x = srcs[r * ncols + c];
+      const XCol d = dst[c];
+      const uint8_t* seg = reinterpret_cast<const uint8_t*>(x.data);
+      const bool ok = seg[x.off_valid + i] != 0;
+      if (ok) atomicOr(const_cast<uint32_t*>(d.valid) + (o >> 5), 1u << (o & 31));
+      if (x.kind == 0) reinterpret_cast<int32_t*>(const_cast<void*>(d.data))[o] = reinterpret_cast<const int32_t*>(seg + x.off_data)[i];
+      else if (x.kind == 1) reinterpret_cast<int64_t*>(const_cast<void*>(d.data))[o] = reinterpret_cast<const int64_t*>(seg + x.off_data)[i];
+      else {
+        const uint32_t len = (uint32_t) reinterpret_cast<const int32_t*>(seg + x.off_data)[i];
+        const uint64_t off = (uint64_t)(seg + x.off_aux + i * (int64_t)x.maxlen - recv);
+        reinterpret_cast<StrView*>(const_cast<void*>(d.data))[o] = ((uint64_t)len << 32) | (uint64_t)(uint32_t)off;
+      }
+    }
+  }
+}
+void launch_exchange_unpack(const XCol* srcs, const XCol* dst, int ncols, const int64_t* row_begin, int world, int64_t max_rows,
+                            const uint8_t* recv, cudaStream_t s) {
+  if (max_rows <= 0) return;
+  exchange_unpack_kernel<<<dim3(grid_for(max_rows, kThreads, 148 * 2), world), kThreads, 0, s>>>(srcs, dst, ncols, row_begin, recv);
+  NDS_CUDA(cudaGetLastError());
+}
+
 // ------------------------------------------------------------------ result export, small results
 // One launch packs a whole (small) result into one contiguous buffer, so that it reaches the host with ONE copy and
 // ONE synchronisation, row count included: block b handles segment b.

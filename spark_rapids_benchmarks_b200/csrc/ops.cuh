@@ -123,6 +123,20 @@ void launch_rank_sort(const uint64_t* ckeys, int W, const int* w_dev, const uint
                       int* out_count, int* overflow, cudaStream_t s);   // *overflow = 1 when rows/candidates exceed rows_bound
 void launch_take_perm(const uint32_t* perm_a, const uint32_t* perm_b, const int* which, int widx, RowCount n, int64_t limit,
                       uint32_t* out_rows, int* out_count, cudaStream_t s);
+// Exchange (exec.cu, Exec::exchange): a batch is packed into one segment per rank, all-gathered with NCCL, and
+// unpacked into concatenated columns.  kind: 0 int32, 1 int64/double, 2 string (values = int32 lengths, bytes in
+// fixed maxlen slots at off_aux).  Error 14: a string longer than the column's declared maximum.
+struct XCol {
+  const void* data;
+  const uint32_t* valid;
+  const uint8_t* strbase;
+  int64_t off_valid, off_data, off_aux;
+  int32_t kind, maxlen;
+};
+void launch_set_count(RowCount n, int32_t* out, cudaStream_t s);
+void launch_exchange_pack(const XCol* cols, int ncols, int64_t n, uint8_t* out, int* err, cudaStream_t s);
+void launch_exchange_unpack(const XCol* srcs, const XCol* dst, int ncols, const int64_t* row_begin, int world, int64_t max_rows,
+                            const uint8_t* recv, cudaStream_t s);
 // Small-result export: segment kinds 0 = raw bytes (multiple of 4), 1 = string column -> int32 offsets at dst_off
 // and characters at aux_off (cap bytes available; error 13 if exceeded), 2 = the row count as one int.
 struct ExportSeg {

@@ -93,12 +93,36 @@ def _add_stats(a, b):
     return out
 
 
+def init_engine_comm(session, group=None):
+    """Collective over torch.distributed: give every rank's engine the NCCL communicator of the plan IR's
+    `exchange` node (rank 0 creates the id, torch.distributed carries its 128 bytes).  Only with the nccl
+    backend - under gloo (CPU tests) the host path below stays in use."""
+    import torch.distributed as tdist
+    if tdist.get_backend(group) != 'nccl':
+        return False
+    box = [session.engine.comm_unique_id() if session.rank == 0 else None]
+    tdist.broadcast_object_list(box, src=0, group=group)
+    session.engine.comm_init(box[0], session.rank, session.world)
+    return True
+
+
 def execute_distributed(session, plan):
-    """Partial plan on this rank's shard -> all-gather of the partial states -> merge on every rank.
-    Leaves the summed statistics of both engine calls in session.dist_stats."""
+    """Engines that share a communicator run ONE plan: partial aggregate -> exchange (NCCL all-gather in device
+    memory) -> merge aggregate -> project -> sort.  Otherwise (gloo, or no communicator): partial plan on this rank's
+    shard -> all-gather of the partial states through the host -> merge on every rank; the summed statistics of
+    both engine calls are left in session.dist_stats."""
     if 'partial' not in plan:
         raise ValueError('plan was not built with distributed=True')
     src = session.source if session.source != 'hbm' else None
+    if getattr(session.engine, 'has_comm', False) and 'fused' in plan:
+        key = '_json_fused_' + session.source
+        payload = plan.get(key)
+        if payload is None:
+            payload = session.engine.encode_plan({'root': plan['fused']}, source=src)
+            plan[key] = payload
+        out = session.engine.execute(payload)
+        session.dist_stats = session.engine.last_stats()
+        return out
     partial = session.engine.execute({'root': plan['partial']}, source=src)
     st = session.engine.last_stats()
     gathered = all_gather_batches(partial, session.comm)

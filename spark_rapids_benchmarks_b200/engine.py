@@ -16,7 +16,9 @@ LIB_PATH = os.path.join(_HERE, 'libndsb200.so')
 SYMBOLS = ['nds_version', 'nds_last_error', 'nds_engine_create', 'nds_engine_destroy',
            'nds_engine_last_error', 'nds_engine_register_table', 'nds_engine_register_arrow',
            'nds_engine_drop_table', 'nds_engine_table_info', 'nds_engine_execute',
-           'nds_engine_last_stats', 'nds_join_probe_i64_noalloc']
+           'nds_engine_last_stats', 'nds_join_probe_i64_noalloc', 'nds_engine_comm_unique_id',
+           'nds_engine_comm_init']
+COMM_ID_BYTES = 128
 
 _lib = None
 
@@ -50,6 +52,8 @@ def load_library(path=None):
     lib.nds_engine_execute.argtypes = [vp, cp, vp, vp]
     lib.nds_engine_last_stats.argtypes = [vp, ctypes.c_char_p, i64]
     lib.nds_join_probe_i64_noalloc.argtypes = [vp, ctypes.c_int32, vp, i64, vp, vp]
+    lib.nds_engine_comm_unique_id.argtypes = [vp, ctypes.c_char_p, i64]
+    lib.nds_engine_comm_init.argtypes = [vp, ctypes.c_char_p, i64, ctypes.c_int, ctypes.c_int]
     if path is None:
         _lib = lib
     return lib
@@ -73,6 +77,7 @@ class Engine:
             self._h = None
             raise EngineError(self._lib.nds_last_error().decode())
         self.rank, self.world = rank, world
+        self.has_comm = False
 
     def _check(self, rc):
         if rc != 0:
@@ -160,6 +165,17 @@ class Engine:
         ca = ctypes.create_string_buffer(_ARRAY_BYTES)
         self._check(self._lib.nds_engine_execute(self._h, payload, ctypes.addressof(cs), ctypes.addressof(ca)))
         return pa.RecordBatch._import_from_c(ctypes.addressof(ca), ctypes.addressof(cs))
+
+    def comm_unique_id(self):
+        """128 opaque bytes (an ncclUniqueId) that rank 0 hands to every other rank's comm_init."""
+        buf = ctypes.create_string_buffer(COMM_ID_BYTES)
+        self._check(self._lib.nds_engine_comm_unique_id(self._h, buf, COMM_ID_BYTES))
+        return buf.raw
+
+    def comm_init(self, comm_id, rank, world):
+        """Collective: every rank's engine joins the NCCL communicator the plan IR's `exchange` node uses."""
+        self._check(self._lib.nds_engine_comm_init(self._h, comm_id, len(comm_id), int(rank), int(world)))
+        self.has_comm = world > 1
 
     def last_stats(self):
         buf = ctypes.create_string_buffer(1 << 20)

@@ -493,6 +493,8 @@ class Planner:
             if final_partial is None:
                 raise PlanError('distributed execution needs an aggregating query')
             out['partial'] = final_partial
+            # one plan for engines that share a communicator: the scan of the gathered states becomes an exchange node
+            out['fused'] = _replace_partial_scan(node, {'op': 'exchange', 'child': final_partial})
         return out
 
     def pred_selectivity(self, c):
@@ -534,8 +536,21 @@ class _AggMap:
         return [dict(s) for s in self.order]
 
 
+def _replace_partial_scan(node, replacement):
+    """Copy of a merge plan in which the scan of `__partial__` is replaced (the rest of the tree is shared)."""
+    if not isinstance(node, dict):
+        return node
+    if node.get('op') == 'scan' and node.get('table') == '__partial__':
+        return replacement
+    out = dict(node)
+    for k in ('child', 'probe', 'build'):
+        if k in out:
+            out[k] = _replace_partial_scan(out[k], replacement)
+    return out
+
+
 def plan_sql(sql_text, distributed=False):
-    """SQL text -> plan dict ({'root': ..., 'output': [...]} [+ 'partial'])."""
+    """SQL text -> plan dict ({'root': ..., 'output': [...]} [+ 'partial', 'fused'])."""
     body = '\n'.join(l for l in sql_text.split('\n') if not l.strip().startswith('--'))
     try:
         ast = parse(body)

@@ -88,6 +88,16 @@ class Session:
         self.engine = Engine(device=device, resident=True, keep_host=keep_host or self.source == 'host',
                              rank=rank, world=world)
         self._stats = None
+        if world > 1:
+            # under torchrun with the nccl backend the engines get a communicator of their own, so that the
+            # exchange between partial and final aggregation stays in device memory (dist.py)
+            try:
+                import torch.distributed as tdist
+                if tdist.is_available() and tdist.is_initialized():
+                    from . import dist
+                    dist.init_engine_comm(self, comm)
+            except ImportError:
+                pass
 
     def conf_items(self):
         d = dict(self.conf)

@@ -1,0 +1,48 @@
+"""Worker of tests/test_gpu_queries.py::test_exchange_over_nccl_two_gpus (launched with torchrun, one rank per GPU)."""
+import math
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    import torch
+    import torch.distributed as tdist
+    rank, world, local = int(os.environ['RANK']), int(os.environ['WORLD_SIZE']), int(os.environ['LOCAL_RANK'])
+    torch.cuda.set_device(local)
+    tdist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    from oracle import nds_queries as oq
+    from spark_rapids_benchmarks_b200 import nds_schema, streams
+    from spark_rapids_benchmarks_b200.session import Session
+    wh = os.environ['NDS_TEST_WAREHOUSE']
+    sess = Session('nccl-exchange-test', device=local, rank=rank, world=world, keep_host=True)
+    assert sess.engine.has_comm, 'engine communicator was not initialised'
+    for t in nds_schema.get_schemas(True):
+        sess.register_table(t, os.path.join(wh, t))
+    ok = 0
+    for query in streams.SUBSET:
+        sql = streams.render(query, overrides={'MANUFACT': 606, 'MANAGER': 63, 'MONTH': 1, 'YEAR': 1998})
+        for source in ('hbm', 'host'):
+            sess.source = source
+            got = sess.sql(sql).toArrow().to_pylist()
+            assert any(o['op'] == 'exchange' for o in sess.last_stats['ops']), 'the native exchange did not run'
+            if rank == 0:
+                exp = oq.run_query(query, sql, wh).to_pylist()
+                assert len(got) == len(exp), (query, len(got), len(exp))
+                for g, e in zip(got, exp):
+                    for k in e:
+                        if isinstance(e[k], float) and g[k] is not None:
+                            assert math.isclose(g[k], e[k], rel_tol=1e-5), (query, k, g[k], e[k])
+                        else:
+                            assert g[k] == e[k], (query, k, g[k], e[k])
+        ok += 1
+    tdist.barrier()
+    if rank == 0:
+        print('EXCHANGE-OK %d' % ok, flush=True)
+    tdist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()

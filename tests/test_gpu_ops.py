@@ -284,3 +284,42 @@ def test_sort_topk_candidate_overflow_falls_back(gpu_engine):
     assert again.column('rid').to_pylist() == rid[order].tolist()
     assert gpu_engine.last_stats()['speculation_retries'] == retries0 + 1
     gpu_engine.drop_table('ovf')
+
+
+@pytest.mark.parametrize('k', [2, 3])
+def test_exchange_loopback_pack_unpack(gpu_engine, tbl, k):
+    """The exchange node's pack -> (all-gather) -> unpack path on one GPU: options.exchange_loopback=k stands in
+    for k ranks that all hold this rank's rows, so the result is the input k times, in rank order - integers,
+    decimals, strings (empty and long) and nulls included.  The filter leaves the row count on the device."""
+    plan = {'op': 'exchange',
+            'child': {'op': 'filter', 'cond': fn('ge', col('g'), lit(3)),
+                      'child': {'op': 'scan', 'table': 't', 'columns': ['a', 'b', 's', 'd', 'g']}}}
+    got = pa.Table.from_batches([gpu_engine.execute(plan, options={'exchange_loopback': k})])
+    keep = pc.fill_null(pc.greater_equal(tbl.column('g'), 3), False)
+    one = tbl.filter(keep).select(['a', 'b', 's', 'd', 'g'])
+    exp = pa.concat_tables([one] * k)
+    assert got.num_rows == exp.num_rows
+    # (the filter compacts with atomics, so row order inside a rank is not the input order: compare as multisets)
+    def rows(t):
+        return sorted(zip(*[t.column(n).to_pylist() for n in exp.schema.names]), key=repr)
+    assert rows(got) == rows(exp)
+    # rank order: the second copy repeats the first, row for row
+    n1 = one.num_rows
+    for name in exp.schema.names:
+        c = got.column(name).to_pylist()
+        assert c[:n1] == c[n1:2 * n1], name
+    # and an aggregate over the gathered rows: every group's sum is k times the single-rank sum
+    agg = {'op': 'sort', 'keys': [{'expr': col('g')}],
+           'child': {'op': 'aggregate', 'keys': [{'name': 'g', 'expr': col('g')}],
+                     'aggs': [{'name': 'sb', 'fn': 'sum', 'expr': col('b')}, {'name': 'c', 'fn': 'count_star'}],
+                     'child': plan}}
+    g1 = pa.Table.from_batches([gpu_engine.execute(agg)]).to_pylist()                      # world = 1: pass-through
+    gk = pa.Table.from_batches([gpu_engine.execute(agg, options={'exchange_loopback': k})]).to_pylist()
+    assert [(r['g'], r['sb'] * k, r['c'] * k) for r in g1] == [(r['g'], r['sb'], r['c']) for r in gk]
+
+
+def test_exchange_empty_input(gpu_engine, tbl):
+    plan = {'op': 'exchange', 'child': {'op': 'filter', 'cond': fn('gt', col('g'), lit(1000)),
+                                        'child': {'op': 'scan', 'table': 't', 'columns': ['a', 's', 'g']}}}
+    got = gpu_engine.execute(plan, options={'exchange_loopback': 2})
+    assert got.num_rows == 0 and got.schema.names == ['a', 's', 'g']

@@ -163,3 +163,39 @@ def test_power_and_validate_cli_as_subprocesses(warehouse, tmp_path):
     assert v.returncode == 0, v.stdout[-2000:] + v.stderr[-2000:]
     assert 'Unmatch Queries' not in v.stdout and v.stdout.count('Results match') == 3
     assert json.load(open(os.path.join(js, summaries[0])))['queryValidationStatus'] == ['Pass']
+
+
+@pytest.mark.parametrize('query', streams.SUBSET)
+def test_fused_exchange_plan_on_one_engine(gpu_engine, warehouse, query):
+    """The single-plan form of the distributed query (partial aggregate -> exchange -> merge aggregate -> sort):
+    with one rank the exchange passes through, with exchange_loopback=2 every partial state arrives twice, which
+    doubles SUM/COUNT and leaves AVG and the row order alone - checked against the oracle either way."""
+    from spark_rapids_benchmarks_b200 import planner
+    import pyarrow as pa
+    sql = streams.render(query, overrides=PARAMS[0])
+    plan = planner.plan_sql(sql, distributed=True)
+    exp = oq.run_query(query, sql, warehouse)
+    got = pa.Table.from_batches([gpu_engine.execute({'root': plan['fused']})])
+    assert rows_equal(got.to_pylist(), exp.to_pylist())
+    twice = pa.Table.from_batches([gpu_engine.execute({'root': plan['fused']}, options={'exchange_loopback': 2})])
+    assert twice.num_rows == exp.num_rows
+    if query == 'query7':          # averages only: unchanged
+        assert rows_equal(twice.to_pylist(), exp.to_pylist())
+
+
+def test_exchange_over_nccl_two_gpus(warehouse, tmp_path):
+    """The real thing: two processes, two GPUs, engines joined by nds_engine_comm_init, every query of the subset
+    through Session.sql() with the exchange in device memory - compared with the oracle on rank 0.  Skipped on a
+    one-GPU box (run it with `gpurun --gpus 2`)."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs two GPUs')
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, NDS_TEST_WAREHOUSE=warehouse)
+    r = subprocess.run([sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2', '--master-addr', '127.0.0.1',
+                        '--master-port', '29533', os.path.join(root, 'tests', 'nccl_exchange_worker.py')],
+                       cwd=root, env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert 'EXCHANGE-OK 6' in r.stdout
