@@ -137,6 +137,8 @@ struct OpStat {
   int64_t bytes = 0;            // algorithmic bytes
   int64_t rows = 0;
   double host_ms = 0;           // wall-clock time the host spent inside this operator (launch + bookkeeping)
+  int64_t row_bytes = 0, fixed_bytes = 0;   // bytes = fixed_bytes + rows * row_bytes once the device-side count is known
+  const int* n_dev = nullptr;
   double t0 = 0;
   cudaEvent_t e0 = nullptr, e1 = nullptr;
 };

@@ -315,6 +315,31 @@ struct Exec {
     if (stats[i].e1) NDS_CUDA(cudaEventRecord(stats[i].e1, s));
   }
 
+  // Algorithmic bytes of a row-at-a-time operator = rows x (bytes of the column slots its programs read: values at
+  // their width, 4 B per row-map hop, 1 bit of validity) + what it writes per row.  The row count may only exist on
+  // the device; in profile mode it is read back after the query (resolve_stat_rows) and the product is formed then.
+  static int64_t row_bytes_of(const Blob& bb) {
+    int64_t b = 0;
+    for (const ColRef& c : bb.cols) b += (c.dtype == DT_I32 ? 4 : 8) + (c.rowmap ? 4 : 0);
+    return b;
+  }
+  void end_stat_rows(size_t i, int64_t row_bytes, RowCount rows, int64_t fixed_bytes = 0) {
+    stats[i].row_bytes = row_bytes;
+    stats[i].n_dev = rows.dev;
+    end_stat(i, fixed_bytes + rows.host * row_bytes, rows.host);
+    stats[i].fixed_bytes = fixed_bytes;
+  }
+  void resolve_stat_rows() {
+    for (OpStat& st : stats) {
+      if (!st.n_dev || st.row_bytes <= 0) continue;
+      int v = 0;
+      if (cudaMemcpy(&v, st.n_dev, 4, cudaMemcpyDeviceToHost) != cudaSuccess) { cudaGetLastError(); continue; }
+      const int64_t n = std::min<int64_t>(v, st.rows);
+      st.rows = n;
+      st.bytes = st.fixed_bytes + n * st.row_bytes;
+    }
+  }
+
   void check_err() {
     int h[4];
     NDS_CUDA(cudaMemcpyAsync(h, err, sizeof h, cudaMemcpyDeviceToHost, s));
@@ -644,6 +669,21 @@ struct Exec {
     std::vector<int64_t> vr_off;                      // per task: offset of its validity/rank scratch (words) or -1
     int64_t vr_words = 0;
     int64_t bytes_in = 0, bytes_out = 0;
+    {
+      // one pass to size the task vectors: growing them page by page costs more than filling them
+      size_t npages = 0;
+      for (const Json& c : jc.a) {
+        auto ci = t.col_index.find(c.s);
+        if (ci == t.col_index.end()) continue;
+        const TableColumn& tc = t.cols[ci->second];
+        for (int f : sel) npages += (size_t)(tc.file_page_begin[f + 1] - tc.file_page_begin[f]);
+      }
+      tasks.reserve(npages);
+      vr_off.reserve(npages);
+      def_idx.reserve(npages);
+      rows_idx.reserve(npages);
+      gen_idx.reserve(npages);
+    }
     for (const Json& c : jc.a) {
       const std::string& cname = c.s;
       Column col;
@@ -729,7 +769,8 @@ struct Exec {
             last_dict = pi.dict;
             bytes_in += (int64_t)tc.dicts[pi.dict].count * (tc.phys == pq::BYTE_ARRAY ? 8 : width);
           }
-          PageTask task;
+          tasks.emplace_back();
+          PageTask& task = tasks.back();
           memset(&task, 0, sizeof task);
           task.src = src_base + pi.off;
           task.out = d_out;
@@ -741,15 +782,16 @@ struct Exec {
           task.src_off = (uint32_t)pi.off;
           task.enc = pi.enc;
           task.bw = pi.bw;
+          const int tix = (int)tasks.size() - 1;
           if (pi.fast && split_decode) {
-            rows_idx.push_back((int)tasks.size());
+            rows_idx.push_back(tix);
             if (d_valid) {
-              def_idx.push_back((int)tasks.size());
+              def_idx.push_back(tix);
               vr_off.push_back(vr_words);
               vr_words += 2 * (((int64_t)pi.num_values + 31) / 32) + 1;
             } else vr_off.push_back(-1);
           } else {
-            gen_idx.push_back((int)tasks.size());
+            gen_idx.push_back(tix);
             vr_off.push_back(-1);
           }
           task.width = (uint8_t)width;
@@ -758,7 +800,6 @@ struct Exec {
             task.dict = src_base + tc.dicts[pi.dict].off;
             task.dict_count = tc.dicts[pi.dict].count;
           }
-          tasks.push_back(task);
           bytes_in += pi.size;
         }
       }
@@ -846,6 +887,7 @@ struct Exec {
     if (t.kind != LType::BOOL) fail("plan: filter condition is not boolean");
     bb.add_prog(code, t);
     Blob::Dev dev = bb.upload(ar, s);
+    const int64_t filter_row_bytes = row_bytes_of(bb);
     RowCount n = in.rc();
     uint32_t* sel = ar.alloc_n<uint32_t>(n.host);
     int* cnt = ar.zeros<int>(1);
@@ -861,7 +903,7 @@ struct Exec {
       o.rowmap = remap(c.rowmap, sel, nout, mc);
       out.cols.push_back(o);
     }
-    end_stat(st, 0, n.host);
+    end_stat_rows(st, filter_row_bytes + 4, n);
     return out;
   }
 
@@ -1182,7 +1224,7 @@ struct Exec {
         out.cols.push_back(o);
       }
     }
-    end_stat(stp, key_bytes, np.host);
+    end_stat_rows(stp, (np.host > 0 ? key_bytes / np.host : 0) + 4 * ((int64_t)chain.size() + 1), np);
     return out;
   }
 
@@ -1284,7 +1326,7 @@ struct Exec {
       c.valid = ovalid + (int64_t)a * vwords;
       out.cols.push_back(c);
     }
-    end_stat(st, 0, n);
+    end_stat_rows(st, row_bytes_of(bb) + 4 + 16 * (int64_t)std::max(naggs, 1), in.rc());   // + slot + aggregate states touched
     return out;
   }
 
@@ -1617,7 +1659,8 @@ struct Exec {
     } else {
       for (size_t c = 0; c < in.cols.size(); ++c) { Column e0 = in.cols[c]; e0.rowmap = nullptr; e0.valid = nullptr; e0.data = ar.alloc(16); out.cols.push_back(e0); }
     }
-    end_stat(st, 0, n);
+    (void)n;
+    end_stat_rows(st, row_bytes_of(bb) + 2 * (int64_t)B, in.rc());    // key columns read, encoded key written and read once
     return out;
   }
 
@@ -1947,6 +1990,7 @@ void Engine::execute_once(const Json& plan, ArrowSchema* out_schema, ArrowArray*
 
     NDS_CUDA(cudaEventRecord(ev1, stream_));
     ex.sync("sync:final");
+    if (ex.profile) ex.resolve_stat_rows();
     trace_ = ex.trace_out;
     launches_ = ex.launches;
     h2d_bytes_ = ex.h2d;

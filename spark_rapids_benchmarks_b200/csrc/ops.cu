@@ -303,44 +303,110 @@ __device__ __forceinline__ bool val_equal(const Val& a, const Val& b, int kind) 
   return a.v == b.v;
 }
 
+// Accumulation goes through a per-CTA cache in shared memory (pre-aggregation): a direct-mapped table of kAggCache
+// entries tagged with the global slot. A row whose slot owns (or can claim) its entry accumulates with shared-memory
+// atomics; the others go straight to the global table. At the end every CTA flushes its entries with one global atomic
+// per aggregate. Few groups (the NDS top-k queries: tens to thousands) -> almost every row stays in shared memory and
+// the same-address contention in L2 disappears; many groups -> the CTA notices that most rows miss and turns the
+// cache off for its remaining rows.
+constexpr int kAggCache = 256;
+__device__ __forceinline__ void agg_apply(int fn, int64_t* acc, int64_t* cnt, int64_t v) {
+  atomicAdd(reinterpret_cast<unsigned long long*>(cnt), 1ull);
+  if (fn == AGG_SUM_I) atomicAdd(reinterpret_cast<unsigned long long*>(acc), (unsigned long long)v);
+  else if (fn == AGG_MIN_I) atomicMin(reinterpret_cast<long long*>(acc), (long long)v);
+  else if (fn == AGG_MAX_I) atomicMax(reinterpret_cast<long long*>(acc), (long long)v);
+  else if (fn == AGG_SUM_F) atomicAdd(reinterpret_cast<double*>(acc), __longlong_as_double(v));
+}
+
 __global__ void __launch_bounds__(kThreads)
 agg_insert_kernel(const Prog* __restrict__ progs, int nkeys, const AggSpec* __restrict__ aggs, int naggs, OpCtx c,
-                  const int* n_dev, int64_t n_host, uint32_t* slots, uint32_t cap_max, int64_t* acc, int64_t* cnt) {
+                  const int* n_dev, int64_t n_host, uint32_t* slots, uint32_t cap_max, int64_t* acc, int64_t* cnt, int use_cache) {
+  extern __shared__ __align__(16) uint8_t agg_smem[];
+  uint32_t* c_tag = reinterpret_cast<uint32_t*>(agg_smem);                       // global slot + 1, 0 = free
+  int64_t* c_acc = reinterpret_cast<int64_t*>(agg_smem + kAggCache * 4);         // [naggs][kAggCache]
+  int64_t* c_cnt = c_acc + (int64_t)naggs * kAggCache;
+  __shared__ int s_seen, s_miss, s_off;
   const int64_t n = row_count(n_dev, n_host);
   const uint64_t cap = agg_capacity(n, cap_max);
   const uint32_t mask = (uint32_t)cap - 1u;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    Val mine[kMaxGroupKeys];
-    uint64_t h = 0x9E3779B97F4A7C15ULL;
-    for (int k = 0; k < nkeys; ++k) {
-      mine[k] = eval_program(progs[k].code, progs[k].n, c.cols, c.lit, i);
-      uint64_t hv = !mine[k].ok ? 0x7F4A7C15ULL
-                    : (progs[k].kind == 2 ? hash_bytes((const uint8_t*)(uintptr_t)mine[k].v, mine[k].len) : (uint64_t)mine[k].v);
-      h = mix64(h ^ hv) + 0x9E3779B97F4A7C15ULL * (k + 1);
+  if (use_cache) {
+    for (int e = threadIdx.x; e < kAggCache; e += blockDim.x) c_tag[e] = 0;
+    for (int k = threadIdx.x; k < naggs * kAggCache; k += blockDim.x) {
+      const int fn = aggs[k / kAggCache].fn;
+      c_acc[k] = fn == AGG_MIN_I ? INT64_MAX : (fn == AGG_MAX_I ? INT64_MIN : 0);
+      c_cnt[k] = 0;
     }
-    uint32_t s = (uint32_t)mix64(h) & mask;
-    for (;;) {
-      uint32_t prev = atomicCAS(&slots[s], 0u, (uint32_t)i + 1u);
-      if (prev == 0) break;
-      const int64_t rep = (int64_t)prev - 1;
-      bool same = true;
-      for (int k = 0; k < nkeys && same; ++k) {
-        Val o = eval_program(progs[k].code, progs[k].n, c.cols, c.lit, rep);
-        same = val_equal(mine[k], o, progs[k].kind);
+    if (threadIdx.x == 0) { s_seen = 0; s_miss = 0; s_off = 0; }
+    __syncthreads();
+  }
+  for (int64_t i0 = blockIdx.x * (int64_t)blockDim.x; i0 < n; i0 += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t i = i0 + threadIdx.x;
+    if (i < n) {
+      Val mine[kMaxGroupKeys];
+      uint64_t h = 0x9E3779B97F4A7C15ULL;
+      for (int k = 0; k < nkeys; ++k) {
+        mine[k] = eval_program(progs[k].code, progs[k].n, c.cols, c.lit, i);
+        uint64_t hv = !mine[k].ok ? 0x7F4A7C15ULL
+                      : (progs[k].kind == 2 ? hash_bytes((const uint8_t*)(uintptr_t)mine[k].v, mine[k].len) : (uint64_t)mine[k].v);
+        h = mix64(h ^ hv) + 0x9E3779B97F4A7C15ULL * (k + 1);
       }
-      if (same) break;
-      s = (s + 1) & mask;
+      uint32_t s = (uint32_t)mix64(h) & mask;
+      for (;;) {
+        uint32_t prev = atomicCAS(&slots[s], 0u, (uint32_t)i + 1u);
+        if (prev == 0) break;
+        const int64_t rep = (int64_t)prev - 1;
+        bool same = true;
+        for (int k = 0; k < nkeys && same; ++k) {
+          Val o = eval_program(progs[k].code, progs[k].n, c.cols, c.lit, rep);
+          same = val_equal(mine[k], o, progs[k].kind);
+        }
+        if (same) break;
+        s = (s + 1) & mask;
+      }
+      bool hit = false;
+      uint32_t e = 0;
+      if (use_cache && !s_off) {
+        e = (s ^ (s >> 8)) & (kAggCache - 1);
+        const uint32_t tag = atomicCAS(&c_tag[e], 0u, s + 1u);
+        hit = tag == 0u || tag == s + 1u;
+        if (!hit) atomicAdd(&s_miss, 1);
+      }
+      for (int a = 0; a < naggs; ++a) {
+        const AggSpec sp = aggs[a];
+        int64_t* pa = hit ? &c_acc[a * kAggCache + e] : &acc[a * cap + s];
+        int64_t* pc = hit ? &c_cnt[a * kAggCache + e] : &cnt[a * cap + s];
+        if (sp.fn == AGG_COUNT_STAR) { atomicAdd(reinterpret_cast<unsigned long long*>(pc), 1ull); continue; }
+        Val v = eval_program(progs[sp.prog].code, progs[sp.prog].n, c.cols, c.lit, i);
+        if (!v.ok) continue;
+        agg_apply(sp.fn, pa, pc, v.v);
+      }
     }
+    if (use_cache && !s_off) {
+      // after the first rounds: if most rows missed the cache this input has too many groups for it
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        s_seen += blockDim.x;
+        if (s_seen >= 4 * kAggCache && s_miss * 2 > s_seen) s_off = 1;
+      }
+      __syncthreads();
+    }
+  }
+  if (!use_cache) return;
+  __syncthreads();
+  for (int e = threadIdx.x; e < kAggCache; e += blockDim.x) {
+    const uint32_t tag = c_tag[e];
+    if (!tag) continue;
+    const uint64_t s = tag - 1u;
     for (int a = 0; a < naggs; ++a) {
-      const AggSpec sp = aggs[a];
-      if (sp.fn == AGG_COUNT_STAR) { atomicAdd(reinterpret_cast<unsigned long long*>(&cnt[a * cap + s]), 1ull); continue; }
-      Val v = eval_program(progs[sp.prog].code, progs[sp.prog].n, c.cols, c.lit, i);
-      if (!v.ok) continue;
-      atomicAdd(reinterpret_cast<unsigned long long*>(&cnt[a * cap + s]), 1ull);
-      if (sp.fn == AGG_SUM_I) atomicAdd(reinterpret_cast<unsigned long long*>(&acc[a * cap + s]), (unsigned long long)v.v);
-      else if (sp.fn == AGG_MIN_I) atomicMin(reinterpret_cast<long long*>(&acc[a * cap + s]), (long long)v.v);
-      else if (sp.fn == AGG_MAX_I) atomicMax(reinterpret_cast<long long*>(&acc[a * cap + s]), (long long)v.v);
-      else if (sp.fn == AGG_SUM_F) atomicAdd(reinterpret_cast<double*>(&acc[a * cap + s]), __longlong_as_double(v.v));
+      const int fn = aggs[a].fn;
+      const int64_t cv = c_cnt[a * kAggCache + e];
+      if (cv == 0) continue;
+      atomicAdd(reinterpret_cast<unsigned long long*>(&cnt[a * cap + s]), (unsigned long long)cv);
+      const int64_t av = c_acc[a * kAggCache + e];
+      if (fn == AGG_SUM_I) atomicAdd(reinterpret_cast<unsigned long long*>(&acc[a * cap + s]), (unsigned long long)av);
+      else if (fn == AGG_MIN_I) atomicMin(reinterpret_cast<long long*>(&acc[a * cap + s]), (long long)av);
+      else if (fn == AGG_MAX_I) atomicMax(reinterpret_cast<long long*>(&acc[a * cap + s]), (long long)av);
+      else if (fn == AGG_SUM_F) atomicAdd(reinterpret_cast<double*>(&acc[a * cap + s]), __longlong_as_double(av));
     }
   }
 }
@@ -378,7 +444,11 @@ void launch_agg_init(const AggSpec* aggs, int naggs, RowCount n, uint32_t cap_ma
 }
 void launch_agg_insert(const Prog* progs, int nkeys, const AggSpec* aggs, int naggs, OpCtx c, RowCount n, uint32_t* slots,
                        uint32_t cap_max, int64_t* acc, int64_t* cnt, cudaStream_t s) {
-  agg_insert_kernel<<<grid_for(n.host), kThreads, 0, s>>>(progs, nkeys, aggs, naggs, c, n.dev, n.host, slots, cap_max, acc, cnt);
+  // shared-memory pre-aggregation needs 16 B per aggregate and cache entry; beyond 48 KB it is simply not used
+  const size_t smem = (size_t)kAggCache * 4 + (size_t)std::max(naggs, 1) * kAggCache * 16;
+  const int use_cache = smem <= 48 * 1024 ? 1 : 0;
+  agg_insert_kernel<<<grid_for(n.host), kThreads, use_cache ? smem : 0, s>>>(progs, nkeys, aggs, naggs, c, n.dev, n.host, slots, cap_max,
+                                                                            acc, cnt, use_cache);
   NDS_CUDA(cudaGetLastError());
 }
 void launch_agg_finalize(const AggSpec* aggs, int naggs, const uint32_t* slots, uint32_t cap_max, RowCount n, const int64_t* acc,

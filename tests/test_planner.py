@@ -74,3 +74,38 @@ def test_parser_details():
     assert q['limit'] == 5 and q['from'] == [('t', 'a')] and q['select'][0][1] == 'y'
     assert q['order'][0][1] is True and q['order'][0][2] is True
     assert q['where'][0] == 'bin' and q['where'][1] == 'or'
+
+
+def test_collect_matches_to_pylist():
+    """DataFrame.collect() converts columns through numpy / raw buffers; it must return exactly what pyarrow's
+    to_pylist() returns (ints, doubles, decimals, dates, strings, nulls, sliced and chunked arrays)."""
+    import datetime
+    import decimal
+    import numpy as np
+    import pyarrow as pa
+    from spark_rapids_benchmarks_b200.session import DataFrame, _column_to_pylist
+    rng = np.random.default_rng(3)
+    n = 257
+    mask = rng.random(n) < 0.2
+    cols = {
+        'i32': pa.array(rng.integers(-2**31, 2**31, n).astype(np.int32), mask=mask),
+        'i64': pa.array(rng.integers(-2**62, 2**62, n), mask=mask),
+        'i64nn': pa.array(rng.integers(-2**62, 2**62, n)),
+        'f64': pa.array(rng.normal(size=n), mask=mask),
+        'dec': pa.array([None if m else decimal.Decimal(int(v)).scaleb(-2) for v, m in zip(rng.integers(-10**15, 10**15, n), mask)], type=pa.decimal128(17, 2)),
+        'dec0': pa.array([decimal.Decimal(int(v)) for v in rng.integers(-10**6, 10**6, n)], type=pa.decimal128(7, 0)),
+        'str': pa.array([None if m else ('s%d-é中' % v if v % 3 else '') for v, m in zip(rng.integers(0, 1000, n), mask)], type=pa.string()),
+        'date': pa.array([None if m else datetime.date(1990, 1, 1) + datetime.timedelta(days=int(v)) for v, m in zip(rng.integers(0, 20000, n), mask)], type=pa.date32()),
+        'bool': pa.array(rng.random(n) < 0.5, mask=mask),      # falls back to to_pylist
+    }
+    t = pa.table(cols)
+    for variant in (t, t.slice(13, 100), pa.concat_tables([t.slice(0, 50), t.slice(200, 57)]), t.slice(0, 0)):
+        for name in variant.schema.names:
+            got = _column_to_pylist(variant.column(name))
+            exp = variant.column(name).to_pylist()
+            assert got == exp, name
+            assert [type(x) for x in got] == [type(x) for x in exp], name
+        rows = DataFrame(variant).collect()
+        assert len(rows) == variant.num_rows
+        if variant.num_rows:
+            assert tuple(rows[0]) == tuple(variant.column(c)[0].as_py() for c in variant.schema.names)

@@ -19,6 +19,9 @@ def main():
     ap.add_argument('--queries', default='')
     ap.add_argument('--no_profile', action='store_true')
     ap.add_argument('--decode_timing', action='store_true')
+    ap.add_argument('--subset_tables', action='store_true', help='generate / register only the tables the six queries read (large SF)')
+    ap.add_argument('--no_keep_host', action='store_true', help='no pinned host copy of the encoded pages (large SF)')
+    ap.add_argument('--summary', default='', help='write a per-operator summary (markdown) to this path')
     ap.add_argument('--trace', action='store_true', help='print the host timeline (marks and sync waits) of the last rep')
     a = ap.parse_args()
     import bench
@@ -31,12 +34,28 @@ def main():
         pass
     args = A()
     args.sf, args.sales_days, args.data_dir = a.sf, a.sales_days, ''
-    bench.ensure_data(args, print)
-    qd = bench.make_stream(args)
+    needed = ['store_sales', 'date_dim', 'item', 'customer_demographics', 'promotion', 'customer', 'customer_address', 'store']
     wh = bench.data_dir(args)
-    sess = Session('profile', device=0, keep_host=True)
-    for t in nds_schema.get_schemas(True):
+    if a.subset_tables:
+        from spark_rapids_benchmarks_b200 import datagen
+        wh = wh + '_subset'
+        t0 = time.time()
+        rows = datagen.ensure(wh, int(a.sf) if a.sf == int(a.sf) else a.sf, tables=needed, sales_days=a.sales_days)
+        print('warehouse %s ready in %.1f s (store_sales rows: %d)' % (wh, time.time() - t0, rows['store_sales']), flush=True)
+        from spark_rapids_benchmarks_b200 import nds_power, streams
+        sp = os.path.join(wh, 'query_0.sql')
+        if not os.path.exists(sp):
+            streams.generate_stream(sp, stream=0)
+        qd = nds_power.gen_sql_from_stream(sp)
+    else:
+        bench.ensure_data(args, print)
+        qd = bench.make_stream(args)
+    sess = Session('profile', device=0, keep_host=not a.no_keep_host)
+    t0 = time.time()
+    for t in (needed if a.subset_tables else nds_schema.get_schemas(True)):
         sess.register_table(t, os.path.join(wh, t))
+    print('registered in %.1f s' % (time.time() - t0), flush=True)
+    summary = {}
     names = [q for q in qd if not a.queries or q in a.queries.split(',')]
     for name in names:
         plan = planner.plan_sql(qd[name])
@@ -52,6 +71,30 @@ def main():
             print('   %-28s %9.3f ms (host %6.3f)  %12d B  %10d rows  %8.1f GB/s' % (o['op'][:28], o['ms'], o.get('host_ms', 0), o['bytes'], o['rows'], gbs))
         if a.trace:
             print_trace(st)
+        for o in st['ops']:
+            if o['ms'] > 0 and o['bytes'] > 0 and not o['op'].startswith('decode:'):
+                e = summary.setdefault(o['op'].split(':')[0], [0.0, 0, 0])
+                e[0] += o['ms']
+                e[1] += o['bytes']
+                e[2] += 1
+    if a.summary:
+        peak = 6557.8
+        try:
+            peak = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json'))).get('hbm_gbs', peak)
+        except Exception:
+            pass
+        lines = ['| operator | launches | total ms | algorithmic MB | achieved GB/s | fraction of %.1f GB/s |' % peak, '|---|---:|---:|---:|---:|---:|']
+        fr = []
+        for op, (ms, b, n) in sorted(summary.items(), key=lambda kv: -kv[1][0]):
+            g = b / (ms * 1e-3) / 1e9
+            fr.append(g / peak)
+            lines.append('| %s | %d | %.3f | %.1f | %.1f | %.3f |' % (op, n, ms, b / 1e6, g, g / peak))
+        fr.sort()
+        lines.append('')
+        lines.append('median operator fraction of the measured HBM peak: %.3f' % (fr[len(fr) // 2] if fr else 0.0))
+        with open(a.summary, 'w') as f:
+            f.write('\n'.join(lines) + '\n')
+        print('\n'.join(lines))
 
 
 def print_trace(st):
