@@ -239,13 +239,14 @@ def main():
                 ops.extend(st['ops'])
         return launches, ops, eng_ms
 
-    def e2e_step():
+    def e2e_step(collect=False):
         h2d = d2h = 0
         for name, sql in qd.items():
             sess.source = 'host'
             sess.sql(sql).collect()
-            h2d += sess.last_stats['h2d_bytes']
-            d2h += sess.last_stats['d2h_bytes']
+            if collect:
+                h2d += sess.last_stats['h2d_bytes']
+                d2h += sess.last_stats['d2h_bytes']
         return h2d, d2h
 
     # ---------------------------------------------------------------- warm-up (both paths)
@@ -264,11 +265,18 @@ def main():
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        l, o, m = resident_step(True)
+        resident_step(False)
         torch.cuda.synchronize()
         e1.record()
         torch.cuda.synchronize()
         total_ms += e0.elapsed_time(e1)
+    barrier()
+    # the same steps once more, untimed, to read the engine's statistics (kernel launches, per-operator events):
+    # fetching and parsing them costs ~0.1 ms per query and does not belong in the timed region
+    for _ in range(args.steps):
+        flush.zero_()
+        barrier()
+        l, o, m = resident_step(True)
         launches += l
         ops.extend(o)
         eng_ms += m
@@ -280,9 +288,12 @@ def main():
         flush.zero_()
         barrier()
         t1 = time.perf_counter()
-        a, b = e2e_step()
+        e2e_step()
         torch.cuda.synchronize()
         t_e2e += time.perf_counter() - t1
+    barrier()
+    for _ in range(args.steps):          # bytes moved per step: from an identical untimed repeat (see above)
+        a, b = e2e_step(True)
         h2d += a
         d2h += b
     barrier()
@@ -367,6 +378,7 @@ def main():
             'config': {'workload': WORKLOAD, 'sf': args.sf, 'store_sales_rows_per_rank': info['rows'], 'files_per_rank': info['files'],
                        'l2': 'flushed (512 MiB write) before every timed step', 'partition_pruning': True,
                        'table_registration_s': setup_s, 'engine_device_ms_per_step': eng_ms / args.steps,
+                       'gpu_launches_counted': 'in an identical untimed repeat of the timed steps',
                        'parallelism': 'fact files sharded over %d GPU(s), dimensions replicated' % world},
             'e2e': {'value': e2e_s, 'unit': 's', 'h2d_bytes_per_step': h2d // args.steps, 'd2h_bytes_per_step': d2h // args.steps},
             'gpu_launches': launches, 'roofline': roof, 'cpu_baseline': cpu, 'clocks': clocks}

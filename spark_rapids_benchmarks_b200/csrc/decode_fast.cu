@@ -22,12 +22,15 @@ constexpr int kTR = 384;                 // rows kernel threads
 constexpr int kEntD = kDefSeg / kChunk;  // entries per resolved segment
 }  // namespace
 
-__global__ void __launch_bounds__(kTD)
+// STAGE = bytes of def-level stream a page may have in this instantiation: the 4 KB variant (every page a 20000-row
+// writer produces) leaves room for 13 CTAs per SM instead of 10, which is what this latency-bound kernel needs.
+template <int STAGE, int MINB>
+__global__ void __launch_bounds__(kTD, MINB)
 def_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ task_idx, int* __restrict__ err) {
   __shared__ uint32_t s_valid[kMaxPageValues / 32];
   __shared__ uint32_t ent_pos[kEntD + 1];
   __shared__ uint32_t ent_k[kEntD + 1];
-  __shared__ __align__(16) uint8_t s_stage[8192 + 48];
+  __shared__ __align__(16) uint8_t s_stage[STAGE + 48];
   __shared__ uint32_t s_hop[kDefSeg];
   __shared__ uint32_t s_long[64][2];
   __shared__ __align__(8) uint64_t s_mbar;
@@ -498,10 +501,11 @@ int rows_slices(int npages) {
   return ns;
 }
 
-void launch_decode_split(const PageTask* d_tasks, const int* d_def_idx, int ndef, const int* d_rows_idx, int nrows, int* d_err,
-                         cudaStream_t stream, int* launches) {
+void launch_decode_split(const PageTask* d_tasks, const int* d_def_idx, int ndef, int max_def_len, const int* d_rows_idx, int nrows,
+                         int* d_err, cudaStream_t stream, int* launches) {
   if (ndef > 0) {
-    def_pages_kernel<<<ndef, kTD, 0, stream>>>(d_tasks, d_def_idx, d_err);
+    if (max_def_len <= 4096) def_pages_kernel<4096, 13><<<ndef, kTD, 0, stream>>>(d_tasks, d_def_idx, d_err);
+    else def_pages_kernel<8192, 8><<<ndef, kTD, 0, stream>>>(d_tasks, d_def_idx, d_err);
     NDS_CUDA(cudaGetLastError());
     ++*launches;
   }

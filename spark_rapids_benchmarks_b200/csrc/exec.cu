@@ -831,7 +831,9 @@ struct Exec {
       // a dedicated pair of events brackets only the decode launches (roofline.achieved in bench.py)
       size_t ks = begin_stat("decode_kernel", true);
       int l = 0;
-      launch_decode_split(d_tasks, d_idx, (int)def_idx.size(), d_idx + def_idx.size(), (int)rows_idx.size(), err, s, &l);
+      int max_def_len = 0;
+      for (int ti : def_idx) max_def_len = std::max<int>(max_def_len, (int)tasks[ti].def_len);
+      launch_decode_split(d_tasks, d_idx, (int)def_idx.size(), max_def_len, d_idx + def_idx.size(), (int)rows_idx.size(), err, s, &l);
       launches += l;
       long long* dbg = nullptr;
       const int ngen = (int)gen_idx.size();

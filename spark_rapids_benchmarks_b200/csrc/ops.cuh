@@ -51,7 +51,7 @@ int decode_slices(int npages);
 // dbg (optional): 8 clock64 checkpoints per CTA, development aid
 void launch_decode_pages(const PageTask* d_tasks, const int* d_idx, int npages, int* d_err, cudaStream_t s, long long* dbg = nullptr);
 // decode_fast.cu: def kernel over d_def_idx pages, then rows kernel over d_rows_idx pages (indices into d_tasks)
-void launch_decode_split(const PageTask* d_tasks, const int* d_def_idx, int ndef, const int* d_rows_idx, int nrows, int* d_err,
+void launch_decode_split(const PageTask* d_tasks, const int* d_def_idx, int ndef, int max_def_len, const int* d_rows_idx, int nrows, int* d_err,
                          cudaStream_t s, int* launches);
 void launch_fill_segments(const int64_t* d_seg_start, const int64_t* d_seg_val, int nseg, int32_t* out, cudaStream_t s);
 

@@ -121,7 +121,7 @@ def execute_distributed(session, plan):
             payload = session.engine.encode_plan({'root': plan['fused']}, source=src)
             plan[key] = payload
         out = session.engine.execute(payload)
-        session.dist_stats = session.engine.last_stats()
+        session.dist_stats = None          # one engine call: Session.last_stats fetches its statistics on demand
         return out
     partial = session.engine.execute({'root': plan['partial']}, source=src)
     st = session.engine.last_stats()

@@ -22,6 +22,7 @@ def main():
     ap.add_argument('--subset_tables', action='store_true', help='generate / register only the tables the six queries read (large SF)')
     ap.add_argument('--no_keep_host', action='store_true', help='no pinned host copy of the encoded pages (large SF)')
     ap.add_argument('--summary', default='', help='write a per-operator summary (markdown) to this path')
+    ap.add_argument('--serial', action='store_true', help='one stream for every operator (kernel times without overlap)')
     ap.add_argument('--trace', action='store_true', help='print the host timeline (marks and sync waits) of the last rep')
     a = ap.parse_args()
     import bench
@@ -62,7 +63,7 @@ def main():
         for rep in range(a.reps):
             t0 = time.perf_counter()
             sess.engine.execute({'root': plan['root']}, source=None if a.source == 'hbm' else a.source, profile=not a.no_profile, decode_timing=a.decode_timing,
-                                options={'trace': True} if a.trace else None)
+                                options=dict(({'trace': True} if a.trace else {}), **({'side_stream': False} if a.serial else {})) or None)
             wall = (time.perf_counter() - t0) * 1e3
             st = sess.engine.last_stats()
         print('== %s: wall %.3f ms, device %.3f ms, host(execute) %.3f ms, launches %d, h2d %d' % (name, wall, st['device_ms'], st.get('host_ms', 0), st['launches'], st['h2d_bytes']))
