@@ -255,6 +255,20 @@ def main():
         out['time_log'] = {'header': lines[0], 'labels': [l.split(',')[1] for l in lines[1:]],
                            'reference_parsers_accept_it': True,
                            'n_rows': len(lines) - 1}
+        # ---- throughput test arithmetic (nds_bench.py:127-157, 207-208)
+        out['get_stream_range'] = [{'n': n, 'which': w, 'out': ref_bench.get_stream_range(n, w)}
+                                   for n in (3, 5, 9, 10) for w in (1, 2)]
+        out['round_up_to_nearest_10_percent'] = [{'in': v, 'out': ref_bench.round_up_to_nearest_10_percent(v)}
+                                                 for v in (0.0, 0.01, 1.0, 1.04, 1.05, 12.345, 99.91, 100.0)]
+        base = os.path.join(tmp, 'thr')
+        times = {1: (1000.25, 1010.5), 2: (1000.75, 1013.26), 3: (999.5, 1001.0), 4: (1002.0, 1012.0)}
+        for k, (a, b) in times.items():
+            with open(base + '_%d.csv' % k, 'w') as f:
+                f.write('application_id,query,time/milliseconds\n')
+                f.write('app,query1,12\napp,Power Start Time,%r\napp,Power End Time,%r\napp,Power Test Time,10\n' % (a, b))
+        out['get_throughput_time'] = {'times': {str(k): list(v) for k, v in times.items()},
+                                      'cases': [{'n': n, 'which': w, 'out': ref_bench.get_throughput_time(base, n, w)}
+                                                for n, w in ((5, 1), (5, 2), (3, 1))]}
     with open(os.path.join(HERE, 'reference_harness.json'), 'w') as f:
         json.dump(out, f, indent=1, sort_keys=True)
     print('wrote', os.path.join(HERE, 'reference_harness.json'), len(out['compare']), 'compare cases')

@@ -199,3 +199,31 @@ def test_exchange_over_nccl_two_gpus(warehouse, tmp_path):
                        cwd=root, env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert 'EXCHANGE-OK 6' in r.stdout
+
+
+def test_throughput_two_streams_share_one_gpu(warehouse, tmp_path):
+    """Throughput mode (reference `nds-throughput`): two power-run processes at once on one GPU, each with its own
+    engine and stream; both must complete, both results must equal the oracle's, and the elapsed time comes out of the
+    two time logs the way nds_bench computes it."""
+    import subprocess
+    import sys
+    import pyarrow.parquet as pq
+    from spark_rapids_benchmarks_b200 import nds_throughput as thr
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    params = {1: PARAMS[0], 2: PARAMS[1]}
+    for k, ov in params.items():
+        streams.generate_stream(str(tmp_path / ('query_%d.sql' % k)), stream=k, overrides=ov)
+    r = subprocess.run([sys.executable, '-m', 'spark_rapids_benchmarks_b200.nds_throughput', '1,2',
+                        sys.executable, '-m', 'spark_rapids_benchmarks_b200.nds_power', warehouse, str(tmp_path / 'query_{}.sql'),
+                        str(tmp_path / 'time_{}.csv'), '--output_prefix', str(tmp_path / 'out_{}')],
+                       capture_output=True, text=True, cwd=root)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    for k in (1, 2):
+        qd = nds_power.gen_sql_from_stream(str(tmp_path / ('query_%d.sql' % k)))
+        assert len(qd) == len(streams.SUBSET)
+        for q, sql in qd.items():
+            got = pq.ParquetDataset(str(tmp_path / ('out_%d' % k) / q)).read()
+            exp = oq.run_query(q, sql, warehouse)
+            assert rows_equal(got.to_pylist(), [dict(zip(got.schema.names, row.values())) for row in exp.to_pylist()]), (k, q)
+    elapsed = thr.get_throughput_time(str(tmp_path / 'time'), 5, 1)        # 5 streams in total -> first test = streams 1, 2
+    assert 0 < elapsed < 600 and abs(elapsed * 10 - round(elapsed * 10)) < 1e-9

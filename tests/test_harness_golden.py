@@ -220,3 +220,41 @@ def test_validate_two_outputs(tmp_path):
         assert nds_validate.main([str(tmp_path / 'r1'), str(tmp_path / 'r2'), str(p)]) != []
         assert nds_validate.main([str(tmp_path / 'r1'), str(tmp_path / 'r3'), str(p), '--sub_queries', 'query3']) == ['query3']
         assert nds_validate.main([str(tmp_path / 'r1'), str(tmp_path / 'r3'), str(p), '--sub_queries', 'query3', '--epsilon', '0.1']) == []
+
+
+def test_throughput_arithmetic_matches_reference(tmp_path):
+    """nds_throughput's stream ranges, rounding and elapsed time against values recorded from the reference's
+    nds_bench.py (get_stream_range, round_up_to_nearest_10_percent, get_throughput_time)."""
+    from spark_rapids_benchmarks_b200 import nds_throughput as thr
+    for c in G['get_stream_range']:
+        assert thr.get_stream_range(c['n'], c['which']) == c['out'], c
+    for c in G['round_up_to_nearest_10_percent']:
+        assert thr.round_up_to_nearest_10_percent(c['in']) == c['out'], c
+    base = str(tmp_path / 'thr')
+    for k, (a, b) in G['get_throughput_time']['times'].items():
+        with open(base + '_%s.csv' % k, 'w') as f:
+            f.write('application_id,query,time/milliseconds\n')
+            f.write('app,query1,12\napp,Power Start Time,%r\napp,Power End Time,%r\napp,Power Test Time,10\n' % (a, b))
+    for c in G['get_throughput_time']['cases']:
+        assert thr.get_throughput_time(base, c['n'], c['which']) == c['out'], c
+
+
+def test_throughput_runner_substitutes_and_reports_failures(tmp_path):
+    """`nds_throughput 1,2,3 <cmd with {}>`: one process per stream, `{}` replaced everywhere, all run concurrently,
+    exit code 123 when any stream fails (what xargs returns for the reference script)."""
+    import subprocess
+    import sys
+    import time
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = tmp_path / 'w.py'
+    script.write_text('import sys, time\nopen(sys.argv[1], "w").write(sys.argv[2]); time.sleep(1.0); sys.exit(int(sys.argv[3]))\n')
+    t0 = time.time()
+    r = subprocess.run([sys.executable, '-m', 'spark_rapids_benchmarks_b200.nds_throughput', '1,2,3', sys.executable, str(script),
+                        str(tmp_path / 'out_{}.txt'), 's{}', '0'], cwd=root, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert time.time() - t0 < 2.9            # three one-second streams ran side by side
+    assert r.stdout.splitlines()[0] == '3'
+    assert [(tmp_path / ('out_%d.txt' % k)).read_text() for k in (1, 2, 3)] == ['s1', 's2', 's3']
+    r = subprocess.run([sys.executable, '-m', 'spark_rapids_benchmarks_b200.nds_throughput', '7', sys.executable, str(script),
+                        str(tmp_path / 'f_{}.txt'), 'x', '5'], cwd=root, capture_output=True, text=True)
+    assert r.returncode == 123
