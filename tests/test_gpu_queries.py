@@ -226,4 +226,5 @@ def test_throughput_two_streams_share_one_gpu(warehouse, tmp_path):
             exp = oq.run_query(q, sql, warehouse)
             assert rows_equal(got.to_pylist(), [dict(zip(got.schema.names, row.values())) for row in exp.to_pylist()]), (k, q)
     elapsed = thr.get_throughput_time(str(tmp_path / 'time'), 5, 1)        # 5 streams in total -> first test = streams 1, 2
-    assert 0 < elapsed < 600 and abs(elapsed * 10 - round(elapsed * 10)) < 1e-9
+    # the time log carries whole epoch seconds (like the reference's), so two sub-second streams may give 0.0
+    assert 0 <= elapsed < 600 and abs(elapsed * 10 - round(elapsed * 10)) < 1e-9
