@@ -48,8 +48,8 @@ decode_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ 
   __shared__ uint32_t ent_k[kEntCap + 1];
   __shared__ uint32_t early_k[kEarlyCap + 1];
   __shared__ uint32_t early_info[kEarlyCap];
-  __shared__ __align__(16) uint8_t s_stage[kStage + 48];
-  __shared__ uint32_t s_hop[kDefSeg];                       // (exit position << 16) | values emitted
+  __shared__ __align__(16) uint8_t s_stage[kStage + 96];
+  __shared__ uint32_t s_hop[kHopWords];                       // (exit position << 16) | values emitted
   __shared__ uint32_t s_long[64][2];                        // long RLE runs of 1s, filled cooperatively
   __shared__ __align__(8) uint64_t s_mbar;
   __shared__ __align__(8) uint64_t s_mbar_dict;

@@ -10,6 +10,10 @@ constexpr int kWords = kMaxPageValues / 32;
 constexpr int kStage = 16384;            // bytes of one hybrid stream staged in shared memory
 constexpr int kEntCap = 1024;            // header entries (position, first value index) per batch
 constexpr int kDefSeg = 2048;            // byte positions resolved per segment of the parallel header walk
+// The hop table has one word per byte position and is written by one thread per 32-position chunk: stored plainly,
+// the 32 lanes of a warp would hit one bank on every access. One pad word per 32 positions spreads them over all banks.
+constexpr int kHopWords = kDefSeg + kDefSeg / 32 + 2;
+__device__ __forceinline__ uint32_t hop_ix(uint32_t x) { return x + (x >> 5); }
 constexpr int kChunk = 32;               // bytes per chunk of the parallel header walk
 constexpr int kUnroll = 4;
 constexpr int kDictStage = 65536;        // dictionary bytes staged in (dynamic) shared memory; larger ones are gathered from L2
@@ -22,6 +26,9 @@ __device__ __forceinline__ uint32_t lds8(uint32_t a) {
   return v;
 }
 
+__device__ __forceinline__ void lds128(uint32_t a, uint32_t& x, uint32_t& y, uint32_t& z, uint32_t& w) {
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(x), "=r"(y), "=r"(z), "=r"(w) : "r"(a));
+}
 __device__ __forceinline__ uint32_t lds32(uint32_t a) {
   uint32_t v;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
@@ -222,7 +229,8 @@ __device__ __forceinline__ void bar_sync(int id, int nthr) { asm volatile("bar.s
 // sd: shared-window address of stream byte 0, L bytes long. Starting at header position w->pos with w->k values
 // covered, resolves up to kDefSeg byte positions: appends (position, first value index) of the first header of every
 // entered kChunk-byte chunk to ent_pos/ent_k (at most kDefSeg/kChunk new entries) and advances *w.
-// Called by the first bar_n threads of the CTA (they synchronise on named barrier bar_id); s_hop is kDefSeg words of scratch.
+// Called by the first bar_n threads of the CTA (they synchronise on named barrier bar_id); s_hop is kHopWords words of scratch;
+// the staging buffer behind sd must be readable up to 64 bytes past the stream's end.
 __device__ __forceinline__ void resolve_segment(uint32_t sd, uint32_t L, uint32_t bw, uint32_t limit, Walker* w, uint32_t* s_hop,
                                                 uint32_t* ent_pos, uint32_t* ent_k, int* n_ent, int tid, int bar_id, int bar_n,
                                                 long long* dbg = nullptr) {
@@ -235,9 +243,32 @@ __device__ __forceinline__ void resolve_segment(uint32_t sd, uint32_t L, uint32_
   // are loaded up front so that the per-position chain is ALU + one hop-table load.
   if ((uint32_t)tid < nchunks) {
     const uint32_t cb = seg0 + tid * kChunk, ce = min(cb + (uint32_t)kChunk, seg1);
+    // The chunk's 34 bytes come in as four aligned 16-byte loads (byte loads at a 32-byte stride between lanes are
+    // 8-way bank conflicts, 34 times over); the stream's misalignment m - the same for every lane - is removed with a
+    // barrel shift over the 16 words, after which every byte sits at a compile-time register and shift.
+    uint32_t A[17];
+    {
+      const uint32_t a0 = (sd + cb) & ~15u, m = (sd + cb) & 15u;
+      lds128(a0, A[0], A[1], A[2], A[3]);
+      lds128(a0 + 16, A[4], A[5], A[6], A[7]);
+      lds128(a0 + 32, A[8], A[9], A[10], A[11]);
+      lds128(a0 + 48, A[12], A[13], A[14], A[15]);
+      A[16] = 0;
+      if (m & 8) {
+#pragma unroll
+        for (int i = 0; i < 15; ++i) A[i] = A[i + 2];
+      }
+      if (m & 4) {
+#pragma unroll
+        for (int i = 0; i < 14; ++i) A[i] = A[i + 1];
+      }
+      const uint32_t sh = (m & 3u) * 8u;
+#pragma unroll
+      for (int i = 0; i < 9; ++i) A[i] = __funnelshift_r(A[i], A[i + 1], sh);
+    }
     uint32_t by[kChunk + 2];
 #pragma unroll
-    for (int j = 0; j < kChunk + 2; ++j) by[j] = cb + j < L ? lds8(sd + cb + j) : 0u;
+    for (int j = 0; j < kChunk + 2; ++j) by[j] = cb + j < L ? ((A[j >> 2] >> ((j & 3) * 8)) & 0xFFu) : 0u;
 #pragma unroll
     for (int j = kChunk - 1; j >= 0; --j) {
       const uint32_t p = cb + j;
@@ -256,12 +287,12 @@ __device__ __forceinline__ void resolve_segment(uint32_t sd, uint32_t L, uint32_
         uint32_t nxt = p + hl + ((h & 1) ? (h >> 1) * bw : bytew);
         if (nxt > L || nxt <= p) nxt = L;
         if (nxt < ce) {
-          uint32_t f = s_hop[nxt - seg0];
+          uint32_t f = s_hop[hop_ix(nxt - seg0)];
           cnt += f & 0xFFFFu;
           nxt = f >> 16;
         }
         if (cnt > 0xFFFFu) cnt = 0xFFFFu;
-        s_hop[p - seg0] = (nxt << 16) | cnt;
+        s_hop[hop_ix(p - seg0)] = (nxt << 16) | cnt;
       }
     }
   }
@@ -275,7 +306,7 @@ __device__ __forceinline__ void resolve_segment(uint32_t sd, uint32_t L, uint32_
       ent_pos[ne] = p;
       ent_k[ne] = k;
       ++ne;
-      uint32_t f = s_hop[p - seg0];
+      uint32_t f = s_hop[hop_ix(p - seg0)];
       k += f & 0xFFFFu;
       p = f >> 16;
     }

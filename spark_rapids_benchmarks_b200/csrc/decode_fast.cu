@@ -30,8 +30,8 @@ def_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ tas
   __shared__ uint32_t s_valid[kMaxPageValues / 32];
   __shared__ uint32_t ent_pos[kEntD + 1];
   __shared__ uint32_t ent_k[kEntD + 1];
-  __shared__ __align__(16) uint8_t s_stage[STAGE + 48];
-  __shared__ uint32_t s_hop[kDefSeg];
+  __shared__ __align__(16) uint8_t s_stage[STAGE + 96];
+  __shared__ uint32_t s_hop[kHopWords];
   __shared__ uint32_t s_long[64][2];
   __shared__ __align__(8) uint64_t s_mbar;
   __shared__ int s_nlong;
@@ -111,8 +111,8 @@ def_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ tas
         const uint32_t cnt = packed ? (h >> 1) * 8 : (h >> 1);
         const uint32_t info = packed ? (((p + hl) << 1) | 1u) : ((lds8(def_sd + p + hl) & 1u) << 1);
         if (r < 16) {
-          s_hop[(tid * 16 + r) * 2] = k;
-          s_hop[(tid * 16 + r) * 2 + 1] = (min(cnt, 0xFFFFu) << 16) | (info & 0xFFFFu);
+          s_hop[tid * 33 + r * 2] = k;                 // 33-word rows: lanes write different banks
+          s_hop[tid * 33 + r * 2 + 1] = (min(cnt, 0xFFFFu) << 16) | (info & 0xFFFFu);
         } else {              // degenerate zero-length runs overflowed the chunk's slots: expand in place
           const uint32_t k1 = min(k + cnt, n);
           if (info & 1) copy_bits(s_valid, def_sd + (info >> 1), nullptr, k, k1);
@@ -127,7 +127,8 @@ def_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ tas
     __syncthreads();
     for (uint32_t idx = tid; idx < (uint32_t)ne * 16; idx += kTD) {
       if ((idx & 15) >= ent_k[idx >> 4]) continue;
-      const uint32_t k = s_hop[idx * 2], ci = s_hop[idx * 2 + 1];
+      const uint32_t hx = (idx >> 4) * 33 + (idx & 15) * 2;
+      const uint32_t k = s_hop[hx], ci = s_hop[hx + 1];
       const uint32_t info = ci & 0xFFFFu;
       const uint32_t k1 = min(k + (ci >> 16), n);
       if (info & 1) copy_bits(s_valid, def_sd + (info >> 1), nullptr, k, k1);
