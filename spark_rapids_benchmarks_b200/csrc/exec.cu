@@ -1092,12 +1092,26 @@ struct Exec {
     return bs;
   }
 
-  // scans, filters and projections only: such a subtree reads nothing another operator of the query produces
+  // scans, filters, projections and joins between them: such a subtree reads nothing another operator of the query
+  // produces (a join inside it stays on the stream the subtree was given)
   static bool independent_subtree(const Json& node) {
     const std::string& op = node.str("op");
     if (op == "scan") return true;
     if (op == "filter" || op == "project") return independent_subtree(node.at("child"));
+    if (op == "join") return !node.bool_or("prune_partitions", false) && independent_subtree(node.at("probe")) && independent_subtree(node.at("build"));
     return false;
+  }
+
+  // rows of the table a scan/filter/project subtree reads (0 when it is something else): an estimate of its cost
+  int64_t subtree_rows(const Json& node) const {
+    const std::string& op = node.str("op");
+    if (op == "scan") {
+      auto it = e.tables_.find(node.str("table"));
+      return it == e.tables_.end() ? 0 : it->second.rows;
+    }
+    if (op == "filter" || op == "project") return subtree_rows(node.at("child"));
+    if (op == "join") return subtree_rows(node.at("probe")) + subtree_rows(node.at("build"));
+    return 0;
   }
 
   // column names a plan subtree produces (static; used to decide whether a join chain can be fused)
@@ -1170,20 +1184,46 @@ struct Exec {
     // Neither the build sides nor the base scan depend on one another: each runs on a stream of its own (round
     // robin over the engine's side streams) and the main stream waits for all of them before the probe pass. Their
     // kernels are small-grid and latency-bound, so they overlap almost completely.
+    // Issue order: the pruning build sides first (their keys start travelling to the host), then the other build sides
+    // from the largest table down - and the base scan as soon as the pruning keys have arrived (polled after every
+    // build side; issuing it earlier would make the host wait for them), so that the scan of the fact table, usually
+    // the longest piece of the query, is not queued behind the issue time of every dimension.
     sides.resize(chain.size());
     int lane_no = 0;
-    for (int pass = 0; pass < 2; ++pass)
-      for (size_t j = 0; j < chain.size(); ++j)
-        if (chain[j]->bool_or("prune_partitions", false) == (pass == 0)) {
-          const bool side = side_stream && independent_subtree(chain[j]->at("build"));
-          if (side) enter_side(lane_no++);
-          sides[j] = build_side(*chain[j], down);
-          if (side) leave_side();
-        }
-    const bool side = side_stream && independent_subtree(base_node);
-    if (side) enter_side(lane_no++);
-    Batch base = exec(base_node, down);
-    if (side) leave_side();
+    std::vector<size_t> order;
+    for (size_t j = 0; j < chain.size(); ++j)
+      if (chain[j]->bool_or("prune_partitions", false)) order.push_back(j);
+    const size_t npruning = order.size();
+    for (size_t j = 0; j < chain.size(); ++j)
+      if (!chain[j]->bool_or("prune_partitions", false)) order.push_back(j);
+    std::stable_sort(order.begin() + npruning, order.end(), [&](size_t a, size_t b) {
+      return subtree_rows(chain[a]->at("build")) > subtree_rows(chain[b]->at("build"));
+    });
+    Batch base;
+    bool base_done = false;
+    auto issue_base = [&]() {
+      const bool side = side_stream && independent_subtree(base_node);
+      if (side) enter_side(lane_no++);
+      base = exec(base_node, down);
+      if (side) leave_side();
+      base_done = true;
+    };
+    auto pruning_keys_arrived = [&]() {
+      for (const RuntimeFilter& f : down) {
+        const RuntimeFilter::State& t = *f.st;
+        if (!t.ready && t.ev && cudaEventQuery(t.ev) != cudaSuccess) { cudaGetLastError(); return false; }
+      }
+      return true;
+    };
+    for (size_t k = 0; k < order.size(); ++k) {
+      const size_t j = order[k];
+      if (!base_done && k >= npruning && side_stream && pruning_keys_arrived()) issue_base();
+      const bool side = side_stream && independent_subtree(chain[j]->at("build"));
+      if (side) enter_side(lane_no++);
+      sides[j] = build_side(*chain[j], down);
+      if (side) leave_side();
+    }
+    if (!base_done) issue_base();
     size_t stp = begin_stat("join_probe_chain");
     RowCount np = base.rc();
     ProbeChain pc;
