@@ -232,6 +232,7 @@ struct Exec {
   bool decode_timing = false;
   bool split_decode = true;      // options.split_decode=false forces every page through the general kernel
   bool side_stream = true;       // options.side_stream=false keeps every operator on one stream
+  int64_t small_scan_pages = 64; // options.small_scan_pages: scans with fewer split-route pages use the general kernel only
   bool speculate = true;         // options.speculate=false: never size a launch on an unverified device-side count
   bool trace = false;            // options.trace: host timeline marks + time spent waiting in each stream sync
   double t_base = 0;
@@ -255,6 +256,7 @@ struct Exec {
       trace = options->bool_or("trace", false);
       side_stream = options->bool_or("side_stream", true);
       speculate = options->bool_or("speculate", true);
+      small_scan_pages = options->int_or("small_scan_pages", 64);
     }
     t_base = now_ms();
     if (!e.side_streams_.empty() && side_stream) {
@@ -808,7 +810,7 @@ struct Exec {
     }
     if (!tasks.empty()) {
       // a scan of a few pages is latency-bound: one general launch beats a def + rows (+ general) sequence
-      if (rows_idx.size() < 64) {
+      if ((int64_t)rows_idx.size() < small_scan_pages) {
         gen_idx.clear();
         for (size_t k = 0; k < tasks.size(); ++k) gen_idx.push_back((int)k);
         def_idx.clear();

@@ -23,6 +23,7 @@ def main():
     ap.add_argument('--no_keep_host', action='store_true', help='no pinned host copy of the encoded pages (large SF)')
     ap.add_argument('--summary', default='', help='write a per-operator summary (markdown) to this path')
     ap.add_argument('--serial', action='store_true', help='one stream for every operator (kernel times without overlap)')
+    ap.add_argument('--opt', action='append', default=[], help='engine option key=int (repeatable), e.g. small_scan_pages=0')
     ap.add_argument('--trace', action='store_true', help='print the host timeline (marks and sync waits) of the last rep')
     a = ap.parse_args()
     import bench
@@ -63,12 +64,16 @@ def main():
         for rep in range(a.reps):
             t0 = time.perf_counter()
             sess.engine.execute({'root': plan['root']}, source=None if a.source == 'hbm' else a.source, profile=not a.no_profile, decode_timing=a.decode_timing,
-                                options=dict(({'trace': True} if a.trace else {}), **({'side_stream': False} if a.serial else {})) or None)
+                                options=dict(({'trace': True} if a.trace else {}), **({'side_stream': False} if a.serial else {}),
+                                             **{kv.split('=')[0]: int(kv.split('=')[1]) for kv in a.opt}) or None)
             wall = (time.perf_counter() - t0) * 1e3
             st = sess.engine.last_stats()
         print('== %s: wall %.3f ms, device %.3f ms, host(execute) %.3f ms, launches %d, h2d %d' % (name, wall, st['device_ms'], st.get('host_ms', 0), st['launches'], st['h2d_bytes']))
         for o in st['ops']:
             gbs = (o['bytes'] / (o['ms'] * 1e-3) / 1e9) if o['ms'] > 0 and o['bytes'] else 0
+            if o['op'].startswith('decode_phases') or o['op'].startswith('decode_routes'):
+                print('   ' + o['op'])
+                continue
             print('   %-28s %9.3f ms (host %6.3f)  %12d B  %10d rows  %8.1f GB/s' % (o['op'][:28], o['ms'], o.get('host_ms', 0), o['bytes'], o['rows'], gbs))
         if a.trace:
             print_trace(st)
