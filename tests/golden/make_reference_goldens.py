@@ -269,6 +269,21 @@ def main():
         out['get_throughput_time'] = {'times': {str(k): list(v) for k, v in times.items()},
                                       'cases': [{'n': n, 'which': w, 'out': ref_bench.get_throughput_time(base, n, w)}
                                                 for n, w in ((5, 1), (5, 2), (3, 1))]}
+        # ---- the reference's load-report parsers on a report written by THIS repo's nds_transcode
+        from spark_rapids_benchmarks_b200 import nds_transcode as my_transcode
+        rawdir = os.path.join(tmp, 'raw', 'store')
+        os.makedirs(rawdir)
+        ncol = len(__import__('spark_rapids_benchmarks_b200.nds_schema', fromlist=['x']).get_schemas(True)['store'].names)
+        with open(os.path.join(rawdir, 'store_1_1.dat'), 'w') as f:
+            f.write('|'.join(['1', 'AAAAAAAABAAAAAAA'] + [''] * (ncol - 2)) + '|\n')
+        rep = os.path.join(tmp, 'load_report.txt')
+        targs = my_transcode.build_parser().parse_args([os.path.join(tmp, 'raw'), os.path.join(tmp, 'wh'), rep, '--tables', 'store'])
+        with contextlib.redirect_stdout(io.StringIO()):
+            my_transcode.transcode(targs)
+        lt, seed = ref_bench.get_load_time(rep), ref_bench.get_load_end_timestamp(rep)
+        assert float(lt) >= 0 and seed.isdigit() and len(seed) == 11
+        out['load_report'] = {'reference_parsers_accept_it': True, 'rngseed_digits': len(seed),
+                              'first_line_prefix': open(rep).readline().split(':')[0]}
     with open(os.path.join(HERE, 'reference_harness.json'), 'w') as f:
         json.dump(out, f, indent=1, sort_keys=True)
     print('wrote', os.path.join(HERE, 'reference_harness.json'), len(out['compare']), 'compare cases')

@@ -258,3 +258,22 @@ def test_throughput_runner_substitutes_and_reports_failures(tmp_path):
     r = subprocess.run([sys.executable, '-m', 'spark_rapids_benchmarks_b200.nds_throughput', '7', sys.executable, str(script),
                         str(tmp_path / 'f_{}.txt'), 'x', '5'], cwd=root, capture_output=True, text=True)
     assert r.returncode == 123
+
+
+def test_load_report_is_what_the_reference_parsers_read(tmp_path):
+    """nds_transcode's report: first line `Load Test Time: <s> seconds`, an 11-digit `RNGSEED used:` line - the two
+    fields the reference's nds_bench.get_load_time / get_load_end_timestamp extract (recorded acceptance in G)."""
+    from spark_rapids_benchmarks_b200 import nds_schema, nds_transcode
+    assert G['load_report']['reference_parsers_accept_it'] is True
+    ncol = len(nds_schema.get_schemas(True)['store'].names)
+    raw = tmp_path / 'raw' / 'store'
+    raw.mkdir(parents=True)
+    (raw / 'store_1_1.dat').write_text('|'.join(['1', 'AAAAAAAABAAAAAAA'] + [''] * (ncol - 2)) + '|\n')
+    rep = str(tmp_path / 'report.txt')
+    args = nds_transcode.build_parser().parse_args([str(tmp_path / 'raw'), str(tmp_path / 'wh'), rep, '--tables', 'store'])
+    with contextlib.redirect_stdout(io.StringIO()):
+        nds_transcode.transcode(args)
+    lines = open(rep).read().split('\n')
+    assert lines[0].split(':')[0] == G['load_report']['first_line_prefix'] and lines[0].endswith(' seconds')
+    seed = [l for l in lines if 'RNGSEED used:' in l][0].split(':')[1].strip()
+    assert seed.isdigit() and len(seed) == G['load_report']['rngseed_digits']
