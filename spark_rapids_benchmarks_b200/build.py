@@ -31,7 +31,7 @@ def build(force=False, verbose=False):
     for src in SOURCES:
         obj = os.path.join(objdir, src + '.o')
         objs.append(obj)
-        cmd = [nvcc] + NVCC_FLAGS + ['-c', os.path.join(CSRC, src), '-o', obj]
+        cmd = [nvcc] + NVCC_FLAGS + os.environ.get('NDS_NVCC_EXTRA', '').split() + ['-c', os.path.join(CSRC, src), '-o', obj]   # NDS_NVCC_EXTRA: tuning experiments
         if verbose:
             print(' '.join(cmd))
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))

@@ -16,6 +16,12 @@
 namespace nds {
 using namespace dec;
 
+#ifndef NDS_UNIFORM_TB
+#define NDS_UNIFORM_TB 8
+#endif
+#ifndef NDS_ROWS_MINB
+#define NDS_ROWS_MINB 3
+#endif
 namespace {
 constexpr int kTD = 64;                  // def kernel threads
 constexpr int kTR = 384;                 // rows kernel threads
@@ -371,6 +377,53 @@ __device__ __forceinline__ void expand_dict(const RowsCtx& c, uint32_t tile0, ui
   }
 }
 
+// The index stream every writer produces for a high-cardinality column is UNIFORM: bit-packed runs of 63 groups (504
+// values, one header byte 0x7F) back to back, the last one shorter. Then value k sits at bit k * bw + 8 * (k / 504 + 1)
+// of the stream and no run cursor is needed at all: full 256-row blocks are straight-line code (null lanes fetch the
+// index of a neighbouring value, so the range check needs no validity), the page tail takes the general path above.
+template <int W, bool DEF, bool SDICT>
+__device__ __forceinline__ void expand_dict_uniform(const RowsCtx& c, uint32_t tile0, uint32_t tile1, int lane) {
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  const uint32_t kmax = (DEF ? c.s_r[c.nw] : c.n) - 1u;
+  const uint32_t dmax = c.dict_count - 1u;
+  const uint32_t off8 = c.vs_mis + 8u;
+  uint32_t mx = 0;
+  constexpr int TB = NDS_UNIFORM_TB;      // tiles per iteration: 2 * TB index loads in flight per thread
+  uint32_t bb = tile0;
+  if (kmax != 0xFFFFFFFFu) {
+    for (; bb + TB <= tile1 && (bb + TB) * 32 <= c.n; bb += TB) {
+      uint32_t ix[TB];
+      bool okv[TB];
+#pragma unroll
+      for (int u = 0; u < TB; ++u) {
+        const uint32_t tcur = bb + u;
+        uint32_t k = tcur * 32 + lane;
+        okv[u] = true;
+        if (DEF) {
+          const uint32_t wv = c.s_v[tcur];
+          k = min(c.s_r[tcur] + __popc(wv & lt_mask), kmax);
+          okv[u] = (wv >> lane) & 1u;
+        }
+        const uint32_t bit = k * c.bw + (k / 504u) * 8u + off8;
+        const uint32_t* wp = c.vwords + (bit >> 5);
+        ix[u] = __funnelshift_r(__ldg(wp), __ldg(wp + 1), bit & 31) & c.bwmask;
+      }
+      const int64_t row_base = c.orow + (int64_t)bb * 32 + lane;
+#pragma unroll
+      for (int u = 0; u < TB; ++u) {
+        mx = max(mx, ix[u]);
+        const uint32_t j = min(ix[u], dmax);
+        int64_t v;
+        if (SDICT) v = W == 4 ? (int64_t)(int32_t)lds32(c.dict_s + j * 4u) : lds64(c.dict_s + j * 8u);
+        else v = W == 4 ? (int64_t)__ldg(reinterpret_cast<const int32_t*>(c.dict) + j) : __ldg(reinterpret_cast<const int64_t*>(c.dict) + j);
+        store_out<W>(c.out, row_base + u * 32, okv[u] ? v : 0);
+      }
+    }
+    if (mx > dmax && c.err) atomicExch(c.err, 6);
+  }
+  if (bb < tile1) expand_dict<W, DEF, SDICT>(c, bb, tile1, lane);
+}
+
 template <int W, bool DEF>
 __device__ __forceinline__ void expand_plain(const RowsCtx& c, const uint8_t* vsrc, uint32_t tile0, uint32_t tile1, int lane) {
   const uint32_t lt_mask = (1u << lane) - 1u;
@@ -403,7 +456,7 @@ __device__ __forceinline__ void expand_plain(const RowsCtx& c, const uint8_t* vs
 
 }  // namespace
 
-__global__ void __launch_bounds__(kTR, 3)
+__global__ void __launch_bounds__(kTR, NDS_ROWS_MINB)
 rows_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ task_idx, int nslices, int* __restrict__ err) {
   __shared__ uint32_t s_v[kMaxPageValues / 32];
   __shared__ uint32_t s_r[kMaxPageValues / 32 + 1];
@@ -411,6 +464,7 @@ rows_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ ta
   __shared__ uint32_t early_info[kEarlyCap];
   __shared__ __align__(8) uint64_t s_mbar_dict;
   __shared__ int s_early_n;
+  __shared__ int s_uniform;
   extern __shared__ __align__(16) uint8_t s_dict[];
 
   const PageTask t = tasks[task_idx[blockIdx.x / nslices]];
@@ -429,6 +483,7 @@ rows_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ ta
 
   if (tid == 0) {
     s_early_n = 0;
+    s_uniform = 0;
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_mbar_dict)));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -445,7 +500,11 @@ rows_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ ta
     w.k = 0;
     int nr = walk_runs_warp(vstream, w, bw, n, kEarlyCap, 1 << 30, early_k, early_info);
     __syncwarp();
-    if (lane == 0) s_early_n = (w.pos >= VL || w.k >= n) ? nr : -1;
+    bool uni = nr > 0;
+    for (int e = lane; e < nr; e += 32)
+      uni = uni && early_k[e] == 504u * (uint32_t)e && early_info[e] == ((((uint32_t)e * (1u + 63u * bw) + 1u) << 1) | 1u);
+    uni = __all_sync(0xFFFFFFFFu, uni);
+    if (lane == 0) { s_early_n = (w.pos >= VL || w.k >= n) ? nr : -1; s_uniform = uni ? 1 : 0; }
   } else if (has_def) {
     // validity + rank words of my tiles (and the sentinel) from the def kernel's scratch
     const int nthr = (is_dict && bw > 0 && bw <= 32) ? kTR - 32 : kTR;
@@ -481,6 +540,11 @@ rows_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ ta
     const uint8_t* vsrc = t.src + values_off;
     if (t.width == 4) { if (has_def) expand_plain<4, true>(c, vsrc, tile0, tile1, lane); else expand_plain<4, false>(c, vsrc, tile0, tile1, lane); }
     else { if (has_def) expand_plain<8, true>(c, vsrc, tile0, tile1, lane); else expand_plain<8, false>(c, vsrc, tile0, tile1, lane); }
+    return;
+  }
+  if (s_uniform && t.dict_count && dict_staged) {        // the common case gets the cursor-free expansion
+    if (t.width == 4) { if (has_def) expand_dict_uniform<4, true, true>(c, tile0, tile1, lane); else expand_dict_uniform<4, false, true>(c, tile0, tile1, lane); }
+    else { if (has_def) expand_dict_uniform<8, true, true>(c, tile0, tile1, lane); else expand_dict_uniform<8, false, true>(c, tile0, tile1, lane); }
     return;
   }
   if (t.width == 4) {
