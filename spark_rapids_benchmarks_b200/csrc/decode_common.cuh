@@ -229,13 +229,15 @@ __device__ __forceinline__ void bar_sync(int id, int nthr) { asm volatile("bar.s
 // sd: shared-window address of stream byte 0, L bytes long. Starting at header position w->pos with w->k values
 // covered, resolves up to kDefSeg byte positions: appends (position, first value index) of the first header of every
 // entered kChunk-byte chunk to ent_pos/ent_k (at most kDefSeg/kChunk new entries) and advances *w.
+// SEG (default kDefSeg) = positions per call; s_hop needs SEG + SEG / 32 + 2 words (kHopWords for the default).
 // Called by the first bar_n threads of the CTA (they synchronise on named barrier bar_id); s_hop is kHopWords words of scratch;
 // the staging buffer behind sd must be readable up to 64 bytes past the stream's end.
+template <int SEG = kDefSeg>
 __device__ __forceinline__ void resolve_segment(uint32_t sd, uint32_t L, uint32_t bw, uint32_t limit, Walker* w, uint32_t* s_hop,
                                                 uint32_t* ent_pos, uint32_t* ent_k, int* n_ent, int tid, int bar_id, int bar_n,
                                                 long long* dbg = nullptr) {
   const uint32_t seg0 = w->pos, k0 = w->k;
-  const uint32_t seg1 = min(seg0 + (uint32_t)kDefSeg, L);
+  const uint32_t seg1 = min(seg0 + (uint32_t)SEG, L);
   const uint32_t nchunks = (seg1 - seg0 + kChunk - 1) / kChunk;
   const uint32_t bytew = (bw + 7) >> 3;
   bar_sync(bar_id, bar_n);

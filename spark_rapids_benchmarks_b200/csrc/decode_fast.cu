@@ -19,30 +19,39 @@ using namespace dec;
 #ifndef NDS_UNIFORM_TB
 #define NDS_UNIFORM_TB 8
 #endif
+#ifndef NDS_DEF_SEG
+#define NDS_DEF_SEG 2048
+#endif
+#ifndef NDS_DEF_TD
+#define NDS_DEF_TD 64
+#endif
+#ifndef NDS_DEF_MINB
+#define NDS_DEF_MINB 13
+#endif
 #ifndef NDS_ROWS_MINB
 #define NDS_ROWS_MINB 3
 #endif
 namespace {
 constexpr int kTD = 64;                  // def kernel threads
 constexpr int kTR = 384;                 // rows kernel threads
-constexpr int kEntD = kDefSeg / kChunk;  // entries per resolved segment
 }  // namespace
 
 // STAGE = bytes of def-level stream a page may have in this instantiation: the 4 KB variant (every page a 20000-row
 // writer produces) leaves room for 13 CTAs per SM instead of 10, which is what this latency-bound kernel needs.
-template <int STAGE, int MINB>
-__global__ void __launch_bounds__(kTD, MINB)
+template <int STAGE, int MINB, int SEG, int TD>
+__global__ void __launch_bounds__(TD, MINB)
 def_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ task_idx, int* __restrict__ err) {
   __shared__ uint32_t s_valid[kMaxPageValues / 32];
+  constexpr int kEntD = SEG / kChunk;      // entries per resolved segment
   __shared__ uint32_t ent_pos[kEntD + 1];
   __shared__ uint32_t ent_k[kEntD + 1];
   __shared__ __align__(16) uint8_t s_stage[STAGE + 96];
-  __shared__ uint32_t s_hop[kHopWords];
+  __shared__ uint32_t s_hop[SEG + SEG / 32 + 2];
   __shared__ uint32_t s_long[64][2];
   __shared__ __align__(8) uint64_t s_mbar;
   __shared__ int s_nlong;
   __shared__ int s_nent;
-  __shared__ uint32_t s_warp_tot[2];
+  __shared__ uint32_t s_warp_tot[TD / 32];
   __shared__ Walker s_walk;
 
   const PageTask t = tasks[task_idx[blockIdx.x]];
@@ -57,7 +66,7 @@ def_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ tas
 
   if (t.def_len == 0) {
     // page without def levels (REQUIRED in this file) of a column that is nullable elsewhere: everything valid
-    for (uint32_t j = tid; j < nwo; j += kTD) {
+    for (uint32_t j = tid; j < nwo; j += TD) {
       uint32_t v = 0xFFFFFFFFu;
       if (j == 0) v &= 0xFFFFFFFFu << sh;
       uint32_t endbit = n + sh - j * 32;
@@ -65,7 +74,7 @@ def_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ tas
       if (j == 0 || j == nwo - 1) atomicOr(&vout[j], v);
       else vout[j] = v;
     }
-    for (uint32_t w = tid; w < nw; w += kTD) {
+    for (uint32_t w = tid; w < nw; w += TD) {
       const uint32_t rem = n - w * 32;
       vr_valid[w] = rem >= 32 ? 0xFFFFFFFFu : ((1u << rem) - 1u);
       vr_rank[w] = w * 32;
@@ -79,7 +88,7 @@ def_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ tas
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_mbar)));
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  for (uint32_t w = tid; w < nw; w += kTD) s_valid[w] = 0;
+  for (uint32_t w = tid; w < nw; w += TD) s_valid[w] = 0;
   __syncthreads();
   const uint8_t* g0 = t.src + 4;
   const uintptr_t a0 = reinterpret_cast<uintptr_t>(g0) & ~uintptr_t(15);
@@ -96,7 +105,7 @@ def_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ tas
   for (;;) {
     if (s_walk.pos >= L || s_walk.k >= n) break;
     if (tid == 0) { s_nent = 0; s_nlong = 0; }
-    resolve_segment(def_sd, L, 1, n, &s_walk, s_hop, ent_pos, ent_k, &s_nent, tid, 0, kTD);
+    resolve_segment<SEG>(def_sd, L, 1, n, &s_walk, s_hop, ent_pos, ent_k, &s_nent, tid, 0, TD);
     // the entered chunks list the runs that start in them into their own 16 slots of the (now free) hop table -
     // a 32-byte chunk holds at most 16 runs of 2+ bytes - then the listed runs are expanded one thread per run
     const int ne = s_nent;
@@ -131,7 +140,7 @@ def_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ tas
       ent_k[tid] = min(r, 16u);       // ent_k is free after phase B: number of listed runs of this entry
     }
     __syncthreads();
-    for (uint32_t idx = tid; idx < (uint32_t)ne * 16; idx += kTD) {
+    for (uint32_t idx = tid; idx < (uint32_t)ne * 16; idx += TD) {
       if ((idx & 15) >= ent_k[idx >> 4]) continue;
       const uint32_t hx = (idx >> 4) * 33 + (idx & 15) * 2;
       const uint32_t k = s_hop[hx], ci = s_hop[hx + 1];
@@ -150,7 +159,7 @@ def_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ tas
     const int nl = min(s_nlong, 64);
     for (int j = 0; j < nl; ++j) {
       const uint32_t b0 = s_long[j][0], b1 = s_long[j][1];
-      for (uint32_t w = (b0 >> 5) + tid; w <= ((b1 - 1) >> 5); w += kTD) {
+      for (uint32_t w = (b0 >> 5) + tid; w <= ((b1 - 1) >> 5); w += TD) {
         const uint32_t lo = max(b0, w << 5), hi = min(b1, (w + 1) << 5);
         const uint32_t cntb = hi - lo;
         atomicOr(&s_valid[w], (cntb == 32 ? 0xFFFFFFFFu : ((1u << cntb) - 1u)) << (lo & 31));
@@ -160,7 +169,7 @@ def_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ tas
   }
   // rank prefix per word
   {
-    const uint32_t per = (nw + kTD - 1) / kTD;
+    const uint32_t per = (nw + TD - 1) / TD;
     const uint32_t w0 = min((uint32_t)tid * per, nw), w1 = min(w0 + per, nw);
     uint32_t sum = 0;
     for (uint32_t w = w0; w < w1; ++w) sum += __popc(s_valid[w]);
@@ -172,16 +181,21 @@ def_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ tas
     __syncthreads();          // s_warp_tot is reused
     if (lane == 31) s_warp_tot[warp] = incl;
     __syncthreads();
-    uint32_t run = (warp == 1 ? s_warp_tot[0] : 0u) + incl - sum;
+    uint32_t run = incl - sum;
+    for (int q = 0; q < warp; ++q) run += s_warp_tot[q];
     for (uint32_t w = w0; w < w1; ++w) {
       vr_rank[w] = run;
       vr_valid[w] = s_valid[w];
       run += __popc(s_valid[w]);
     }
-    if (tid == 0) vr_rank[nw] = s_warp_tot[0] + s_warp_tot[1];
+    if (tid == 0) {
+      uint32_t tot = 0;
+      for (int q = 0; q < TD / 32; ++q) tot += s_warp_tot[q];
+      vr_rank[nw] = tot;
+    }
   }
   // validity bitmap of the output column (the page may start at any bit)
-  for (uint32_t j = tid; j < nwo; j += kTD) {
+  for (uint32_t j = tid; j < nwo; j += TD) {
     uint32_t lo = j < nw ? s_valid[j] : 0u;
     uint32_t hi = (j > 0 && j - 1 < nw) ? s_valid[j - 1] : 0u;
     uint32_t v = sh ? ((lo << sh) | (hi >> (32 - sh))) : lo;
@@ -569,8 +583,9 @@ int rows_slices(int npages) {
 void launch_decode_split(const PageTask* d_tasks, const int* d_def_idx, int ndef, int max_def_len, const int* d_rows_idx, int nrows,
                          int* d_err, cudaStream_t stream, int* launches) {
   if (ndef > 0) {
-    if (max_def_len <= 4096) def_pages_kernel<4096, 13><<<ndef, kTD, 0, stream>>>(d_tasks, d_def_idx, d_err);
-    else def_pages_kernel<8192, 8><<<ndef, kTD, 0, stream>>>(d_tasks, d_def_idx, d_err);
+    static_assert(NDS_DEF_SEG / 32 <= NDS_DEF_TD, "one thread per 32-byte chunk of a segment");
+    if (max_def_len <= 4096) def_pages_kernel<4096, NDS_DEF_MINB, NDS_DEF_SEG, NDS_DEF_TD><<<ndef, NDS_DEF_TD, 0, stream>>>(d_tasks, d_def_idx, d_err);
+    else def_pages_kernel<8192, 8, kDefSeg, kTD><<<ndef, kTD, 0, stream>>>(d_tasks, d_def_idx, d_err);
     NDS_CUDA(cudaGetLastError());
     ++*launches;
   }
