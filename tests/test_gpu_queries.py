@@ -228,3 +228,29 @@ def test_throughput_two_streams_share_one_gpu(warehouse, tmp_path):
     elapsed = thr.get_throughput_time(str(tmp_path / 'time'), 5, 1)        # 5 streams in total -> first test = streams 1, 2
     # the time log carries whole epoch seconds (like the reference's), so two sub-second streams may give 0.0
     assert 0 <= elapsed < 600 and abs(elapsed * 10 - round(elapsed * 10)) < 1e-9
+
+
+def test_repeated_queries_do_not_leak(gpu_engine, warehouse):
+    """The power run's loop in miniature: 150 executions of two plans (one of them failing every few rounds) must
+    leave device memory, the event pool and the side streams where they were - and keep giving the same answer."""
+    import torch
+    from spark_rapids_benchmarks_b200 import planner
+    from spark_rapids_benchmarks_b200.engine import EngineError
+    import pyarrow as pa
+    plans = [planner.plan_sql(streams.render(q, overrides=PARAMS[0])) for q in ('query7', 'query42')]
+    bad = {'op': 'join', 'type': 'inner', 'probe_key': 'ss_item_sk', 'build_key': 'i_manufact_id',       # duplicate build keys -> error
+           'probe': {'op': 'scan', 'table': 'store_sales', 'columns': ['ss_item_sk']},
+           'build': {'op': 'scan', 'table': 'item', 'columns': ['i_manufact_id']}}
+    first = [pa.Table.from_batches([gpu_engine.execute({'root': p['root']})]).to_pylist() for p in plans]
+    torch.cuda.synchronize()
+    free0 = torch.cuda.mem_get_info()[0]
+    for it in range(75):
+        for p, exp in zip(plans, first):
+            got = pa.Table.from_batches([gpu_engine.execute({'root': p['root']}, source='host' if it % 2 else None)]).to_pylist()
+            assert got == exp
+        if it % 10 == 0:
+            with pytest.raises(EngineError):
+                gpu_engine.execute(bad)
+    torch.cuda.synchronize()
+    free1 = torch.cuda.mem_get_info()[0]
+    assert free0 - free1 < (64 << 20), (free0, free1)       # the async pool may keep a few blocks; nothing grows per query
