@@ -84,6 +84,11 @@ struct TableColumn {
   std::vector<DictInfo> dicts;
   std::vector<int64_t> file_page_begin;  // per file: first page index (size nfiles + 1)
   std::vector<int64_t> file_byte_begin;  // per file: first staged byte (16 B aligned), size nfiles + 1
+  // One PageTask per page with everything that does not depend on the query filled in at registration: src / dict
+  // hold OFFSETS into the encoded buffer (dict: offset + 1, 0 = no dictionary), out_row the page's first row inside its
+  // file, vr != null marks a split-route page. A scan copies a file's run of templates and patches five fields.
+  std::vector<PageTask> task_tmpl;
+  std::vector<int64_t> file_bytes_in;    // per file: page payload bytes + dictionary bytes a scan of it reads
 };
 struct MemColumn {                      // table registered from Arrow buffers
   std::string name;

@@ -762,47 +762,34 @@ struct Exec {
         }
       }
       col.strbase = src_base;
-      int last_dict = -1;
+      // the registration-time templates of each selected file, copied in one piece and patched (engine.h, task_tmpl)
       for (size_t k = 0; k < sel.size(); ++k) {
-        int f = sel[k];
-        for (int64_t p = tc.file_page_begin[f]; p < tc.file_page_begin[f + 1]; ++p) {
-          const PageInfo& pi = tc.pages[p];
-          if (pi.dict >= 0 && pi.dict != last_dict) {       // each dictionary page is read once per scan
-            last_dict = pi.dict;
-            bytes_in += (int64_t)tc.dicts[pi.dict].count * (tc.phys == pq::BYTE_ARRAY ? 8 : width);
-          }
-          tasks.emplace_back();
-          PageTask& task = tasks.back();
-          memset(&task, 0, sizeof task);
-          task.src = src_base + pi.off;
+        const int f = sel[k];
+        const int64_t p0 = tc.file_page_begin[f], p1 = tc.file_page_begin[f + 1];
+        const size_t base = tasks.size();
+        tasks.insert(tasks.end(), tc.task_tmpl.begin() + p0, tc.task_tmpl.begin() + p1);
+        bytes_in += tc.file_bytes_in[f];
+        const int64_t r0 = row_start[k];
+        for (size_t q = base; q < tasks.size(); ++q) {
+          PageTask& task = tasks[q];
+          const bool fast = task.vr != nullptr;
+          task.vr = nullptr;
+          task.src = src_base + reinterpret_cast<uintptr_t>(task.src);
+          if (task.dict) task.dict = src_base + (reinterpret_cast<uintptr_t>(task.dict) - 1);
           task.out = d_out;
           task.valid = d_valid;
-          task.out_row = row_start[k] + pi.row_in_file;
-          task.size = pi.size;
-          task.num_values = pi.num_values;
-          task.def_len = pi.def_len;
-          task.src_off = (uint32_t)pi.off;
-          task.enc = pi.enc;
-          task.bw = pi.bw;
-          const int tix = (int)tasks.size() - 1;
-          if (pi.fast && split_decode) {
-            rows_idx.push_back(tix);
+          task.out_row += r0;
+          if (fast && split_decode) {
+            rows_idx.push_back((int)q);
             if (d_valid) {
-              def_idx.push_back(tix);
+              def_idx.push_back((int)q);
               vr_off.push_back(vr_words);
-              vr_words += 2 * (((int64_t)pi.num_values + 31) / 32) + 1;
+              vr_words += 2 * (((int64_t)task.num_values + 31) / 32) + 1;
             } else vr_off.push_back(-1);
           } else {
-            gen_idx.push_back(tix);
+            gen_idx.push_back((int)q);
             vr_off.push_back(-1);
           }
-          task.width = (uint8_t)width;
-          task.phys = tc.phys == pq::BYTE_ARRAY ? 1 : 0;
-          if (pi.dict >= 0) {
-            task.dict = src_base + tc.dicts[pi.dict].off;
-            task.dict_count = tc.dicts[pi.dict].count;
-          }
-          bytes_in += pi.size;
         }
       }
       bytes_out += N * width + (tc.nullable ? N / 8 : 0);

@@ -321,6 +321,38 @@ void Engine::register_table(const std::string& name, const std::string& path, co
     t.encoded_bytes += tc.enc_bytes;
     if (tc.phys == pq::BYTE_ARRAY && tc.enc_bytes > 0xFFFFFFFFll)
       fail("string column '" + tc.name + "' exceeds 4 GiB of encoded bytes");
+    // scan-time task templates (engine.h)
+    const int width = tc.lt.dtype() == DT_I32 ? 4 : 8;
+    tc.task_tmpl.resize(tc.pages.size());
+    tc.file_bytes_in.assign(tc.file_page_begin.size() - 1, 0);
+    for (size_t f = 0; f + 1 < tc.file_page_begin.size(); ++f) {
+      int last_dict = -1;
+      for (int64_t p = tc.file_page_begin[f]; p < tc.file_page_begin[f + 1]; ++p) {
+        const PageInfo& pi = tc.pages[p];
+        PageTask& task = tc.task_tmpl[p];
+        memset(&task, 0, sizeof task);
+        task.src = reinterpret_cast<const uint8_t*>((uintptr_t)pi.off);
+        task.out_row = pi.row_in_file;
+        task.size = pi.size;
+        task.num_values = pi.num_values;
+        task.def_len = pi.def_len;
+        task.src_off = (uint32_t)pi.off;
+        task.enc = pi.enc;
+        task.bw = pi.bw;
+        task.width = (uint8_t)width;
+        task.phys = tc.phys == pq::BYTE_ARRAY ? 1 : 0;
+        task.vr = pi.fast ? reinterpret_cast<uint32_t*>((uintptr_t)1) : nullptr;
+        tc.file_bytes_in[f] += pi.size;
+        if (pi.dict >= 0) {
+          task.dict = reinterpret_cast<const void*>((uintptr_t)(tc.dicts[pi.dict].off + 1));
+          task.dict_count = tc.dicts[pi.dict].count;
+          if (pi.dict != last_dict) {          // each dictionary page is read once per scan
+            last_dict = pi.dict;
+            tc.file_bytes_in[f] += (int64_t)tc.dicts[pi.dict].count * (tc.phys == pq::BYTE_ARRAY ? 8 : width);
+          }
+        }
+      }
+    }
   }
   if (t.part_col.size() && t.col_index.count(t.part_col))
     fail("partition column '" + t.part_col + "' is also stored in the files of '" + name + "'");
