@@ -185,6 +185,8 @@ class Engine {
   int64_t pin_cap_ = 0;
   uint8_t* slab_ = nullptr;     // device slab behind the per-query bump allocator
   int64_t slab_cap_ = 0;
+  int64_t slab_wanted_ = 0;     // > slab_cap_: a query overflowed the slab; grown before the next query runs
+  void grow_slab_if_wanted();
   void* comm_ = nullptr;          // ncclComm_t of the exchange operator (nccl_dyn.h); null until comm_init
   int comm_rank_ = 0, comm_world_ = 1;
   int64_t spec_retries_ = 0;    // queries re-run because a device-side size assumption failed (stats: speculation_retries)

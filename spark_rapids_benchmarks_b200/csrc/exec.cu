@@ -23,6 +23,7 @@ struct Arena {
   uint8_t* slab = nullptr;
   int64_t slab_cap = 0, slab_off = 0;
   int64_t zero_off = 0, zero_cap = 0;   // pre-zeroed prefix of the slab for counters and flags
+  int64_t overflow_bytes = 0;           // what did not fit the slab this query (the engine grows the slab for the next one)
   uint8_t* pin = nullptr;       // pinned staging ring owned by the engine (reset per query)
   int64_t pin_cap = 0, pin_off = 0;
   explicit Arena(cudaStream_t st) : s(st) {}
@@ -49,6 +50,7 @@ struct Arena {
     void* p = nullptr;
     NDS_CUDA(cudaMallocAsync(&p, (size_t)bytes + 64, s));
     ptrs.push_back(p);
+    overflow_bytes += need;
     return p;
   }
   template <typename T>
@@ -281,6 +283,7 @@ struct Exec {
 
   ~Exec() {     // a failed query still returns its timing events to the pool
     e.zero_dirty_ = ar.zero_off;
+    if (ar.overflow_bytes > 0) e.slab_wanted_ = std::max(e.slab_wanted_, ar.slab_off + ar.overflow_bytes + ar.overflow_bytes / 4);
     if (s_saved) { cudaStreamSynchronize(s); s = s_saved; ar.s = s; }     // failed inside a side-stream section
     if (ev_start) e.put_event(ev_start);
     for (cudaEvent_t ev : side_events) e.put_event(ev);
@@ -666,7 +669,11 @@ struct Exec {
     if (N >= (int64_t(1) << 31)) fail("scan of '" + tname + "' selects 2^31 or more rows; shard the table across GPUs");
     out.n_max = N;
     size_t st = begin_stat("decode:" + tname, true);
-    std::vector<PageTask> tasks;
+    // the task list is built in place in the pinned upload ring (one copy less); a std::vector only when the ring is full
+    std::vector<PageTask> tasks_fallback;
+    PageTask* tasks = nullptr;
+    size_t ntasks = 0;
+    bool tasks_pinned = false;
     std::vector<int> def_idx, rows_idx, gen_idx;     // routes: split def/rows kernels vs the general kernel
     std::vector<int64_t> vr_off;                      // per task: offset of its validity/rank scratch (words) or -1
     int64_t vr_words = 0;
@@ -680,7 +687,9 @@ struct Exec {
         const TableColumn& tc = t.cols[ci->second];
         for (int f : sel) npages += (size_t)(tc.file_page_begin[f + 1] - tc.file_page_begin[f]);
       }
-      tasks.reserve(npages);
+      tasks = reinterpret_cast<PageTask*>(ar.pin_take((int64_t)(npages * sizeof(PageTask)) + 16));
+      tasks_pinned = tasks != nullptr;
+      if (!tasks) { tasks_fallback.resize(npages + 1); tasks = tasks_fallback.data(); }
       vr_off.reserve(npages);
       def_idx.reserve(npages);
       rows_idx.reserve(npages);
@@ -736,6 +745,7 @@ struct Exec {
       const int width = tc.lt.dtype() == DT_I32 ? 4 : 8;
       void* d_out = ar.alloc(N * width);
       uint32_t* d_valid = tc.nullable ? ar.zeros<uint32_t>((N + 31) / 32 + 1) : nullptr;
+      mark("scan:col_alloc");
       col.data = d_out;
       col.valid = d_valid;
       // ---- where do the encoded bytes come from
@@ -766,11 +776,12 @@ struct Exec {
       for (size_t k = 0; k < sel.size(); ++k) {
         const int f = sel[k];
         const int64_t p0 = tc.file_page_begin[f], p1 = tc.file_page_begin[f + 1];
-        const size_t base = tasks.size();
-        tasks.insert(tasks.end(), tc.task_tmpl.begin() + p0, tc.task_tmpl.begin() + p1);
+        const size_t base = ntasks;
+        if (p1 > p0) memcpy(tasks + ntasks, tc.task_tmpl.data() + p0, (size_t)(p1 - p0) * sizeof(PageTask));
+        ntasks += (size_t)(p1 - p0);
         bytes_in += tc.file_bytes_in[f];
         const int64_t r0 = row_start[k];
-        for (size_t q = base; q < tasks.size(); ++q) {
+        for (size_t q = base; q < ntasks; ++q) {
           PageTask& task = tasks[q];
           const bool fast = task.vr != nullptr;
           task.vr = nullptr;
@@ -795,11 +806,12 @@ struct Exec {
       bytes_out += N * width + (tc.nullable ? N / 8 : 0);
       out.cols.push_back(col);
     }
-    if (!tasks.empty()) {
+    mark("scan:tasks_built");
+    if (ntasks > 0) {
       // a scan of a few pages is latency-bound: one general launch beats a def + rows (+ general) sequence
       if ((int64_t)rows_idx.size() < small_scan_pages) {
         gen_idx.clear();
-        for (size_t k = 0; k < tasks.size(); ++k) gen_idx.push_back((int)k);
+        for (size_t k = 0; k < ntasks; ++k) gen_idx.push_back((int)k);
         def_idx.clear();
         rows_idx.clear();
         vr_words = 0;
@@ -807,9 +819,10 @@ struct Exec {
       }
       // scratch of the split route: per nullable page its validity words and their rank prefix
       uint32_t* d_vr = vr_words ? ar.alloc_n<uint32_t>(vr_words) : nullptr;
-      for (size_t k = 0; k < tasks.size(); ++k) tasks[k].vr = vr_off[k] >= 0 ? d_vr + vr_off[k] : nullptr;
-      PageTask* d_tasks = ar.alloc_n<PageTask>((int64_t)tasks.size());
-      ar.upload(d_tasks, tasks.data(), (int64_t)(tasks.size() * sizeof(PageTask)));
+      for (size_t k = 0; k < ntasks; ++k) tasks[k].vr = vr_off[k] >= 0 ? d_vr + vr_off[k] : nullptr;
+      PageTask* d_tasks = ar.alloc_n<PageTask>((int64_t)ntasks);
+      if (tasks_pinned) NDS_CUDA(cudaMemcpyAsync(d_tasks, tasks, ntasks * sizeof(PageTask), cudaMemcpyHostToDevice, s));
+      else ar.upload(d_tasks, tasks, (int64_t)(ntasks * sizeof(PageTask)));
       std::vector<int> idx_all;
       idx_all.reserve(def_idx.size() + rows_idx.size() + gen_idx.size());
       idx_all.insert(idx_all.end(), def_idx.begin(), def_idx.end());
@@ -818,6 +831,7 @@ struct Exec {
       int* d_idx = ar.alloc_n<int>((int64_t)idx_all.size());
       ar.upload(d_idx, idx_all.data(), (int64_t)(idx_all.size() * sizeof(int)));
       // a dedicated pair of events brackets only the decode launches (roofline.achieved in bench.py)
+      mark("scan:uploaded");
       size_t ks = begin_stat("decode_kernel", true);
       int l = 0;
       int max_def_len = 0;
@@ -1757,6 +1771,7 @@ void Engine::execute(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_
 void Engine::execute_once(const Json& plan, ArrowSchema* out_schema, ArrowArray* out_array, bool speculate) {
   const double t_exec0 = Exec::now_ms();
   NDS_CUDA(cudaSetDevice(device));
+  grow_slab_if_wanted();
   const Json* options = plan.find("options");
   const Json& root = plan.has("root") ? plan.at("root") : plan;
   cudaEvent_t ev0 = get_event(), ev1 = get_event();
@@ -2096,6 +2111,25 @@ Engine::Engine(const Json& cfg) {
     pin_ = nullptr;
     pin_cap_ = 0;
   }
+}
+
+// The previous query did not fit the per-query slab and fell back to cudaMallocAsync (tens of microseconds per column
+// at SF100): make the slab large enough for a query of that size, within a quarter of the memory that is free now.
+void Engine::grow_slab_if_wanted() {
+  if (slab_wanted_ <= slab_cap_) return;
+  size_t free_b = 0, total_b = 0;
+  NDS_CUDA(cudaStreamSynchronize(stream_));
+  NDS_CUDA(cudaMemGetInfo(&free_b, &total_b));
+  const int64_t limit = slab_cap_ + (int64_t)(free_b / 4);
+  const int64_t want = std::min<int64_t>(align_up(slab_wanted_, 64 << 20), limit);
+  slab_wanted_ = 0;
+  if (want <= slab_cap_) return;
+  uint8_t* fresh = nullptr;
+  if (cudaMalloc(reinterpret_cast<void**>(&fresh), (size_t)want) != cudaSuccess) { cudaGetLastError(); return; }
+  if (slab_) cudaFree(slab_);
+  slab_ = fresh;
+  slab_cap_ = want;
+  zero_dirty_ = -1;
 }
 
 cudaEvent_t Engine::get_event() {

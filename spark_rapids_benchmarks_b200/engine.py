@@ -67,11 +67,13 @@ class Engine:
     """One engine per process and GPU (the reference runs one SparkSession per stream process,
     /root/reference/nds/nds-throughput:23)."""
 
-    def __init__(self, device=0, resident=True, keep_host=False, rank=0, world=1):
+    def __init__(self, device=0, resident=True, keep_host=False, rank=0, world=1, slab_mb=None):
         self._lib = load_library()
         self._h = ctypes.c_void_p()
-        cfg = json.dumps({'device': device, 'resident': resident, 'keep_host': keep_host,
-                          'rank': rank, 'world': world}).encode()
+        cfg = {'device': device, 'resident': resident, 'keep_host': keep_host, 'rank': rank, 'world': world}
+        if slab_mb is not None:
+            cfg['slab_mb'] = int(slab_mb)      # initial size of the per-query device slab (grows when a query overflows it)
+        cfg = json.dumps(cfg).encode()
         rc = self._lib.nds_engine_create(cfg, ctypes.byref(self._h))
         if rc != 0:
             self._h = None

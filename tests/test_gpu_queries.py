@@ -254,3 +254,22 @@ def test_repeated_queries_do_not_leak(gpu_engine, warehouse):
     torch.cuda.synchronize()
     free1 = torch.cuda.mem_get_info()[0]
     assert free0 - free1 < (64 << 20), (free0, free1)       # the async pool may keep a few blocks; nothing grows per query
+
+
+def test_small_slab_overflows_then_grows(warehouse):
+    """An engine whose per-query slab is far too small: the first query falls back to stream-ordered allocations, the
+    slab is grown before the next one - same answers throughout."""
+    from spark_rapids_benchmarks_b200 import engine, nds_schema, planner
+    import pyarrow as pa
+    eng = engine.Engine(device=0, slab_mb=1)
+    try:
+        for t in ('store_sales', 'date_dim', 'item', 'customer_demographics', 'promotion'):
+            eng.register_table(t, os.path.join(warehouse, t))
+        sql = streams.render('query7', overrides=PARAMS[0])
+        exp = oq.run_query('query7', sql, warehouse)
+        plan = planner.plan_sql(sql)
+        for _ in range(3):
+            got = pa.Table.from_batches([eng.execute({'root': plan['root']})])
+            assert rows_equal(got.to_pylist(), exp.to_pylist())
+    finally:
+        eng.close()
