@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <exception>
 #include <memory>
 #include <unordered_set>
 #include "engine.h"
@@ -285,6 +286,13 @@ struct Exec {
     e.zero_dirty_ = ar.zero_off;
     if (ar.overflow_bytes > 0) e.slab_wanted_ = std::max(e.slab_wanted_, ar.slab_off + ar.overflow_bytes + ar.overflow_bytes / 4);
     if (s_saved) { cudaStreamSynchronize(s); s = s_saved; ar.s = s; }     // failed inside a side-stream section
+    if (std::uncaught_exceptions() > 0) {
+      // a failed query may leave work queued on the side streams that still writes into the slab: drain them before
+      // the next query reuses that memory
+      for (cudaStream_t st : e.side_streams_) cudaStreamSynchronize(st);
+      cudaStreamSynchronize(e.stream_);
+      cudaGetLastError();
+    }
     if (ev_start) e.put_event(ev_start);
     for (cudaEvent_t ev : side_events) e.put_event(ev);
     for (auto& st : rf_states)
