@@ -109,3 +109,33 @@ def test_collect_matches_to_pylist():
         assert len(rows) == variant.num_rows
         if variant.num_rows:
             assert tuple(rows[0]) == tuple(variant.column(c)[0].as_py() for c in variant.schema.names)
+
+
+def test_distributed_plan_has_partial_merge_and_fused_forms():
+    """plan_sql(distributed=True): 'partial' (scan -> joins -> partial aggregate), 'root' (merge over __partial__) and
+    'fused' (the same merge tree with the __partial__ scan replaced by exchange{partial}); AVG travels as SUM + COUNT."""
+    from spark_rapids_benchmarks_b200 import planner, streams
+
+    def ops(node, out):
+        out.append(node['op'])
+        for k in ('child', 'probe', 'build'):
+            if k in node:
+                ops(node[k], out)
+        return out
+    for q in streams.SUBSET:
+        p = planner.plan_sql(streams.render(q), distributed=True)
+        assert set(p) >= {'root', 'partial', 'fused', 'output'}
+        assert p['partial']['op'] == 'aggregate'
+        root_ops, fused_ops = ops(p['root'], []), ops(p['fused'], [])
+        assert 'exchange' not in root_ops and root_ops.count('scan') == 1
+        i = fused_ops.index('exchange')
+        assert fused_ops[:i] == root_ops[:root_ops.index('scan')]              # same merge tree above the exchange
+        assert fused_ops[i + 1:] == ops(p['partial'], [])                      # the partial plan below it
+        merge = p['root']
+        while merge['op'] != 'aggregate':
+            merge = merge['child']
+        assert {a['fn'] for a in merge['aggs']} <= {'sum', 'min', 'max'}       # counts are summed when merging
+        assert merge['child'] == {'op': 'scan', 'table': '__partial__',
+                                  'columns': [k['name'] for k in merge['keys']] + [a['name'] for a in merge['aggs']]}
+    single = planner.plan_sql(streams.render('query3'))
+    assert 'partial' not in single and 'fused' not in single
