@@ -33,10 +33,11 @@ NDS_API const char* nds_version(void);
 NDS_API const char* nds_last_error(void);
 
 /* Create an engine bound to one GPU.  cfg_json: {"device":0, "resident":true, "keep_host":false,
- * "rank":0, "world":1}.  resident: encoded column chunks are kept in HBM; keep_host: a pinned host
+ * "rank":0, "world":1, "slab_mb":512}.  resident: encoded column chunks are kept in HBM; keep_host: a pinned host
  * copy is kept as well so that a plan can run with {"options":{"source":"host"}} (host->device copy
  * of the needed chunks inside the query).  rank/world: hive-partitioned (fact) tables are sharded by
- * file across `world` engines, dimension tables are replicated.
+ * file across `world` engines, dimension tables are replicated.  slab_mb: initial size of the per-query
+ * device slab (it grows when a query overflows it).
  * Replaces: SparkSession.builder...getOrCreate()   /root/reference/nds/nds_power.py:224-240 */
 NDS_API int nds_engine_create(const char* cfg_json, nds_engine** out);
 
@@ -66,6 +67,9 @@ NDS_API int nds_engine_table_info(nds_engine* e, const char* name, char* buf, in
 /* Execute one physical plan (JSON plan IR, DESIGN.md "Plan IR") and return the result as one record
  * batch.  The caller owns out_schema/out_array and must call their release callbacks.
  * An unsupported node or expression fails with a message; nothing is computed on the CPU.
+ * Optional top-level "options": {"source":"hbm"|"host", "profile":bool (CUDA events per operator in the statistics),
+ * "trace":bool (host timeline), and the test / measurement switches "side_stream", "speculate", "split_decode",
+ * "small_scan_pages", "exchange_loopback"} - DESIGN.md, Plan IR.
  * Replaces: df = spark.sql(query); df.collect()     /root/reference/nds/nds_power.py:130-132 */
 NDS_API int nds_engine_execute(nds_engine* e, const char* plan_json, struct ArrowSchema* out_schema, struct ArrowArray* out_array);
 

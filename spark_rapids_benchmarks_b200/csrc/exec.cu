@@ -1309,15 +1309,32 @@ struct Exec {
       korigin.push_back(origin);
     }
     std::vector<AggSpec> specs;
+    std::vector<std::vector<Instr>> agg_codes;      // compiled argument of each aggregate (empty: count(*) / count-ref)
     for (const Json& a : jaggs.a) {
       const std::string& fn = a.str("fn");
       AggSpec sp;
       LType ot;
+      std::vector<Instr> agg_code_of_this;
       if (fn == "count_star") { sp.fn = AGG_COUNT_STAR; sp.prog = -1; ot.kind = LType::INT; }
       else {
         std::vector<Instr> code;
         LType t = compile(a.at("expr"), in, bb, code);
+        int same_as = -1;          // an earlier aggregate over the very same compiled expression
+        for (size_t j = 0; j < agg_codes.size() && same_as < 0; ++j)
+          if (specs[j].fn != AGG_COUNT_STAR && specs[j].fn != AGG_COUNT_REF && agg_codes[j].size() == code.size() &&
+              (code.empty() || memcmp(agg_codes[j].data(), code.data(), code.size() * sizeof(Instr)) == 0))
+            same_as = (int)j;
+        if (fn == "count" && same_as >= 0) {
+          sp.fn = AGG_COUNT_REF;
+          sp.prog = same_as;
+          ot.kind = LType::INT;
+          specs.push_back(sp);
+          atypes.push_back(ot);
+          agg_codes.emplace_back();
+          continue;
+        }
         sp.prog = bb.add_prog(code, t);
+        agg_code_of_this = code;
         if (fn == "count") { sp.fn = AGG_COUNT; ot.kind = LType::INT; }
         else if (t.kind == LType::STR) fail("plan: " + fn + " over strings is not supported");
         else if (fn == "sum") {
@@ -1338,6 +1355,7 @@ struct Exec {
       }
       specs.push_back(sp);
       atypes.push_back(ot);
+      agg_codes.push_back(std::move(agg_code_of_this));
     }
     Batch out;
     if (n == 0) {

@@ -375,6 +375,7 @@ agg_insert_kernel(const Prog* __restrict__ progs, int nkeys, const AggSpec* __re
         const AggSpec sp = aggs[a];
         int64_t* pa = hit ? &c_acc[a * kAggCache + e] : &acc[a * cap + s];
         int64_t* pc = hit ? &c_cnt[a * kAggCache + e] : &cnt[a * cap + s];
+        if (sp.fn == AGG_COUNT_REF) continue;
         if (sp.fn == AGG_COUNT_STAR) { atomicAdd(reinterpret_cast<unsigned long long*>(pc), 1ull); continue; }
         Val v = eval_program(progs[sp.prog].code, progs[sp.prog].n, c.cols, c.lit, i);
         if (!v.ok) continue;
@@ -426,9 +427,10 @@ agg_finalize_kernel(const AggSpec* __restrict__ aggs, int naggs, const uint32_t*
     rep_out[g] = rep - 1;
     for (int a = 0; a < naggs; ++a) {
       const int fn = aggs[a].fn;
-      int64_t c = cnt[(uint64_t)a * cap + s];
-      int64_t v = (fn == AGG_COUNT || fn == AGG_COUNT_STAR) ? c : acc[(uint64_t)a * cap + s];
-      bool ok = (fn == AGG_COUNT || fn == AGG_COUNT_STAR) ? true : c > 0;
+      const bool counting = fn == AGG_COUNT || fn == AGG_COUNT_STAR || fn == AGG_COUNT_REF;
+      int64_t c = cnt[(uint64_t)(fn == AGG_COUNT_REF ? aggs[a].prog : a) * cap + s];
+      int64_t v = counting ? c : acc[(uint64_t)a * cap + s];
+      bool ok = counting ? true : c > 0;
       out_vals[a * out_stride + g] = ok ? v : 0;
       if (ok) atomicOr(&out_valid[a * valid_stride_words + (g >> 5)], 1u << (g & 31));
     }

@@ -30,7 +30,9 @@ struct HashTable {
   uint32_t mask;
 };
 
-enum AggFn : int32_t { AGG_SUM_I = 0, AGG_COUNT = 1, AGG_COUNT_STAR = 2, AGG_MIN_I = 3, AGG_MAX_I = 4, AGG_SUM_F = 5 };
+// AGG_COUNT_REF: count(x) where another aggregate over the same x already counts the non-null rows (AVG = SUM + COUNT):
+// prog holds that aggregate's index, nothing is accumulated, the finalize step reads the other aggregate's counter.
+enum AggFn : int32_t { AGG_SUM_I = 0, AGG_COUNT = 1, AGG_COUNT_STAR = 2, AGG_MIN_I = 3, AGG_MAX_I = 4, AGG_SUM_F = 5, AGG_COUNT_REF = 6 };
 struct AggSpec {
   int32_t fn;
   int32_t prog;          // index into the program array, -1 for count(*)
