@@ -194,6 +194,8 @@ struct RuntimeFilter {           // dynamic partition pruning: build-side join k
     int64_t nb = 0;
     bool is32 = false;
     std::vector<uint8_t> pageable;      // backing store when the pinned ring is full
+    const uint32_t* hbits = nullptr;    // device-built bitmap over [lo, hi] (32-bit words) when the partition range is known
+    int64_t hbits_words = 0;
     // a bitmap over [lo, hi] when the key range is small (surrogate keys are dense), else a sorted list
     int64_t lo = 0, hi = -1;
     std::vector<uint64_t> bits;
@@ -379,6 +381,12 @@ struct Exec {
       mark("wait_done", now_ms() - t0);
       e.put_event(t.ev);
       t.ev = nullptr;
+    }
+    if (t.hbits) {                     // the bitmap was built on the device: repack 32-bit words into the 64-bit ones
+      t.bits.assign((size_t)((t.hbits_words + 1) / 2), 0);
+      for (int64_t w = 0; w < t.hbits_words; ++w) t.bits[(size_t)(w >> 1)] |= (uint64_t)t.hbits[w] << ((w & 1) * 32);
+      t.ready = true;
+      return;
     }
     int64_t hcount = std::min<int64_t>(*t.hcount, t.nb);
     std::vector<int64_t> keys;
@@ -1069,12 +1077,37 @@ struct Exec {
     end_stat(stb, nb * 8 + (int64_t)cap * 12, nb);
     // dynamic partition pruning: ship the (small) build key set to the host and let the scan skip files
     if (node.bool_or("prune_partitions", false)) {
-      Json kexpr = col_expr(bk);
-      Column flat = eval_to_column(kexpr, bk, build, nullptr, build.rc());
       RuntimeFilter rf;
       rf.column = bs.pk;
       rf.st = std::make_shared<RuntimeFilter::State>();
       RuntimeFilter::State& t = *rf.st;
+      // the partition values of the table(s) partitioned by the probe key bound the keys that matter
+      int64_t plo = INT64_MAX, phi = INT64_MIN;
+      for (const auto& kv : e.tables_)
+        if (kv.second.part_col == bs.pk)
+          for (const FileInfo& fi : kv.second.files)
+            if (!fi.part_null) { plo = std::min(plo, fi.part_val); phi = std::max(phi, fi.part_val); }
+      if (nb > 0 && plo <= phi && phi - plo < (int64_t(1) << 22)) {
+        // few partitions: a bitmap over their value range is filled on the device and only that travels to the host
+        t.lo = plo;
+        t.hi = phi;
+        t.hbits_words = (phi - plo) / 32 + 1;
+        uint32_t* dbits = ar.zeros<uint32_t>(t.hbits_words);
+        launch_keys_to_bitmap(build.cols[kb].ref(), build.rc(), plo, phi, dbits, s);
+        ++launches;
+        uint8_t* hbuf = ar.pin_take(t.hbits_words * 4);
+        if (!hbuf) { t.pageable.resize((size_t)t.hbits_words * 4); hbuf = t.pageable.data(); }
+        t.hbits = reinterpret_cast<const uint32_t*>(hbuf);
+        NDS_CUDA(cudaMemcpyAsync(hbuf, dbits, (size_t)t.hbits_words * 4, cudaMemcpyDeviceToHost, s));
+        t.ev = e.get_event();
+        NDS_CUDA(cudaEventRecord(t.ev, s));
+        rf_states.push_back(rf.st);
+        d2h += t.hbits_words * 4;
+        down.push_back(std::move(rf));
+        return bs;
+      }
+      Json kexpr = col_expr(bk);
+      Column flat = eval_to_column(kexpr, bk, build, nullptr, build.rc());
       if (nb > 0) {
         // keys of the upper-bound row range and the exact count: copies queued now, read when the scan needs them
         t.is32 = flat.lt.dtype() == DT_I32;

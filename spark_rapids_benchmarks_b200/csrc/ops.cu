@@ -180,6 +180,23 @@ join_build_kernel(ColRef key, const int* n_dev, int64_t n_host, HashTable ht, in
   }
 }
 
+// Dynamic partition pruning: the build keys that fall into [lo, hi] (the range of the probe table's partition values)
+// become bits of a small bitmap, so that a few hundred bytes travel to the host instead of every build key.
+__global__ void __launch_bounds__(kThreads)
+keys_to_bitmap_kernel(ColRef key, const int* n_dev, int64_t n_host, int64_t lo, int64_t hi, uint32_t* bits) {
+  const int64_t n = row_count(n_dev, n_host);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    Val k = load_col(key, i);
+    if (!k.ok || k.v < lo || k.v > hi) continue;
+    const uint64_t d = (uint64_t)(k.v - lo);
+    atomicOr(&bits[d >> 5], 1u << (d & 31));
+  }
+}
+void launch_keys_to_bitmap(ColRef key, RowCount n, int64_t lo, int64_t hi, uint32_t* bits, cudaStream_t s) {
+  keys_to_bitmap_kernel<<<grid_for(n.host), kThreads, 0, s>>>(key, n.dev, n.host, lo, hi, bits);
+  NDS_CUDA(cudaGetLastError());
+}
+
 __global__ void __launch_bounds__(kThreads)
 join_probe_kernel(ColRef key, const int* n_dev, int64_t n_host, HashTable ht, uint32_t* __restrict__ out_probe,
                   uint32_t* __restrict__ out_build, int* out_count) {

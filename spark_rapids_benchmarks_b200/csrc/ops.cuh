@@ -73,6 +73,8 @@ void launch_project_multi(const ProjSpec* specs, int nspecs, OpCtx c, RowCount n
 void launch_compose(const uint32_t* inner, const uint32_t* idx, RowCount n, uint32_t* out, cudaStream_t s);
 void launch_fill_i64(int64_t* p, int64_t v, int64_t n, cudaStream_t s);
 void launch_join_build(ColRef key, RowCount n, HashTable ht, int* flags, cudaStream_t s);
+// bits: ceil((hi - lo + 1) / 32) pre-zeroed words; bit (k - lo) is set for every non-null build key k in [lo, hi]
+void launch_keys_to_bitmap(ColRef key, RowCount n, int64_t lo, int64_t hi, uint32_t* bits, cudaStream_t s);
 void launch_join_probe(ColRef key, RowCount n, HashTable ht, uint32_t* out_probe, uint32_t* out_build, int* out_count,
                        cudaStream_t s);
 constexpr int kMaxChain = 8;
