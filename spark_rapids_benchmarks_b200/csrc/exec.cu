@@ -1065,18 +1065,23 @@ struct Exec {
     // small build sides (every dimension table): size the table from the upper bound, no host round trip
     const int64_t nb_bound = build.rc().host;
     const int64_t nb = nb_bound <= (int64_t(4) << 20) ? nb_bound : count(build);
-    size_t stb = begin_stat("join_build");
-    HashTable& ht = bs.ht;
-    uint32_t cap = next_pow2(2 * nb);
-    ht.mask = cap - 1;
-    ht.keys = ar.alloc_n<int64_t>(cap);
-    ht.vals = ar.alloc_n<uint32_t>(cap);
-    launch_fill_i64(ht.keys, kEmptyKey, cap, s);
-    launch_join_build(build.cols[kb].ref(), build.rc(), ht, err + 1, s);
-    launches += 2;
-    end_stat(stb, nb * 8 + (int64_t)cap * 12, nb);
-    // dynamic partition pruning: ship the (small) build key set to the host and let the scan skip files
-    if (node.bool_or("prune_partitions", false)) {
+    auto build_table = [&]() {
+      size_t stb = begin_stat("join_build");
+      HashTable& ht = bs.ht;
+      uint32_t cap = next_pow2(2 * nb);
+      ht.mask = cap - 1;
+      ht.keys = ar.alloc_n<int64_t>(cap);
+      ht.vals = ar.alloc_n<uint32_t>(cap);
+      launch_fill_i64(ht.keys, kEmptyKey, cap, s);
+      launch_join_build(build.cols[kb].ref(), build.rc(), ht, err + 1, s);
+      launches += 2;
+      end_stat(stb, nb * 8 + (int64_t)cap * 12, nb);
+    };
+    const bool prune = node.bool_or("prune_partitions", false);
+    if (!prune) build_table();
+    // dynamic partition pruning: ship the (small) build key set to the host and let the scan skip files. The keys are
+    // queued for the host BEFORE the hash table is built: the scan that waits for them is the head of the critical path.
+    if (prune) {
       RuntimeFilter rf;
       rf.column = bs.pk;
       rf.st = std::make_shared<RuntimeFilter::State>();
@@ -1103,9 +1108,11 @@ struct Exec {
         NDS_CUDA(cudaEventRecord(t.ev, s));
         rf_states.push_back(rf.st);
         d2h += t.hbits_words * 4;
+        build_table();
         down.push_back(std::move(rf));
         return bs;
       }
+      build_table();
       Json kexpr = col_expr(bk);
       Column flat = eval_to_column(kexpr, bk, build, nullptr, build.rc());
       if (nb > 0) {
