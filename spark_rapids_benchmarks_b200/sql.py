@@ -4,7 +4,7 @@ In the reference, `spark_session.sql(query)` (/root/reference/nds/nds_power.py:1
 plans the statement inside Spark (Catalyst).  No JVM exists on the build or GPU boxes, so the host
 side carries its own parser for the subset of Spark SQL the supported templates use:
 
-    SELECT <exprs [AS alias]> FROM <t [alias], ...> [WHERE <expr>] [GROUP BY ...]
+    SELECT <exprs [AS alias]> FROM <t [alias], ... | t [INNER] JOIN u ON <expr> ...> [WHERE <expr>] [GROUP BY ...]
     [ORDER BY <expr [ASC|DESC] [NULLS FIRST|LAST]>, ...] [LIMIT n]
 
 Anything outside the subset raises SqlError - the statement is never silently approximated.
@@ -97,11 +97,26 @@ class Parser:
             select.append(self.select_item())
         self.expect('kw', 'from')
         tables = [self.table_ref()]
-        while self.accept('op', ','):
-            tables.append(self.table_ref())
-        if self.peek()[0] == 'kw' and self.peek()[1] in ('join', 'inner', 'left', 'right', 'full'):
-            raise SqlError('explicit JOIN syntax is not supported by the B200 planner yet')
+        on_conds = []
+        while True:
+            if self.accept('op', ','):
+                tables.append(self.table_ref())
+                continue
+            tok = self.peek()
+            if tok[0] == 'kw' and tok[1] in ('left', 'right', 'full', 'outer'):
+                raise SqlError('%s OUTER JOIN is not supported by the B200 planner yet (inner joins only)' % tok[1].upper())
+            if tok == ('kw', 'inner') or tok == ('kw', 'join'):
+                # [INNER] JOIN t ON cond  ==  , t  ... WHERE cond: an inner join's ON clause is just another conjunct
+                self.kw('inner')
+                self.expect('kw', 'join')
+                tables.append(self.table_ref())
+                self.expect('kw', 'on')
+                on_conds.append(self.expr())
+                continue
+            break
         where = self.expr() if self.kw('where') else None
+        for c in reversed(on_conds):
+            where = c if where is None else ('bin', 'and', c, where)
         group = []
         if self.kw('group'):
             self.expect('kw', 'by')

@@ -139,3 +139,23 @@ def test_distributed_plan_has_partial_merge_and_fused_forms():
                                   'columns': [k['name'] for k in merge['keys']] + [a['name'] for a in merge['aggs']]}
     single = planner.plan_sql(streams.render('query3'))
     assert 'partial' not in single and 'fused' not in single
+
+
+def test_explicit_inner_join_syntax_plans_like_comma_joins():
+    """`a JOIN b ON a.x = b.y` is the comma join with the ON condition as one more WHERE conjunct: same plan. Outer joins raise."""
+    import pytest
+    from spark_rapids_benchmarks_b200 import planner
+    comma = '''select d_year, i_brand_id, sum(ss_ext_sales_price) s from date_dim, store_sales, item
+               where d_date_sk = ss_sold_date_sk and ss_item_sk = i_item_sk and i_manufact_id = 7 and d_moy = 11
+               group by d_year, i_brand_id order by d_year, s desc, i_brand_id limit 100'''
+    explicit = '''select d_year, i_brand_id, sum(ss_ext_sales_price) s
+                  from date_dim join store_sales on d_date_sk = ss_sold_date_sk inner join item on ss_item_sk = i_item_sk
+                  where i_manufact_id = 7 and d_moy = 11
+                  group by d_year, i_brand_id order by d_year, s desc, i_brand_id limit 100'''
+    assert planner.plan_sql(explicit) == planner.plan_sql(comma)
+    mixed = comma.replace('from date_dim, store_sales, item\n               where d_date_sk = ss_sold_date_sk and',
+                          'from date_dim join store_sales on d_date_sk = ss_sold_date_sk, item\n               where')
+    assert planner.plan_sql(mixed) == planner.plan_sql(comma)
+    for kind in ('left', 'left outer', 'right', 'full outer'):
+        with pytest.raises(planner.PlanError, match='OUTER JOIN is not supported'):
+            planner.plan_sql(explicit.replace('inner join item', kind + ' join item'))
