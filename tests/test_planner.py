@@ -159,3 +159,14 @@ def test_explicit_inner_join_syntax_plans_like_comma_joins():
     for kind in ('left', 'left outer', 'right', 'full outer'):
         with pytest.raises(planner.PlanError, match='OUTER JOIN is not supported'):
             planner.plan_sql(explicit.replace('inner join item', kind + ' join item'))
+
+
+def test_table_aliases_and_qualified_columns_plan_identically():
+    from spark_rapids_benchmarks_b200 import planner
+    plain = '''select d_year, i_brand_id, sum(ss_ext_sales_price) s from date_dim, store_sales, item
+               where d_date_sk = ss_sold_date_sk and ss_item_sk = i_item_sk and i_manufact_id = 7 and d_moy = 11
+               group by d_year, i_brand_id order by d_year, s desc, i_brand_id limit 100'''
+    aliased = '''select dt.d_year, it.i_brand_id, sum(ss.ss_ext_sales_price) s from date_dim dt, store_sales as ss, item it
+                 where dt.d_date_sk = ss.ss_sold_date_sk and ss.ss_item_sk = it.i_item_sk and it.i_manufact_id = 7 and dt.d_moy = 11
+                 group by dt.d_year, it.i_brand_id order by dt.d_year, s desc, it.i_brand_id limit 100'''
+    assert planner.plan_sql(aliased) == planner.plan_sql(plain)
