@@ -273,3 +273,35 @@ def test_small_slab_overflows_then_grows(warehouse):
             assert rows_equal(got.to_pylist(), exp.to_pylist())
     finally:
         eng.close()
+
+
+def test_predicate_forms_and_min_max_count_through_sql(gpu_engine, warehouse):
+    """SQL shapes outside the six templates, through the whole path (parser -> planner -> engine): IN lists, BETWEEN, OR,
+    explicit JOIN ... ON, MIN / MAX / COUNT(*) / COUNT(col) next to SUM - against pyarrow on the same files."""
+    import pyarrow as pa
+    import pyarrow.compute as pc
+    sql = '''select i_category_id, d_moy, sum(ss_ext_sales_price) s, min(ss_sales_price) lo, max(ss_sales_price) hi,
+                    count(*) n, count(ss_coupon_amt) nc
+             from store_sales join date_dim on ss_sold_date_sk = d_date_sk join item on ss_item_sk = i_item_sk
+             where d_moy in (1, 2, 12) and d_year between 1998 and 1999 and (i_category_id = 3 or i_manager_id between 10 and 40)
+             group by i_category_id, d_moy
+             order by i_category_id, d_moy limit 100'''
+    got = _Sess(gpu_engine).sql(sql).toArrow()
+    dd = oq.read_dim(warehouse, 'date_dim', ['d_date_sk', 'd_year', 'd_moy'])
+    dd = dd.filter(pc.and_(pc.is_in(dd['d_moy'], value_set=pa.array([1, 2, 12])),
+                           pc.and_(pc.greater_equal(dd['d_year'], 1998), pc.less_equal(dd['d_year'], 1999))))
+    it = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_category_id', 'i_manager_id'])
+    keep = pc.or_kleene(pc.equal(it['i_category_id'], 3),
+                        pc.and_kleene(pc.greater_equal(it['i_manager_id'], 10), pc.less_equal(it['i_manager_id'], 40)))
+    it = it.filter(pc.fill_null(keep, False))
+    fact = oq.read_fact(warehouse, 'store_sales', 'ss_sold_date_sk',
+                        ['ss_sold_date_sk', 'ss_item_sk', 'ss_ext_sales_price', 'ss_sales_price', 'ss_coupon_amt'], dd['d_date_sk'].to_pylist())
+    j = fact.join(dd, keys='ss_sold_date_sk', right_keys='d_date_sk', join_type='inner').join(it, keys='ss_item_sk', right_keys='i_item_sk',
+                                                                                               join_type='inner')
+    g = j.group_by(['i_category_id', 'd_moy']).aggregate([('ss_ext_sales_price', 'sum'), ('ss_sales_price', 'min'), ('ss_sales_price', 'max'),
+                                                         ([], 'count_all'), ('ss_coupon_amt', 'count')])
+    rows = sorted(g.to_pylist(), key=lambda r: ((r['i_category_id'] is not None, r['i_category_id']), (r['d_moy'] is not None, r['d_moy'])))[:100]
+    assert got.num_rows == len(rows) and got.num_rows > 0
+    exp_cols = ['i_category_id', 'd_moy', 'ss_ext_sales_price_sum', 'ss_sales_price_min', 'ss_sales_price_max', 'count_all', 'ss_coupon_amt_count']
+    for name, ename in zip(got.schema.names, exp_cols):
+        assert got.column(name).to_pylist() == [r[ename] for r in rows], name
