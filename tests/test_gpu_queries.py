@@ -305,3 +305,60 @@ def test_predicate_forms_and_min_max_count_through_sql(gpu_engine, warehouse):
     exp_cols = ['i_category_id', 'd_moy', 'ss_ext_sales_price_sum', 'ss_sales_price_min', 'ss_sales_price_max', 'count_all', 'ss_coupon_amt_count']
     for name, ename in zip(got.schema.names, exp_cols):
         assert got.column(name).to_pylist() == [r[ename] for r in rows], name
+
+
+def test_aggregates_over_expressions_through_sql(gpu_engine, warehouse):
+    """Arithmetic inside and around aggregates (decimal - decimal, bigint * decimal, CASE WHEN, int + literal, MAX - MIN,
+    CAST to double, decimal * literal) through the SQL path; expectation from plain Python Decimal / int arithmetic over
+    the rows pyarrow joins.  Exact for integers and decimals, 1e-9 relative for the double."""
+    import decimal
+    import pyarrow as pa
+    import pyarrow.compute as pc
+    sql = '''select i_category_id,
+                    sum(ss_ext_sales_price - ss_coupon_amt) a, sum(ss_quantity * ss_sales_price) b,
+                    sum(case when i_manager_id < 50 then ss_ext_sales_price else 0 end) c, sum(ss_quantity + 1) d,
+                    max(ss_quantity) - min(ss_quantity) e, sum(cast(ss_quantity as double)) f, sum(ss_ext_sales_price * 2) g
+             from store_sales, date_dim, item
+             where ss_sold_date_sk = d_date_sk and ss_item_sk = i_item_sk and d_year = 1998 and d_moy = 1
+             group by i_category_id order by i_category_id limit 100'''
+    got = _Sess(gpu_engine).sql(sql).toArrow().to_pylist()
+    dd = oq.read_dim(warehouse, 'date_dim', ['d_date_sk', 'd_year', 'd_moy'])
+    dd = dd.filter(pc.and_(pc.equal(dd['d_year'], 1998), pc.equal(dd['d_moy'], 1)))
+    it = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_category_id', 'i_manager_id'])
+    fact = oq.read_fact(warehouse, 'store_sales', 'ss_sold_date_sk',
+                        ['ss_sold_date_sk', 'ss_item_sk', 'ss_ext_sales_price', 'ss_sales_price', 'ss_coupon_amt', 'ss_quantity'],
+                        dd['d_date_sk'].to_pylist())
+    j = fact.join(dd, keys='ss_sold_date_sk', right_keys='d_date_sk', join_type='inner').join(it, keys='ss_item_sk', right_keys='i_item_sk',
+                                                                                               join_type='inner')
+    groups = {}
+    for r in j.to_pylist():
+        groups.setdefault(r['i_category_id'], []).append(r)
+
+    def ssum(vals):
+        vals = [v for v in vals if v is not None]
+        return sum(vals) if vals else None
+
+    def both(x, y, f):
+        return None if x is None or y is None else f(x, y)
+    exp = []
+    for cat in sorted(groups, key=lambda c: (c is not None, c)):
+        rs = groups[cat]
+        q = [r['ss_quantity'] for r in rs if r['ss_quantity'] is not None]
+        exp.append({
+            'i_category_id': cat,
+            'a': ssum(both(r['ss_ext_sales_price'], r['ss_coupon_amt'], lambda x, y: x - y) for r in rs),
+            'b': ssum(both(r['ss_quantity'], r['ss_sales_price'], lambda x, y: x * y) for r in rs),
+            'c': ssum((r['ss_ext_sales_price'] if (r['i_manager_id'] is not None and r['i_manager_id'] < 50) else decimal.Decimal(0)) for r in rs),
+            'd': ssum(both(r['ss_quantity'], 1, lambda x, y: x + y) for r in rs),
+            'e': (max(q) - min(q)) if q else None,
+            'f': float(sum(q)) if q else None,
+            'g': ssum(both(r['ss_ext_sales_price'], 2, lambda x, y: x * y) for r in rs),
+        })
+    exp = exp[:100]
+    assert len(got) == len(exp) and len(got) > 3
+    for g, e in zip(got, exp):
+        for k in e:
+            if k == 'f' and e[k] is not None:
+                assert g[k] is not None and abs(g[k] - e[k]) <= 1e-9 * max(1.0, abs(e[k])), (k, g, e)
+            else:
+                assert g[k] == e[k], (k, g[k], e[k], g['i_category_id'])
