@@ -362,3 +362,61 @@ def test_aggregates_over_expressions_through_sql(gpu_engine, warehouse):
                 assert g[k] is not None and abs(g[k] - e[k]) <= 1e-9 * max(1.0, abs(e[k])), (k, g, e)
             else:
                 assert g[k] == e[k], (k, g[k], e[k], g['i_category_id'])
+
+
+def test_non_aggregating_and_single_table_queries_through_sql(gpu_engine, warehouse):
+    """Shapes without GROUP BY or without a join: a filtered star join ordered by a measure (top-k over raw rows), a
+    group-by over a computed string key on one dimension table, and a plain ORDER BY ... DESC NULLS FIRST - vs pyarrow."""
+    import pyarrow as pa
+    import pyarrow.compute as pc
+    sess = _Sess(gpu_engine)
+    # 1. top-k over joined rows
+    got = sess.sql('''select ss_ticket_number, ss_item_sk, ss_quantity, i_brand from store_sales, item, date_dim
+                      where ss_item_sk = i_item_sk and ss_sold_date_sk = d_date_sk and d_year = 1998 and d_moy = 2 and ss_quantity > 90
+                      order by ss_quantity desc, ss_ticket_number, ss_item_sk limit 50''').toArrow().to_pylist()
+    dd = oq.read_dim(warehouse, 'date_dim', ['d_date_sk', 'd_year', 'd_moy'])
+    dd = dd.filter(pc.and_(pc.equal(dd['d_year'], 1998), pc.equal(dd['d_moy'], 2)))
+    it = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_brand'])
+    fact = oq.read_fact(warehouse, 'store_sales', 'ss_sold_date_sk', ['ss_sold_date_sk', 'ss_item_sk', 'ss_ticket_number', 'ss_quantity'],
+                        dd['d_date_sk'].to_pylist())
+    fact = fact.filter(pc.fill_null(pc.greater(fact['ss_quantity'], 90), False))
+    j = fact.join(it, keys='ss_item_sk', right_keys='i_item_sk', join_type='inner')
+    rows = sorted(j.select(['ss_ticket_number', 'ss_item_sk', 'ss_quantity', 'i_brand']).to_pylist(),
+                  key=lambda r: (-r['ss_quantity'], r['ss_ticket_number'], r['ss_item_sk']))[:50]
+    assert got == rows and len(got) > 5
+    # 2. group by a computed string key, one table
+    got = sess.sql('''select substr(i_brand, 1, 6) b, count(*) n from item where i_manager_id < 20
+                      group by substr(i_brand, 1, 6) order by n desc, b limit 10''').toArrow().to_pylist()
+    it = oq.read_dim(warehouse, 'item', ['i_brand', 'i_manager_id'])
+    counts = {}
+    for r in it.to_pylist():
+        if r['i_manager_id'] is not None and r['i_manager_id'] < 20:
+            k = None if r['i_brand'] is None else r['i_brand'][:6]
+            counts[k] = counts.get(k, 0) + 1
+    exp = sorted(({'b': k, 'n': v} for k, v in counts.items()), key=lambda r: (-r['n'], (r['b'] is not None, r['b'])))[:10]   # NULLS FIRST asc
+    assert got == exp and len(got) > 1
+    # 3. ORDER BY ... DESC NULLS FIRST on strings
+    got = sess.sql('''select i_brand, i_class from item where i_category_id = 2
+                      order by i_brand desc nulls first, i_class limit 20''').toArrow().to_pylist()
+    it = oq.read_dim(warehouse, 'item', ['i_brand', 'i_class', 'i_category_id'])
+    rs = [{'i_brand': r['i_brand'], 'i_class': r['i_class']} for r in it.to_pylist() if r['i_category_id'] == 2]
+    import functools
+
+    def cmp(x, y):
+        a, b = x['i_brand'], y['i_brand']
+        if a != b:
+            if a is None:
+                return -1
+            if b is None:
+                return 1
+            return -1 if a.encode() > b.encode() else 1            # descending
+        a, b = x['i_class'], y['i_class']
+        if a == b:
+            return 0
+        if a is None:
+            return -1                                               # ascending: NULLS FIRST
+        if b is None:
+            return 1
+        return -1 if a.encode() < b.encode() else 1
+    exp = sorted(rs, key=functools.cmp_to_key(cmp))[:20]
+    assert got == exp and len(got) > 1
