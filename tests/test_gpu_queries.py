@@ -420,3 +420,22 @@ def test_non_aggregating_and_single_table_queries_through_sql(gpu_engine, wareho
         return -1 if a.encode() < b.encode() else 1
     exp = sorted(rs, key=functools.cmp_to_key(cmp))[:20]
     assert got == exp and len(got) > 1
+
+
+def test_string_predicates_through_sql(gpu_engine, warehouse):
+    """String IN lists, <>, >= / < (byte order) and IS [NOT] NULL on dictionary-encoded string columns, vs plain Python."""
+    sess = _Sess(gpu_engine)
+    it = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_category', 'i_class', 'i_brand']).to_pylist()
+    cats = sorted({r['i_category'] for r in it if r['i_category'] is not None})
+    classes = sorted({r['i_class'] for r in it if r['i_class'] is not None})
+    brands = sorted({r['i_brand'] for r in it if r['i_brand'] is not None}, key=lambda s: s.encode())
+    pick, bad_class, mid = cats[:2] + cats[-1:], classes[len(classes) // 2], brands[len(brands) // 2]
+    sql = """select i_item_sk, i_category, i_class, i_brand from item
+             where i_category in (%s) and i_class <> '%s' and (i_brand >= '%s' or i_brand is null) and i_class is not null
+             order by i_item_sk limit 100000""" % (', '.join("'%s'" % c.replace("'", "''") for c in pick), bad_class.replace("'", "''"),
+                                                    mid.replace("'", "''"))
+    got = sess.sql(sql).toArrow().to_pylist()
+    exp = [r for r in it if r['i_category'] in pick and r['i_class'] is not None and r['i_class'] != bad_class and
+           (r['i_brand'] is None or r['i_brand'].encode() >= mid.encode())]
+    exp.sort(key=lambda r: r['i_item_sk'])
+    assert got == exp and len(got) > 0
