@@ -439,3 +439,44 @@ def test_string_predicates_through_sql(gpu_engine, warehouse):
            (r['i_brand'] is None or r['i_brand'].encode() >= mid.encode())]
     exp.sort(key=lambda r: r['i_item_sk'])
     assert got == exp and len(got) > 0
+
+
+@pytest.mark.parametrize('fact,pcol,sql,dims,measure', [
+    ('catalog_sales', 'cs_sold_date_sk',
+     '''select i_category_id k, sum(cs_ext_sales_price) s, count(*) n from catalog_sales, date_dim, item
+        where cs_sold_date_sk = d_date_sk and cs_item_sk = i_item_sk and d_year = 1998 and d_moy = 1
+        group by i_category_id order by i_category_id limit 100''',
+     {'year': 1998, 'moy': 1, 'item_key': 'cs_item_sk', 'group': 'i_category_id'}, 'cs_ext_sales_price'),
+    ('web_returns', 'wr_returned_date_sk',
+     '''select d_moy k, sum(wr_return_amt) s, count(*) n from web_returns, date_dim
+        where wr_returned_date_sk = d_date_sk and d_year = 1998 group by d_moy order by d_moy limit 100''',
+     {'year': 1998, 'moy': None, 'item_key': None, 'group': 'd_moy'}, 'wr_return_amt'),
+    ('inventory', 'inv_date_sk',
+     '''select inv_warehouse_sk k, sum(inv_quantity_on_hand) s, count(*) n from inventory, date_dim
+        where inv_date_sk = d_date_sk and d_year = 1998 and d_moy = 1 group by inv_warehouse_sk order by inv_warehouse_sk limit 100''',
+     {'year': 1998, 'moy': 1, 'item_key': None, 'group': 'inv_warehouse_sk'}, 'inv_quantity_on_hand'),
+])
+def test_other_fact_tables_prune_and_aggregate(gpu_engine, warehouse, fact, pcol, sql, dims, measure):
+    """The engine is not store_sales-specific: the same star join + partition pruning + group-by on catalog_sales,
+    web_returns and inventory (each partitioned by its own date key), vs pyarrow."""
+    import pyarrow.compute as pc
+    got = _Sess(gpu_engine).sql(sql).toArrow().to_pylist()
+    dd = oq.read_dim(warehouse, 'date_dim', ['d_date_sk', 'd_year', 'd_moy'])
+    cond = pc.equal(dd['d_year'], dims['year'])
+    if dims['moy'] is not None:
+        cond = pc.and_(cond, pc.equal(dd['d_moy'], dims['moy']))
+    dd = dd.filter(cond)
+    cols = [pcol, measure] + ([dims['item_key']] if dims['item_key'] else []) + ([dims['group']] if dims['group'].startswith('inv_') else [])
+    f = oq.read_fact(warehouse, fact, pcol, cols, dd['d_date_sk'].to_pylist())
+    j = f.join(dd, keys=pcol, right_keys='d_date_sk', join_type='inner')
+    if dims['item_key']:
+        it = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_category_id'])
+        j = j.join(it, keys=dims['item_key'], right_keys='i_item_sk', join_type='inner')
+    groups = {}
+    for r in j.to_pylist():
+        g = groups.setdefault(r[dims['group']], [None, 0])
+        g[1] += 1
+        if r[measure] is not None:
+            g[0] = r[measure] if g[0] is None else g[0] + r[measure]
+    exp = [{'k': k, 's': v[0], 'n': v[1]} for k, v in sorted(groups.items(), key=lambda kv: (kv[0] is not None, kv[0]))][:100]
+    assert got == exp and len(got) > 0
