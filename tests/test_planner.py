@@ -170,3 +170,32 @@ def test_table_aliases_and_qualified_columns_plan_identically():
                  where dt.d_date_sk = ss.ss_sold_date_sk and ss.ss_item_sk = it.i_item_sk and it.i_manufact_id = 7 and dt.d_moy = 11
                  group by dt.d_year, it.i_brand_id order by dt.d_year, s desc, it.i_brand_id limit 100'''
     assert planner.plan_sql(aliased) == planner.plan_sql(plain)
+
+
+def test_dataframe_writer_formats_and_modes(tmp_path):
+    """The slice of DataFrameWriter the harness uses: parquet and csv outputs, overwrite vs the default errorifexists,
+    anything else raises (reference nds_power.py:133-135 writes `df.write.format(f).mode('overwrite').save(path)`)."""
+    import decimal
+    import os
+    import pyarrow as pa
+    import pyarrow.parquet as pq
+    import pytest
+    from spark_rapids_benchmarks_b200.engine import EngineError
+    from spark_rapids_benchmarks_b200.session import DataFrame
+    t = pa.table({'k': pa.array([1, 2, None]), 'd': pa.array([decimal.Decimal('1.50'), None, decimal.Decimal('-2.25')], type=pa.decimal128(7, 2)),
+                  's': pa.array(['a', None, 'c,d'])})
+    df = DataFrame(t)
+    p = str(tmp_path / 'out_parquet')
+    df.write.format('parquet').mode('overwrite').save(p)
+    assert os.path.exists(os.path.join(p, '_SUCCESS'))
+    assert pq.ParquetDataset(p).read().equals(t)
+    df.toDF('x', 'y', 'z').write.format('parquet').mode('overwrite').save(p)           # overwrite replaces the folder
+    assert pq.ParquetDataset(p).read().schema.names == ['x', 'y', 'z']
+    with pytest.raises(EngineError):
+        df.write.format('parquet').save(p)                                              # default mode: errorifexists
+    c = str(tmp_path / 'out_csv')
+    df.write.format('csv').mode('overwrite').save(c)
+    text = open([os.path.join(c, f) for f in os.listdir(c) if f.endswith('.csv')][0]).read()
+    assert text.splitlines()[0].replace('"', '') == 'k,d,s' and '"c,d"' in text
+    with pytest.raises(EngineError):
+        df.write.format('orc').mode('overwrite').save(str(tmp_path / 'out_orc'))
