@@ -480,3 +480,26 @@ def test_other_fact_tables_prune_and_aggregate(gpu_engine, warehouse, fact, pcol
             g[0] = r[measure] if g[0] is None else g[0] + r[measure]
     exp = [{'k': k, 's': v[0], 'n': v[1]} for k, v in sorted(groups.items(), key=lambda kv: (kv[0] is not None, kv[0]))][:100]
     assert got == exp and len(got) > 0
+
+
+def test_null_group_keys_through_sql(gpu_engine, warehouse):
+    """GROUP BY over nullable fact columns: NULL keys form their own groups and sort first (ascending); vs plain Python."""
+    import pyarrow.compute as pc
+    got = _Sess(gpu_engine).sql('''select ss_store_sk, ss_promo_sk, count(*) n, sum(ss_net_paid) s, count(ss_net_paid) c
+                                   from store_sales, date_dim where ss_sold_date_sk = d_date_sk and d_year = 1998 and d_moy = 1
+                                   group by ss_store_sk, ss_promo_sk order by ss_store_sk, ss_promo_sk limit 1000''').toArrow().to_pylist()
+    dd = oq.read_dim(warehouse, 'date_dim', ['d_date_sk', 'd_year', 'd_moy'])
+    dd = dd.filter(pc.and_(pc.equal(dd['d_year'], 1998), pc.equal(dd['d_moy'], 1)))
+    f = oq.read_fact(warehouse, 'store_sales', 'ss_sold_date_sk', ['ss_sold_date_sk', 'ss_store_sk', 'ss_promo_sk', 'ss_net_paid'],
+                     dd['d_date_sk'].to_pylist())
+    groups = {}
+    for r in f.to_pylist():
+        g = groups.setdefault((r['ss_store_sk'], r['ss_promo_sk']), [0, None, 0])
+        g[0] += 1
+        if r['ss_net_paid'] is not None:
+            g[1] = r['ss_net_paid'] if g[1] is None else g[1] + r['ss_net_paid']
+            g[2] += 1
+    key = lambda kv: tuple((v is not None, v if v is not None else 0) for v in kv[0])
+    exp = [{'ss_store_sk': k[0], 'ss_promo_sk': k[1], 'n': v[0], 's': v[1], 'c': v[2]} for k, v in sorted(groups.items(), key=key)][:1000]
+    assert got == exp
+    assert any(r['ss_store_sk'] is None for r in got) and any(r['ss_promo_sk'] is None for r in got)
