@@ -503,3 +503,18 @@ def test_null_group_keys_through_sql(gpu_engine, warehouse):
     exp = [{'ss_store_sk': k[0], 'ss_promo_sk': k[1], 'n': v[0], 's': v[1], 'c': v[2]} for k, v in sorted(groups.items(), key=key)][:1000]
     assert got == exp
     assert any(r['ss_store_sk'] is None for r in got) and any(r['ss_promo_sk'] is None for r in got)
+
+
+def test_host_source_equals_resident_source_on_other_shapes(gpu_engine):
+    """Pages copied from pinned host memory inside the query (`b200.source=host`) give the same rows as pages resident in
+    HBM, for fact tables and query shapes the six templates do not touch."""
+    sqls = ['''select i_category_id k, sum(cs_ext_sales_price) s, count(*) n from catalog_sales, date_dim, item
+               where cs_sold_date_sk = d_date_sk and cs_item_sk = i_item_sk and d_year = 1998 group by i_category_id order by i_category_id limit 100''',
+            '''select inv_warehouse_sk k, sum(inv_quantity_on_hand) s from inventory, date_dim where inv_date_sk = d_date_sk and d_moy = 1
+               group by inv_warehouse_sk order by inv_warehouse_sk limit 100''',
+            '''select sr_item_sk, sr_ticket_number, sr_return_amt from store_returns where sr_return_quantity > 95
+               order by sr_return_amt desc, sr_ticket_number, sr_item_sk limit 40''']
+    for sql in sqls:
+        a = _Sess(gpu_engine, 'hbm').sql(sql).toArrow()
+        b = _Sess(gpu_engine, 'host').sql(sql).toArrow()
+        assert a.num_rows > 0 and a.equals(b), sql
