@@ -1,8 +1,9 @@
 #!/usr/bin/env python3
-"""bench.py - NDS power-run seconds on the SF10 star-join subset (BASELINE.json configs[1]).
+"""bench.py - NDS power-run seconds at SF100 (the scale factor BASELINE.json's metric is quoted on).
 
-One "step" = one power run of the six-query stream (q3, q7, q19, q42, q52, q55) over the seeded
-synthetic SF10 warehouse (uncompressed Parquet, reference layout).  Prints ONE JSON line:
+One "step" = one power run of the six-query star-join stream (q3, q7, q19, q42, q52, q55: the statements this
+engine plans; the TPC templates of the other 93 are not in the reference) over the seeded synthetic SF100
+warehouse (uncompressed Parquet, reference layout; `--sf 10` gives BASELINE.json configs[1]).  Prints ONE JSON line:
 
   value      seconds per step with the encoded column chunks already resident in HBM, plans prebuilt,
              timed with CUDA events around each step (L2 flushed before every step), max over ranks
@@ -12,6 +13,9 @@ synthetic SF10 warehouse (uncompressed Parquet, reference layout).  Prints ONE J
              CUDA-event launch time vs the measured HBM peak in MEASURED_PEAKS.json; timed in extra single-stream
              steps because inside the timed region other streams' kernels share the SMs (that figure: in_step)
   cpu_baseline  the oracle's pyarrow-Acero restatement ("port", NOT Spark) on the same warehouse/stream
+  per_query     per statement: ms with resident pages (CUDA events) and ms end to end from host buffers
+  per_operator  per operator kind: CUDA-event ms, algorithmic bytes, fraction of the measured HBM peak (single-stream pass)
+  parity_checked  every statement's rows were compared with the CPU oracle's before timing (at every N; a mismatch aborts)
 
 `--impl reference` times that CPU restatement as the reference arm (Spark itself cannot run here:
 no JVM / pyspark on either box - BASELINE.md section 2).
@@ -31,8 +35,17 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-METRIC = 'NDS power-run seconds (SF10 star-join subset q3,q7,q19,q42,q52,q55)'
-WORKLOAD = 'NDS SF10 star-join aggregate subset (q3,q7,q19,q42,q52,q55), uncompressed Parquet, reference layout'
+def sf_label(sf):
+    return str(int(sf)) if sf == int(sf) else str(sf)
+
+
+def metric_name(sf):
+    return 'NDS power-run seconds (SF%s, star-join stream q3,q7,q19,q42,q52,q55)' % sf_label(sf)
+
+
+def workload_name(sf):
+    return ('NDS SF%s power run of the six-query star-join stream (q3,q7,q19,q42,q52,q55), uncompressed Parquet, '
+            'reference layout' % sf_label(sf))
 
 
 def parse_args():
@@ -41,7 +54,7 @@ def parse_args():
     ap.add_argument('--steps', type=int, default=5)
     ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    ap.add_argument('--sf', type=float, default=10)
+    ap.add_argument('--sf', type=float, default=100)
     ap.add_argument('--data_dir', default=os.environ.get('NDS_B200_DATA', ''))
     ap.add_argument('--sales_days', type=int, default=1823)
     ap.add_argument('--skip_cpu_baseline', action='store_true')
@@ -134,26 +147,38 @@ def use_all_host_threads():
     return n
 
 
-def cpu_power_run(query_dict, wh):
+def cpu_power_run(query_dict, wh, per_query=None):
     from oracle import nds_queries as oq
     t0 = time.perf_counter()
     rows = 0
     for name, sql in query_dict.items():
+        t1 = time.perf_counter()
         rows += oq.run_query(name, sql, wh).num_rows
+        if per_query is not None:
+            per_query.setdefault(name, []).append(time.perf_counter() - t1)
     return time.perf_counter() - t0, rows
 
 
-def measure_cpu(query_dict, wh, warmup, steps):
+def measure_cpu(query_dict, wh, warmup, steps, budget_s=150.0):
+    """Median of `steps` runs after `warmup` warm-ups (3 and 5), cut short - and said so -
+    when the projected time exceeds the budget."""
     import pyarrow as pa
     use_all_host_threads()
-    for _ in range(warmup):
+    t_first, _ = cpu_power_run(query_dict, wh)
+    done_w = 1
+    while done_w < warmup and t_first * (done_w + 1 + steps) <= budget_s:
         cpu_power_run(query_dict, wh)
-    times = [cpu_power_run(query_dict, wh)[0] for _ in range(steps)]
-    return statistics.median(times), pa.cpu_count()
+        done_w += 1
+    n = max(1, min(steps, int((budget_s - t_first * done_w) / max(t_first, 1e-6))))
+    per_query = {}
+    times = [cpu_power_run(query_dict, wh, per_query)[0] for _ in range(n)]
+    return statistics.median(times), pa.cpu_count(), done_w, n, {k: statistics.median(v) * 1000.0 for k, v in per_query.items()}
 
 
 def run_reference(args, rank, world):
-    """Reference arm: the CPU restatement of the path (oracle, pyarrow-Acero, all host threads)."""
+    """Reference arm: the CPU restatement of the path (oracle, pyarrow-Acero, all host threads).  Each step is the
+    whole six-query stream on the whole warehouse; when the projected run exceeds ~4 minutes fewer steps are timed
+    (reported in cpu_baseline.sample)."""
     if rank != 0:
         return
     log = lambda *a: print('[bench:reference]', *a, file=sys.stderr, flush=True)
@@ -162,22 +187,50 @@ def run_reference(args, rank, world):
     import pyarrow as pa
     use_all_host_threads()
     wh = data_dir(args)
-    for _ in range(args.warmup):
+    budget = 240.0
+    t_first, _ = cpu_power_run(qd, wh)
+    warm = 1
+    while warm < args.warmup and t_first * (warm + 1 + args.steps) <= budget:
         cpu_power_run(qd, wh)
+        warm += 1
+    steps = max(1, min(args.steps, int((budget - t_first * warm) / max(t_first, 1e-6))))
+    per_query = {}
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        cpu_power_run(qd, wh)
-    per_step = (time.perf_counter() - t0) / args.steps
-    line = {'impl': 'reference', 'metric': METRIC, 'value': per_step, 'unit': 's', 'n_gpus': args.gpus, 'steps': args.steps,
+    for _ in range(steps):
+        cpu_power_run(qd, wh, per_query)
+    per_step = (time.perf_counter() - t0) / steps
+    sample = 'the full six-query stream on the full SF%s warehouse per step, page cache warm; %d warm-up and %d timed steps run' % (
+        sf_label(args.sf), warm, steps)
+    line = {'impl': 'reference', 'metric': metric_name(args.sf), 'value': per_step, 'unit': 's', 'n_gpus': args.gpus, 'steps': args.steps,
             'warmup': args.warmup, 'ms_per_step': per_step * 1000.0, 'higher_is_better': False, 'scaling': 'strong',
             'vs_baseline': None, 'dtype': 'int64', 'data': 'synthetic',
-            'config': {'workload': WORKLOAD, 'engine': 'pyarrow-Acero CPU restatement (oracle port), not Spark: no JVM/pyspark on this box',
-                       'sf': args.sf, 'partition_pruning': True},
-            'cpu_baseline': {'value': per_step, 'unit': 's', 'cores': pa.cpu_count(), 'kind': 'port',
-                             'sample': 'the full six-query stream per step, page cache warm'},
+            'config': {'workload': workload_name(args.sf), 'engine': 'pyarrow-Acero CPU restatement (oracle port), not Spark: no JVM/pyspark on this box',
+                       'sf': args.sf, 'partition_pruning': True, 'steps_run': steps, 'warmup_run': warm},
+            'per_query': {k: {'ms_cpu': statistics.median(v) * 1000.0} for k, v in per_query.items()},
+            'cpu_baseline': {'value': per_step, 'unit': 's', 'cores': pa.cpu_count(), 'kind': 'port', 'sample': sample},
             'e2e': {'value': per_step, 'unit': 's', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
     print(json.dumps(line), flush=True)
+
+
+def rows_match(got, exp, rel_tol=1e-5):
+    """Exact for integers, strings, decimals, dates and row order; doubles within nds_validate's epsilon."""
+    import math
+    if got.schema.names != exp.schema.names or got.num_rows != exp.num_rows:
+        return False
+    for name in got.schema.names:
+        a, b = got.column(name).to_pylist(), exp.column(name).to_pylist()
+        for x, y in zip(a, b):
+            if isinstance(y, float) and isinstance(x, float):
+                if not math.isclose(x, y, rel_tol=rel_tol):
+                    return False
+            elif x != y:
+                return False
+    return True
+
+
+OP_KINDS = ('decode_kernel', 'scan_probe', 'gather_decode', 'filter', 'project', 'join_build', 'join_probe', 'join_probe_chain',
+            'aggregate', 'sort', 'exchange', 'dim_pipeline')
 
 
 def main():
@@ -227,11 +280,18 @@ def main():
     plans = {name: planner.plan_sql(sql, distributed=world > 1) for name, sql in qd.items()}
     flush = torch.empty(512 << 20, dtype=torch.uint8, device='cuda')   # > 126 MB L2
 
-    def resident_step(collect):
+    def ev():
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        return e
+
+    def resident_step(collect, marks=None):
         launches, ops, eng_ms = 0, [], 0.0
         for name, plan in plans.items():
             sess.source = 'hbm'
             sess.execute_plan(plan)
+            if marks is not None:
+                marks.append(ev())
             if collect:
                 st = sess.last_stats
                 launches += st['launches']
@@ -239,15 +299,42 @@ def main():
                 ops.extend(st['ops'])
         return launches, ops, eng_ms
 
-    def e2e_step(collect=False):
+    def e2e_step(collect=False, times=None):
         h2d = d2h = 0
         for name, sql in qd.items():
+            t1 = time.perf_counter()
             sess.source = 'host'
             sess.sql(sql).collect()
+            if times is not None:
+                times.setdefault(name, []).append(time.perf_counter() - t1)
             if collect:
                 h2d += sess.last_stats['h2d_bytes']
                 d2h += sess.last_stats['d2h_bytes']
         return h2d, d2h
+
+    # ---------------------------------------------------------------- parity: every statement against the CPU oracle, untimed
+    # Every rank runs the statement (N > 1: the exchange is a collective and every rank ends with the full result);
+    # rank 0 compares its rows with the oracle's on the unsharded warehouse.  A mismatch aborts the run.
+    parity_detail = {}
+    use_all_host_threads()
+    for name, sql in qd.items():
+        row = {}
+        for source in ('hbm', 'host'):
+            sess.source = source
+            got = sess.sql(sql).toArrow()
+            if rank == 0:
+                if 'exp' not in row:
+                    from oracle import nds_queries as oq
+                    row['exp'] = oq.run_query(name, sql, wh)
+                ok = rows_match(got, row['exp'])
+                parity_detail.setdefault(name, {})[source] = ok
+                if not ok:
+                    log('PARITY MISMATCH %s (source=%s): engine %s... oracle %s...' % (name, source, got.to_pylist()[:2], row['exp'].to_pylist()[:2]))
+                    os._exit(3)
+        if rank == 0:
+            parity_detail[name]['rows'] = row['exp'].num_rows
+    log('parity: %d statements match the CPU oracle on both sources' % len(qd))
+    barrier()
 
     # ---------------------------------------------------------------- warm-up (both paths)
     for _ in range(max(args.warmup, 3)):
@@ -260,16 +347,18 @@ def main():
     if rank == 0:
         sampler.start()
     total_ms, launches, ops, eng_ms = 0.0, 0, [], 0.0
+    q_ms = {name: 0.0 for name in plans}
     for _ in range(args.steps):
         flush.zero_()
         barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        resident_step(False)
+        marks = [ev()]
+        resident_step(False, marks)
         torch.cuda.synchronize()
-        e1.record()
+        e1 = ev()
         torch.cuda.synchronize()
-        total_ms += e0.elapsed_time(e1)
+        total_ms += marks[0].elapsed_time(e1)
+        for k, name in enumerate(plans):
+            q_ms[name] += marks[k].elapsed_time(marks[k + 1])
     barrier()
     # the same steps once more, untimed, to read the engine's statistics (kernel launches, per-operator events):
     # fetching and parsing them costs ~0.1 ms per query and does not belong in the timed region
@@ -284,11 +373,12 @@ def main():
     # ---------------------------------------------------------------- e2e: host buffers, public API
     t_e2e = 0.0
     h2d = d2h = 0
+    q_e2e = {}
     for _ in range(args.steps):
         flush.zero_()
         barrier()
         t1 = time.perf_counter()
-        e2e_step()
+        e2e_step(times=q_e2e)
         torch.cuda.synchronize()
         t_e2e += time.perf_counter() - t1
     barrier()
@@ -298,18 +388,21 @@ def main():
         d2h += b
     barrier()
     clocks = sampler.stop() if rank == 0 else None
-    # ---------------------------------------------------------------- roofline pass: the same steps on ONE stream
-    # In the timed region the fact-table decode shares the SMs with the build-side kernels of the other streams, so
-    # its CUDA-event bracket there is not the kernel's own duration.  These extra steps (same plans, same inputs,
-    # L2 flushed) keep every operator on one stream: the decode kernels run alone, as they do under ncu.
+    # ---------------------------------------------------------------- roofline pass: the same steps on ONE stream, per-operator events
+    # In the timed region the fact-table kernels share the SMs with the build-side kernels of the other streams, so
+    # their CUDA-event brackets there are not the kernels' own durations.  These extra steps (same plans, same inputs,
+    # L2 flushed) keep every operator on one stream with a pair of events around each: the kernels run alone, as
+    # they do under ncu.
     serial_ops = []
     for _ in range(args.steps):
         flush.zero_()
         torch.cuda.synchronize()
         for name, plan in plans.items():
-            # N > 1: the rank-local part of the plan (scan -> joins -> partial aggregate) holds the decode launches
-            sess.engine.execute({'root': plan.get('partial', plan['root'])}, options={'side_stream': False})
-            serial_ops.extend(sess.engine.last_stats()['ops'])
+            # N > 1: the rank-local part of the plan (scan -> joins -> partial aggregate) holds the fact-table launches
+            sess.engine.execute({'root': plan.get('partial', plan['root'])}, profile=True, options={'side_stream': False})
+            for o in sess.engine.last_stats()['ops']:
+                o['query'] = name
+                serial_ops.append(o)
     barrier()
 
     ms_per_step = total_ms / args.steps
@@ -322,42 +415,71 @@ def main():
         tdist.all_reduce(c, op=tdist.ReduceOp.SUM)
         launches, h2d, d2h = int(c[0]), int(c[1]), int(c[2])
 
-    # ---------------------------------------------------------------- roofline of the dominant kernel (rank 0's launches)
-    dec = [o for o in serial_ops if o['op'] == 'decode_kernel' and o['ms'] > 0]
-    dec_in_step = [o for o in ops if o['op'] == 'decode_kernel' and o['ms'] > 0]
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
     except Exception:
         pass
     peak = peaks.get('hbm_gbs', 6650.0)
+
+    # ---------------------------------------------------------------- per-operator table (rank 0's launches, single-stream pass)
+    per_op = {}
+    for o in serial_ops:
+        kind = o['op'].split(':')[0]
+        if kind not in OP_KINDS or o['ms'] <= 0 or o['bytes'] <= 0:
+            continue
+        a = per_op.setdefault(kind, {'ms': 0.0, 'bytes': 0, 'n': 0})
+        a['ms'] += o['ms']
+        a['bytes'] += o['bytes']
+        a['n'] += 1
+    for a in per_op.values():
+        a['gbs'] = a['bytes'] / (a['ms'] * 1e-3) / 1e9
+        a['frac'] = a['gbs'] / peak
+        a['ms'] /= args.steps
+        a['bytes'] //= args.steps
+        a['n'] //= args.steps
+    fr = sorted(a['frac'] for a in per_op.values())
+    median_frac = fr[len(fr) // 2] if fr else None
+    tot_b = sum(a['bytes'] for a in per_op.values())
+    tot_ms = sum(a['ms'] for a in per_op.values())
+    weighted_frac = (tot_b / (tot_ms * 1e-3) / 1e9 / peak) if tot_ms > 0 else None
+
+    # ---------------------------------------------------------------- roofline of the dominant kernel (rank 0's launches)
+    # dominant = the operator kind with the most device time in the single-stream pass; its largest launch is reported
     roof = None
-    if dec:
-        # the dominant launch: the largest decode launch of the stream (query7's store_sales scan), one per step
-        big = max(o['bytes'] for o in dec)
-        top = [o for o in dec if o['bytes'] == big]
-        ach = big / (sum(o['ms'] for o in top) / len(top) * 1e-3) / 1e9
-        all_bytes = sum(o['bytes'] for o in dec)
-        all_ms = sum(o['ms'] for o in dec)
-        traffic = None
-        tp = os.path.join(ROOT, 'profiles', 'decode_traffic.json')
+    fact_kinds = [k for k in ('scan_probe', 'decode_kernel') if k in per_op]
+    if fact_kinds:
+        dom = max(fact_kinds, key=lambda k: per_op[k]['ms'])
+        cand = [o for o in serial_ops if o['op'].split(':')[0] == dom and o['ms'] > 0]
+        big = max(o['bytes'] for o in cand)
+        top = [o for o in cand if o['bytes'] == big]
+        avg_ms = sum(o['ms'] for o in top) / len(top)
+        ach = big / (avg_ms * 1e-3) / 1e9
+        in_step = [o for o in ops if o['op'].split(':')[0] == dom and o['ms'] > 0 and o['bytes'] == big]
+        in_us = sum(o['ms'] for o in in_step) / max(len(in_step), 1) * 1000.0
+        traffic, traffic_src = None, None
+        tp = os.path.join(ROOT, 'profiles', 'kernel_traffic.json')
         if os.path.exists(tp) and world == 1:
             try:
-                traffic = json.load(open(tp)).get('dram_bytes_per_launch')
+                tj = json.load(open(tp)).get(dom, {})
+                if tj.get('sf') == args.sf:
+                    traffic, traffic_src = tj.get('dram_bytes_per_launch'), 'static: ' + tj.get('source', 'profiles/')
             except Exception:
-                traffic = None
-        top_in = [o for o in dec_in_step if o['bytes'] == big]
-        in_us = sum(o['ms'] for o in top_in) / max(len(top_in), 1) * 1000.0
-        roof = {'bound': 'hbm', 'kernel': 'def_pages_kernel + rows_pages_kernel (split page decode, one launch each)', 'achieved': ach, 'peak': peak, 'unit': 'GB/s', 'frac': ach / peak,
-                'traffic': traffic, 'peak_source': 'MEASURED_PEAKS.json (measured)' if 'hbm_gbs' in peaks else 'fallback 6.65 TB/s',
-                'launch': 'largest decode launch of the stream (store_sales scan of query7), %d launches' % len(top),
+                pass
+        kernel_names = {'scan_probe': 'def_pages_kernel + scan_probe_kernel (fused page decode -> join-chain probe, fact scan)',
+                        'decode_kernel': 'def_pages_kernel + rows_pages_kernel (split page decode, one launch each)'}
+        dec_all = [o for o in serial_ops if o['op'].split(':')[0] == dom and o['ms'] > 0]
+        roof = {'bound': 'hbm', 'kernel': kernel_names[dom], 'achieved': ach, 'peak': peak, 'unit': 'GB/s', 'frac': ach / peak,
+                'traffic': traffic, 'traffic_source': traffic_src,
+                'peak_source': 'MEASURED_PEAKS.json (measured)' if 'hbm_gbs' in peaks else 'fallback 6.65 TB/s',
+                'launch': 'largest %s launch of the stream (%s), %d launches' % (dom, top[0].get('query', '?'), len(top)),
                 'measured': 'CUDA events on the launching stream, in %d extra steps after the timed region that keep every operator on '
                             'one stream (options.side_stream=false) so that the kernels run alone; in_step is the same launch inside the '
                             'timed region, where build-side kernels on other streams share the SMs' % args.steps,
                 'in_step': {'avg_launch_us': in_us, 'achieved': (big / (in_us * 1e-6) / 1e9) if in_us > 0 else None},
-                'algorithmic_bytes_per_launch': big, 'avg_launch_us': sum(o['ms'] for o in top) / len(top) * 1000.0,
-                'all_decode_launches': {'n': len(dec), 'achieved': all_bytes / (all_ms * 1e-3) / 1e9,
-                                        'share_of_step': sum(o['ms'] for o in dec_in_step) / (eng_ms if eng_ms > 0 else 1.0)}}
+                'algorithmic_bytes_per_launch': big, 'avg_launch_us': avg_ms * 1000.0,
+                'all_launches_of_kind': {'n': len(dec_all), 'achieved': sum(o['bytes'] for o in dec_all) / (sum(o['ms'] for o in dec_all) * 1e-3) / 1e9,
+                                         'share_of_step': per_op[dom]['ms'] / tot_ms if tot_ms > 0 else None}}
 
     sys.stdout.flush()
     os.dup2(saved_stdout, 1)
@@ -368,28 +490,34 @@ def main():
         return
     # ---------------------------------------------------------------- CPU baseline (rank 0, N = 1 only)
     cpu = None
+    cpu_q = {}
     if world == 1 and not args.skip_cpu_baseline:
-        sec, cores = measure_cpu(qd, wh, 1, 2)
+        sec, cores, w_run, n_run, cpu_q = measure_cpu(qd, wh, 3, 5)
         cpu = {'value': sec, 'unit': 's', 'cores': cores, 'kind': 'port',
-               'sample': 'the full six-query stream (median of 2 after 1 warm-up), pyarrow-Acero restatement, not Spark'}
-    line = {'metric': METRIC, 'value': ms_per_step / 1000.0, 'unit': 's', 'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3),
+               'sample': 'the full six-query stream on the full warehouse (median of %d after %d warm-ups), pyarrow-Acero restatement, not Spark' % (n_run, w_run)}
+    per_query = {}
+    for name in plans:
+        per_query[name] = {'ms_resident': q_ms[name] / args.steps,
+                           'ms_e2e': statistics.mean(q_e2e.get(name, [0.0])) * 1000.0}
+        if name in cpu_q:
+            per_query[name]['ms_cpu'] = cpu_q[name]
+        if name in parity_detail:
+            per_query[name]['rows'] = parity_detail[name].get('rows')
+    line = {'metric': metric_name(args.sf), 'value': ms_per_step / 1000.0, 'unit': 's', 'n_gpus': world, 'steps': args.steps, 'warmup': max(args.warmup, 3),
             'ms_per_step': ms_per_step, 'higher_is_better': False, 'scaling': 'strong', 'vs_baseline': None, 'dtype': 'int64',
             'data': 'synthetic',
-            'config': {'workload': WORKLOAD, 'sf': args.sf, 'store_sales_rows_per_rank': info['rows'], 'files_per_rank': info['files'],
+            'config': {'workload': workload_name(args.sf), 'sf': args.sf, 'store_sales_rows_per_rank': info['rows'], 'files_per_rank': info['files'],
                        'l2': 'flushed (512 MiB write) before every timed step', 'partition_pruning': True,
                        'table_registration_s': setup_s, 'engine_device_ms_per_step': eng_ms / args.steps,
                        'gpu_launches_counted': 'in an identical untimed repeat of the timed steps',
-                       'parallelism': 'fact files sharded over %d GPU(s), dimensions replicated' % world},
+                       'parallelism': 'fact files sharded over %d GPU(s), dimensions replicated' % world,
+                       'value_excludes': 'SQL planning (plans prebuilt); e2e includes it, like the reference\'s timed region (nds_power.py:130)'},
             'e2e': {'value': e2e_s, 'unit': 's', 'h2d_bytes_per_step': h2d // args.steps, 'd2h_bytes_per_step': d2h // args.steps},
-            'gpu_launches': launches, 'roofline': roof, 'cpu_baseline': cpu, 'clocks': clocks}
-    if args.profile_ops:
-        agg = {}
-        for o in ops:
-            a = agg.setdefault(o['op'].split(':')[0], [0.0, 0, 0])
-            a[0] += o['ms']
-            a[1] += o['bytes']
-            a[2] += 1
-        line['ops'] = {k: {'ms': v[0], 'bytes': v[1], 'n': v[2]} for k, v in agg.items()}
+            'gpu_launches': launches, 'roofline': roof, 'cpu_baseline': cpu, 'clocks': clocks,
+            'parity_checked': True, 'parity': {'against': 'CPU oracle (oracle/nds_queries.py, Acero) on the unsharded warehouse, both sources; '
+                                                           'exact except doubles at rel 1e-5', 'statements': len(parity_detail)},
+            'per_query': per_query, 'per_operator': per_op, 'median_operator_frac': median_frac,
+            'bytes_weighted_operator_frac': weighted_frac}
     print(json.dumps(line), flush=True)
     if world > 1:
         tdist.destroy_process_group()

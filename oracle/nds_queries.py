@@ -60,12 +60,14 @@ def read_dim(warehouse, table, columns):
 def read_fact(warehouse, table, part_col, columns, part_values=None, shard=None):
     """Read a hive-partitioned fact table, keeping only partitions whose value is in part_values
     (what Spark's dynamic partition pruning does for these joins).  shard=(rank, world) keeps every
-    world-th file like the engine's multi-GPU sharding."""
+    world-th file like the engine's multi-GPU sharding.  The selected files are read by a pool of
+    threads (pyarrow releases the GIL while it decodes), so the scan uses the host's cores like the
+    joins and the group-by do."""
     d = os.path.join(warehouse, table)
-    parts = []
     file_idx = 0
     want = None if part_values is None else set(int(v) for v in part_values)
     cols = [c for c in columns if c != part_col]
+    todo = []
     for e in sorted(os.listdir(d)):
         p = os.path.join(d, e)
         if not os.path.isdir(p):
@@ -81,10 +83,21 @@ def read_fact(warehouse, table, part_col, columns, part_values=None, shard=None)
                 continue
             if want is not None and (v is None or v not in want):
                 continue
-            t = pq.ParquetFile(os.path.join(p, f)).read(columns=cols)
-            if part_col in columns:
-                t = t.append_column(part_col, pa.array([v] * t.num_rows, type=pa.int32()))
-            parts.append(t)
+            todo.append((os.path.join(p, f), v))
+
+    def read_one(job):
+        path, v = job
+        t = pq.ParquetFile(path).read(columns=cols, use_threads=False)
+        if part_col in columns:
+            t = t.append_column(part_col, pa.array([v] * t.num_rows, type=pa.int32()))
+        return t
+
+    if len(todo) > 4:
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max(1, min(pa.cpu_count(), 64))) as ex:
+            parts = list(ex.map(read_one, todo))
+    else:
+        parts = [read_one(j) for j in todo]
     if not parts:
         sch = pq.ParquetFile(_any_file(d)).schema_arrow
         fields = [sch.field(c) for c in cols] + ([pa.field(part_col, pa.int32())] if part_col in columns else [])

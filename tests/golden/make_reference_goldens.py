@@ -44,6 +44,7 @@ def install_stub_pyspark():
     class _T:
         def __init__(self, *a, **k):
             self.a = a
+            self.k = k
 
         @classmethod
         def typeName(cls):
@@ -284,6 +285,42 @@ def main():
         assert float(lt) >= 0 and seed.isdigit() and len(seed) == 11
         out['load_report'] = {'reference_parsers_accept_it': True, 'rngseed_digits': len(seed),
                               'first_line_prefix': open(rep).readline().split(':')[0]}
+        # ---- composite metric (nds_bench.py:334-357)
+        pm_cases = [('100', 4, 1200.0, 3600.0, 5000.0, 5200.0, 300.0, 320.0), ('1000', 2, 86400.0, 7200.5, 9000.0, 9100.25, 1000.0, 900.0),
+                    ('10', 1, 50.0, 12.5, 30.0, 31.0, 4.0, 5.0), ('3000', 8, 100000.0, 50000.0, 120000.0, 118000.0, 20000.0, 21000.0)]
+        out['get_perf_metric'] = [{'args': list(c), 'out': ref_bench.get_perf_metric(*c)} for c in pm_cases]
+        out['get_throughput_stream_nums'] = [{'n': n, 'which': w, 'out': ref_bench.get_throughput_stream_nums(n, w)}
+                                             for n in (3, 9) for w in (1, 2)]
+        # ---- schema catalogue: types and nullability as the reference's get_schemas builds them (nds_schema.py:49-716)
+        import nds_schema as ref_schema
+
+        def type_str(t):
+            n = type(t).__name__
+            if n == 'IntegerType':
+                return 'int32'
+            if n == 'LongType':
+                return 'int64'
+            if n == 'DoubleType':
+                return 'double'
+            if n == 'DateType':
+                return 'date'
+            if n == 'StringType':
+                return 'string'
+            if n == 'TimestampType':
+                return 'timestamp'
+            if n == 'DecimalType':
+                return 'decimal(%d,%d)' % (t.a[0], t.a[1])
+            if n in ('CharType', 'VarcharType'):
+                return '%s(%d)' % (n[:-4].lower(), t.a[0])
+            raise SystemExit('unmapped reference type ' + n)
+
+        def dump(schemas):
+            # a list of [table, columns] pairs: the JSON file is written with sorted keys and the table order matters
+            return [[tbl, [[f.a[0], type_str(f.a[1]), bool(f.k.get('nullable', f.a[2] if len(f.a) > 2 else True))] for f in st.a[0]]]
+                    for tbl, st in schemas.items()]
+        out['schemas'] = {'source_decimal': dump(ref_schema.get_schemas(True)), 'source_double': dump(ref_schema.get_schemas(False)),
+                          'maintenance_decimal': dump(ref_schema.get_maintenance_schemas(True)),
+                          'maintenance_double': dump(ref_schema.get_maintenance_schemas(False))}
     with open(os.path.join(HERE, 'reference_harness.json'), 'w') as f:
         json.dump(out, f, indent=1, sort_keys=True)
     print('wrote', os.path.join(HERE, 'reference_harness.json'), len(out['compare']), 'compare cases')

@@ -277,3 +277,45 @@ def test_load_report_is_what_the_reference_parsers_read(tmp_path):
     assert lines[0].split(':')[0] == G['load_report']['first_line_prefix'] and lines[0].endswith(' seconds')
     seed = [l for l in lines if 'RNGSEED used:' in l][0].split(':')[1].strip()
     assert seed.isdigit() and len(seed) == G['load_report']['rngseed_digits']
+
+
+def test_composite_metric_and_report_parsers(tmp_path):
+    """nds_bench.get_perf_metric (reference nds_bench.py:334-357) and the report parsers beside it, against values the
+    reference's own functions returned."""
+    from spark_rapids_benchmarks_b200 import nds_bench
+    for c in G['get_perf_metric']:
+        assert nds_bench.get_perf_metric(*c['args']) == c['out'], c
+    for c in G['get_throughput_stream_nums']:
+        assert nds_bench.get_throughput_stream_nums(c['n'], c['which']) == c['out']
+    rep = tmp_path / 'load.txt'
+    rep.write_text('Load Test Time: 1234 seconds\nLoad Test Finished at: x\nRNGSEED used: 07291122510\n')
+    assert nds_bench.get_load_time(str(rep)) == '1234' and nds_bench.get_load_end_timestamp(str(rep)) == '07291122510'
+    log = tmp_path / 'time.csv'
+    log.write_text('application_id,query,time/milliseconds\napp,query3,12\napp,Power Start Time,100\napp,Power End Time,111\napp,Power Test Time,11838\n')
+    assert nds_bench.get_power_time(str(log)) == '11838'
+    with pytest.raises(Exception):
+        nds_bench.get_power_time(str(rep))
+    out = tmp_path / 'metrics.csv'
+    nds_bench.write_metrics_report(str(out), {'scale_factor': 100, 'perf_metric': 42})
+    assert out.read_text() == 'scale_factor,100\nperf_metric,42\n'
+
+
+@pytest.mark.parametrize('which', ['source_decimal', 'source_double', 'maintenance_decimal', 'maintenance_double'])
+def test_schema_types_and_nullability_match_the_reference(which):
+    """Every column's name, type and nullability for the 24 source and 12 maintenance tables, as the reference's
+    get_schemas(use_decimal) / get_maintenance_schemas(use_decimal) build them (recorded by executing
+    /root/reference/nds/nds_schema.py under a stub pyspark - independent of the text extraction behind _schema_data.py)."""
+    from spark_rapids_benchmarks_b200 import nds_schema
+    use_decimal = which.endswith('decimal')
+    mine = nds_schema.get_schemas(use_decimal) if which.startswith('source') else nds_schema.get_maintenance_schemas(use_decimal)
+    ref = dict((t, cols) for t, cols in G['schemas'][which])
+    assert list(mine) == [t for t, _ in G['schemas'][which]]      # same tables, same order
+    for table, cols in ref.items():
+        sch = mine[table]
+        assert sch.names == [c[0] for c in cols], table
+        for (name, typ, nullable), field in zip(cols, sch):
+            assert field.nullable == nullable, (table, name)
+            assert field.type == nds_schema.arrow_type(typ, True), (table, name, typ, field.type)
+    if which == 'source_decimal':
+        spec = {t: [(n, ty, nu) for n, ty, nu in nds_schema.column_spec(t)] for t in ref}
+        assert spec == {t: [tuple(c) for c in cols] for t, cols in ref.items()}
