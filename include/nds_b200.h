@@ -107,7 +107,8 @@ NDS_API int nds_engine_last_stats(nds_engine* e, char* buf, int64_t buflen);
  * it until the process exits.  There is ONE table per GPU, reused by every call and left holding the last
  * call's keys; each call clears it first.  Two calls whose GPU work overlaps (different streams or threads)
  * would race on it - serialise them.  The first call on a device looks the table's address up
- * (cudaGetSymbolAddress, with that device current); make that first call outside any stream capture.
+ * (cudaGetSymbolAddress, with that device current), and EVERY call ends by copying its status flags to the host and
+ * synchronising cuda_stream: call it outside any stream capture, the first time and every time after.
  * On failure returns non-zero and nds_last_error() holds the message. */
 #define NDS_NOALLOC_MAX_BUILD_KEYS 65536
 NDS_API int nds_join_probe_i64_noalloc(const int64_t* build_keys_dev, int32_t n_build, const int64_t* probe_keys_dev,

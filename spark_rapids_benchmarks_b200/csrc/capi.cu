@@ -25,6 +25,12 @@ struct nds_engine {
     cudaGetLastError();                                                 \
     return 1;                                                           \
   }                                                                     \
+  catch (...) {                                                         \
+    if (e) (e)->impl->last_error = "unknown internal error";            \
+    else nds::set_global_error("unknown internal error");               \
+    cudaGetLastError();                                                 \
+    return 1;                                                           \
+  }                                                                     \
   return 0;
 
 static int copy_out(const std::string& s, char* buf, int64_t buflen) {

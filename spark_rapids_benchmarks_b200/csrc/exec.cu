@@ -102,9 +102,26 @@ int64_t pow10i(int k) {
 }
 
 uint32_t next_pow2(int64_t v) {
+  if (v > (int64_t(1) << 31)) fail("hash table for " + std::to_string(v / 2) + " rows exceeds 2^31 slots; shard the build side across GPUs");
   uint32_t c = 64;
   while ((int64_t)c < v) c <<= 1;
   return c;
+}
+
+// Deepest evaluation stack a postfix program reaches (expr.cuh: eval_program keeps kEvalStack values in registers /
+// local memory): leaves push, binary operators pop one, if() pops two.
+int stack_depth(const std::vector<Instr>& code) {
+  int d = 0, mx = 0;
+  for (const Instr& in : code) {
+    switch (in.op) {
+      case OP_COL: case OP_LIT_I: case OP_LIT_F: case OP_LIT_S: case OP_LIT_NULL: ++d; break;
+      case OP_NOT: case OP_ISNULL: case OP_ISNOTNULL: case OP_NEG_I: case OP_NEG_F: case OP_I2F: case OP_SUBSTR: break;
+      case OP_IF: d -= 2; break;
+      default: d -= 1; break;          // every other operator is binary
+    }
+    mx = std::max(mx, d);
+  }
+  return mx;
 }
 
 LType parse_type(const std::string& s) {
@@ -136,6 +153,10 @@ struct Blob {
     return (int)cols.size() - 1;
   }
   int add_prog(std::vector<Instr> code, const LType& t) {
+    const int depth = stack_depth(code);
+    if (depth > kEvalStack)
+      fail("plan: expression too deep (needs " + std::to_string(depth) + " stack entries, the evaluator has " + std::to_string(kEvalStack) +
+           "): nest fewer CASE branches / operands");
     progs.push_back(std::move(code));
     kinds.push_back(t.kind == LType::STR ? 2 : (t.kind == LType::F64 ? 1 : 0));
     return (int)progs.size() - 1;
@@ -225,7 +246,9 @@ struct RuntimeFilter {           // dynamic partition pruning: build-side join k
 
 }  // namespace
 
-struct SpeculationFailed {};     // a device-side size assumption did not hold; Engine::execute re-runs the plan without them
+struct SpeculationFailed : std::exception {     // a device-side size assumption did not hold; Engine::execute re-runs the plan without them
+  const char* what() const noexcept override { return "device-side size speculation failed twice"; }
+};
 
 struct Exec {
   Engine& e;
@@ -1393,6 +1416,15 @@ struct Exec {
           ot.is32 = false;
         } else fail("plan: unsupported aggregate function '" + fn + "'");
       }
+      if (a.has("type")) {
+        // the planner's declared result type (the merge side of a two-phase aggregate re-applies SUM to partial sums and
+        // must not widen the decimal precision a second time)
+        LType forced = parse_type(a.str("type"));
+        if ((forced.kind == LType::F64) != (ot.kind == LType::F64) || forced.kind == LType::STR)
+          fail("plan: type annotation '" + a.str("type") + "' contradicts aggregate '" + a.str("name") + "'");
+        ot = forced;
+        ot.is32 = false;
+      }
       specs.push_back(sp);
       atypes.push_back(ot);
       agg_codes.push_back(std::move(agg_code_of_this));
@@ -1841,6 +1873,10 @@ void Engine::execute_once(const Json& plan, ArrowSchema* out_schema, ArrowArray*
   const Json* options = plan.find("options");
   const Json& root = plan.has("root") ? plan.at("root") : plan;
   cudaEvent_t ev0 = get_event(), ev1 = get_event();
+  struct EventGuard {          // a failed or retried query returns its timing events to the pool too
+    Engine& en; cudaEvent_t a, b; bool armed = true;
+    ~EventGuard() { if (armed) { en.put_event(a); en.put_event(b); } }
+  } ev_guard{*this, ev0, ev1};
   NDS_CUDA(cudaEventRecord(ev0, stream_));
   std::vector<OpStat> op_stats;
   {
@@ -2076,6 +2112,12 @@ void Engine::execute_once(const Json& plan, ArrowSchema* out_schema, ArrowArray*
         bp = {hvalid, wide};
       } else if (col.lt.kind == LType::STR) {
         bp = {hvalid, hoffs_v[c], hchars_v[c]};
+      } else if (col.lt.kind == LType::DATE && dt != DT_I32) {
+        // a date that went through if() / min / max is held as int64 on the device; Arrow's date32 ("tdD") is 4 bytes wide
+        int32_t* narrow = (int32_t*)malloc(std::max<int64_t>(n * 4, 8));
+        apv->bufs.push_back(narrow);
+        for (int64_t i = 0; i < n; ++i) narrow[i] = (int32_t) reinterpret_cast<int64_t*>(hdata)[i];
+        bp = {hvalid, narrow};
       } else {
         bp = {hvalid, hdata};
       }
@@ -2112,6 +2154,7 @@ void Engine::execute_once(const Json& plan, ArrowSchema* out_schema, ArrowArray*
   float ms = 0;
   cudaEventElapsedTime(&ms, ev0, ev1);
   exec_ms_ = ms;
+  ev_guard.armed = false;
   put_event(ev0);
   put_event(ev1);
   for (OpStat& st : op_stats) {

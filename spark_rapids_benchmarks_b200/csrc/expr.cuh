@@ -39,7 +39,7 @@ struct Val {
   bool ok;        // not NULL
 };
 
-constexpr int kEvalStack = 8;
+constexpr int kEvalStack = 16;
 
 __device__ __forceinline__ int str_cmp(const uint8_t* a, uint32_t la, const uint8_t* b, uint32_t lb) {
   uint32_t m = la < lb ? la : lb;

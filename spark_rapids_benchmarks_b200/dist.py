@@ -111,9 +111,14 @@ def execute_distributed(session, plan):
     memory) -> merge aggregate -> project -> sort.  Otherwise (gloo, or no communicator): partial plan on this rank's
     shard -> all-gather of the partial states through the host -> merge on every rank; the summed statistics of
     both engine calls are left in session.dist_stats."""
+    src = session.source if session.source != 'hbm' else None
+    if plan.get('replicated'):
+        # the root table is replicated on every rank: each rank computes the whole result, nothing is exchanged
+        out = session.engine.execute({'root': plan['root']}, source=src)
+        session.dist_stats = None
+        return out
     if 'partial' not in plan:
         raise ValueError('plan was not built with distributed=True')
-    src = session.source if session.source != 'hbm' else None
     if getattr(session.engine, 'has_comm', False) and 'fused' in plan:
         key = '_json_fused_' + session.source
         payload = plan.get(key)

@@ -306,7 +306,12 @@ class Planner:
         return k
 
     # ---- the plan ---------------------------------------------------------------------------------------------
-    def plan(self, distributed=False):
+    def plan(self, distributed=False, sharded=None):
+        """distributed: plan partial aggregate -> exchange -> merge for engines that each hold a shard of the root table.
+        sharded: names of the tables the engines really hold in shards (None: the hive-partitioned fact tables of
+        TABLE_PARTITIONING).  A query whose root table is replicated on every rank is planned as a single-GPU plan
+        and marked 'replicated': every rank computes the whole result and nothing is exchanged - summing the ranks'
+        identical partial states would multiply every SUM and COUNT by the world size."""
         q = self.q
         conj = []
 
@@ -336,6 +341,9 @@ class Planner:
         if len(facts) > 1:
             raise PlanError('joins between fact tables (%s) are not supported yet' % ', '.join(facts))
         root = facts[0] if facts else self.tables[0]
+        replicated_root = distributed and root not in (nds_schema.TABLE_PARTITIONING if sharded is None else sharded)
+        if replicated_root:
+            distributed = False
         # ---- columns each table must produce
         need = {t: set() for t in self.tables}
         used = set()
@@ -441,8 +449,9 @@ class Planner:
                 final_partial = agg_node
                 merge = {'op': 'aggregate',
                          'keys': [{'name': k['name'], 'expr': _col(k['name'])} for k in keys],
+                         # 'type': the declared result type, so that the merged SUM of partial sums is not widened twice
                          'aggs': [{'name': a['name'], 'fn': {'count': 'sum', 'count_star': 'sum'}.get(a['fn'], a['fn']),
-                                   'expr': _col(a['name'])} for a in agg_map.specs()],
+                                   'expr': _col(a['name']), 'type': agg_map.types[a['name']]} for a in agg_map.specs()],
                          'child': {'op': 'scan', 'table': '__partial__',
                                    'columns': [k['name'] for k in keys] + [a['name'] for a in agg_map.specs()]}}
                 node = merge
@@ -489,6 +498,8 @@ class Planner:
                     keys.append({'expr': _col(n), 'desc': False})
             node = {'op': 'sort', 'keys': keys, 'limit': -1 if q['limit'] is None else q['limit'], 'child': node}
         out = {'root': node, 'output': [{'name': n, 'type': t} for n, _, t in out_cols]}
+        if replicated_root:
+            out['replicated'] = True
         if distributed:
             if final_partial is None:
                 raise PlanError('distributed execution needs an aggregating query')
@@ -520,6 +531,7 @@ class _AggMap:
     def __init__(self):
         self.items = {}
         self.order = []
+        self.types = {}
 
     def add(self, fn, ir, rtype):
         key = (fn, repr(ir))
@@ -530,6 +542,7 @@ class _AggMap:
             if ir is not None:
                 spec['expr'] = ir
             self.order.append(spec)
+            self.types[name] = rtype
         return self.items[key]
 
     def specs(self):
@@ -549,11 +562,11 @@ def _replace_partial_scan(node, replacement):
     return out
 
 
-def plan_sql(sql_text, distributed=False):
-    """SQL text -> plan dict ({'root': ..., 'output': [...]} [+ 'partial', 'fused'])."""
+def plan_sql(sql_text, distributed=False, sharded=None):
+    """SQL text -> plan dict ({'root': ..., 'output': [...]} [+ 'partial', 'fused' | 'replicated'])."""
     body = '\n'.join(l for l in sql_text.split('\n') if not l.strip().startswith('--'))
     try:
         ast = parse(body)
     except SqlError as e:
         raise PlanError(str(e))
-    return Planner(ast).plan(distributed=distributed)
+    return Planner(ast).plan(distributed=distributed, sharded=sharded)

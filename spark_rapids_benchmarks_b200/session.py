@@ -129,6 +129,7 @@ class Session:
         self.engine = Engine(device=device, resident=True, keep_host=keep_host or self.source == 'host',
                              rank=rank, world=world)
         self._stats = None
+        self._sharded = set()           # tables this rank holds a shard of (the others are replicated on every rank)
         if world > 1:
             # under torchrun with the nccl backend the engines get a communicator of their own, so that the
             # exchange between partial and final aggregation stays in device memory (dist.py)
@@ -147,9 +148,15 @@ class Session:
 
     def register_table(self, name, path, fmt='parquet'):
         self.engine.register_table(name, path, fmt)
+        if self.world > 1:
+            # the engine shards hive-partitioned tables by file and replicates the rest (tables.cu)
+            if self.engine.table_info(name).get('partition_column'):
+                self._sharded.add(name)
+            else:
+                self._sharded.discard(name)
 
     def plan(self, query):
-        return planner.plan_sql(query, distributed=self.world > 1)
+        return planner.plan_sql(query, distributed=self.world > 1, sharded=self._sharded if self.world > 1 else None)
 
     def sql(self, query):
         plan = self.plan(query)

@@ -38,6 +38,17 @@ def main():
                         else:
                             assert g[k] == e[k], (query, k, g[k], e[k])
         ok += 1
+    # schemas must not depend on the GPU count: sum(decimal(7,2)) stays decimal(17,2) through the merge
+    sess.source = 'hbm'
+    t3 = sess.sql(streams.render('query3', overrides={'MANUFACT': 606, 'MONTH': 1})).toArrow()
+    assert str(t3.schema.field('sum_agg').type) == 'decimal128(17, 2)', t3.schema
+    # a query over a replicated table: every rank computes the whole answer, nothing is exchanged, nothing is multiplied
+    import pyarrow.compute as pc
+    got = sess.sql('select i_category, count(*) cnt, sum(i_manager_id) s from item group by i_category order by i_category').toArrow()
+    item = oq.read_dim(wh, 'item', ['i_category', 'i_manager_id'])
+    exp = item.group_by('i_category').aggregate([([], 'count_all'), ('i_manager_id', 'sum')]).sort_by([('i_category', 'ascending')])
+    rows = {r['i_category']: (r['count_all'], r['i_manager_id_sum']) for r in exp.to_pylist()}
+    assert {r['i_category']: (r['cnt'], r['s']) for r in got.to_pylist()} == rows, (got.to_pylist()[:3], exp.to_pylist()[:3])
     tdist.barrier()
     if rank == 0:
         print('EXCHANGE-OK %d' % ok, flush=True)

@@ -323,3 +323,52 @@ def test_exchange_empty_input(gpu_engine, tbl):
                                         'child': {'op': 'scan', 'table': 't', 'columns': ['a', 's', 'g']}}}
     got = gpu_engine.execute(plan, options={'exchange_loopback': 2})
     assert got.num_rows == 0 and got.schema.names == ['a', 's', 'g']
+
+
+def test_expression_deeper_than_the_evaluator_stack_is_refused(gpu_engine, tbl):
+    """CASE with many branches nests if() two stack entries per level: the compiler must refuse what the evaluator
+    cannot hold instead of writing past its stack."""
+    from spark_rapids_benchmarks_b200.engine import EngineError
+
+    def case(depth):
+        e = lit(0)
+        for k in range(depth):
+            e = fn('if', fn('eq', col('g'), lit(k)), lit(100 + k), e)
+        return e
+    plan = lambda depth: {'op': 'project', 'exprs': [{'name': 'x', 'expr': case(depth)}, {'name': 'g', 'expr': col('g')}],
+                          'child': {'op': 'scan', 'table': 't', 'columns': ['g']}}
+    got = pa.Table.from_batches([gpu_engine.execute(plan(5))])          # a 5-branch CASE fits
+    exp = [None if g is None else (100 + g if g < 5 else 0) for g in tbl['g'].to_pylist()]
+    assert [x if g is not None else None for x, g in zip(got['x'].to_pylist(), got['g'].to_pylist())] == exp
+    with pytest.raises(EngineError, match='too deep'):
+        gpu_engine.execute(plan(40))
+
+
+def test_dates_through_case_and_min_max_export_as_date32(gpu_engine):
+    """A DATE that passes through if() or min()/max() is held as int64 on the device; the Arrow export must still be a
+    well-formed date32 column."""
+    import datetime
+    rng = np.random.default_rng(5)
+    n = 1000
+    days = rng.integers(9000, 12000, n).astype(np.int32)
+    d = pa.array(days, type=pa.int32(), mask=rng.random(n) < 0.1).cast(pa.date32())
+    k = pa.array(rng.integers(0, 7, n).astype(np.int64))
+    gpu_engine.register_arrow('dt', pa.table({'k': k, 'd': d}))
+    scan = {'op': 'scan', 'table': 'dt', 'columns': ['k', 'd']}
+    got = pa.Table.from_batches([gpu_engine.execute({'op': 'project', 'exprs': [
+        {'name': 'c', 'expr': fn('if', fn('lt', col('k'), lit(3)), col('d'), lit(None, 'date'))}, {'name': 'k', 'expr': col('k')},
+        {'name': 'd', 'expr': col('d')}], 'child': scan})])
+    assert got.schema.field('c').type == pa.date32()
+    assert got['c'].to_pylist() == [dv if kv < 3 else None for dv, kv in zip(got['d'].to_pylist(), got['k'].to_pylist())]
+    agg = pa.Table.from_batches([gpu_engine.execute({'op': 'sort', 'keys': [{'expr': col('k')}], 'child': {
+        'op': 'aggregate', 'keys': [{'name': 'k', 'expr': col('k')}],
+        'aggs': [{'name': 'lo', 'fn': 'min', 'expr': col('d')}, {'name': 'hi', 'fn': 'max', 'expr': col('d')}], 'child': scan}})])
+    assert agg.schema.field('lo').type == pa.date32() and agg.schema.field('hi').type == pa.date32()
+    by = {}
+    for kv, dv in zip(k.to_pylist(), d.to_pylist()):
+        if dv is not None:
+            by.setdefault(kv, []).append(dv)
+    assert agg['lo'].to_pylist() == [min(by[kv]) for kv in agg['k'].to_pylist()]
+    assert agg['hi'].to_pylist() == [max(by[kv]) for kv in agg['k'].to_pylist()]
+    assert isinstance(agg['lo'].to_pylist()[0], datetime.date)
+    gpu_engine.drop_table('dt')

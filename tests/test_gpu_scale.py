@@ -1,0 +1,88 @@
+"""GPU parity at a BASELINE.json scale: the six-query stream on an SF1 warehouse (2,880,404 store_sales rows) whose
+sales fall on 182 days, so that a partition file holds ~15.8 k rows - the page shape of the SF10 / SF100 bench
+warehouses (one 15.8 k-row page per column chunk, index streams of back-to-back 504-value bit-packed runs).
+The tiny SF 0.01 warehouse of the other tests never reaches these routes:
+
+  * the cursor-free rows path of the split page decode and the fused scan -> probe kernels over full-size pages,
+  * dictionaries larger than the shared-memory stage (customer keys, measures),
+  * the top-k prefilter (query7: ~9000 groups > the rank sort's 8192-row limit),
+  * the group-by with more groups than its shared-memory cache.
+
+Every statement is compared with the CPU oracle on both sources (pages resident in HBM / copied from host
+buffers inside the query): bit exact for integers, strings, decimals and row order, doubles at rel 1e-5.
+"""
+import math
+import os
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+SALES_DAYS = 182
+PARAMS = [{'MANUFACT': 606, 'MANAGER': 63, 'MONTH': 3, 'YEAR': 1998, 'GEN': 'M', 'MS': 'S', 'ES': 'College'},
+          {'MANUFACT': 17, 'MANAGER': 8, 'MONTH': 5, 'YEAR': 1998, 'GEN': 'F', 'MS': 'W', 'ES': 'Primary'}]
+
+
+@pytest.fixture(scope='module')
+def sf1(tmp_path_factory):
+    from spark_rapids_benchmarks_b200 import datagen, engine
+    d = os.environ.get('NDS_TEST_WAREHOUSE_SF1') or str(tmp_path_factory.mktemp('nds_sf1_d182'))
+    tables = list(datagen.SUBSET_TABLES)
+    rows = datagen.ensure(d, 1, tables=tables, sales_days=SALES_DAYS)
+    assert rows['store_sales'] == 2880404
+    eng = engine.Engine(device=0, resident=True, keep_host=True)
+    for t in tables:
+        eng.register_table(t, os.path.join(d, t))
+    yield d, eng
+    eng.close()
+
+
+def rows_equal(got, exp):
+    if len(got) != len(exp):
+        return False
+    for g, e in zip(got, exp):
+        if g.keys() != e.keys():
+            return False
+        for k in g:
+            if isinstance(e[k], float) and g[k] is not None:
+                if not math.isclose(g[k], e[k], rel_tol=1e-5):
+                    return False
+            elif g[k] != e[k]:
+                return False
+    return True
+
+
+@pytest.mark.parametrize('pi', range(len(PARAMS)))
+def test_six_query_stream_at_sf1_matches_oracle(sf1, pi):
+    from oracle import nds_queries as oq
+    from spark_rapids_benchmarks_b200 import streams
+    from tests.test_gpu_queries import _Sess
+    wh, eng = sf1
+    info = eng.table_info('store_sales')
+    assert info['rows'] == 2880404 and info['files'] == SALES_DAYS + 1
+    pages = [c['pages'] for c in info['columns'] if c['name'] == 'ss_item_sk'][0]
+    assert pages == info['files']                         # one ~15.8 k-row page per column chunk
+    for query in streams.SUBSET:
+        sql = streams.render(query, overrides=PARAMS[pi])
+        exp = oq.run_query(query, sql, wh)
+        assert exp.num_rows > 0, query
+        for source in ('hbm', 'host'):
+            s = _Sess(eng, source)
+            got = s.sql(sql).toArrow()
+            assert got.schema.names == exp.schema.names
+            assert [str(t) for t in got.schema.types] == [str(t) for t in exp.schema.types], (got.schema, exp.schema)
+            assert rows_equal(got.to_pylist(), exp.to_pylist()), (query, source, got.to_pylist()[:3], exp.to_pylist()[:3])
+
+
+def test_query7_at_sf1_takes_the_large_routes(sf1):
+    """The routes the small warehouse cannot reach are really taken here: thousands of groups (more than the group-by's
+    shared-memory cache and than the rank sort's direct limit)."""
+    from spark_rapids_benchmarks_b200 import planner, streams
+    wh, eng = sf1
+    sql = streams.render('query7', overrides=PARAMS[0])
+    plan = planner.plan_sql(sql)
+    node = plan['root']
+    while node['op'] != 'aggregate':
+        node = node['child']
+    groups = eng.execute({'root': node})
+    assert groups.num_rows > 8192, groups.num_rows

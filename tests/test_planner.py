@@ -199,3 +199,32 @@ def test_dataframe_writer_formats_and_modes(tmp_path):
     assert text.splitlines()[0].replace('"', '') == 'k,d,s' and '"c,d"' in text
     with pytest.raises(EngineError):
         df.write.format('orc').mode('overwrite').save(str(tmp_path / 'out_orc'))
+
+
+def test_distributed_plan_of_a_replicated_root_is_not_split():
+    """A query whose root table every rank holds in full (a dimension table, or a fact table that was stored
+    unpartitioned) must not be planned as partial -> exchange -> merge: each rank's 'partial' would be the whole
+    answer and the merge would multiply every SUM / COUNT by the world size."""
+    from spark_rapids_benchmarks_b200 import planner, streams
+    p = planner.plan_sql('select i_category, count(*) cnt, sum(i_manager_id) s from item group by i_category order by i_category', distributed=True)
+    assert p.get('replicated') is True and 'partial' not in p and 'fused' not in p
+    # a fact table the engines do not hold in shards (sharded = what Session learned from table_info)
+    sql = streams.render('query3')
+    assert 'partial' in planner.plan_sql(sql, distributed=True)
+    assert 'partial' in planner.plan_sql(sql, distributed=True, sharded={'store_sales'})
+    q = planner.plan_sql(sql, distributed=True, sharded=set())
+    assert q.get('replicated') is True and 'partial' not in q
+    assert q['root'] == planner.plan_sql(sql)['root']
+
+
+def test_merge_aggregates_carry_the_declared_type():
+    """sum(decimal(7,2)) is decimal(17,2) on one GPU; the merge of partial sums must declare the same type instead of
+    widening it to decimal(27,2) (the Arrow / Parquet result schema must not depend on the GPU count)."""
+    from spark_rapids_benchmarks_b200 import planner, streams
+    p = planner.plan_sql(streams.render('query7'), distributed=True)
+    merge = p['root']
+    while merge['op'] != 'aggregate':
+        merge = merge['child']
+    types = {a['name']: a['type'] for a in merge['aggs']}
+    assert sorted(set(types.values())) == ['decimal(17,2)', 'int64']
+    assert all('type' not in a for a in p['partial']['aggs'])

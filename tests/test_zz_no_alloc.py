@@ -6,7 +6,8 @@ by a library fails or slips past the pool's spill accounting, so such a caller n
 hash table is not allocated per call.  This entry point keeps the table in a fixed array inside the
 library (at most NDS_NOALLOC_MAX_BUILD_KEYS = 65536 build keys).
 
-The test drives it through the C ABI with caller-owned device buffers and checks it, bit for bit,
+The test drives it through the C ABI with caller-owned device buffers and checks it, bit for bit, first
+against a plain dictionary lookup on the host (an oracle that shares no code with the kernels) and then
 against the regular entry point (nds_engine_execute running a join plan), twice in a row: the table is
 shared between calls and still holds the first call's keys when the second one starts.
 This file sorts last on purpose (pytest collects files alphabetically).
@@ -38,6 +39,12 @@ def _reference_via_engine(eng, build, probe):
     return out
 
 
+def _reference_on_host(build, probe):
+    """The definition itself: position of each probe key among the (unique) build keys, -1 if absent."""
+    where = {int(k): i for i, k in enumerate(build.tolist())}
+    return np.array([where.get(int(k), -1) for k in probe.tolist()], dtype=np.int32)
+
+
 def _call_noalloc(lib, torch, build, probe):
     d_build = torch.from_numpy(build).cuda()
     d_probe = torch.from_numpy(probe).cuda()
@@ -61,8 +68,10 @@ def test_noalloc_join_matches_engine_twice_in_a_row():
              (np.array([-5, 7, 2 ** 40, 14, 18], dtype=np.int64), rng.integers(-10, 60, 4099).astype(np.int64))]
     for build, probe in cases:
         got = _call_noalloc(lib, torch, build, probe)
+        oracle = _reference_on_host(build, probe)
+        assert got.dtype == oracle.dtype and np.array_equal(got, oracle)   # integer indices: bit-exact
         exp = _reference_via_engine(eng, build, probe)
-        assert got.dtype == exp.dtype and np.array_equal(got, exp)      # integer indices: bit-exact
+        assert got.dtype == exp.dtype and np.array_equal(got, exp)      # and identical to the allocating entry point
         assert (got >= 0).sum() > 0 and (got < 0).sum() > 0
     # empty sides
     e = np.empty(0, dtype=np.int64)
