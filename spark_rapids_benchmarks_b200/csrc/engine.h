@@ -57,6 +57,11 @@ struct PageInfo {
   uint8_t enc;                 // 0 PLAIN, 1 dictionary
   uint8_t bw = 0;              // dictionary index bit width (first byte of the values section)
   uint8_t fast = 0;            // 1: eligible for the split def/rows kernels (PLAIN fixed width, or few long index runs)
+  // 1: value k of the page can be addressed without walking run headers - PLAIN fixed width, a one-entry dictionary
+  // (bit width 0), or an index stream of back-to-back 504-value bit-packed runs (every header byte 0x7F, the last run
+  // shorter): what the fused scan -> probe kernels and the late-materialising gather need (fused_scan.cu)
+  uint8_t direct = 0;
+  uint32_t direct_values = 0;  // values the uniform index stream holds (>= the page's non-null count when well formed)
 };
 struct DictInfo {
   int64_t off;                 // fixed width: values; BYTE_ARRAY: StrView table (chars follow)
@@ -89,6 +94,12 @@ struct TableColumn {
   // file, vr != null marks a split-route page. A scan copies a file's run of templates and patches five fields.
   std::vector<PageTask> task_tmpl;
   std::vector<int64_t> file_bytes_in;    // per file: page payload bytes + dictionary bytes a scan of it reads
+  std::vector<uint8_t> file_direct;      // per file: every page is directly addressable (PageInfo::direct) and def_len <= 8192
+  // value range from the Parquet column-chunk statistics (INT32 / INT64 columns; valid only when every chunk had them):
+  // bounds the direct-address join table built over this column (ops.cu, dense tables)
+  bool has_stats = false;
+  int64_t stat_lo = 0, stat_hi = -1;
+  int stat_chunks = 0, total_chunks = 0;
 };
 struct MemColumn {                      // table registered from Arrow buffers
   std::string name;

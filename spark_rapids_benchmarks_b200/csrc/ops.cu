@@ -168,6 +168,12 @@ join_build_kernel(ColRef key, const int* n_dev, int64_t n_host, HashTable ht, in
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     Val k = load_col(key, i);
     if (!k.ok) continue;                       // NULL keys never match an equi-join
+    if (ht.dense) {
+      const uint64_t d = (uint64_t)(k.v - ht.lo);
+      if (d >= (uint64_t)ht.range) { atomicOr(flags, 4); continue; }      // outside the range the column statistics promised
+      if (atomicCAS(&ht.dense[d], 0u, (uint32_t)i + 1u) != 0u) atomicOr(flags, 1);
+      continue;
+    }
     if (k.v == kEmptyKey) { atomicOr(flags, 2); continue; }
     uint32_t s = (uint32_t)mix64((uint64_t)k.v) & ht.mask;
     for (;;) {
@@ -207,15 +213,7 @@ join_probe_kernel(ColRef key, const int* n_dev, int64_t n_host, HashTable ht, ui
     uint32_t b = 0;
     if (i < n) {
       Val k = load_col(key, i);
-      if (k.ok && k.v != kEmptyKey) {
-        uint32_t s = (uint32_t)mix64((uint64_t)k.v) & ht.mask;
-        for (;;) {
-          int64_t cur = ht.keys[s];
-          if (cur == k.v) { hit = true; b = ht.vals[s]; break; }
-          if (cur == kEmptyKey) break;
-          s = (s + 1) & ht.mask;
-        }
-      }
+      if (k.ok) hit = ht_find(ht, k.v, b);
     }
     int pos = warp_append(hit, out_count);
     if (hit) { out_probe[pos] = (uint32_t)i; out_build[pos] = b; }
@@ -237,16 +235,7 @@ join_probe_chain_kernel(const ProbeChain c, const int* n_dev, int64_t n_host, ui
       b[j] = 0;
       if (j < c.n && hit) {
         Val k = load_col(c.key[j], i);
-        hit = false;
-        if (k.ok && k.v != kEmptyKey) {
-          uint32_t s = (uint32_t)mix64((uint64_t)k.v) & c.ht[j].mask;
-          for (;;) {
-            int64_t cur = c.ht[j].keys[s];
-            if (cur == k.v) { hit = true; b[j] = c.ht[j].vals[s]; break; }
-            if (cur == kEmptyKey) break;
-            s = (s + 1) & c.ht[j].mask;
-          }
-        }
+        hit = k.ok && ht_find(c.ht[j], k.v, b[j]);
       }
     }
     int pos = warp_append(hit, out_count);

@@ -24,11 +24,41 @@ struct RowCount {        // rows of a batch: device-side count if known only the
 
 constexpr int64_t kEmptyKey = INT64_MIN;
 
+// Join table over the build side's keys, one of two layouts:
+//  * open addressing (dense == nullptr): 64-bit keys + 32-bit payload (the build-side batch row), linear probing,
+//    load factor <= 0.5;
+//  * direct addressing (dense != nullptr): the keys are known to lie in [lo, lo + range) - the Parquet statistics of a
+//    surrogate-key column - and dense[key - lo] holds build row + 1 (0: no such key).  One 4-byte load per probe and
+//    no hashing: the perfect-hash special case every NDS dimension key falls into.
 struct HashTable {
-  int64_t* keys;
-  uint32_t* vals;
-  uint32_t mask;
+  int64_t* keys = nullptr;
+  uint32_t* vals = nullptr;
+  uint32_t mask = 0;
+  uint32_t range = 0;
+  uint32_t* dense = nullptr;
+  int64_t lo = 0;
 };
+
+#ifdef __CUDACC__
+// build row of `key` (a non-null key), or false
+__device__ __forceinline__ bool ht_find(const HashTable& ht, int64_t key, uint32_t& row) {
+  if (ht.dense) {
+    const uint64_t d = (uint64_t)(key - ht.lo);
+    if (d >= (uint64_t)ht.range) return false;
+    const uint32_t v = __ldg(ht.dense + d);
+    row = v - 1u;
+    return v != 0u;
+  }
+  if (key == kEmptyKey) return false;
+  uint32_t s = (uint32_t)mix64((uint64_t)key) & ht.mask;
+  for (;;) {
+    const int64_t cur = ht.keys[s];
+    if (cur == key) { row = ht.vals[s]; return true; }
+    if (cur == kEmptyKey) return false;
+    s = (s + 1) & ht.mask;
+  }
+}
+#endif
 
 // AGG_COUNT_REF: count(x) where another aggregate over the same x already counts the non-null rows (AVG = SUM + COUNT):
 // prog holds that aggregate's index, nothing is accumulated, the finalize step reads the other aggregate's counter.

@@ -113,8 +113,25 @@ SchemaElement parse_schema_element(TC& c) {
   return e;
 }
 
+// Statistics struct of a column chunk: keeps the raw min / max bytes (new-style fields win over the deprecated ones)
+void parse_statistics(TC& c, std::string& mn, std::string& mx) {
+  std::string old_min, old_max, new_min, new_max;
+  bool have_new_min = false, have_new_max = false, have_old_min = false, have_old_max = false;
+  int16_t fid = 0; int t;
+  while (c.next_field(fid, t)) {
+    if (t == 8 && fid == 1) { old_max = c.binary(); have_old_max = true; }
+    else if (t == 8 && fid == 2) { old_min = c.binary(); have_old_min = true; }
+    else if (t == 8 && fid == 5) { new_max = c.binary(); have_new_max = true; }
+    else if (t == 8 && fid == 6) { new_min = c.binary(); have_new_min = true; }
+    else c.skip(t);
+  }
+  if (have_new_min && have_new_max) { mn = new_min; mx = new_max; }
+  else if (have_old_min && have_old_max) { mn = old_min; mx = old_max; }
+}
+
 ColumnChunk parse_column_meta(TC& c) {
   ColumnChunk m;
+  std::string smin, smax;
   int16_t fid = 0; int t;
   while (c.next_field(fid, t)) {
     switch (fid) {
@@ -130,8 +147,15 @@ ColumnChunk parse_column_meta(TC& c) {
       case 7: m.total_compressed = c.zigzag(); break;
       case 9: m.data_page_offset = c.zigzag(); break;
       case 11: m.dictionary_page_offset = c.zigzag(); break;
+      case 12: if (t == 12) parse_statistics(c, smin, smax); else c.skip(t); break;
       default: c.skip(t);
     }
+  }
+  const size_t w = m.type == INT32 ? 4 : (m.type == INT64 ? 8 : 0);
+  if (w && smin.size() == w && smax.size() == w) {
+    if (w == 4) { int32_t a, b; memcpy(&a, smin.data(), 4); memcpy(&b, smax.data(), 4); m.min_i = a; m.max_i = b; }
+    else { memcpy(&m.min_i, smin.data(), 8); memcpy(&m.max_i, smax.data(), 8); }
+    m.has_minmax = m.min_i <= m.max_i;
   }
   return m;
 }

@@ -34,6 +34,10 @@ struct ColumnChunk {
   int64_t data_page_offset = 0;
   int64_t dictionary_page_offset = -1;
   std::string path;
+  // Statistics.min_value / max_value (fields 6 / 5; the deprecated min / max, fields 2 / 1, as a fallback) of
+  // INT32 / INT64 chunks, little-endian PLAIN bytes; has_minmax only when both were present and well-formed
+  bool has_minmax = false;
+  int64_t min_i = 0, max_i = 0;
 };
 
 struct RowGroup {

@@ -188,6 +188,12 @@ void Engine::register_table(const std::string& name, const std::string& path, co
         TableColumn& tc = t.cols[c];
         if (!tc.supported) continue;
         const pq::ColumnChunk& cc = rg.columns[c];
+        ++tc.total_chunks;
+        if (cc.has_minmax) {
+          if (tc.stat_chunks == 0) { tc.stat_lo = cc.min_i; tc.stat_hi = cc.max_i; }
+          else { tc.stat_lo = std::min(tc.stat_lo, cc.min_i); tc.stat_hi = std::max(tc.stat_hi, cc.max_i); }
+          ++tc.stat_chunks;
+        }
         if (cc.codec != 0)
           fail("column '" + tc.name + "' in '" + fi.path + "' is compressed (codec " + std::to_string(cc.codec) +
                "); this engine reads uncompressed parquet only (nds_transcode --compression none)");
@@ -292,6 +298,31 @@ void Engine::register_table(const std::string& name, const std::string& path, co
                 pi.fast = runs <= 64;
               }
             }
+            // directly addressable pages (engine.h, PageInfo::direct): the whole index stream is checked here, once
+            pi.direct = 0;
+            if (pi.def_len <= 8192 && ph.num_values > 0) {
+              if (pi.enc == 0) pi.direct = tc.phys != pq::BYTE_ARRAY;
+              else if (pi.bw == 0) pi.direct = 1;
+              else {
+                int64_t p = values_off + 1;
+                const int64_t full = 1 + 63 * (int64_t)pi.bw;
+                int64_t covered = 0;
+                bool ok = true;
+                while (p < psize && ok) {
+                  const uint8_t h = payload[p];
+                  if (h == 0x7F && p + full <= psize) { p += full; covered += 504; continue; }
+                  // the last run: a shorter bit-packed run with a one-byte header that ends the stream
+                  if (!(h & 1) || h >= 0x80) { ok = false; break; }
+                  const int64_t groups = h >> 1;
+                  if (p + 1 + groups * pi.bw > psize) { ok = false; break; }
+                  covered += groups * 8;
+                  p += 1 + groups * pi.bw;
+                  if (p != psize) ok = false;
+                }
+                pi.direct = ok && covered >= 0;
+                pi.direct_values = (uint32_t)std::min<int64_t>(covered, 0x7FFFFFFF);
+              }
+            }
             // place the payload so that its values section is 16 B aligned
             int64_t cur = (int64_t)tc.stage.size();
             int64_t off = align_up(cur + values_off, 16) - values_off;
@@ -325,10 +356,13 @@ void Engine::register_table(const std::string& name, const std::string& path, co
     const int width = tc.lt.dtype() == DT_I32 ? 4 : 8;
     tc.task_tmpl.resize(tc.pages.size());
     tc.file_bytes_in.assign(tc.file_page_begin.size() - 1, 0);
+    tc.file_direct.assign(tc.file_page_begin.size() - 1, 1);
+    tc.has_stats = tc.total_chunks > 0 && tc.stat_chunks == tc.total_chunks && tc.lt.kind != LType::STR && tc.lt.kind != LType::F64;
     for (size_t f = 0; f + 1 < tc.file_page_begin.size(); ++f) {
       int last_dict = -1;
       for (int64_t p = tc.file_page_begin[f]; p < tc.file_page_begin[f + 1]; ++p) {
         const PageInfo& pi = tc.pages[p];
+        if (!pi.direct) tc.file_direct[f] = 0;
         PageTask& task = tc.task_tmpl[p];
         memset(&task, 0, sizeof task);
         task.src = reinterpret_cast<const uint8_t*>((uintptr_t)pi.off);
