@@ -6,7 +6,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, 'libndsb200.so')
-SOURCES = ['capi.cu', 'exec.cu', 'tables.cu', 'ops.cu', 'decode.cu', 'decode_fast.cu', 'noalloc.cu', 'parquet_meta.cc', 'nccl_dyn.cc']
+SOURCES = ['capi.cu', 'exec.cu', 'tables.cu', 'ops.cu', 'decode.cu', 'decode_fast.cu', 'fused_scan.cu', 'noalloc.cu', 'parquet_meta.cc', 'nccl_dyn.cc']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17',
               '-Xcompiler', '-fPIC', '-Xcompiler', '-fvisibility=hidden']
 

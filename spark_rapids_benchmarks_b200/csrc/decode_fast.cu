@@ -61,8 +61,8 @@ def_pages_kernel(const PageTask* __restrict__ tasks, const int* __restrict__ tas
   uint32_t* vr_valid = t.vr;
   uint32_t* vr_rank = t.vr + nw;
   const uint32_t sh = (uint32_t)(t.out_row & 31);
-  uint32_t* vout = t.valid + (t.out_row >> 5);
-  const uint32_t nwo = (n + sh + 31) >> 5;
+  uint32_t* vout = t.valid ? t.valid + (t.out_row >> 5) : nullptr;   // null: only the page-local words are wanted (fused scan)
+  const uint32_t nwo = vout ? (n + sh + 31) >> 5 : 0u;
 
   if (t.def_len == 0) {
     // page without def levels (REQUIRED in this file) of a column that is nullable elsewhere: everything valid

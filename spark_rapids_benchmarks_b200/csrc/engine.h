@@ -127,6 +127,10 @@ struct Column {
   const uint32_t* valid = nullptr;
   const uint32_t* rowmap = nullptr;
   const uint8_t* strbase = nullptr;
+  // value range promised by the Parquet statistics of the table column this one still is (unchanged values, possibly
+  // fewer rows); lost by anything computed.  Lets a join build a direct-address table over it (ops.cuh, HashTable).
+  bool has_range = false;
+  int64_t range_lo = 0, range_hi = -1;
   ColRef ref() const {
     ColRef r;
     r.data = data; r.valid = valid; r.rowmap = rowmap; r.strbase = strbase; r.dtype = lt.dtype(); r.pad = 0;

@@ -262,6 +262,8 @@ struct Exec {
   bool side_stream = true;       // options.side_stream=false keeps every operator on one stream
   int64_t small_scan_pages = 64; // options.small_scan_pages: scans with fewer split-route pages use the general kernel only
   bool speculate = true;         // options.speculate=false: never size a launch on an unverified device-side count
+  bool dense_tables = true;      // options.dense_tables=false: every join table is an open-addressing hash table
+  bool fused_scan = true;        // options.fused_scan=false: fact scans decode every column, then probe (decode_fast.cu + ops.cu)
   bool trace = false;            // options.trace: host timeline marks + time spent waiting in each stream sync
   double t_base = 0;
   std::string trace_out;
@@ -285,6 +287,8 @@ struct Exec {
       side_stream = options->bool_or("side_stream", true);
       speculate = options->bool_or("speculate", true);
       small_scan_pages = options->int_or("small_scan_pages", 64);
+      dense_tables = options->bool_or("dense_tables", true);
+      fused_scan = options->bool_or("fused_scan", true);
     }
     t_base = now_ms();
     if (!e.side_streams_.empty() && side_stream) {
@@ -391,6 +395,7 @@ struct Exec {
     if (h[2]) throw SpeculationFailed();
     if (h[1] & 1) fail("hash join: duplicate keys on the build side (only unique build keys are supported)");
     if (h[1] & 2) fail("hash join: key equals the reserved empty marker");
+    if (h[1] & 4) fail("hash join: a build key lies outside the range its column's Parquet statistics state (corrupt statistics)");
   }
 
   // ---- dynamic partition pruning: wait for the build keys (usually long since on the host) and index them
@@ -670,6 +675,52 @@ struct Exec {
   }
 
   // ---------------------------------------------------------------- scan
+  struct FileSel {                 // files of a table that survive partition pruning, and where their rows start
+    std::vector<int> sel;
+    std::vector<int64_t> row_start;      // sel.size() + 1 entries
+    int64_t N = 0;
+    bool pruned = false;
+  };
+  FileSel select_files(Table& t, std::vector<RuntimeFilter>& filters) {
+    const RuntimeFilter* rf = nullptr;
+    for (const RuntimeFilter& f : filters)
+      if (f.column == t.part_col && !t.part_col.empty()) rf = &f;
+    if (rf) resolve(*rf);
+    FileSel fs;
+    fs.pruned = rf != nullptr;
+    for (size_t f = 0; f < t.files.size(); ++f) {
+      const FileInfo& fi = t.files[f];
+      if (rf && (fi.part_null || !rf->contains(fi.part_val))) continue;
+      fs.sel.push_back((int)f);
+      fs.row_start.push_back(fs.N);
+      fs.N += fi.rows;
+    }
+    fs.row_start.push_back(fs.N);
+    return fs;
+  }
+  // Address of staged byte 0 of a column for a scan of the selected files: the resident copy in HBM, or - source=host - a
+  // per-query device buffer into which the selected files' byte ranges are copied (adjacent ranges coalesced).
+  const uint8_t* column_bytes(TableColumn& tc, const std::vector<int>& sel) {
+    if (sel.empty()) return nullptr;
+    if (!source_host) {
+      if (!tc.d_enc) fail("engine was created with resident=false; use source=host");
+      return tc.d_enc;
+    }
+    if (!tc.h_enc) fail("engine was created without keep_host; source=host is unavailable");
+    const int64_t span_b = tc.file_byte_begin[sel.front()], span_e = tc.file_byte_begin[sel.back() + 1];
+    uint8_t* tr = (uint8_t*)ar.alloc(span_e - span_b + 256);
+    size_t k = 0;
+    while (k < sel.size()) {
+      size_t k2 = k;
+      while (k2 + 1 < sel.size() && sel[k2 + 1] == sel[k2] + 1) ++k2;
+      const int64_t b0 = tc.file_byte_begin[sel[k]], b1 = tc.file_byte_begin[sel[k2] + 1];
+      NDS_CUDA(cudaMemcpyAsync(tr + (b0 - span_b), tc.h_enc + b0, b1 - b0, cudaMemcpyHostToDevice, s));
+      h2d += b1 - b0;
+      k = k2 + 1;
+    }
+    return tr - span_b;
+  }
+
   Batch scan(const Json& node, std::vector<RuntimeFilter>& filters) {
     const std::string& tname = node.str("table");
     auto it = e.tables_.find(tname);
@@ -690,21 +741,10 @@ struct Exec {
       return out;
     }
     // ---- partition pruning (Spark: dynamic partition pruning on the broadcast side's keys)
-    const RuntimeFilter* rf = nullptr;
-    for (const RuntimeFilter& f : filters)
-      if (f.column == t.part_col && !t.part_col.empty()) rf = &f;
-    if (rf) resolve(*rf);
-    std::vector<int> sel;
-    std::vector<int64_t> row_start;
-    int64_t N = 0;
-    for (size_t f = 0; f < t.files.size(); ++f) {
-      const FileInfo& fi = t.files[f];
-      if (rf && (fi.part_null || !rf->contains(fi.part_val))) continue;
-      sel.push_back((int)f);
-      row_start.push_back(N);
-      N += fi.rows;
-    }
-    row_start.push_back(N);
+    FileSel fs = select_files(t, filters);
+    std::vector<int>& sel = fs.sel;
+    std::vector<int64_t>& row_start = fs.row_start;
+    const int64_t N = fs.N;
     if (N >= (int64_t(1) << 31)) fail("scan of '" + tname + "' selects 2^31 or more rows; shard the table across GPUs");
     out.n_max = N;
     size_t st = begin_stat("decode:" + tname, true);
@@ -781,6 +821,9 @@ struct Exec {
       TableColumn& tc = t.cols[ci->second];
       if (!tc.supported) fail("column '" + cname + "' of '" + tname + "' cannot be decoded: " + tc.why_unsupported);
       col.lt = tc.lt;
+      col.has_range = tc.has_stats;
+      col.range_lo = tc.stat_lo;
+      col.range_hi = tc.stat_hi;
       const int width = tc.lt.dtype() == DT_I32 ? 4 : 8;
       void* d_out = ar.alloc(N * width);
       uint32_t* d_valid = tc.nullable ? ar.zeros<uint32_t>((N + 31) / 32 + 1) : nullptr;
@@ -788,28 +831,7 @@ struct Exec {
       col.data = d_out;
       col.valid = d_valid;
       // ---- where do the encoded bytes come from
-      const uint8_t* src_base = nullptr;   // address of staged byte 0
-      if (!sel.empty()) {
-        if (source_host) {
-          if (!tc.h_enc) fail("engine was created without keep_host; source=host is unavailable");
-          int64_t span_b = tc.file_byte_begin[sel.front()], span_e = tc.file_byte_begin[sel.back() + 1];
-          uint8_t* tr = (uint8_t*)ar.alloc(span_e - span_b + 256);
-          // copy only the selected files' byte ranges, adjacent ranges coalesced
-          size_t k = 0;
-          while (k < sel.size()) {
-            size_t k2 = k;
-            while (k2 + 1 < sel.size() && sel[k2 + 1] == sel[k2] + 1) ++k2;
-            int64_t b0 = tc.file_byte_begin[sel[k]], b1 = tc.file_byte_begin[sel[k2] + 1];
-            NDS_CUDA(cudaMemcpyAsync(tr + (b0 - span_b), tc.h_enc + b0, b1 - b0, cudaMemcpyHostToDevice, s));
-            h2d += b1 - b0;
-            k = k2 + 1;
-          }
-          src_base = tr - span_b;
-        } else {
-          if (!tc.d_enc) fail("engine was created with resident=false; use source=host");
-          src_base = tc.d_enc;
-        }
-      }
+      const uint8_t* src_base = column_bytes(tc, sel);   // address of staged byte 0
       col.strbase = src_base;
       // the registration-time templates of each selected file, copied in one piece and patched (engine.h, task_tmpl)
       for (size_t k = 0; k < sel.size(); ++k) {
@@ -1091,12 +1113,25 @@ struct Exec {
     auto build_table = [&]() {
       size_t stb = begin_stat("join_build");
       HashTable& ht = bs.ht;
+      const Column& kc = build.cols[kb];
+      // surrogate keys are dense: when the column statistics bound the keys to a range not much larger than the table,
+      // the join table is a direct-address array over that range (ops.cuh) instead of an open-addressing hash table
+      const int64_t range = kc.has_range ? kc.range_hi - kc.range_lo + 1 : 0;
+      if (dense_tables && kc.has_range && range > 0 && range <= (int64_t(1) << 26) && range <= 16 * std::max<int64_t>(nb_bound, 1) + 65536) {
+        ht.dense = ar.zeros<uint32_t>(range);
+        ht.lo = kc.range_lo;
+        ht.range = (uint32_t)range;
+        launch_join_build(kc.ref(), build.rc(), ht, err + 1, s);
+        ++launches;
+        end_stat(stb, nb * 8 + range * 4, nb);
+        return;
+      }
       uint32_t cap = next_pow2(2 * nb);
       ht.mask = cap - 1;
       ht.keys = ar.alloc_n<int64_t>(cap);
       ht.vals = ar.alloc_n<uint32_t>(cap);
       launch_fill_i64(ht.keys, kEmptyKey, cap, s);
-      launch_join_build(build.cols[kb].ref(), build.rc(), ht, err + 1, s);
+      launch_join_build(kc.ref(), build.rc(), ht, err + 1, s);
       launches += 2;
       end_stat(stb, nb * 8 + (int64_t)cap * 12, nb);
     };
@@ -1166,6 +1201,296 @@ struct Exec {
     return bs;
   }
 
+
+  // ---------------------------------------------------------------- fused scan -> probe (fused_scan.cu)
+  struct FusedCol {                 // one column of the base table the fused scan touches
+    std::string name;
+    TableColumn* tc = nullptr;      // null: the partition column
+    bool is_key = false, is_payload = false;
+    int64_t task0 = 0;              // first task of this column in the combined task array
+    const int32_t* d_file_page0 = nullptr;
+  };
+  struct FusedPlan {
+    Table* t = nullptr;
+    FileSel fs;
+    std::vector<FusedCol> cols;                 // key columns first (probe order), then payload-only columns
+    std::vector<int> key_side;                  // per key column: index into `sides` / `chain`
+    int part_side = -1;                         // chain index of the join on the partition column, or -1
+    PageTask* d_tasks = nullptr;
+    int64_t pages_per_col = 0;                  // pages of one key column (all key columns have the same)
+    FusedChunk* d_chunks = nullptr;
+    int nchunks = 0;
+    int64_t* d_part_val = nullptr;
+    uint8_t* d_part_null = nullptr;
+    int64_t key_bytes_in = 0;
+  };
+
+  // Decides whether the probe side of a join chain can run as the fused scan and, if so, selects the files, builds and
+  // uploads the page tasks of every column involved and launches the def-level kernel.  Returns false (nothing launched)
+  // when the shape does not fit; the caller then decodes and probes the ordinary way.
+  bool fused_prepare(const Json& base_node, const std::vector<const Json*>& chain, std::vector<RuntimeFilter>& down, FusedPlan& fp) {
+    if (!fused_scan || !split_decode || base_node.str("op") != "scan") return false;
+    auto it = e.tables_.find(base_node.str("table"));
+    if (it == e.tables_.end()) return false;
+    Table& t = it->second;
+    if (t.is_mem) return false;
+    std::set<std::string> key_only;
+    if (const Json* ko = base_node.find("key_only"))
+      for (const Json& c : ko->a) key_only.insert(c.s);
+    // ---- columns: probe keys in probe order (innermost join first), then the payload
+    auto add_col = [&](const std::string& name) -> int {
+      for (size_t i = 0; i < fp.cols.size(); ++i)
+        if (fp.cols[i].name == name) return (int)i;
+      FusedCol fc;
+      fc.name = name;
+      if (name != t.part_col) {
+        auto ci = t.col_index.find(name);
+        if (ci == t.col_index.end()) return -1;
+        fc.tc = &t.cols[ci->second];
+        if (!fc.tc->supported || fc.tc->lt.kind == LType::STR) return -1;
+      }
+      fp.cols.push_back(fc);
+      return (int)fp.cols.size() - 1;
+    };
+    for (size_t q = 0; q < chain.size(); ++q) {
+      const size_t j = chain.size() - 1 - q;
+      const std::string& pk = chain[j]->str("probe_key");
+      if (pk == t.part_col && !t.part_col.empty()) {
+        if (fp.part_side >= 0) return false;
+        fp.part_side = (int)j;
+        continue;
+      }
+      const int ci = add_col(pk);
+      if (ci < 0 || fp.cols[ci].is_key) return false;        // unknown / string key, or the same key probed twice
+      fp.cols[ci].is_key = true;
+      fp.key_side.push_back((int)j);
+    }
+    const int nkeys = (int)fp.key_side.size();
+    if (nkeys < 1) return false;
+    for (const Json& c : base_node.at("columns").a) {
+      if (key_only.count(c.s)) continue;
+      const int ci = add_col(c.s);
+      if (ci < 0) return false;
+      fp.cols[ci].is_payload = true;
+    }
+    // ---- files
+    fp.t = &t;
+    fp.fs = select_files(t, down);
+    const std::vector<int>& sel = fp.fs.sel;
+    if (sel.empty() || fp.fs.N <= 0 || fp.fs.N >= (int64_t(1) << 31)) return false;
+    for (const FusedCol& fc : fp.cols) {
+      if (!fc.tc) continue;
+      for (int f : sel)
+        if (!fc.tc->file_direct[f]) return false;             // a page that needs a run-header walk
+    }
+    // the key columns must be cut into pages at the same rows
+    const TableColumn& k0 = *fp.cols[0].tc;
+    for (int c = 1; c < nkeys; ++c) {
+      const TableColumn& kc = *fp.cols[c].tc;
+      for (int f : sel) {
+        const int64_t a0 = k0.file_page_begin[f], a1 = k0.file_page_begin[f + 1], b0 = kc.file_page_begin[f];
+        if (kc.file_page_begin[f + 1] - b0 != a1 - a0) return false;
+        for (int64_t p = 0; p < a1 - a0; ++p)
+          if (k0.pages[a0 + p].num_values != kc.pages[b0 + p].num_values) return false;
+      }
+    }
+    mark("fused:checked");
+    // ---- page tasks of every column, file by file (the same templates the ordinary scan patches)
+    size_t npages = 0;
+    for (const FusedCol& fc : fp.cols)
+      if (fc.tc)
+        for (int f : sel) npages += (size_t)(fc.tc->file_page_begin[f + 1] - fc.tc->file_page_begin[f]);
+    std::vector<PageTask> tasks_fallback;
+    PageTask* tasks = reinterpret_cast<PageTask*>(ar.pin_take((int64_t)(npages * sizeof(PageTask)) + 16));
+    const bool tasks_pinned = tasks != nullptr;
+    if (!tasks) { tasks_fallback.resize(npages + 1); tasks = tasks_fallback.data(); }
+    std::vector<int> def_idx;
+    std::vector<int64_t> vr_off(npages, -1);
+    std::vector<int32_t> file_page0;            // per column with pages: sel.size() + 1 entries
+    std::vector<size_t> fp0_off(fp.cols.size(), 0);
+    int64_t vr_words = 0;
+    size_t ntasks = 0;
+    int max_def_len = 0;
+    size_t sdef = begin_stat("def_levels", true);
+    int64_t def_bytes = 0;
+    for (size_t c = 0; c < fp.cols.size(); ++c) {
+      FusedCol& fc = fp.cols[c];
+      if (!fc.tc) continue;
+      TableColumn& tc = *fc.tc;
+      const uint8_t* src_base = column_bytes(tc, sel);
+      fc.task0 = (int64_t)ntasks;
+      fp0_off[c] = file_page0.size();
+      for (size_t k = 0; k < sel.size(); ++k) {
+        const int f = sel[k];
+        const int64_t p0 = tc.file_page_begin[f], p1 = tc.file_page_begin[f + 1];
+        file_page0.push_back((int32_t)(ntasks - (size_t)fc.task0));
+        const size_t base = ntasks;
+        if (p1 > p0) memcpy(tasks + ntasks, tc.task_tmpl.data() + p0, (size_t)(p1 - p0) * sizeof(PageTask));
+        ntasks += (size_t)(p1 - p0);
+        if (fc.is_key) fp.key_bytes_in += tc.file_bytes_in[f];
+        for (size_t q = base; q < ntasks; ++q) {
+          PageTask& task = tasks[q];
+          task.vr = nullptr;
+          task.src = src_base + reinterpret_cast<uintptr_t>(task.src);
+          if (task.dict) task.dict = src_base + (reinterpret_cast<uintptr_t>(task.dict) - 1);
+          task.out = nullptr;
+          task.valid = nullptr;              // no column-wide bitmap: only the page-local validity / rank words are wanted
+          task.out_row += fp.fs.row_start[k];
+          if (tc.nullable) {
+            def_idx.push_back((int)q);
+            vr_off[q] = vr_words;
+            vr_words += 2 * (((int64_t)task.num_values + 31) / 32) + 1;
+            max_def_len = std::max<int>(max_def_len, (int)task.def_len);
+            def_bytes += task.def_len;
+            if (fc.is_key) fp.key_bytes_in -= task.def_len;      // the def kernel reads those, not the probe kernel
+          }
+        }
+      }
+      file_page0.push_back((int32_t)(ntasks - (size_t)fc.task0));
+    }
+    fp.pages_per_col = (int64_t)file_page0[fp0_off[0] + sel.size()];
+    uint32_t* d_vr = vr_words ? ar.alloc_n<uint32_t>(vr_words) : nullptr;
+    for (size_t q = 0; q < ntasks; ++q) tasks[q].vr = vr_off[q] >= 0 ? d_vr + vr_off[q] : nullptr;
+    fp.d_tasks = ar.alloc_n<PageTask>((int64_t)ntasks);
+    if (tasks_pinned) NDS_CUDA(cudaMemcpyAsync(fp.d_tasks, tasks, ntasks * sizeof(PageTask), cudaMemcpyHostToDevice, s));
+    else ar.upload(fp.d_tasks, tasks, (int64_t)(ntasks * sizeof(PageTask)));
+    // ---- chunks of the key pages, per-file partition values, per-column page directories: one upload
+    std::vector<FusedChunk> chunks;
+    {
+      const TableColumn& kc = *fp.cols[0].tc;
+      uint32_t page = 0;
+      for (size_t k = 0; k < sel.size(); ++k)
+        for (int64_t p = kc.file_page_begin[sel[k]]; p < kc.file_page_begin[sel[k] + 1]; ++p, ++page)
+          for (uint32_t r0 = 0; r0 < kc.pages[p].num_values; r0 += kFusedChunk) chunks.push_back(FusedChunk{page, r0, (uint32_t)k, 0});
+    }
+    fp.nchunks = (int)chunks.size();
+    std::vector<int64_t> pv(sel.size());
+    std::vector<uint8_t> pn(sel.size());
+    for (size_t k = 0; k < sel.size(); ++k) { pv[k] = t.files[sel[k]].part_null ? 0 : t.files[sel[k]].part_val; pn[k] = t.files[sel[k]].part_null ? 1 : 0; }
+    const int64_t off_chunks = 0;
+    const int64_t off_pv = align_up(off_chunks + (int64_t)(chunks.size() * sizeof(FusedChunk)), 16);
+    const int64_t off_pn = align_up(off_pv + (int64_t)pv.size() * 8, 16);
+    const int64_t off_fp0 = align_up(off_pn + (int64_t)pn.size(), 16);
+    const int64_t off_def = align_up(off_fp0 + (int64_t)file_page0.size() * 4, 16);
+    const int64_t total = off_def + (int64_t)def_idx.size() * 4 + 16;
+    std::vector<uint8_t> h((size_t)total, 0);
+    if (!chunks.empty()) memcpy(h.data() + off_chunks, chunks.data(), chunks.size() * sizeof(FusedChunk));
+    memcpy(h.data() + off_pv, pv.data(), pv.size() * 8);
+    memcpy(h.data() + off_pn, pn.data(), pn.size());
+    if (!file_page0.empty()) memcpy(h.data() + off_fp0, file_page0.data(), file_page0.size() * 4);
+    if (!def_idx.empty()) memcpy(h.data() + off_def, def_idx.data(), def_idx.size() * 4);
+    uint8_t* d = (uint8_t*)ar.alloc(total);
+    ar.upload(d, h.data(), total);
+    fp.d_chunks = reinterpret_cast<FusedChunk*>(d + off_chunks);
+    fp.d_part_val = reinterpret_cast<int64_t*>(d + off_pv);
+    fp.d_part_null = d + off_pn;
+    for (size_t c = 0; c < fp.cols.size(); ++c)
+      if (fp.cols[c].tc) fp.cols[c].d_file_page0 = reinterpret_cast<const int32_t*>(d + off_fp0) + fp0_off[c];
+    mark("fused:uploaded");
+    // ---- def levels of every nullable column involved -> page-local validity + rank words
+    int l = 0;
+    launch_decode_split(fp.d_tasks, reinterpret_cast<const int*>(d + off_def), (int)def_idx.size(), max_def_len, nullptr, 0, err, s, &l);
+    launches += l;
+    end_stat(sdef, def_bytes + vr_words * 4, fp.fs.N);
+    return true;
+  }
+
+  // The probe kernel over the prepared scan (after every build side is done), then the payload of the survivors.
+  Batch fused_probe(FusedPlan& fp, const std::vector<const Json*>& chain, std::vector<BuiltSide>& sides) {
+    const int64_t N = fp.fs.N;
+    const int nkeys = (int)fp.key_side.size();
+    // survivors: a star join keeps a small part of the fact rows; room for an eighth of them (at least 1 M), and if that
+    // ever overflows the kernel raises err[2] and the query is run again with room for all
+    const int64_t cap = speculate ? std::min<int64_t>(N, std::max<int64_t>(N / 8, int64_t(1) << 20)) : N;
+    size_t stp = begin_stat("scan_probe", true);
+    FusedScanArgs a;
+    memset(&a, 0, sizeof a);
+    a.nkeys = nkeys;
+    for (int c = 0; c < nkeys; ++c) {
+      BuiltSide& bs = sides[(size_t)fp.key_side[c]];
+      if (!is_intlike(fp.cols[c].tc->lt)) fail("plan: join keys must be integer columns");
+      a.key[c].tasks = fp.d_tasks + fp.cols[c].task0;
+      a.key[c].ht = bs.ht;
+      a.key[c].out_build = ar.alloc_n<uint32_t>(cap);
+    }
+    if (fp.part_side >= 0) {
+      a.has_part = 1;
+      a.part_ht = sides[(size_t)fp.part_side].ht;
+      a.part_out_build = ar.alloc_n<uint32_t>(cap);
+      a.file_part_val = fp.d_part_val;
+    }
+    a.chunks = fp.d_chunks;
+    a.out_row = ar.alloc_n<uint32_t>(cap);
+    a.out_file = ar.alloc_n<uint32_t>(cap);
+    a.out_count = ar.zeros<int>(1);
+    a.cap = (uint32_t)cap;
+    a.err = err;
+    launch_scan_probe(a, fp.nchunks, s);
+    ++launches;
+    RowCount nout{a.out_count, cap};
+    end_stat_rows(stp, 4 * ((int64_t)chain.size() + 2), nout, fp.key_bytes_in);
+    Batch out;
+    out.n_max = cap;
+    out.n_dev = a.out_count;
+    // ---- payload columns of the survivors
+    std::vector<GatherCol> gcs;
+    int64_t gather_row_bytes = 0;
+    for (const FusedCol& fc : fp.cols) {
+      if (!fc.is_payload) continue;
+      Column col;
+      col.name = fc.name;
+      GatherCol g;
+      memset(&g, 0, sizeof g);
+      if (fc.tc) {
+        col.lt = fc.tc->lt;
+        col.has_range = fc.tc->has_stats;
+        col.range_lo = fc.tc->stat_lo;
+        col.range_hi = fc.tc->stat_hi;
+        g.tasks = fp.d_tasks + fc.task0;
+        g.file_page0 = fc.d_file_page0;
+      } else {
+        col.lt.kind = LType::INT;
+        col.lt.is32 = true;
+        g.is_part = 1;
+      }
+      g.width = col.lt.dtype() == DT_I32 ? 4 : 8;
+      void* d = ar.alloc(cap * g.width);
+      uint32_t* v = ar.alloc_n<uint32_t>((cap + 31) / 32 + 1);
+      g.out = d;
+      g.out_valid = v;
+      col.data = d;
+      col.valid = v;
+      out.cols.push_back(col);
+      gcs.push_back(g);
+      gather_row_bytes += 3 * g.width + 8 + 4;       // index word + dictionary entry + value written, rank words, row id
+    }
+    if (!gcs.empty()) {
+      size_t stg = begin_stat("gather_decode", true);
+      GatherCol* d_gcs = ar.alloc_n<GatherCol>((int64_t)gcs.size());
+      ar.upload(d_gcs, gcs.data(), (int64_t)(gcs.size() * sizeof(GatherCol)));
+      launch_gather_decode(d_gcs, (int)gcs.size(), a.out_row, a.out_file, a.out_count, cap, fp.d_part_val, fp.d_part_null, err, s);
+      ++launches;
+      end_stat_rows(stg, gather_row_bytes, nout);
+    }
+    // ---- build-side columns in the order the unfused plan produces them (innermost join first)
+    for (size_t q = 0; q < chain.size(); ++q) {
+      const size_t j = chain.size() - 1 - q;
+      const BuiltSide& bs = sides[j];
+      const uint32_t* map = nullptr;
+      if ((int)j == fp.part_side) map = a.part_out_build;
+      for (int c = 0; c < nkeys; ++c)
+        if (fp.key_side[c] == (int)j) map = a.key[c].out_build;
+      MapCache mb;
+      for (const Column& c : bs.build.cols) {
+        if (out.find(c.name) >= 0) continue;
+        Column o = c;
+        o.rowmap = remap(c.rowmap, map, nout, mb);
+        out.cols.push_back(o);
+      }
+    }
+    return out;
+  }
+
   // scans, filters, projections and joins between them: such a subtree reads nothing another operator of the query
   // produces (a join inside it stays on the stream the subtree was given)
   static bool independent_subtree(const Json& node) {
@@ -1210,7 +1535,8 @@ struct Exec {
       cur = &cur->at("probe");
     }
     const Json& base_node = *cur;
-    bool fuse = chain.size() >= 2 && base_node.str("op") != "join";
+    // (a single join over a Parquet scan also takes this route: the fused scan needs no decoded key column)
+    bool fuse = (chain.size() >= 2 || (base_node.str("op") == "scan" && fused_scan && split_decode)) && base_node.str("op") != "join";
     if (fuse) {
       std::set<std::string> base_cols;
       plan_columns(base_node, base_cols);
@@ -1275,10 +1601,14 @@ struct Exec {
     });
     Batch base;
     bool base_done = false;
+    FusedPlan fplan;
+    bool fused_ready = false;
     auto issue_base = [&]() {
       const bool side = side_stream && independent_subtree(base_node);
       if (side) enter_side(lane_no++);
-      base = exec(base_node, down);
+      // a Parquet fact scan under the chain: decode the probe keys inside the probe kernel instead of materialising columns
+      fused_ready = fused_prepare(base_node, chain, down, fplan);
+      if (!fused_ready) base = exec(base_node, down);
       if (side) leave_side();
       base_done = true;
     };
@@ -1298,6 +1628,7 @@ struct Exec {
       if (side) leave_side();
     }
     if (!base_done) issue_base();
+    if (fused_ready) return fused_probe(fplan, chain, sides);
     size_t stp = begin_stat("join_probe_chain");
     RowCount np = base.rc();
     ProbeChain pc;

@@ -1,0 +1,259 @@
+// Fused fact-table scan: page decode -> join-chain probe in one kernel, and late materialisation of the surviving rows.
+//
+// A star-join query reads a few columns of a fact table, probes the join tables of its dimensions with the key columns
+// and keeps a small fraction of the rows (NDS query7: ~1 %).  Decoding every column of every row into HBM first
+// (decode_fast.cu) and probing the decoded keys afterwards (ops.cu, join_probe_chain_kernel) writes and re-reads the
+// decoded columns and decodes measures of rows no join keeps.  Here instead:
+//
+//   scan_probe_kernel    one CTA per 4096-row chunk of a page.  Pass A: every thread decodes four consecutive values of
+//                        the FIRST probe key straight from the page (validity / rank words of the def kernel -> value
+//                        index -> bit-packed dictionary index -> dictionary -> key), probes that join's table and queues
+//                        the hits in shared memory.  Pass B: one thread per queued row decodes the remaining probe keys
+//                        of that row only and walks the rest of the chain; survivors are appended to the output with the
+//                        matched build row of every join.  No decoded key column ever exists in memory.
+//   gather_decode_kernel one thread per survivor and payload column: the value of that row only (page lookup by row,
+//                        rank from the def kernel's words, index, dictionary) into a flat column + validity bitmap.
+//
+// Both rely on pages whose value k can be addressed without walking run headers (engine.h, PageInfo::direct): PLAIN
+// fixed-width pages, one-entry dictionaries, and index streams of back-to-back 504-value bit-packed runs, where value
+// k sits at bit k * bw + 8 * (k / 504 + 1) of the stream.  Exec::join falls back to decode + probe for anything else.
+//
+// Spark operators these replace: FileSourceScanExec + BroadcastHashJoinExec chains under whole-stage codegen; the
+// reference hands SQL text to Spark at /root/reference/nds/nds_power.py:130.
+#include "decode_common.cuh"
+#include "ops.cuh"
+
+namespace nds {
+
+namespace {
+
+struct PageView {                 // what decoding one value of a page needs, hoisted out of the row loop
+  const uint32_t* words;          // 4 B aligned base of the index stream (dictionary pages)
+  const uint8_t* plain;           // PLAIN values (16 B aligned)
+  const void* dict;
+  const uint32_t* vr_valid;       // validity words of the page (def kernel scratch), nullptr = no nulls
+  const uint32_t* vr_rank;        // rank prefix per word; vr_rank[nw] = non-null values in the page
+  int64_t out_row;                // global row of the page's first row
+  uint32_t n;                     // rows in the page
+  uint32_t dict_count;
+  uint32_t bw, bwmask;
+  uint32_t off8;                  // bit offset of value 0 from `words`: stream misalignment + the first header byte
+  uint32_t kmax;                  // last valid value index (non-null count - 1; 0 when the page holds no value)
+  uint32_t is_dict, width;
+};
+
+__device__ __forceinline__ PageView make_view(const PageTask& t) {
+  PageView v;
+  const uint32_t values_off = t.def_len ? 4u + t.def_len : 0u;
+  const uint32_t nw = (t.num_values + 31u) >> 5;
+  v.n = t.num_values;
+  v.out_row = t.out_row;
+  v.is_dict = t.enc == 1;
+  v.width = t.width;
+  v.dict = t.dict;
+  v.dict_count = t.dict_count;
+  v.bw = t.bw;
+  v.bwmask = t.bw >= 32 ? 0xFFFFFFFFu : ((1u << t.bw) - 1u);
+  v.plain = t.src + values_off;
+  const uint8_t* vstream = t.src + values_off + 1;
+  v.words = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(vstream) & ~uintptr_t(3));
+  v.off8 = (uint32_t)(reinterpret_cast<uintptr_t>(vstream) & 3) * 8u + 8u;
+  v.vr_valid = t.vr;
+  v.vr_rank = t.vr ? t.vr + nw : nullptr;
+  const uint32_t nn = t.vr ? t.vr[2 * nw] : t.num_values;
+  v.kmax = nn ? nn - 1u : 0u;
+  return v;
+}
+
+// value index k (k-th non-null value of the page) -> value; false + error 6 when a dictionary index is out of range
+__device__ __forceinline__ bool page_value(const PageView& v, uint32_t k, int64_t& out, int* err) {
+  if (!v.is_dict) {
+    out = v.width == 4 ? (int64_t)__ldg(reinterpret_cast<const int32_t*>(v.plain) + k)
+                       : (int64_t)__ldg(reinterpret_cast<const long long*>(v.plain) + k);
+    return true;
+  }
+  uint32_t ix = 0;
+  if (v.bw) {
+    const uint32_t bit = k * v.bw + (k / 504u) * 8u + v.off8;
+    const uint32_t* wp = v.words + (bit >> 5);
+    ix = __funnelshift_r(__ldg(wp), __ldg(wp + 1), bit & 31) & v.bwmask;
+  }
+  if (ix >= v.dict_count) { if (err) atomicExch(err, 6); return false; }
+  out = v.width == 4 ? (int64_t)__ldg(reinterpret_cast<const int32_t*>(v.dict) + ix)
+                     : (int64_t)__ldg(reinterpret_cast<const long long*>(v.dict) + ix);
+  return true;
+}
+
+// row r of the page -> (is it non-null, its value index)
+__device__ __forceinline__ bool row_rank(const PageView& v, uint32_t r, uint32_t& k) {
+  if (!v.vr_valid) { k = r; return true; }
+  const uint32_t w = __ldg(v.vr_valid + (r >> 5));
+  k = __ldg(v.vr_rank + (r >> 5)) + __popc(w & ((1u << (r & 31)) - 1u));
+  return (w >> (r & 31)) & 1u;
+}
+
+}  // namespace
+
+__global__ void __launch_bounds__(kFusedThreads)
+scan_probe_kernel(const FusedScanArgs a) {
+  __shared__ PageView s_view[kMaxChain];
+  __shared__ uint16_t q_row[kFusedChunk];          // pass A hits: row inside the chunk
+  __shared__ uint32_t q_b0[kFusedChunk];           //              matched build row of the first join
+  __shared__ int s_nq;
+  __shared__ int s_part_ok;
+  __shared__ uint32_t s_part_row;
+
+  const FusedChunk ch = a.chunks[blockIdx.x];
+  const int tid = threadIdx.x;
+  if (tid < a.nkeys) s_view[tid] = make_view(a.key[tid].tasks[ch.page]);
+  if (tid == 32) {
+    s_nq = 0;
+    s_part_ok = 1;
+    s_part_row = 0;
+    if (a.has_part) {
+      // the join on the partition column: one lookup per file (the value is the directory name's)
+      uint32_t r = 0;
+      s_part_ok = ht_find(a.part_ht, a.file_part_val[ch.file], r) ? 1 : 0;
+      s_part_row = r;
+    }
+  }
+  __syncthreads();
+  if (!s_part_ok) return;
+
+  // ---- pass A: the first probe key of every row of the chunk, four consecutive rows per thread
+  {
+    const PageView v = s_view[0];
+    const HashTable ht = a.key[0].ht;
+    const uint32_t rend = min(ch.row0 + (uint32_t)kFusedChunk, v.n);
+    for (uint32_t base = ch.row0 + (uint32_t)tid * 4u; base < rend; base += kFusedThreads * 4u) {
+      uint32_t vbits = 0xFu, k0 = base;
+      if (v.vr_valid) {
+        const uint32_t w = __ldg(v.vr_valid + (base >> 5));
+        const uint32_t sh = base & 31u;       // multiple of 4: the four rows share one validity word
+        k0 = __ldg(v.vr_rank + (base >> 5)) + __popc(w & ((1u << sh) - 1u));
+        vbits = (w >> sh) & 0xFu;
+      }
+      if (base + 4u > rend) vbits &= (1u << (rend - base)) - 1u;
+      if (!vbits) continue;
+      // straight-line: every slot fetches a value (null slots the neighbouring one's, clamped to the page's last), the
+      // validity bits decide afterwards - four independent load chains in flight per thread
+      int64_t key[4];
+      bool okv[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t k = min(k0 + __popc(vbits & ((1u << u) - 1u)), v.kmax);
+        okv[u] = page_value(v, k, key[u], a.err) && ((vbits >> u) & 1u);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        uint32_t b = 0;
+        if (okv[u] && ht_find(ht, key[u], b)) {
+          const int pos = atomicAdd(&s_nq, 1);
+          q_row[pos] = (uint16_t)(base + u - ch.row0);
+          q_b0[pos] = b;
+        }
+      }
+    }
+  }
+  __syncthreads();
+
+  // ---- pass B: the remaining joins for the queued rows only; survivors go to the output
+  const int nq = s_nq;
+  const int nq_round = (nq + 31) & ~31;
+  const uint32_t row_base = (uint32_t)s_view[0].out_row;
+  for (int i = tid; i < nq_round; i += kFusedThreads) {
+    bool alive = i < nq;
+    uint32_t r = 0;
+    uint32_t b[kMaxChain];
+#pragma unroll
+    for (int j = 0; j < kMaxChain; ++j) b[j] = 0;
+    if (alive) { r = ch.row0 + q_row[i]; b[0] = q_b0[i]; }
+#pragma unroll
+    for (int j = 1; j < kMaxChain; ++j) {
+      if (j < a.nkeys && alive) {
+        uint32_t k;
+        int64_t key;
+        alive = row_rank(s_view[j], r, k) && page_value(s_view[j], k, key, a.err) && ht_find(a.key[j].ht, key, b[j]);
+      }
+    }
+    const uint32_t m = __ballot_sync(0xFFFFFFFFu, alive);
+    if (!m) continue;
+    const int lane = tid & 31, leader = __ffs(m) - 1;
+    int pos0 = 0;
+    if (lane == leader) pos0 = atomicAdd(a.out_count, __popc(m));
+    pos0 = __shfl_sync(0xFFFFFFFFu, pos0, leader);
+    if (alive) {
+      const uint32_t pos = (uint32_t)pos0 + __popc(m & ((1u << lane) - 1u));
+      if (pos < a.cap) {
+        a.out_row[pos] = row_base + r;
+        a.out_file[pos] = ch.file;
+#pragma unroll
+        for (int j = 0; j < kMaxChain; ++j)
+          if (j < a.nkeys) a.key[j].out_build[pos] = b[j];
+        if (a.has_part) a.part_out_build[pos] = s_part_row;
+      } else {
+        atomicExch(a.err + 2, 1);      // more survivors than the speculative capacity: the query is run again with room for all
+      }
+    }
+  }
+}
+
+void launch_scan_probe(const FusedScanArgs& args, int nchunks, cudaStream_t s) {
+  if (nchunks <= 0) return;
+  scan_probe_kernel<<<nchunks, kFusedThreads, 0, s>>>(args);
+  NDS_CUDA(cudaGetLastError());
+}
+
+// One survivor per thread, every payload column in turn (a handful of columns, a few percent of the rows).
+__global__ void __launch_bounds__(256)
+gather_decode_kernel(const GatherCol* __restrict__ cols, int ncols, const uint32_t* __restrict__ rows, const uint32_t* __restrict__ files,
+                     const int* n_dev, int64_t cap, const int64_t* __restrict__ file_part_val, const uint8_t* __restrict__ file_part_null,
+                     int* err) {
+  int64_t n = *n_dev;
+  if (n > cap) n = cap;
+  const int64_t nround = (n + 31) & ~int64_t(31);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nround; i += (int64_t)gridDim.x * blockDim.x) {
+    const bool live = i < n;
+    const uint32_t g = live ? rows[i] : 0u;
+    const uint32_t f = live ? files[i] : 0u;
+    for (int c = 0; c < ncols; ++c) {
+      const GatherCol gc = cols[c];
+      bool ok = false;
+      int64_t val = 0;
+      if (live) {
+        if (gc.is_part) {
+          ok = !file_part_null[f];
+          val = file_part_val[f];
+        } else {
+          // the page of this column that holds global row g: the file's pages are in row order
+          int lo = gc.file_page0[f], hi = gc.file_page0[f + 1] - 1;
+          while (lo < hi) {
+            const int mid = (lo + hi + 1) >> 1;
+            if (gc.tasks[mid].out_row <= (int64_t)g) lo = mid; else hi = mid - 1;
+          }
+          const PageView v = make_view(gc.tasks[lo]);
+          const uint32_t r = (uint32_t)((int64_t)g - v.out_row);
+          uint32_t k;
+          if (r < v.n && row_rank(v, r, k)) ok = page_value(v, k, val, err);
+        }
+      }
+      const uint32_t m = __ballot_sync(0xFFFFFFFFu, ok);
+      if ((threadIdx.x & 31) == 0) gc.out_valid[i >> 5] = m;
+      if (live) {
+        if (gc.width == 4) reinterpret_cast<int32_t*>(gc.out)[i] = ok ? (int32_t)val : 0;
+        else reinterpret_cast<int64_t*>(gc.out)[i] = ok ? val : 0;
+      }
+    }
+  }
+}
+
+void launch_gather_decode(const GatherCol* d_cols, int ncols, const uint32_t* rows, const uint32_t* files, const int* n_dev, int64_t cap,
+                          const int64_t* file_part_val, const uint8_t* file_part_null, int* err, cudaStream_t s) {
+  if (ncols <= 0 || cap <= 0) return;
+  int64_t g = (cap + 255) / 256;
+  if (g > 148 * 8) g = 148 * 8;
+  gather_decode_kernel<<<(int)g, 256, 0, s>>>(d_cols, ncols, rows, files, n_dev, cap, file_part_val, file_part_null, err);
+  NDS_CUDA(cudaGetLastError());
+}
+
+}  // namespace nds

@@ -116,6 +116,47 @@ struct ProbeChain {            // a left-deep chain of inner hash joins probed i
   int32_t pad;
 };
 void launch_join_probe_chain(const ProbeChain& chain, RowCount n, uint32_t* out_probe, int* out_count, cudaStream_t s);
+
+// fused_scan.cu: page decode -> join-chain probe in one kernel over directly addressable pages, then the payload
+// columns of the surviving rows only (late materialisation).
+constexpr int kFusedThreads = 256;
+constexpr int kFusedChunk = 4096;          // rows of one page a CTA of scan_probe_kernel handles
+struct FusedChunk {
+  uint32_t page;                           // index into every key column's task array (the key columns are aligned page for page)
+  uint32_t row0;                           // first row of the chunk inside the page (multiple of kFusedChunk)
+  uint32_t file;                           // index of the page's file among the scan's selected files
+  uint32_t pad;
+};
+struct FusedKey {
+  const PageTask* tasks;                   // src / dict / vr patched, out_row = global first row of the page
+  HashTable ht;
+  uint32_t* out_build;                     // matched build row per survivor
+};
+struct FusedScanArgs {
+  FusedKey key[kMaxChain];                 // probe order: most selective join first
+  int32_t nkeys;
+  int32_t has_part;                        // the chain also joins on the partition column: one lookup per file
+  HashTable part_ht;
+  uint32_t* part_out_build;
+  const int64_t* file_part_val;            // per selected file
+  const FusedChunk* chunks;
+  uint32_t* out_row;                       // global row of each survivor
+  uint32_t* out_file;                      // selected-file index of each survivor
+  int* out_count;
+  uint32_t cap;                            // capacity of the output arrays; overflow raises err[2]
+  int* err;
+};
+void launch_scan_probe(const FusedScanArgs& args, int nchunks, cudaStream_t s);
+struct GatherCol {
+  const PageTask* tasks;                   // this column's tasks for the selected files, scan order (null: the partition column)
+  const int32_t* file_page0;               // per selected file: first task; [nsel] = task count
+  void* out;
+  uint32_t* out_valid;
+  int32_t width;                           // 4 or 8 bytes per output value
+  int32_t is_part;
+};
+void launch_gather_decode(const GatherCol* d_cols, int ncols, const uint32_t* rows, const uint32_t* files, const int* n_dev, int64_t cap,
+                          const int64_t* file_part_val, const uint8_t* file_part_null, int* err, cudaStream_t s);
 // Hash group-by.  slots / acc / cnt are allocated for cap_max = agg_capacity_for(upper bound of the input rows); the
 // kernels size the table from the row count on the device (<= cap_max), so no host round trip is needed.
 // acc / cnt: naggs * cap_max int64 each; out_valid: naggs * valid_stride_words words (cleared by launch_agg_init).

@@ -385,6 +385,22 @@ class Planner:
         for ta, ca, tb, cb in remaining:       # extra equalities between already-joined tables
             post.append(('bin', 'eq', ('col', None, ca), ('col', None, cb)))
 
+        # columns a table's scan must hand on as data: everything used outside the equi-join conditions that became joins.
+        # A probe key used for nothing else is 'key_only': the fused scan probes with it and never materialises it.
+        payload = set()
+        for e, _ in q['select']:
+            self.columns_of(e, payload)
+        for e in q['group']:
+            self.columns_of(e, payload)
+        for e, _, _ in q['order']:
+            if not (e[0] == 'col' and e[1] is None and e[2] in select_aliases):
+                self.columns_of(e, payload)
+        for flt in table_filters.values():
+            for c in flt:
+                self.columns_of(c, payload)
+        for c in post:
+            self.columns_of(c, payload)
+
         def selectivity(t):
             s = 1.0
             for c in table_filters.get(t, []):
@@ -396,6 +412,9 @@ class Planner:
         def subtree(t):
             cols = sorted(need[t], key=lambda c: [n for n, _, _ in nds_schema.SOURCE_TABLES[t]].index(c))
             node = {'op': 'scan', 'table': t, 'columns': cols}
+            key_only = [c for c in cols if c not in payload and any(pk == c for pk, _, _ in children[t])]
+            if key_only:
+                node['key_only'] = key_only
             flt = table_filters.get(t, [])
             if flt:
                 irs = [self.expr(c)[0] for c in flt]

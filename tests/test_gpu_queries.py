@@ -518,3 +518,42 @@ def test_host_source_equals_resident_source_on_other_shapes(gpu_engine):
         a = _Sess(gpu_engine, 'hbm').sql(sql).toArrow()
         b = _Sess(gpu_engine, 'host').sql(sql).toArrow()
         assert a.num_rows > 0 and a.equals(b), sql
+
+
+@pytest.mark.parametrize('query', streams.SUBSET)
+@pytest.mark.parametrize('opts', [{'fused_scan': False}, {'dense_tables': False}, {'fused_scan': False, 'dense_tables': False},
+                                  {'speculate': False}])
+def test_routes_agree_with_the_oracle(gpu_engine, warehouse, query, opts):
+    """The fact scan has two routes - fused page decode -> probe with late materialisation (fused_scan.cu), and decode
+    every column then probe (decode_fast.cu + ops.cu) - and a join table two layouts (direct-address over the key
+    range the column statistics give, open addressing).  Every combination must give the oracle's rows."""
+    from spark_rapids_benchmarks_b200 import planner
+    import pyarrow as pa
+    sql = streams.render(query, overrides=PARAMS[0])
+    plan = planner.plan_sql(sql)
+    exp = oq.run_query(query, sql, warehouse)
+    for source in (None, 'host'):
+        got = pa.Table.from_batches([gpu_engine.execute({'root': plan['root']}, source=source, options=opts)])
+        assert rows_equal(got.to_pylist(), exp.to_pylist()), (query, opts, source)
+        ops = [o['op'] for o in gpu_engine.last_stats()['ops']]
+        assert ('scan_probe' in ops) == opts.get('fused_scan', True), ops
+
+
+def test_fused_scan_keeps_key_columns_the_query_reads(gpu_engine, warehouse):
+    """A probe key that is also grouped on / selected is a payload column too: the fused scan must hand it on."""
+    import pyarrow as pa
+    import pyarrow.compute as pc
+    sql = ('select ss_item_sk, ss_sold_date_sk, count(*) cnt, sum(ss_quantity) q from store_sales, item, date_dim '
+           'where ss_item_sk = i_item_sk and ss_sold_date_sk = d_date_sk and i_manager_id = 63 and d_moy = 1 '
+           'group by ss_item_sk, ss_sold_date_sk order by ss_item_sk, ss_sold_date_sk limit 100')
+    got = _Sess(gpu_engine).sql(sql).toArrow()
+    assert any(o['op'] == 'scan_probe' for o in gpu_engine.last_stats()['ops'])
+    it = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_manager_id'])
+    it = it.filter(pc.equal(it['i_manager_id'], 63).fill_null(False))
+    dd = oq.read_dim(warehouse, 'date_dim', ['d_date_sk', 'd_moy'])
+    dd = dd.filter(pc.equal(dd['d_moy'], 1).fill_null(False))
+    ss = oq.read_fact(warehouse, 'store_sales', 'ss_sold_date_sk', ['ss_sold_date_sk', 'ss_item_sk', 'ss_quantity'], dd['d_date_sk'].to_pylist())
+    j = ss.join(it, keys='ss_item_sk', right_keys='i_item_sk', join_type='inner').join(dd, keys='ss_sold_date_sk', right_keys='d_date_sk', join_type='inner')
+    g = j.group_by(['ss_item_sk', 'ss_sold_date_sk']).aggregate([([], 'count_all'), ('ss_quantity', 'sum')])
+    exp = sorted(((r['ss_item_sk'], r['ss_sold_date_sk'], r['count_all'], r['ss_quantity_sum']) for r in g.to_pylist()))[:100]
+    assert [(r['ss_item_sk'], r['ss_sold_date_sk'], r['cnt'], r['q']) for r in got.to_pylist()] == exp
