@@ -61,7 +61,7 @@ def test_six_query_stream_at_sf1_matches_oracle(sf1, pi):
     info = eng.table_info('store_sales')
     assert info['rows'] == 2880404 and info['files'] == SALES_DAYS + 1
     pages = [c['pages'] for c in info['columns'] if c['name'] == 'ss_item_sk'][0]
-    assert pages == info['files']                         # one ~15.8 k-row page per column chunk
+    assert info['files'] <= pages <= info['files'] + 8    # one ~15.8 k-row page per date file, a few 20 k-row pages in the NULL partition
     for query in streams.SUBSET:
         sql = streams.render(query, overrides=PARAMS[pi])
         exp = oq.run_query(query, sql, wh)
