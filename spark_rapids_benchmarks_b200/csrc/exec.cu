@@ -1234,6 +1234,11 @@ struct Exec {
     if (it == e.tables_.end()) return false;
     Table& t = it->second;
     if (t.is_mem) return false;
+    // why a Parquet scan under a join chain did not take the fused route shows up in the statistics (profile mode)
+    auto decline = [&](const std::string& why) {
+      if (profile || trace) { size_t di = begin_stat("fused_scan_declined(" + t.name + "): " + why); end_stat(di, 0, 0); }
+      return false;
+    };
     std::set<std::string> key_only;
     if (const Json* ko = base_node.find("key_only"))
       for (const Json& c : ko->a) key_only.insert(c.s);
@@ -1247,7 +1252,7 @@ struct Exec {
         auto ci = t.col_index.find(name);
         if (ci == t.col_index.end()) return -1;
         fc.tc = &t.cols[ci->second];
-        if (!fc.tc->supported || fc.tc->lt.kind == LType::STR) return -1;
+        if (!fc.tc->supported || fc.tc->lt.kind == LType::STR) return -1;     // strings are not gathered (yet): ordinary route
       }
       fp.cols.push_back(fc);
       return (int)fp.cols.size() - 1;
@@ -1256,32 +1261,33 @@ struct Exec {
       const size_t j = chain.size() - 1 - q;
       const std::string& pk = chain[j]->str("probe_key");
       if (pk == t.part_col && !t.part_col.empty()) {
-        if (fp.part_side >= 0) return false;
+        if (fp.part_side >= 0) return decline("two joins on the partition column");
         fp.part_side = (int)j;
         continue;
       }
       const int ci = add_col(pk);
-      if (ci < 0 || fp.cols[ci].is_key) return false;        // unknown / string key, or the same key probed twice
+      if (ci < 0 || fp.cols[ci].is_key) return decline("probe key '" + pk + "' is not a fixed-width column, or is probed twice");
       fp.cols[ci].is_key = true;
       fp.key_side.push_back((int)j);
     }
     const int nkeys = (int)fp.key_side.size();
-    if (nkeys < 1) return false;
+    if (nkeys < 1) return decline("no probe key besides the partition column");
     for (const Json& c : base_node.at("columns").a) {
       if (key_only.count(c.s)) continue;
       const int ci = add_col(c.s);
-      if (ci < 0) return false;
+      if (ci < 0) return decline("payload column '" + c.s + "' is a string / unsupported column");
       fp.cols[ci].is_payload = true;
     }
     // ---- files
     fp.t = &t;
     fp.fs = select_files(t, down);
     const std::vector<int>& sel = fp.fs.sel;
-    if (sel.empty() || fp.fs.N <= 0 || fp.fs.N >= (int64_t(1) << 31)) return false;
+    if (sel.empty() || fp.fs.N <= 0) return decline("no rows selected");
+    if (fp.fs.N >= (int64_t(1) << 31)) return decline("2^31 or more rows selected");
     for (const FusedCol& fc : fp.cols) {
       if (!fc.tc) continue;
       for (int f : sel)
-        if (!fc.tc->file_direct[f]) return false;             // a page that needs a run-header walk
+        if (!fc.tc->file_direct[f]) return decline("column '" + fc.name + "' has a page that needs a run-header walk (file " + std::to_string(f) + ")");
     }
     // the key columns must be cut into pages at the same rows
     const TableColumn& k0 = *fp.cols[0].tc;
@@ -1289,9 +1295,9 @@ struct Exec {
       const TableColumn& kc = *fp.cols[c].tc;
       for (int f : sel) {
         const int64_t a0 = k0.file_page_begin[f], a1 = k0.file_page_begin[f + 1], b0 = kc.file_page_begin[f];
-        if (kc.file_page_begin[f + 1] - b0 != a1 - a0) return false;
+        if (kc.file_page_begin[f + 1] - b0 != a1 - a0) return decline("key columns are paged differently");
         for (int64_t p = 0; p < a1 - a0; ++p)
-          if (k0.pages[a0 + p].num_values != kc.pages[b0 + p].num_values) return false;
+          if (k0.pages[a0 + p].num_values != kc.pages[b0 + p].num_values) return decline("key columns are paged differently");
       }
     }
     mark("fused:checked");
@@ -1399,9 +1405,9 @@ struct Exec {
   Batch fused_probe(FusedPlan& fp, const std::vector<const Json*>& chain, std::vector<BuiltSide>& sides) {
     const int64_t N = fp.fs.N;
     const int nkeys = (int)fp.key_side.size();
-    // survivors: a star join keeps a small part of the fact rows; room for an eighth of them (at least 1 M), and if that
-    // ever overflows the kernel raises err[2] and the query is run again with room for all
-    const int64_t cap = speculate ? std::min<int64_t>(N, std::max<int64_t>(N / 8, int64_t(1) << 20)) : N;
+    // survivors: a star join over a large fact scan keeps a small part of the rows; beyond 16 M selected rows there is room
+    // for an eighth of them, and if that ever overflows the kernel raises err[2] and the query is run again with room for all
+    const int64_t cap = (speculate && N > (int64_t(16) << 20)) ? N / 8 : N;
     size_t stp = begin_stat("scan_probe", true);
     FusedScanArgs a;
     memset(&a, 0, sizeof a);

@@ -19,21 +19,25 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 SALES_DAYS = 182
+# the same rows on 18 days: ~152 k rows and eight 20000-row pages per column chunk, dictionaries of ~0.5 MB whose index
+# bit width grows from page to page - the shape of the SF100 bench warehouse's partition files
+FEW_DAYS = 18
 PARAMS = [{'MANUFACT': 606, 'MANAGER': 63, 'MONTH': 3, 'YEAR': 1998, 'GEN': 'M', 'MS': 'S', 'ES': 'College'},
           {'MANUFACT': 17, 'MANAGER': 8, 'MONTH': 5, 'YEAR': 1998, 'GEN': 'F', 'MS': 'W', 'ES': 'Primary'}]
 
 
-@pytest.fixture(scope='module')
-def sf1(tmp_path_factory):
+@pytest.fixture(scope='module', params=[SALES_DAYS, FEW_DAYS])
+def sf1(request, tmp_path_factory):
     from spark_rapids_benchmarks_b200 import datagen, engine
-    d = os.environ.get('NDS_TEST_WAREHOUSE_SF1') or str(tmp_path_factory.mktemp('nds_sf1_d182'))
+    days = request.param
+    d = (os.environ.get('NDS_TEST_WAREHOUSE_SF1') or str(tmp_path_factory.mktemp('nds_sf1'))) + '_d%d' % days
     tables = list(datagen.SUBSET_TABLES)
-    rows = datagen.ensure(d, 1, tables=tables, sales_days=SALES_DAYS)
+    rows = datagen.ensure(d, 1, tables=tables, sales_days=days)
     assert rows['store_sales'] == 2880404
     eng = engine.Engine(device=0, resident=True, keep_host=True)
     for t in tables:
         eng.register_table(t, os.path.join(d, t))
-    yield d, eng
+    yield d, eng, days
     eng.close()
 
 
@@ -57,13 +61,17 @@ def test_six_query_stream_at_sf1_matches_oracle(sf1, pi):
     from oracle import nds_queries as oq
     from spark_rapids_benchmarks_b200 import streams
     from tests.test_gpu_queries import _Sess
-    wh, eng = sf1
+    wh, eng, days = sf1
     info = eng.table_info('store_sales')
-    assert info['rows'] == 2880404 and info['files'] == SALES_DAYS + 1
+    assert info['rows'] == 2880404 and info['files'] == days + 1
     pages = [c['pages'] for c in info['columns'] if c['name'] == 'ss_item_sk'][0]
-    assert info['files'] <= pages <= info['files'] + 8    # one ~15.8 k-row page per date file, a few 20 k-row pages in the NULL partition
+    if days == SALES_DAYS:
+        assert info['files'] <= pages <= info['files'] + 8    # one ~15.8 k-row page per date file, a few 20 k-row pages in the NULL partition
+    else:
+        assert pages >= 7 * days                              # eight pages per date file
     for query in streams.SUBSET:
-        sql = streams.render(query, overrides=PARAMS[pi])
+        # the 18-day warehouse only has sales in January 1998
+        sql = streams.render(query, overrides=PARAMS[pi] if days == SALES_DAYS else dict(PARAMS[pi], MONTH=1))
         exp = oq.run_query(query, sql, wh)
         assert exp.num_rows > 0, query
         for source in ('hbm', 'host'):
@@ -72,13 +80,15 @@ def test_six_query_stream_at_sf1_matches_oracle(sf1, pi):
             assert got.schema.names == exp.schema.names
             assert [str(t) for t in got.schema.types] == [str(t) for t in exp.schema.types], (got.schema, exp.schema)
             assert rows_equal(got.to_pylist(), exp.to_pylist()), (query, source, got.to_pylist()[:3], exp.to_pylist()[:3])
+            ops = [o['op'] for o in eng.last_stats()['ops']]
+            assert 'scan_probe' in ops and not any(o.startswith('decode:store_sales') for o in ops), (query, ops)   # the fused fact scan ran
 
 
 def test_query7_at_sf1_takes_the_large_routes(sf1):
     """The routes the small warehouse cannot reach are really taken here: thousands of groups (more than the group-by's
     shared-memory cache and than the rank sort's direct limit)."""
     from spark_rapids_benchmarks_b200 import planner, streams
-    wh, eng = sf1
+    wh, eng, days = sf1
     sql = streams.render('query7', overrides=PARAMS[0])
     plan = planner.plan_sql(sql)
     node = plan['root']
