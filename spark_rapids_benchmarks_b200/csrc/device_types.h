@@ -32,6 +32,10 @@ struct PageTask {
   uint8_t phys;          // 0 fixed-width, 1 BYTE_ARRAY
   uint8_t bw;            // dictionary index bit width (enc == 1)
   uint32_t* vr;          // split decode only: page-local scratch [nw validity words][nw + 1 rank words] (nw = ceil(n/32))
+  // directly addressable dictionary pages (engine.h, PageInfo::direct): values from index tail_k on are one RLE run of
+  // dictionary index tail_ix (writers flush a trailing value or two that way); 0xFFFFFFFF = the page has no such tail
+  uint32_t tail_k;
+  uint32_t tail_ix;
 };
 
 // Column reference as kernels see it.

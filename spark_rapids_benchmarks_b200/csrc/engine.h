@@ -58,9 +58,11 @@ struct PageInfo {
   uint8_t bw = 0;              // dictionary index bit width (first byte of the values section)
   uint8_t fast = 0;            // 1: eligible for the split def/rows kernels (PLAIN fixed width, or few long index runs)
   // 1: value k of the page can be addressed without walking run headers - PLAIN fixed width, a one-entry dictionary
-  // (bit width 0), or an index stream of back-to-back 504-value bit-packed runs (every header byte 0x7F, the last run
-  // shorter): what the fused scan -> probe kernels and the late-materialising gather need (fused_scan.cu)
+  // (bit width 0), or an index stream of back-to-back 504-value bit-packed runs (every header byte 0x7F), then at most
+  // one shorter bit-packed run, then at most one closing RLE run (tail_k / tail_ix): what the fused scan -> probe
+  // kernels and the late-materialising gather need (fused_scan.cu)
   uint8_t direct = 0;
+  uint32_t tail_k = 0xFFFFFFFFu, tail_ix = 0;
   uint32_t direct_values = 0;  // values the uniform index stream holds (>= the page's non-null count when well formed)
 };
 struct DictInfo {

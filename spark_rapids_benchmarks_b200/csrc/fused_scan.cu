@@ -40,6 +40,7 @@ struct PageView {                 // what decoding one value of a page needs, ho
   uint32_t off8;                  // bit offset of value 0 from `words`: stream misalignment + the first header byte
   uint32_t kmax;                  // last valid value index (non-null count - 1; 0 when the page holds no value)
   uint32_t is_dict, width;
+  uint32_t tail_k, tail_ix;       // values from tail_k on: one closing RLE run of index tail_ix (PageTask)
 };
 
 __device__ __forceinline__ PageView make_view(const PageTask& t) {
@@ -62,6 +63,8 @@ __device__ __forceinline__ PageView make_view(const PageTask& t) {
   v.vr_rank = t.vr ? t.vr + nw : nullptr;
   const uint32_t nn = t.vr ? t.vr[2 * nw] : t.num_values;
   v.kmax = nn ? nn - 1u : 0u;
+  v.tail_k = t.tail_k;
+  v.tail_ix = t.tail_ix;
   return v;
 }
 
@@ -73,7 +76,8 @@ __device__ __forceinline__ bool page_value(const PageView& v, uint32_t k, int64_
     return true;
   }
   uint32_t ix = 0;
-  if (v.bw) {
+  if (k >= v.tail_k) ix = v.tail_ix;
+  else if (v.bw) {
     const uint32_t bit = k * v.bw + (k / 504u) * 8u + v.off8;
     const uint32_t* wp = v.words + (bit >> 5);
     ix = __funnelshift_r(__ldg(wp), __ldg(wp + 1), bit & 31) & v.bwmask;

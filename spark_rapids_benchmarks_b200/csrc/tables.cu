@@ -311,13 +311,27 @@ void Engine::register_table(const std::string& name, const std::string& path, co
                 while (p < psize && ok) {
                   const uint8_t h = payload[p];
                   if (h == 0x7F && p + full <= psize) { p += full; covered += 504; continue; }
-                  // the last run: a shorter bit-packed run with a one-byte header that ends the stream
-                  if (!(h & 1) || h >= 0x80) { ok = false; break; }
-                  const int64_t groups = h >> 1;
-                  if (p + 1 + groups * pi.bw > psize) { ok = false; break; }
-                  covered += groups * 8;
-                  p += 1 + groups * pi.bw;
-                  if (p != psize) ok = false;
+                  // after the full runs: at most one shorter bit-packed run (one-byte header) ...
+                  if ((h & 1) && h < 0x80) {
+                    const int64_t groups = h >> 1;
+                    if (p + 1 + groups * pi.bw > psize) { ok = false; break; }
+                    covered += groups * 8;
+                    p += 1 + groups * pi.bw;
+                  }
+                  if (p == psize) break;
+                  // ... and at most one closing RLE run (what the writer makes of a last value or two)
+                  uint64_t hv = 0;
+                  int sft = 0;
+                  uint8_t c;
+                  do { c = payload[p++]; hv |= (uint64_t)(c & 0x7F) << sft; sft += 7; } while ((c & 0x80) && p < psize && sft < 35);
+                  const int64_t bytew = (pi.bw + 7) / 8;
+                  if ((hv & 1) || p + bytew != psize) { ok = false; break; }
+                  uint32_t v = 0;
+                  for (int64_t b = 0; b < bytew; ++b) v |= (uint32_t)payload[p + b] << (8 * b);
+                  pi.tail_k = (uint32_t)covered;
+                  pi.tail_ix = v;
+                  covered += (int64_t)(hv >> 1);
+                  p += bytew;
                 }
                 pi.direct = ok && covered >= 0;
                 pi.direct_values = (uint32_t)std::min<int64_t>(covered, 0x7FFFFFFF);
@@ -376,6 +390,8 @@ void Engine::register_table(const std::string& name, const std::string& path, co
         task.width = (uint8_t)width;
         task.phys = tc.phys == pq::BYTE_ARRAY ? 1 : 0;
         task.vr = pi.fast ? reinterpret_cast<uint32_t*>((uintptr_t)1) : nullptr;
+        task.tail_k = pi.direct ? pi.tail_k : 0xFFFFFFFFu;
+        task.tail_ix = pi.tail_ix;
         tc.file_bytes_in[f] += pi.size;
         if (pi.dict >= 0) {
           task.dict = reinterpret_cast<const void*>((uintptr_t)(tc.dicts[pi.dict].off + 1));
