@@ -7,6 +7,7 @@
 #include "json.h"
 #include "ops.cuh"
 #include "parquet_meta.h"
+#include <vector_types.h>
 
 // Arrow C Data Interface (https://arrow.apache.org/docs/format/CDataInterface.html)
 extern "C" {
@@ -96,6 +97,14 @@ struct TableColumn {
   // file, vr != null marks a split-route page. A scan copies a file's run of templates and patches five fields.
   std::vector<PageTask> task_tmpl;
   std::vector<int64_t> file_bytes_in;    // per file: page payload bytes + dictionary bytes a scan of it reads
+  // Device copies for the fused scan (fused_scan.cu, expand_tasks_kernel): the templates, and per page its offset inside
+  // its file's validity / rank scratch (words) and the index of its first 4096-row chunk inside its file; per file the
+  // totals a scan needs to place a file's pages without touching them on the host.
+  PageTask* d_tmpl = nullptr;
+  uint2* d_page_aux = nullptr;           // x: vr words before this page in its file, y: chunks before this page in its file
+  std::vector<int32_t> file_vr_words, file_chunks, file_max_def;
+  std::vector<int64_t> file_def_bytes;
+  std::vector<uint2> aux_stage;          // host copy of d_page_aux while registering
   std::vector<uint8_t> file_direct;      // per file: every page is directly addressable (PageInfo::direct) and def_len <= 8192
   // value range from the Parquet column-chunk statistics (INT32 / INT64 columns; valid only when every chunk had them):
   // bounds the direct-address join table built over this column (ops.cu, dense tables)

@@ -1223,6 +1223,7 @@ struct Exec {
     int64_t* d_part_val = nullptr;
     uint8_t* d_part_null = nullptr;
     int64_t key_bytes_in = 0;
+    cudaEvent_t ev_payload_def = nullptr;       // the payload columns' def kernel ran on another stream: the gather waits for it
   };
 
   // Decides whether the probe side of a join chain can run as the fused scan and, if so, selects the files, builds and
@@ -1301,101 +1302,118 @@ struct Exec {
       }
     }
     mark("fused:checked");
-    // ---- page tasks of every column, file by file (the same templates the ordinary scan patches)
-    size_t npages = 0;
-    for (const FusedCol& fc : fp.cols)
-      if (fc.tc)
-        for (int f : sel) npages += (size_t)(fc.tc->file_page_begin[f + 1] - fc.tc->file_page_begin[f]);
-    std::vector<PageTask> tasks_fallback;
-    PageTask* tasks = reinterpret_cast<PageTask*>(ar.pin_take((int64_t)(npages * sizeof(PageTask)) + 16));
-    const bool tasks_pinned = tasks != nullptr;
-    if (!tasks) { tasks_fallback.resize(npages + 1); tasks = tasks_fallback.data(); }
-    std::vector<int> def_idx;
-    std::vector<int64_t> vr_off(npages, -1);
-    std::vector<int32_t> file_page0;            // per column with pages: sel.size() + 1 entries
-    std::vector<size_t> fp0_off(fp.cols.size(), 0);
-    int64_t vr_words = 0;
-    size_t ntasks = 0;
-    int max_def_len = 0;
+    // ---- place whole files: the page tasks themselves are expanded on the device from the registration-time templates
+    // (expand_tasks_kernel); the host only adds up per-file page / chunk / scratch totals
     size_t sdef = begin_stat("def_levels", true);
-    int64_t def_bytes = 0;
-    for (size_t c = 0; c < fp.cols.size(); ++c) {
-      FusedCol& fc = fp.cols[c];
-      if (!fc.tc) continue;
-      TableColumn& tc = *fc.tc;
-      const uint8_t* src_base = column_bytes(tc, sel);
-      fc.task0 = (int64_t)ntasks;
-      fp0_off[c] = file_page0.size();
-      for (size_t k = 0; k < sel.size(); ++k) {
-        const int f = sel[k];
-        const int64_t p0 = tc.file_page_begin[f], p1 = tc.file_page_begin[f + 1];
-        file_page0.push_back((int32_t)(ntasks - (size_t)fc.task0));
-        const size_t base = ntasks;
-        if (p1 > p0) memcpy(tasks + ntasks, tc.task_tmpl.data() + p0, (size_t)(p1 - p0) * sizeof(PageTask));
-        ntasks += (size_t)(p1 - p0);
-        if (fc.is_key) fp.key_bytes_in += tc.file_bytes_in[f];
-        for (size_t q = base; q < ntasks; ++q) {
-          PageTask& task = tasks[q];
-          task.vr = nullptr;
-          task.src = src_base + reinterpret_cast<uintptr_t>(task.src);
-          if (task.dict) task.dict = src_base + (reinterpret_cast<uintptr_t>(task.dict) - 1);
-          task.out = nullptr;
-          task.valid = nullptr;              // no column-wide bitmap: only the page-local validity / rank words are wanted
-          task.out_row += fp.fs.row_start[k];
+    std::vector<FileJob> jobs;
+    jobs.reserve(fp.cols.size() * sel.size());
+    std::vector<int64_t> job_vr;                 // per job: offset (words) of the file's scratch, -1 = none
+    job_vr.reserve(jobs.capacity());
+    std::vector<int32_t> file_page0;             // per column with pages: sel.size() + 1 entries
+    std::vector<size_t> fp0_off(fp.cols.size(), 0);
+    int64_t ntasks = 0, vr_words = 0, def_bytes = 0;
+    int ndef_key = 0, ndef_all = 0, nchunks = 0, max_def_key = 0, max_def_pay = 0;
+    // def page list: the key columns' pages first (the probe kernel waits for those), then the payload-only columns'
+    for (int pass = 0; pass < 2; ++pass) {
+      for (size_t c = 0; c < fp.cols.size(); ++c) {
+        FusedCol& fc = fp.cols[c];
+        if (!fc.tc || (pass == 0) != fc.is_key) continue;
+        TableColumn& tc = *fc.tc;
+        const uint8_t* src_base = column_bytes(tc, sel);
+        fc.task0 = ntasks;
+        fp0_off[c] = file_page0.size();
+        for (size_t k = 0; k < sel.size(); ++k) {
+          const int f = sel[k];
+          FileJob j;
+          memset(&j, 0, sizeof j);
+          j.tmpl = tc.d_tmpl;
+          j.page_aux = tc.d_page_aux;
+          j.src_base = src_base;
+          j.row_start = fp.fs.row_start[k];
+          j.page_begin = (int32_t)tc.file_page_begin[f];
+          j.npages = (int32_t)(tc.file_page_begin[f + 1] - tc.file_page_begin[f]);
+          j.out_task0 = (int32_t)ntasks;
+          j.col_task0 = (int32_t)fc.task0;
+          j.def_base = -1;
+          j.chunk_base = -1;
+          j.file = (int32_t)k;
+          file_page0.push_back((int32_t)(ntasks - fc.task0));
+          ntasks += j.npages;
+          if (fc.is_key) fp.key_bytes_in += tc.file_bytes_in[f];
+          int64_t vo = -1;
           if (tc.nullable) {
-            def_idx.push_back((int)q);
-            vr_off[q] = vr_words;
-            vr_words += 2 * (((int64_t)task.num_values + 31) / 32) + 1;
-            max_def_len = std::max<int>(max_def_len, (int)task.def_len);
-            def_bytes += task.def_len;
-            if (fc.is_key) fp.key_bytes_in -= task.def_len;      // the def kernel reads those, not the probe kernel
+            j.def_base = ndef_all;
+            ndef_all += j.npages;
+            vo = vr_words;
+            vr_words += tc.file_vr_words[f];
+            def_bytes += tc.file_def_bytes[f];
+            if (fc.is_key) { fp.key_bytes_in -= tc.file_def_bytes[f]; max_def_key = std::max(max_def_key, tc.file_max_def[f]); }
+            else max_def_pay = std::max(max_def_pay, tc.file_max_def[f]);
           }
+          if (c == 0) { j.chunk_base = nchunks; nchunks += tc.file_chunks[f]; }
+          jobs.push_back(j);
+          job_vr.push_back(vo);
         }
+        file_page0.push_back((int32_t)(ntasks - fc.task0));
       }
-      file_page0.push_back((int32_t)(ntasks - (size_t)fc.task0));
+      if (pass == 0) ndef_key = ndef_all;
     }
     fp.pages_per_col = (int64_t)file_page0[fp0_off[0] + sel.size()];
+    fp.nchunks = nchunks;
     uint32_t* d_vr = vr_words ? ar.alloc_n<uint32_t>(vr_words) : nullptr;
-    for (size_t q = 0; q < ntasks; ++q) tasks[q].vr = vr_off[q] >= 0 ? d_vr + vr_off[q] : nullptr;
-    fp.d_tasks = ar.alloc_n<PageTask>((int64_t)ntasks);
-    if (tasks_pinned) NDS_CUDA(cudaMemcpyAsync(fp.d_tasks, tasks, ntasks * sizeof(PageTask), cudaMemcpyHostToDevice, s));
-    else ar.upload(fp.d_tasks, tasks, (int64_t)(ntasks * sizeof(PageTask)));
-    // ---- chunks of the key pages, per-file partition values, per-column page directories: one upload
-    std::vector<FusedChunk> chunks;
-    {
-      const TableColumn& kc = *fp.cols[0].tc;
-      uint32_t page = 0;
-      for (size_t k = 0; k < sel.size(); ++k)
-        for (int64_t p = kc.file_page_begin[sel[k]]; p < kc.file_page_begin[sel[k] + 1]; ++p, ++page)
-          for (uint32_t r0 = 0; r0 < kc.pages[p].num_values; r0 += kFusedChunk) chunks.push_back(FusedChunk{page, r0, (uint32_t)k, 0});
-    }
-    fp.nchunks = (int)chunks.size();
+    for (size_t q = 0; q < jobs.size(); ++q) jobs[q].vr_base = job_vr[q] >= 0 ? d_vr + job_vr[q] : nullptr;
+    fp.d_tasks = ar.alloc_n<PageTask>(std::max<int64_t>(ntasks, 1));
+    int* d_def_idx = ar.alloc_n<int>(std::max(ndef_all, 1));
+    fp.d_chunks = ar.alloc_n<FusedChunk>(std::max(nchunks, 1));
+    // ---- jobs, per-file partition values, per-column page directories: one upload
     std::vector<int64_t> pv(sel.size());
     std::vector<uint8_t> pn(sel.size());
     for (size_t k = 0; k < sel.size(); ++k) { pv[k] = t.files[sel[k]].part_null ? 0 : t.files[sel[k]].part_val; pn[k] = t.files[sel[k]].part_null ? 1 : 0; }
-    const int64_t off_chunks = 0;
-    const int64_t off_pv = align_up(off_chunks + (int64_t)(chunks.size() * sizeof(FusedChunk)), 16);
+    const int64_t off_jobs = 0;
+    const int64_t off_pv = align_up(off_jobs + (int64_t)(jobs.size() * sizeof(FileJob)), 16);
     const int64_t off_pn = align_up(off_pv + (int64_t)pv.size() * 8, 16);
     const int64_t off_fp0 = align_up(off_pn + (int64_t)pn.size(), 16);
-    const int64_t off_def = align_up(off_fp0 + (int64_t)file_page0.size() * 4, 16);
-    const int64_t total = off_def + (int64_t)def_idx.size() * 4 + 16;
-    std::vector<uint8_t> h((size_t)total, 0);
-    if (!chunks.empty()) memcpy(h.data() + off_chunks, chunks.data(), chunks.size() * sizeof(FusedChunk));
-    memcpy(h.data() + off_pv, pv.data(), pv.size() * 8);
-    memcpy(h.data() + off_pn, pn.data(), pn.size());
-    if (!file_page0.empty()) memcpy(h.data() + off_fp0, file_page0.data(), file_page0.size() * 4);
-    if (!def_idx.empty()) memcpy(h.data() + off_def, def_idx.data(), def_idx.size() * 4);
+    const int64_t total = off_fp0 + (int64_t)file_page0.size() * 4 + 16;
+    uint8_t* hbuf = ar.pin_take(total);
+    std::vector<uint8_t> pageable;
+    const bool pinned = hbuf != nullptr;
+    if (!hbuf) { pageable.resize((size_t)total); hbuf = pageable.data(); }
+    memcpy(hbuf + off_jobs, jobs.data(), jobs.size() * sizeof(FileJob));
+    memcpy(hbuf + off_pv, pv.data(), pv.size() * 8);
+    memcpy(hbuf + off_pn, pn.data(), pn.size());
+    if (!file_page0.empty()) memcpy(hbuf + off_fp0, file_page0.data(), file_page0.size() * 4);
     uint8_t* d = (uint8_t*)ar.alloc(total);
-    ar.upload(d, h.data(), total);
-    fp.d_chunks = reinterpret_cast<FusedChunk*>(d + off_chunks);
+    if (pinned) NDS_CUDA(cudaMemcpyAsync(d, hbuf, (size_t)total, cudaMemcpyHostToDevice, s));
+    else ar.upload(d, hbuf, total);
     fp.d_part_val = reinterpret_cast<int64_t*>(d + off_pv);
     fp.d_part_null = d + off_pn;
     for (size_t c = 0; c < fp.cols.size(); ++c)
       if (fp.cols[c].tc) fp.cols[c].d_file_page0 = reinterpret_cast<const int32_t*>(d + off_fp0) + fp0_off[c];
+    launch_expand_tasks(reinterpret_cast<const FileJob*>(d + off_jobs), (int)jobs.size(), fp.d_tasks, d_def_idx, fp.d_chunks, s);
+    ++launches;
     mark("fused:uploaded");
-    // ---- def levels of every nullable column involved -> page-local validity + rank words
+    // ---- def levels -> page-local validity + rank words: the key columns' on this stream (the probe kernel needs them),
+    // the payload-only columns' on another stream, beside the probe kernel (only the gather needs those)
     int l = 0;
-    launch_decode_split(fp.d_tasks, reinterpret_cast<const int*>(d + off_def), (int)def_idx.size(), max_def_len, nullptr, 0, err, s, &l);
+    launch_decode_split(fp.d_tasks, d_def_idx, ndef_key, max_def_key, nullptr, 0, err, s, &l);
+    if (ndef_all > ndef_key) {
+      cudaStream_t s2 = s;
+      if (side_stream && e.side_streams_.size() >= 2)
+        for (cudaStream_t cand : e.side_streams_)
+          if (cand != s && cand != e.stream_) s2 = cand;
+      if (s2 != s) {
+        cudaEvent_t ev_up = e.get_event();
+        NDS_CUDA(cudaEventRecord(ev_up, s));
+        side_events.push_back(ev_up);
+        NDS_CUDA(cudaStreamWaitEvent(s2, ev_up, 0));
+      }
+      launch_decode_split(fp.d_tasks, d_def_idx + ndef_key, ndef_all - ndef_key, max_def_pay, nullptr, 0, err, s2, &l);
+      if (s2 != s) {
+        fp.ev_payload_def = e.get_event();
+        NDS_CUDA(cudaEventRecord(fp.ev_payload_def, s2));
+        side_events.push_back(fp.ev_payload_def);
+      }
+    }
     launches += l;
     end_stat(sdef, def_bytes + vr_words * 4, fp.fs.N);
     return true;
@@ -1471,6 +1489,7 @@ struct Exec {
       gather_row_bytes += 3 * g.width + 8 + 4;       // index word + dictionary entry + value written, rank words, row id
     }
     if (!gcs.empty()) {
+      if (fp.ev_payload_def) NDS_CUDA(cudaStreamWaitEvent(s, fp.ev_payload_def, 0));
       size_t stg = begin_stat("gather_decode", true);
       GatherCol* d_gcs = ar.alloc_n<GatherCol>((int64_t)gcs.size());
       ar.upload(d_gcs, gcs.data(), (int64_t)(gcs.size() * sizeof(GatherCol)));

@@ -98,6 +98,38 @@ __device__ __forceinline__ bool row_rank(const PageView& v, uint32_t r, uint32_t
 
 }  // namespace
 
+// Page tasks of a scan, made on the device: one warp per (column, selected file).
+__global__ void __launch_bounds__(128)
+expand_tasks_kernel(const FileJob* __restrict__ jobs, int njobs, PageTask* __restrict__ tasks, int* __restrict__ def_idx,
+                    FusedChunk* __restrict__ chunks) {
+  const int w = (int)((blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+  if (w >= njobs) return;
+  const FileJob j = jobs[w];
+  for (int p = lane; p < j.npages; p += 32) {
+    PageTask t = j.tmpl[j.page_begin + p];
+    const uint2 aux = j.page_aux[j.page_begin + p];
+    t.src = j.src_base + reinterpret_cast<uintptr_t>(t.src);
+    if (t.dict) t.dict = j.src_base + (reinterpret_cast<uintptr_t>(t.dict) - 1);
+    t.out = nullptr;
+    t.valid = nullptr;
+    t.out_row += j.row_start;
+    t.vr = j.vr_base ? j.vr_base + aux.x : nullptr;
+    tasks[j.out_task0 + p] = t;
+    if (j.def_base >= 0) def_idx[j.def_base + p] = j.out_task0 + p;
+    if (j.chunk_base >= 0) {
+      uint32_t c = (uint32_t)j.chunk_base + aux.y;
+      for (uint32_t r0 = 0; r0 < t.num_values; r0 += kFusedChunk, ++c)
+        chunks[c] = FusedChunk{(uint32_t)(j.out_task0 + p - j.col_task0), r0, (uint32_t)j.file, 0u};
+    }
+  }
+}
+
+void launch_expand_tasks(const FileJob* d_jobs, int njobs, PageTask* tasks, int* def_idx, FusedChunk* chunks, cudaStream_t s) {
+  if (njobs <= 0) return;
+  expand_tasks_kernel<<<(njobs * 32 + 127) / 128, 128, 0, s>>>(d_jobs, njobs, tasks, def_idx, chunks);
+  NDS_CUDA(cudaGetLastError());
+}
+
 __global__ void __launch_bounds__(kFusedThreads)
 scan_probe_kernel(const FusedScanArgs a) {
   __shared__ PageView s_view[kMaxChain];

@@ -147,6 +147,23 @@ struct FusedScanArgs {
   int* err;
 };
 void launch_scan_probe(const FusedScanArgs& args, int nchunks, cudaStream_t s);
+// One (column, selected file) pair of a fused scan: expand_tasks_kernel copies the file's page templates, patches them
+// and lists the pages (def kernel) and their 4096-row chunks (probe kernel) - the host only places whole files.
+struct FileJob {
+  const PageTask* tmpl;                    // the column's templates (device), indexed from page 0 of the table
+  const uint2* page_aux;
+  const uint8_t* src_base;                 // address of staged byte 0 of the column for this query
+  uint32_t* vr_base;                       // this file's validity / rank scratch, or nullptr (column without nulls)
+  int64_t row_start;                       // global row of the file's first row
+  int32_t page_begin, npages;              // the file's pages within tmpl
+  int32_t out_task0;                       // where the file's first task goes in the combined task array
+  int32_t col_task0;                       // first task of the column (chunk page numbers are relative to it)
+  int32_t def_base;                        // where the file's pages go in the def kernel's page list, or -1
+  int32_t chunk_base;                      // where the file's chunks go in the chunk list, or -1 (not the first key column)
+  int32_t file;                            // index among the selected files
+  int32_t pad;
+};
+void launch_expand_tasks(const FileJob* d_jobs, int njobs, PageTask* tasks, int* def_idx, FusedChunk* chunks, cudaStream_t s);
 struct GatherCol {
   const PageTask* tasks;                   // this column's tasks for the selected files, scan order (null: the partition column)
   const int32_t* file_page0;               // per selected file: first task; [nsel] = task count

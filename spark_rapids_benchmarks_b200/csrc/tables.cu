@@ -371,6 +371,24 @@ void Engine::register_table(const std::string& name, const std::string& path, co
     tc.task_tmpl.resize(tc.pages.size());
     tc.file_bytes_in.assign(tc.file_page_begin.size() - 1, 0);
     tc.file_direct.assign(tc.file_page_begin.size() - 1, 1);
+    tc.file_vr_words.assign(tc.file_page_begin.size() - 1, 0);
+    tc.file_chunks.assign(tc.file_page_begin.size() - 1, 0);
+    tc.file_max_def.assign(tc.file_page_begin.size() - 1, 0);
+    tc.file_def_bytes.assign(tc.file_page_begin.size() - 1, 0);
+    std::vector<uint2> page_aux(tc.pages.size());
+    for (size_t f = 0; f + 1 < tc.file_page_begin.size(); ++f) {
+      uint32_t vw = 0, ch = 0;
+      for (int64_t p = tc.file_page_begin[f]; p < tc.file_page_begin[f + 1]; ++p) {
+        page_aux[p] = make_uint2(vw, ch);
+        vw += 2 * ((tc.pages[p].num_values + 31) / 32) + 1;
+        ch += (tc.pages[p].num_values + kFusedChunk - 1) / kFusedChunk;
+        tc.file_max_def[f] = std::max<int32_t>(tc.file_max_def[f], (int32_t)tc.pages[p].def_len);
+        tc.file_def_bytes[f] += tc.pages[p].def_len;
+      }
+      tc.file_vr_words[f] = (int32_t)vw;
+      tc.file_chunks[f] = (int32_t)ch;
+    }
+    tc.aux_stage.swap(page_aux);
     tc.has_stats = tc.total_chunks > 0 && tc.stat_chunks == tc.total_chunks && tc.lt.kind != LType::STR && tc.lt.kind != LType::F64;
     for (size_t f = 0; f + 1 < tc.file_page_begin.size(); ++f) {
       int last_dict = -1;
@@ -411,6 +429,15 @@ void Engine::register_table(const std::string& name, const std::string& path, co
   NDS_CUDA(cudaSetDevice(device));
   for (TableColumn& tc : t.cols) {
     if (!tc.supported || tc.enc_bytes == 0) { tc.stage.clear(); tc.stage.shrink_to_fit(); continue; }
+    if (!tc.task_tmpl.empty()) {
+      NDS_CUDA(cudaMalloc(&tc.d_tmpl, tc.task_tmpl.size() * sizeof(PageTask)));
+      NDS_CUDA(cudaMemcpyAsync(tc.d_tmpl, tc.task_tmpl.data(), tc.task_tmpl.size() * sizeof(PageTask), cudaMemcpyHostToDevice, stream_));
+      NDS_CUDA(cudaMalloc(&tc.d_page_aux, tc.aux_stage.size() * sizeof(uint2)));
+      NDS_CUDA(cudaMemcpyAsync(tc.d_page_aux, tc.aux_stage.data(), tc.aux_stage.size() * sizeof(uint2), cudaMemcpyHostToDevice, stream_));
+      NDS_CUDA(cudaStreamSynchronize(stream_));
+      tc.aux_stage.clear();
+      tc.aux_stage.shrink_to_fit();
+    }
     if (resident_) {
       NDS_CUDA(cudaMalloc(&tc.d_enc, tc.enc_bytes + 256));
       NDS_CUDA(cudaMemcpyAsync(tc.d_enc, tc.stage.data(), tc.enc_bytes, cudaMemcpyHostToDevice, stream_));
@@ -435,6 +462,8 @@ void Engine::drop_table(const std::string& name) {
   if (it == tables_.end()) return;
   for (TableColumn& tc : it->second.cols) {
     if (tc.d_enc) cudaFree(tc.d_enc);
+    if (tc.d_tmpl) cudaFree(tc.d_tmpl);
+    if (tc.d_page_aux) cudaFree(tc.d_page_aux);
     if (tc.h_enc) cudaFreeHost(tc.h_enc);
   }
   for (MemColumn& mc : it->second.mem_cols) {
