@@ -263,6 +263,7 @@ struct Exec {
   int64_t small_scan_pages = 64; // options.small_scan_pages: scans with fewer split-route pages use the general kernel only
   bool speculate = true;         // options.speculate=false: never size a launch on an unverified device-side count
   bool dense_tables = true;      // options.dense_tables=false: every join table is an open-addressing hash table
+  bool topk_stream = true;       // options.topk_stream=false: ORDER BY ... LIMIT takes the multi-launch select / rank-sort route
   bool fused_scan = true;        // options.fused_scan=false: fact scans decode every column, then probe (decode_fast.cu + ops.cu)
   bool trace = false;            // options.trace: host timeline marks + time spent waiting in each stream sync
   double t_base = 0;
@@ -289,6 +290,7 @@ struct Exec {
       small_scan_pages = options->int_or("small_scan_pages", 64);
       dense_tables = options->bool_or("dense_tables", true);
       fused_scan = options->bool_or("fused_scan", true);
+      topk_stream = options->bool_or("topk_stream", true);
     }
     t_base = now_ms();
     if (!e.side_streams_.empty() && side_stream) {
@@ -2051,6 +2053,19 @@ struct Exec {
     if (nb > 0) {
       RowCount rc = in.rc();
       Blob::Dev dev = bb.upload(ar, s, keys.data(), (int64_t)keys.size() * sizeof(SortKey));
+      if (topk_stream && limit >= 1 && limit <= kTopkMaxK && B <= kTopkMaxKeyBytes) {
+        // ORDER BY ... LIMIT k: one launch, whatever the row count turns out to be on the device
+        const int ctas = topk_stream_ctas(nb);
+        const int Bw = (B + 7) / 8;
+        uint64_t* scratch = ar.alloc_n<uint64_t>(topk_stream_scratch_words(ctas, Bw));
+        uint64_t* fin_keys = ar.alloc_n<uint64_t>((int64_t)ctas * limit * Bw);
+        uint32_t* cta_rows = ar.alloc_n<uint32_t>((int64_t)ctas * limit);
+        int* meta = ar.zeros<int>(ctas + 2);
+        out_count = meta + ctas + 1;
+        launch_topk_stream(dev.progs, reinterpret_cast<const SortKey*>(dev.extra), (int)keys.size(), dev.ctx, rc, B, (int)limit, ctas, scratch,
+                           fin_keys, cta_rows, meta, meta + ctas, rows, out_count, err, s);
+        ++launches;
+      } else {
       uint8_t* keybuf = (uint8_t*)ar.alloc(nb * B);
       int* active = ar.zeros<int>(B + 1);
       launch_encode_keys(dev.progs, reinterpret_cast<const SortKey*>(dev.extra), (int)keys.size(), dev.ctx, rc, keybuf, B, active, err, s);
@@ -2135,6 +2150,7 @@ struct Exec {
           launch_take_perm(pa, pb, which, np, rn, limit, rows, out_count, s);
           ++launches;
         }
+      }
       }
     }
     if (in.n_exact >= 0 || !in.n_dev) {

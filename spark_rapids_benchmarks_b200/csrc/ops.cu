@@ -538,6 +538,193 @@ void launch_encode_keys(const Prog* progs, const SortKey* keys, int nk, OpCtx c,
   NDS_CUDA(cudaGetLastError());
 }
 
+// ------------------------------------------------------------------ sort: ORDER BY ... LIMIT k in one launch
+// Streaming top-k: every CTA walks its share of the rows in 256-row tiles; a thread encodes its row's key (the same
+// order-preserving byte string the radix route sorts) and keeps it only if it beats the CTA's current k-th best key.
+// Kept keys collect in a 512-slot candidate area in shared memory; when it fills, a bitonic sort of the slot indices
+// (45 compare-exchange steps, keys stay put) finds the k best, which move, sorted, into the other half of a ping-pong
+// pair, and the k-th becomes the new threshold - after the first tiles almost every row fails the threshold compare
+// and costs nothing more.  The last CTA to finish (atomic ticket) streams every CTA's <= k survivors through the same
+// routine and writes the result rows.  One launch replaces encode + compact + four select passes + collect + rank
+// sort; ties are broken by row id, so the order is total and the outcome deterministic.
+constexpr int kTopkThreads = 256;
+constexpr int kTopkCand = 512;
+constexpr int kTopkSmemMax = 200 * 1024;      // candidate areas beyond this stay in global memory (very wide keys)
+
+__device__ __forceinline__ uint64_t bswap64(uint64_t v) {
+  const uint32_t lo = (uint32_t)v, hi = (uint32_t)(v >> 32);
+  return ((uint64_t)__byte_perm(lo, 0, 0x0123) << 32) | (uint64_t)__byte_perm(hi, 0, 0x0123);
+}
+// (key a, row ra) ordered before (key b, row rb)?  keys: Bw 8-byte words holding big-endian byte strings.
+// CG: a was written by another CTA - read it through L2
+template <bool CG>
+__device__ __forceinline__ bool topk_less(const uint64_t* a, uint32_t ra, const uint64_t* b, uint32_t rb, int Bw) {
+  for (int w = 0; w < Bw; ++w) {
+    const uint64_t x = CG ? __ldcg(a + w) : a[w], y = b[w];
+    if (x != y) return bswap64(x) < bswap64(y);
+  }
+  return ra < rb;
+}
+
+struct TopkState {
+  uint64_t* area[2];        // ping-pong candidate key areas of this CTA, kTopkCand slots of Bw words (shared or global)
+  uint32_t* row[2];         // row ids of the candidates (shared memory)
+  uint16_t* perm;           // kTopkCand slot indices (shared memory)
+  int cur;                  // which area collects
+  int Bw, k;
+  bool have_thresh;         // area[cur][0 .. k) is the sorted k best of everything offered so far
+};
+
+// CTA-wide: keep the k best of the m collected candidates, sorted, in the other area.  Returns the new count.
+__device__ __forceinline__ int topk_shrink(TopkState& st, int m, int* s_m) {
+  const int tid = threadIdx.x;
+  const uint64_t* A = st.area[st.cur];
+  const uint32_t* rA = st.row[st.cur];
+  for (int i = tid; i < kTopkCand; i += kTopkThreads) st.perm[i] = (uint16_t)i;
+  // bitonic sort of the slot indices; slots >= m rank after everything
+  for (int size = 2; size <= kTopkCand; size <<= 1) {
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      __syncthreads();
+      const int i = 2 * tid - (tid & (stride - 1)), j = i + stride;
+      const bool up = (i & size) == 0;
+      const int a = st.perm[i], b = st.perm[j];
+      bool b_before_a;
+      if (b >= m) b_before_a = (a >= m) && b < a;
+      else if (a >= m) b_before_a = true;
+      else b_before_a = topk_less<false>(A + (int64_t)b * st.Bw, rA[b], A + (int64_t)a * st.Bw, rA[a], st.Bw);
+      if (b_before_a == up) { st.perm[i] = (uint16_t)b; st.perm[j] = (uint16_t)a; }
+    }
+  }
+  __syncthreads();
+  const int kept = m < st.k ? m : st.k;
+  uint64_t* B = st.area[st.cur ^ 1];
+  uint32_t* rB = st.row[st.cur ^ 1];
+  for (int idx = tid; idx < kept * st.Bw; idx += kTopkThreads) {
+    const int r = idx / st.Bw, w = idx - r * st.Bw;
+    B[(int64_t)r * st.Bw + w] = A[(int64_t)st.perm[r] * st.Bw + w];
+  }
+  for (int r = tid; r < kept; r += kTopkThreads) rB[r] = rA[st.perm[r]];
+  if (tid == 0) *s_m = kept;
+  __syncthreads();
+  st.cur ^= 1;
+  st.have_thresh = kept == st.k;
+  return kept;
+}
+
+// CTA-wide: offer one candidate per thread (have = this thread has one; key = its Bw words in global memory).
+template <bool CG>
+__device__ __forceinline__ void topk_offer(TopkState& st, bool have, uint32_t row, const uint64_t* key, int* s_m) {
+  bool keep = have;
+  if (keep && st.have_thresh)
+    keep = topk_less<CG>(key, row, st.area[st.cur] + (int64_t)(st.k - 1) * st.Bw, st.row[st.cur][st.k - 1], st.Bw);
+  if (keep) {
+    const int pos = atomicAdd(s_m, 1);            // at most kTopkThreads appends per call: the area cannot overflow
+    uint64_t* dst = st.area[st.cur] + (int64_t)pos * st.Bw;
+    for (int w = 0; w < st.Bw; ++w) dst[w] = CG ? __ldcg(key + w) : key[w];
+    st.row[st.cur][pos] = row;
+  }
+  __syncthreads();
+  const int m = *s_m;
+  __syncthreads();
+  if (m > kTopkCand - kTopkThreads) topk_shrink(st, m, s_m);
+}
+
+__global__ void __launch_bounds__(kTopkThreads)
+topk_stream_kernel(const Prog* __restrict__ progs, const SortKey* __restrict__ keys, int nk, OpCtx c, const int* n_dev, int64_t n_host,
+                   int B, int Bw, int k, int smem_areas, uint64_t* scratch, uint64_t* fin_keys, uint32_t* cta_rows, int* cta_count,
+                   int* done, uint32_t* out_rows, int* out_count, int* err) {
+  extern __shared__ __align__(16) uint64_t topk_smem[];
+  __shared__ uint32_t s_row[2][kTopkCand];
+  __shared__ uint16_t s_perm[kTopkCand];
+  __shared__ int s_m;
+  __shared__ int s_last;
+  const int tid = threadIdx.x;
+  const int64_t n = row_count(n_dev, n_host);
+  // global scratch per CTA: 256 staging slots (+ the two candidate areas when they do not fit shared memory)
+  const int64_t per_cta = (int64_t)(kTopkThreads + (smem_areas ? 0 : 2 * kTopkCand)) * Bw;
+  uint64_t* my = scratch + (int64_t)blockIdx.x * per_cta;
+  TopkState st;
+  st.area[0] = smem_areas ? topk_smem : my + (int64_t)kTopkThreads * Bw;
+  st.area[1] = st.area[0] + (int64_t)kTopkCand * Bw;
+  st.row[0] = s_row[0];
+  st.row[1] = s_row[1];
+  st.perm = s_perm;
+  st.cur = 0;
+  st.Bw = Bw;
+  st.k = k;
+  st.have_thresh = false;
+  if (tid == 0) s_m = 0;
+  __syncthreads();
+  uint64_t* stage = my + (int64_t)tid * Bw;
+  uint8_t* mykey = reinterpret_cast<uint8_t*>(stage);
+  for (int64_t t0 = (int64_t)blockIdx.x * kTopkThreads; t0 < n; t0 += (int64_t)gridDim.x * kTopkThreads) {
+    const int64_t i = t0 + tid;
+    const bool have = i < n;
+    if (have) {
+      encode_row(progs, keys, nk, c, i, mykey, nullptr, nullptr, err);
+      for (int b = B; b < Bw * 8; ++b) mykey[b] = 0;
+    }
+    topk_offer<false>(st, have, (uint32_t)i, stage, &s_m);
+  }
+  int kept = topk_shrink(st, s_m, &s_m);
+  // this CTA's survivors, sorted: keys and rows to global memory for the merge
+  {
+    const uint64_t* A = st.area[st.cur];
+    uint64_t* fin = fin_keys + (int64_t)blockIdx.x * k * Bw;
+    for (int idx = tid; idx < kept * Bw; idx += kTopkThreads) fin[idx] = A[idx];
+    for (int i = tid; i < kept; i += kTopkThreads) cta_rows[(int64_t)blockIdx.x * k + i] = st.row[st.cur][i];
+    if (tid == 0) cta_count[blockIdx.x] = kept;
+  }
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) s_last = atomicAdd(done, 1) == (int)gridDim.x - 1;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  // ---- the last CTA merges every CTA's survivors (same areas, started afresh)
+  st.cur = 0;
+  st.have_thresh = false;
+  if (tid == 0) s_m = 0;
+  __syncthreads();
+  for (int src = 0; src < (int)gridDim.x; ++src) {
+    const int cnt = __ldcg(cta_count + src);
+    if (cnt == 0) continue;                                  // uniform
+    const bool have = tid < cnt;
+    const uint32_t row = have ? __ldcg(cta_rows + (int64_t)src * k + tid) : 0u;
+    topk_offer<true>(st, have, row, fin_keys + ((int64_t)src * k + tid) * Bw, &s_m);
+  }
+  kept = topk_shrink(st, s_m, &s_m);
+  for (int i = tid; i < kept; i += kTopkThreads) out_rows[i] = st.row[st.cur][i];
+  if (tid == 0) *out_count = kept;
+}
+
+int topk_stream_ctas(int64_t n_bound) {
+  int64_t g = (n_bound + 4 * kTopkThreads - 1) / (4 * kTopkThreads);
+  return (int)(g < 1 ? 1 : (g > 64 ? 64 : g));
+}
+static bool topk_areas_in_smem(int Bw) { return (int64_t)2 * kTopkCand * Bw * 8 <= kTopkSmemMax; }
+int64_t topk_stream_scratch_words(int ctas, int Bw) {
+  return (int64_t)ctas * (kTopkThreads + (topk_areas_in_smem(Bw) ? 0 : 2 * kTopkCand)) * Bw;
+}
+
+void launch_topk_stream(const Prog* progs, const SortKey* keys, int nk, OpCtx c, RowCount n, int B, int k, int ctas, uint64_t* scratch,
+                        uint64_t* fin_keys, uint32_t* cta_rows, int* cta_count, int* done, uint32_t* out_rows, int* out_count, int* err,
+                        cudaStream_t s) {
+  const int Bw = (B + 7) / 8;
+  const bool in_smem = topk_areas_in_smem(Bw);
+  const size_t smem = in_smem ? (size_t)2 * kTopkCand * Bw * 8 : 0;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  NDS_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    NDS_CUDA(cudaFuncSetAttribute(topk_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTopkSmemMax));
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
+  }
+  topk_stream_kernel<<<ctas, kTopkThreads, smem, s>>>(progs, keys, nk, c, n.dev, n.host, B, Bw, k, in_smem ? 1 : 0, scratch, fin_keys, cta_rows,
+                                                      cta_count, done, out_rows, out_count, err);
+  NDS_CUDA(cudaGetLastError());
+}
+
 // ------------------------------------------------------------------ sort: LSD radix, 8-bit digits
 // Pass p (p = 0 is the least significant byte B-1) reads the live permutation buffer which[p], and, unless all rows
 // share the digit (skip), scatters into the other buffer; which[p+1] records the result. Three kernels per

@@ -209,7 +209,7 @@ def test_empty_inputs(gpu_engine):
     assert got.num_rows == 0 and got.schema.names == ['k', 'sv']
 
 
-def _sort_case(gpu_engine, n, limit, pattern, keep_frac, seed):
+def _sort_case(gpu_engine, n, limit, pattern, keep_frac, seed, options=None):
     """Every sort route: rank sort (<= 8192 rows, count on the device), top-k prefilter + rank sort over the
     candidates, candidate overflow -> LSD radix, no LIMIT -> LSD radix; expected order from numpy.lexsort."""
     rng = np.random.default_rng(seed)
@@ -232,7 +232,7 @@ def _sort_case(gpu_engine, n, limit, pattern, keep_frac, seed):
                       'child': {'op': 'scan', 'table': 'srt', 'columns': ['k1', 'k2', 'w', 'v', 'rid']}}}
     if limit is not None:
         plan['limit'] = limit
-    got = gpu_engine.execute(plan)
+    got = gpu_engine.execute(plan, options=options)
     keep = v >= thr
     kk1, kk2, kw, krid = k1[keep], k2[keep], words[keep], rid[keep]
     # fixed-width ASCII strings: descending order = ascending order of the negated code points
@@ -257,6 +257,18 @@ def _sort_case(gpu_engine, n, limit, pattern, keep_frac, seed):
 ])
 def test_sort_routes(gpu_engine, n, limit, pattern, keep):
     _sort_case(gpu_engine, n, limit, pattern, keep, seed=n + (limit or 0))
+    if limit is not None and limit <= 128:
+        # LIMIT <= 128 takes the one-launch streaming top-k by default; the select / rank-sort route must agree
+        _sort_case(gpu_engine, n, limit, pattern, keep, seed=n + (limit or 0), options={'topk_stream': False})
+
+
+@pytest.mark.parametrize('n,limit', [(3, 1), (255, 128), (257, 100), (700, 100), (70000, 128), (1500000, 100), (1500000, 3)])
+def test_streaming_topk_sizes(gpu_engine, n, limit):
+    """The one-launch top-k at sizes around its tile (256 rows), its candidate area (512) and its grid (64 CTAs), with
+    heavy ties on the leading keys and with most rows filtered out on the device."""
+    _sort_case(gpu_engine, n, limit, 'ties', 1.0, seed=n * 7 + limit)
+    _sort_case(gpu_engine, n, limit, 'flat', 0.35, seed=n * 11 + limit)
+    _sort_case(gpu_engine, n, limit, 'unique', 1.0, seed=n * 13 + limit)
 
 
 def test_sort_topk_candidate_overflow_falls_back(gpu_engine):
@@ -273,15 +285,19 @@ def test_sort_topk_candidate_overflow_falls_back(gpu_engine):
     gpu_engine.execute({'op': 'scan', 'table': 'ovf', 'columns': ['rid']})
     retries0 = gpu_engine.last_stats().get('speculation_retries', 0)
     got = gpu_engine.execute({'op': 'sort', 'limit': 50, 'keys': [{'expr': col('k'), 'desc': True}, {'expr': col('rid')}],
-                              'child': {'op': 'scan', 'table': 'ovf', 'columns': ['k', 'rid']}})
+                              'child': {'op': 'scan', 'table': 'ovf', 'columns': ['k', 'rid']}}, options={'topk_stream': False})
     order = np.lexsort([rid, -k])[:50]
     assert got.column('rid').to_pylist() == rid[order].tolist()
     # the device-sized first attempt reported the overflow and the engine ran the plan again without speculation
     assert gpu_engine.last_stats()['speculation_retries'] == retries0 + 1
     plan = {'op': 'sort', 'limit': 50, 'keys': [{'expr': col('k'), 'desc': True}, {'expr': col('rid')}],
             'child': {'op': 'scan', 'table': 'ovf', 'columns': ['k', 'rid']}}
-    again = gpu_engine.execute(plan, options={'speculate': False})
+    again = gpu_engine.execute(plan, options={'speculate': False, 'topk_stream': False})
     assert again.column('rid').to_pylist() == rid[order].tolist()
+    assert gpu_engine.last_stats()['speculation_retries'] == retries0 + 1
+    # the default route (streaming top-k) has no candidate list to overflow: same rows, no retry
+    dflt = gpu_engine.execute(plan)
+    assert dflt.column('rid').to_pylist() == rid[order].tolist()
     assert gpu_engine.last_stats()['speculation_retries'] == retries0 + 1
     gpu_engine.drop_table('ovf')
 
