@@ -1709,7 +1709,6 @@ struct Exec {
     const Json& jaggs = node.at("aggs");
     const int nkeys = (int)jkeys.a.size(), naggs = (int)jaggs.a.size();
     if (nkeys > kMaxGroupKeys) fail("plan: more than " + std::to_string(kMaxGroupKeys) + " group-by keys");
-    if (nkeys == 0) fail("plan: aggregation without group-by keys is not supported yet");
     // Row count of the input: exact if already known; otherwise its upper bound, with the table sized on the device
     // (ops.cu, agg_capacity) - unless that would reserve more than kAggReserveMax bytes, then one host round trip.
     constexpr int64_t kAggReserveMax = int64_t(6) << 30;
@@ -1788,7 +1787,7 @@ struct Exec {
       agg_codes.push_back(std::move(agg_code_of_this));
     }
     Batch out;
-    if (n == 0) {
+    if (n == 0 && nkeys > 0) {
       out.n_max = 0;
       out.n_exact = 0;
       for (int k = 0; k < nkeys; ++k) { Column c; c.name = jkeys.a[k].str("name"); c.lt = ktypes[k]; if (c.lt.kind == LType::BOOL) c.lt.kind = LType::INT; c.data = ar.alloc(16); out.cols.push_back(c); }
@@ -1796,6 +1795,8 @@ struct Exec {
       end_stat(st, 0, 0);
       return out;
     }
+    // a keyless aggregate has one group whatever the input (also none at all: agg_keyless_fix_kernel): one slot, one row out
+    if (nkeys == 0) n = 1;
     Blob::Dev dev = bb.upload(ar, s, specs.data(), (int64_t)specs.size() * sizeof(AggSpec));
     const AggSpec* d_specs = reinterpret_cast<const AggSpec*>(dev.extra);
     const uint32_t cap = agg_capacity_for(n);
@@ -1811,6 +1812,7 @@ struct Exec {
     launch_agg_insert(dev.progs, nkeys, d_specs, naggs, dev.ctx, in.rc(), slots, cap, acc, cnt, s);
     launch_agg_finalize(d_specs, naggs, slots, cap, in.rc(), acc, cnt, rep, ovals, ovalid, n, vwords, ng, s);
     launches += 3;
+    if (nkeys == 0) { launch_agg_keyless_fix(d_specs, naggs, ng, rep, ovals, ovalid, n, vwords, s); ++launches; }
     out.n_max = n;
     out.n_dev = ng;
     RowCount nout{ng, n};
@@ -2058,12 +2060,14 @@ struct Exec {
         const int ctas = topk_stream_ctas(nb);
         const int Bw = (B + 7) / 8;
         uint64_t* scratch = ar.alloc_n<uint64_t>(topk_stream_scratch_words(ctas, Bw));
-        uint64_t* fin_keys = ar.alloc_n<uint64_t>((int64_t)ctas * limit * Bw);
-        uint32_t* cta_rows = ar.alloc_n<uint32_t>((int64_t)ctas * limit);
-        int* meta = ar.zeros<int>(ctas + 2);
-        out_count = meta + ctas + 1;
+        const int groups = topk_stream_groups(ctas);
+        uint64_t* fin_keys = ar.alloc_n<uint64_t>((int64_t)(ctas + groups) * limit * Bw);
+        uint32_t* fin_rows = ar.alloc_n<uint32_t>((int64_t)(ctas + groups) * limit);
+        int* fin_count = ar.alloc_n<int>(ctas + groups);
+        int* meta = ar.zeros<int>(groups + 3);              // tickets (1 + groups), then the result count
+        out_count = meta + groups + 2;
         launch_topk_stream(dev.progs, reinterpret_cast<const SortKey*>(dev.extra), (int)keys.size(), dev.ctx, rc, B, (int)limit, ctas, scratch,
-                           fin_keys, cta_rows, meta, meta + ctas, rows, out_count, err, s);
+                           fin_keys, fin_rows, fin_count, meta, rows, out_count, err, s);
         ++launches;
       } else {
       uint8_t* keybuf = (uint8_t*)ar.alloc(nb * B);

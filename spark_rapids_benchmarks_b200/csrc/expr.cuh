@@ -67,6 +67,8 @@ __device__ __forceinline__ Val load_col(const ColRef& c, int64_t row) {
 
 __device__ inline Val eval_program(const Instr* __restrict__ code, int ncode, const ColRef* __restrict__ cols,
                                    const uint8_t* __restrict__ lit, int64_t row) {
+  // a bare column reference (group keys, aggregate arguments, sort keys, gathers: most programs): no interpreter loop
+  if (ncode == 1 && code[0].op == OP_COL) return load_col(cols[code[0].a], row);
   Val st[kEvalStack];
   int sp = 0;
   for (int pc = 0; pc < ncode; ++pc) {

@@ -300,6 +300,7 @@ __device__ __forceinline__ bool val_equal(const Val& a, const Val& b, int kind) 
   if (!a.ok) return true;
   if (kind == 2) {
     if (a.len != b.len) return false;
+    if (a.v == b.v) return true;               // the same dictionary entry (or the same bytes): no compare needed
     const uint8_t* x = (const uint8_t*)(uintptr_t)a.v;
     const uint8_t* y = (const uint8_t*)(uintptr_t)b.v;
     for (uint32_t i = 0; i < a.len; ++i)
@@ -347,6 +348,7 @@ agg_insert_kernel(const Prog* __restrict__ progs, int nkeys, const AggSpec* __re
   }
   for (int64_t i0 = blockIdx.x * (int64_t)blockDim.x; i0 < n; i0 += (int64_t)gridDim.x * blockDim.x) {
     const int64_t i = i0 + threadIdx.x;
+    const uint32_t active = __ballot_sync(0xFFFFFFFFu, i < n);      // the lanes that have a row: they run the body together
     if (i < n) {
       Val mine[kMaxGroupKeys];
       uint64_t h = 0x9E3779B97F4A7C15ULL;
@@ -369,9 +371,13 @@ agg_insert_kernel(const Prog* __restrict__ progs, int nkeys, const AggSpec* __re
         if (same) break;
         s = (s + 1) & mask;
       }
+      // Every row of the warp in the same group (few groups, or none at all - a keyless aggregate): SUM / COUNT are reduced
+      // across the warp (redux) and one lane applies them, instead of 32 atomics on one address.
+      const int lane = threadIdx.x & 31, leader = __ffs(active) - 1;
+      const bool uniform = __popc(active) > 1 && __all_sync(active, s == __shfl_sync(active, s, leader));
       bool hit = false;
       uint32_t e = 0;
-      if (use_cache && !s_off) {
+      if (use_cache && !s_off && (!uniform || lane == leader)) {
         e = (s ^ (s >> 8)) & (kAggCache - 1);
         const uint32_t tag = atomicCAS(&c_tag[e], 0u, s + 1u);
         hit = tag == 0u || tag == s + 1u;
@@ -382,8 +388,24 @@ agg_insert_kernel(const Prog* __restrict__ progs, int nkeys, const AggSpec* __re
         int64_t* pa = hit ? &c_acc[a * kAggCache + e] : &acc[a * cap + s];
         int64_t* pc = hit ? &c_cnt[a * kAggCache + e] : &cnt[a * cap + s];
         if (sp.fn == AGG_COUNT_REF) continue;
+        Val v;
+        v.ok = true; v.v = 0; v.len = 0;
+        if (sp.fn != AGG_COUNT_STAR) v = eval_program(progs[sp.prog].code, progs[sp.prog].n, c.cols, c.lit, i);
+        if (uniform && (sp.fn == AGG_SUM_I || sp.fn == AGG_COUNT || sp.fn == AGG_COUNT_STAR)) {
+          const unsigned cntv = __reduce_add_sync(active, v.ok ? 1u : 0u);
+          unsigned long long sum = 0;
+          if (sp.fn == AGG_SUM_I) {
+            // 64-bit sum from four 16-bit digit sums (each fits 21 bits for 32 lanes); wraps like the atomics do
+            const unsigned long long x = v.ok ? (unsigned long long)v.v : 0ull;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) sum += (unsigned long long)__reduce_add_sync(active, (unsigned)((x >> (16 * q)) & 0xFFFFull)) << (16 * q);
+          }
+          if (lane != leader || cntv == 0) continue;
+          atomicAdd(reinterpret_cast<unsigned long long*>(pc), (unsigned long long)cntv);
+          if (sp.fn == AGG_SUM_I) atomicAdd(reinterpret_cast<unsigned long long*>(pa), sum);
+          continue;
+        }
         if (sp.fn == AGG_COUNT_STAR) { atomicAdd(reinterpret_cast<unsigned long long*>(pc), 1ull); continue; }
-        Val v = eval_program(progs[sp.prog].code, progs[sp.prog].n, c.cols, c.lit, i);
         if (!v.ok) continue;
         agg_apply(sp.fn, pa, pc, v.v);
       }
@@ -441,6 +463,24 @@ agg_finalize_kernel(const AggSpec* __restrict__ aggs, int naggs, const uint32_t*
       if (ok) atomicOr(&out_valid[a * valid_stride_words + (g >> 5)], 1u << (g & 31));
     }
   }
+}
+
+// A keyless aggregate (no GROUP BY) yields exactly one row, also over an empty input: COUNT = 0, everything else NULL.
+__global__ void agg_keyless_fix_kernel(const AggSpec* __restrict__ aggs, int naggs, int* ngroups, uint32_t* rep_out, int64_t* out_vals,
+                                       uint32_t* out_valid, int64_t out_stride, int64_t valid_stride_words) {
+  if (threadIdx.x != 0 || blockIdx.x != 0 || *ngroups != 0) return;
+  *ngroups = 1;
+  rep_out[0] = 0;
+  for (int a = 0; a < naggs; ++a) {
+    const int fn = aggs[a].fn;
+    out_vals[a * out_stride] = 0;
+    out_valid[a * valid_stride_words] = (fn == AGG_COUNT || fn == AGG_COUNT_STAR || fn == AGG_COUNT_REF) ? 1u : 0u;
+  }
+}
+void launch_agg_keyless_fix(const AggSpec* aggs, int naggs, int* ngroups, uint32_t* rep_out, int64_t* out_vals, uint32_t* out_valid,
+                            int64_t out_stride, int64_t valid_stride_words, cudaStream_t s) {
+  agg_keyless_fix_kernel<<<1, 32, 0, s>>>(aggs, naggs, ngroups, rep_out, out_vals, out_valid, out_stride, valid_stride_words);
+  NDS_CUDA(cudaGetLastError());
 }
 
 void launch_agg_init(const AggSpec* aggs, int naggs, RowCount n, uint32_t cap_max, uint32_t* slots, int64_t* acc, int64_t* cnt,
@@ -629,16 +669,47 @@ __device__ __forceinline__ void topk_offer(TopkState& st, bool have, uint32_t ro
   if (m > kTopkCand - kTopkThreads) topk_shrink(st, m, s_m);
 }
 
+// CTA-wide: stream the sorted survivor lists of sources [s0, s1) through the top-k routine, started afresh.
+__device__ __forceinline__ int topk_merge(TopkState& st, int s0, int s1, const uint64_t* keys_base, const uint32_t* rows_base,
+                                          const int* counts, int* s_m) {
+  const int tid = threadIdx.x;
+  st.cur = 0;
+  st.have_thresh = false;
+  if (tid == 0) *s_m = 0;
+  __syncthreads();
+  for (int src = s0; src < s1; ++src) {
+    const int cnt = __ldcg(counts + src);
+    if (cnt == 0) continue;                                  // uniform
+    const bool have = tid < cnt;
+    const uint32_t row = have ? __ldcg(rows_base + (int64_t)src * st.k + tid) : 0u;
+    topk_offer<true>(st, have, row, keys_base + ((int64_t)src * st.k + tid) * st.Bw, s_m);
+  }
+  return topk_shrink(st, *s_m, s_m);
+}
+
+// sorted survivors of this CTA -> slot `slot` of a (keys, rows, counts) triple in global memory
+__device__ __forceinline__ void topk_publish(const TopkState& st, int kept, int slot, uint64_t* keys_base, uint32_t* rows_base, int* counts) {
+  const int tid = threadIdx.x;
+  const uint64_t* A = st.area[st.cur];
+  uint64_t* fin = keys_base + (int64_t)slot * st.k * st.Bw;
+  for (int idx = tid; idx < kept * st.Bw; idx += kTopkThreads) fin[idx] = A[idx];
+  for (int i = tid; i < kept; i += kTopkThreads) rows_base[(int64_t)slot * st.k + i] = st.row[st.cur][i];
+  if (tid == 0) counts[slot] = kept;
+}
+
+constexpr int kTopkGroup = 16;      // CTAs whose survivors one CTA merges before the final merge (two-level last-CTA pattern)
+
 __global__ void __launch_bounds__(kTopkThreads)
 topk_stream_kernel(const Prog* __restrict__ progs, const SortKey* __restrict__ keys, int nk, OpCtx c, const int* n_dev, int64_t n_host,
-                   int B, int Bw, int k, int smem_areas, uint64_t* scratch, uint64_t* fin_keys, uint32_t* cta_rows, int* cta_count,
-                   int* done, uint32_t* out_rows, int* out_count, int* err) {
+                   int B, int Bw, int k, int smem_areas, uint64_t* scratch, uint64_t* fin_keys, uint32_t* fin_rows, int* fin_count,
+                   int* tickets, uint32_t* out_rows, int* out_count, int* err) {
   extern __shared__ __align__(16) uint64_t topk_smem[];
   __shared__ uint32_t s_row[2][kTopkCand];
   __shared__ uint16_t s_perm[kTopkCand];
   __shared__ int s_m;
   __shared__ int s_last;
   const int tid = threadIdx.x;
+  const int nctas = (int)gridDim.x, ngroups = (nctas + kTopkGroup - 1) / kTopkGroup;
   const int64_t n = row_count(n_dev, n_host);
   // global scratch per CTA: 256 staging slots (+ the two candidate areas when they do not fit shared memory)
   const int64_t per_cta = (int64_t)(kTopkThreads + (smem_areas ? 0 : 2 * kTopkCand)) * Bw;
@@ -667,48 +738,48 @@ topk_stream_kernel(const Prog* __restrict__ progs, const SortKey* __restrict__ k
     topk_offer<false>(st, have, (uint32_t)i, stage, &s_m);
   }
   int kept = topk_shrink(st, s_m, &s_m);
-  // this CTA's survivors, sorted: keys and rows to global memory for the merge
-  {
-    const uint64_t* A = st.area[st.cur];
-    uint64_t* fin = fin_keys + (int64_t)blockIdx.x * k * Bw;
-    for (int idx = tid; idx < kept * Bw; idx += kTopkThreads) fin[idx] = A[idx];
-    for (int i = tid; i < kept; i += kTopkThreads) cta_rows[(int64_t)blockIdx.x * k + i] = st.row[st.cur][i];
-    if (tid == 0) cta_count[blockIdx.x] = kept;
-  }
+  // level 0 -> level 1: this CTA's survivors; the last CTA of each group of kTopkGroup merges the group's lists
+  uint64_t* keys1 = fin_keys;
+  uint32_t* rows1 = fin_rows;
+  int* count1 = fin_count;
+  uint64_t* keys2 = fin_keys + (int64_t)nctas * k * Bw;
+  uint32_t* rows2 = fin_rows + (int64_t)nctas * k;
+  int* count2 = fin_count + nctas;
+  topk_publish(st, kept, (int)blockIdx.x, keys1, rows1, count1);
+  const int g = (int)blockIdx.x / kTopkGroup;
+  const int g0 = g * kTopkGroup, g1 = min(g0 + kTopkGroup, nctas);
   __threadfence();
   __syncthreads();
-  if (tid == 0) s_last = atomicAdd(done, 1) == (int)gridDim.x - 1;
+  if (tid == 0) s_last = atomicAdd(tickets + 1 + g, 1) == (g1 - g0) - 1;
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  // ---- the last CTA merges every CTA's survivors (same areas, started afresh)
-  st.cur = 0;
-  st.have_thresh = false;
-  if (tid == 0) s_m = 0;
+  kept = topk_merge(st, g0, g1, keys1, rows1, count1, &s_m);
+  // level 1 -> result: the last group to finish merges the groups' lists and writes the rows
+  topk_publish(st, kept, g, keys2, rows2, count2);
+  __threadfence();
   __syncthreads();
-  for (int src = 0; src < (int)gridDim.x; ++src) {
-    const int cnt = __ldcg(cta_count + src);
-    if (cnt == 0) continue;                                  // uniform
-    const bool have = tid < cnt;
-    const uint32_t row = have ? __ldcg(cta_rows + (int64_t)src * k + tid) : 0u;
-    topk_offer<true>(st, have, row, fin_keys + ((int64_t)src * k + tid) * Bw, &s_m);
-  }
-  kept = topk_shrink(st, s_m, &s_m);
+  if (tid == 0) s_last = atomicAdd(tickets, 1) == ngroups - 1;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  kept = topk_merge(st, 0, ngroups, keys2, rows2, count2, &s_m);
   for (int i = tid; i < kept; i += kTopkThreads) out_rows[i] = st.row[st.cur][i];
   if (tid == 0) *out_count = kept;
 }
 
 int topk_stream_ctas(int64_t n_bound) {
-  int64_t g = (n_bound + 4 * kTopkThreads - 1) / (4 * kTopkThreads);
-  return (int)(g < 1 ? 1 : (g > 64 ? 64 : g));
+  int64_t g = (n_bound + kTopkThreads - 1) / kTopkThreads;
+  return (int)(g < 1 ? 1 : (g > 592 ? 592 : g));
 }
+int topk_stream_groups(int ctas) { return (ctas + kTopkGroup - 1) / kTopkGroup; }
 static bool topk_areas_in_smem(int Bw) { return (int64_t)2 * kTopkCand * Bw * 8 <= kTopkSmemMax; }
 int64_t topk_stream_scratch_words(int ctas, int Bw) {
   return (int64_t)ctas * (kTopkThreads + (topk_areas_in_smem(Bw) ? 0 : 2 * kTopkCand)) * Bw;
 }
 
 void launch_topk_stream(const Prog* progs, const SortKey* keys, int nk, OpCtx c, RowCount n, int B, int k, int ctas, uint64_t* scratch,
-                        uint64_t* fin_keys, uint32_t* cta_rows, int* cta_count, int* done, uint32_t* out_rows, int* out_count, int* err,
+                        uint64_t* fin_keys, uint32_t* fin_rows, int* fin_count, int* tickets, uint32_t* out_rows, int* out_count, int* err,
                         cudaStream_t s) {
   const int Bw = (B + 7) / 8;
   const bool in_smem = topk_areas_in_smem(Bw);
@@ -720,8 +791,8 @@ void launch_topk_stream(const Prog* progs, const SortKey* keys, int nk, OpCtx c,
     NDS_CUDA(cudaFuncSetAttribute(topk_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTopkSmemMax));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
-  topk_stream_kernel<<<ctas, kTopkThreads, smem, s>>>(progs, keys, nk, c, n.dev, n.host, B, Bw, k, in_smem ? 1 : 0, scratch, fin_keys, cta_rows,
-                                                      cta_count, done, out_rows, out_count, err);
+  topk_stream_kernel<<<ctas, kTopkThreads, smem, s>>>(progs, keys, nk, c, n.dev, n.host, B, Bw, k, in_smem ? 1 : 0, scratch, fin_keys, fin_rows,
+                                                      fin_count, tickets, out_rows, out_count, err);
   NDS_CUDA(cudaGetLastError());
 }
 

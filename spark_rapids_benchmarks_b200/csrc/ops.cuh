@@ -185,18 +185,21 @@ void launch_agg_insert(const Prog* progs, int nkeys, const AggSpec* aggs, int na
 void launch_agg_finalize(const AggSpec* aggs, int naggs, const uint32_t* slots, uint32_t cap_max, RowCount n, const int64_t* acc,
                          const int64_t* cnt, uint32_t* rep_out, int64_t* out_vals, uint32_t* out_valid, int64_t out_stride,
                          int64_t valid_stride_words, int* ngroups, cudaStream_t s);
+void launch_agg_keyless_fix(const AggSpec* aggs, int naggs, int* ngroups, uint32_t* rep_out, int64_t* out_vals, uint32_t* out_valid,
+                            int64_t out_stride, int64_t valid_stride_words, cudaStream_t s);
 void launch_str_maxlen(Prog p, OpCtx c, RowCount n, int* out_max, cudaStream_t s);
 void launch_encode_keys(const Prog* progs, const SortKey* keys, int nk, OpCtx c, RowCount n, uint8_t* keybuf, int B, int* active,
                         int* err, cudaStream_t s);
 // ORDER BY ... LIMIT k (k <= kTopkMaxK) in ONE launch (ops.cu, topk_stream_kernel).  scratch: topk_stream_scratch_words
-// 64-bit words; fin_keys: ctas * k * ceil(B / 8) words; cta_rows: ctas * k; cta_count: ctas ints; done: one zeroed int.
-// out_rows[0 .. min(k, n)) sorted, out_count[0] = min(k, n).
+// 64-bit words; with g = topk_stream_groups(ctas): fin_keys (ctas + g) * k * ceil(B / 8) words, fin_rows (ctas + g) * k,
+// fin_count ctas + g ints, tickets 1 + g zeroed ints.  out_rows[0 .. min(k, n)) sorted, out_count[0] = min(k, n).
 constexpr int kTopkMaxK = 128;
 constexpr int kTopkMaxKeyBytes = 1024;
 int topk_stream_ctas(int64_t n_bound);
+int topk_stream_groups(int ctas);
 int64_t topk_stream_scratch_words(int ctas, int Bw);
 void launch_topk_stream(const Prog* progs, const SortKey* keys, int nk, OpCtx c, RowCount n, int B, int k, int ctas, uint64_t* scratch,
-                        uint64_t* fin_keys, uint32_t* cta_rows, int* cta_count, int* done, uint32_t* out_rows, int* out_count, int* err,
+                        uint64_t* fin_keys, uint32_t* fin_rows, int* fin_count, int* tickets, uint32_t* out_rows, int* out_count, int* err,
                         cudaStream_t s);
 // Stable LSD radix sort of row ids by B-byte big-endian keys (8-bit digits).
 //  * launch_radix_sort_small: one CTA, rows <= kSmallSortMax, skips bytes whose active[] flag is 0; the index of

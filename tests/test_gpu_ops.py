@@ -388,3 +388,46 @@ def test_dates_through_case_and_min_max_export_as_date32(gpu_engine):
     assert agg['hi'].to_pylist() == [max(by[kv]) for kv in agg['k'].to_pylist()]
     assert isinstance(agg['lo'].to_pylist()[0], datetime.date)
     gpu_engine.drop_table('dt')
+
+
+def test_keyless_aggregate(gpu_engine, tbl):
+    """SELECT sum / count / min / max without GROUP BY: one row - also when no input row survives (COUNT 0, the rest NULL).
+    Every warp of the insert kernel sees one group, so this is the warp-reduction path of the group-by."""
+    def run(cond):
+        child = {'op': 'scan', 'table': 't', 'columns': ['a', 'b', 'd', 'g']}
+        if cond is not None:
+            child = {'op': 'filter', 'cond': cond, 'child': child}
+        return pa.Table.from_batches([gpu_engine.execute({'op': 'aggregate', 'keys': [], 'aggs': [
+            {'name': 'n', 'fn': 'count_star'}, {'name': 'ca', 'fn': 'count', 'expr': col('a')}, {'name': 'sa', 'fn': 'sum', 'expr': col('a')},
+            {'name': 'sb', 'fn': 'sum', 'expr': col('b')}, {'name': 'sd', 'fn': 'sum', 'expr': col('d')},
+            {'name': 'lo', 'fn': 'min', 'expr': col('b')}, {'name': 'hi', 'fn': 'max', 'expr': col('b')}], 'child': child})])
+    got = run(None).to_pylist()
+    assert got == [{'n': tbl.num_rows, 'ca': pc.count(tbl['a']).as_py(), 'sa': pc.sum(tbl['a']).as_py(), 'sb': pc.sum(tbl['b']).as_py(),
+                    'sd': pc.sum(tbl['d']).as_py(), 'lo': pc.min(tbl['b']).as_py(), 'hi': pc.max(tbl['b']).as_py()}]
+    keep = pc.fill_null(pc.greater(tbl['g'], 6), False)
+    sub = tbl.filter(keep)
+    got = run(fn('gt', col('g'), lit(6))).to_pylist()
+    assert got == [{'n': sub.num_rows, 'ca': pc.count(sub['a']).as_py(), 'sa': pc.sum(sub['a']).as_py(), 'sb': pc.sum(sub['b']).as_py(),
+                    'sd': pc.sum(sub['d']).as_py(), 'lo': pc.min(sub['b']).as_py(), 'hi': pc.max(sub['b']).as_py()}]
+    none = run(fn('gt', col('g'), lit(1000))).to_pylist()
+    assert none == [{'n': 0, 'ca': 0, 'sa': None, 'sb': None, 'sd': None, 'lo': None, 'hi': None}]
+
+
+def test_group_by_with_few_groups_per_warp(gpu_engine):
+    """Sorted input: every warp of the insert kernel holds one group (the warp-reduced path), group boundaries fall inside
+    warps (the per-lane path), and negative values / NULLs go through the 16-bit digit sums."""
+    rng = np.random.default_rng(99)
+    n = 50000
+    k = np.sort(rng.integers(0, 37, n)).astype(np.int64)
+    v = pa.array(rng.integers(-2**40, 2**40, n), mask=rng.random(n) < 0.2)
+    gpu_engine.register_arrow('fg', pa.table({'k': k, 'v': v}))
+    got = pa.Table.from_batches([gpu_engine.execute({'op': 'sort', 'keys': [{'expr': col('k')}], 'child': {
+        'op': 'aggregate', 'keys': [{'name': 'k', 'expr': col('k')}],
+        'aggs': [{'name': 's', 'fn': 'sum', 'expr': col('v')}, {'name': 'c', 'fn': 'count', 'expr': col('v')}, {'name': 'n', 'fn': 'count_star'}],
+        'child': {'op': 'scan', 'table': 'fg', 'columns': ['k', 'v']}}})])
+    exp = pa.table({'k': k, 'v': v}).group_by('k').aggregate([('v', 'sum'), ('v', 'count'), ([], 'count_all')]).sort_by('k')
+    assert got['k'].to_pylist() == exp['k'].to_pylist()
+    assert got['s'].to_pylist() == exp['v_sum'].to_pylist()
+    assert got['c'].to_pylist() == exp['v_count'].to_pylist()
+    assert got['n'].to_pylist() == exp['count_all'].to_pylist()
+    gpu_engine.drop_table('fg')

@@ -557,3 +557,23 @@ def test_fused_scan_keeps_key_columns_the_query_reads(gpu_engine, warehouse):
     g = j.group_by(['ss_item_sk', 'ss_sold_date_sk']).aggregate([([], 'count_all'), ('ss_quantity', 'sum')])
     exp = sorted(((r['ss_item_sk'], r['ss_sold_date_sk'], r['count_all'], r['ss_quantity_sum']) for r in g.to_pylist()))[:100]
     assert [(r['ss_item_sk'], r['ss_sold_date_sk'], r['cnt'], r['q']) for r in got.to_pylist()] == exp
+
+
+def test_keyless_aggregate_over_a_star_join(gpu_engine, warehouse):
+    """SELECT aggregates without GROUP BY through SQL: one row; and an empty selection still gives one row."""
+    import decimal
+    import pyarrow.compute as pc
+    sql = ('select count(*) n, sum(ss_quantity) q, avg(ss_sales_price) p, min(ss_item_sk) lo, max(ss_item_sk) hi '
+           'from store_sales, date_dim where ss_sold_date_sk = d_date_sk and d_moy = %d')
+    dd = oq.read_dim(warehouse, 'date_dim', ['d_date_sk', 'd_moy'])
+    for moy in (1, 7):                      # the tiny warehouse has sales in January and February only
+        keys = dd.filter(pc.equal(dd['d_moy'], moy).fill_null(False))['d_date_sk'].to_pylist()
+        ss = oq.read_fact(warehouse, 'store_sales', 'ss_sold_date_sk', ['ss_sold_date_sk', 'ss_quantity', 'ss_sales_price', 'ss_item_sk'], keys)
+        got = _Sess(gpu_engine).sql(sql % moy).toArrow().to_pylist()
+        if ss.num_rows == 0:
+            assert got == [{'n': 0, 'q': None, 'p': None, 'lo': None, 'hi': None}]
+            continue
+        total, cnt = pc.sum(ss['ss_sales_price']).as_py(), pc.count(ss['ss_sales_price']).as_py()
+        avg = (decimal.Decimal(total) / cnt).quantize(decimal.Decimal('0.000001'), rounding=decimal.ROUND_HALF_UP)
+        assert got == [{'n': ss.num_rows, 'q': pc.sum(ss['ss_quantity']).as_py(), 'p': avg, 'lo': pc.min(ss['ss_item_sk']).as_py(),
+                        'hi': pc.max(ss['ss_item_sk']).as_py()}]
