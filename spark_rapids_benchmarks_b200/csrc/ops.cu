@@ -621,18 +621,22 @@ __device__ __forceinline__ int topk_shrink(TopkState& st, int m, int* s_m) {
   const uint64_t* A = st.area[st.cur];
   const uint32_t* rA = st.row[st.cur];
   for (int i = tid; i < kTopkCand; i += kTopkThreads) st.perm[i] = (uint16_t)i;
-  // bitonic sort of the slot indices; slots >= m rank after everything
-  for (int size = 2; size <= kTopkCand; size <<= 1) {
+  // bitonic sort of the slot indices over the next power of two >= m; slots >= m rank after everything
+  int span = 2;
+  while (span < m) span <<= 1;
+  for (int size = 2; size <= span; size <<= 1) {
     for (int stride = size >> 1; stride > 0; stride >>= 1) {
       __syncthreads();
       const int i = 2 * tid - (tid & (stride - 1)), j = i + stride;
-      const bool up = (i & size) == 0;
-      const int a = st.perm[i], b = st.perm[j];
-      bool b_before_a;
-      if (b >= m) b_before_a = (a >= m) && b < a;
-      else if (a >= m) b_before_a = true;
-      else b_before_a = topk_less<false>(A + (int64_t)b * st.Bw, rA[b], A + (int64_t)a * st.Bw, rA[a], st.Bw);
-      if (b_before_a == up) { st.perm[i] = (uint16_t)b; st.perm[j] = (uint16_t)a; }
+      if (j < span) {
+        const bool up = (i & size) == 0;
+        const int a = st.perm[i], b = st.perm[j];
+        bool b_before_a;
+        if (b >= m) b_before_a = (a >= m) && b < a;
+        else if (a >= m) b_before_a = true;
+        else b_before_a = topk_less<false>(A + (int64_t)b * st.Bw, rA[b], A + (int64_t)a * st.Bw, rA[a], st.Bw);
+        if (b_before_a == up) { st.perm[i] = (uint16_t)b; st.perm[j] = (uint16_t)a; }
+      }
     }
   }
   __syncthreads();
@@ -669,22 +673,44 @@ __device__ __forceinline__ void topk_offer(TopkState& st, bool have, uint32_t ro
   if (m > kTopkCand - kTopkThreads) topk_shrink(st, m, s_m);
 }
 
-// CTA-wide: stream the sorted survivor lists of sources [s0, s1) through the top-k routine, started afresh.
+// CTA-wide: stream the survivor lists of sources [s0, s1) (at most kTopkMaxSrc of them, <= k entries each) through the
+// top-k routine, started afresh: the lists are taken as one flat sequence, kTopkThreads candidates per round.
+// sort_result: the result must come out sorted (the final merge); otherwise <= k unsorted survivors are fine.
+constexpr int kTopkMaxSrc = 64;
 __device__ __forceinline__ int topk_merge(TopkState& st, int s0, int s1, const uint64_t* keys_base, const uint32_t* rows_base,
-                                          const int* counts, int* s_m) {
+                                          const int* counts, int* s_m, int* s_pre, bool sort_result) {
   const int tid = threadIdx.x;
+  const int ns = s1 - s0;
   st.cur = 0;
   st.have_thresh = false;
   if (tid == 0) *s_m = 0;
+  if (tid < ns) s_pre[tid + 1] = __ldcg(counts + s0 + tid);
   __syncthreads();
-  for (int src = s0; src < s1; ++src) {
-    const int cnt = __ldcg(counts + src);
-    if (cnt == 0) continue;                                  // uniform
-    const bool have = tid < cnt;
-    const uint32_t row = have ? __ldcg(rows_base + (int64_t)src * st.k + tid) : 0u;
-    topk_offer<true>(st, have, row, keys_base + ((int64_t)src * st.k + tid) * st.Bw, s_m);
+  if (tid == 0) {
+    s_pre[0] = 0;
+    for (int q = 0; q < ns; ++q) s_pre[q + 1] += s_pre[q];
   }
-  return topk_shrink(st, *s_m, s_m);
+  __syncthreads();
+  const int total = s_pre[ns];
+  for (int c0 = 0; c0 < total; c0 += kTopkThreads) {
+    const int cidx = c0 + tid;
+    const bool have = cidx < total;
+    int src = 0, e = 0;
+    if (have) {
+      int lo = 0, hi = ns - 1;                     // the source whose range holds candidate cidx
+      while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (s_pre[mid] <= cidx) lo = mid; else hi = mid - 1;
+      }
+      src = s0 + lo;
+      e = cidx - s_pre[lo];
+    }
+    const uint32_t row = have ? __ldcg(rows_base + (int64_t)src * st.k + e) : 0u;
+    topk_offer<true>(st, have, row, keys_base + ((int64_t)src * st.k + e) * st.Bw, s_m);
+  }
+  const int m = *s_m;
+  if (m <= st.k && !sort_result) return m;
+  return topk_shrink(st, m, s_m);
 }
 
 // sorted survivors of this CTA -> slot `slot` of a (keys, rows, counts) triple in global memory
@@ -697,6 +723,7 @@ __device__ __forceinline__ void topk_publish(const TopkState& st, int kept, int 
   if (tid == 0) counts[slot] = kept;
 }
 
+static_assert(592 / 16 <= kTopkMaxSrc, "final merge fan-in");
 constexpr int kTopkGroup = 16;      // CTAs whose survivors one CTA merges before the final merge (two-level last-CTA pattern)
 
 __global__ void __launch_bounds__(kTopkThreads)
@@ -708,6 +735,7 @@ topk_stream_kernel(const Prog* __restrict__ progs, const SortKey* __restrict__ k
   __shared__ uint16_t s_perm[kTopkCand];
   __shared__ int s_m;
   __shared__ int s_last;
+  __shared__ int s_pre[kTopkMaxSrc + 1];
   const int tid = threadIdx.x;
   const int nctas = (int)gridDim.x, ngroups = (nctas + kTopkGroup - 1) / kTopkGroup;
   const int64_t n = row_count(n_dev, n_host);
@@ -737,7 +765,8 @@ topk_stream_kernel(const Prog* __restrict__ progs, const SortKey* __restrict__ k
     }
     topk_offer<false>(st, have, (uint32_t)i, stage, &s_m);
   }
-  int kept = topk_shrink(st, s_m, &s_m);
+  // (<= k collected candidates are handed on as they are: only the result has to be sorted)
+  int kept = s_m > k ? topk_shrink(st, s_m, &s_m) : s_m;
   // level 0 -> level 1: this CTA's survivors; the last CTA of each group of kTopkGroup merges the group's lists
   uint64_t* keys1 = fin_keys;
   uint32_t* rows1 = fin_rows;
@@ -754,7 +783,7 @@ topk_stream_kernel(const Prog* __restrict__ progs, const SortKey* __restrict__ k
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  kept = topk_merge(st, g0, g1, keys1, rows1, count1, &s_m);
+  kept = topk_merge(st, g0, g1, keys1, rows1, count1, &s_m, s_pre, false);
   // level 1 -> result: the last group to finish merges the groups' lists and writes the rows
   topk_publish(st, kept, g, keys2, rows2, count2);
   __threadfence();
@@ -763,7 +792,7 @@ topk_stream_kernel(const Prog* __restrict__ progs, const SortKey* __restrict__ k
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  kept = topk_merge(st, 0, ngroups, keys2, rows2, count2, &s_m);
+  kept = topk_merge(st, 0, ngroups, keys2, rows2, count2, &s_m, s_pre, true);
   for (int i = tid; i < kept; i += kTopkThreads) out_rows[i] = st.row[st.cur][i];
   if (tid == 0) *out_count = kept;
 }
