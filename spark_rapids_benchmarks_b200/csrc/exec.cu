@@ -263,6 +263,7 @@ struct Exec {
   int64_t small_scan_pages = 64; // options.small_scan_pages: scans with fewer split-route pages use the general kernel only
   bool speculate = true;         // options.speculate=false: never size a launch on an unverified device-side count
   bool dense_tables = true;      // options.dense_tables=false: every join table is an open-addressing hash table
+  bool exchange_single = true;   // options.exchange_single=false: the exchange reads the row counts back (two collectives)
   bool topk_stream = true;       // options.topk_stream=false: ORDER BY ... LIMIT takes the multi-launch select / rank-sort route
   bool fused_scan = true;        // options.fused_scan=false: fact scans decode every column, then probe (decode_fast.cu + ops.cu)
   bool trace = false;            // options.trace: host timeline marks + time spent waiting in each stream sync
@@ -291,6 +292,7 @@ struct Exec {
       dense_tables = options->bool_or("dense_tables", true);
       fused_scan = options->bool_or("fused_scan", true);
       topk_stream = options->bool_or("topk_stream", true);
+      exchange_single = options->bool_or("exchange_single", true);
     }
     t_base = now_ms();
     if (!e.side_streams_.empty() && side_stream) {
@@ -1876,6 +1878,70 @@ struct Exec {
       if (!which.empty() && in.rc().host > 0) {
         std::vector<Column> fc = eval_columns(exs, in, nullptr, in.rc());
         for (size_t k = 0; k < which.size(); ++k) flat[which[k]] = fc[k];
+      }
+    }
+    // ---- speculative route: ONE collective and no host round trip.  Every rank sends a fixed-capacity segment whose
+    // header holds its row count; the unpack kernel reads the headers on the device.  More rows than the capacity raise
+    // err[2] and the query runs again on the exact two-step route below.
+    constexpr int64_t kXchgSpecRows = int64_t(128) << 10;
+    if (speculate && exchange_single && ncols <= kXchgHeader / 4 - 1) {
+      std::vector<XCol> proto(ncols);
+      bool ok_types = true;
+      for (int c = 0; c < ncols; ++c) {
+        XCol& x = proto[c];
+        memset(&x, 0, sizeof x);
+        const LType& t = flat[c].lt;
+        x.kind = t.kind == LType::STR ? 2 : (t.dtype() == DT_I32 ? 0 : 1);
+        x.maxlen = t.kind == LType::STR ? t.maxlen : 0;
+        if (t.kind == LType::STR && t.maxlen <= 0) ok_types = false;
+      }
+      const int64_t cap_rows = std::max<int64_t>(std::min<int64_t>(in.rc().host, kXchgSpecRows), 1);
+      SegLayout L = seg_layout(proto, cap_rows);
+      const int64_t seg_bytes = kXchgHeader + L.bytes;
+      if (ok_types && seg_bytes * world < (int64_t(1) << 32)) {
+        for (int c = 0; c < ncols; ++c) { proto[c].off_valid = L.off_valid[c]; proto[c].off_data = L.off_data[c]; proto[c].off_aux = L.off_aux[c]; }
+        std::vector<XCol> mine = proto, dst(ncols);
+        for (int c = 0; c < ncols; ++c) { mine[c].data = flat[c].data; mine[c].valid = flat[c].valid; mine[c].strbase = flat[c].strbase; }
+        uint8_t* d_send = (uint8_t*)ar.alloc(seg_bytes);
+        uint8_t* d_recv = (uint8_t*)ar.alloc(seg_bytes * world);
+        const int64_t Nmax = cap_rows * world;
+        const int64_t vwords = (Nmax + 31) / 32 + 1;
+        Batch out;
+        out.n_max = Nmax;
+        out.n_dev = ar.zeros<int>(1);
+        for (int c = 0; c < ncols; ++c) {
+          Column oc;
+          oc.name = flat[c].name;
+          oc.lt = flat[c].lt;
+          const int w = proto[c].kind == 0 ? 4 : 8;
+          oc.data = ar.alloc(Nmax * w);
+          oc.valid = ar.zeros<uint32_t>(vwords);
+          oc.strbase = proto[c].kind == 2 ? d_recv : nullptr;
+          out.cols.push_back(oc);
+          memset(&dst[c], 0, sizeof(XCol));
+          dst[c].data = oc.data;
+          dst[c].valid = oc.valid;
+          dst[c].kind = proto[c].kind;
+        }
+        // descriptors: [mine][proto][dst] in one upload
+        std::vector<XCol> all3;
+        all3.insert(all3.end(), mine.begin(), mine.end());
+        all3.insert(all3.end(), proto.begin(), proto.end());
+        all3.insert(all3.end(), dst.begin(), dst.end());
+        XCol* d_desc = ar.alloc_n<XCol>((int64_t)all3.size());
+        ar.upload(d_desc, all3.data(), (int64_t)(all3.size() * sizeof(XCol)));
+        launch_exchange_pack_dev(d_desc, ncols, in.rc(), cap_rows, d_send, err, s);
+        ++launches;
+        if (loop > 0) {
+          for (int r = 0; r < world; ++r)
+            NDS_CUDA(cudaMemcpyAsync(d_recv + (int64_t)r * seg_bytes, d_send, (size_t)seg_bytes, cudaMemcpyDeviceToDevice, s));
+        } else {
+          nccl_check(nccl_api().AllGather(d_send, d_recv, (size_t)seg_bytes, kNcclChar, e.comm_, s), "ncclAllGather(segments)");
+        }
+        launch_exchange_unpack_dev(d_desc + ncols, d_desc + 2 * ncols, ncols, world, cap_rows, seg_bytes, d_recv, out.n_dev, err, s);
+        ++launches;
+        end_stat(st, seg_bytes * (world - 1), Nmax);
+        return out;
       }
     }
     // ---- counts (and string slot widths: the widest any rank declares) travel first

@@ -621,12 +621,15 @@ __device__ __forceinline__ int topk_shrink(TopkState& st, int m, int* s_m) {
   const uint64_t* A = st.area[st.cur];
   const uint32_t* rA = st.row[st.cur];
   for (int i = tid; i < kTopkCand; i += kTopkThreads) st.perm[i] = (uint16_t)i;
+  __syncthreads();
   // bitonic sort of the slot indices over the next power of two >= m; slots >= m rank after everything
   int span = 2;
   while (span < m) span <<= 1;
   for (int size = 2; size <= span; size <<= 1) {
     for (int stride = size >> 1; stride > 0; stride >>= 1) {
-      __syncthreads();
+      // strides below 32 pair elements inside the 64-element chunk a warp owns (thread t <-> elements 2t - t % stride and
+      // + stride): only the warp itself wrote them in the previous step
+      if (stride >= 32) __syncthreads(); else __syncwarp();
       const int i = 2 * tid - (tid & (stride - 1)), j = i + stride;
       if (j < span) {
         const bool up = (i & size) == 0;
@@ -1384,6 +1387,92 @@ void launch_exchange_unpack(const XCol* srcs, const XCol* dst, int ncols, const 
                             const uint8_t* recv, cudaStream_t s) {
   if (max_rows <= 0) return;
   exchange_unpack_kernel<<<dim3(grid_for(max_rows, kThreads, 148 * 2), world), kThreads, 0, s>>>(srcs, dst, ncols, row_begin, recv);
+  NDS_CUDA(cudaGetLastError());
+}
+
+// ---- the same exchange with the row counts left on the device: ONE collective, no host round trip.
+// A segment has a fixed capacity (cap_rows rows, laid out for that capacity) and starts with a 64-byte header:
+// int32 row count, then the string slot width of every column.  The unpack kernel reads every rank's header itself.
+__global__ void __launch_bounds__(kThreads)
+exchange_pack_dev_kernel(const XCol* __restrict__ cols, int ncols, const int* n_dev, int64_t n_host, int64_t cap_rows,
+                         uint8_t* __restrict__ out, int* err) {
+  int64_t n = row_count(n_dev, n_host);
+  if (n > cap_rows) {            // more rows than the speculative capacity: the query runs again with exact sizes
+    if (blockIdx.x == 0 && threadIdx.x == 0) atomicExch(err + 2, 1);
+    n = cap_rows;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    int32_t* h = reinterpret_cast<int32_t*>(out);
+    h[0] = (int32_t)n;
+    for (int c = 0; c < ncols && c < kXchgHeader / 4 - 1; ++c) h[1 + c] = cols[c].kind == 2 ? cols[c].maxlen : 0;
+  }
+  uint8_t* body = out + kXchgHeader;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    for (int c = 0; c < ncols; ++c) {
+      const XCol x = cols[c];
+      const bool ok = !x.valid || ((x.valid[i >> 5] >> (i & 31)) & 1u);
+      body[x.off_valid + i] = ok ? 1 : 0;
+      if (x.kind == 0) reinterpret_cast<int32_t*>(body + x.off_data)[i] = ok ? reinterpret_cast<const int32_t*>(x.data)[i] : 0;
+      else if (x.kind == 1) reinterpret_cast<int64_t*>(body + x.off_data)[i] = ok ? reinterpret_cast<const int64_t*>(x.data)[i] : 0;
+      else {
+        const StrView v = ok ? reinterpret_cast<const StrView*>(x.data)[i] : 0;
+        int len = (int)(v >> 32);
+        if (len > x.maxlen) { if (err) atomicExch(err, 14); len = x.maxlen; }
+        reinterpret_cast<int32_t*>(body + x.off_data)[i] = len;
+        const uint8_t* p = x.strbase + (uint32_t)v;
+        uint8_t* q = body + x.off_aux + i * (int64_t)x.maxlen;
+        for (int b = 0; b < len; ++b) q[b] = p[b];
+      }
+    }
+  }
+}
+void launch_exchange_pack_dev(const XCol* cols, int ncols, RowCount n, int64_t cap_rows, uint8_t* out, int* err, cudaStream_t s) {
+  exchange_pack_dev_kernel<<<grid_for(std::min<int64_t>(n.host, cap_rows)), kThreads, 0, s>>>(cols, ncols, n.dev, n.host, cap_rows, out, err);
+  NDS_CUDA(cudaGetLastError());
+}
+
+// blockIdx.y = source rank.  proto[c]: column c's layout inside a segment (offsets for cap_rows; the same for every
+// rank), dst[c]: the concatenated output column (valid bitmap pre-zeroed).  total_out[0] = rows of all ranks.
+__global__ void __launch_bounds__(kThreads)
+exchange_unpack_dev_kernel(const XCol* __restrict__ proto, const XCol* __restrict__ dst, int ncols, int world, int64_t seg_bytes,
+                           const uint8_t* __restrict__ recv, int* total_out, int* err) {
+  const int r = blockIdx.y;
+  int64_t before = 0, total = 0;
+  for (int q = 0; q < world; ++q) {
+    const int32_t* h = reinterpret_cast<const int32_t*>(recv + (int64_t)q * seg_bytes);
+    const int64_t nq = h[0];
+    if (q < r) before += nq;
+    total += nq;
+    // every rank must have laid its strings out with the same slot widths (they come from table metadata)
+    if (blockIdx.x == 0 && threadIdx.x == 0 && r == 0)
+      for (int c = 0; c < ncols && c < kXchgHeader / 4 - 1; ++c)
+        if (proto[c].kind == 2 && h[1 + c] != proto[c].maxlen) atomicExch(err, 15);
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && r == 0) *total_out = (int)total;
+  const uint8_t* seg = recv + (int64_t)r * seg_bytes;
+  const int64_t n = reinterpret_cast<const int32_t*>(seg)[0];
+  const uint8_t* body = seg + kXchgHeader;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t o = before + i;
+    for (int c = 0; c < ncols; ++c) {
+      const XCol x = proto[c];
+      const XCol d = dst[c];
+      const bool ok = body[x.off_valid + i] != 0;
+      if (ok) atomicOr(const_cast<uint32_t*>(d.valid) + (o >> 5), 1u << (o & 31));
+      if (x.kind == 0) reinterpret_cast<int32_t*>(const_cast<void*>(d.data))[o] = reinterpret_cast<const int32_t*>(body + x.off_data)[i];
+      else if (x.kind == 1) reinterpret_cast<int64_t*>(const_cast<void*>(d.data))[o] = reinterpret_cast<const int64_t*>(body + x.off_data)[i];
+      else {
+        const uint32_t len = (uint32_t) reinterpret_cast<const int32_t*>(body + x.off_data)[i];
+        const uint64_t off = (uint64_t)(body + x.off_aux + i * (int64_t)x.maxlen - recv);
+        reinterpret_cast<StrView*>(const_cast<void*>(d.data))[o] = ((uint64_t)len << 32) | (uint64_t)(uint32_t)off;
+      }
+    }
+  }
+}
+void launch_exchange_unpack_dev(const XCol* proto, const XCol* dst, int ncols, int world, int64_t cap_rows, int64_t seg_bytes,
+                                const uint8_t* recv, int* total_out, int* err, cudaStream_t s) {
+  exchange_unpack_dev_kernel<<<dim3(grid_for(std::max<int64_t>(cap_rows, 1), kThreads, 148 * 2), world), kThreads, 0, s>>>(
+      proto, dst, ncols, world, seg_bytes, recv, total_out, err);
   NDS_CUDA(cudaGetLastError());
 }
 

@@ -242,6 +242,12 @@ void launch_set_count(RowCount n, int32_t* out, cudaStream_t s);
 void launch_exchange_pack(const XCol* cols, int ncols, int64_t n, uint8_t* out, int* err, cudaStream_t s);
 void launch_exchange_unpack(const XCol* srcs, const XCol* dst, int ncols, const int64_t* row_begin, int world, int64_t max_rows,
                             const uint8_t* recv, cudaStream_t s);
+// The same with the row counts left on the device (one collective, no host round trip): fixed-capacity segments with a
+// kXchgHeader-byte header (row count, string slot widths); more rows than cap_rows raise err[2] (speculation failed).
+constexpr int kXchgHeader = 64;
+void launch_exchange_pack_dev(const XCol* cols, int ncols, RowCount n, int64_t cap_rows, uint8_t* out, int* err, cudaStream_t s);
+void launch_exchange_unpack_dev(const XCol* proto, const XCol* dst, int ncols, int world, int64_t cap_rows, int64_t seg_bytes,
+                                const uint8_t* recv, int* total_out, int* err, cudaStream_t s);
 // Small-result export: segment kinds 0 = raw bytes (multiple of 4), 1 = string column -> int32 offsets at dst_off
 // and characters at aux_off (cap bytes available; error 13 if exceeded), 2 = the row count as one int.
 struct ExportSeg {

@@ -302,15 +302,19 @@ def test_sort_topk_candidate_overflow_falls_back(gpu_engine):
     gpu_engine.drop_table('ovf')
 
 
+@pytest.mark.parametrize('single', [True, False])
 @pytest.mark.parametrize('k', [2, 3])
-def test_exchange_loopback_pack_unpack(gpu_engine, tbl, k):
+def test_exchange_loopback_pack_unpack(gpu_engine, tbl, k, single):
     """The exchange node's pack -> (all-gather) -> unpack path on one GPU: options.exchange_loopback=k stands in
     for k ranks that all hold this rank's rows, so the result is the input k times, in rank order - integers,
     decimals, strings (empty and long) and nulls included.  The filter leaves the row count on the device."""
     plan = {'op': 'exchange',
             'child': {'op': 'filter', 'cond': fn('ge', col('g'), lit(3)),
                       'child': {'op': 'scan', 'table': 't', 'columns': ['a', 'b', 's', 'd', 'g']}}}
-    got = pa.Table.from_batches([gpu_engine.execute(plan, options={'exchange_loopback': k})])
+    # single: one collective of fixed-capacity segments with the row counts in their headers (no host round trip);
+    # otherwise the counts are read back first and the segments sized exactly
+    xopts = {'exchange_loopback': k, 'exchange_single': single}
+    got = pa.Table.from_batches([gpu_engine.execute(plan, options=xopts)])
     keep = pc.fill_null(pc.greater_equal(tbl.column('g'), 3), False)
     one = tbl.filter(keep).select(['a', 'b', 's', 'd', 'g'])
     exp = pa.concat_tables([one] * k)
@@ -330,15 +334,33 @@ def test_exchange_loopback_pack_unpack(gpu_engine, tbl, k):
                      'aggs': [{'name': 'sb', 'fn': 'sum', 'expr': col('b')}, {'name': 'c', 'fn': 'count_star'}],
                      'child': plan}}
     g1 = pa.Table.from_batches([gpu_engine.execute(agg)]).to_pylist()                      # world = 1: pass-through
-    gk = pa.Table.from_batches([gpu_engine.execute(agg, options={'exchange_loopback': k})]).to_pylist()
+    gk = pa.Table.from_batches([gpu_engine.execute(agg, options=xopts)]).to_pylist()
     assert [(r['g'], r['sb'] * k, r['c'] * k) for r in g1] == [(r['g'], r['sb'], r['c']) for r in gk]
 
 
 def test_exchange_empty_input(gpu_engine, tbl):
     plan = {'op': 'exchange', 'child': {'op': 'filter', 'cond': fn('gt', col('g'), lit(1000)),
                                         'child': {'op': 'scan', 'table': 't', 'columns': ['a', 's', 'g']}}}
-    got = gpu_engine.execute(plan, options={'exchange_loopback': 2})
-    assert got.num_rows == 0 and got.schema.names == ['a', 's', 'g']
+    for single in (True, False):
+        got = gpu_engine.execute(plan, options={'exchange_loopback': 2, 'exchange_single': single})
+        assert got.num_rows == 0 and got.schema.names == ['a', 's', 'g']
+
+
+def test_exchange_beyond_the_speculative_capacity_is_retried(gpu_engine):
+    """More rows than a single-collective segment holds (128 k): the pack kernel reports it and the query runs again with
+    the counts read back - same rows."""
+    n = 200000
+    rid = np.arange(n, dtype=np.int64)
+    gpu_engine.register_arrow('big', pa.table({'rid': rid, 'v': (rid * 7 % 1000).astype(np.int32)}))
+    gpu_engine.execute({'op': 'scan', 'table': 'big', 'columns': ['rid']})
+    retries0 = gpu_engine.last_stats().get('speculation_retries', 0)
+    plan = {'op': 'aggregate', 'keys': [], 'aggs': [{'name': 'n', 'fn': 'count_star'}, {'name': 's', 'fn': 'sum', 'expr': col('rid')}],
+            'child': {'op': 'exchange', 'child': {'op': 'filter', 'cond': fn('ge', col('v'), lit(0)),
+                                                  'child': {'op': 'scan', 'table': 'big', 'columns': ['rid', 'v']}}}}
+    got = pa.Table.from_batches([gpu_engine.execute(plan, options={'exchange_loopback': 2})]).to_pylist()
+    assert got == [{'n': 2 * n, 's': 2 * int(rid.sum())}]
+    assert gpu_engine.last_stats()['speculation_retries'] == retries0 + 1
+    gpu_engine.drop_table('big')
 
 
 def test_expression_deeper_than_the_evaluator_stack_is_refused(gpu_engine, tbl):
