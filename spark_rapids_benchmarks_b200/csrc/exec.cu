@@ -263,7 +263,10 @@ struct Exec {
   int64_t small_scan_pages = 64; // options.small_scan_pages: scans with fewer split-route pages use the general kernel only
   bool speculate = true;         // options.speculate=false: never size a launch on an unverified device-side count
   bool dense_tables = true;      // options.dense_tables=false: every join table is an open-addressing hash table
-  bool exchange_single = true;   // options.exchange_single=false: the exchange reads the row counts back (two collectives)
+  // options.exchange_single=true: the exchange is one collective of fixed-capacity segments (options.exchange_rows rows,
+  // 128 k by default) with the row counts in their headers and no host round trip; by default the counts are all-gathered
+  // and read back first, so that the segments carry exactly the rows there are
+  bool exchange_single = false;
   bool topk_stream = true;       // options.topk_stream=false: ORDER BY ... LIMIT takes the multi-launch select / rank-sort route
   bool fused_scan = true;        // options.fused_scan=false: fact scans decode every column, then probe (decode_fast.cu + ops.cu)
   bool trace = false;            // options.trace: host timeline marks + time spent waiting in each stream sync
@@ -292,7 +295,7 @@ struct Exec {
       dense_tables = options->bool_or("dense_tables", true);
       fused_scan = options->bool_or("fused_scan", true);
       topk_stream = options->bool_or("topk_stream", true);
-      exchange_single = options->bool_or("exchange_single", true);
+      exchange_single = options->bool_or("exchange_single", false);
     }
     t_base = now_ms();
     if (!e.side_streams_.empty() && side_stream) {
@@ -1884,7 +1887,7 @@ struct Exec {
     // header holds its row count; the unpack kernel reads the headers on the device.  More rows than the capacity raise
     // err[2] and the query runs again on the exact two-step route below.
     constexpr int64_t kXchgSpecRows = int64_t(128) << 10;
-    if (speculate && exchange_single && ncols <= kXchgHeader / 4 - 1) {
+    if (speculate && exchange_single && ncols <= kXchgHeader / 4 - 2) {
       std::vector<XCol> proto(ncols);
       bool ok_types = true;
       for (int c = 0; c < ncols; ++c) {
@@ -1895,7 +1898,8 @@ struct Exec {
         x.maxlen = t.kind == LType::STR ? t.maxlen : 0;
         if (t.kind == LType::STR && t.maxlen <= 0) ok_types = false;
       }
-      const int64_t cap_rows = std::max<int64_t>(std::min<int64_t>(in.rc().host, kXchgSpecRows), 1);
+      // (the capacity must be the same on every rank: nothing rank-local - like this rank's row bound - may enter it)
+      const int64_t cap_rows = opts ? std::max<int64_t>(opts->int_or("exchange_rows", kXchgSpecRows), 1) : kXchgSpecRows;
       SegLayout L = seg_layout(proto, cap_rows);
       const int64_t seg_bytes = kXchgHeader + L.bytes;
       if (ok_types && seg_bytes * world < (int64_t(1) << 32)) {
@@ -1945,17 +1949,19 @@ struct Exec {
       }
     }
     // ---- counts (and string slot widths: the widest any rank declares) travel first
-    std::vector<int32_t> meta(1 + ncols, 0);
+    std::vector<int32_t> meta(2 + ncols, 0);
     for (int c = 0; c < ncols; ++c) {
       const LType& t = flat[c].lt;
       if (t.kind == LType::STR && t.maxlen <= 0) fail("plan: exchange of string column '" + flat[c].name + "' without a known maximum length");
       meta[1 + c] = t.kind == LType::STR ? t.maxlen : 0;
     }
-    const int mlen = 1 + ncols;
+    // the last word carries this rank's "a device-side size assumption failed" flag (err[2]): a rank that has to run the
+    // query again must take every other rank with it, or the collectives of the second attempt would have no partners
+    const int mlen = 2 + ncols;
     int32_t* d_meta = ar.alloc_n<int32_t>(mlen);
     int32_t* d_all = ar.alloc_n<int32_t>((int64_t)mlen * world);
     ar.upload(d_meta, meta.data(), mlen * 4);
-    launch_set_count(in.rc(), d_meta, s);
+    launch_set_count(in.rc(), d_meta, s, err + 2, d_meta + 1 + ncols);
     ++launches;
     if (loop > 0) {
       for (int r = 0; r < world; ++r)
@@ -1969,6 +1975,8 @@ struct Exec {
     NDS_CUDA(cudaMemcpyAsync(hall, d_all, all.size() * 4, cudaMemcpyDeviceToHost, s));
     sync("sync:exchange_counts");
     d2h += (int64_t)all.size() * 4;
+    for (int r = 0; r < world; ++r)
+      if (hall[(int64_t)r * mlen + 1 + ncols]) throw SpeculationFailed();
     std::vector<int64_t> row_begin(world + 1, 0);
     int64_t max_rows = 0;
     std::vector<XCol> proto(ncols);

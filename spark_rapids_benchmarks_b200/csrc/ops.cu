@@ -1325,9 +1325,13 @@ void launch_take_perm(const uint32_t* perm_a, const uint32_t* perm_b, const int*
 // lengths as the values and their bytes in fixed slots of the column's maximum length (no prefix sum, no second size
 // exchange - NVLink has the bandwidth to spare).  XCol::off_* are byte offsets inside the segment; they depend on
 // the row count only, so every rank can lay out every other rank's segment once the counts are known.
-__global__ void set_count_kernel(const int* n_dev, int64_t n_host, int32_t* out) { out[0] = (int32_t)row_count(n_dev, n_host); }
-void launch_set_count(RowCount n, int32_t* out, cudaStream_t s) {
-  set_count_kernel<<<1, 1, 0, s>>>(n.dev, n.host, out);
+// flag_out (optional) receives *flag_in != 0: this rank's "a device-side size assumption failed" state travels with the count
+__global__ void set_count_kernel(const int* n_dev, int64_t n_host, int32_t* out, const int* flag_in, int32_t* flag_out) {
+  out[0] = (int32_t)row_count(n_dev, n_host);
+  if (flag_out) flag_out[0] = (flag_in && *flag_in) ? 1 : 0;
+}
+void launch_set_count(RowCount n, int32_t* out, cudaStream_t s, const int* flag_in, int32_t* flag_out) {
+  set_count_kernel<<<1, 1, 0, s>>>(n.dev, n.host, out, flag_in, flag_out);
   NDS_CUDA(cudaGetLastError());
 }
 
@@ -1397,14 +1401,13 @@ __global__ void __launch_bounds__(kThreads)
 exchange_pack_dev_kernel(const XCol* __restrict__ cols, int ncols, const int* n_dev, int64_t n_host, int64_t cap_rows,
                          uint8_t* __restrict__ out, int* err) {
   int64_t n = row_count(n_dev, n_host);
-  if (n > cap_rows) {            // more rows than the speculative capacity: the query runs again with exact sizes
-    if (blockIdx.x == 0 && threadIdx.x == 0) atomicExch(err + 2, 1);
-    n = cap_rows;
-  }
+  const bool over = n > cap_rows;   // more rows than the speculative capacity: the query runs again with exact sizes
+  if (over) n = cap_rows;
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     int32_t* h = reinterpret_cast<int32_t*>(out);
     h[0] = (int32_t)n;
-    for (int c = 0; c < ncols && c < kXchgHeader / 4 - 1; ++c) h[1 + c] = cols[c].kind == 2 ? cols[c].maxlen : 0;
+    for (int c = 0; c < ncols && c < kXchgHeader / 4 - 2; ++c) h[1 + c] = cols[c].kind == 2 ? cols[c].maxlen : 0;
+    h[kXchgHeader / 4 - 1] = (err[2] || over) ? 1 : 0;      // a failed size assumption on ANY rank must make EVERY rank run the query again
   }
   uint8_t* body = out + kXchgHeader;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
@@ -1445,8 +1448,9 @@ exchange_unpack_dev_kernel(const XCol* __restrict__ proto, const XCol* __restric
     total += nq;
     // every rank must have laid its strings out with the same slot widths (they come from table metadata)
     if (blockIdx.x == 0 && threadIdx.x == 0 && r == 0)
-      for (int c = 0; c < ncols && c < kXchgHeader / 4 - 1; ++c)
+      for (int c = 0; c < ncols && c < kXchgHeader / 4 - 2; ++c)
         if (proto[c].kind == 2 && h[1 + c] != proto[c].maxlen) atomicExch(err, 15);
+    if (blockIdx.x == 0 && threadIdx.x == 0 && r == 0 && h[kXchgHeader / 4 - 1]) atomicExch(err + 2, 1);
   }
   if (blockIdx.x == 0 && threadIdx.x == 0 && r == 0) *total_out = (int)total;
   const uint8_t* seg = recv + (int64_t)r * seg_bytes;

@@ -238,7 +238,7 @@ struct XCol {
   int64_t off_valid, off_data, off_aux;
   int32_t kind, maxlen;
 };
-void launch_set_count(RowCount n, int32_t* out, cudaStream_t s);
+void launch_set_count(RowCount n, int32_t* out, cudaStream_t s, const int* flag_in = nullptr, int32_t* flag_out = nullptr);
 void launch_exchange_pack(const XCol* cols, int ncols, int64_t n, uint8_t* out, int* err, cudaStream_t s);
 void launch_exchange_unpack(const XCol* srcs, const XCol* dst, int ncols, const int64_t* row_begin, int world, int64_t max_rows,
                             const uint8_t* recv, cudaStream_t s);

@@ -38,6 +38,14 @@ def main():
                         else:
                             assert g[k] == e[k], (query, k, g[k], e[k])
         ok += 1
+    # the one-collective form of the exchange (fixed-capacity segments, row counts in their headers, no host round trip)
+    # gives the same rows as the default two-step form
+    import pyarrow as pa
+    for query in ('query3', 'query7'):
+        plan = sess.plan(streams.render(query, overrides={'MANUFACT': 606, 'MANAGER': 63, 'MONTH': 1, 'YEAR': 1998}))
+        two = pa.Table.from_batches([sess.engine.execute({'root': plan['fused']})]).to_pylist()
+        one = pa.Table.from_batches([sess.engine.execute({'root': plan['fused']}, options={'exchange_single': True})]).to_pylist()
+        assert one == two and len(one) > 0, query
     # schemas must not depend on the GPU count: sum(decimal(7,2)) stays decimal(17,2) through the merge
     sess.source = 'hbm'
     t3 = sess.sql(streams.render('query3', overrides={'MANUFACT': 606, 'MONTH': 1})).toArrow()

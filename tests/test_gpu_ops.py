@@ -357,7 +357,7 @@ def test_exchange_beyond_the_speculative_capacity_is_retried(gpu_engine):
     plan = {'op': 'aggregate', 'keys': [], 'aggs': [{'name': 'n', 'fn': 'count_star'}, {'name': 's', 'fn': 'sum', 'expr': col('rid')}],
             'child': {'op': 'exchange', 'child': {'op': 'filter', 'cond': fn('ge', col('v'), lit(0)),
                                                   'child': {'op': 'scan', 'table': 'big', 'columns': ['rid', 'v']}}}}
-    got = pa.Table.from_batches([gpu_engine.execute(plan, options={'exchange_loopback': 2})]).to_pylist()
+    got = pa.Table.from_batches([gpu_engine.execute(plan, options={'exchange_loopback': 2, 'exchange_single': True})]).to_pylist()
     assert got == [{'n': 2 * n, 's': 2 * int(rid.sum())}]
     assert gpu_engine.last_stats()['speculation_retries'] == retries0 + 1
     gpu_engine.drop_table('big')

@@ -194,9 +194,20 @@ def test_exchange_over_nccl_two_gpus(warehouse, tmp_path):
         pytest.skip('needs two GPUs')
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     env = dict(os.environ, NDS_TEST_WAREHOUSE=warehouse)
-    r = subprocess.run([sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2', '--master-addr', '127.0.0.1',
-                        '--master-port', '29533', os.path.join(root, 'tests', 'nccl_exchange_worker.py')],
-                       cwd=root, env=env, capture_output=True, text=True, timeout=600)
+    # own process group, killed as a whole on a timeout: a worker left behind in a collective would keep both GPUs busy
+    import signal
+    p = subprocess.Popen([sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2', '--master-addr', '127.0.0.1',
+                          '--master-port', '29533', os.path.join(root, 'tests', 'nccl_exchange_worker.py')],
+                         cwd=root, env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, start_new_session=True)
+    try:
+        out, errs = p.communicate(timeout=300)
+    except subprocess.TimeoutExpired:
+        os.killpg(p.pid, signal.SIGKILL)
+        out, errs = p.communicate()
+        raise AssertionError('the two-GPU exchange run did not finish in 300 s\n' + out[-2000:] + errs[-3000:])
+
+    class r:
+        returncode, stdout, stderr = p.returncode, out, errs
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert 'EXCHANGE-OK 6' in r.stdout
 
