@@ -1097,14 +1097,21 @@ struct Exec {
     Batch build;
     HashTable ht;
     std::string pk, bk;
+    bool multi = false;          // repeated build keys are chained (HashTable::next)
   };
 
   // Executes the build child of a join node, builds its hash table and, for a partition-pruning join, turns the build
   // keys into a runtime filter for the scan below.
   BuiltSide build_side(const Json& node, std::vector<RuntimeFilter>& down) {
     const std::string type = node.str_or("type", "inner");
-    if (type != "inner") fail("plan: join type '" + type + "' is not supported yet");
+    if (type != "inner" && type != "semi" && type != "anti" && type != "left")
+      fail("plan: join type '" + type + "' is not supported (inner, left, semi, anti)");
+    // semi / anti joins only ask whether a key exists: repeated build keys are fine.  inner / left joins over a build side
+    // that is not declared unique chain the repeated keys (multi table) and expand the probe rows.
+    const bool existence = type == "semi" || type == "anti";
+    const bool multi = !existence && !node.bool_or("unique_build", true);
     BuiltSide bs;
+    bs.multi = multi;
     std::vector<RuntimeFilter> none;
     bs.build = exec(node.at("build"), none);
     Batch& build = bs.build;
@@ -1128,7 +1135,8 @@ struct Exec {
         ht.dense = ar.zeros<uint32_t>(range);
         ht.lo = kc.range_lo;
         ht.range = (uint32_t)range;
-        launch_join_build(kc.ref(), build.rc(), ht, err + 1, s);
+        if (multi) ht.next = ar.alloc_n<uint32_t>(std::max<int64_t>(nb_bound, 1));
+        launch_join_build(kc.ref(), build.rc(), ht, err + 1, s, existence);
         ++launches;
         end_stat(stb, nb * 8 + range * 4, nb);
         return;
@@ -1136,9 +1144,10 @@ struct Exec {
       uint32_t cap = next_pow2(2 * nb);
       ht.mask = cap - 1;
       ht.keys = ar.alloc_n<int64_t>(cap);
-      ht.vals = ar.alloc_n<uint32_t>(cap);
+      ht.vals = multi ? ar.zeros<uint32_t>(cap) : ar.alloc_n<uint32_t>(cap);
+      if (multi) ht.next = ar.alloc_n<uint32_t>(std::max<int64_t>(nb_bound, 1));
       launch_fill_i64(ht.keys, kEmptyKey, cap, s);
-      launch_join_build(kc.ref(), build.rc(), ht, err + 1, s);
+      launch_join_build(kc.ref(), build.rc(), ht, err + 1, s, existence);
       launches += 2;
       end_stat(stb, nb * 8 + (int64_t)cap * 12, nb);
     };
@@ -1573,7 +1582,7 @@ struct Exec {
       std::set<std::string> base_cols;
       plan_columns(base_node, base_cols);
       for (const Json* j : chain)
-        if (!base_cols.count(j->str("probe_key")) || j->str_or("type", "inner") != "inner") fuse = false;
+        if (!base_cols.count(j->str("probe_key")) || j->str_or("type", "inner") != "inner" || !j->bool_or("unique_build", true)) fuse = false;
     }
     if (!fuse) {
       std::vector<RuntimeFilter> down = filters;
@@ -1584,27 +1593,52 @@ struct Exec {
       if (!is_intlike(probe.cols[kp].lt)) fail("plan: join keys must be integer columns");
       size_t stp = begin_stat("join_probe");
       RowCount np = probe.rc();
-      uint32_t* out_p = ar.alloc_n<uint32_t>(np.host);
-      uint32_t* out_b = ar.alloc_n<uint32_t>(np.host);
-      int* cnt = ar.zeros<int>(1);
-      launch_join_probe(probe.cols[kp].ref(), np, bs.ht, out_p, out_b, cnt, s);
-      ++launches;
+      const std::string jtype = node.str_or("type", "inner");
+      const int kind = jtype == "semi" ? JOIN_SEMI : (jtype == "anti" ? JOIN_ANTI : (jtype == "left" ? JOIN_LEFT : JOIN_INNER));
+      const bool with_build = kind == JOIN_INNER || kind == JOIN_LEFT;
+      uint32_t* out_p = nullptr;
+      uint32_t* out_b = nullptr;
       Batch out;
-      out.n_max = np.host;
-      out.n_dev = cnt;
-      RowCount nout{cnt, np.host};
+      if (bs.multi) {
+        // repeated build keys: count the output rows first (one read-back), then write them
+        unsigned long long* tot = ar.zeros<unsigned long long>(2);
+        launch_join_probe_multi_count(probe.cols[kp].ref(), np, bs.ht, kind, tot, s);
+        ++launches;
+        unsigned long long h_tot = 0;
+        NDS_CUDA(cudaMemcpyAsync(&h_tot, tot, 8, cudaMemcpyDeviceToHost, s));
+        sync("sync:join_multi_count");
+        d2h += 8;
+        if (h_tot >= (1ull << 31)) fail("hash join: 2^31 or more output rows; shard the tables across GPUs");
+        const int64_t total = (int64_t)h_tot;
+        out_p = ar.alloc_n<uint32_t>(std::max<int64_t>(total, 1));
+        out_b = ar.alloc_n<uint32_t>(std::max<int64_t>(total, 1));
+        launch_join_probe_multi_write(probe.cols[kp].ref(), np, bs.ht, kind, out_p, out_b, tot + 1, s);
+        ++launches;
+        out.n_max = total;
+        out.n_exact = total;
+      } else {
+        out_p = ar.alloc_n<uint32_t>(np.host);
+        out_b = with_build ? ar.alloc_n<uint32_t>(np.host) : nullptr;
+        int* cnt = ar.zeros<int>(1);
+        launch_join_probe(probe.cols[kp].ref(), np, bs.ht, out_p, out_b, cnt, s, kind);
+        ++launches;
+        out.n_max = np.host;
+        out.n_dev = cnt;
+      }
+      RowCount nout = out.rc();
       MapCache mp, mb;
       for (const Column& c : probe.cols) {
         Column o = c;
         o.rowmap = remap(c.rowmap, out_p, nout, mp);
         out.cols.push_back(o);
       }
-      for (const Column& c : bs.build.cols) {
-        if (out.find(c.name) >= 0) continue;
-        Column o = c;
-        o.rowmap = remap(c.rowmap, out_b, nout, mb);
-        out.cols.push_back(o);
-      }
+      if (with_build)
+        for (const Column& c : bs.build.cols) {
+          if (out.find(c.name) >= 0) continue;
+          Column o = c;
+          o.rowmap = remap(c.rowmap, out_b, nout, mb);
+          out.cols.push_back(o);
+        }
       end_stat(stp, np.host * (probe.cols[kp].lt.dtype() == DT_I32 ? 4 : 8), np.host);
       return out;
     }

@@ -40,6 +40,7 @@ struct Val {
 };
 
 constexpr int kEvalStack = 16;
+constexpr uint32_t kNoRow = 0xFFFFFFFFu;      // row-map entry of an outer join's unmatched row: every column it maps reads NULL
 
 __device__ __forceinline__ int str_cmp(const uint8_t* a, uint32_t la, const uint8_t* b, uint32_t lb) {
   uint32_t m = la < lb ? la : lb;
@@ -53,9 +54,10 @@ __device__ __forceinline__ int str_cmp(const uint8_t* a, uint32_t la, const uint
 __device__ __forceinline__ Val load_col(const ColRef& c, int64_t row) {
   Val r;
   int64_t b = c.rowmap ? (int64_t)c.rowmap[row] : row;
-  r.ok = !c.valid || ((c.valid[b >> 5] >> (b & 31)) & 1u);
   r.len = 0;
   r.v = 0;
+  if (b == (int64_t)kNoRow) { r.ok = false; return r; }       // the unmatched side of an outer join
+  r.ok = !c.valid || ((c.valid[b >> 5] >> (b & 31)) & 1u);
   if (c.dtype == DT_I32) r.v = reinterpret_cast<const int32_t*>(c.data)[b];
   else if (c.dtype == DT_STR) {
     StrView s = reinterpret_cast<const StrView*>(c.data)[b];

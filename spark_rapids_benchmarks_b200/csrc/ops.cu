@@ -143,7 +143,10 @@ __global__ void compose_kernel(const uint32_t* __restrict__ inner, const uint32_
                                int64_t n_host, uint32_t* __restrict__ out) {
   const int64_t n = row_count(n_dev, n_host);
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    out[i] = inner[idx[i]];
+  {
+    const uint32_t j = idx[i];
+    out[i] = j == kNoRow ? kNoRow : inner[j];      // an outer join's unmatched row stays unmatched through every composition
+  }
 }
 void launch_compose(const uint32_t* inner, const uint32_t* idx, RowCount n, uint32_t* out, cudaStream_t s) {
   compose_kernel<<<grid_for(n.host), kThreads, 0, s>>>(inner, idx, n.dev, n.host, out);
@@ -163,7 +166,7 @@ void launch_fill_i64(int64_t* p, int64_t v, int64_t n, cudaStream_t s) {
 // Open addressing, linear probing, 64-bit keys + 32-bit payload (the build-side batch row).
 // Build keys must be unique (FK -> PK joins); a duplicate raises flag bit 0.
 __global__ void __launch_bounds__(kThreads)
-join_build_kernel(ColRef key, const int* n_dev, int64_t n_host, HashTable ht, int* flags) {
+join_build_kernel(ColRef key, const int* n_dev, int64_t n_host, HashTable ht, int* flags, int allow_dup) {
   const int64_t n = row_count(n_dev, n_host);
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     Val k = load_col(key, i);
@@ -171,7 +174,8 @@ join_build_kernel(ColRef key, const int* n_dev, int64_t n_host, HashTable ht, in
     if (ht.dense) {
       const uint64_t d = (uint64_t)(k.v - ht.lo);
       if (d >= (uint64_t)ht.range) { atomicOr(flags, 4); continue; }      // outside the range the column statistics promised
-      if (atomicCAS(&ht.dense[d], 0u, (uint32_t)i + 1u) != 0u) atomicOr(flags, 1);
+      if (ht.next) ht.next[i] = atomicExch(&ht.dense[d], (uint32_t)i + 1u);   // push onto the key's chain
+      else if (atomicCAS(&ht.dense[d], 0u, (uint32_t)i + 1u) != 0u && !allow_dup) atomicOr(flags, 1);
       continue;
     }
     if (k.v == kEmptyKey) { atomicOr(flags, 2); continue; }
@@ -179,8 +183,12 @@ join_build_kernel(ColRef key, const int* n_dev, int64_t n_host, HashTable ht, in
     for (;;) {
       unsigned long long prev = atomicCAS(reinterpret_cast<unsigned long long*>(&ht.keys[s]),
                                           (unsigned long long)kEmptyKey, (unsigned long long)k.v);
-      if ((int64_t)prev == kEmptyKey) { ht.vals[s] = (uint32_t)i; break; }
-      if ((int64_t)prev == k.v) { atomicOr(flags, 1); break; }
+      if (ht.next) {
+        if ((int64_t)prev == kEmptyKey || (int64_t)prev == k.v) { ht.next[i] = atomicExch(&ht.vals[s], (uint32_t)i + 1u); break; }
+      } else {
+        if ((int64_t)prev == kEmptyKey) { ht.vals[s] = (uint32_t)i; break; }
+        if ((int64_t)prev == k.v) { if (!allow_dup) atomicOr(flags, 1); break; }
+      }
       s = (s + 1) & ht.mask;
     }
   }
@@ -205,7 +213,7 @@ void launch_keys_to_bitmap(ColRef key, RowCount n, int64_t lo, int64_t hi, uint3
 
 __global__ void __launch_bounds__(kThreads)
 join_probe_kernel(ColRef key, const int* n_dev, int64_t n_host, HashTable ht, uint32_t* __restrict__ out_probe,
-                  uint32_t* __restrict__ out_build, int* out_count) {
+                  uint32_t* __restrict__ out_build, int* out_count, int kind) {
   const int64_t n = row_count(n_dev, n_host);
   const int64_t nround = (n + 31) & ~int64_t(31);
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nround; i += (int64_t)gridDim.x * blockDim.x) {
@@ -215,8 +223,14 @@ join_probe_kernel(ColRef key, const int* n_dev, int64_t n_host, HashTable ht, ui
       Val k = load_col(key, i);
       if (k.ok) hit = ht_find(ht, k.v, b);
     }
-    int pos = warp_append(hit, out_count);
-    if (hit) { out_probe[pos] = (uint32_t)i; out_build[pos] = b; }
+    // inner / semi keep the matching rows, anti the others (a NULL key matches nothing), left keeps every row
+    const bool keep = i < n && (kind == JOIN_LEFT || (kind == JOIN_ANTI ? !hit : hit));
+    int pos = warp_append(keep, out_count);
+    if (keep) {
+      out_probe[pos] = (uint32_t)i;
+      if (kind == JOIN_INNER) out_build[pos] = b;
+      else if (kind == JOIN_LEFT) out_build[pos] = hit ? b : kNoRow;
+    }
   }
 }
 
@@ -252,13 +266,54 @@ void launch_join_probe_chain(const ProbeChain& chain, RowCount n, uint32_t* out_
   NDS_CUDA(cudaGetLastError());
 }
 
-void launch_join_build(ColRef key, RowCount n, HashTable ht, int* flags, cudaStream_t s) {
-  join_build_kernel<<<grid_for(n.host), kThreads, 0, s>>>(key, n.dev, n.host, ht, flags);
+void launch_join_build(ColRef key, RowCount n, HashTable ht, int* flags, cudaStream_t s, bool allow_dup) {
+  join_build_kernel<<<grid_for(n.host), kThreads, 0, s>>>(key, n.dev, n.host, ht, flags, allow_dup ? 1 : 0);
   NDS_CUDA(cudaGetLastError());
 }
 void launch_join_probe(ColRef key, RowCount n, HashTable ht, uint32_t* out_probe, uint32_t* out_build, int* out_count,
-                       cudaStream_t s) {
-  join_probe_kernel<<<grid_for(n.host), kThreads, 0, s>>>(key, n.dev, n.host, ht, out_probe, out_build, out_count);
+                       cudaStream_t s, int kind) {
+  join_probe_kernel<<<grid_for(n.host), kThreads, 0, s>>>(key, n.dev, n.host, ht, out_probe, out_build, out_count, kind);
+  NDS_CUDA(cudaGetLastError());
+}
+
+// Repeated build keys: a probe row has as many output rows as its key's chain is long (left: at least one).
+__global__ void __launch_bounds__(kThreads)
+join_probe_multi_count_kernel(ColRef key, const int* n_dev, int64_t n_host, HashTable ht, int kind, unsigned long long* out_total) {
+  const int64_t n = row_count(n_dev, n_host);
+  unsigned long long mine = 0;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    Val k = load_col(key, i);
+    uint32_t c = 0;
+    if (k.ok)
+      for (uint32_t l = ht_first(ht, k.v); l; l = ht_next(ht, l)) ++c;
+    mine += (c == 0 && kind == JOIN_LEFT) ? 1u : c;
+  }
+  for (int d = 16; d; d >>= 1) mine += __shfl_xor_sync(0xFFFFFFFFu, mine, d);
+  if ((threadIdx.x & 31) == 0 && mine) atomicAdd(out_total, mine);
+}
+__global__ void __launch_bounds__(kThreads)
+join_probe_multi_write_kernel(ColRef key, const int* n_dev, int64_t n_host, HashTable ht, int kind, uint32_t* __restrict__ out_probe,
+                              uint32_t* __restrict__ out_build, unsigned long long* cursor) {
+  const int64_t n = row_count(n_dev, n_host);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    Val k = load_col(key, i);
+    uint32_t c = 0;
+    if (k.ok)
+      for (uint32_t l = ht_first(ht, k.v); l; l = ht_next(ht, l)) ++c;
+    const uint32_t rows = (c == 0 && kind == JOIN_LEFT) ? 1u : c;
+    if (!rows) continue;
+    unsigned long long pos = atomicAdd(cursor, (unsigned long long)rows);
+    if (c == 0) { out_probe[pos] = (uint32_t)i; out_build[pos] = kNoRow; continue; }
+    for (uint32_t l = ht_first(ht, k.v); l; l = ht_next(ht, l), ++pos) { out_probe[pos] = (uint32_t)i; out_build[pos] = l - 1u; }
+  }
+}
+void launch_join_probe_multi_count(ColRef key, RowCount n, HashTable ht, int kind, unsigned long long* out_total, cudaStream_t s) {
+  join_probe_multi_count_kernel<<<grid_for(n.host), kThreads, 0, s>>>(key, n.dev, n.host, ht, kind, out_total);
+  NDS_CUDA(cudaGetLastError());
+}
+void launch_join_probe_multi_write(ColRef key, RowCount n, HashTable ht, int kind, uint32_t* out_probe, uint32_t* out_build,
+                                   unsigned long long* cursor, cudaStream_t s) {
+  join_probe_multi_write_kernel<<<grid_for(n.host), kThreads, 0, s>>>(key, n.dev, n.host, ht, kind, out_probe, out_build, cursor);
   NDS_CUDA(cudaGetLastError());
 }
 

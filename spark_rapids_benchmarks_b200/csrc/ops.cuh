@@ -30,6 +30,8 @@ constexpr int64_t kEmptyKey = INT64_MIN;
 //  * direct addressing (dense != nullptr): the keys are known to lie in [lo, lo + range) - the Parquet statistics of a
 //    surrogate-key column - and dense[key - lo] holds build row + 1 (0: no such key).  One 4-byte load per probe and
 //    no hashing: the perfect-hash special case every NDS dimension key falls into.
+// multi (next != nullptr): build keys may repeat; the slot holds the head of a chain through next[] (entries are
+// build row + 1, 0 ends the chain) and a probe walks it (ht_first / ht_next).
 struct HashTable {
   int64_t* keys = nullptr;
   uint32_t* vals = nullptr;
@@ -37,6 +39,7 @@ struct HashTable {
   uint32_t range = 0;
   uint32_t* dense = nullptr;
   int64_t lo = 0;
+  uint32_t* next = nullptr;
 };
 
 #ifdef __CUDACC__
@@ -53,11 +56,17 @@ __device__ __forceinline__ bool ht_find(const HashTable& ht, int64_t key, uint32
   uint32_t s = (uint32_t)mix64((uint64_t)key) & ht.mask;
   for (;;) {
     const int64_t cur = ht.keys[s];
-    if (cur == key) { row = ht.vals[s]; return true; }
+    if (cur == key) { row = ht.next ? ht.vals[s] - 1u : ht.vals[s]; return true; }
     if (cur == kEmptyKey) return false;
     s = (s + 1) & ht.mask;
   }
 }
+// multi tables: first match of `key` as a chain link (build row + 1, 0 = none); ht_next follows the chain
+__device__ __forceinline__ uint32_t ht_first(const HashTable& ht, int64_t key) {
+  uint32_t row;
+  return ht_find(ht, key, row) ? row + 1u : 0u;
+}
+__device__ __forceinline__ uint32_t ht_next(const HashTable& ht, uint32_t link) { return ht.next[link - 1u]; }
 #endif
 
 // AGG_COUNT_REF: count(x) where another aggregate over the same x already counts the non-null rows (AVG = SUM + COUNT):
@@ -102,11 +111,19 @@ struct ProjSpec {        // one output column of a multi-column projection
 void launch_project_multi(const ProjSpec* specs, int nspecs, OpCtx c, RowCount n, const uint32_t* rows, int* err, cudaStream_t s);
 void launch_compose(const uint32_t* inner, const uint32_t* idx, RowCount n, uint32_t* out, cudaStream_t s);
 void launch_fill_i64(int64_t* p, int64_t v, int64_t n, cudaStream_t s);
-void launch_join_build(ColRef key, RowCount n, HashTable ht, int* flags, cudaStream_t s);
+// allow_dup: repeated build keys are not an error (semi / anti joins only ask whether a key exists; multi tables chain them)
+void launch_join_build(ColRef key, RowCount n, HashTable ht, int* flags, cudaStream_t s, bool allow_dup = false);
 // bits: ceil((hi - lo + 1) / 32) pre-zeroed words; bit (k - lo) is set for every non-null build key k in [lo, hi]
 void launch_keys_to_bitmap(ColRef key, RowCount n, int64_t lo, int64_t hi, uint32_t* bits, cudaStream_t s);
+enum JoinKind : int { JOIN_INNER = 0, JOIN_SEMI = 1, JOIN_ANTI = 2, JOIN_LEFT = 3 };
+// inner: matching probe rows + their build row; semi / anti: probe rows with / without a match (out_build unused);
+// left: every probe row, out_build = the build row or kNoRow.  Unique-key tables.
 void launch_join_probe(ColRef key, RowCount n, HashTable ht, uint32_t* out_probe, uint32_t* out_build, int* out_count,
-                       cudaStream_t s);
+                       cudaStream_t s, int kind = JOIN_INNER);
+// multi tables (repeated build keys), inner / left: pass 1 counts the output rows, pass 2 writes them (any order)
+void launch_join_probe_multi_count(ColRef key, RowCount n, HashTable ht, int kind, unsigned long long* out_total, cudaStream_t s);
+void launch_join_probe_multi_write(ColRef key, RowCount n, HashTable ht, int kind, uint32_t* out_probe, uint32_t* out_build,
+                                   unsigned long long* cursor, cudaStream_t s);
 constexpr int kMaxChain = 8;
 struct ProbeChain {            // a left-deep chain of inner hash joins probed in one pass over the base rows
   ColRef key[kMaxChain];

@@ -453,3 +453,79 @@ def test_group_by_with_few_groups_per_warp(gpu_engine):
     assert got['c'].to_pylist() == exp['v_count'].to_pylist()
     assert got['n'].to_pylist() == exp['count_all'].to_pylist()
     gpu_engine.drop_table('fg')
+
+
+def _join_tables(seed=17, n=6000, nd=400, dup=False):
+    rng = np.random.default_rng(seed)
+    keys = rng.integers(50, 50 + nd // (3 if dup else 1), nd).astype(np.int32) if dup else np.arange(50, 50 + nd, dtype=np.int32)
+    dim = pa.table({'k': pa.array(keys, mask=rng.random(nd) < (0.03 if dup else 0.0)),
+                    'name': pa.array(['n%03d' % (i % 41) for i in range(nd)]),
+                    'w': pa.array(rng.integers(0, 1000, nd)), 'brow': pa.array(np.arange(nd, dtype=np.int64))})
+    fact = pa.table({'fk': pa.array(rng.integers(0, 700, n).astype(np.int32), mask=rng.random(n) < 0.05),
+                     'v': pa.array(rng.integers(0, 10**6, n)), 'rid': pa.array(np.arange(n, dtype=np.int64))})
+    return dim, fact
+
+
+@pytest.mark.parametrize('jtype,pa_type', [('semi', 'left semi'), ('anti', 'left anti'), ('left', 'left outer')])
+@pytest.mark.parametrize('dense', [True, False])
+def test_join_semi_anti_left(gpu_engine, jtype, pa_type, dense):
+    """Left semi / anti / outer joins against pyarrow: NULL probe keys match nothing (semi drops them, anti and outer keep
+    them), the unmatched side of an outer join reads NULL in every build column - also through a later filter + sort."""
+    dim, fact = _join_tables()
+    gpu_engine.register_arrow('jd', dim)
+    gpu_engine.register_arrow('jf', fact)
+    build = {'op': 'filter', 'cond': fn('lt', col('w'), lit(600)), 'child': {'op': 'scan', 'table': 'jd', 'columns': ['k', 'name', 'w', 'brow']}}
+    plan = {'op': 'sort', 'keys': [{'expr': col('rid')}],
+            'child': {'op': 'join', 'type': jtype, 'probe': {'op': 'scan', 'table': 'jf', 'columns': ['fk', 'v', 'rid']}, 'build': build,
+                      'probe_key': 'fk', 'build_key': 'k'}}
+    got = pa.Table.from_batches([gpu_engine.execute(plan, options={'dense_tables': dense})])
+    d2 = dim.filter(pc.less(dim['w'], 600))
+    exp = fact.join(d2, keys='fk', right_keys='k', join_type=pa_type).sort_by('rid')
+    assert got.num_rows == exp.num_rows
+    cols = ['fk', 'v', 'rid'] + (['name', 'w', 'brow'] if jtype == 'left' else [])
+    assert got.schema.names == cols
+    for c in cols:
+        assert got[c].to_pylist() == exp[c].to_pylist(), c
+    if jtype == 'left':
+        # a predicate over the NULL-extended side and an aggregate above the outer join
+        plan2 = {'op': 'aggregate', 'keys': [], 'aggs': [{'name': 'n', 'fn': 'count_star'}, {'name': 'cw', 'fn': 'count', 'expr': col('w')},
+                                                          {'name': 'sw', 'fn': 'sum', 'expr': col('w')}],
+                 'child': {'op': 'filter', 'cond': fn('or', fn('isnull', col('name')), fn('gt', col('w'), lit(300))), 'child': plan['child']}}
+        got2 = pa.Table.from_batches([gpu_engine.execute(plan2, options={'dense_tables': dense})]).to_pylist()
+        keep = pc.fill_null(pc.or_kleene(pc.is_null(exp['name']), pc.greater(exp['w'], 300)), False)
+        e2 = exp.filter(keep)
+        assert got2 == [{'n': e2.num_rows, 'cw': pc.count(e2['w']).as_py(), 'sw': pc.sum(e2['w']).as_py()}]
+    gpu_engine.drop_table('jd')
+    gpu_engine.drop_table('jf')
+
+
+@pytest.mark.parametrize('jtype,pa_type', [('inner', 'inner'), ('left', 'left outer'), ('semi', 'left semi'), ('anti', 'left anti')])
+@pytest.mark.parametrize('dense', [True, False])
+def test_join_repeated_build_keys(gpu_engine, jtype, pa_type, dense):
+    """Build keys that repeat (and NULL build keys): inner / left joins expand every probe row by its matches
+    (unique_build=false -> chained table, count pass + write pass), semi / anti joins only ask for existence."""
+    dim, fact = _join_tables(seed=23, dup=True)
+    gpu_engine.register_arrow('jd', dim)
+    gpu_engine.register_arrow('jf', fact)
+    node = {'op': 'join', 'type': jtype, 'probe': {'op': 'scan', 'table': 'jf', 'columns': ['fk', 'v', 'rid']},
+            'build': {'op': 'scan', 'table': 'jd', 'columns': ['k', 'w', 'brow']}, 'probe_key': 'fk', 'build_key': 'k'}
+    if jtype in ('inner', 'left'):
+        node['unique_build'] = False
+    with_build = jtype in ('inner', 'left')
+    keys = [{'expr': col('rid')}] + ([{'expr': col('brow')}] if with_build else [])
+    got = pa.Table.from_batches([gpu_engine.execute({'op': 'sort', 'keys': keys, 'child': node}, options={'dense_tables': dense})])
+    exp = fact.join(dim.filter(pc.is_valid(dim['k'])), keys='fk', right_keys='k', join_type=pa_type)
+    exp = exp.sort_by([('rid', 'ascending')] + ([('brow', 'ascending')] if with_build else []))
+    assert got.num_rows == exp.num_rows and (jtype != 'inner' or got.num_rows > fact.num_rows // 2)
+    for c in ['fk', 'v', 'rid'] + (['w', 'brow'] if with_build else []):
+        assert got[c].to_pylist() == exp[c].to_pylist(), c
+    gpu_engine.drop_table('jd')
+    gpu_engine.drop_table('jf')
+
+
+def test_distinct_is_an_aggregate_without_aggregates(gpu_engine, tbl):
+    got = pa.Table.from_batches([gpu_engine.execute({'op': 'sort', 'keys': [{'expr': col('g')}, {'expr': col('s')}], 'child': {
+        'op': 'aggregate', 'keys': [{'name': 'g', 'expr': col('g')}, {'name': 's', 'expr': col('s')}], 'aggs': [],
+        'child': {'op': 'scan', 'table': 't', 'columns': ['g', 's']}}})])
+    exp = sorted(set(zip(tbl['g'].to_pylist(), tbl['s'].to_pylist())), key=lambda r: ((r[0] is not None, r[0] or 0), (r[1] is not None, (r[1] or '').encode())))
+    assert list(zip(got['g'].to_pylist(), got['s'].to_pylist())) == exp
