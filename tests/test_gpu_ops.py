@@ -483,9 +483,11 @@ def test_join_semi_anti_left(gpu_engine, jtype, pa_type, dense):
     exp = fact.join(d2, keys='fk', right_keys='k', join_type=pa_type).sort_by('rid')
     assert got.num_rows == exp.num_rows
     cols = ['fk', 'v', 'rid'] + (['name', 'w', 'brow'] if jtype == 'left' else [])
-    assert got.schema.names == cols
+    assert got.schema.names == ['fk', 'v', 'rid'] + (['k', 'name', 'w', 'brow'] if jtype == 'left' else [])
     for c in cols:
         assert got[c].to_pylist() == exp[c].to_pylist(), c
+    if jtype == 'left':       # the build key itself: the probe key where a match exists, NULL elsewhere
+        assert got['k'].to_pylist() == [f if b is not None else None for f, b in zip(exp['fk'].to_pylist(), exp['brow'].to_pylist())]
     if jtype == 'left':
         # a predicate over the NULL-extended side and an aggregate above the outer join
         plan2 = {'op': 'aggregate', 'keys': [], 'aggs': [{'name': 'n', 'fn': 'count_star'}, {'name': 'cw', 'fn': 'count', 'expr': col('w')},
@@ -519,6 +521,7 @@ def test_join_repeated_build_keys(gpu_engine, jtype, pa_type, dense):
     assert got.num_rows == exp.num_rows and (jtype != 'inner' or got.num_rows > fact.num_rows // 2)
     for c in ['fk', 'v', 'rid'] + (['w', 'brow'] if with_build else []):
         assert got[c].to_pylist() == exp[c].to_pylist(), c
+    assert ('k' in got.schema.names) == with_build
     gpu_engine.drop_table('jd')
     gpu_engine.drop_table('jf')
 
