@@ -12,6 +12,12 @@ Planning rules (all result-preserving for inner equi-joins):
     snowflake children joined in first) is a unique-key build side;
   * joins are ordered most-selective first by a static estimate; the join on the fact table's
     partition column is marked `prune_partitions` (Spark's dynamic partition pruning) and goes last;
+  * `t LEFT JOIN u ON t.a = u.b [AND <u-only conditions>]` becomes a left outer join above t's inner joins (WHERE
+    conditions on u run after it); `[NOT] EXISTS (select .. from u where u.b = t.a [and ..])` and
+    `t.a [NOT] IN (select b from u [where ..])` become semi / anti joins (NOT IN needs a NOT NULL subquery column and
+    drops NULL t.a, as SQL's three-valued logic does); a build key that is not its table's primary key makes the join
+    `unique_build: false` (repeated keys are chained and expand the probe rows);
+  * SELECT DISTINCT is a GROUP BY over the select list without aggregates; HAVING is a filter above the aggregate;
   * AVG is planned as SUM and COUNT plus a final divide (decimal: scale + 4, HALF_UP - Spark's
     Average for DecimalType; integer: double);
   * ORDER BY keys are followed by every remaining output column as tie-breakers so that the
@@ -325,8 +331,52 @@ class Planner:
                 conj.append(e)
         split(q['where'])
         edges, table_filters, post = [], {}, []
+        # ---- subquery conjuncts -> semi / anti joins: (outer column, subquery table, its key column, its filters, type)
+        sub_joins = []
+        plain = []
+        for c in conj:
+            if c[0] in ('exists', 'in_sub'):
+                sub_joins.append(self.plan_subquery(c))
+            else:
+                plain.append(c)
+        conj = plain
+        # ---- LEFT JOINs: (outer column, joined table, its key column, its ON-clause filters)
+        left_joins = []
+        left_tables = set()
+        for alias, on in q.get('left_joins', []):
+            tl = self.alias[alias]
+            parts = []
+
+            def split_on(e):
+                if e[0] == 'bin' and e[1] == 'and':
+                    split_on(e[2])
+                    split_on(e[3])
+                else:
+                    parts.append(e)
+            split_on(on)
+            key, flt = None, []
+            for c in parts:
+                tabs = self.tables_of(c)
+                if c[0] == 'bin' and c[1] == 'eq' and c[2][0] == 'col' and c[3][0] == 'col' and len(tabs) == 2 and tl in tabs:
+                    a, b = self.resolve(c[2]), self.resolve(c[3])
+                    if key is not None:
+                        raise PlanError('LEFT JOIN %s: more than one equality in ON is not supported yet' % tl)
+                    key = (b, a) if self.col_table[a] == tl else (a, b)
+                elif tabs == {tl}:
+                    flt.append(c)
+                else:
+                    raise PlanError('LEFT JOIN %s: ON must be one equality with an earlier table plus conditions on %s only' % (tl, tl))
+            if key is None:
+                raise PlanError('LEFT JOIN %s: ON needs an equality with an earlier table' % tl)
+            if self.col_table[key[0]] in left_tables:
+                raise PlanError('LEFT JOIN %s: joining to another left-joined table is not supported yet' % tl)
+            left_joins.append((key[0], tl, key[1], flt))
+            left_tables.add(tl)
         for c in conj:
             tabs = self.tables_of(c)
+            if tabs & left_tables:
+                post.append(c)          # WHERE conditions over the NULL-extended side run after the outer join
+                continue
             if (c[0] == 'bin' and c[1] == 'eq' and c[2][0] == 'col' and c[3][0] == 'col' and len(tabs) == 2):
                 a, b = self.resolve(c[2]), self.resolve(c[3])
                 edges.append((self.col_table[a], a, self.col_table[b], b))
@@ -337,7 +387,9 @@ class Planner:
             else:
                 post.append(c)
         # ---- root (fact) table
-        facts = [t for t in self.tables if t in nds_schema.TABLE_PARTITIONING]
+        facts = [t for t in self.tables if t in nds_schema.TABLE_PARTITIONING and t not in left_tables]
+        if [t for t in left_tables if t in nds_schema.TABLE_PARTITIONING] and facts:
+            raise PlanError('joins between fact tables are not supported yet')
         if len(facts) > 1:
             raise PlanError('joins between fact tables (%s) are not supported yet' % ', '.join(facts))
         root = facts[0] if facts else self.tables[0]
@@ -358,6 +410,14 @@ class Planner:
             self.columns_of(e, used)
         for c in conj:
             self.columns_of(c, used)
+        for okey, tl, ikey, flt in left_joins:
+            used.update([okey, ikey])
+            for c in flt:
+                self.columns_of(c, used)
+        for sj in sub_joins:
+            used.add(sj['outer'])
+        if q.get('having') is not None:
+            self.columns_of(q['having'], used)
         for c in used:
             need[self.col_table[c]].add(c)
         # ---- join tree
@@ -380,7 +440,7 @@ class Planner:
                 frontier.append(nxt)
                 remaining.remove(e)
         for t in self.tables:
-            if t not in visited:
+            if t not in visited and t not in left_tables:
                 raise PlanError('table %r is not connected by an equi-join (cross joins are not supported)' % t)
         for ta, ca, tb, cb in remaining:       # extra equalities between already-joined tables
             post.append(('bin', 'eq', ('col', None, ca), ('col', None, cb)))
@@ -400,6 +460,15 @@ class Planner:
                 self.columns_of(c, payload)
         for c in post:
             self.columns_of(c, payload)
+        for okey, tl, ikey, flt in left_joins:
+            payload.add(okey)
+        for sj in sub_joins:
+            payload.add(sj['outer'])
+        if q.get('having') is not None:
+            self.columns_of(q['having'], payload)
+
+        def is_primary_key(table, column):
+            return nds_schema.SOURCE_TABLES[table][0][0] == column and table not in nds_schema.TABLE_PARTITIONING
 
         def selectivity(t):
             s = 1.0
@@ -429,6 +498,25 @@ class Planner:
                 node = {'op': 'join', 'type': 'inner', 'probe': node, 'build': subtree(ct), 'probe_key': pk, 'build_key': ck}
                 if prune:
                     node['prune_partitions'] = True
+                if not is_primary_key(ct, ck):
+                    node['unique_build'] = False
+            for okey, tl, ikey, lflt in left_joins:
+                if self.col_table[okey] != t:
+                    continue
+                bcols = sorted(need[tl], key=lambda c: [n for n, _, _ in nds_schema.SOURCE_TABLES[tl]].index(c))
+                build = {'op': 'scan', 'table': tl, 'columns': bcols}
+                if lflt:
+                    irs = [self.expr(c)[0] for c in lflt]
+                    build = {'op': 'filter', 'cond': irs[0] if len(irs) == 1 else _fn('and', *irs), 'child': build}
+                node = {'op': 'join', 'type': 'left', 'probe': node, 'build': build, 'probe_key': okey, 'build_key': ikey}
+                if not is_primary_key(tl, ikey):
+                    node['unique_build'] = False
+            for sj in sub_joins:
+                if self.col_table[sj['outer']] != t:
+                    continue
+                if sj['drop_null_outer']:
+                    node = {'op': 'filter', 'cond': _fn('isnotnull', _col(sj['outer'])), 'child': node}
+                node = {'op': 'join', 'type': sj['type'], 'probe': node, 'build': sj['build'], 'probe_key': sj['outer'], 'build_key': sj['key']}
             return node
         node = subtree(root)
         if post:
@@ -444,6 +532,15 @@ class Planner:
             return any(has_agg(x) if isinstance(x, tuple) else any(has_agg(y) for y in x if isinstance(y, tuple))
                        for x in a[1:] if isinstance(x, (tuple, list)))
         is_agg = bool(q['group']) or any(has_agg(e) for e, _ in q['select'])
+        group_asts = list(q['group'])
+        if q.get('distinct'):
+            # SELECT DISTINCT a, b == SELECT a, b GROUP BY a, b (no aggregates, no GROUP BY of its own)
+            if is_agg:
+                raise PlanError('SELECT DISTINCT together with GROUP BY / aggregates is not supported yet')
+            is_agg = True
+            group_asts = [e for e, _ in q['select']]
+        if q.get('having') is not None and not is_agg:
+            raise PlanError('HAVING without GROUP BY / aggregates')
         out_cols = []          # [(name, ir, type)]
         names = []
         for e, alias in q['select']:
@@ -451,13 +548,14 @@ class Planner:
         final_partial = None
         if is_agg:
             key_map, keys = {}, []
-            for i, g in enumerate(q['group']):
+            for i, g in enumerate(group_asts):
                 ir, t = self.expr(g)
                 name = ir['col'] if 'col' in ir else '_gk%d' % i
                 key_map[self.ast_key(g)] = (name, t)
                 keys.append({'name': name, 'expr': ir, '_type': t})
             agg_map = _AggMap()
             sel_ir = [self.expr(e, agg_map, key_map) for e, _ in q['select']]
+            having_ir = self.expr(q['having'], agg_map, key_map)[0] if q.get('having') is not None else None
             order_extra = []
             for e, desc, nf in q['order']:
                 order_extra.append(None if (e[0] == 'col' and e[1] is None and e[2] in select_aliases)
@@ -476,6 +574,8 @@ class Planner:
                 node = merge
             else:
                 node = agg_node
+            if having_ir is not None:        # HAVING: a filter over the (merged) groups
+                node = {'op': 'filter', 'cond': having_ir, 'child': node}
             for (ir, t), name in zip(sel_ir, names):
                 out_cols.append((name, ir, t))
         else:
@@ -507,7 +607,7 @@ class Planner:
             # deterministic tie-break: the remaining output columns - unless the ORDER BY keys already contain
             # every GROUP BY key, in which case no two result rows can tie
             total = False
-            if is_agg and q['group']:
+            if is_agg and group_asts:
                 key_outs = []
                 for kname, _ in key_map.values():
                     key_outs.append([n for n, oir, _ in out_cols if oir == _col(kname)])
@@ -526,6 +626,77 @@ class Planner:
             # one plan for engines that share a communicator: the scan of the gathered states becomes an exchange node
             out['fused'] = _replace_partial_scan(node, {'op': 'exchange', 'child': final_partial})
         return out
+
+    def plan_subquery(self, c):
+        """('exists', q2, negated) | ('in_sub', x, q2, negated) -> {'outer', 'key', 'build', 'type', 'drop_null_outer'}.
+        The subquery reads one table that the outer query does not; EXISTS correlates it with one equality."""
+        q2 = c[1] if c[0] == 'exists' else c[2]
+        negated = c[2] if c[0] == 'exists' else c[3]
+        if len(q2['from']) != 1 or q2['group'] or q2.get('having') or q2['order'] or q2['limit'] is not None or q2.get('left_joins'):
+            raise PlanError('subqueries are supported over one table, without GROUP BY / ORDER BY / LIMIT')
+        t2, a2 = q2['from'][0]
+        if t2 not in nds_schema.SOURCE_TABLES:
+            raise PlanError('unknown table %r' % t2)
+        if t2 in self.tables:
+            raise PlanError('a subquery over a table of the outer query (%s) is not supported yet' % t2)
+        inner_cols = {n for n, _, _ in nds_schema.SOURCE_TABLES[t2]}
+
+        def res(node):               # column of the subquery's table, or of the outer query
+            _, qual, name = node
+            if qual is not None and qual == a2:
+                if name not in inner_cols:
+                    raise PlanError('column %r is not in table %r' % (name, t2))
+                return name, True
+            if qual is None and name in inner_cols:
+                return name, True
+            return self.resolve(node), False
+        parts = []
+
+        def split(e):
+            if e is None:
+                return
+            if e[0] == 'bin' and e[1] == 'and':
+                split(e[2])
+                split(e[3])
+            else:
+                parts.append(e)
+        split(q2['where'])
+        sub = Planner({'from': [(t2, a2)], 'select': [], 'where': None, 'group': [], 'order': [], 'limit': None})
+        key, outer, flt = None, None, []
+        for e in parts:
+            if e[0] == 'bin' and e[1] == 'eq' and e[2][0] == 'col' and e[3][0] == 'col':
+                (n1, in1), (n2, in2) = res(e[2]), res(e[3])
+                if in1 != in2:
+                    if key is not None:
+                        raise PlanError('a subquery correlated by more than one equality is not supported yet')
+                    key, outer = (n1, n2) if in1 else (n2, n1)
+                    continue
+            cols = sub.columns_of(e)          # raises on columns outside the subquery's table
+            flt.append(e)
+        if c[0] == 'in_sub':
+            if key is not None:
+                raise PlanError('a correlated IN subquery is not supported yet')
+            if len(q2['select']) != 1 or q2['select'][0][0][0] != 'col' or c[1][0] != 'col':
+                raise PlanError('IN (subquery): one column on each side is supported')
+            key, inner = res(q2['select'][0][0])
+            if not inner:
+                raise PlanError('IN (subquery): the selected column must belong to the subquery table')
+            outer = self.resolve(c[1])
+        elif key is None:
+            raise PlanError('EXISTS (subquery) needs an equality with a column of the outer query')
+        nullable = {n: nu for n, _, nu in nds_schema.SOURCE_TABLES[t2]}[key]
+        if c[0] == 'in_sub' and negated and nullable:
+            raise PlanError('NOT IN over a nullable subquery column (%s) is not supported: one NULL empties the result' % key)
+        need = {key}
+        for e in flt:
+            need |= sub.columns_of(e)
+        order = [n for n, _, _ in nds_schema.SOURCE_TABLES[t2]]
+        build = {'op': 'scan', 'table': t2, 'columns': sorted(need, key=order.index)}
+        if flt:
+            irs = [sub.expr(e)[0] for e in flt]
+            build = {'op': 'filter', 'cond': irs[0] if len(irs) == 1 else _fn('and', *irs), 'child': build}
+        return {'outer': outer, 'key': key, 'build': build, 'type': 'anti' if negated else 'semi',
+                'drop_null_outer': c[0] == 'in_sub' and negated}
 
     def pred_selectivity(self, c):
         k = c[0]

@@ -4,14 +4,19 @@ In the reference, `spark_session.sql(query)` (/root/reference/nds/nds_power.py:1
 plans the statement inside Spark (Catalyst).  No JVM exists on the build or GPU boxes, so the host
 side carries its own parser for the subset of Spark SQL the supported templates use:
 
-    SELECT <exprs [AS alias]> FROM <t [alias], ... | t [INNER] JOIN u ON <expr> ...> [WHERE <expr>] [GROUP BY ...]
-    [ORDER BY <expr [ASC|DESC] [NULLS FIRST|LAST]>, ...] [LIMIT n]
+    SELECT [DISTINCT] <exprs [AS alias]> FROM <t [alias], ... | t [INNER] JOIN u ON <expr> | t LEFT [OUTER] JOIN u ON <expr> ...>
+    [WHERE <expr>] [GROUP BY ...] [HAVING <expr>] [ORDER BY <expr [ASC|DESC] [NULLS FIRST|LAST]>, ...] [LIMIT n]
+
+with `[NOT] EXISTS (SELECT ... FROM t WHERE ...)` and `x [NOT] IN (SELECT c FROM t [WHERE ...])` as WHERE conjuncts
+(one-table subqueries; planner.py turns them into semi / anti joins).
 
 Anything outside the subset raises SqlError - the statement is never silently approximated.
 The AST is plain tuples:  ('col', qualifier|None, name) | ('num', text) | ('str', value) | ('null',)
  | ('call', fname, [args], distinct) | ('bin', op, l, r) | ('not', x) | ('neg', x)
  | ('isnull', x, negated) | ('between', x, lo, hi, negated) | ('in', x, [items], negated)
  | ('case', [(cond, value)...], else|None) | ('cast', x, typename) | ('star',)
+ | ('exists', query, negated) | ('in_sub', x, query, negated)
+A query is {'select', 'from', 'where', 'group', 'having', 'order', 'limit', 'distinct', 'left_joins': [(alias, on_expr)]}.
 """
 import re
 
@@ -86,25 +91,35 @@ class Parser:
         return None
 
     # ---- statement -----------------------------------------------------------------------------
-    def parse_query(self):
+    def parse_query(self, sub=False):
         if self.peek() == ('kw', 'with'):
             raise SqlError('WITH (common table expressions) is not supported by the B200 planner yet')
         self.expect('kw', 'select')
-        if self.kw('distinct'):
-            raise SqlError('SELECT DISTINCT is not supported by the B200 planner yet')
+        distinct = bool(self.kw('distinct'))
         select = [self.select_item()]
         while self.accept('op', ','):
             select.append(self.select_item())
         self.expect('kw', 'from')
         tables = [self.table_ref()]
         on_conds = []
+        left_joins = []
         while True:
             if self.accept('op', ','):
                 tables.append(self.table_ref())
                 continue
             tok = self.peek()
-            if tok[0] == 'kw' and tok[1] in ('left', 'right', 'full', 'outer'):
-                raise SqlError('%s OUTER JOIN is not supported by the B200 planner yet (inner joins only)' % tok[1].upper())
+            if tok == ('kw', 'left'):
+                # LEFT [OUTER] JOIN t ON cond: t joins the tables before it, rows without a match keep NULLs in t's columns
+                self.next()
+                self.kw('outer')
+                self.expect('kw', 'join')
+                ref = self.table_ref()
+                tables.append(ref)
+                self.expect('kw', 'on')
+                left_joins.append((ref[1], self.expr()))
+                continue
+            if tok[0] == 'kw' and tok[1] in ('right', 'full', 'outer'):
+                raise SqlError('%s OUTER JOIN is not supported by the B200 planner yet (inner and left joins only)' % tok[1].upper())
             if tok == ('kw', 'inner') or tok == ('kw', 'join'):
                 # [INNER] JOIN t ON cond  ==  , t  ... WHERE cond: an inner join's ON clause is just another conjunct
                 self.kw('inner')
@@ -125,8 +140,7 @@ class Parser:
             group.append(self.expr())
             while self.accept('op', ','):
                 group.append(self.expr())
-        if self.kw('having'):
-            raise SqlError('HAVING is not supported by the B200 planner yet')
+        having = self.expr() if self.kw('having') else None
         order = []
         if self.kw('order'):
             self.expect('kw', 'by')
@@ -136,10 +150,12 @@ class Parser:
         limit = None
         if self.kw('limit'):
             limit = int(self.expect('num')[1])
-        self.accept('op', ';')
-        if self.peek()[0] != 'eof':
-            raise SqlError('unsupported trailing SQL: %r' % self.peek()[1])
-        return {'select': select, 'from': tables, 'where': where, 'group': group, 'order': order, 'limit': limit}
+        if not sub:
+            self.accept('op', ';')
+            if self.peek()[0] != 'eof':
+                raise SqlError('unsupported trailing SQL: %r' % self.peek()[1])
+        return {'select': select, 'from': tables, 'where': where, 'group': group, 'having': having, 'order': order, 'limit': limit,
+                'distinct': distinct, 'left_joins': left_joins}
 
     def select_item(self):
         if self.accept('op', '*'):
@@ -194,7 +210,16 @@ class Parser:
 
     def not_expr(self):
         if self.kw('not'):
-            return ('not', self.not_expr())
+            inner = self.not_expr()
+            if inner[0] == 'exists':
+                return ('exists', inner[1], not inner[2])
+            return ('not', inner)
+        if self.peek() == ('kw', 'exists'):
+            self.next()
+            self.expect('op', '(')
+            q = self.parse_query(sub=True)
+            self.expect('op', ')')
+            return ('exists', q, False)
         return self.predicate()
 
     def predicate(self):
@@ -220,7 +245,9 @@ class Parser:
         if self.kw('in'):
             self.expect('op', '(')
             if self.peek() == ('kw', 'select'):
-                raise SqlError('IN (subquery) is not supported by the B200 planner yet')
+                q = self.parse_query(sub=True)
+                self.expect('op', ')')
+                return ('in_sub', e, q, neg)
             items = [self.expr()]
             while self.accept('op', ','):
                 items.append(self.expr())

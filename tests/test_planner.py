@@ -52,13 +52,18 @@ def test_distributed_plan_splits_at_the_aggregate():
 
 @pytest.mark.parametrize('text', [
     'select * from item',
-    'select i_item_sk from item where i_item_sk in (select ss_item_sk from store_sales)',
+    'select i_item_sk from item where i_item_sk in (select ss_item_sk from store_sales, date_dim where ss_sold_date_sk = d_date_sk)',   # multi-table subquery
+    'select i_item_sk from item where i_item_sk not in (select ss_customer_sk from store_sales)',   # NOT IN over a nullable column
+    'select i_item_sk from item where exists (select 1 from item where i_manager_id = 3)',          # uncorrelated / same table
+    'select i_item_sk from item where i_item_sk = (select max(ss_item_sk) from store_sales)',      # scalar subquery
     'select i_item_sk, rank() over (partition by i_brand order by i_item_sk) from item',
     'select i_brand, sum(i_item_sk) from item group by rollup(i_brand)',
     'with x as (select 1) select * from x',
     'select i_item_sk from item, store',                                     # cross join
     'select ss_item_sk from store_sales, store_returns where ss_item_sk = sr_item_sk',   # fact-fact join
-    'select distinct i_brand from item',
+    'select distinct i_brand, count(*) from item group by i_brand',
+    'select i_brand from item having count(*) > 1 and i_brand > \'a\'',       # HAVING over a non-grouped column
+    'select i_brand from item left join promotion on p_item_sk = i_item_sk left join store on s_store_sk = p_promo_sk',   # chained outer joins
     'select i_brand from item where i_brand like \'a%\'',
     'select i_brand, count(distinct i_item_sk) from item group by i_brand',
     'select nope from item',
@@ -156,9 +161,47 @@ def test_explicit_inner_join_syntax_plans_like_comma_joins():
     mixed = comma.replace('from date_dim, store_sales, item\n               where d_date_sk = ss_sold_date_sk and',
                           'from date_dim join store_sales on d_date_sk = ss_sold_date_sk, item\n               where')
     assert planner.plan_sql(mixed) == planner.plan_sql(comma)
-    for kind in ('left', 'left outer', 'right', 'full outer'):
+    for kind in ('right', 'full outer'):
         with pytest.raises(planner.PlanError, match='OUTER JOIN is not supported'):
             planner.plan_sql(explicit.replace('inner join item', kind + ' join item'))
+    # LEFT [OUTER] JOIN plans a left join above the inner chain; the WHERE condition on the joined table runs after it
+    for kind in ('left', 'left outer'):
+        p = planner.plan_sql(explicit.replace('inner join item', kind + ' join item'))
+        node = p['root']
+        while node['op'] != 'aggregate':
+            node = node['child']
+        flt = node['child']
+        assert flt['op'] == 'filter' and flt['child']['op'] == 'join' and flt['child']['type'] == 'left'
+        assert flt['child']['build'] == {'op': 'scan', 'table': 'item', 'columns': ['i_item_sk', 'i_brand_id', 'i_manufact_id']}
+
+
+def test_subqueries_distinct_having_plan_shapes():
+    from spark_rapids_benchmarks_b200 import planner
+
+    def find(node, op):
+        out = []
+        if node.get('op') == op:
+            out.append(node)
+        for k in ('child', 'probe', 'build'):
+            if k in node:
+                out += find(node[k], op)
+        return out
+    p = planner.plan_sql('select c_customer_sk from customer where exists (select 1 from store_sales ss where ss.ss_customer_sk = c_customer_sk '
+                         'and ss_quantity > 90) and c_current_addr_sk not in (select ca_address_sk from customer_address) order by c_customer_sk')
+    joins = find(p['root'], 'join')
+    assert [(j['type'], j['probe_key'], j['build_key']) for j in joins] == [('anti', 'c_current_addr_sk', 'ca_address_sk'),
+                                                                             ('semi', 'c_customer_sk', 'ss_customer_sk')]
+    assert joins[0]['probe']['op'] == 'filter' and joins[0]['probe']['cond']['fn'] == 'isnotnull'      # NOT IN drops NULL outer values
+    p = planner.plan_sql('select distinct i_category, i_class from item')
+    agg = find(p['root'], 'aggregate')[0]
+    assert [k['name'] for k in agg['keys']] == ['i_category', 'i_class'] and agg['aggs'] == []
+    p = planner.plan_sql('select i_brand, sum(i_current_price) s from item group by i_brand having sum(i_current_price) > 10 and count(*) > 1',
+                         distributed=True, sharded={'item'})
+    flt = find(p['root'], 'filter')[0]
+    assert flt['child']['op'] == 'aggregate' and flt['child']['child']['table'] == '__partial__'       # HAVING runs over the merged groups
+    # a join on a column that is not the build table's primary key chains repeated keys
+    p = planner.plan_sql('select i_brand, count(*) c from item, promotion where p_item_sk = i_item_sk group by i_brand')
+    assert find(p['root'], 'join')[0].get('unique_build') is False
 
 
 def test_table_aliases_and_qualified_columns_plan_identically():
