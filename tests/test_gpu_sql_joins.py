@@ -22,19 +22,19 @@ def _key(row):
 
 
 def test_left_join_repeated_keys_having(gpu_engine, warehouse):
-    sql = ("select i_brand, count(*) c, count(p_promo_sk) cp, sum(p_cost) pc from item left join promotion "
-           "on p_item_sk = i_item_sk and p_channel_tv = 'N' where i_manager_id < 40 group by i_brand "
-           "having count(*) > 2 order by i_brand limit 1000")
+    sql = ("select i_category, count(*) c, count(p_promo_sk) cp, sum(p_cost) pc from item left join promotion "
+           "on p_item_sk = i_item_sk and p_channel_tv = 'N' where i_manager_id < 70 group by i_category "
+           "having count(*) > 2 order by i_category limit 1000")
     got = _Sess(gpu_engine).sql(sql).toArrow()
-    it = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_brand', 'i_manager_id'])
-    it = it.filter(pc.less(it['i_manager_id'], 40).fill_null(False))
+    it = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_category', 'i_manager_id'])
+    it = it.filter(pc.less(it['i_manager_id'], 70).fill_null(False))
     pr = oq.read_dim(warehouse, 'promotion', ['p_promo_sk', 'p_item_sk', 'p_cost', 'p_channel_tv'])
     pr = pr.filter(pc.equal(pr['p_channel_tv'], 'N').fill_null(False)).filter(pc.is_valid(pr.filter(pc.equal(pr['p_channel_tv'], 'N').fill_null(False))['p_item_sk']))
     j = it.join(pr, keys='i_item_sk', right_keys='p_item_sk', join_type='left outer')
-    g = j.group_by('i_brand').aggregate([([], 'count_all'), ('p_promo_sk', 'count'), ('p_cost', 'sum')])
-    exp = sorted([(r['i_brand'], r['count_all'], r['p_promo_sk_count'], r['p_cost_sum']) for r in g.to_pylist() if r['count_all'] > 2], key=_key)[:1000]
-    assert _rows(got, ['i_brand', 'c', 'cp', 'pc']) == exp
-    assert len(exp) > 10 and any(r[2] > 0 for r in exp) and any(r[2] == 0 for r in exp)
+    g = j.group_by('i_category').aggregate([([], 'count_all'), ('p_promo_sk', 'count'), ('p_cost', 'sum')])
+    exp = sorted([(r['i_category'], r['count_all'], r['p_promo_sk_count'], r['p_cost_sum']) for r in g.to_pylist() if r['count_all'] > 2], key=_key)[:1000]
+    assert _rows(got, ['i_category', 'c', 'cp', 'pc']) == exp
+    assert len(exp) > 3 and any(r[2] > 0 for r in exp) and j.num_rows > it.num_rows
 
 
 def test_left_join_where_on_the_outer_side(gpu_engine, warehouse):
@@ -65,24 +65,22 @@ def test_exists_and_not_in_subqueries(gpu_engine, warehouse):
 
 
 def test_not_exists_over_a_fact_scan(gpu_engine, warehouse):
-    """An anti join above the fact table's star join, then a keyless / grouped aggregate."""
-    sql = ("select d_year, count(*) n, sum(ss_quantity) q from store_sales, date_dim where ss_sold_date_sk = d_date_sk and d_moy = 1 "
-           "and not exists (select 1 from item where i_item_sk = ss_item_sk and i_manager_id < 50) and ss_item_sk in "
-           "(select i_item_sk from item i2 where i2.i_category_id <= 5) group by d_year order by d_year")
-    with pytest.raises(Exception):
-        _Sess(gpu_engine).sql(sql)             # the same table twice in one statement (item, item i2) stays unsupported
-    sql = ("select d_year, count(*) n, sum(ss_quantity) q from store_sales, date_dim where ss_sold_date_sk = d_date_sk and d_moy = 1 "
-           "and not exists (select 1 from item where i_item_sk = ss_item_sk and i_manager_id < 50) group by d_year order by d_year")
-    got = _Sess(gpu_engine).sql(sql).toArrow()
+    """Anti and semi joins above the fact table's star join (two subqueries over the same dimension), then an aggregate."""
+    base = ("select d_year, count(*) n, sum(ss_quantity) q from store_sales, date_dim where ss_sold_date_sk = d_date_sk and d_moy = 1 "
+            "and not exists (select 1 from item where i_item_sk = ss_item_sk and i_manager_id < 50)%s group by d_year order by d_year")
     dd = oq.read_dim(warehouse, 'date_dim', ['d_date_sk', 'd_year', 'd_moy'])
     dd = dd.filter(pc.equal(dd['d_moy'], 1).fill_null(False))
     ss = oq.read_fact(warehouse, 'store_sales', 'ss_sold_date_sk', ['ss_sold_date_sk', 'ss_item_sk', 'ss_quantity'], dd['d_date_sk'].to_pylist())
-    it = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_manager_id'])
+    it = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_manager_id', 'i_category_id'])
     low = it.filter(pc.less(it['i_manager_id'], 50).fill_null(False)).select(['i_item_sk'])
+    cat = it.filter(pc.less_equal(it['i_category_id'], 5).fill_null(False)).select(['i_item_sk'])
     j = ss.join(dd, keys='ss_sold_date_sk', right_keys='d_date_sk', join_type='inner').join(low, keys='ss_item_sk', right_keys='i_item_sk', join_type='left anti')
-    g = j.group_by('d_year').aggregate([([], 'count_all'), ('ss_quantity', 'sum')]).sort_by('d_year')
-    assert _rows(got, ['d_year', 'n', 'q']) == [(r['d_year'], r['count_all'], r['ss_quantity_sum']) for r in g.to_pylist()]
-    assert got.num_rows > 0
+    for extra, jj in (('', j), (' and ss_item_sk in (select i_item_sk from item i2 where i2.i_category_id <= 5)',
+                            j.join(cat, keys='ss_item_sk', right_keys='i_item_sk', join_type='left semi'))):
+        got = _Sess(gpu_engine).sql(base % extra).toArrow()
+        g = jj.group_by('d_year').aggregate([([], 'count_all'), ('ss_quantity', 'sum')]).sort_by('d_year')
+        assert _rows(got, ['d_year', 'n', 'q']) == [(r['d_year'], r['count_all'], r['ss_quantity_sum']) for r in g.to_pylist()]
+        assert got.num_rows > 0
 
 
 def test_select_distinct(gpu_engine, warehouse):
