@@ -1895,6 +1895,183 @@ struct Exec {
     return L;
   }
 
+  // Hash-partition exchange (all-to-all): row i goes to rank hash(keys) % world.  Spark: ShuffleExchange(hashpartitioning);
+  // here the per-destination row counts of every rank are all-gathered first (one host read-back), then every rank packs
+  // one segment per destination and a grouped ncclSend / ncclRecv pair per peer moves them over NVLink.
+  Batch exchange_hash(const Json& node, Batch& in, std::vector<Column>& flat, int world, int loop, size_t st) {
+    const int ncols = (int)flat.size();
+    if (world > 255) fail("exchange: more than 255 ranks");
+    Batch fb;                       // the flattened child as a batch (the key programs read it)
+    fb.n_max = in.n_max;
+    fb.n_dev = in.n_dev;
+    fb.n_exact = in.n_exact;
+    fb.cols = flat;
+    Blob bb;
+    const Json& jkeys = node.at("keys");
+    if (jkeys.a.empty()) fail("plan: hash exchange without keys");
+    for (const Json& k : jkeys.a) {
+      std::vector<Instr> code;
+      Json ce = col_expr(k.s);
+      LType t = compile(ce, fb, bb, code);
+      bb.add_prog(code, t);
+    }
+    Blob::Dev dev = bb.upload(ar, s);
+    const int64_t nb = std::max<int64_t>(in.rc().host, 1);
+    uint8_t* dest = (uint8_t*)ar.alloc(nb);
+    // meta of one rank: rows per destination [world], rows, "size assumption failed" flag, string slot width per column
+    const int mlen = world + 2 + ncols;
+    std::vector<int32_t> meta(mlen, 0);
+    for (int c = 0; c < ncols; ++c) {
+      const LType& t = flat[c].lt;
+      if (t.kind == LType::STR && t.maxlen <= 0) fail("plan: exchange of string column '" + flat[c].name + "' without a known maximum length");
+      meta[world + 2 + c] = t.kind == LType::STR ? t.maxlen : 0;
+    }
+    int32_t* d_meta = ar.alloc_n<int32_t>(mlen);
+    int32_t* d_all = ar.alloc_n<int32_t>((int64_t)mlen * world);
+    ar.upload(d_meta, meta.data(), mlen * 4);
+    launch_exchange_dest(dev.progs, (int)jkeys.a.size(), dev.ctx, in.rc(), world, dest, d_meta, s);
+    launch_set_count(in.rc(), d_meta + world, s, err + 2, d_meta + world + 1);
+    launches += 2;
+    if (loop > 0) {
+      for (int r = 0; r < world; ++r)
+        NDS_CUDA(cudaMemcpyAsync(d_all + (int64_t)r * mlen, d_meta, mlen * 4, cudaMemcpyDeviceToDevice, s));
+    } else {
+      nccl_check(nccl_api().AllGather(d_meta, d_all, (size_t)mlen * 4, kNcclChar, e.comm_, s), "ncclAllGather(partition counts)");
+    }
+    std::vector<int32_t> all((size_t)mlen * world);
+    uint8_t* pin = ar.pin_take((int64_t)all.size() * 4);
+    int32_t* hall = pin ? reinterpret_cast<int32_t*>(pin) : all.data();
+    NDS_CUDA(cudaMemcpyAsync(hall, d_all, all.size() * 4, cudaMemcpyDeviceToHost, s));
+    sync("sync:exchange_counts");
+    d2h += (int64_t)all.size() * 4;
+    for (int r = 0; r < world; ++r)
+      if (hall[(int64_t)r * mlen + world + 1]) throw SpeculationFailed();
+    const int my = loop > 0 ? 0 : e.comm_rank_;
+    std::vector<XCol> proto(ncols);
+    for (int c = 0; c < ncols; ++c) {
+      XCol& x = proto[c];
+      memset(&x, 0, sizeof x);
+      const LType& t = flat[c].lt;
+      x.kind = t.kind == LType::STR ? 2 : (t.dtype() == DT_I32 ? 0 : 1);
+      for (int r = 0; r < world; ++r) x.maxlen = std::max(x.maxlen, hall[(int64_t)r * mlen + world + 2 + c]);
+    }
+    const int64_t n_local = std::max<int32_t>(hall[(int64_t)my * mlen + world], 0);
+    in.n_exact = n_local;
+    std::vector<int64_t> begin(world + 1, 0), send_off(world + 1, 0), recv_off(world + 1, 0), row_begin(world + 1, 0);
+    std::vector<SegLayout> Ls(world), Lr(world);
+    int64_t max_from = 0;
+    for (int d = 0; d < world; ++d) {
+      const int64_t to = std::max<int32_t>(hall[(int64_t)my * mlen + d], 0), from = std::max<int32_t>(hall[(int64_t)d * mlen + my], 0);
+      begin[d + 1] = begin[d] + to;
+      Ls[d] = seg_layout(proto, to);
+      Lr[d] = seg_layout(proto, from);
+      send_off[d + 1] = send_off[d] + Ls[d].bytes;
+      recv_off[d + 1] = recv_off[d] + Lr[d].bytes;
+      row_begin[d + 1] = row_begin[d] + from;
+      max_from = std::max(max_from, from);
+    }
+    if (begin[world] != n_local) fail("exchange: partition counts do not add up");
+    const int64_t N = row_begin[world];
+    if (N >= (int64_t(1) << 31)) fail("exchange: 2^31 or more rows arrive at one rank");
+    uint8_t* d_send = (uint8_t*)ar.alloc(std::max<int64_t>(send_off[world], 16));
+    uint8_t* d_recv = (uint8_t*)ar.alloc(std::max<int64_t>(recv_off[world], 16));
+    // ---- rows ordered by destination, one packed segment per destination
+    if (n_local > 0) {
+      int64_t* d_begin = ar.alloc_n<int64_t>(world + 1);
+      ar.upload(d_begin, begin.data(), (world + 1) * 8);
+      int32_t* cursor = ar.zeros<int32_t>(world);
+      uint32_t* perm = ar.alloc_n<uint32_t>(n_local);
+      launch_exchange_perm(dest, n_local, d_begin, cursor, perm, s);
+      std::vector<XCol> desc((size_t)ncols * (world + 1));
+      for (int c = 0; c < ncols; ++c) {
+        XCol x = proto[c];
+        x.data = flat[c].data;
+        x.valid = flat[c].valid;
+        x.strbase = flat[c].strbase;
+        desc[c] = x;
+      }
+      for (int d = 0; d < world; ++d)
+        for (int c = 0; c < ncols; ++c) {
+          XCol x = proto[c];
+          x.data = d_send + send_off[d];
+          x.off_valid = Ls[d].off_valid[c];
+          x.off_data = Ls[d].off_data[c];
+          x.off_aux = Ls[d].off_aux[c];
+          desc[(size_t)ncols * (d + 1) + c] = x;
+        }
+      XCol* d_desc = ar.alloc_n<XCol>((int64_t)desc.size());
+      ar.upload(d_desc, desc.data(), (int64_t)(desc.size() * sizeof(XCol)));
+      launch_exchange_pack_perm(d_desc, d_desc + ncols, ncols, perm, d_begin, world, n_local, err, s);
+      launches += 2;
+    }
+    // ---- all-to-all
+    int64_t bytes_out = 0;
+    if (loop > 0) {
+      for (int r = 0; r < world; ++r)        // every emulated rank holds my rows: each sends me its partition 0
+        if (Lr[r].bytes > 0 && hall[(int64_t)r * mlen + my] > 0)
+          NDS_CUDA(cudaMemcpyAsync(d_recv + recv_off[r], d_send + send_off[my], (size_t)Ls[my].bytes, cudaMemcpyDeviceToDevice, s));
+    } else {
+      const NcclApi& nc = nccl_api();
+      nccl_check(nc.GroupStart(), "ncclGroupStart");
+      for (int p = 0; p < world; ++p) {
+        const int64_t to = hall[(int64_t)my * mlen + p], from = hall[(int64_t)p * mlen + my];
+        if (p == my) {
+          if (to > 0) NDS_CUDA(cudaMemcpyAsync(d_recv + recv_off[p], d_send + send_off[p], (size_t)Ls[p].bytes, cudaMemcpyDeviceToDevice, s));
+          continue;
+        }
+        if (to > 0) { nccl_check(nc.Send(d_send + send_off[p], (size_t)Ls[p].bytes, kNcclChar, p, e.comm_, s), "ncclSend"); bytes_out += Ls[p].bytes; }
+        if (from > 0) nccl_check(nc.Recv(d_recv + recv_off[p], (size_t)Lr[p].bytes, kNcclChar, p, e.comm_, s), "ncclRecv");
+      }
+      nccl_check(nc.GroupEnd(), "ncclGroupEnd");
+    }
+    // ---- unpack the received segments into concatenated columns
+    Batch out;
+    out.n_max = N;
+    out.n_exact = N;
+    std::vector<XCol> srcs((size_t)world * ncols), dst(ncols);
+    const int64_t vwords = (N + 31) / 32 + 1;
+    for (int c = 0; c < ncols; ++c) {
+      Column oc;
+      oc.name = flat[c].name;
+      oc.lt = flat[c].lt;
+      if (oc.lt.kind == LType::STR) oc.lt.maxlen = proto[c].maxlen;
+      const int w = proto[c].kind == 0 ? 4 : 8;
+      oc.data = ar.alloc(std::max<int64_t>(N, 1) * w);
+      oc.valid = ar.zeros<uint32_t>(vwords);
+      oc.strbase = proto[c].kind == 2 ? d_recv : nullptr;
+      out.cols.push_back(oc);
+      memset(&dst[c], 0, sizeof(XCol));
+      dst[c].data = oc.data;
+      dst[c].valid = oc.valid;
+      dst[c].kind = proto[c].kind;
+    }
+    for (int r = 0; r < world; ++r)
+      for (int c = 0; c < ncols; ++c) {
+        XCol x = proto[c];
+        x.data = d_recv + recv_off[r];
+        x.off_valid = Lr[r].off_valid[c];
+        x.off_data = Lr[r].off_data[c];
+        x.off_aux = Lr[r].off_aux[c];
+        srcs[(size_t)r * ncols + c] = x;
+      }
+    if (N > 0) {
+      const int64_t bytes_desc = (int64_t)(srcs.size() + dst.size()) * (int64_t)sizeof(XCol) + (world + 1) * 8;
+      uint8_t* d_desc = (uint8_t*)ar.alloc(bytes_desc);
+      std::vector<uint8_t> h((size_t)bytes_desc);
+      memcpy(h.data(), srcs.data(), srcs.size() * sizeof(XCol));
+      memcpy(h.data() + srcs.size() * sizeof(XCol), dst.data(), dst.size() * sizeof(XCol));
+      memcpy(h.data() + (srcs.size() + dst.size()) * sizeof(XCol), row_begin.data(), (world + 1) * 8);
+      ar.upload(d_desc, h.data(), bytes_desc);
+      const XCol* d_srcs = reinterpret_cast<const XCol*>(d_desc);
+      launch_exchange_unpack(d_srcs, d_srcs + srcs.size(), ncols, reinterpret_cast<const int64_t*>(d_desc + (srcs.size() + dst.size()) * sizeof(XCol)),
+                             world, max_from, d_recv, s);
+      ++launches;
+    }
+    stats[st].op = "exchange:hash";
+    end_stat(st, bytes_out, N);       // bytes that leave this GPU over NVLink
+    return out;
+  }
+
   Batch exchange(const Json& node, std::vector<RuntimeFilter>& filters) {
     Batch in = exec(node.at("child"), filters);
     const int loop = (int)(opts ? opts->int_or("exchange_loopback", 0) : 0);
@@ -1917,6 +2094,7 @@ struct Exec {
         for (size_t k = 0; k < which.size(); ++k) flat[which[k]] = fc[k];
       }
     }
+    if (node.str_or("mode", "gather") == "hash") return exchange_hash(node, in, flat, world, loop, st);
     // ---- speculative route: ONE collective and no host round trip.  Every rank sends a fixed-capacity segment whose
     // header holds its row count; the unpack kernel reads the headers on the device.  More rows than the capacity raise
     // err[2] and the query runs again on the exact two-step route below.

@@ -26,6 +26,10 @@ static void load() {
   g_api.CommInitRank = reinterpret_cast<int (*)(void**, int, NcclUniqueId, int)>(sym("ncclCommInitRank"));
   g_api.CommDestroy = reinterpret_cast<int (*)(void*)>(sym("ncclCommDestroy"));
   g_api.AllGather = reinterpret_cast<int (*)(const void*, void*, size_t, int, void*, cudaStream_t)>(sym("ncclAllGather"));
+  g_api.Send = reinterpret_cast<int (*)(const void*, size_t, int, int, void*, cudaStream_t)>(sym("ncclSend"));
+  g_api.Recv = reinterpret_cast<int (*)(void*, size_t, int, int, void*, cudaStream_t)>(sym("ncclRecv"));
+  g_api.GroupStart = reinterpret_cast<int (*)()>(sym("ncclGroupStart"));
+  g_api.GroupEnd = reinterpret_cast<int (*)()>(sym("ncclGroupEnd"));
   g_api.GetErrorString = reinterpret_cast<const char* (*)(int)>(sym("ncclGetErrorString"));
   g_api.GetVersion = reinterpret_cast<int (*)(int*)>(sym("ncclGetVersion"));
 }

@@ -1449,6 +1449,79 @@ void launch_exchange_unpack(const XCol* srcs, const XCol* dst, int ncols, const 
   NDS_CUDA(cudaGetLastError());
 }
 
+// ---- hash-partition exchange (Spark: ShuffleExchange(hashpartitioning(keys))): every row goes to rank hash(keys) % world.
+// exchange_dest_kernel: the destination of every row (the group-by's hash, over values - never pointers - so that all
+// ranks agree) and the rows per destination; exchange_perm_kernel: rows ordered by destination; exchange_pack_perm_kernel:
+// one segment per destination, laid out for that destination's row count.
+__global__ void __launch_bounds__(kThreads)
+exchange_dest_kernel(const Prog* __restrict__ progs, int nkeys, OpCtx c, const int* n_dev, int64_t n_host, int world,
+                     uint8_t* __restrict__ dest, int32_t* __restrict__ counts) {
+  const int64_t n = row_count(n_dev, n_host);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    uint64_t h = 0x9E3779B97F4A7C15ULL;
+    for (int k = 0; k < nkeys; ++k) {
+      const Val v = eval_program(progs[k].code, progs[k].n, c.cols, c.lit, i);
+      const uint64_t hv = !v.ok ? 0x7F4A7C15ULL : (progs[k].kind == 2 ? hash_bytes((const uint8_t*)(uintptr_t)v.v, v.len) : (uint64_t)v.v);
+      h = mix64(h ^ hv) + 0x9E3779B97F4A7C15ULL * (k + 1);
+    }
+    const int d = (int)(mix64(h) % (uint64_t)world);
+    dest[i] = (uint8_t)d;
+    atomicAdd(&counts[d], 1);
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) counts[world] = (int32_t)n;
+}
+void launch_exchange_dest(const Prog* progs, int nkeys, OpCtx c, RowCount n, int world, uint8_t* dest, int32_t* counts, cudaStream_t s) {
+  exchange_dest_kernel<<<grid_for(n.host), kThreads, 0, s>>>(progs, nkeys, c, n.dev, n.host, world, dest, counts);
+  NDS_CUDA(cudaGetLastError());
+}
+__global__ void __launch_bounds__(kThreads)
+exchange_perm_kernel(const uint8_t* __restrict__ dest, int64_t n, const int64_t* __restrict__ begin, int32_t* cursor, uint32_t* __restrict__ perm) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int d = dest[i];
+    perm[begin[d] + atomicAdd(&cursor[d], 1)] = (uint32_t)i;
+  }
+}
+void launch_exchange_perm(const uint8_t* dest, int64_t n, const int64_t* begin, int32_t* cursor, uint32_t* perm, cudaStream_t s) {
+  if (n <= 0) return;
+  exchange_perm_kernel<<<grid_for(n), kThreads, 0, s>>>(dest, n, begin, cursor, perm);
+  NDS_CUDA(cudaGetLastError());
+}
+// segs[d * ncols + c]: column c inside destination d's segment (data = segment base, offsets for that segment's rows)
+__global__ void __launch_bounds__(kThreads)
+exchange_pack_perm_kernel(const XCol* __restrict__ cols, const XCol* __restrict__ segs, int ncols, const uint32_t* __restrict__ perm,
+                          const int64_t* __restrict__ begin, int world, int64_t n, int* err) {
+  for (int64_t p = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; p < n; p += (int64_t)gridDim.x * blockDim.x) {
+    int d = 0;
+    while (d + 1 < world && begin[d + 1] <= p) ++d;
+    const int64_t j = p - begin[d];
+    const int64_t i = perm[p];
+    for (int c = 0; c < ncols; ++c) {
+      const XCol x = cols[c];
+      const XCol sg = segs[d * ncols + c];
+      uint8_t* out = const_cast<uint8_t*>(reinterpret_cast<const uint8_t*>(sg.data));
+      const bool ok = !x.valid || ((x.valid[i >> 5] >> (i & 31)) & 1u);
+      out[sg.off_valid + j] = ok ? 1 : 0;
+      if (x.kind == 0) reinterpret_cast<int32_t*>(out + sg.off_data)[j] = ok ? reinterpret_cast<const int32_t*>(x.data)[i] : 0;
+      else if (x.kind == 1) reinterpret_cast<int64_t*>(out + sg.off_data)[j] = ok ? reinterpret_cast<const int64_t*>(x.data)[i] : 0;
+      else {
+        const StrView v = ok ? reinterpret_cast<const StrView*>(x.data)[i] : 0;
+        int len = (int)(v >> 32);
+        if (len > sg.maxlen) { if (err) atomicExch(err, 14); len = sg.maxlen; }
+        reinterpret_cast<int32_t*>(out + sg.off_data)[j] = len;
+        const uint8_t* q = x.strbase + (uint32_t)v;
+        uint8_t* w = out + sg.off_aux + j * (int64_t)sg.maxlen;
+        for (int b = 0; b < len; ++b) w[b] = q[b];
+      }
+    }
+  }
+}
+void launch_exchange_pack_perm(const XCol* cols, const XCol* segs, int ncols, const uint32_t* perm, const int64_t* begin, int world,
+                               int64_t n, int* err, cudaStream_t s) {
+  if (n <= 0) return;
+  exchange_pack_perm_kernel<<<grid_for(n), kThreads, 0, s>>>(cols, segs, ncols, perm, begin, world, n, err);
+  NDS_CUDA(cudaGetLastError());
+}
+
 // ---- the same exchange with the row counts left on the device: ONE collective, no host round trip.
 // A segment has a fixed capacity (cap_rows rows, laid out for that capacity) and starts with a 64-byte header:
 // int32 row count, then the string slot width of every column.  The unpack kernel reads every rank's header itself.

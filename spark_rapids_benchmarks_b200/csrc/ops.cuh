@@ -259,6 +259,12 @@ void launch_set_count(RowCount n, int32_t* out, cudaStream_t s, const int* flag_
 void launch_exchange_pack(const XCol* cols, int ncols, int64_t n, uint8_t* out, int* err, cudaStream_t s);
 void launch_exchange_unpack(const XCol* srcs, const XCol* dst, int ncols, const int64_t* row_begin, int world, int64_t max_rows,
                             const uint8_t* recv, cudaStream_t s);
+// Hash-partition exchange: destination rank of every row (dest[i] = hash(keys) % world; counts[0 .. world) rows per
+// destination, counts[world] = rows), the rows ordered by destination, and one packed segment per destination.
+void launch_exchange_dest(const Prog* progs, int nkeys, OpCtx c, RowCount n, int world, uint8_t* dest, int32_t* counts, cudaStream_t s);
+void launch_exchange_perm(const uint8_t* dest, int64_t n, const int64_t* begin, int32_t* cursor, uint32_t* perm, cudaStream_t s);
+void launch_exchange_pack_perm(const XCol* cols, const XCol* segs, int ncols, const uint32_t* perm, const int64_t* begin, int world,
+                               int64_t n, int* err, cudaStream_t s);
 // The same with the row counts left on the device (one collective, no host round trip): fixed-capacity segments with a
 // kXchgHeader-byte header (row count, string slot widths); more rows than cap_rows raise err[2] (speculation failed).
 constexpr int kXchgHeader = 64;

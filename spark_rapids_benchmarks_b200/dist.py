@@ -120,10 +120,13 @@ def execute_distributed(session, plan):
     if 'partial' not in plan:
         raise ValueError('plan was not built with distributed=True')
     if getattr(session.engine, 'has_comm', False) and 'fused' in plan:
-        key = '_json_fused_' + session.source
+        # b200.agg_exchange=hash: the partial states are hash-partitioned by the group keys (all-to-all) and every rank
+        # merges its own groups; the default all-gathers them and every rank merges everything (cheaper for few groups)
+        form = 'fused_hash' if session.conf.get('b200.agg_exchange', 'gather') == 'hash' and 'fused_hash' in plan else 'fused'
+        key = '_json_%s_%s' % (form, session.source)
         payload = plan.get(key)
         if payload is None:
-            payload = session.engine.encode_plan({'root': plan['fused']}, source=src)
+            payload = session.engine.encode_plan({'root': plan[form]}, source=src)
             plan[key] = payload
         out = session.engine.execute(payload)
         session.dist_stats = None          # one engine call: Session.last_stats fetches its statistics on demand

@@ -625,6 +625,16 @@ class Planner:
             out['partial'] = final_partial
             # one plan for engines that share a communicator: the scan of the gathered states becomes an exchange node
             out['fused'] = _replace_partial_scan(node, {'op': 'exchange', 'child': final_partial})
+            # the same with Spark's own shape - HashAggregate(partial) -> Exchange(hashpartitioning(keys)) -> HashAggregate(final):
+            # the partial states are hash-partitioned by the group keys (all-to-all), every rank merges and ranks ITS groups
+            # only, and the per-rank results (at most LIMIT rows each) are gathered and ranked once more
+            gkeys = [k['name'] for k in final_partial['keys']]
+            if gkeys:
+                local = _replace_partial_scan(node, {'op': 'exchange', 'mode': 'hash', 'keys': gkeys, 'child': final_partial})
+                top = {'op': 'exchange', 'child': local}
+                if node['op'] == 'sort':
+                    top = {'op': 'sort', 'keys': node['keys'], 'limit': node['limit'], 'child': top}
+                out['fused_hash'] = top
         return out
 
     def plan_subquery(self, c):

@@ -46,6 +46,25 @@ def main():
         two = pa.Table.from_batches([sess.engine.execute({'root': plan['fused']})]).to_pylist()
         one = pa.Table.from_batches([sess.engine.execute({'root': plan['fused']}, options={'exchange_single': True})]).to_pylist()
         assert one == two and len(one) > 0, query
+    # Spark's own plan shape: partial aggregate -> hash-partition all-to-all (grouped ncclSend / ncclRecv) -> every rank merges and
+    # ranks its own groups -> gather of the per-rank top rows -> final ranking.  Same rows as the all-gather form.
+    for query in streams.SUBSET:
+        plan = sess.plan(streams.render(query, overrides={'MANUFACT': 606, 'MANAGER': 63, 'MONTH': 1, 'YEAR': 1998}))
+        two = pa.Table.from_batches([sess.engine.execute({'root': plan['fused']})]).to_pylist()
+        hashed = pa.Table.from_batches([sess.engine.execute({'root': plan['fused_hash']})]).to_pylist()
+        assert any(o['op'] == 'exchange:hash' for o in sess.engine.last_stats()['ops']), 'the all-to-all did not run'
+        assert len(hashed) == len(two) and len(two) > 0, query
+        for a, b in zip(hashed, two):
+            for k in b:
+                if isinstance(b[k], float) and a[k] is not None:
+                    assert math.isclose(a[k], b[k], rel_tol=1e-5), (query, k)
+                else:
+                    assert a[k] == b[k], (query, k, a[k], b[k])
+    sess.conf['b200.agg_exchange'] = 'hash'
+    via_session = sess.sql(streams.render('query42', overrides={'MANAGER': 63, 'MONTH': 1, 'YEAR': 1998})).toArrow().to_pylist()
+    assert any(o['op'] == 'exchange:hash' for o in sess.last_stats['ops'])
+    sess.conf['b200.agg_exchange'] = 'gather'
+    assert via_session == sess.sql(streams.render('query42', overrides={'MANAGER': 63, 'MONTH': 1, 'YEAR': 1998})).toArrow().to_pylist()
     # schemas must not depend on the GPU count: sum(decimal(7,2)) stays decimal(17,2) through the merge
     sess.source = 'hbm'
     t3 = sess.sql(streams.render('query3', overrides={'MANUFACT': 606, 'MONTH': 1})).toArrow()

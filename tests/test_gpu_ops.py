@@ -532,3 +532,35 @@ def test_distinct_is_an_aggregate_without_aggregates(gpu_engine, tbl):
         'child': {'op': 'scan', 'table': 't', 'columns': ['g', 's']}}})])
     exp = sorted(set(zip(tbl['g'].to_pylist(), tbl['s'].to_pylist())), key=lambda r: ((r[0] is not None, r[0] or 0), (r[1] is not None, (r[1] or '').encode())))
     assert list(zip(got['g'].to_pylist(), got['s'].to_pylist())) == exp
+
+
+@pytest.mark.parametrize('k', [2, 3])
+def test_hash_exchange_loopback_keeps_whole_groups(gpu_engine, tbl, k):
+    """The hash-partition exchange on one GPU (exchange_loopback=k: k ranks that all hold this rank's rows, so this rank
+    receives partition 0 of each): every row arrives k times or not at all, rows with equal keys (NULL keys included) go
+    the same way, and about 1/k of the keys land here - integers, decimals, strings and nulls intact."""
+    plan = {'op': 'exchange', 'mode': 'hash', 'keys': ['g', 's'],
+            'child': {'op': 'filter', 'cond': fn('ge', col('a'), lit(-40)),
+                      'child': {'op': 'scan', 'table': 't', 'columns': ['a', 'b', 's', 'd', 'g']}}}
+    got = pa.Table.from_batches([gpu_engine.execute(plan, options={'exchange_loopback': k})])
+    keep = pc.fill_null(pc.greater_equal(tbl.column('a'), -40), False)
+    one = tbl.filter(keep).select(['a', 'b', 's', 'd', 'g'])
+    names = one.schema.names
+    from collections import Counter
+    src = Counter(zip(*[one.column(n).to_pylist() for n in names]))
+    out = Counter(zip(*[got.column(n).to_pylist() for n in names]))
+    assert all(r in src and c == k * src[r] for r, c in out.items())           # whole rows, k copies each
+    here = {(r[4], r[2]) for r in out}                                         # keys (g, s) that landed on this rank
+    assert all(((r[4], r[2]) in here) == (r in out) for r in src)              # a key's rows all go the same way
+    all_keys = {(r[4], r[2]) for r in src}
+    assert 0.2 / k < len(here) / len(all_keys) < min(1.0, 2.5 / k)
+    # an aggregate over the partition: groups are complete, so per-group sums are exactly k times the single-rank sums
+    agg = lambda child: {'op': 'sort', 'keys': [{'expr': col('g')}, {'expr': col('s')}],
+                         'child': {'op': 'aggregate', 'keys': [{'name': 'g', 'expr': col('g')}, {'name': 's', 'expr': col('s')}],
+                                   'aggs': [{'name': 'sb', 'fn': 'sum', 'expr': col('b')}, {'name': 'c', 'fn': 'count_star'}], 'child': child}}
+    full = {(r['g'], r['s']): (r['sb'], r['c']) for r in pa.Table.from_batches([gpu_engine.execute(agg(plan['child']))]).to_pylist()}
+    part = pa.Table.from_batches([gpu_engine.execute(agg(plan), options={'exchange_loopback': k})]).to_pylist()
+    assert len(part) == len(here)
+    for r in part:
+        sb, c = full[(r['g'], r['s'])]
+        assert r['c'] == k * c and r['sb'] == (None if sb is None else k * sb)
