@@ -13,6 +13,7 @@ def main():
     ap.add_argument('--sf', type=float, default=1)
     ap.add_argument('--sales_days', type=int, default=182)
     ap.add_argument('--month', type=int, default=3)
+    ap.add_argument('--trace', action='store_true', help='production schedule (side streams) with the host timeline of every query')
     a = ap.parse_args()
     import __graft_entry__ as entry
     entry.build()
@@ -26,6 +27,18 @@ def main():
         eng.register_table(t, os.path.join(wh, t))
     for q in streams.SUBSET:
         plan = planner.plan_sql(streams.render(q, overrides={'MONTH': a.month, 'YEAR': 1998, 'MANUFACT': 606, 'MANAGER': 63}))
+        if a.trace:
+            for _ in range(3):
+                out = eng.execute({'root': plan['root']}, options={'trace': True})
+            st = eng.last_stats()
+            print('== %s: %d rows, device %.3f ms, host %.3f ms, %d launches' % (q, out.num_rows, st['device_ms'], st.get('host_ms', 0), st['launches']))
+            prev = 0.0
+            for label, t, wait in st.get('trace', []):
+                if label in ('end', 'scan:col_alloc'):
+                    continue
+                print('      t=%8.3f ms (+%.3f)  %s%s' % (t, t - prev, label, '   waited %.3f ms' % wait if wait >= 0 else ''))
+                prev = t
+            continue
         out = eng.execute({'root': plan['root']}, profile=True, options={'side_stream': False})
         st = eng.last_stats()
         print('== %s: %d rows, device %.3f ms, %d launches' % (q, out.num_rows, st['device_ms'], st['launches']))
