@@ -321,14 +321,16 @@ void launch_join_probe_multi_write(ColRef key, RowCount n, HashTable ht, int kin
 // The table is ALLOCATED for the upper bound of the input rows (cap_max slots) but SIZED on the device from the actual
 // row count: every kernel derives the same power-of-two capacity from n, so only that part is cleared, probed and
 // compacted, and the host never waits for the count of the join below.
+// (a power of two of at least 4/3 of the rows: the load factor stays below 0.75 even if every row is a group of its own,
+// and the table - cleared and compacted in full - is half the size "twice the rows" would make it for most row counts)
 __host__ __device__ __forceinline__ uint32_t agg_capacity(int64_t n, uint32_t cap_max) {
   uint32_t c = 64;
-  while ((int64_t)c < 2 * n && c < cap_max) c <<= 1;
+  while ((int64_t)c < n + n / 3 + 1 && c < cap_max) c <<= 1;
   return c < cap_max ? c : cap_max;
 }
 uint32_t agg_capacity_for(int64_t n_bound) {
   uint32_t c = 64;
-  while ((int64_t)c < 2 * n_bound && c < (1u << 31)) c <<= 1;
+  while ((int64_t)c < n_bound + n_bound / 3 + 1 && c < (1u << 31)) c <<= 1;
   return c;
 }
 
@@ -343,7 +345,11 @@ agg_init_kernel(const AggSpec* __restrict__ aggs, int naggs, const int* n_dev, i
   for (int a = 0; a < naggs; ++a) {
     const int fn = aggs[a].fn;
     const int64_t init = fn == AGG_MIN_I ? INT64_MAX : (fn == AGG_MAX_I ? INT64_MIN : 0);
-    for (int64_t i = t0; i < (int64_t)cap; i += stride) { acc[a * cap + i] = init; cnt[a * cap + i] = 0; }
+    // a count that shares another aggregate's counter owns no state of its own; plain counts never touch acc
+    if (fn != AGG_COUNT_REF) {
+      const bool counting = fn == AGG_COUNT || fn == AGG_COUNT_STAR;
+      for (int64_t i = t0; i < (int64_t)cap; i += stride) { if (!counting) acc[a * cap + i] = init; cnt[a * cap + i] = 0; }
+    }
     const int64_t vw = min((n + 31) / 32 + 1, valid_stride_words);
     for (int64_t i = t0; i < vw; i += stride) out_valid[a * valid_stride_words + i] = 0;
   }
