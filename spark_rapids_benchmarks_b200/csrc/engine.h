@@ -215,6 +215,16 @@ class Engine {
   void grow_slab_if_wanted();
   void* comm_ = nullptr;          // ncclComm_t of the exchange operator (nccl_dyn.h); null until comm_init
   int comm_rank_ = 0, comm_world_ = 1;
+  // Peer-push exchange (ops.cuh, PeerWindow): this rank's window in HBM, its peers' windows mapped through CUDA IPC at
+  // comm_init, and how often each half has been used (the arrival counters are monotonic).
+  uint8_t* xwin_ = nullptr;
+  std::vector<uint8_t*> xpeers_;
+  bool xpeer_ok_ = false;          // every rank mapped every window: the exchange may push over NVLink
+  int64_t xwin_half_bytes_ = 0;
+  int64_t xwin_uses_[2] = {0, 0}, xwin_seq_ = 0;
+  int64_t xwin_mb_ = 128;          // cfg exchange_window_mb: size of one window half
+  void ensure_window();
+  void close_windows();
   int64_t spec_retries_ = 0;    // queries re-run because a device-side size assumption failed (stats: speculation_retries)
   int64_t zero_dirty_ = -1;     // bytes of the slab's zeroed prefix the last query used (-1: unknown)
   std::vector<cudaEvent_t> event_pool_;

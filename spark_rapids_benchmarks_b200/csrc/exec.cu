@@ -267,6 +267,9 @@ struct Exec {
   // 128 k by default) with the row counts in their headers and no host round trip; by default the counts are all-gathered
   // and read back first, so that the segments carry exactly the rows there are
   bool exchange_single = false;
+  // options.exchange_peer=false: never the peer-push exchange (rows packed straight into the peers' windows over NVLink,
+  // row counts in the slot headers, no NCCL call and no host round trip) - the default whenever the windows are mapped
+  bool exchange_peer = true;
   bool topk_stream = true;       // options.topk_stream=false: ORDER BY ... LIMIT takes the multi-launch select / rank-sort route
   bool fused_scan = true;        // options.fused_scan=false: fact scans decode every column, then probe (decode_fast.cu + ops.cu)
   bool trace = false;            // options.trace: host timeline marks + time spent waiting in each stream sync
@@ -296,6 +299,7 @@ struct Exec {
       fused_scan = options->bool_or("fused_scan", true);
       topk_stream = options->bool_or("topk_stream", true);
       exchange_single = options->bool_or("exchange_single", false);
+      exchange_peer = options->bool_or("exchange_peer", true);
     }
     t_base = now_ms();
     if (!e.side_streams_.empty() && side_stream) {
@@ -398,7 +402,8 @@ struct Exec {
   void check_err_values(const int* h) {
     if (h[0]) fail("device kernel reported error code " + std::to_string(h[0]) +
                    " (3-6: malformed parquet page, 11: string projection outside its column buffer, 12: sort key wider than its declared maximum, 13: result string "
-                   "longer than its column's known maximum)");
+                   "longer than its column's known maximum, 14: exchanged string longer than its declared maximum, 15: ranks disagree on string widths, "
+                   "16: a peer's rows did not arrive within the exchange's time limit - re-create the communicator)");
     if (h[2]) throw SpeculationFailed();
     if (h[1] & 1) fail("hash join: duplicate keys on the build side (only unique build keys are supported)");
     if (h[1] & 2) fail("hash join: key equals the reserved empty marker");
@@ -2095,6 +2100,78 @@ struct Exec {
       }
     }
     if (node.str_or("mode", "gather") == "hash") return exchange_hash(node, in, flat, world, loop, st);
+    // ---- peer-push route (default between the GPUs of one node): no NCCL call, no host round trip.  The push kernel packs
+    // this rank's rows straight into its slot of every peer's window over NVLink and raises the peers' arrival counters;
+    // the unpack kernel waits for all `world` arrivals and copies the rows out.  More rows than a slot holds, or a failed
+    // size assumption on any rank, sends every rank to the second attempt (exact NCCL route).
+    if (speculate && exchange_peer && ncols <= kXchgHeader / 4 - 2 && world <= kPeerMaxWorld && (loop > 0 || e.xpeer_ok_)) {
+      std::vector<XCol> proto(ncols);
+      bool ok_types = true;
+      int64_t row_bytes = 0;
+      for (int c = 0; c < ncols; ++c) {
+        XCol& x = proto[c];
+        memset(&x, 0, sizeof x);
+        const LType& t = flat[c].lt;
+        x.kind = t.kind == LType::STR ? 2 : (t.dtype() == DT_I32 ? 0 : 1);
+        x.maxlen = t.kind == LType::STR ? t.maxlen : 0;
+        if (t.kind == LType::STR && t.maxlen <= 0) ok_types = false;
+        row_bytes += 1 + (x.kind == 1 ? 8 : 4) + x.maxlen;
+      }
+      if (ok_types) {
+        e.ensure_window();
+        PeerWindow w;
+        memset(&w, 0, sizeof w);
+        w.world = world;
+        w.me = loop > 0 ? 0 : e.comm_rank_;
+        w.half_bytes = e.xwin_half_bytes_;
+        w.slot_bytes = (e.xwin_half_bytes_ / world) & ~int64_t(255);
+        w.ctrl_bytes = kPeerCtrlBytes;
+        for (int p = 0; p < world; ++p) w.win[p] = loop > 0 ? e.xwin_ : e.xpeers_[p];
+        // rows a slot holds: the layout is per column, so solve for it (and keep the bound modest: 256 k rows)
+        int64_t cap_rows = std::min<int64_t>((w.slot_bytes - kXchgHeader - 256 - 48 * ncols) / std::max<int64_t>(row_bytes, 1), int64_t(256) << 10);
+        while (cap_rows > 0 && kXchgHeader + seg_layout(proto, cap_rows).bytes > w.slot_bytes) --cap_rows;
+        if (cap_rows >= 1) {
+          SegLayout L = seg_layout(proto, cap_rows);
+          for (int c = 0; c < ncols; ++c) { proto[c].off_valid = L.off_valid[c]; proto[c].off_data = L.off_data[c]; proto[c].off_aux = L.off_aux[c]; }
+          std::vector<XCol> mine = proto, dst(ncols);
+          for (int c = 0; c < ncols; ++c) { mine[c].data = flat[c].data; mine[c].valid = flat[c].valid; mine[c].strbase = flat[c].strbase; }
+          const int64_t Nmax = cap_rows * world;
+          const int64_t vwords = (Nmax + 31) / 32 + 1;
+          Batch out;
+          out.n_max = Nmax;
+          out.n_dev = ar.zeros<int>(1);
+          for (int c = 0; c < ncols; ++c) {
+            Column oc;
+            oc.name = flat[c].name;
+            oc.lt = flat[c].lt;
+            const int wd = proto[c].kind == 0 ? 4 : 8;
+            oc.data = ar.alloc(Nmax * wd);
+            oc.valid = ar.zeros<uint32_t>(vwords);
+            oc.strbase = proto[c].kind == 2 ? e.xwin_ : nullptr;
+            out.cols.push_back(oc);
+            memset(&dst[c], 0, sizeof(XCol));
+            dst[c].data = oc.data;
+            dst[c].valid = oc.valid;
+            dst[c].kind = proto[c].kind;
+          }
+          std::vector<XCol> all3;
+          all3.insert(all3.end(), mine.begin(), mine.end());
+          all3.insert(all3.end(), proto.begin(), proto.end());
+          all3.insert(all3.end(), dst.begin(), dst.end());
+          XCol* d_desc = ar.alloc_n<XCol>((int64_t)all3.size());
+          ar.upload(d_desc, all3.data(), (int64_t)(all3.size() * sizeof(XCol)));
+          const int half = (int)(e.xwin_seq_++ & 1);
+          const uint32_t wanted = (uint32_t)(++e.xwin_uses_[half] * world);
+          int* ticket = ar.zeros<int>(1);
+          launch_peer_push(d_desc, d_desc + ncols, ncols, in.rc(), cap_rows, w, half, loop > 0 ? 1 : 0, ticket, err, s);
+          launch_peer_unpack(d_desc + ncols, d_desc + 2 * ncols, ncols, w, half, wanted, cap_rows, out.n_dev, err, s);
+          launches += 2;
+          stats[st].op = "exchange:peer";
+          end_stat_rows(st, row_bytes, RowCount{out.n_dev, Nmax});
+          return out;
+        }
+      }
+    }
     // ---- speculative route: ONE collective and no host round trip.  Every rank sends a fixed-capacity segment whose
     // header holds its row count; the unpack kernel reads the headers on the device.  More rows than the capacity raise
     // err[2] and the query runs again on the exact two-step route below.
@@ -2853,6 +2930,7 @@ Engine::Engine(const Json& cfg) {
   keep_host_ = cfg.bool_or("keep_host", false);
   rank = (int)cfg.int_or("rank", 0);
   world = (int)cfg.int_or("world", 1);
+  xwin_mb_ = std::max<int64_t>(cfg.int_or("exchange_window_mb", 128), 1);
   if (world < 1 || rank < 0 || rank >= world) fail("engine config: bad rank/world");
   int ndev = 0;
   cudaError_t ce = cudaGetDeviceCount(&ndev);
@@ -2934,10 +3012,81 @@ void Engine::comm_init(const std::string& id_bytes, int rank_in, int world_in) {
   NcclUniqueId id;
   memcpy(id.internal, id_bytes.data(), sizeof id.internal);
   nccl_check(nccl_api().CommInitRank(&comm_, world_in, id, rank_in), "ncclCommInitRank");
+  // ---- windows of the peer-push exchange: allocate mine, all-gather the IPC handles, map the peers'.  Any failure
+  // (no peer access, a refused mapping) leaves the NCCL exchange in charge - on every rank, or on none.
+  close_windows();
+  xpeer_ok_ = false;
+  if (world_in > kPeerMaxWorld) return;
+  ensure_window();
+  cudaIpcMemHandle_t mine;
+  int ok = cudaIpcGetMemHandle(&mine, xwin_) == cudaSuccess ? 1 : 0;
+  if (!ok) cudaGetLastError();
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+  const size_t rec = 64 + 8;
+  std::vector<uint8_t> host(rec * world_in, 0);
+  memcpy(host.data() + rec * rank_in, &mine, 64);
+  memcpy(host.data() + rec * rank_in + 64, &ok, sizeof ok);
+  uint8_t* d_all = nullptr;
+  NDS_CUDA(cudaMalloc(&d_all, rec * world_in));
+  NDS_CUDA(cudaMemcpy(d_all, host.data(), rec * world_in, cudaMemcpyHostToDevice));
+  nccl_check(nccl_api().AllGather(d_all + rec * rank_in, d_all, rec, kNcclChar, comm_, stream_), "ncclAllGather(window handles)");
+  NDS_CUDA(cudaStreamSynchronize(stream_));
+  NDS_CUDA(cudaMemcpy(host.data(), d_all, rec * world_in, cudaMemcpyDeviceToHost));
+  xpeers_.assign(world_in, nullptr);
+  xpeers_[rank_in] = xwin_;
+  int all_ok = 1;
+  for (int p = 0; p < world_in; ++p) {
+    int pok = 0;
+    memcpy(&pok, host.data() + rec * p + 64, sizeof pok);
+    if (!pok) all_ok = 0;
+  }
+  if (all_ok)
+    for (int p = 0; p < world_in && all_ok; ++p) {
+      if (p == rank_in) continue;
+      cudaIpcMemHandle_t h;
+      memcpy(&h, host.data() + rec * p, 64);
+      void* ptr = nullptr;
+      if (cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { cudaGetLastError(); all_ok = 0; break; }
+      xpeers_[p] = (uint8_t*)ptr;
+    }
+  // second round: a rank that could not map a window must switch the others off too
+  int* d_flag = reinterpret_cast<int*>(d_all);
+  std::vector<int> flags(world_in, 0);
+  flags[rank_in] = all_ok;
+  NDS_CUDA(cudaMemcpy(d_flag, flags.data(), sizeof(int) * world_in, cudaMemcpyHostToDevice));
+  nccl_check(nccl_api().AllGather(d_flag + rank_in, d_flag, sizeof(int), kNcclChar, comm_, stream_), "ncclAllGather(window status)");
+  NDS_CUDA(cudaStreamSynchronize(stream_));
+  NDS_CUDA(cudaMemcpy(flags.data(), d_flag, sizeof(int) * world_in, cudaMemcpyDeviceToHost));
+  cudaFree(d_all);
+  xpeer_ok_ = true;
+  for (int f : flags) xpeer_ok_ = xpeer_ok_ && f != 0;
+  if (!xpeer_ok_) {
+    for (int p = 0; p < world_in; ++p)
+      if (p != rank_in && xpeers_[p]) { cudaIpcCloseMemHandle(xpeers_[p]); xpeers_[p] = nullptr; }
+  }
+}
+
+// The local window: control block (arrival counters, zeroed once) + two halves.
+void Engine::ensure_window() {
+  if (xwin_) return;
+  xwin_half_bytes_ = xwin_mb_ << 20;
+  NDS_CUDA(cudaMalloc(reinterpret_cast<void**>(&xwin_), (size_t)(kPeerCtrlBytes + 2 * xwin_half_bytes_)));
+  NDS_CUDA(cudaMemset(xwin_, 0, (size_t)kPeerCtrlBytes));
+  xwin_uses_[0] = xwin_uses_[1] = 0;
+  xwin_seq_ = 0;
+}
+
+void Engine::close_windows() {
+  for (size_t p = 0; p < xpeers_.size(); ++p)
+    if (xpeers_[p] && xpeers_[p] != xwin_) cudaIpcCloseMemHandle(xpeers_[p]);
+  xpeers_.clear();
+  if (xwin_) { cudaFree(xwin_); xwin_ = nullptr; }
+  xpeer_ok_ = false;
 }
 
 Engine::~Engine() {
   cudaSetDevice(device);
+  close_windows();
   if (comm_) { nccl_api().CommDestroy(comm_); comm_ = nullptr; }
   for (cudaEvent_t e : event_pool_) cudaEventDestroy(e);
   std::vector<std::string> names;

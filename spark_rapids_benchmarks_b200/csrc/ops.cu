@@ -1614,6 +1614,135 @@ void launch_exchange_unpack_dev(const XCol* proto, const XCol* dst, int ncols, i
   NDS_CUDA(cudaGetLastError());
 }
 
+// ---- peer-push exchange: pack into every peer's window over NVLink, arrive, wait, unpack (ops.cuh, PeerWindow)
+__device__ __forceinline__ uint8_t* peer_slot(const PeerWindow& w, int rank, int half, int slot) {
+  return w.win[rank] + w.ctrl_bytes + (int64_t)half * w.half_bytes + (int64_t)slot * w.slot_bytes;
+}
+__device__ __forceinline__ uint32_t* peer_arrivals(const PeerWindow& w, int rank, int half) {
+  return reinterpret_cast<uint32_t*>(w.win[rank] + half * 64);
+}
+
+__global__ void __launch_bounds__(kThreads)
+peer_push_kernel(const XCol* __restrict__ cols, const XCol* __restrict__ proto, int ncols, const int* n_dev, int64_t n_host, int64_t cap_rows,
+                 const PeerWindow w, int half, int loopback, int* ticket, int* err) {
+  __shared__ int s_last;
+  int64_t n = row_count(n_dev, n_host);
+  const bool over = n > cap_rows;
+  if (over) n = 0;                                   // nothing is sent: the header says why
+  // loopback (one GPU, tests): this rank plays every sender - it fills all `world` slots of its own window
+  const int ntargets = w.world;
+  for (int t = 0; t < ntargets; ++t) {
+    uint8_t* slot = loopback ? peer_slot(w, w.me, half, t) : peer_slot(w, t, half, w.me);
+    uint8_t* body = slot + kXchgHeader;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+      for (int c = 0; c < ncols; ++c) {
+        const XCol x = cols[c];
+        const XCol pr = proto[c];
+        const bool ok = !x.valid || ((x.valid[i >> 5] >> (i & 31)) & 1u);
+        body[pr.off_valid + i] = ok ? 1 : 0;
+        if (x.kind == 0) reinterpret_cast<int32_t*>(body + pr.off_data)[i] = ok ? reinterpret_cast<const int32_t*>(x.data)[i] : 0;
+        else if (x.kind == 1) reinterpret_cast<int64_t*>(body + pr.off_data)[i] = ok ? reinterpret_cast<const int64_t*>(x.data)[i] : 0;
+        else {
+          const StrView v = ok ? reinterpret_cast<const StrView*>(x.data)[i] : 0;
+          int len = (int)(v >> 32);
+          if (len > pr.maxlen) { if (err) atomicExch(err, 14); len = pr.maxlen; }
+          reinterpret_cast<int32_t*>(body + pr.off_data)[i] = len;
+          const uint8_t* q = x.strbase + (uint32_t)v;
+          uint8_t* o = body + pr.off_aux + i * (int64_t)pr.maxlen;
+          for (int b = 0; b < len; ++b) o[b] = q[b];
+        }
+      }
+    }
+  }
+  // every CTA's rows are out (system-wide) before the last CTA raises the arrival counters
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(ticket, 1) == (int)gridDim.x - 1;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence_system();
+  for (int t = threadIdx.x; t < ntargets; t += blockDim.x) {
+    uint8_t* slot = loopback ? peer_slot(w, w.me, half, t) : peer_slot(w, t, half, w.me);
+    int32_t* h = reinterpret_cast<int32_t*>(slot);
+    for (int c = 0; c < ncols && c < kXchgHeader / 4 - 2; ++c) h[1 + c] = proto[c].kind == 2 ? proto[c].maxlen : 0;
+    h[kXchgHeader / 4 - 1] = (err[2] || over) ? 1 : 0;
+    h[0] = over ? -1 : (int32_t)n;
+    __threadfence_system();
+    atomicAdd_system(peer_arrivals(w, loopback ? w.me : t, half), 1u);
+  }
+}
+void launch_peer_push(const XCol* cols, const XCol* proto, int ncols, RowCount n, int64_t cap_rows, PeerWindow w, int half, int loopback,
+                      int* ticket, int* err, cudaStream_t s) {
+  peer_push_kernel<<<grid_for(std::min<int64_t>(n.host, cap_rows), kThreads, 148 * 2), kThreads, 0, s>>>(cols, proto, ncols, n.dev, n.host, cap_rows, w,
+                                                                                                       half, loopback, ticket, err);
+  NDS_CUDA(cudaGetLastError());
+}
+
+__global__ void __launch_bounds__(kThreads)
+peer_unpack_kernel(const XCol* __restrict__ proto, const XCol* __restrict__ dst, int ncols, const PeerWindow w, int half, uint32_t arrivals_wanted,
+                   int* total_out, int* err) {
+  __shared__ int s_ok;
+  // wait (bounded: ~4 s of SM clocks) until every rank's push into this half has arrived
+  if (threadIdx.x == 0) {
+    volatile uint32_t* arr = peer_arrivals(w, w.me, half);
+    const long long t0 = clock64();
+    int ok = 1;
+    while ((int32_t)(*arr - arrivals_wanted) < 0) {
+      if (clock64() - t0 > 8000000000LL) { ok = 0; break; }
+      __nanosleep(100);
+    }
+    __threadfence_system();
+    s_ok = ok;
+    if (!ok) atomicExch(err, 16);
+  }
+  __syncthreads();
+  if (!s_ok) return;
+  const int r = blockIdx.y;
+  int64_t before = 0, total = 0;
+  bool failed = false;
+  for (int q = 0; q < w.world; ++q) {
+    const volatile int32_t* h = reinterpret_cast<const volatile int32_t*>(peer_slot(w, w.me, half, q));
+    const int64_t nq = h[0];
+    if (nq < 0 || h[kXchgHeader / 4 - 1]) failed = true;
+    if (q < r && nq > 0) before += nq;
+    if (nq > 0) total += nq;
+    if (blockIdx.x == 0 && threadIdx.x == 0 && r == 0)
+      for (int c = 0; c < ncols && c < kXchgHeader / 4 - 2; ++c)
+        if (proto[c].kind == 2 && h[1 + c] != proto[c].maxlen) atomicExch(err, 15);
+  }
+  if (failed) {      // some rank could not send (too many rows) or had a failed size assumption: every rank runs the query again
+    if (blockIdx.x == 0 && threadIdx.x == 0 && r == 0) { atomicExch(err + 2, 1); *total_out = 0; }
+    return;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && r == 0) *total_out = (int)total;
+  const uint8_t* slot = peer_slot(w, w.me, half, r);
+  const int64_t n = reinterpret_cast<const volatile int32_t*>(slot)[0];
+  const uint8_t* body = slot + kXchgHeader;
+  const uint8_t* base = w.win[w.me];
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t o = before + i;
+    for (int c = 0; c < ncols; ++c) {
+      const XCol x = proto[c];
+      const XCol d = dst[c];
+      const bool ok = __ldcg(body + x.off_valid + i) != 0;
+      if (ok) atomicOr(const_cast<uint32_t*>(d.valid) + (o >> 5), 1u << (o & 31));
+      if (x.kind == 0) reinterpret_cast<int32_t*>(const_cast<void*>(d.data))[o] = __ldcg(reinterpret_cast<const int32_t*>(body + x.off_data) + i);
+      else if (x.kind == 1) reinterpret_cast<int64_t*>(const_cast<void*>(d.data))[o] = __ldcg(reinterpret_cast<const long long*>(body + x.off_data) + i);
+      else {
+        const uint32_t len = (uint32_t)__ldcg(reinterpret_cast<const int32_t*>(body + x.off_data) + i);
+        const uint64_t off = (uint64_t)(body + x.off_aux + i * (int64_t)x.maxlen - base);
+        reinterpret_cast<StrView*>(const_cast<void*>(d.data))[o] = ((uint64_t)len << 32) | (uint64_t)(uint32_t)off;
+      }
+    }
+  }
+}
+void launch_peer_unpack(const XCol* proto, const XCol* dst, int ncols, PeerWindow w, int half, uint32_t arrivals_wanted, int64_t cap_rows,
+                        int* total_out, int* err, cudaStream_t s) {
+  peer_unpack_kernel<<<dim3(grid_for(std::max<int64_t>(cap_rows, 1), kThreads, 16), w.world), kThreads, 0, s>>>(proto, dst, ncols, w, half,
+                                                                                                               arrivals_wanted, total_out, err);
+  NDS_CUDA(cudaGetLastError());
+}
+
 // ------------------------------------------------------------------ result export, small results
 // One launch packs a whole (small) result into one contiguous buffer, so that it reaches the host with ONE copy and
 // ONE synchronisation, row count included: block b handles segment b.

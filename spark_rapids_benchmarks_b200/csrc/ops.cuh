@@ -271,6 +271,24 @@ constexpr int kXchgHeader = 64;
 void launch_exchange_pack_dev(const XCol* cols, int ncols, RowCount n, int64_t cap_rows, uint8_t* out, int* err, cudaStream_t s);
 void launch_exchange_unpack_dev(const XCol* proto, const XCol* dst, int ncols, int world, int64_t cap_rows, int64_t seg_bytes,
                                 const uint8_t* recv, int* total_out, int* err, cudaStream_t s);
+// Peer-push exchange (all-gather without NCCL and without a host round trip): every rank owns a window in its HBM that
+// its peers map through CUDA IPC; a rank's push kernel packs its rows straight into slot `me` of every peer's window
+// over NVLink and then raises that peer's arrival counter; the unpack kernel of each rank waits - bounded - until all
+// `world` pushes of this use of the window half have arrived and copies the rows out.  The window has two halves used
+// alternately, each with `world` slots of slot_bytes (a kXchgHeader header, then the columns laid out for cap_rows rows).
+struct PeerWindow {
+  uint8_t* win[16];            // base of every rank's window as mapped into this process (win[me] = the local one)
+  int32_t world, me;
+  int64_t half_bytes, slot_bytes, ctrl_bytes;
+};
+constexpr int kPeerMaxWorld = 16;
+constexpr int64_t kPeerCtrlBytes = 256;      // per window: arrival counter of half 0 at +0, of half 1 at +64 (uint32, monotonic)
+// header of a slot: [0] rows (-1: the sender had more rows than a slot holds), [1 + c] string slot width of column c,
+// [15] the sender's "a size assumption failed" flag
+void launch_peer_push(const XCol* cols, const XCol* proto, int ncols, RowCount n, int64_t cap_rows, PeerWindow w, int half, int loopback,
+                      int* ticket, int* err, cudaStream_t s);
+void launch_peer_unpack(const XCol* proto, const XCol* dst, int ncols, PeerWindow w, int half, uint32_t arrivals_wanted, int64_t cap_rows,
+                        int* total_out, int* err, cudaStream_t s);
 // Small-result export: segment kinds 0 = raw bytes (multiple of 4), 1 = string column -> int32 offsets at dst_off
 // and characters at aux_off (cap bytes available; error 13 if exceeded), 2 = the row count as one int.
 struct ExportSeg {

@@ -27,7 +27,8 @@ def main():
         for source in ('hbm', 'host'):
             sess.source = source
             got = sess.sql(sql).toArrow().to_pylist()
-            assert any(o['op'] == 'exchange' for o in sess.last_stats['ops']), 'the native exchange did not run'
+            # the default exchange between the GPUs of a node: rows pushed into the peers' windows over NVLink (CUDA IPC)
+            assert any(o['op'] == 'exchange:peer' for o in sess.last_stats['ops']), 'the peer-push exchange did not run: %s' % [o['op'] for o in sess.last_stats['ops']]
             if rank == 0:
                 exp = oq.run_query(query, sql, wh).to_pylist()
                 assert len(got) == len(exp), (query, len(got), len(exp))
@@ -43,9 +44,11 @@ def main():
     import pyarrow as pa
     for query in ('query3', 'query7'):
         plan = sess.plan(streams.render(query, overrides={'MANUFACT': 606, 'MANAGER': 63, 'MONTH': 1, 'YEAR': 1998}))
-        two = pa.Table.from_batches([sess.engine.execute({'root': plan['fused']})]).to_pylist()
-        one = pa.Table.from_batches([sess.engine.execute({'root': plan['fused']}, options={'exchange_single': True})]).to_pylist()
-        assert one == two and len(one) > 0, query
+        two = pa.Table.from_batches([sess.engine.execute({'root': plan['fused']}, options={'exchange_peer': False})]).to_pylist()
+        assert any(o['op'] == 'exchange' for o in sess.engine.last_stats()['ops']), 'the NCCL exchange did not run'
+        one = pa.Table.from_batches([sess.engine.execute({'root': plan['fused']}, options={'exchange_peer': False, 'exchange_single': True})]).to_pylist()
+        peer = pa.Table.from_batches([sess.engine.execute({'root': plan['fused']})]).to_pylist()
+        assert one == two and peer == two and len(one) > 0, query
     # Spark's own plan shape: partial aggregate -> hash-partition all-to-all (grouped ncclSend / ncclRecv) -> every rank merges and
     # ranks its own groups -> gather of the per-rank top rows -> final ranking.  Same rows as the all-gather form.
     for query in streams.SUBSET:

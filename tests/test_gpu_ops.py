@@ -302,18 +302,21 @@ def test_sort_topk_candidate_overflow_falls_back(gpu_engine):
     gpu_engine.drop_table('ovf')
 
 
-@pytest.mark.parametrize('single', [True, False])
+XROUTES = {'peer': {}, 'single': {'exchange_peer': False, 'exchange_single': True}, 'exact': {'exchange_peer': False}}
+
+
+@pytest.mark.parametrize('route', sorted(XROUTES))
 @pytest.mark.parametrize('k', [2, 3])
-def test_exchange_loopback_pack_unpack(gpu_engine, tbl, k, single):
+def test_exchange_loopback_pack_unpack(gpu_engine, tbl, k, route):
     """The exchange node's pack -> (all-gather) -> unpack path on one GPU: options.exchange_loopback=k stands in
     for k ranks that all hold this rank's rows, so the result is the input k times, in rank order - integers,
     decimals, strings (empty and long) and nulls included.  The filter leaves the row count on the device."""
     plan = {'op': 'exchange',
             'child': {'op': 'filter', 'cond': fn('ge', col('g'), lit(3)),
                       'child': {'op': 'scan', 'table': 't', 'columns': ['a', 'b', 's', 'd', 'g']}}}
-    # single: one collective of fixed-capacity segments with the row counts in their headers (no host round trip);
-    # otherwise the counts are read back first and the segments sized exactly
-    xopts = {'exchange_loopback': k, 'exchange_single': single}
+    # peer (default): rows packed straight into the peers' windows, row counts in the slot headers, no host round trip;
+    # single: one NCCL collective of fixed-capacity segments; exact: the counts are read back first, segments sized exactly
+    xopts = dict({'exchange_loopback': k}, **XROUTES[route])
     got = pa.Table.from_batches([gpu_engine.execute(plan, options=xopts)])
     keep = pc.fill_null(pc.greater_equal(tbl.column('g'), 3), False)
     one = tbl.filter(keep).select(['a', 'b', 's', 'd', 'g'])
@@ -341,15 +344,15 @@ def test_exchange_loopback_pack_unpack(gpu_engine, tbl, k, single):
 def test_exchange_empty_input(gpu_engine, tbl):
     plan = {'op': 'exchange', 'child': {'op': 'filter', 'cond': fn('gt', col('g'), lit(1000)),
                                         'child': {'op': 'scan', 'table': 't', 'columns': ['a', 's', 'g']}}}
-    for single in (True, False):
-        got = gpu_engine.execute(plan, options={'exchange_loopback': 2, 'exchange_single': single})
+    for route in XROUTES.values():
+        got = gpu_engine.execute(plan, options=dict({'exchange_loopback': 2}, **route))
         assert got.num_rows == 0 and got.schema.names == ['a', 's', 'g']
 
 
 def test_exchange_beyond_the_speculative_capacity_is_retried(gpu_engine):
-    """More rows than a single-collective segment holds (128 k): the pack kernel reports it and the query runs again with
-    the counts read back - same rows."""
-    n = 200000
+    """More rows than a speculative segment holds (peer window slot: 256 k rows, single collective: 128 k): the pack kernel
+    reports it and the query runs again with the counts read back - same rows."""
+    n = 300000
     rid = np.arange(n, dtype=np.int64)
     gpu_engine.register_arrow('big', pa.table({'rid': rid, 'v': (rid * 7 % 1000).astype(np.int32)}))
     gpu_engine.execute({'op': 'scan', 'table': 'big', 'columns': ['rid']})
@@ -357,9 +360,19 @@ def test_exchange_beyond_the_speculative_capacity_is_retried(gpu_engine):
     plan = {'op': 'aggregate', 'keys': [], 'aggs': [{'name': 'n', 'fn': 'count_star'}, {'name': 's', 'fn': 'sum', 'expr': col('rid')}],
             'child': {'op': 'exchange', 'child': {'op': 'filter', 'cond': fn('ge', col('v'), lit(0)),
                                                   'child': {'op': 'scan', 'table': 'big', 'columns': ['rid', 'v']}}}}
-    got = pa.Table.from_batches([gpu_engine.execute(plan, options={'exchange_loopback': 2, 'exchange_single': True})]).to_pylist()
-    assert got == [{'n': 2 * n, 's': 2 * int(rid.sum())}]
-    assert gpu_engine.last_stats()['speculation_retries'] == retries0 + 1
+    for i, route in enumerate(('peer', 'single')):
+        got = pa.Table.from_batches([gpu_engine.execute(plan, options=dict({'exchange_loopback': 2}, **XROUTES[route]))]).to_pylist()
+        assert got == [{'n': 2 * n, 's': 2 * int(rid.sum())}], route
+        assert gpu_engine.last_stats()['speculation_retries'] == retries0 + 1 + i, route
+    # the same exchange twice more: the window halves alternate and their arrival counters keep counting
+    small = {'op': 'aggregate', 'keys': [], 'aggs': [{'name': 'n', 'fn': 'count_star'}],
+             'child': {'op': 'exchange', 'child': {'op': 'filter', 'cond': fn('lt', col('v'), lit(10)),
+                                                   'child': {'op': 'scan', 'table': 'big', 'columns': ['rid', 'v']}}}}
+    exp_n = 3 * int(((rid * 7 % 1000) < 10).sum())
+    for _ in range(5):
+        got = pa.Table.from_batches([gpu_engine.execute(small, options={'exchange_loopback': 3})]).to_pylist()
+        assert got == [{'n': exp_n}]
+        assert any(o['op'] == 'exchange:peer' for o in gpu_engine.last_stats()['ops'])
     gpu_engine.drop_table('big')
 
 

@@ -13,6 +13,7 @@ def main():
     ap.add_argument('--sf', type=float, default=1)
     ap.add_argument('--sales_days', type=int, default=182)
     ap.add_argument('--month', type=int, default=3)
+    ap.add_argument('--loopback', type=int, default=0, help='run the distributed (partial -> exchange -> merge) plan with exchange_loopback=k')
     ap.add_argument('--trace', action='store_true', help='production schedule (side streams) with the host timeline of every query')
     a = ap.parse_args()
     import __graft_entry__ as entry
@@ -26,10 +27,12 @@ def main():
     for t in tables:
         eng.register_table(t, os.path.join(wh, t))
     for q in streams.SUBSET:
-        plan = planner.plan_sql(streams.render(q, overrides={'MONTH': a.month, 'YEAR': 1998, 'MANUFACT': 606, 'MANAGER': 63}))
+        plan = planner.plan_sql(streams.render(q, overrides={'MONTH': a.month, 'YEAR': 1998, 'MANUFACT': 606, 'MANAGER': 63}), distributed=a.loopback > 0)
+        if a.loopback > 0:
+            plan['root'] = plan['fused']
         if a.trace:
             for _ in range(3):
-                out = eng.execute({'root': plan['root']}, options={'trace': True})
+                out = eng.execute({'root': plan['root']}, options=dict({'trace': True}, **({'exchange_loopback': a.loopback} if a.loopback else {})))
             st = eng.last_stats()
             print('== %s: %d rows, device %.3f ms, host %.3f ms, %d launches' % (q, out.num_rows, st['device_ms'], st.get('host_ms', 0), st['launches']))
             prev = 0.0
