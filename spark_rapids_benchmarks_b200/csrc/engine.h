@@ -216,7 +216,7 @@ class Engine {
   void* comm_ = nullptr;          // ncclComm_t of the exchange operator (nccl_dyn.h); null until comm_init
   int comm_rank_ = 0, comm_world_ = 1;
   // Peer-push exchange (ops.cuh, PeerWindow): this rank's window in HBM, its peers' windows mapped through CUDA IPC at
-  // comm_init, and how often each half has been used (the arrival counters are monotonic).
+  // comm_init, and how many arrivals each half has been promised so far (the arrival counters are monotonic).
   uint8_t* xwin_ = nullptr;
   std::vector<uint8_t*> xpeers_;
   bool xpeer_ok_ = false;          // every rank mapped every window: the exchange may push over NVLink

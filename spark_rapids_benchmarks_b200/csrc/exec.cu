@@ -2161,7 +2161,7 @@ struct Exec {
           XCol* d_desc = ar.alloc_n<XCol>((int64_t)all3.size());
           ar.upload(d_desc, all3.data(), (int64_t)(all3.size() * sizeof(XCol)));
           const int half = (int)(e.xwin_seq_++ & 1);
-          const uint32_t wanted = (uint32_t)(++e.xwin_uses_[half] * world);
+          const uint32_t wanted = (uint32_t)(e.xwin_uses_[half] += world);      // arrivals this half has seen, this use included
           int* ticket = ar.zeros<int>(1);
           launch_peer_push(d_desc, d_desc + ncols, ncols, in.rc(), cap_rows, w, half, loop > 0 ? 1 : 0, ticket, err, s);
           launch_peer_unpack(d_desc + ncols, d_desc + 2 * ncols, ncols, w, half, wanted, cap_rows, out.n_dev, err, s);
