@@ -229,7 +229,7 @@ def rows_match(got, exp, rel_tol=1e-5):
     return True
 
 
-OP_KINDS = ('decode_kernel', 'scan_probe', 'gather_decode', 'filter', 'project', 'join_build', 'join_probe', 'join_probe_chain',
+OP_KINDS = ('decode_kernel', 'def_levels', 'scan_probe', 'gather_decode', 'filter', 'project', 'join_build', 'join_probe', 'join_probe_chain',
             'aggregate', 'sort', 'exchange', 'dim_pipeline')
 
 
