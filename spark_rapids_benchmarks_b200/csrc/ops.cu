@@ -787,7 +787,7 @@ __device__ __forceinline__ void topk_publish(const TopkState& st, int kept, int 
   if (tid == 0) counts[slot] = kept;
 }
 
-static_assert(592 / 16 <= kTopkMaxSrc, "final merge fan-in");
+static_assert((148 + 15) / 16 <= kTopkMaxSrc, "final merge fan-in");
 constexpr int kTopkGroup = 16;      // CTAs whose survivors one CTA merges before the final merge (two-level last-CTA pattern)
 
 __global__ void __launch_bounds__(kTopkThreads)
@@ -863,7 +863,9 @@ topk_stream_kernel(const Prog* __restrict__ progs, const SortKey* __restrict__ k
 
 int topk_stream_ctas(int64_t n_bound) {
   int64_t g = (n_bound + kTopkThreads - 1) / kTopkThreads;
-  return (int)(g < 1 ? 1 : (g > 592 ? 592 : g));
+  // at most one CTA per SM: the candidate areas can take most of an SM's shared memory, and a CTA without rows still costs a
+  // scheduling slot, a publish and a ticket
+  return (int)(g < 1 ? 1 : (g > 148 ? 148 : g));
 }
 int topk_stream_groups(int ctas) { return (ctas + kTopkGroup - 1) / kTopkGroup; }
 static bool topk_areas_in_smem(int Bw) { return (int64_t)2 * kTopkCand * Bw * 8 <= kTopkSmemMax; }
