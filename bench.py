@@ -296,6 +296,8 @@ def main():
                 st = sess.last_stats
                 launches += st['launches']
                 eng_ms += st['device_ms']
+                for o in st['ops']:
+                    o['query'] = name
                 ops.extend(st['ops'])
         return launches, ops, eng_ms
 
@@ -455,7 +457,8 @@ def main():
         top = [o for o in cand if o['bytes'] == big]
         avg_ms = sum(o['ms'] for o in top) / len(top)
         ach = big / (avg_ms * 1e-3) / 1e9
-        in_step = [o for o in ops if o['op'].split(':')[0] == dom and o['ms'] > 0 and o['bytes'] == big]
+        # the same launch inside the timed schedule (the untimed statistics repeat): same statement, same operator
+        in_step = [o for o in ops if o['op'].split(':')[0] == dom and o['ms'] > 0 and o.get('query') == top[0].get('query')]
         in_us = sum(o['ms'] for o in in_step) / max(len(in_step), 1) * 1000.0
         traffic, traffic_src = None, None
         tp = os.path.join(ROOT, 'profiles', 'kernel_traffic.json')
@@ -466,7 +469,8 @@ def main():
                     traffic, traffic_src = tj.get('dram_bytes_per_launch'), 'static: ' + tj.get('source', 'profiles/')
             except Exception:
                 pass
-        kernel_names = {'scan_probe': 'def_pages_kernel + scan_probe_kernel (fused page decode -> join-chain probe, fact scan)',
+        kernel_names = {'scan_probe': 'scan_probe_kernel (fused page decode -> join-chain probe over the fact scan; the def-level kernel that '
+                                      'precedes it is the def_levels row of per_operator)',
                         'decode_kernel': 'def_pages_kernel + rows_pages_kernel (split page decode, one launch each)'}
         dec_all = [o for o in serial_ops if o['op'].split(':')[0] == dom and o['ms'] > 0]
         roof = {'bound': 'hbm', 'kernel': kernel_names[dom], 'achieved': ach, 'peak': peak, 'unit': 'GB/s', 'frac': ach / peak,
