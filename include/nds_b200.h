@@ -79,7 +79,10 @@ NDS_API int nds_engine_execute(nds_engine* e, const char* plan_json, struct Arro
  * torch.distributed, MPI, a file), and every process calls nds_engine_comm_init with its rank - a collective call.
  * Replaces: the shuffle between HashAggregate(partial) and HashAggregate(final) that Spark inserts for
  * `spark.sql.shuffle.partitions`   /root/reference/nds/power_run_gpu.template:29, power_run_cpu.template:27
- * (the reference has no call site of its own - the exchange is inside spark.sql()). */
+ * (the reference has no call site of its own - the exchange is inside spark.sql()).
+ * nds_engine_comm_init also allocates this engine's exchange window in device memory and maps every peer's window through
+ * CUDA IPC (all ranks on one node): the default exchange then packs rows straight into the peers' windows over NVLink and
+ * uses NCCL only as the fallback / second attempt.  Every rank must execute the same plans in the same order. */
 #define NDS_COMM_ID_BYTES 128
 NDS_API int nds_engine_comm_unique_id(nds_engine* e, char* out, int64_t out_len);
 NDS_API int nds_engine_comm_init(nds_engine* e, const char* id, int64_t id_len, int rank, int world);
