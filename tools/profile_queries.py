@@ -84,7 +84,7 @@ def main():
                 e[1] += o['bytes']
                 e[2] += 1
     if a.summary:
-        peak = 6557.8
+        peak = 6549.1
         try:
             peak = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json'))).get('hbm_gbs', peak)
         except Exception:
