@@ -271,6 +271,8 @@ struct Exec {
   // row counts in the slot headers, no NCCL call and no host round trip) - the default whenever the windows are mapped
   bool exchange_peer = true;
   bool topk_stream = true;       // options.topk_stream=false: ORDER BY ... LIMIT takes the multi-launch select / rank-sort route
+  bool probe_bloom = true;       // options.probe_bloom=false: the fused scan never uses the persistent variant with a shared-memory key filter
+  int64_t probe_bloom_chunks = 4 * 148;   // options.probe_bloom_chunks: 4096-row chunks from which that variant is used (tests: 1)
   bool fused_scan = true;        // options.fused_scan=false: fact scans decode every column, then probe (decode_fast.cu + ops.cu)
   bool trace = false;            // options.trace: host timeline marks + time spent waiting in each stream sync
   double t_base = 0;
@@ -297,6 +299,8 @@ struct Exec {
       small_scan_pages = options->int_or("small_scan_pages", 64);
       dense_tables = options->bool_or("dense_tables", true);
       fused_scan = options->bool_or("fused_scan", true);
+      probe_bloom = options->bool_or("probe_bloom", true);
+      probe_bloom_chunks = options->int_or("probe_bloom_chunks", 4 * 148);
       topk_stream = options->bool_or("topk_stream", true);
       exchange_single = options->bool_or("exchange_single", false);
       exchange_peer = options->bool_or("exchange_peer", true);
@@ -1470,6 +1474,22 @@ struct Exec {
     a.out_count = ar.zeros<int>(1);
     a.cap = (uint32_t)cap;
     a.err = err;
+    a.nchunks = fp.nchunks;
+    // a large scan whose first join has a direct-address table: existence filter of that join's keys in shared memory
+    // (exact when the key range fits 144 KB of bits, else several keys per bit), persistent CTAs
+    if (probe_bloom && a.key[0].ht.dense && !a.key[0].ht.next && fp.nchunks >= probe_bloom_chunks) {
+      const uint32_t range = a.key[0].ht.range;
+      uint32_t shift = 0;
+      while (((((uint64_t)range >> shift) + 31) / 32) > (uint64_t)kBloomMaxWords) ++shift;
+      a.bloom_words = (uint32_t)((((uint64_t)range >> shift) + 31) / 32 + 1);
+      a.bloom_shift = shift;
+      a.bloom_range = range;
+      a.bloom_lo = a.key[0].ht.lo;
+      uint32_t* bits = ar.zeros<uint32_t>(a.bloom_words);
+      launch_bloom_from_dense(a.key[0].ht.dense, range, shift, bits, s);
+      ++launches;
+      a.bloom = bits;
+    }
     launch_scan_probe(a, fp.nchunks, s);
     ++launches;
     RowCount nout{a.out_count, cap};

@@ -234,9 +234,151 @@ scan_probe_kernel(const FusedScanArgs a) {
   }
 }
 
+// Persistent variant for large scans whose first join has a direct-address table: one 1024-thread CTA per SM loops over
+// the chunks with an existence filter of the first join's keys in shared memory (FusedScanArgs::bloom).  A row whose key
+// misses the filter - most rows of a selective star join - never touches the join table; the rest is the plain kernel.
+constexpr int kPersistThreads = 1024;
+__global__ void __launch_bounds__(kPersistThreads, 1)
+scan_probe_persistent_kernel(const FusedScanArgs a) {
+  extern __shared__ __align__(16) uint32_t s_bloom[];
+  __shared__ PageView s_view[kMaxChain];
+  __shared__ uint16_t q_row[kFusedChunk];
+  __shared__ uint32_t q_b0[kFusedChunk];
+  __shared__ int s_nq;
+  __shared__ int s_part_ok;
+  __shared__ uint32_t s_part_row;
+  const int tid = threadIdx.x;
+  for (uint32_t w = tid; w < a.bloom_words; w += kPersistThreads) s_bloom[w] = __ldg(a.bloom + w);
+  const HashTable ht0 = a.key[0].ht;
+  for (int cidx = blockIdx.x; cidx < a.nchunks; cidx += gridDim.x) {
+    const FusedChunk ch = a.chunks[cidx];
+    __syncthreads();                       // the previous chunk's pass B is done with the views and the queues
+    if (tid < a.nkeys) s_view[tid] = make_view(a.key[tid].tasks[ch.page]);
+    if (tid == 32) {
+      s_nq = 0;
+      s_part_ok = 1;
+      s_part_row = 0;
+      if (a.has_part) {
+        uint32_t r = 0;
+        s_part_ok = ht_find(a.part_ht, a.file_part_val[ch.file], r) ? 1 : 0;
+        s_part_row = r;
+      }
+    }
+    __syncthreads();
+    if (!s_part_ok) continue;
+    // ---- pass A: 1024 threads x 4 consecutive rows = the whole chunk in one step
+    {
+      const PageView& v = s_view[0];
+      const uint32_t rend = min(ch.row0 + (uint32_t)kFusedChunk, v.n);
+      const uint32_t base = ch.row0 + (uint32_t)tid * 4u;
+      if (base < rend) {
+        uint32_t vbits = 0xFu, k0 = base;
+        if (v.vr_valid) {
+          const uint32_t w = __ldg(v.vr_valid + (base >> 5));
+          const uint32_t sh = base & 31u;
+          k0 = __ldg(v.vr_rank + (base >> 5)) + __popc(w & ((1u << sh) - 1u));
+          vbits = (w >> sh) & 0xFu;
+        }
+        if (base + 4u > rend) vbits &= (1u << (rend - base)) - 1u;
+        if (vbits) {
+          int64_t key[4];
+          bool okv[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const uint32_t k = min(k0 + __popc(vbits & ((1u << u) - 1u)), v.kmax);
+            okv[u] = page_value(v, k, key[u], a.err) && ((vbits >> u) & 1u);
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const uint64_t d = (uint64_t)(key[u] - a.bloom_lo);
+            bool cand = okv[u] && d < (uint64_t)a.bloom_range;
+            if (cand) {
+              const uint32_t bit = (uint32_t)d >> a.bloom_shift;
+              cand = (s_bloom[bit >> 5] >> (bit & 31)) & 1u;
+            }
+            uint32_t b = 0;
+            if (cand && ht_find(ht0, key[u], b)) {
+              const int pos = atomicAdd(&s_nq, 1);
+              q_row[pos] = (uint16_t)(base + u - ch.row0);
+              q_b0[pos] = b;
+            }
+          }
+        }
+      }
+    }
+    __syncthreads();
+    // ---- pass B: as in the plain kernel
+    const int nq = s_nq;
+    const int nq_round = (nq + 31) & ~31;
+    const uint32_t row_base = (uint32_t)s_view[0].out_row;
+    for (int i = tid; i < nq_round; i += kPersistThreads) {
+      bool alive = i < nq;
+      uint32_t r = 0;
+      uint32_t b[kMaxChain];
+#pragma unroll
+      for (int j = 0; j < kMaxChain; ++j) b[j] = 0;
+      if (alive) { r = ch.row0 + q_row[i]; b[0] = q_b0[i]; }
+#pragma unroll
+      for (int j = 1; j < kMaxChain; ++j) {
+        if (j < a.nkeys && alive) {
+          uint32_t k;
+          int64_t key;
+          alive = row_rank(s_view[j], r, k) && page_value(s_view[j], k, key, a.err) && ht_find(a.key[j].ht, key, b[j]);
+        }
+      }
+      const uint32_t m = __ballot_sync(0xFFFFFFFFu, alive);
+      if (!m) continue;
+      const int lane = tid & 31, leader = __ffs(m) - 1;
+      int pos0 = 0;
+      if (lane == leader) pos0 = atomicAdd(a.out_count, __popc(m));
+      pos0 = __shfl_sync(0xFFFFFFFFu, pos0, leader);
+      if (alive) {
+        const uint32_t pos = (uint32_t)pos0 + __popc(m & ((1u << lane) - 1u));
+        if (pos < a.cap) {
+          a.out_row[pos] = row_base + r;
+          a.out_file[pos] = ch.file;
+#pragma unroll
+          for (int j = 0; j < kMaxChain; ++j)
+            if (j < a.nkeys) a.key[j].out_build[pos] = b[j];
+          if (a.has_part) a.part_out_build[pos] = s_part_row;
+        } else {
+          atomicExch(a.err + 2, 1);
+        }
+      }
+    }
+  }
+}
+
+__global__ void bloom_from_dense_kernel(const uint32_t* __restrict__ dense, uint32_t range, uint32_t shift, uint32_t* bloom) {
+  for (uint32_t d = blockIdx.x * blockDim.x + threadIdx.x; d < range; d += gridDim.x * blockDim.x)
+    if (__ldg(dense + d)) {
+      const uint32_t bit = d >> shift;
+      atomicOr(&bloom[bit >> 5], 1u << (bit & 31));
+    }
+}
+void launch_bloom_from_dense(const uint32_t* dense, uint32_t range, uint32_t shift, uint32_t* bloom, cudaStream_t s) {
+  if (!range) return;
+  int g = (int)((range + 255) / 256);
+  if (g > 148 * 8) g = 148 * 8;
+  bloom_from_dense_kernel<<<g, 256, 0, s>>>(dense, range, shift, bloom);
+  NDS_CUDA(cudaGetLastError());
+}
+
 void launch_scan_probe(const FusedScanArgs& args, int nchunks, cudaStream_t s) {
   if (nchunks <= 0) return;
-  scan_probe_kernel<<<nchunks, kFusedThreads, 0, s>>>(args);
+  if (args.bloom) {
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    NDS_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+      NDS_CUDA(cudaFuncSetAttribute(scan_probe_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBloomMaxWords * 4));
+      if (dev >= 0 && dev < 64) attr_set[dev] = true;
+    }
+    const int grid = nchunks < 148 ? nchunks : 148;
+    scan_probe_persistent_kernel<<<grid, kPersistThreads, (size_t)args.bloom_words * 4, s>>>(args);
+  } else {
+    scan_probe_kernel<<<nchunks, kFusedThreads, 0, s>>>(args);
+  }
   NDS_CUDA(cudaGetLastError());
 }
 

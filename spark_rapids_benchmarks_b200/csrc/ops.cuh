@@ -162,8 +162,18 @@ struct FusedScanArgs {
   int* out_count;
   uint32_t cap;                            // capacity of the output arrays; overflow raises err[2]
   int* err;
+  // Existence filter of the FIRST join for the persistent variant: bit ((key - lo) >> shift) of `bloom` is set when some
+  // build key maps there (shift 0: exact).  Each CTA keeps a copy in shared memory, so that most rows are rejected without
+  // touching the join table (a random 4-byte read that costs a 32-byte L2 sector per row).  nullptr: the plain variant.
+  const uint32_t* bloom;
+  int64_t bloom_lo;
+  uint32_t bloom_range, bloom_shift, bloom_words;
+  int32_t nchunks;
 };
+constexpr int kBloomMaxWords = 36 * 1024;      // 144 KB of shared memory for the filter (+ 25 KB for the queues)
 void launch_scan_probe(const FusedScanArgs& args, int nchunks, cudaStream_t s);
+// dense join table -> existence filter (bloom_words pre-zeroed words)
+void launch_bloom_from_dense(const uint32_t* dense, uint32_t range, uint32_t shift, uint32_t* bloom, cudaStream_t s);
 // One (column, selected file) pair of a fused scan: expand_tasks_kernel copies the file's page templates, patches them
 // and lists the pages (def kernel) and their 4096-row chunks (probe kernel) - the host only places whole files.
 struct FileJob {
