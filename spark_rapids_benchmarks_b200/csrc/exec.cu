@@ -271,8 +271,13 @@ struct Exec {
   // row counts in the slot headers, no NCCL call and no host round trip) - the default whenever the windows are mapped
   bool exchange_peer = true;
   bool topk_stream = true;       // options.topk_stream=false: ORDER BY ... LIMIT takes the multi-launch select / rank-sort route
-  bool probe_bloom = true;       // options.probe_bloom=false: the fused scan never uses the persistent variant with a shared-memory key filter
-  int64_t probe_bloom_chunks = 4 * 148;   // options.probe_bloom_chunks: 4096-row chunks from which that variant is used (tests: 1)
+  // options.probe_bloom=true: large fused scans use the persistent probe kernel with the first join's keys as an existence
+  // filter in shared memory (scan_probe_persistent_kernel).  OFF by default: measured slower than the plain kernel (SF10
+  // query7: 0.49 ms against 0.21 ms) - one 1024-thread CTA per SM hides the load latency worse than six 256-thread CTAs,
+  // and the saved join-table reads do not make up for it.  Kept switchable for the next attempt (several chunks in flight
+  // per CTA); options.probe_bloom_chunks = 4096-row chunks from which it applies.
+  bool probe_bloom = false;
+  int64_t probe_bloom_chunks = 4 * 148;
   bool fused_scan = true;        // options.fused_scan=false: fact scans decode every column, then probe (decode_fast.cu + ops.cu)
   bool trace = false;            // options.trace: host timeline marks + time spent waiting in each stream sync
   double t_base = 0;
@@ -299,7 +304,7 @@ struct Exec {
       small_scan_pages = options->int_or("small_scan_pages", 64);
       dense_tables = options->bool_or("dense_tables", true);
       fused_scan = options->bool_or("fused_scan", true);
-      probe_bloom = options->bool_or("probe_bloom", true);
+      probe_bloom = options->bool_or("probe_bloom", false);
       probe_bloom_chunks = options->int_or("probe_bloom_chunks", 4 * 148);
       topk_stream = options->bool_or("topk_stream", true);
       exchange_single = options->bool_or("exchange_single", false);

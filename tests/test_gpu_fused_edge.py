@@ -96,8 +96,8 @@ def _run(root, expect_fused):
         from spark_rapids_benchmarks_b200 import planner
         plain = pa.Table.from_batches([eng.execute({'root': planner.plan_sql(SQL)['root']}, options={'fused_scan': False})])
         out['plain'] = [tuple(r.values()) for r in plain.to_pylist()]
-        # the persistent probe kernel with the first join's keys as a filter in shared memory (large scans take it by themselves)
-        pers = pa.Table.from_batches([eng.execute({'root': planner.plan_sql(SQL)['root']}, options={'probe_bloom_chunks': 1})])
+        # the persistent probe kernel with the first join's keys as a filter in shared memory (an option: measured slower than the plain kernel so far)
+        pers = pa.Table.from_batches([eng.execute({'root': planner.plan_sql(SQL)['root']}, options={'probe_bloom': True, 'probe_bloom_chunks': 1})])
         out['persistent'] = [tuple(r.values()) for r in pers.to_pylist()]
         return out
     finally:
