@@ -83,7 +83,10 @@ struct TableColumn {
   bool nullable = false;
   bool supported = true;
   std::string why_unsupported;
-  std::vector<uint8_t> stage;          // host copy of the encoded pages while registering
+  std::vector<uint8_t> stage;          // host copy of the encoded pages while registering (file 0, or one file of a worker thread)
+  std::vector<std::pair<int64_t, uint32_t>> view_tables;   // while registering: (offset, entries) of the string-view tables in `stage`
+  std::vector<int64_t> part_base;      // while registering: where each file's bytes start in the column's buffer
+  int64_t total_bytes = 0;
   uint8_t* h_enc = nullptr;            // pinned (cudaHostAlloc) host copy kept when keep_host: source of source=host scans
   bool pinned = false;
   uint8_t* d_enc = nullptr;            // resident copy in HBM

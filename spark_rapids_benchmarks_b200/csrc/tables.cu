@@ -6,6 +6,9 @@
 // `store()` (/root/reference/nds/nds_transcode.py:131-150): fact tables as <col>=<value>/ directories with
 // the partition column only in the directory name, dimension tables as one file.
 #include <algorithm>
+#include <atomic>
+#include <mutex>
+#include <thread>
 #include <dirent.h>
 #include <fcntl.h>
 #include <sys/stat.h>
@@ -141,12 +144,11 @@ void Engine::register_table(const std::string& name, const std::string& path, co
   for (size_t i = 0; i < all.size(); ++i)
     if (t.part_col.empty() || world <= 1 || (int)(i % world) == rank) t.files.push_back(all[i]);
 
-  // ---- parse + stage -----------------------------------------------------------------------------------
-  std::vector<uint8_t> buf;
-  bool first = true;
-  std::vector<int> max_def;
-  for (size_t fidx = 0; fidx < t.files.size(); ++fidx) {
+  // ---- parse + stage: the first file establishes the schema; the others are parsed and staged by a pool of threads, each
+  // into buffers of its own (offsets relative to the file), and placed one after the other afterwards
+  auto stage_one = [&](size_t fidx, std::vector<TableColumn>& cols, bool first) {
     FileInfo& fi = t.files[fidx];
+    std::vector<uint8_t> buf;
     read_file(fi.path, buf);
     pq::FileMeta fm = pq::parse_footer(buf.data(), (int64_t)buf.size());
     if (fm.schema.empty()) fail("empty schema in '" + fi.path + "'");
@@ -160,23 +162,22 @@ void Engine::register_table(const std::string& name, const std::string& path, co
         tc.phys = e.type;
         tc.lt = logical_of(e, tc.supported, tc.why_unsupported);
         if (e.repetition == 2) { tc.supported = false; tc.why_unsupported = "repeated field"; }
-        t.col_index[tc.name] = (int)t.cols.size();
-        t.cols.push_back(std::move(tc));
+        t.col_index[tc.name] = (int)cols.size();
+        cols.push_back(std::move(tc));
       }
-      first = false;
-    } else if (ncol != (int)t.cols.size()) {
+    } else if (ncol != (int)cols.size()) {
       fail("schema mismatch between files of table '" + name + "'");
     }
-    max_def.assign(ncol, 0);
+    std::vector<int> max_def(ncol, 0);
     for (int c = 0; c < ncol; ++c) {
       const pq::SchemaElement& e = fm.schema[c + 1];
-      if (e.name != t.cols[c].name || e.type != t.cols[c].phys) fail("schema mismatch in '" + fi.path + "'");
+      if (e.name != cols[c].name || e.type != cols[c].phys) fail("schema mismatch in '" + fi.path + "'");
       max_def[c] = e.repetition == 1 ? 1 : 0;
-      if (max_def[c]) t.cols[c].nullable = true;
+      if (max_def[c]) cols[c].nullable = true;
     }
     fi.rows = fm.num_rows;
     for (int c = 0; c < ncol; ++c) {
-      TableColumn& tc = t.cols[c];
+      TableColumn& tc = cols[c];
       stage_align(tc.stage, 16);
       tc.file_page_begin.push_back((int64_t)tc.pages.size());
       tc.file_byte_begin.push_back((int64_t)tc.stage.size());
@@ -185,7 +186,7 @@ void Engine::register_table(const std::string& name, const std::string& path, co
     for (const pq::RowGroup& rg : fm.row_groups) {
       if ((int)rg.columns.size() != ncol) fail("row group column count mismatch in '" + fi.path + "'");
       for (int c = 0; c < ncol; ++c) {
-        TableColumn& tc = t.cols[c];
+        TableColumn& tc = cols[c];
         if (!tc.supported) continue;
         const pq::ColumnChunk& cc = rg.columns[c];
         ++tc.total_chunks;
@@ -231,6 +232,7 @@ void Engine::register_table(const std::string& name, const std::string& path, co
                 p += 4 + len;
               }
               di.off = views_off;
+              tc.view_tables.emplace_back(views_off, di.count);
             } else {
               di.off = (int64_t)tc.stage.size();
               tc.stage.insert(tc.stage.end(), payload, payload + psize);
@@ -356,13 +358,90 @@ void Engine::register_table(const std::string& name, const std::string& path, co
       row_base += rg.num_rows;
     }
     if (row_base != fi.rows) fail("row group rows do not add up in '" + fi.path + "'");
-    t.rows += fi.rows;
+    };
+  if (!t.files.empty()) stage_one(0, t.cols, true);
+  const size_t nfiles = t.files.size();
+  std::vector<std::vector<TableColumn>> parts(nfiles);        // parts[f]: file f's columns (f >= 1), local offsets
+  if (nfiles > 1) {
+    auto clone_schema = [&]() {
+      std::vector<TableColumn> c(t.cols.size());
+      for (size_t k = 0; k < t.cols.size(); ++k) {
+        c[k].name = t.cols[k].name;
+        c[k].phys = t.cols[k].phys;
+        c[k].lt = t.cols[k].lt;
+        c[k].lt.maxlen = 0;
+        c[k].supported = t.cols[k].supported;
+        c[k].why_unsupported = t.cols[k].why_unsupported;
+      }
+      return c;
+    };
+    unsigned hw = std::thread::hardware_concurrency();
+    const size_t nthreads = std::max<size_t>(1, std::min<size_t>({(size_t)16, (size_t)std::max(1u, hw / (unsigned)std::max(world, 1)), nfiles - 1}));
+    std::atomic<size_t> next{1};
+    std::mutex err_mu;
+    std::string first_error;
+    auto worker = [&]() {
+      for (;;) {
+        const size_t f = next.fetch_add(1);
+        if (f >= nfiles) return;
+        try {
+          parts[f] = clone_schema();
+          stage_one(f, parts[f], false);
+        } catch (const std::exception& ex) {
+          std::lock_guard<std::mutex> l(err_mu);
+          if (first_error.empty()) first_error = ex.what();
+          next.store(nfiles);
+          return;
+        }
+      }
+    };
+    std::vector<std::thread> pool;
+    for (size_t k = 0; k < nthreads; ++k) pool.emplace_back(worker);
+    for (std::thread& th : pool) th.join();
+    if (!first_error.empty()) fail(first_error);
+  }
+  // ---- place the files: global byte / page / dictionary offsets, string-view tables rebased
+  for (size_t f = 0; f < nfiles; ++f) t.rows += t.files[f].rows;
+  for (size_t c = 0; c < t.cols.size(); ++c) {
+    TableColumn& tc = t.cols[c];
+    tc.part_base.assign(nfiles, 0);
+    int64_t cur = (int64_t)tc.stage.size();          // file 0 is already in place (base 0)
+    for (size_t f = 1; f < nfiles; ++f) {
+      TableColumn& pc = parts[f][c];
+      const int64_t base = align_up(cur, 16);
+      tc.part_base[f] = base;
+      tc.file_page_begin.push_back((int64_t)tc.pages.size());
+      tc.file_byte_begin.push_back(base);
+      const int dict_base = (int)tc.dicts.size();
+      for (DictInfo di : pc.dicts) { di.off += base; tc.dicts.push_back(di); }
+      for (PageInfo pi : pc.pages) { pi.off += base; if (pi.dict >= 0) pi.dict += dict_base; tc.pages.push_back(pi); }
+      for (const auto& vt : pc.view_tables)
+        for (uint32_t k = 0; k < vt.second; ++k) {
+          uint64_t v;
+          memcpy(&v, pc.stage.data() + vt.first + 8 * (int64_t)k, 8);
+          const uint64_t off = (v & 0xFFFFFFFFull) + (uint64_t)base;
+          if (off > 0xFFFFFFFFull) fail("string column '" + tc.name + "' exceeds 4 GiB of encoded bytes");
+          v = (v & 0xFFFFFFFF00000000ull) | off;
+          memcpy(pc.stage.data() + vt.first + 8 * (int64_t)k, &v, 8);
+        }
+      tc.nullable = tc.nullable || pc.nullable;
+      tc.lt.maxlen = std::max(tc.lt.maxlen, pc.lt.maxlen);
+      if (pc.stat_chunks) {
+        if (tc.stat_chunks == 0) { tc.stat_lo = pc.stat_lo; tc.stat_hi = pc.stat_hi; }
+        else { tc.stat_lo = std::min(tc.stat_lo, pc.stat_lo); tc.stat_hi = std::max(tc.stat_hi, pc.stat_hi); }
+      }
+      tc.stat_chunks += pc.stat_chunks;
+      tc.total_chunks += pc.total_chunks;
+      cur = base + (int64_t)pc.stage.size();
+      pc.pages.clear();
+      pc.pages.shrink_to_fit();
+    }
+    tc.total_bytes = align_up(cur, 16);
   }
   for (TableColumn& tc : t.cols) {
-    stage_align(tc.stage, 16);
     tc.file_page_begin.push_back((int64_t)tc.pages.size());
-    tc.file_byte_begin.push_back((int64_t)tc.stage.size());
-    tc.enc_bytes = (int64_t)tc.stage.size();
+    tc.file_byte_begin.push_back(tc.total_bytes);
+    tc.enc_bytes = tc.total_bytes;
     t.encoded_bytes += tc.enc_bytes;
     if (tc.phys == pq::BYTE_ARRAY && tc.enc_bytes > 0xFFFFFFFFll)
       fail("string column '" + tc.name + "' exceeds 4 GiB of encoded bytes");
@@ -428,7 +507,12 @@ void Engine::register_table(const std::string& name, const std::string& path, co
   // ---- upload -------------------------------------------------------------------------------------------
   NDS_CUDA(cudaSetDevice(device));
   for (TableColumn& tc : t.cols) {
-    if (!tc.supported || tc.enc_bytes == 0) { tc.stage.clear(); tc.stage.shrink_to_fit(); continue; }
+    if (!tc.supported || tc.enc_bytes == 0) {
+      tc.stage.clear();
+      tc.stage.shrink_to_fit();
+      for (size_t f = 1; f < nfiles; ++f) { parts[f][(size_t)(&tc - t.cols.data())].stage.clear(); }
+      continue;
+    }
     if (!tc.task_tmpl.empty()) {
       NDS_CUDA(cudaMalloc(&tc.d_tmpl, tc.task_tmpl.size() * sizeof(PageTask)));
       NDS_CUDA(cudaMemcpyAsync(tc.d_tmpl, tc.task_tmpl.data(), tc.task_tmpl.size() * sizeof(PageTask), cudaMemcpyHostToDevice, stream_));
@@ -438,20 +522,31 @@ void Engine::register_table(const std::string& name, const std::string& path, co
       tc.aux_stage.clear();
       tc.aux_stage.shrink_to_fit();
     }
+    const size_t cidx = (size_t)(&tc - t.cols.data());
+    auto part_bytes = [&](size_t f) -> const std::vector<uint8_t>& { return f == 0 ? tc.stage : parts[f][cidx].stage; };
     if (resident_) {
       NDS_CUDA(cudaMalloc(&tc.d_enc, tc.enc_bytes + 256));
-      NDS_CUDA(cudaMemcpyAsync(tc.d_enc, tc.stage.data(), tc.enc_bytes, cudaMemcpyHostToDevice, stream_));
+      NDS_CUDA(cudaMemsetAsync(tc.d_enc, 0, tc.enc_bytes + 256, stream_));        // the alignment gaps between files
+      for (size_t f = 0; f < nfiles; ++f) {
+        const std::vector<uint8_t>& b = part_bytes(f);
+        if (!b.empty()) NDS_CUDA(cudaMemcpyAsync(tc.d_enc + tc.part_base[f], b.data(), b.size(), cudaMemcpyHostToDevice, stream_));
+      }
       NDS_CUDA(cudaStreamSynchronize(stream_));
     }
     if (keep_host_) {
       // page-locked memory from the driver (not a registered std::vector): host->device copies out of it run at the
       // full PCIe rate
       NDS_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&tc.h_enc), (size_t)tc.enc_bytes + 256, cudaHostAllocDefault));
-      memcpy(tc.h_enc, tc.stage.data(), (size_t)tc.enc_bytes);
+      memset(tc.h_enc, 0, (size_t)tc.enc_bytes + 256);
+      for (size_t f = 0; f < nfiles; ++f) {
+        const std::vector<uint8_t>& b = part_bytes(f);
+        if (!b.empty()) memcpy(tc.h_enc + tc.part_base[f], b.data(), b.size());
+      }
       tc.pinned = true;
     }
     tc.stage.clear();
     tc.stage.shrink_to_fit();
+    for (size_t f = 1; f < nfiles; ++f) { parts[f][cidx].stage.clear(); parts[f][cidx].stage.shrink_to_fit(); }
   }
   drop_table(name);
   tables_[name] = std::move(t);

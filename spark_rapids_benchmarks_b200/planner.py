@@ -265,7 +265,11 @@ class Planner:
     def agg_ref(self, ast, agg_map):
         fname, args, distinct = ast[1], ast[2], ast[3]
         if distinct:
-            raise PlanError('%s(DISTINCT ...) is not supported yet' % fname)
+            # count(DISTINCT x): planned as two aggregates - group by (keys, x) first, then count x per key (plan())
+            if fname != 'count' or len(args) != 1 or args[0] == ('star',):
+                raise PlanError('%s(DISTINCT ...) is not supported yet (count(DISTINCT x) is)' % fname)
+            x, _ = self.expr(args[0])
+            return _col(agg_map.add('count_distinct', x, 'int64')), 'int64'
         if fname == 'count' and (not args or args[0] == ('star',)):
             name = agg_map.add('count_star', None, 'int64')
             return _col(name), 'int64'
@@ -560,8 +564,31 @@ class Planner:
             for e, desc, nf in q['order']:
                 order_extra.append(None if (e[0] == 'col' and e[1] is None and e[2] in select_aliases)
                                    else self.expr(e, agg_map, key_map))
-            agg_node = {'op': 'aggregate', 'keys': [{'name': k['name'], 'expr': k['expr']} for k in keys],
-                        'aggs': agg_map.specs(), 'child': node}
+            specs = agg_map.specs()
+            dist = [a for a in specs if a['fn'] == 'count_distinct']
+            if dist:
+                # count(DISTINCT x) [+ other aggregates]: the inner aggregate groups by (keys, x) and carries the other
+                # aggregates as partial states; the outer one counts x per key (NULL x is not counted) and merges the states
+                if distributed:
+                    raise PlanError('count(DISTINCT ...) is not supported across GPUs yet')
+                if len({repr(a['expr']) for a in dist}) != 1:
+                    raise PlanError('count(DISTINCT ...) over more than one expression is not supported yet')
+                inner_aggs = [a for a in specs if a['fn'] != 'count_distinct']
+                inner = {'op': 'aggregate',
+                         'keys': [{'name': k['name'], 'expr': k['expr']} for k in keys] + [{'name': '_dx', 'expr': dist[0]['expr']}],
+                         'aggs': inner_aggs, 'child': node}
+                outer_aggs = []
+                for a in specs:
+                    if a['fn'] == 'count_distinct':
+                        outer_aggs.append({'name': a['name'], 'fn': 'count', 'expr': _col('_dx')})
+                    else:
+                        outer_aggs.append({'name': a['name'], 'fn': {'count': 'sum', 'count_star': 'sum'}.get(a['fn'], a['fn']),
+                                           'expr': _col(a['name']), 'type': agg_map.types[a['name']]})
+                agg_node = {'op': 'aggregate', 'keys': [{'name': k['name'], 'expr': _col(k['name'])} for k in keys],
+                            'aggs': outer_aggs, 'child': inner}
+            else:
+                agg_node = {'op': 'aggregate', 'keys': [{'name': k['name'], 'expr': k['expr']} for k in keys],
+                            'aggs': specs, 'child': node}
             if distributed:
                 final_partial = agg_node
                 merge = {'op': 'aggregate',

@@ -102,3 +102,19 @@ def test_inner_join_on_a_repeated_build_key(gpu_engine, warehouse):
     j = it.join(pr.filter(pc.is_valid(pr['p_item_sk'])), keys='i_item_sk', right_keys='p_item_sk', join_type='inner')
     exp = sorted(zip(j['i_item_sk'].to_pylist(), j['p_promo_sk'].to_pylist()))
     assert _rows(got, ['i_item_sk', 'p_promo_sk']) == exp and len(exp) > 0
+
+
+def test_count_distinct(gpu_engine, warehouse):
+    """count(DISTINCT x) next to other aggregates: two-level aggregation (group by (keys, x), then count / merge per key);
+    NULL x is not counted; also without GROUP BY."""
+    sql = ("select i_category, count(distinct i_manager_id) nm, count(*) n, sum(i_current_price) p, min(i_item_sk) lo "
+           "from item group by i_category order by i_category")
+    got = _Sess(gpu_engine).sql(sql).toArrow()
+    it = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_category', 'i_manager_id', 'i_current_price'])
+    g = it.group_by('i_category').aggregate([('i_manager_id', 'count_distinct'), ([], 'count_all'), ('i_current_price', 'sum'), ('i_item_sk', 'min')])
+    exp = sorted(((r['i_category'], r['i_manager_id_count_distinct'], r['count_all'], r['i_current_price_sum'], r['i_item_sk_min'])
+                  for r in g.to_pylist()), key=_key)
+    assert _rows(got, ['i_category', 'nm', 'n', 'p', 'lo']) == exp
+    got = _Sess(gpu_engine).sql("select count(distinct ss_customer_sk) c, count(ss_customer_sk) n from store_sales").toArrow().to_pylist()
+    ss = oq.read_fact(warehouse, 'store_sales', 'ss_sold_date_sk', ['ss_customer_sk'])
+    assert got == [{'c': pc.count_distinct(ss['ss_customer_sk']).as_py(), 'n': pc.count(ss['ss_customer_sk']).as_py()}]

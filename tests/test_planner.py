@@ -65,7 +65,8 @@ def test_distributed_plan_splits_at_the_aggregate():
     'select i_brand from item having count(*) > 1 and i_brand > \'a\'',       # HAVING over a non-grouped column
     'select i_brand from item left join promotion on p_item_sk = i_item_sk left join store on s_store_sk = p_promo_sk',   # chained outer joins
     'select i_brand from item where i_brand like \'a%\'',
-    'select i_brand, count(distinct i_item_sk) from item group by i_brand',
+    'select i_brand, sum(distinct i_item_sk) from item group by i_brand',
+    'select i_brand, count(distinct i_item_sk), count(distinct i_class) from item group by i_brand',
     'select nope from item',
 ])
 def test_unsupported_sql_raises(text):
