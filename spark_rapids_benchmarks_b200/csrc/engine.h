@@ -174,11 +174,14 @@ struct OpStat {
   int64_t row_bytes = 0, fixed_bytes = 0;   // bytes = fixed_bytes + rows * row_bytes once the device-side count is known
   const int* n_dev = nullptr;
   double t0 = 0;
+  double start_ms = -1;         // device time from the query's first event to this operator's (profile mode)
   cudaEvent_t e0 = nullptr, e1 = nullptr;
 };
 
 typedef int (*nds_allgather_fn)(void* ctx, const void* send_dev, int64_t send_bytes, void* recv_dev,
                                 int64_t max_bytes_per_rank, int64_t* recv_bytes);
+
+constexpr int kDimLanes = 6, kBaseLane = 6, kLowLane = 7;
 
 class Engine {
  public:
@@ -201,6 +204,7 @@ class Engine {
  private:
   friend struct Exec;
   cudaStream_t stream_ = nullptr;
+  // lanes 0..kDimLanes-1: build sides; kBaseLane: the fact scan; kLowLane: its payload columns' def levels
   std::vector<cudaStream_t> side_streams_;   // build sides and base scan of a join chain run side by side (exec.cu: enter_side / leave_side)
   bool resident_ = true, keep_host_ = false;
   std::map<std::string, Table> tables_;

@@ -278,6 +278,10 @@ struct Exec {
   // per CTA); options.probe_bloom_chunks = 4096-row chunks from which it applies.
   bool probe_bloom = false;
   int64_t probe_bloom_chunks = 4 * 148;
+  // options.dict_match=false: the fused scan tests the first join per row (dictionary entry, then join table) instead of
+  // once per dictionary entry and file (dict_match_kernel); options.dict_match_chunks = 4096-row chunks from which it applies
+  bool dict_match = true;
+  int64_t dict_match_chunks = 2048;
   bool fused_scan = true;        // options.fused_scan=false: fact scans decode every column, then probe (decode_fast.cu + ops.cu)
   bool trace = false;            // options.trace: host timeline marks + time spent waiting in each stream sync
   double t_base = 0;
@@ -305,6 +309,8 @@ struct Exec {
       dense_tables = options->bool_or("dense_tables", true);
       fused_scan = options->bool_or("fused_scan", true);
       probe_bloom = options->bool_or("probe_bloom", false);
+      dict_match = options->bool_or("dict_match", true);
+      dict_match_chunks = options->int_or("dict_match_chunks", 2048);
       probe_bloom_chunks = options->int_or("probe_bloom_chunks", 4 * 148);
       topk_stream = options->bool_or("topk_stream", true);
       exchange_single = options->bool_or("exchange_single", false);
@@ -456,7 +462,8 @@ struct Exec {
     // a subtree made of scans/filters/builds reads registered table bytes and its own allocations only: all it must
     // wait for is the arena's zeroed prefix (ev_start, recorded when the query began) - not what the main stream
     // queued since
-    cudaStream_t side = e.side_streams_[(size_t)which % e.side_streams_.size()];
+    // which >= 0: one of the build-side lanes; kBaseLane: the fact scan's lane
+    cudaStream_t side = which == kBaseLane ? e.side_streams_[kBaseLane] : e.side_streams_[(size_t)which % kDimLanes];
     NDS_CUDA(cudaStreamWaitEvent(side, ev_start, 0));
     s_saved = s;
     s = side;
@@ -1249,6 +1256,7 @@ struct Exec {
     PageTask* d_tasks = nullptr;
     int64_t pages_per_col = 0;                  // pages of one key column (all key columns have the same)
     FusedChunk* d_chunks = nullptr;
+    int32_t* d_page_file = nullptr;             // per page of the first key column: its file among the selected files
     int nchunks = 0;
     int64_t* d_part_val = nullptr;
     uint8_t* d_part_null = nullptr;
@@ -1395,6 +1403,7 @@ struct Exec {
     fp.d_tasks = ar.alloc_n<PageTask>(std::max<int64_t>(ntasks, 1));
     int* d_def_idx = ar.alloc_n<int>(std::max(ndef_all, 1));
     fp.d_chunks = ar.alloc_n<FusedChunk>(std::max(nchunks, 1));
+    fp.d_page_file = ar.alloc_n<int32_t>(std::max<int64_t>(fp.pages_per_col, 1));
     // ---- jobs, per-file partition values, per-column page directories: one upload
     std::vector<int64_t> pv(sel.size());
     std::vector<uint8_t> pn(sel.size());
@@ -1419,7 +1428,7 @@ struct Exec {
     fp.d_part_null = d + off_pn;
     for (size_t c = 0; c < fp.cols.size(); ++c)
       if (fp.cols[c].tc) fp.cols[c].d_file_page0 = reinterpret_cast<const int32_t*>(d + off_fp0) + fp0_off[c];
-    launch_expand_tasks(reinterpret_cast<const FileJob*>(d + off_jobs), (int)jobs.size(), fp.d_tasks, d_def_idx, fp.d_chunks, s);
+    launch_expand_tasks(reinterpret_cast<const FileJob*>(d + off_jobs), (int)jobs.size(), fp.d_tasks, d_def_idx, fp.d_chunks, fp.d_page_file, s);
     ++launches;
     mark("fused:uploaded");
     // ---- def levels -> page-local validity + rank words: the key columns' on this stream (the probe kernel needs them),
@@ -1428,9 +1437,7 @@ struct Exec {
     launch_decode_split(fp.d_tasks, d_def_idx, ndef_key, max_def_key, nullptr, 0, err, s, &l);
     if (ndef_all > ndef_key) {
       cudaStream_t s2 = s;
-      if (side_stream && e.side_streams_.size() >= 2)
-        for (cudaStream_t cand : e.side_streams_)
-          if (cand != s && cand != e.stream_) s2 = cand;
+      if (side_stream && (int)e.side_streams_.size() > kLowLane) s2 = e.side_streams_[kLowLane];
       if (s2 != s) {
         cudaEvent_t ev_up = e.get_event();
         NDS_CUDA(cudaEventRecord(ev_up, s));
@@ -1494,6 +1501,56 @@ struct Exec {
       launch_bloom_from_dense(a.key[0].ht.dense, range, shift, bits, s);
       ++launches;
       a.bloom = bits;
+    }
+    // the first join tested once per dictionary entry and file instead of once per row: every selected file's pages of
+    // the first key column share one dictionary (one row group per file), whose entries the match kernel reads in order
+    if (dict_match && !a.bloom && fp.nchunks >= dict_match_chunks) {
+      const TableColumn& tc = *fp.cols[0].tc;
+      const std::vector<int>& sel = fp.fs.sel;
+      std::vector<int32_t> dict_task(sel.size(), -1);
+      uint32_t max_dict = 0;
+      bool ok = true;
+      int64_t task = 0, entries = 0;
+      for (size_t k = 0; k < sel.size() && ok; ++k) {
+        int32_t dict = -1;
+        for (int64_t p = tc.file_page_begin[sel[k]]; p < tc.file_page_begin[sel[k] + 1]; ++p, ++task) {
+          const PageInfo& pg = tc.pages[p];
+          if (pg.num_values > 65535u) { ok = false; break; }   // the probe kernel queues 16-bit row numbers
+          if (pg.enc != 1 || pg.dict < 0) continue;            // PLAIN page: tested per row
+          if (dict >= 0 && pg.dict != dict) { ok = false; break; }    // several dictionaries in one file (several row groups)
+          if (dict < 0) { dict = pg.dict; dict_task[k] = (int32_t)task; }
+        }
+        if (dict >= 0) { max_dict = std::max(max_dict, tc.dicts[dict].count); entries += tc.dicts[dict].count; }
+      }
+      // worth it when the dictionaries are smaller than the rows they stand for
+      const uint32_t stride = ((max_dict + 31) / 32 + 3) & ~3u;
+      if (ok && max_dict > 0 && entries < N && stride <= (uint32_t)kDictMatchMaxWords) {
+        size_t sdm = begin_stat("dict_match");       // inside the scan_probe statistic: part of the same operator
+        uint32_t* bits = ar.alloc_n<uint32_t>((int64_t)stride * (int64_t)sel.size());
+        int32_t* d_dt = ar.alloc_n<int32_t>((int64_t)sel.size());
+        ar.upload(d_dt, dict_task.data(), (int64_t)sel.size() * 4);
+        // coarse existence bits of a direct-address table's key range: 32 KB of shared memory in the match kernel
+        const HashTable& h0 = a.key[0].ht;
+        const uint32_t* coarse = nullptr;
+        uint32_t cwords = 0, cshift = 0;
+        if (h0.dense && h0.range > 0) {
+          while (((((uint64_t)h0.range >> cshift) + 31) / 32 + 4) > (uint64_t)kDictMatchCoarseWords) ++cshift;
+          cwords = (uint32_t)(((((uint64_t)h0.range >> cshift) + 31) / 32 + 4) & ~uint64_t(3));
+          uint32_t* cb = ar.zeros<uint32_t>(cwords);
+          launch_bloom_from_dense(h0.dense, h0.range, cshift, cb, s);
+          ++launches;
+          coarse = cb;
+        }
+        launch_dict_match(a.key[0].tasks, d_dt, (int)sel.size(), max_dict, tc.lt.dtype() == DT_I32 ? 4 : 8, h0, coarse, cwords, cshift, bits, stride, s);
+        ++launches;
+        a.dmatch = bits;
+        a.dmatch_stride = stride;
+        a.page_file = fp.d_page_file;
+        a.npages = (int32_t)fp.pages_per_col;
+        // a few CTAs per page when there are not many pages: several waves of CTAs keep the tail short
+        a.split = fp.pages_per_col >= 148 * 8 * 4 ? 1 : (fp.pages_per_col >= 148 * 8 ? 2 : 5);
+        end_stat(sdm, entries * (tc.lt.dtype() == DT_I32 ? 4 : 8) + entries / 8, entries);
+      }
     }
     launch_scan_probe(a, fp.nchunks, s);
     ++launches;
@@ -1701,7 +1758,7 @@ struct Exec {
     bool fused_ready = false;
     auto issue_base = [&]() {
       const bool side = side_stream && independent_subtree(base_node);
-      if (side) enter_side(lane_no++);
+      if (side) enter_side(kBaseLane);
       // a Parquet fact scan under the chain: decode the probe keys inside the probe kernel instead of materialising columns
       fused_ready = fused_prepare(base_node, chain, down, fplan);
       if (!fused_ready) base = exec(base_node, down);
@@ -1719,7 +1776,7 @@ struct Exec {
       const size_t j = order[k];
       if (!base_done && k >= npruning && side_stream && pruning_keys_arrived()) issue_base();
       const bool side = side_stream && independent_subtree(chain[j]->at("build"));
-      if (side) enter_side(lane_no++);
+      if (side) enter_side(lane_no++ % kDimLanes);
       sides[j] = build_side(*chain[j], down);
       if (side) leave_side();
     }
@@ -2919,18 +2976,20 @@ void Engine::execute_once(const Json& plan, ArrowSchema* out_schema, ArrowArray*
   cudaEventElapsedTime(&ms, ev0, ev1);
   exec_ms_ = ms;
   ev_guard.armed = false;
-  put_event(ev0);
-  put_event(ev1);
   for (OpStat& st : op_stats) {
     if (st.e0 && st.e1) {
       float t = 0;
       if (cudaEventElapsedTime(&t, st.e0, st.e1) == cudaSuccess) st.ms = t;
+      else cudaGetLastError();
+      if (cudaEventElapsedTime(&t, ev0, st.e0) == cudaSuccess) st.start_ms = t;
       else cudaGetLastError();
     }
     if (st.e0) put_event(st.e0);
     if (st.e1) put_event(st.e1);
     st.e0 = st.e1 = nullptr;
   }
+  put_event(ev0);
+  put_event(ev1);
   stats_ = std::move(op_stats);
   host_ms_ = Exec::now_ms() - t_exec0;
 }
@@ -2943,7 +3002,7 @@ std::string Engine::stats_json() const {
     if (i) s += ",";
     s += "{\"op\":\"" + json_escape(stats_[i].op) + "\",\"ms\":" + std::to_string(stats_[i].ms) + ",\"bytes\":" +
          std::to_string(stats_[i].bytes) + ",\"rows\":" + std::to_string(stats_[i].rows) + ",\"host_ms\":" +
-         std::to_string(stats_[i].host_ms) + "}";
+         std::to_string(stats_[i].host_ms) + ",\"start_ms\":" + std::to_string(stats_[i].start_ms) + "}";
   }
   s += "]}";
   return s;
@@ -2963,8 +3022,12 @@ Engine::Engine(const Json& cfg) {
     fail(std::string("no CUDA device is available (") + cudaGetErrorString(ce) + "); the NDS B200 engine has no CPU path");
   if (device >= ndev) fail("engine config: device " + std::to_string(device) + " does not exist");
   NDS_CUDA(cudaSetDevice(device));
+  // Lanes: the build sides of a join chain, the fact scan's key columns, and the def-level kernel over the payload columns
+  // (which only the gather after the probe pass needs) each get a stream.  Stream priorities (build sides first, payload
+  // last) were measured at SF100 and changed nothing: query7 is bound by the sum of the kernels' SM time, so what the build
+  // sides gain the gather loses waiting for the deprioritised payload kernel.  All lanes share one priority.
   NDS_CUDA(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
-  for (int k = 0; k < 6; ++k) {
+  for (int k = 0; k <= kLowLane; ++k) {
     cudaStream_t st;
     NDS_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
     side_streams_.push_back(st);

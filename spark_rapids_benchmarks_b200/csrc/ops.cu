@@ -674,6 +674,7 @@ struct TopkState {
   int cur;                  // which area collects
   int Bw, k;
   bool have_thresh;         // area[cur][0 .. k) is the sorted k best of everything offered so far
+  bool sorted;              // nothing was appended since the last shrink: area[cur][0 .. count) is sorted
 };
 
 // CTA-wide: keep the k best of the m collected candidates, sorted, in the other area.  Returns the new count.
@@ -716,6 +717,7 @@ __device__ __forceinline__ int topk_shrink(TopkState& st, int m, int* s_m) {
   __syncthreads();
   st.cur ^= 1;
   st.have_thresh = kept == st.k;
+  st.sorted = true;
   return kept;
 }
 
@@ -731,7 +733,7 @@ __device__ __forceinline__ void topk_offer(TopkState& st, bool have, uint32_t ro
     for (int w = 0; w < st.Bw; ++w) dst[w] = CG ? __ldcg(key + w) : key[w];
     st.row[st.cur][pos] = row;
   }
-  __syncthreads();
+  if (__syncthreads_or(keep)) st.sorted = false;
   const int m = *s_m;
   __syncthreads();
   if (m > kTopkCand - kTopkThreads) topk_shrink(st, m, s_m);
@@ -747,6 +749,7 @@ __device__ __forceinline__ int topk_merge(TopkState& st, int s0, int s1, const u
   const int ns = s1 - s0;
   st.cur = 0;
   st.have_thresh = false;
+  st.sorted = false;
   if (tid == 0) *s_m = 0;
   if (tid < ns) s_pre[tid + 1] = __ldcg(counts + s0 + tid);
   __syncthreads();
@@ -773,7 +776,7 @@ __device__ __forceinline__ int topk_merge(TopkState& st, int s0, int s1, const u
     topk_offer<true>(st, have, row, keys_base + ((int64_t)src * st.k + e) * st.Bw, s_m);
   }
   const int m = *s_m;
-  if (m <= st.k && !sort_result) return m;
+  if (m <= st.k && (!sort_result || st.sorted)) return m;
   return topk_shrink(st, m, s_m);
 }
 
@@ -801,8 +804,14 @@ topk_stream_kernel(const Prog* __restrict__ progs, const SortKey* __restrict__ k
   __shared__ int s_last;
   __shared__ int s_pre[kTopkMaxSrc + 1];
   const int tid = threadIdx.x;
-  const int nctas = (int)gridDim.x, ngroups = (nctas + kTopkGroup - 1) / kTopkGroup;
   const int64_t n = row_count(n_dev, n_host);
+  // The grid is sized for the host's bound of the row count; the count itself is only known here.  A CTA gets at least two
+  // tiles of rows (one candidate area), the CTAs beyond that leave at once and take no part in the merges: a thousand rows
+  // are two CTAs and one merge, instead of 148 publishes, ten group merges and a final merge of mostly empty lists.
+  const int64_t want = (n + 2 * kTopkThreads - 1) / (2 * kTopkThreads);
+  const int nctas = (int)(want < 1 ? 1 : (want > (int64_t)gridDim.x ? (int64_t)gridDim.x : want));
+  if ((int)blockIdx.x >= nctas) return;
+  const int ngroups = (nctas + kTopkGroup - 1) / kTopkGroup;
   // global scratch per CTA: 256 staging slots (+ the two candidate areas when they do not fit shared memory)
   const int64_t per_cta = (int64_t)(kTopkThreads + (smem_areas ? 0 : 2 * kTopkCand)) * Bw;
   uint64_t* my = scratch + (int64_t)blockIdx.x * per_cta;
@@ -816,11 +825,12 @@ topk_stream_kernel(const Prog* __restrict__ progs, const SortKey* __restrict__ k
   st.Bw = Bw;
   st.k = k;
   st.have_thresh = false;
+  st.sorted = false;
   if (tid == 0) s_m = 0;
   __syncthreads();
   uint64_t* stage = my + (int64_t)tid * Bw;
   uint8_t* mykey = reinterpret_cast<uint8_t*>(stage);
-  for (int64_t t0 = (int64_t)blockIdx.x * kTopkThreads; t0 < n; t0 += (int64_t)gridDim.x * kTopkThreads) {
+  for (int64_t t0 = (int64_t)blockIdx.x * kTopkThreads; t0 < n; t0 += (int64_t)nctas * kTopkThreads) {
     const int64_t i = t0 + tid;
     const bool have = i < n;
     if (have) {
@@ -830,6 +840,12 @@ topk_stream_kernel(const Prog* __restrict__ progs, const SortKey* __restrict__ k
     topk_offer<false>(st, have, (uint32_t)i, stage, &s_m);
   }
   // (<= k collected candidates are handed on as they are: only the result has to be sorted)
+  if (nctas == 1) {                     // the only CTA: its sorted candidates are the result
+    const int res = (st.sorted && s_m <= k) ? s_m : topk_shrink(st, s_m, &s_m);
+    for (int i = tid; i < res; i += kTopkThreads) out_rows[i] = st.row[st.cur][i];
+    if (tid == 0) *out_count = res;
+    return;
+  }
   int kept = s_m > k ? topk_shrink(st, s_m, &s_m) : s_m;
   // level 0 -> level 1: this CTA's survivors; the last CTA of each group of kTopkGroup merges the group's lists
   uint64_t* keys1 = fin_keys;
@@ -847,7 +863,12 @@ topk_stream_kernel(const Prog* __restrict__ progs, const SortKey* __restrict__ k
   __syncthreads();
   if (!s_last) return;
   __threadfence();
-  kept = topk_merge(st, g0, g1, keys1, rows1, count1, &s_m, s_pre, false);
+  kept = topk_merge(st, g0, g1, keys1, rows1, count1, &s_m, s_pre, ngroups == 1);
+  if (ngroups == 1) {                   // one group: its merge is the final one
+    for (int i = tid; i < kept; i += kTopkThreads) out_rows[i] = st.row[st.cur][i];
+    if (tid == 0) *out_count = kept;
+    return;
+  }
   // level 1 -> result: the last group to finish merges the groups' lists and writes the rows
   topk_publish(st, kept, g, keys2, rows2, count2);
   __threadfence();

@@ -169,7 +169,24 @@ struct FusedScanArgs {
   int64_t bloom_lo;
   uint32_t bloom_range, bloom_shift, bloom_words;
   int32_t nchunks;
+  // Per selected file: one bit per dictionary entry of the first key column, set when the entry is a key of the first join
+  // (dict_match_kernel).  dmatch_stride words per file; nullptr = test the join table per row.
+  const uint32_t* dmatch;
+  uint32_t dmatch_stride;
+  const int32_t* page_file;                // per page of the first key column: index of its file among the selected files
+  int32_t npages, split;                   // scan_probe_dm_kernel: `split` CTAs share a page's chunks
 };
+// dict_match_kernel: kDictMatchEntries dictionary entries per CTA; `coarse` = existence bits of the first join's key range,
+// one bit per 2^coarse_shift keys (launch_bloom_from_dense), copied to shared memory; 0 words = test the table directly.
+// The match bits of one file must fit the probe kernel's shared memory: kDictMatchMaxWords.
+constexpr int kDictMatchThreads = 512;
+constexpr int kDictMatchEntries = 16384;
+constexpr int kDictMatchCoarseWords = 8192;     // 32 KB
+constexpr int kDictMatchMaxWords = 16384;       // 64 KB: dictionaries of up to 524288 entries
+constexpr int kDmQueue = 6144;                  // queued rows (uint16 row in page) before pass B must run
+void launch_dict_match(const PageTask* tasks, const int32_t* dict_task, int nfiles, uint32_t max_dict, int width, const HashTable& ht,
+                       const uint32_t* coarse, uint32_t coarse_words, uint32_t coarse_shift, uint32_t* out, uint32_t stride_words,
+                       cudaStream_t s);
 constexpr int kBloomMaxWords = 36 * 1024;      // 144 KB of shared memory for the filter (+ 25 KB for the queues)
 void launch_scan_probe(const FusedScanArgs& args, int nchunks, cudaStream_t s);
 // dense join table -> existence filter (bloom_words pre-zeroed words)
@@ -190,7 +207,8 @@ struct FileJob {
   int32_t file;                            // index among the selected files
   int32_t pad;
 };
-void launch_expand_tasks(const FileJob* d_jobs, int njobs, PageTask* tasks, int* def_idx, FusedChunk* chunks, cudaStream_t s);
+void launch_expand_tasks(const FileJob* d_jobs, int njobs, PageTask* tasks, int* def_idx, FusedChunk* chunks, int32_t* page_file,
+                         cudaStream_t s);
 struct GatherCol {
   const PageTask* tasks;                   // this column's tasks for the selected files, scan order (null: the partition column)
   const int32_t* file_page0;               // per selected file: first task; [nsel] = task count

@@ -262,9 +262,11 @@ def test_sort_routes(gpu_engine, n, limit, pattern, keep):
         _sort_case(gpu_engine, n, limit, pattern, keep, seed=n + (limit or 0), options={'topk_stream': False})
 
 
-@pytest.mark.parametrize('n,limit', [(3, 1), (255, 128), (257, 100), (700, 100), (70000, 128), (1500000, 100), (1500000, 3)])
+@pytest.mark.parametrize('n,limit', [(3, 1), (255, 128), (257, 100), (700, 100), (1024, 100), (1025, 100), (4097, 128), (16384, 100),
+                                     (16385, 100), (70000, 128), (1500000, 100), (1500000, 3)])
 def test_streaming_topk_sizes(gpu_engine, n, limit):
-    """The one-launch top-k at sizes around its tile (256 rows), its candidate area (512) and its grid (64 CTAs), with
+    """The one-launch top-k at sizes around its tile (256 rows), its candidate area (512), one CTA's minimum share (1024 rows:
+    one CTA and no merge up to there), one merge group (16 CTAs: a single merge up to 16384 rows) and its grid, with
     heavy ties on the leading keys and with most rows filtered out on the device."""
     _sort_case(gpu_engine, n, limit, 'ties', 1.0, seed=n * 7 + limit)
     _sort_case(gpu_engine, n, limit, 'flat', 0.35, seed=n * 11 + limit)

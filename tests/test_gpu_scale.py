@@ -58,8 +58,9 @@ def rows_equal(got, exp):
 
 @pytest.mark.parametrize('pi', range(len(PARAMS)))
 def test_six_query_stream_at_sf1_matches_oracle(sf1, pi):
+    import pyarrow as pa
     from oracle import nds_queries as oq
-    from spark_rapids_benchmarks_b200 import streams
+    from spark_rapids_benchmarks_b200 import planner, streams
     from tests.test_gpu_queries import _Sess
     wh, eng, days = sf1
     info = eng.table_info('store_sales')
@@ -82,6 +83,10 @@ def test_six_query_stream_at_sf1_matches_oracle(sf1, pi):
             assert rows_equal(got.to_pylist(), exp.to_pylist()), (query, source, got.to_pylist()[:3], exp.to_pylist()[:3])
             ops = [o['op'] for o in eng.last_stats()['ops']]
             assert 'scan_probe' in ops and not any(o.startswith('decode:store_sales') for o in ops), (query, ops)   # the fused fact scan ran
+        # the first join tested per dictionary entry and file (dict_match_kernel; on by itself from 2048 chunks = 8 M rows)
+        got = pa.Table.from_batches([eng.execute(planner.plan_sql(sql), options={'dict_match_chunks': 1})])
+        assert rows_equal(got.to_pylist(), exp.to_pylist()), query
+        assert 'dict_match' in [o['op'] for o in eng.last_stats()['ops']], query
 
 
 def test_query7_at_sf1_takes_the_large_routes(sf1):

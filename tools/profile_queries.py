@@ -24,6 +24,8 @@ def main():
     ap.add_argument('--summary', default='', help='write a per-operator summary (markdown) to this path')
     ap.add_argument('--serial', action='store_true', help='one stream for every operator (kernel times without overlap)')
     ap.add_argument('--opt', action='append', default=[], help='engine option key=int (repeatable), e.g. small_scan_pages=0')
+    ap.add_argument('--world', type=int, default=1, help='one rank of N on this GPU: 1/N of the fact files, distributed plans, the exchange '
+                                                         'emulated in device memory (exchange_loopback=N)')
     ap.add_argument('--trace', action='store_true', help='print the host timeline (marks and sync waits) of the last rep')
     a = ap.parse_args()
     import bench
@@ -52,7 +54,7 @@ def main():
     else:
         bench.ensure_data(args, print)
         qd = bench.make_stream(args)
-    sess = Session('profile', device=0, keep_host=not a.no_keep_host)
+    sess = Session('profile', device=0, keep_host=not a.no_keep_host, rank=0, world=a.world)
     t0 = time.time()
     for t in (needed if a.subset_tables else nds_schema.get_schemas(True)):
         sess.register_table(t, os.path.join(wh, t))
@@ -60,11 +62,12 @@ def main():
     summary = {}
     names = [q for q in qd if not a.queries or q in a.queries.split(',')]
     for name in names:
-        plan = planner.plan_sql(qd[name])
+        plan = planner.plan_sql(qd[name], distributed=a.world > 1)
         for rep in range(a.reps):
             t0 = time.perf_counter()
-            sess.engine.execute({'root': plan['root']}, source=None if a.source == 'hbm' else a.source, profile=not a.no_profile, decode_timing=a.decode_timing,
+            sess.engine.execute({'root': plan['fused' if a.world > 1 else 'root']}, source=None if a.source == 'hbm' else a.source, profile=not a.no_profile, decode_timing=a.decode_timing,
                                 options=dict(({'trace': True} if a.trace else {}), **({'side_stream': False} if a.serial else {}),
+                                             **({'exchange_loopback': a.world} if a.world > 1 else {}),
                                              **{kv.split('=')[0]: int(kv.split('=')[1]) for kv in a.opt}) or None)
             wall = (time.perf_counter() - t0) * 1e3
             st = sess.engine.last_stats()
@@ -74,7 +77,8 @@ def main():
             if o['op'].startswith('decode_phases') or o['op'].startswith('decode_routes'):
                 print('   ' + o['op'])
                 continue
-            print('   %-28s %9.3f ms (host %6.3f)  %12d B  %10d rows  %8.1f GB/s' % (o['op'][:28], o['ms'], o.get('host_ms', 0), o['bytes'], o['rows'], gbs))
+            print('   %-28s %9.3f ms (host %6.3f)  %12d B  %10d rows  %8.1f GB/s   [%7.3f .. %7.3f]' % (o['op'][:28], o['ms'], o.get('host_ms', 0), o['bytes'], o['rows'], gbs,
+                                                                                                o.get('start_ms', -1), o.get('start_ms', -1) + o['ms']))
         if a.trace:
             print_trace(st)
         for o in st['ops']:
