@@ -9,9 +9,10 @@ warehouse (uncompressed Parquet, reference layout; `--sf 10` gives BASELINE.json
              timed with CUDA events around each step (L2 flushed before every step), max over ranks
   e2e        seconds per step through the public API (Session.sql(text).collect()): SQL planning, host->
              device copy of the needed encoded pages from pinned host memory, execution, result read-back
-  roofline   the page decode (def_pages_kernel + rows_pages_kernel, the dominant kernels): algorithmic bytes /
-             CUDA-event launch time vs the measured HBM peak in MEASURED_PEAKS.json; timed in extra single-stream
-             steps because inside the timed region other streams' kernels share the SMs (that figure: in_step)
+  roofline   the operator of the Parquet path (def levels / fused scan -> probe / gather / dimension decode) with the
+             most device time in the step, its largest launch: algorithmic bytes / CUDA-event launch time vs the
+             measured HBM peak in MEASURED_PEAKS.json; timed in extra single-stream steps because inside the timed
+             region other streams' kernels share the SMs (that figure: in_step)
   cpu_baseline  the oracle's pyarrow-Acero restatement ("port", NOT Spark) on the same warehouse/stream
   per_query     per statement: ms with resident pages (CUDA events) and ms end to end from host buffers
   per_operator  per operator kind: CUDA-event ms, algorithmic bytes, fraction of the measured HBM peak (single-stream pass)
@@ -449,7 +450,7 @@ def main():
     # ---------------------------------------------------------------- roofline of the dominant kernel (rank 0's launches)
     # dominant = the operator kind with the most device time in the single-stream pass; its largest launch is reported
     roof = None
-    fact_kinds = [k for k in ('scan_probe', 'decode_kernel') if k in per_op]
+    fact_kinds = [k for k in ('def_levels', 'scan_probe', 'decode_kernel', 'gather_decode') if k in per_op]     # the Parquet path's kernels
     if fact_kinds:
         dom = max(fact_kinds, key=lambda k: per_op[k]['ms'])
         cand = [o for o in serial_ops if o['op'].split(':')[0] == dom and o['ms'] > 0]
@@ -469,9 +470,12 @@ def main():
                     traffic, traffic_src = tj.get('dram_bytes_per_launch'), 'static: ' + tj.get('source', 'profiles/')
             except Exception:
                 pass
-        kernel_names = {'scan_probe': 'scan_probe_kernel (fused page decode -> join-chain probe over the fact scan; the def-level kernel that '
-                                      'precedes it is the def_levels row of per_operator)',
-                        'decode_kernel': 'def_pages_kernel + rows_pages_kernel (split page decode, one launch each)'}
+        kernel_names = {'scan_probe': 'dict_match_kernel + scan_probe_dm_kernel (fused page decode -> join-chain probe over the fact scan; the '
+                                      'def-level kernel that precedes them is the def_levels row of per_operator)',
+                        'def_levels': "def_pages_kernel over the fact scan's nullable key and payload columns (def levels -> page-local validity + "
+                                      'rank words); instruction-issue-bound, not HBM-bound: see profiles/',
+                        'gather_decode': 'gather_decode_kernel (payload columns of the surviving rows)',
+                        'decode_kernel': 'def_pages_kernel + rows_pages_kernel + decode_pages_kernel (page decode of the dimension tables)'}
         dec_all = [o for o in serial_ops if o['op'].split(':')[0] == dom and o['ms'] > 0]
         roof = {'bound': 'hbm', 'kernel': kernel_names[dom], 'achieved': ach, 'peak': peak, 'unit': 'GB/s', 'frac': ach / peak,
                 'traffic': traffic, 'traffic_source': traffic_src,

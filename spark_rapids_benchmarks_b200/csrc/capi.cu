@@ -1,6 +1,8 @@
 // extern "C" surface of libndsb200.so (declared in include/nds_b200.h).
 #include <mutex>
 #include "engine.h"
+#include <memory>
+#include <unordered_map>
 #include "../../include/nds_b200.h"
 
 namespace nds {
@@ -14,7 +16,11 @@ void set_global_error(const std::string& s) {
 
 struct nds_engine {
   nds::Engine* impl;
+  // parsed plans by their JSON text: a statement that is run again (every step of a power run) skips the parse, like a
+  // prepared statement.  Bounded; cleared when full.
+  std::unordered_map<std::string, std::shared_ptr<const nds::Json>> plans;
 };
+static constexpr size_t kPlanCacheEntries = 256;
 
 #define NDS_API_BEGIN try {
 #define NDS_API_END(e)                                                  \
@@ -102,8 +108,17 @@ NDS_API int nds_engine_execute(nds_engine* e, const char* plan_json, struct Arro
   if (!e) return 2;
   NDS_API_BEGIN
   if (!plan_json || !out_schema || !out_array) nds::fail("nds_engine_execute: null argument");
-  nds::Json plan = nds::JsonParser(plan_json).parse();
-  e->impl->execute(plan, out_schema, out_array);
+  std::shared_ptr<const nds::Json> plan;
+  std::string text(plan_json);
+  auto it = e->plans.find(text);
+  if (it != e->plans.end()) {
+    plan = it->second;
+  } else {
+    plan = std::make_shared<const nds::Json>(nds::JsonParser(plan_json).parse());
+    if (e->plans.size() >= kPlanCacheEntries) e->plans.clear();
+    e->plans.emplace(std::move(text), plan);
+  }
+  e->impl->execute(*plan, out_schema, out_array);
   NDS_API_END(e)
 }
 

@@ -99,6 +99,10 @@ def _run(root, expect_fused):
         # the persistent probe kernel with the first join's keys as a filter in shared memory (an option: measured slower than the plain kernel so far)
         pers = pa.Table.from_batches([eng.execute({'root': planner.plan_sql(SQL)['root']}, options={'probe_bloom': True, 'probe_bloom_chunks': 1})])
         out['persistent'] = [tuple(r.values()) for r in pers.to_pylist()]
+        # the route large scans take by themselves: first join tested per dictionary entry (dict_match_kernel + scan_probe_dm_kernel)
+        for source in (None, 'host'):
+            r = pa.Table.from_batches([eng.execute({'root': planner.plan_sql(SQL)['root']}, source=source, options={'dict_match_chunks': 1})])
+            out['dict_match/%s' % source] = [tuple(x.values()) for x in r.to_pylist()]
         return out
     finally:
         eng.close()
