@@ -282,6 +282,7 @@ struct Exec {
   // once per dictionary entry and file (dict_match_kernel); options.dict_match_chunks = 4096-row chunks from which it applies
   bool dict_match = true;
   int64_t dict_match_chunks = 2048;
+  bool build_filter = true;      // options.build_filter=false: a filtered build side is filtered first, then built (two or three launches)
   bool fused_scan = true;        // options.fused_scan=false: fact scans decode every column, then probe (decode_fast.cu + ops.cu)
   bool trace = false;            // options.trace: host timeline marks + time spent waiting in each stream sync
   double t_base = 0;
@@ -311,6 +312,7 @@ struct Exec {
       probe_bloom = options->bool_or("probe_bloom", false);
       dict_match = options->bool_or("dict_match", true);
       dict_match_chunks = options->int_or("dict_match_chunks", 2048);
+      build_filter = options->bool_or("build_filter", true);
       probe_bloom_chunks = options->int_or("probe_bloom_chunks", 4 * 148);
       topk_stream = options->bool_or("topk_stream", true);
       exchange_single = options->bool_or("exchange_single", false);
@@ -974,6 +976,9 @@ struct Exec {
   // ---------------------------------------------------------------- filter
   Batch filter(const Json& node, std::vector<RuntimeFilter>& filters) {
     Batch in = exec(node.at("child"), filters);
+    return filter_batch(node, in);
+  }
+  Batch filter_batch(const Json& node, Batch& in) {
     size_t st = begin_stat("filter");
     Blob bb;
     std::vector<Instr> code;
@@ -1121,6 +1126,75 @@ struct Exec {
     bool multi = false;          // repeated build keys are chained (HashTable::next)
   };
 
+  // The value range of the partitions of the table(s) partitioned by `pk` (dynamic partition pruning), or false.
+  bool partition_range(const std::string& pk, int64_t& plo, int64_t& phi) const {
+    plo = INT64_MAX;
+    phi = INT64_MIN;
+    for (const auto& kv : e.tables_)
+      if (kv.second.part_col == pk)
+        for (const FileInfo& fi : kv.second.files)
+          if (!fi.part_null) { plo = std::min(plo, fi.part_val); phi = std::max(phi, fi.part_val); }
+    return plo <= phi && phi - plo < (int64_t(1) << 22);
+  }
+
+  // Filter + build of a dimension in ONE launch (join_build_filter_kernel): the predicate of `fnode` is evaluated over the
+  // unfiltered scan `in` and the rows that pass are entered into a direct-address table under their row in `in`, which then
+  // is the build side (no selection vector, no row map between the probe's matched rows and the decoded columns); a pruning
+  // join's key bitmap is filled in the same pass.  False (nothing launched) when the table cannot be a direct-address one
+  // or the pruning keys would have to travel as a list.
+  bool build_filtered(const Json& node, const Json& fnode, Batch& in, bool existence, BuiltSide& bs, std::vector<RuntimeFilter>& down) {
+    const int kb = in.find(bs.bk);
+    if (kb < 0 || !is_intlike(in.cols[kb].lt)) return false;
+    const Column& kc = in.cols[kb];
+    const int64_t nb_bound = in.rc().host;
+    const int64_t range = kc.has_range ? kc.range_hi - kc.range_lo + 1 : 0;
+    if (!dense_tables || !kc.has_range || range <= 0 || range > (int64_t(1) << 26) || range > 16 * std::max<int64_t>(nb_bound, 1) + 65536 ||
+        nb_bound <= 0 || nb_bound >= (int64_t(1) << 31))
+      return false;
+    const bool prune = node.bool_or("prune_partitions", false);
+    int64_t plo = 0, phi = -1;
+    if (prune && !partition_range(bs.pk, plo, phi)) return false;
+    size_t stb = begin_stat("join_build");
+    Blob bb;
+    std::vector<Instr> code;
+    LType t = compile(fnode.at("cond"), in, bb, code);
+    if (t.kind != LType::BOOL) fail("plan: filter condition is not boolean");
+    bb.add_prog(code, t);
+    Blob::Dev dev = bb.upload(ar, s);
+    HashTable& ht = bs.ht;
+    ht.dense = ar.zeros<uint32_t>(range);
+    ht.lo = kc.range_lo;
+    ht.range = (uint32_t)range;
+    uint32_t* dbits = nullptr;
+    std::shared_ptr<RuntimeFilter::State> st;
+    if (prune) {
+      st = std::make_shared<RuntimeFilter::State>();
+      st->lo = plo;
+      st->hi = phi;
+      st->hbits_words = (phi - plo) / 32 + 1;
+      dbits = ar.zeros<uint32_t>(st->hbits_words);
+    }
+    launch_join_build_filter(dev.host_progs[0], dev.ctx, kc.ref(), in.rc(), ht, err + 1, existence, plo, phi, dbits, s);
+    ++launches;
+    if (prune) {
+      RuntimeFilter rf;
+      rf.column = bs.pk;
+      rf.st = st;
+      uint8_t* hbuf = ar.pin_take(st->hbits_words * 4);
+      if (!hbuf) { st->pageable.resize((size_t)st->hbits_words * 4); hbuf = st->pageable.data(); }
+      st->hbits = reinterpret_cast<const uint32_t*>(hbuf);
+      NDS_CUDA(cudaMemcpyAsync(hbuf, dbits, (size_t)st->hbits_words * 4, cudaMemcpyDeviceToHost, s));
+      st->ev = e.get_event();
+      NDS_CUDA(cudaEventRecord(st->ev, s));
+      rf_states.push_back(st);
+      d2h += st->hbits_words * 4;
+      down.push_back(std::move(rf));
+    }
+    end_stat(stb, nb_bound * (row_bytes_of(bb) + 8) + range * 4, nb_bound);
+    bs.build = in;
+    return true;
+  }
+
   // Executes the build child of a join node, builds its hash table and, for a partition-pruning join, turns the build
   // keys into a runtime filter for the scan below.
   BuiltSide build_side(const Json& node, std::vector<RuntimeFilter>& down) {
@@ -1134,10 +1208,18 @@ struct Exec {
     BuiltSide bs;
     bs.multi = multi;
     std::vector<RuntimeFilter> none;
-    bs.build = exec(node.at("build"), none);
-    Batch& build = bs.build;
     bs.bk = node.str("build_key");
     bs.pk = node.str("probe_key");
+    const Json& bnode = node.at("build");
+    if (build_filter && !multi && bnode.str("op") == "filter" && bnode.at("child").str("op") == "scan") {
+      // a filtered dimension scan: filter + build in one pass when the table can be a direct-address one (build_filtered)
+      Batch in = exec(bnode.at("child"), none);
+      if (build_filtered(node, bnode, in, existence, bs, down)) return bs;
+      bs.build = filter_batch(bnode, in);
+    } else {
+      bs.build = exec(bnode, none);
+    }
+    Batch& build = bs.build;
     const std::string& bk = bs.bk;
     int kb = build.find(bk);
     if (kb < 0) fail("plan: build key '" + bk + "' not found");
@@ -1182,12 +1264,8 @@ struct Exec {
       rf.st = std::make_shared<RuntimeFilter::State>();
       RuntimeFilter::State& t = *rf.st;
       // the partition values of the table(s) partitioned by the probe key bound the keys that matter
-      int64_t plo = INT64_MAX, phi = INT64_MIN;
-      for (const auto& kv : e.tables_)
-        if (kv.second.part_col == bs.pk)
-          for (const FileInfo& fi : kv.second.files)
-            if (!fi.part_null) { plo = std::min(plo, fi.part_val); phi = std::max(phi, fi.part_val); }
-      if (nb > 0 && plo <= phi && phi - plo < (int64_t(1) << 22)) {
+      int64_t plo = 0, phi = -1;
+      if (partition_range(bs.pk, plo, phi) && nb > 0) {
         // few partitions: a bitmap over their value range is filled on the device and only that travels to the host
         t.lo = plo;
         t.hi = phi;

@@ -266,6 +266,35 @@ void launch_join_probe_chain(const ProbeChain& chain, RowCount n, uint32_t* out_
   NDS_CUDA(cudaGetLastError());
 }
 
+// Filter + build in one pass over an unfiltered build side (a dimension scan under a filter): the predicate is evaluated per
+// row and the rows that pass go straight into a direct-address table with their row in the UNFILTERED batch as the value,
+// so no selection vector is written and the probe's matched rows address the decoded columns directly.  prune_bits != null:
+// the keys inside [prune_lo, prune_hi] of the rows that pass also set a bit (dynamic partition pruning, keys_to_bitmap_kernel).
+__global__ void __launch_bounds__(kThreads)
+join_build_filter_kernel(Prog pred, OpCtx c, ColRef key, const int* n_dev, int64_t n_host, HashTable ht, int* flags, int allow_dup,
+                         int64_t prune_lo, int64_t prune_hi, uint32_t* prune_bits) {
+  const int64_t n = row_count(n_dev, n_host);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const Val pv = eval_program(pred.code, pred.n, c.cols, c.lit, i);
+    if (!pv.ok || pv.v == 0) continue;
+    const Val k = load_col(key, i);
+    if (!k.ok) continue;                       // NULL keys never match an equi-join
+    const uint64_t d = (uint64_t)(k.v - ht.lo);
+    if (d >= (uint64_t)ht.range) { atomicOr(flags, 4); continue; }
+    if (atomicCAS(&ht.dense[d], 0u, (uint32_t)i + 1u) != 0u && !allow_dup) atomicOr(flags, 1);
+    if (prune_bits && k.v >= prune_lo && k.v <= prune_hi) {
+      const uint64_t b = (uint64_t)(k.v - prune_lo);
+      atomicOr(&prune_bits[b >> 5], 1u << (b & 31));
+    }
+  }
+}
+void launch_join_build_filter(Prog pred, OpCtx c, ColRef key, RowCount n, HashTable ht, int* flags, bool allow_dup, int64_t prune_lo,
+                              int64_t prune_hi, uint32_t* prune_bits, cudaStream_t s) {
+  join_build_filter_kernel<<<grid_for(n.host), kThreads, 0, s>>>(pred, c, key, n.dev, n.host, ht, flags, allow_dup ? 1 : 0, prune_lo, prune_hi,
+                                                                 prune_bits);
+  NDS_CUDA(cudaGetLastError());
+}
+
 void launch_join_build(ColRef key, RowCount n, HashTable ht, int* flags, cudaStream_t s, bool allow_dup) {
   join_build_kernel<<<grid_for(n.host), kThreads, 0, s>>>(key, n.dev, n.host, ht, flags, allow_dup ? 1 : 0);
   NDS_CUDA(cudaGetLastError());

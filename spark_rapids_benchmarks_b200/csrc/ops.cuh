@@ -115,6 +115,9 @@ void launch_fill_i64(int64_t* p, int64_t v, int64_t n, cudaStream_t s);
 void launch_join_build(ColRef key, RowCount n, HashTable ht, int* flags, cudaStream_t s, bool allow_dup = false);
 // bits: ceil((hi - lo + 1) / 32) pre-zeroed words; bit (k - lo) is set for every non-null build key k in [lo, hi]
 void launch_keys_to_bitmap(ColRef key, RowCount n, int64_t lo, int64_t hi, uint32_t* bits, cudaStream_t s);
+// filter + direct-address build (+ pruning bitmap) in one pass over the unfiltered build side; table values = unfiltered rows
+void launch_join_build_filter(Prog pred, OpCtx c, ColRef key, RowCount n, HashTable ht, int* flags, bool allow_dup, int64_t prune_lo,
+                              int64_t prune_hi, uint32_t* prune_bits, cudaStream_t s);
 enum JoinKind : int { JOIN_INNER = 0, JOIN_SEMI = 1, JOIN_ANTI = 2, JOIN_LEFT = 3 };
 // inner: matching probe rows + their build row; semi / anti: probe rows with / without a match (out_build unused);
 // left: every probe row, out_build = the build row or kNoRow.  Unique-key tables.

@@ -534,7 +534,8 @@ def test_host_source_equals_resident_source_on_other_shapes(gpu_engine):
 @pytest.mark.parametrize('query', streams.SUBSET)
 @pytest.mark.parametrize('opts', [{'fused_scan': False}, {'dense_tables': False}, {'fused_scan': False, 'dense_tables': False},
                                   {'speculate': False}, {'topk_stream': False}, {'probe_bloom': True, 'probe_bloom_chunks': 1},
-                                  {'dict_match_chunks': 1}, {'dict_match_chunks': 1, 'dense_tables': False}, {'dict_match': False}])
+                                  {'dict_match_chunks': 1}, {'dict_match_chunks': 1, 'dense_tables': False}, {'dict_match': False},
+                                  {'build_filter': False}])
 def test_routes_agree_with_the_oracle(gpu_engine, warehouse, query, opts):
     """The fact scan has two routes - fused page decode -> probe with late materialisation (fused_scan.cu), and decode
     every column then probe (decode_fast.cu + ops.cu) - and a join table two layouts (direct-address over the key
