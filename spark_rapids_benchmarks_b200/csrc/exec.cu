@@ -2777,6 +2777,7 @@ void Engine::execute_once(const Json& plan, ArrowSchema* out_schema, ArrowArray*
     ~EventGuard() { if (armed) { en.put_event(a); en.put_event(b); } }
   } ev_guard{*this, ev0, ev1};
   NDS_CUDA(cudaEventRecord(ev0, stream_));
+  bool ev1_recorded = false;
   std::vector<OpStat> op_stats;
   {
     Exec ex(*this, options);
@@ -2894,6 +2895,8 @@ void Engine::execute_once(const Json& plan, ArrowSchema* out_schema, ArrowArray*
         ++ex.launches;
         NDS_CUDA(cudaMemcpyAsync(dpack + off_err, ex.err, sizeof h_err, cudaMemcpyDeviceToDevice, stream_));
         NDS_CUDA(cudaMemcpyAsync(hpack, dpack, (size_t)total, cudaMemcpyDeviceToHost, stream_));
+        NDS_CUDA(cudaEventRecord(ev1, stream_));       // the query's last device operation: no second wait for the timing event
+        ev1_recorded = true;
         ex.sync("sync:export");
         ex.d2h += total;
         memcpy(h_err, hpack + off_err, sizeof h_err);
@@ -3041,8 +3044,10 @@ void Engine::execute_once(const Json& plan, ArrowSchema* out_schema, ArrowArray*
     out_array->release = release_array;
     out_array->private_data = apv;
 
-    NDS_CUDA(cudaEventRecord(ev1, stream_));
-    ex.sync("sync:final");
+    if (!ev1_recorded) {
+      NDS_CUDA(cudaEventRecord(ev1, stream_));
+      ex.sync("sync:final");
+    }
     if (ex.profile) ex.resolve_stat_rows();
     trace_ = ex.trace_out;
     launches_ = ex.launches;
