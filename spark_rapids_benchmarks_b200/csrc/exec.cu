@@ -1909,6 +1909,115 @@ struct Exec {
   // ---------------------------------------------------------------- aggregate
   Batch aggregate(const Json& node, std::vector<RuntimeFilter>& filters) {
     Batch in = exec(node.at("child"), filters);
+    return aggregate_batch(node, in);
+  }
+
+  // GROUP BY ROLLUP (Spark: Expand + HashAggregate over the grouping sets): levels[0] is the finest
+  // aggregate over the child, every further level aggregates the level before it (the planner wrote its keys as column
+  // references and its aggregates in their merge form), and the result is the concatenation of all levels under the
+  // columns of the first one - a key a level does not group by is NULL there.  Row counts stay on the device: the levels'
+  // offsets in the output are a prefix sum computed by a one-thread kernel.
+  Batch rollup(const Json& node, std::vector<RuntimeFilter>& filters) {
+    Batch in = exec(node.at("child"), filters);
+    const Json& jlevels = node.at("levels");
+    const int nl = (int)jlevels.a.size();
+    if (nl < 1 || nl > 16) fail("plan: rollup needs 1..16 levels");
+    std::vector<Batch> lv;
+    lv.reserve(nl);
+    lv.push_back(aggregate_batch(jlevels.a[0], in));
+    for (int i = 1; i < nl; ++i) lv.push_back(aggregate_batch(jlevels.a[i], lv[i - 1]));
+    size_t st = begin_stat("rollup_union");
+    // every level's columns as flat columns (row maps resolved), one launch per level
+    const size_t nc = lv[0].cols.size();
+    std::vector<std::vector<Column>> flat(nl);
+    std::vector<std::vector<int>> present(nl, std::vector<int>(nc, 0));
+    std::vector<Json> ces(nc);
+    for (size_t c = 0; c < nc; ++c) ces[c] = col_expr(lv[0].cols[c].name);
+    int64_t N = 0;
+    for (int i = 0; i < nl; ++i) {
+      std::vector<std::pair<std::string, const Json*>> exs;
+      for (size_t c = 0; c < nc; ++c)
+        if (lv[i].find(lv[0].cols[c].name) >= 0) { present[i][c] = 1; exs.emplace_back(lv[0].cols[c].name, &ces[c]); }
+      if (lv[i].rc().host > 0) flat[i] = eval_columns(exs, lv[i], nullptr, lv[i].rc());
+      N += lv[i].rc().host;
+    }
+    if (N >= (int64_t(1) << 31)) fail("rollup: 2^31 or more result rows");
+    // per-level row counts and their prefix sum on the device
+    std::vector<int> hcnt(nl, 0);
+    int* d_cnt = ar.alloc_n<int>(nl);
+    int* d_bound = ar.alloc_n<int>(nl);
+    int* d_off = ar.alloc_n<int>(nl + 1);
+    for (int i = 0; i < nl; ++i) hcnt[i] = (int)lv[i].rc().host;
+    ar.upload(d_cnt, hcnt.data(), (int64_t)nl * 4);
+    ar.upload(d_bound, hcnt.data(), (int64_t)nl * 4);
+    for (int i = 0; i < nl; ++i)
+      if (lv[i].n_dev && lv[i].n_exact < 0) NDS_CUDA(cudaMemcpyAsync(d_cnt + i, lv[i].n_dev, 4, cudaMemcpyDeviceToDevice, s));
+    launch_prefix_counts(d_cnt, d_bound, nl, d_off, s);
+    ++launches;
+    Batch out;
+    out.n_max = N;
+    out.n_dev = d_off + nl;
+    std::vector<UnionSeg> segs;
+    const int64_t vwords = (N + 31) / 32 + 1;
+    for (size_t c = 0; c < nc; ++c) {
+      Column oc;
+      bool have = false;
+      for (int i = 0; i < nl && !have; ++i) {
+        if (!present[i][c] || flat[i].empty()) continue;
+        int k = 0;
+        for (size_t q = 0; q < c; ++q) k += present[i][q];
+        oc = flat[i][(size_t)k];
+        have = true;
+      }
+      if (!have) {                 // no level has a row: an empty column of the declared type
+        oc = lv[0].cols[c];
+        oc.rowmap = nullptr;
+        if (oc.lt.kind == LType::BOOL) { oc.lt.kind = LType::INT; oc.lt.is32 = false; }
+      }
+      const int w = oc.lt.dtype() == DT_I32 ? 4 : 8;
+      void* d = ar.alloc(std::max<int64_t>(N, 1) * w);
+      uint32_t* v = ar.zeros<uint32_t>(vwords);
+      for (int i = 0; i < nl; ++i) {
+        if (lv[i].rc().host <= 0) continue;
+        UnionSeg g;
+        memset(&g, 0, sizeof g);
+        g.dst = d;
+        g.dst_valid = v;
+        g.n_dev = lv[i].n_dev && lv[i].n_exact < 0 ? lv[i].n_dev : nullptr;
+        g.n_host = lv[i].rc().host;
+        g.off = d_off + i;
+        g.width = w;
+        if (present[i][c] && !flat[i].empty()) {
+          int k = 0;
+          for (size_t q = 0; q < c; ++q) k += present[i][q];
+          const Column& fc = flat[i][(size_t)k];
+          if (fc.lt.dtype() != oc.lt.dtype()) fail("rollup: column '" + oc.name + "' changes its type between levels");
+          if (fc.lt.kind == LType::STR && fc.strbase != oc.strbase) fail("rollup: string column '" + oc.name + "' has different sources");
+          g.src = fc.data;
+          g.src_valid = fc.valid;
+          g.present = 1;
+        }
+        segs.push_back(g);
+      }
+      oc.data = d;
+      oc.valid = v;
+      oc.rowmap = nullptr;
+      oc.has_range = false;
+      out.cols.push_back(oc);
+    }
+    if (!segs.empty()) {
+      UnionSeg* d_segs = ar.alloc_n<UnionSeg>((int64_t)segs.size());
+      ar.upload(d_segs, segs.data(), (int64_t)(segs.size() * sizeof(UnionSeg)));
+      int64_t biggest = 1;
+      for (int i = 0; i < nl; ++i) biggest = std::max<int64_t>(biggest, lv[i].rc().host);
+      launch_union_copy(d_segs, (int)segs.size(), biggest, s);
+      ++launches;
+    }
+    end_stat(st, 0, N);
+    return out;
+  }
+
+  Batch aggregate_batch(const Json& node, Batch& in) {
     const Json& jkeys = node.at("keys");
     const Json& jaggs = node.at("aggs");
     const int nkeys = (int)jkeys.a.size(), naggs = (int)jaggs.a.size();
@@ -2713,6 +2822,7 @@ struct Exec {
     if (op == "project") return project(node, filters);
     if (op == "join") return join(node, filters);
     if (op == "aggregate") return aggregate(node, filters);
+    if (op == "rollup") return rollup(node, filters);
     if (op == "sort") return sort(node, filters);
     if (op == "exchange") return exchange(node, filters);
     fail("plan: unsupported plan node '" + op + "' (no CPU fallback exists)");

@@ -346,6 +346,46 @@ void launch_join_probe_multi_write(ColRef key, RowCount n, HashTable ht, int kin
   NDS_CUDA(cudaGetLastError());
 }
 
+// ------------------------------------------------------------------ concatenation of row sets (rollup levels)
+__global__ void prefix_counts_kernel(const int* __restrict__ cnt, const int* __restrict__ bound, int n, int* __restrict__ off) {
+  if (blockIdx.x || threadIdx.x) return;
+  int run = 0;
+  off[0] = 0;
+  for (int i = 0; i < n; ++i) {
+    int c = cnt[i];
+    if (c > bound[i]) c = bound[i];
+    if (c < 0) c = 0;
+    run += c;
+    off[i + 1] = run;
+  }
+}
+void launch_prefix_counts(const int* d_cnt, const int* d_bound, int n, int* d_off, cudaStream_t s) {
+  prefix_counts_kernel<<<1, 32, 0, s>>>(d_cnt, d_bound, n, d_off);
+  NDS_CUDA(cudaGetLastError());
+}
+
+__global__ void __launch_bounds__(kThreads)
+union_copy_kernel(const UnionSeg* __restrict__ segs) {
+  const UnionSeg g = segs[blockIdx.y];
+  const int64_t n = row_count(g.n_dev, g.n_host);
+  const int64_t off = *g.off;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t o = off + i;
+    const bool ok = g.present && ((g.src_valid[i >> 5] >> (i & 31)) & 1u);
+    if (g.width == 4) reinterpret_cast<int32_t*>(g.dst)[o] = ok ? reinterpret_cast<const int32_t*>(g.src)[i] : 0;
+    else reinterpret_cast<int64_t*>(g.dst)[o] = ok ? reinterpret_cast<const int64_t*>(g.src)[i] : 0;
+    if (ok) atomicOr(&g.dst_valid[o >> 5], 1u << (o & 31));
+  }
+}
+void launch_union_copy(const UnionSeg* d_segs, int nsegs, int64_t max_rows, cudaStream_t s) {
+  if (nsegs <= 0) return;
+  int64_t gx = (max_rows + kThreads - 1) / kThreads;
+  if (gx < 1) gx = 1;
+  if (gx > 148 * 4) gx = 148 * 4;
+  union_copy_kernel<<<dim3((unsigned)gx, (unsigned)nsegs), kThreads, 0, s>>>(d_segs);
+  NDS_CUDA(cudaGetLastError());
+}
+
 // ------------------------------------------------------------------ hash group-by
 // The table is ALLOCATED for the upper bound of the input rows (cap_max slots) but SIZED on the device from the actual
 // row count: every kernel derives the same power-of-two capacity from n, so only that part is cleared, probed and

@@ -186,6 +186,22 @@ constexpr int kDictMatchThreads = 512;
 constexpr int kDictMatchEntries = 16384;
 constexpr int kDictMatchCoarseWords = 8192;     // 32 KB
 constexpr int kDictMatchMaxWords = 16384;       // 64 KB: dictionaries of up to 524288 entries
+// Concatenation of row sets under one column (rollup levels): segment = one source column of one level, copied to the rows
+// [*off, *off + n) of the destination; present == 0 writes NULLs.  The destination's validity words start out zero.
+struct UnionSeg {
+  const void* src;
+  const uint32_t* src_valid;
+  void* dst;
+  uint32_t* dst_valid;
+  const int* n_dev;            // row count of the level on the device, or nullptr: n_host is exact
+  int64_t n_host;
+  const int* off;              // first destination row (device)
+  int32_t width;               // 4 or 8 bytes per value
+  int32_t present;
+};
+void launch_union_copy(const UnionSeg* d_segs, int nsegs, int64_t max_rows, cudaStream_t s);
+// off[0] = 0, off[i + 1] = off[i] + min(cnt[i], bound[i]) for i < n (one thread); bound: the host's upper bounds (device copy)
+void launch_prefix_counts(const int* d_cnt, const int* d_bound, int n, int* d_off, cudaStream_t s);
 constexpr int kDmQueue = 6144;                  // queued rows (uint16 row in page) before pass B must run
 void launch_dict_match(const PageTask* tasks, const int32_t* dict_task, int nfiles, uint32_t max_dict, int width, const HashTable& ht,
                        const uint32_t* coarse, uint32_t coarse_words, uint32_t coarse_shift, uint32_t* out, uint32_t stride_words,

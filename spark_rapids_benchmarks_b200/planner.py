@@ -566,6 +566,8 @@ class Planner:
                                    else self.expr(e, agg_map, key_map))
             specs = agg_map.specs()
             dist = [a for a in specs if a['fn'] == 'count_distinct']
+            if dist and q.get('rollup'):
+                raise PlanError('count(DISTINCT ...) under GROUP BY ROLLUP is not supported yet')
             if dist:
                 # count(DISTINCT x) [+ other aggregates]: the inner aggregate groups by (keys, x) and carries the other
                 # aggregates as partial states; the outer one counts x per key (NULL x is not counted) and merges the states
@@ -586,6 +588,22 @@ class Planner:
                                            'expr': _col(a['name']), 'type': agg_map.types[a['name']]})
                 agg_node = {'op': 'aggregate', 'keys': [{'name': k['name'], 'expr': _col(k['name'])} for k in keys],
                             'aggs': outer_aggs, 'child': inner}
+            elif q.get('rollup'):
+                # GROUP BY ROLLUP(k1 .. kn): one engine operator runs the finest aggregate over the child, then every coarser
+                # level over the level before it (SUM of sums, SUM of counts, MIN of mins ...), and concatenates the levels
+                # with NULL for the rolled-up keys.  The grand total groups by a constant instead of by nothing: like
+                # Spark's Expand + Aggregate it yields no row when there is no input row.
+                if distributed:
+                    raise PlanError('GROUP BY ROLLUP is not supported across GPUs yet')
+                merged = [{'name': a['name'], 'fn': {'count': 'sum', 'count_star': 'sum'}.get(a['fn'], a['fn']),
+                           'expr': _col(a['name']), 'type': agg_map.types[a['name']]} for a in specs]
+                levels = [{'keys': [{'name': k['name'], 'expr': k['expr']} for k in keys], 'aggs': specs}]
+                for depth in range(len(keys) - 1, -1, -1):
+                    lkeys = [{'name': k['name'], 'expr': _col(k['name'])} for k in keys[:depth]]
+                    if not lkeys:
+                        lkeys = [{'name': '_rollup_all', 'expr': {'lit': 0, 'type': 'int64'}}]
+                    levels.append({'keys': lkeys, 'aggs': merged})
+                agg_node = {'op': 'rollup', 'levels': levels, 'child': node}
             else:
                 agg_node = {'op': 'aggregate', 'keys': [{'name': k['name'], 'expr': k['expr']} for k in keys],
                             'aggs': specs, 'child': node}
@@ -634,7 +652,7 @@ class Planner:
             # deterministic tie-break: the remaining output columns - unless the ORDER BY keys already contain
             # every GROUP BY key, in which case no two result rows can tie
             total = False
-            if is_agg and group_asts:
+            if is_agg and group_asts and not q.get('rollup'):      # (a rolled-up row ties with the NULL group of its key)
                 key_outs = []
                 for kname, _ in key_map.values():
                     key_outs.append([n for n, oir, _ in out_cols if oir == _col(kname)])

@@ -16,7 +16,8 @@ The AST is plain tuples:  ('col', qualifier|None, name) | ('num', text) | ('str'
  | ('isnull', x, negated) | ('between', x, lo, hi, negated) | ('in', x, [items], negated)
  | ('case', [(cond, value)...], else|None) | ('cast', x, typename) | ('star',)
  | ('exists', query, negated) | ('in_sub', x, query, negated)
-A query is {'select', 'from', 'where', 'group', 'having', 'order', 'limit', 'distinct', 'left_joins': [(alias, on_expr)]}.
+A query is {'select', 'from', 'where', 'group', 'having', 'order', 'limit', 'distinct', 'left_joins': [(alias, on_expr)],
+'rollup': GROUP BY ROLLUP(...)}.
 """
 import re
 
@@ -133,13 +134,21 @@ class Parser:
         for c in reversed(on_conds):
             where = c if where is None else ('bin', 'and', c, where)
         group = []
+        rollup = False
         if self.kw('group'):
             self.expect('kw', 'by')
-            if self.peek() == ('kw', 'rollup'):
-                raise SqlError('GROUP BY ROLLUP is not supported by the B200 planner yet')
-            group.append(self.expr())
-            while self.accept('op', ','):
+            if self.kw('rollup'):
+                # GROUP BY ROLLUP(a, b, ...): the grouping sets (a, b, ...), ..., (a), ()
+                rollup = True
+                self.expect('op', '(')
                 group.append(self.expr())
+                while self.accept('op', ','):
+                    group.append(self.expr())
+                self.expect('op', ')')
+            else:
+                group.append(self.expr())
+                while self.accept('op', ','):
+                    group.append(self.expr())
         having = self.expr() if self.kw('having') else None
         order = []
         if self.kw('order'):
@@ -155,7 +164,7 @@ class Parser:
             if self.peek()[0] != 'eof':
                 raise SqlError('unsupported trailing SQL: %r' % self.peek()[1])
         return {'select': select, 'from': tables, 'where': where, 'group': group, 'having': having, 'order': order, 'limit': limit,
-                'distinct': distinct, 'left_joins': left_joins}
+                'distinct': distinct, 'left_joins': left_joins, 'rollup': rollup}
 
     def select_item(self):
         if self.accept('op', '*'):

@@ -118,3 +118,60 @@ def test_count_distinct(gpu_engine, warehouse):
     got = _Sess(gpu_engine).sql("select count(distinct ss_customer_sk) c, count(ss_customer_sk) n from store_sales").toArrow().to_pylist()
     ss = oq.read_fact(warehouse, 'store_sales', 'ss_sold_date_sk', ['ss_customer_sk'])
     assert got == [{'c': pc.count_distinct(ss['ss_customer_sk']).as_py(), 'n': pc.count(ss['ss_customer_sk']).as_py()}]
+
+
+def _rollup_expected(table, keys, aggs, finish):
+    """Rows of GROUP BY ROLLUP(keys) restated with pyarrow: one group_by per level, NULL for the keys a level rolls up."""
+    rows = []
+    for depth in range(len(keys), -1, -1):
+        ks = keys[:depth]
+        if ks:
+            g = table.group_by(ks).aggregate(aggs)
+        else:
+            if table.num_rows == 0:
+                continue
+            g = table.append_column('_all', pa.array([0] * table.num_rows)).group_by(['_all']).aggregate(aggs)
+        for r in g.to_pylist():
+            rows.append(tuple(r.get(k) if k in ks else None for k in keys) + finish(r))
+    return sorted(rows, key=_key)
+
+
+def test_group_by_rollup(gpu_engine, warehouse):
+    """GROUP BY ROLLUP over a dimension (string keys, NULL groups beside rolled-up rows, avg = merged sum / merged count) and over
+    the fused fact scan (row counts of the levels only exist on the device); and no row at all when no row qualifies."""
+    sql = ("select i_category, i_class, count(*) n, count(i_current_price) c, sum(i_current_price) p, avg(i_current_price) a, "
+           "min(i_item_sk) lo, max(i_item_sk) hi from item where i_manager_id < 60 group by rollup(i_category, i_class) "
+           "order by i_category, i_class, n, lo limit 100000")
+    got = _Sess(gpu_engine).sql(sql).toArrow()
+    it = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_category', 'i_class', 'i_current_price', 'i_manager_id'])
+    it = it.filter(pc.less(it['i_manager_id'], 60).fill_null(False))
+
+    def fin(r):
+        s, c = r['i_current_price_sum'], r['i_current_price_count']
+        avg = None if not c else (decimal.Decimal(s) / c).quantize(decimal.Decimal('0.000001'), rounding=decimal.ROUND_HALF_UP)
+        return (r['count_all'], c, s, avg, r['i_item_sk_min'], r['i_item_sk_max'])
+    exp = _rollup_expected(it, ['i_category', 'i_class'],
+                           [([], 'count_all'), ('i_current_price', 'count'), ('i_current_price', 'sum'), ('i_item_sk', 'min'), ('i_item_sk', 'max')], fin)
+    rows = _rows(got, ['i_category', 'i_class', 'n', 'c', 'p', 'a', 'lo', 'hi'])
+    assert sorted(rows, key=_key) == exp
+    assert len(exp) > 20 and sum(1 for r in exp if r[0] is None and r[1] is None) >= 1
+    assert 'rollup_union' in [o['op'] for o in gpu_engine.last_stats()['ops']]
+    # the grand total is the last level: count(*) over everything that passed the filter
+    assert max(r[2] for r in rows) == it.num_rows
+
+    sql = ("select d_moy, i_category, sum(ss_quantity) q, count(*) n from store_sales, date_dim, item where ss_sold_date_sk = d_date_sk "
+           "and ss_item_sk = i_item_sk and i_manager_id < 30 and d_year = 1998 group by rollup(d_moy, i_category) "
+           "order by d_moy, i_category, n, q limit 100000")
+    got = _Sess(gpu_engine).sql(sql).toArrow()
+    ss = oq.read_fact(warehouse, 'store_sales', 'ss_sold_date_sk', ['ss_sold_date_sk', 'ss_item_sk', 'ss_quantity'])
+    dd = oq.read_dim(warehouse, 'date_dim', ['d_date_sk', 'd_moy', 'd_year'])
+    dd = dd.filter(pc.equal(dd['d_year'], 1998).fill_null(False)).select(['d_date_sk', 'd_moy'])
+    i2 = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_category', 'i_manager_id'])
+    i2 = i2.filter(pc.less(i2['i_manager_id'], 30).fill_null(False)).select(['i_item_sk', 'i_category'])
+    j = ss.join(dd, keys='ss_sold_date_sk', right_keys='d_date_sk', join_type='inner').join(i2, keys='ss_item_sk', right_keys='i_item_sk', join_type='inner')
+    exp = _rollup_expected(j, ['d_moy', 'i_category'], [('ss_quantity', 'sum'), ([], 'count_all')], lambda r: (r['ss_quantity_sum'], r['count_all']))
+    assert sorted(_rows(got, ['d_moy', 'i_category', 'q', 'n']), key=_key) == exp and len(exp) > 5
+    assert 'scan_probe' in [o['op'] for o in gpu_engine.last_stats()['ops']]
+
+    got = _Sess(gpu_engine).sql("select i_category, count(*) n from item where i_manager_id < 0 group by rollup(i_category) order by i_category").toArrow()
+    assert got.num_rows == 0

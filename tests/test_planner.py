@@ -57,7 +57,7 @@ def test_distributed_plan_splits_at_the_aggregate():
     'select i_item_sk from item where exists (select 1 from item where i_manager_id = 3)',          # uncorrelated / same table
     'select i_item_sk from item where i_item_sk = (select max(ss_item_sk) from store_sales)',      # scalar subquery
     'select i_item_sk, rank() over (partition by i_brand order by i_item_sk) from item',
-    'select i_brand, sum(i_item_sk) from item group by rollup(i_brand)',
+    'select i_brand, count(distinct i_item_sk) from item group by rollup(i_brand)',
     'with x as (select 1) select * from x',
     'select i_item_sk from item, store',                                     # cross join
     'select ss_item_sk from store_sales, store_returns where ss_item_sk = sr_item_sk',   # fact-fact join
@@ -272,3 +272,23 @@ def test_merge_aggregates_carry_the_declared_type():
     types = {a['name']: a['type'] for a in merge['aggs']}
     assert sorted(set(types.values())) == ['decimal(17,2)', 'int64']
     assert all('type' not in a for a in p['partial']['aggs'])
+
+
+def test_rollup_plan_shape():
+    """GROUP BY ROLLUP(a, b): one `rollup` node whose first level is the finest aggregate over the child and whose further levels
+    aggregate the level before them in merge form (SUM of counts ...); the grand total groups by a constant."""
+    p = planner.plan_sql('select i_category, i_class, count(*) n, avg(i_current_price) a, min(i_item_sk) lo from item '
+                         'group by rollup(i_category, i_class) order by i_category, i_class limit 10')
+    node = p['root']
+    while node['op'] != 'rollup':
+        node = node['child']
+    lv = node['levels']
+    assert [[k['name'] for k in l['keys']] for l in lv] == [['i_category', 'i_class'], ['i_category'], ['_rollup_all']]
+    assert {a['fn'] for a in lv[0]['aggs']} == {'count_star', 'sum', 'count', 'min'}
+    assert {a['fn'] for a in lv[1]['aggs']} == {'sum', 'min'} and all(a['expr'] == {'col': a['name']} for a in lv[2]['aggs'])
+    assert node['child']['op'] == 'scan'
+    # every output column breaks ties: a rolled-up row has the same keys as the NULL group of the key it rolled up
+    sort = p['root']
+    assert sort['op'] == 'sort' and len(sort['keys']) == 5
+    with pytest.raises(planner.PlanError):
+        planner.plan_sql('select i_category, count(*) from store_sales, item where ss_item_sk = i_item_sk group by rollup(i_category)', distributed=True)
