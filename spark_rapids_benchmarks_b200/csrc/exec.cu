@@ -2017,7 +2017,15 @@ struct Exec {
     return out;
   }
 
-  Batch aggregate_batch(const Json& node, Batch& in) {
+  // Window aggregates `fn(x) OVER (PARTITION BY keys)` (no ORDER BY, no frame; Spark: WindowExec): the
+  // child's rows with one more column per aggregate.  The partitions are accumulated like groups (agg_insert_kernel); then
+  // every row reads its partition's state (win_gather_kernel) - nothing is sorted and the groups are never compacted.
+  Batch window(const Json& node, std::vector<RuntimeFilter>& filters) {
+    Batch in = exec(node.at("child"), filters);
+    return aggregate_batch(node, in, true);
+  }
+
+  Batch aggregate_batch(const Json& node, Batch& in, bool per_row = false) {
     const Json& jkeys = node.at("keys");
     const Json& jaggs = node.at("aggs");
     const int nkeys = (int)jkeys.a.size(), naggs = (int)jaggs.a.size();
@@ -2029,7 +2037,8 @@ struct Exec {
     if (in.n_dev && in.n_exact < 0 &&
         (int64_t)agg_capacity_for(n) * (4 + 16 * (int64_t)std::max(naggs, 1)) + n * 8 * (int64_t)std::max(naggs, 1) > kAggReserveMax)
       n = count(in);
-    size_t st = begin_stat("aggregate");
+    if (per_row && nkeys == 0) fail("plan: a window aggregate needs PARTITION BY keys");
+    size_t st = begin_stat(per_row ? "window" : "aggregate");
     Blob bb;
     std::vector<LType> ktypes, atypes;
     std::vector<int> korigin;
@@ -2100,6 +2109,12 @@ struct Exec {
       agg_codes.push_back(std::move(agg_code_of_this));
     }
     Batch out;
+    if (per_row && n == 0) {
+      out = in;
+      for (int a = 0; a < naggs; ++a) { Column c; c.name = jaggs.a[a].str("name"); c.lt = atypes[a]; c.data = ar.alloc(16); c.valid = ar.zeros<uint32_t>(1); out.cols.push_back(c); }
+      end_stat(st, 0, 0);
+      return out;
+    }
     if (n == 0 && nkeys > 0) {
       out.n_max = 0;
       out.n_exact = 0;
@@ -2123,6 +2138,21 @@ struct Exec {
     int* ng = ar.zeros<int>(1);
     launch_agg_init(d_specs, naggs, in.rc(), cap, slots, acc, cnt, ovalid, vwords, s);
     launch_agg_insert(dev.progs, nkeys, d_specs, naggs, dev.ctx, in.rc(), slots, cap, acc, cnt, s);
+    if (per_row) {
+      launch_win_gather(dev.progs, nkeys, d_specs, naggs, dev.ctx, in.rc(), slots, cap, acc, cnt, ovals, ovalid, n, vwords, s);
+      launches += 3;
+      out = in;
+      for (int a = 0; a < naggs; ++a) {
+        Column c;
+        c.name = jaggs.a[a].str("name");
+        c.lt = atypes[a];
+        c.data = ovals + (int64_t)a * n;
+        c.valid = ovalid + (int64_t)a * vwords;
+        out.cols.push_back(c);
+      }
+      end_stat_rows(st, row_bytes_of(bb) * 2 + 4 + 24 * (int64_t)std::max(naggs, 1), in.rc());
+      return out;
+    }
     launch_agg_finalize(d_specs, naggs, slots, cap, in.rc(), acc, cnt, rep, ovals, ovalid, n, vwords, ng, s);
     launches += 3;
     if (nkeys == 0) { launch_agg_keyless_fix(d_specs, naggs, ng, rep, ovals, ovalid, n, vwords, s); ++launches; }
@@ -2823,6 +2853,7 @@ struct Exec {
     if (op == "join") return join(node, filters);
     if (op == "aggregate") return aggregate(node, filters);
     if (op == "rollup") return rollup(node, filters);
+    if (op == "window") return window(node, filters);
     if (op == "sort") return sort(node, filters);
     if (op == "exchange") return exchange(node, filters);
     fail("plan: unsupported plan node '" + op + "' (no CPU fallback exists)");

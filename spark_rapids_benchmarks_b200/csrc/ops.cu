@@ -595,6 +595,69 @@ agg_finalize_kernel(const AggSpec* __restrict__ aggs, int naggs, const uint32_t*
   }
 }
 
+// Window aggregates over PARTITION BY keys (no ORDER BY, no frame): after agg_insert_kernel has accumulated the partitions'
+// states, every ROW looks its partition's slot up again (same hash, same probe sequence, keys compared with the slot's
+// representative row) and reads the finished value - the groups are never compacted.  out_vals[a * out_stride + row].
+__global__ void __launch_bounds__(kThreads)
+win_gather_kernel(const Prog* __restrict__ progs, int nkeys, const AggSpec* __restrict__ aggs, int naggs, OpCtx c, const int* n_dev,
+                  int64_t n_host, const uint32_t* __restrict__ slots, uint32_t cap_max, const int64_t* __restrict__ acc,
+                  const int64_t* __restrict__ cnt, int64_t* __restrict__ out_vals, uint32_t* __restrict__ out_valid, int64_t out_stride,
+                  int64_t valid_stride_words) {
+  const int64_t n = row_count(n_dev, n_host);
+  const uint64_t cap = agg_capacity(n, cap_max);
+  const uint32_t mask = (uint32_t)cap - 1u;
+  const int64_t nround = (n + 31) & ~int64_t(31);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < nround; i += (int64_t)gridDim.x * blockDim.x) {
+    const bool live = i < n;
+    bool found = false;
+    uint32_t s = 0;
+    if (live) {
+      Val mine[kMaxGroupKeys];
+      uint64_t h = 0x9E3779B97F4A7C15ULL;
+      for (int k = 0; k < nkeys; ++k) {
+        mine[k] = eval_program(progs[k].code, progs[k].n, c.cols, c.lit, i);
+        uint64_t hv = !mine[k].ok ? 0x7F4A7C15ULL
+                      : (progs[k].kind == 2 ? hash_bytes((const uint8_t*)(uintptr_t)mine[k].v, mine[k].len) : (uint64_t)mine[k].v);
+        h = mix64(h ^ hv) + 0x9E3779B97F4A7C15ULL * (k + 1);
+      }
+      s = (uint32_t)mix64(h) & mask;
+      for (;;) {
+        const uint32_t prev = slots[s];
+        if (prev == 0) break;
+        const int64_t rep = (int64_t)prev - 1;
+        bool same = true;
+        for (int k = 0; k < nkeys && same; ++k) {
+          Val o = eval_program(progs[k].code, progs[k].n, c.cols, c.lit, rep);
+          same = val_equal(mine[k], o, progs[k].kind);
+        }
+        if (same) { found = true; break; }
+        s = (s + 1) & mask;
+      }
+    }
+    for (int a = 0; a < naggs; ++a) {
+      const int fn = aggs[a].fn;
+      const bool counting = fn == AGG_COUNT || fn == AGG_COUNT_STAR || fn == AGG_COUNT_REF;
+      int64_t v = 0;
+      bool ok = false;
+      if (found) {
+        const int64_t cv = cnt[(uint64_t)(fn == AGG_COUNT_REF ? aggs[a].prog : a) * cap + s];
+        v = counting ? cv : acc[(uint64_t)a * cap + s];
+        ok = counting ? true : cv > 0;
+      }
+      const uint32_t m = __ballot_sync(0xFFFFFFFFu, ok);
+      if ((threadIdx.x & 31) == 0) out_valid[a * valid_stride_words + (i >> 5)] = m;
+      if (live) out_vals[a * out_stride + i] = ok ? v : 0;
+    }
+  }
+}
+void launch_win_gather(const Prog* progs, int nkeys, const AggSpec* aggs, int naggs, OpCtx c, RowCount n, const uint32_t* slots,
+                       uint32_t cap_max, const int64_t* acc, const int64_t* cnt, int64_t* out_vals, uint32_t* out_valid, int64_t out_stride,
+                       int64_t valid_stride_words, cudaStream_t s) {
+  win_gather_kernel<<<grid_for(n.host), kThreads, 0, s>>>(progs, nkeys, aggs, naggs, c, n.dev, n.host, slots, cap_max, acc, cnt, out_vals,
+                                                          out_valid, out_stride, valid_stride_words);
+  NDS_CUDA(cudaGetLastError());
+}
+
 // A keyless aggregate (no GROUP BY) yields exactly one row, also over an empty input: COUNT = 0, everything else NULL.
 __global__ void agg_keyless_fix_kernel(const AggSpec* __restrict__ aggs, int naggs, int* ngroups, uint32_t* rep_out, int64_t* out_vals,
                                        uint32_t* out_valid, int64_t out_stride, int64_t valid_stride_words) {

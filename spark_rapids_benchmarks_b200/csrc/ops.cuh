@@ -249,6 +249,10 @@ void launch_agg_insert(const Prog* progs, int nkeys, const AggSpec* aggs, int na
 void launch_agg_finalize(const AggSpec* aggs, int naggs, const uint32_t* slots, uint32_t cap_max, RowCount n, const int64_t* acc,
                          const int64_t* cnt, uint32_t* rep_out, int64_t* out_vals, uint32_t* out_valid, int64_t out_stride,
                          int64_t valid_stride_words, int* ngroups, cudaStream_t s);
+// window aggregates: the partition's finished state per input row (after launch_agg_init + launch_agg_insert)
+void launch_win_gather(const Prog* progs, int nkeys, const AggSpec* aggs, int naggs, OpCtx c, RowCount n, const uint32_t* slots,
+                       uint32_t cap_max, const int64_t* acc, const int64_t* cnt, int64_t* out_vals, uint32_t* out_valid, int64_t out_stride,
+                       int64_t valid_stride_words, cudaStream_t s);
 void launch_agg_keyless_fix(const AggSpec* aggs, int naggs, int* ngroups, uint32_t* rep_out, int64_t* out_vals, uint32_t* out_valid,
                             int64_t out_stride, int64_t valid_stride_words, cudaStream_t s);
 void launch_str_maxlen(Prog p, OpCtx c, RowCount n, int* out_max, cudaStream_t s);

@@ -230,6 +230,8 @@ class Planner:
             if op == 'div':
                 return _fn('div', l, r), 'double'
             raise PlanError('operator %r' % op)
+        if kind == 'wcall':
+            return self.win_ref(ast, agg_map, key_map)
         if kind == 'call':
             fname = ast[1]
             if fname in AGG_FUNCS:
@@ -290,6 +292,48 @@ class Planner:
             return _col(sname), sum_t
         cname = agg_map.add('count', x, 'int64')
         if m:   # Spark Average(DecimalType(p,s)) -> DecimalType(p+4, s+4)
+            rt = 'decimal(%d,%d)' % (min(38, int(m.group(1)) + 4), int(m.group(2)) + 4)
+            return _fn('decavg', _col(sname), _col(cname), up=4, type=rt), rt
+        if t == 'double':
+            return _fn('div', _col(sname), _col(cname)), 'double'
+        return _fn('divi2f', _col(sname), _col(cname)), 'double'
+
+    # ---- window aggregates: fn(x) OVER (PARTITION BY keys) ---------------------------------------------------
+    def win_ref(self, ast, agg_map, key_map):
+        """The argument and the partition keys are expressions over the rows the window sees: the groups of an aggregating
+        query (sum(sum(x)) over (partition by k): the inner sum is an ordinary aggregate), else the joined rows."""
+        fname, args, part = ast[1], ast[2], ast[3]
+        wm = getattr(self, '_win', None)
+        if wm is None:
+            raise PlanError('window function %s() is not allowed here (select list only)' % fname)
+        if fname not in ('sum', 'avg', 'min', 'max', 'count'):
+            raise PlanError('window function %s() is not supported yet (sum / avg / min / max / count over PARTITION BY are)' % fname)
+        if not part:
+            raise PlanError('a window without PARTITION BY is not supported yet')
+        self._win = None                     # no window inside a window's argument
+        try:
+            pirs = [self.expr(p, agg_map, key_map)[0] for p in part]
+            if fname == 'count' and (not args or args[0] == ('star',)):
+                return _col(wm.add(pirs, 'count_star', None, 'int64')), 'int64'
+            if len(args) != 1:
+                raise PlanError('%s() takes one argument' % fname)
+            x, t = self.expr(args[0], agg_map, key_map)
+        finally:
+            self._win = wm
+        if fname == 'count':
+            return _col(wm.add(pirs, 'count', x, 'int64')), 'int64'
+        if not _is_num(t) and t != 'double':
+            raise PlanError('%s() over %s is not supported' % (fname, t))
+        m = _DEC.match(t)
+        if fname in ('min', 'max'):
+            rt = t if t != 'int32' else 'int64'
+            return _col(wm.add(pirs, fname, x, rt)), rt
+        sum_t = 'decimal(%d,%s)' % (min(38, int(m.group(1)) + 10), m.group(2)) if m else ('double' if t == 'double' else 'int64')
+        sname = wm.add(pirs, 'sum', x, sum_t)
+        if fname == 'sum':
+            return _col(sname), sum_t
+        cname = wm.add(pirs, 'count', x, 'int64')
+        if m:
             rt = 'decimal(%d,%d)' % (min(38, int(m.group(1)) + 4), int(m.group(2)) + 4)
             return _fn('decavg', _col(sname), _col(cname), up=4, type=rt), rt
         if t == 'double':
@@ -558,7 +602,11 @@ class Planner:
                 key_map[self.ast_key(g)] = (name, t)
                 keys.append({'name': name, 'expr': ir, '_type': t})
             agg_map = _AggMap()
-            sel_ir = [self.expr(e, agg_map, key_map) for e, _ in q['select']]
+            self._win = win_map = _WinMap()
+            try:
+                sel_ir = [self.expr(e, agg_map, key_map) for e, _ in q['select']]
+            finally:
+                self._win = None
             having_ir = self.expr(q['having'], agg_map, key_map)[0] if q.get('having') is not None else None
             order_extra = []
             for e, desc, nf in q['order']:
@@ -621,12 +669,24 @@ class Planner:
                 node = agg_node
             if having_ir is not None:        # HAVING: a filter over the (merged) groups
                 node = {'op': 'filter', 'cond': having_ir, 'child': node}
+            if win_map.parts:                # window aggregates see the groups that are left
+                if q.get('rollup'):
+                    raise PlanError('window functions over GROUP BY ROLLUP are not supported yet')
+                node = win_map.wrap(node)
             for (ir, t), name in zip(sel_ir, names):
                 out_cols.append((name, ir, t))
         else:
-            for (e, _), name in zip(q['select'], names):
-                ir, t = self.expr(e)
-                out_cols.append((name, ir, t))
+            self._win = win_map = _WinMap()
+            try:
+                for (e, _), name in zip(q['select'], names):
+                    ir, t = self.expr(e)
+                    out_cols.append((name, ir, t))
+            finally:
+                self._win = None
+            if win_map.parts:
+                if distributed:
+                    raise PlanError('window functions are not supported across GPUs yet')
+                node = win_map.wrap(node)
             order_extra = [None if (e[0] == 'col' and e[1] is None and e[2] in select_aliases) else self.expr(e)
                            for e, _, _ in q['order']]
         node = {'op': 'project', 'exprs': [{'name': n, 'expr': ir} for n, ir, _ in out_cols], 'child': node}
@@ -770,6 +830,37 @@ class Planner:
         if k == 'in':
             return min(1.0, 0.02 * len(c[2]))
         return 0.5
+
+
+class _WinMap:
+    """Window aggregates of a select list, grouped by their PARTITION BY list: one engine `window` node per list."""
+    def __init__(self):
+        self.parts = []          # [(partition irs, [agg specs])]
+        self.names = {}
+        self.count = 0
+
+    def add(self, pirs, fn, ir, rtype):
+        key = (repr(pirs), fn, repr(ir))
+        if key in self.names:
+            return self.names[key]
+        name = '_win%d' % self.count
+        self.count += 1
+        self.names[key] = name
+        spec = {'name': name, 'fn': fn}
+        if ir is not None:
+            spec['expr'] = ir
+        for p, specs in self.parts:
+            if repr(p) == repr(pirs):
+                specs.append(spec)
+                break
+        else:
+            self.parts.append((pirs, [spec]))
+        return name
+
+    def wrap(self, node):
+        for i, (pirs, specs) in enumerate(self.parts):
+            node = {'op': 'window', 'keys': [{'name': '_wk%d_%d' % (i, j), 'expr': p} for j, p in enumerate(pirs)], 'aggs': specs, 'child': node}
+        return node
 
 
 class _AggMap:

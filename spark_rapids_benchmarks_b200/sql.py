@@ -12,7 +12,7 @@ with `[NOT] EXISTS (SELECT ... FROM t WHERE ...)` and `x [NOT] IN (SELECT c FROM
 
 Anything outside the subset raises SqlError - the statement is never silently approximated.
 The AST is plain tuples:  ('col', qualifier|None, name) | ('num', text) | ('str', value) | ('null',)
- | ('call', fname, [args], distinct) | ('bin', op, l, r) | ('not', x) | ('neg', x)
+ | ('call', fname, [args], distinct) | ('wcall', fname, [args], [partition exprs]) | ('bin', op, l, r) | ('not', x) | ('neg', x)
  | ('isnull', x, negated) | ('between', x, lo, hi, negated) | ('in', x, [items], negated)
  | ('case', [(cond, value)...], else|None) | ('cast', x, typename) | ('star',)
  | ('exists', query, negated) | ('in_sub', x, query, negated)
@@ -342,8 +342,21 @@ class Parser:
                     while self.accept('op', ','):
                         args.append(self.expr())
                 self.expect('op', ')')
-                if self.peek() == ('kw', 'over'):
-                    raise SqlError('window functions are not supported by the B200 planner yet')
+                if self.kw('over'):
+                    # fn(x) OVER (PARTITION BY a, b): aggregate window functions without ORDER BY / frame
+                    if distinct:
+                        raise SqlError('DISTINCT in a window function is not supported')
+                    self.expect('op', '(')
+                    part = []
+                    if self.kw('partition'):
+                        self.expect('kw', 'by')
+                        part.append(self.expr())
+                        while self.accept('op', ','):
+                            part.append(self.expr())
+                    if self.peek() != ('op', ')'):
+                        raise SqlError('window ORDER BY / frames are not supported by the B200 planner yet')
+                    self.expect('op', ')')
+                    return ('wcall', tok[1], args, part)
                 return ('call', tok[1], args, distinct)
             if self.accept('op', '.'):
                 return ('col', tok[1], self.expect('id')[1])

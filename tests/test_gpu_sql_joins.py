@@ -175,3 +175,57 @@ def test_group_by_rollup(gpu_engine, warehouse):
 
     got = _Sess(gpu_engine).sql("select i_category, count(*) n from item where i_manager_id < 0 group by rollup(i_category) order by i_category").toArrow()
     assert got.num_rows == 0
+
+
+def test_window_aggregates_over_partitions(gpu_engine, warehouse):
+    """fn(x) OVER (PARTITION BY ...): over the joined rows of a dimension (two partition lists, NULL keys are a partition of their
+    own, decimal avg) and over the groups of a star join (NDS query98's revenue ratio: sum(sum(x)) over (partition by i_class))."""
+    import math
+    sql = ("select i_item_sk, i_class, avg(i_current_price) over (partition by i_class) a, count(*) over (partition by i_class) n, "
+           "count(i_current_price) over (partition by i_class) c, max(i_item_sk) over (partition by i_category, i_class) hi, "
+           "min(i_current_price) over (partition by i_category, i_class) lo from item where i_manager_id < 70 order by i_item_sk limit 100000")
+    got = _Sess(gpu_engine).sql(sql).toArrow().to_pylist()
+    it = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_category', 'i_class', 'i_current_price', 'i_manager_id'])
+    it = it.filter(pc.less(it['i_manager_id'], 70).fill_null(False)).to_pylist()
+    by_class, by_cc = {}, {}
+    for r in it:
+        by_class.setdefault(r['i_class'], []).append(r)
+        by_cc.setdefault((r['i_category'], r['i_class']), []).append(r)
+    exp = []
+    for r in sorted(it, key=lambda r: r['i_item_sk']):
+        g = by_class[r['i_class']]
+        prices = [x['i_current_price'] for x in g if x['i_current_price'] is not None]
+        avg = (sum(prices) / len(prices)).quantize(decimal.Decimal('0.000001'), rounding=decimal.ROUND_HALF_UP) if prices else None
+        g2 = by_cc[(r['i_category'], r['i_class'])]
+        p2 = [x['i_current_price'] for x in g2 if x['i_current_price'] is not None]
+        exp.append({'i_item_sk': r['i_item_sk'], 'i_class': r['i_class'], 'a': avg, 'n': len(g), 'c': len(prices),
+                    'hi': max(x['i_item_sk'] for x in g2), 'lo': min(p2) if p2 else None})
+    assert got == exp and len(exp) > 50 and any(r['n'] > 1 for r in exp)
+    assert [o['op'] for o in gpu_engine.last_stats()['ops']].count('window') == 2
+
+    sql = ("select i_item_id, i_class, sum(ss_ext_sales_price) itemrevenue, "
+           "sum(ss_ext_sales_price) * 100 / sum(sum(ss_ext_sales_price)) over (partition by i_class) revenueratio "
+           "from store_sales, item, date_dim where ss_item_sk = i_item_sk and i_category in ('Sports', 'Books', 'Home') "
+           "and ss_sold_date_sk = d_date_sk and d_year = 1998 group by i_item_id, i_class "
+           "order by i_class, i_item_id, itemrevenue limit 100000")
+    got = _Sess(gpu_engine).sql(sql).toArrow().to_pylist()
+    ss = oq.read_fact(warehouse, 'store_sales', 'ss_sold_date_sk', ['ss_sold_date_sk', 'ss_item_sk', 'ss_ext_sales_price'])
+    dd = oq.read_dim(warehouse, 'date_dim', ['d_date_sk', 'd_year'])
+    dd = dd.filter(pc.equal(dd['d_year'], 1998).fill_null(False)).select(['d_date_sk'])
+    i2 = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_item_id', 'i_class', 'i_category'])
+    i2 = i2.filter(pc.is_in(i2['i_category'], value_set=pa.array(['Sports', 'Books', 'Home'])).fill_null(False)).select(['i_item_sk', 'i_item_id', 'i_class'])
+    j = ss.join(dd, keys='ss_sold_date_sk', right_keys='d_date_sk', join_type='left semi').join(i2, keys='ss_item_sk', right_keys='i_item_sk', join_type='inner')
+    g = j.group_by(['i_item_id', 'i_class']).aggregate([('ss_ext_sales_price', 'sum')]).to_pylist()
+    tot = {}
+    for r in g:
+        if r['ss_ext_sales_price_sum'] is not None:
+            tot[r['i_class']] = tot.get(r['i_class'], 0) + r['ss_ext_sales_price_sum']
+    exp = sorted(((r['i_class'], r['i_item_id'], r['ss_ext_sales_price_sum']) for r in g), key=_key)
+    assert [(r['i_class'], r['i_item_id'], r['itemrevenue']) for r in got] == exp and len(exp) > 20
+    for r in got:
+        if r['itemrevenue'] is None or not tot.get(r['i_class']):
+            assert r['revenueratio'] is None
+        else:
+            assert math.isclose(r['revenueratio'], float(r['itemrevenue'] * 100) / float(tot[r['i_class']]), rel_tol=1e-9), r
+    ops = [o['op'] for o in gpu_engine.last_stats()['ops']]
+    assert 'window' in ops and 'scan_probe' in ops

@@ -292,3 +292,28 @@ def test_rollup_plan_shape():
     assert sort['op'] == 'sort' and len(sort['keys']) == 5
     with pytest.raises(planner.PlanError):
         planner.plan_sql('select i_category, count(*) from store_sales, item where ss_item_sk = i_item_sk group by rollup(i_category)', distributed=True)
+
+
+def test_window_plan_shape():
+    """fn(x) OVER (PARTITION BY k): one `window` node per partition list above the aggregate (sum(sum(x)) over ...: the inner sum is
+    an ordinary aggregate) or above the joins; ORDER BY / frames, rank() and an empty OVER () raise."""
+    p = planner.plan_sql('select i_class, i_brand, sum(i_current_price) s, sum(sum(i_current_price)) over (partition by i_class) t, '
+                         'count(*) over (partition by i_class) n, max(sum(i_item_sk)) over (partition by i_brand) m '
+                         'from item group by i_class, i_brand order by i_class, i_brand limit 10')
+    node = p['root']
+    seen = []
+    while 'child' in node:
+        seen.append(node['op'])
+        if node['op'] == 'window':
+            assert node['keys'][0]['expr'] in ({'col': 'i_class'}, {'col': 'i_brand'})
+        node = node['child']
+    assert seen == ['sort', 'project', 'window', 'window', 'aggregate']
+    p = planner.plan_sql('select i_item_sk, avg(i_current_price) over (partition by i_class) a from item where i_manager_id = 1')
+    w = p['root']['child']
+    assert w['op'] == 'window' and {a['fn'] for a in w['aggs']} == {'sum', 'count'} and w['child']['op'] == 'filter'
+    for bad in ('select i_item_sk, sum(i_item_sk) over () from item',
+                'select i_item_sk, sum(i_item_sk) over (partition by i_class order by i_item_sk) from item',
+                'select i_item_sk, row_number() over (partition by i_class) from item',
+                'select i_item_sk from item where sum(i_item_sk) over (partition by i_class) > 3'):
+        with pytest.raises(planner.PlanError):
+            planner.plan_sql(bad)
