@@ -71,7 +71,11 @@ class Planner:
         self.col_types = catalog or nds_schema.column_types()
         self.col_table = nds_schema.column_table()
         self.alias = {}
+        if any(e == ('star',) for e, _ in ast['select']):
+            raise PlanError('SELECT * is only supported over a derived table')
         for name, alias in ast['from']:
+            if isinstance(name, tuple):
+                raise PlanError('a derived table joined with other tables is not supported yet')
             if name not in nds_schema.SOURCE_TABLES:
                 raise PlanError('unknown table %r' % name)
             if alias in self.alias:
@@ -190,6 +194,10 @@ class Planner:
             for cond, val in reversed(ast[1]):
                 c, _ = self.expr(cond, agg_map, key_map)
                 v, tv = self.expr(val, agg_map, key_map)
+                if 'lit' in res and res['lit'] is None:          # ELSE NULL / no ELSE: a NULL of the branch's type
+                    res = {'lit': None, 'type': tv}
+                elif 'lit' in v and v['lit'] is None:
+                    v, tv = {'lit': None, 'type': t}, t
                 res, t = _fn('if', c, v, res), tv
             return res, t
         if kind == 'cast':
@@ -245,6 +253,11 @@ class Planner:
                 start = self.const_int(ast[2][1])
                 ln = self.const_int(ast[2][2]) if len(ast[2]) > 2 else (1 << 30)
                 return _fn('substr', x, start=start, len=ln), 'string'
+            if fname == 'abs' and len(ast[2]) == 1:
+                x, t = self.expr(ast[2][0], agg_map, key_map)
+                if not _is_num(t) and t != 'double':
+                    raise PlanError('abs() over %s' % t)
+                return _fn('if', _fn('lt', x, {'lit': 0, 'type': 'int64'}), _fn('neg', x), x), t
             raise PlanError('function %s() is not supported yet' % fname)
         raise PlanError('unsupported expression %r' % (kind,))
 
@@ -898,6 +911,67 @@ def _replace_partial_scan(node, replacement):
     return out
 
 
+class _DerivedPlanner(Planner):
+    """The outer query of `select ... from (subquery) alias [where ...] [order by ...] [limit n]`: columns resolve against the
+    subquery's output; no joins, no aggregation of its own (NDS query53 / 63 / 89: a filter over window results)."""
+    def __init__(self, ast, alias, outputs):
+        self.q = ast
+        self.col_types = {o['name']: o['type'] for o in outputs}
+        self.col_table = {}
+        self.alias = {alias: '__derived__'}
+        self.tables = ['__derived__']
+        self.outputs = outputs
+
+    def resolve(self, node):
+        _, qual, name = node
+        if qual is not None and qual not in self.alias:
+            raise PlanError('unknown table alias %r' % qual)
+        if name not in self.col_types:
+            raise PlanError('unknown column %r' % name)
+        return name
+
+    def plan_over(self, inner_root):
+        q = self.q
+        if q['group'] or q.get('having') is not None or q.get('distinct') or q.get('left_joins'):
+            raise PlanError('GROUP BY / HAVING / DISTINCT / joins over a derived table are not supported yet')
+        node = inner_root
+        if q['where'] is not None:
+            cond, t = self.expr(q['where'])
+            if t != 'bool':
+                raise PlanError('WHERE condition is not boolean')
+            node = {'op': 'filter', 'cond': cond, 'child': node}
+        out_cols = []
+        for e, alias in q['select']:
+            if e == ('star',):
+                out_cols += [(o['name'], _col(o['name']), o['type']) for o in self.outputs]
+                continue
+            ir, t = self.expr(e)
+            out_cols.append((alias if alias else self.text(e), ir, t))
+        names = [n for n, _, _ in out_cols]
+        if len(set(names)) != len(names):
+            raise PlanError('duplicate output column names over a derived table')
+        node = {'op': 'project', 'exprs': [{'name': n, 'expr': ir} for n, ir, _ in out_cols], 'child': node}
+        if q['order'] or q['limit'] is not None:
+            keys, used = [], []
+            for e, desc, nf in q['order']:
+                if e[0] == 'col' and e[1] is None and e[2] in names:
+                    name = e[2]
+                else:
+                    ir, _ = self.expr(e)
+                    match = [n for n, oir, _ in out_cols if oir == ir]
+                    if not match:
+                        raise PlanError('ORDER BY expression %s is not in the select list (not supported yet)' % self.text(e))
+                    name = match[0]
+                k = {'expr': _col(name), 'desc': bool(desc)}
+                if nf is not None:
+                    k['nulls_first'] = bool(nf)
+                keys.append(k)
+                used.append(name)
+            keys += [{'expr': _col(n), 'desc': False} for n in names if n not in used]      # deterministic tie-break
+            node = {'op': 'sort', 'keys': keys, 'limit': -1 if q['limit'] is None else q['limit'], 'child': node}
+        return {'root': node, 'output': [{'name': n, 'type': t} for n, _, t in out_cols]}
+
+
 def plan_sql(sql_text, distributed=False, sharded=None):
     """SQL text -> plan dict ({'root': ..., 'output': [...]} [+ 'partial', 'fused' | 'replicated'])."""
     body = '\n'.join(l for l in sql_text.split('\n') if not l.strip().startswith('--'))
@@ -905,4 +979,13 @@ def plan_sql(sql_text, distributed=False, sharded=None):
         ast = parse(body)
     except SqlError as e:
         raise PlanError(str(e))
+    if len(ast['from']) == 1 and isinstance(ast['from'][0][0], tuple):
+        # select ... from (subquery) alias ...: the subquery is planned as a query of its own, the outer query over its output
+        if distributed:
+            raise PlanError('derived tables are not supported across GPUs yet')
+        (_, sub), alias = ast['from'][0]
+        if len(sub['from']) == 1 and isinstance(sub['from'][0][0], tuple):
+            raise PlanError('nested derived tables are not supported yet')
+        inner = Planner(sub).plan()
+        return _DerivedPlanner(ast, alias, inner['output']).plan_over(inner['root'])
     return Planner(ast).plan(distributed=distributed, sharded=sharded)

@@ -168,7 +168,7 @@ class Parser:
 
     def select_item(self):
         if self.accept('op', '*'):
-            raise SqlError('SELECT * is not supported by the B200 planner yet')
+            return (('star',), None)       # the planner expands it over a derived table; over base tables it raises
         e = self.expr()
         alias = None
         if self.kw('as'):
@@ -178,8 +178,16 @@ class Parser:
         return (e, alias)
 
     def table_ref(self):
-        if self.peek() == ('op', '('):
-            raise SqlError('derived tables (subqueries in FROM) are not supported by the B200 planner yet')
+        if self.accept('op', '('):
+            # derived table: ( select ... ) [as] alias
+            if self.peek() != ('kw', 'select'):
+                raise SqlError('expected a subquery after ( in FROM')
+            sub = self.parse_query(sub=True)
+            self.expect('op', ')')
+            self.kw('as')
+            if self.peek()[0] != 'id':
+                raise SqlError('a derived table needs an alias')
+            return (('subquery', sub), self.next()[1])
         name = self.expect('id')[1]
         alias = None
         if self.kw('as'):

@@ -229,3 +229,34 @@ def test_window_aggregates_over_partitions(gpu_engine, warehouse):
             assert math.isclose(r['revenueratio'], float(r['itemrevenue'] * 100) / float(tot[r['i_class']]), rel_tol=1e-9), r
     ops = [o['op'] for o in gpu_engine.last_stats()['ops']]
     assert 'window' in ops and 'scan_probe' in ops
+
+
+def test_derived_table_with_window_filter(gpu_engine, warehouse):
+    """NDS query53's shape: a star join grouped by (manufacturer, day of week; the small warehouse sells in one quarter only), the manufacturer's average over them as a window
+    aggregate, and an outer query over that derived table keeping the quarters that deviate by more than 10 %."""
+    sql = ("select * from (select i_manufact_id, sum(ss_sales_price) sum_sales, "
+           "avg(sum(ss_sales_price)) over (partition by i_manufact_id) avg_quarterly_sales "
+           "from item, store_sales, date_dim where ss_item_sk = i_item_sk and ss_sold_date_sk = d_date_sk "
+           "and d_year = 1998 group by i_manufact_id, d_dow) tmp1 "
+           "where case when avg_quarterly_sales > 0 then abs(sum_sales - avg_quarterly_sales) / avg_quarterly_sales else null end > 0.1 "
+           "order by avg_quarterly_sales, sum_sales, i_manufact_id limit 100")
+    got = _Sess(gpu_engine).sql(sql).toArrow()
+    ss = oq.read_fact(warehouse, 'store_sales', 'ss_sold_date_sk', ['ss_sold_date_sk', 'ss_item_sk', 'ss_sales_price'])
+    dd = oq.read_dim(warehouse, 'date_dim', ['d_date_sk', 'd_year', 'd_dow'])
+    dd = dd.filter(pc.equal(dd['d_year'], 1998).fill_null(False)).select(['d_date_sk', 'd_dow'])
+    it = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_manufact_id'])
+    j = ss.join(dd, keys='ss_sold_date_sk', right_keys='d_date_sk', join_type='inner').join(it, keys='ss_item_sk', right_keys='i_item_sk', join_type='inner')
+    g = j.group_by(['i_manufact_id', 'd_dow']).aggregate([('ss_sales_price', 'sum')]).to_pylist()
+    per = {}
+    for r in g:
+        per.setdefault(r['i_manufact_id'], []).append(r['ss_sales_price_sum'])
+    rows = []
+    for r in g:
+        sums = [x for x in per[r['i_manufact_id']] if x is not None]
+        avg = (sum(sums) / len(sums)).quantize(decimal.Decimal('0.000001'), rounding=decimal.ROUND_HALF_UP) if sums else None
+        s = r['ss_sales_price_sum']
+        if avg is not None and avg > 0 and s is not None and abs(float(s - avg)) / float(avg) > 0.1:
+            rows.append((avg, s, r['i_manufact_id']))
+    exp = sorted(rows, key=_key)[:100]
+    assert _rows(got, ['avg_quarterly_sales', 'sum_sales', 'i_manufact_id']) == exp and len(exp) > 10
+    assert got.schema.names == ['i_manufact_id', 'sum_sales', 'avg_quarterly_sales']

@@ -52,6 +52,9 @@ def test_distributed_plan_splits_at_the_aggregate():
 
 @pytest.mark.parametrize('text', [
     'select * from item',
+    'select * from (select i_item_sk from item) t, store',                     # derived table joined with another table
+    'select x from (select i_item_sk from item) t',                            # unknown column of the derived table
+    'select count(*) from (select i_item_sk from item) t',                     # aggregation over a derived table
     'select i_item_sk from item where i_item_sk in (select ss_item_sk from store_sales, date_dim where ss_sold_date_sk = d_date_sk)',   # multi-table subquery
     'select i_item_sk from item where i_item_sk not in (select ss_customer_sk from store_sales)',   # NOT IN over a nullable column
     'select i_item_sk from item where exists (select 1 from item where i_manager_id = 3)',          # uncorrelated / same table
@@ -317,3 +320,24 @@ def test_window_plan_shape():
                 'select i_item_sk from item where sum(i_item_sk) over (partition by i_class) > 3'):
         with pytest.raises(planner.PlanError):
             planner.plan_sql(bad)
+
+
+def test_derived_table_plan_shape():
+    """select ... from (subquery) alias where ... order by ... limit: the subquery's plan with a filter / project / sort of the outer
+    query on top (NDS query53 / 63 / 89); CASE ... ELSE NULL takes the type of its branch; abs(x) = if(x < 0, -x, x)."""
+    p = planner.plan_sql('select * from (select i_manufact_id, sum(i_current_price) s, avg(sum(i_current_price)) over (partition by i_manufact_id) a '
+                         'from item group by i_manufact_id, i_class) t where case when a > 0 then abs(s - a) / a else null end > 0.1 '
+                         'order by a, s, i_manufact_id limit 100')
+    ops = []
+    node = p['root']
+    while 'child' in node:
+        ops.append(node['op'])
+        node = node['child']
+    assert ops == ['sort', 'project', 'filter', 'project', 'window', 'aggregate'] and node['op'] == 'scan'
+    assert [o['name'] for o in p['output']] == ['i_manufact_id', 's', 'a']
+    cond = p['root']['child']['child']['cond']
+    case = cond['args'][0]
+    assert cond['fn'] == 'gt' and case['fn'] == 'if' and case['args'][2] == {'lit': None, 'type': 'double'}
+    assert case['args'][1]['fn'] == 'div' and case['args'][1]['args'][0]['fn'] == 'if'      # abs()
+    p = planner.plan_sql('select t.i_item_sk k, i_class from (select i_item_sk, i_class from item where i_manager_id = 1) as t order by k')
+    assert [o['name'] for o in p['output']] == ['k', 'i_class']
