@@ -101,7 +101,7 @@ struct TableColumn {
   std::vector<PageTask> task_tmpl;
   std::vector<int64_t> file_bytes_in;    // per file: page payload bytes + dictionary bytes a scan of it reads
   // Device copies for the fused scan (fused_scan.cu, expand_tasks_kernel): the templates, and per page its offset inside
-  // its file's validity / rank scratch (words) and the index of its first 4096-row chunk inside its file; per file the
+  // its file's validity / rank scratch (words) and the index of its first 2048-row chunk inside its file; per file the
   // totals a scan needs to place a file's pages without touching them on the host.
   PageTask* d_tmpl = nullptr;
   uint2* d_page_aux = nullptr;           // x: vr words before this page in its file, y: chunks before this page in its file

@@ -275,13 +275,13 @@ struct Exec {
   // filter in shared memory (scan_probe_persistent_kernel).  OFF by default: measured slower than the plain kernel (SF10
   // query7: 0.49 ms against 0.21 ms) - one 1024-thread CTA per SM hides the load latency worse than six 256-thread CTAs,
   // and the saved join-table reads do not make up for it.  Kept switchable for the next attempt (several chunks in flight
-  // per CTA); options.probe_bloom_chunks = 4096-row chunks from which it applies.
+  // per CTA); options.probe_bloom_chunks = 2048-row chunks from which it applies.
   bool probe_bloom = false;
   int64_t probe_bloom_chunks = 4 * 148;
   // options.dict_match=false: the fused scan tests the first join per row (dictionary entry, then join table) instead of
-  // once per dictionary entry and file (dict_match_kernel); options.dict_match_chunks = 4096-row chunks from which it applies
+  // once per dictionary entry and file (dict_match_kernel); options.dict_match_chunks = 2048-row chunks from which it applies
   bool dict_match = true;
-  int64_t dict_match_chunks = 2048;
+  int64_t dict_match_chunks = 4096;
   bool build_filter = true;      // options.build_filter=false: a filtered build side is filtered first, then built (two or three launches)
   bool fused_scan = true;        // options.fused_scan=false: fact scans decode every column, then probe (decode_fast.cu + ops.cu)
   bool trace = false;            // options.trace: host timeline marks + time spent waiting in each stream sync
@@ -311,7 +311,7 @@ struct Exec {
       fused_scan = options->bool_or("fused_scan", true);
       probe_bloom = options->bool_or("probe_bloom", false);
       dict_match = options->bool_or("dict_match", true);
-      dict_match_chunks = options->int_or("dict_match_chunks", 2048);
+      dict_match_chunks = options->int_or("dict_match_chunks", 4096);
       build_filter = options->bool_or("build_filter", true);
       probe_bloom_chunks = options->int_or("probe_bloom_chunks", 4 * 148);
       topk_stream = options->bool_or("topk_stream", true);

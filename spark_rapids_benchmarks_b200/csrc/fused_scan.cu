@@ -5,7 +5,7 @@
 // (decode_fast.cu) and probing the decoded keys afterwards (ops.cu, join_probe_chain_kernel) writes and re-reads the
 // decoded columns and decodes measures of rows no join keeps.  Here instead:
 //
-//   scan_probe_kernel    one CTA per 4096-row chunk of a page.  Pass A: every thread decodes four consecutive values of
+//   scan_probe_kernel    one CTA per 2048-row chunk of a page.  Pass A: every thread decodes four consecutive values of
 //                        the FIRST probe key straight from the page (validity / rank words of the def kernel -> value
 //                        index -> bit-packed dictionary index -> dictionary -> key), probes that join's table and queues
 //                        the hits in shared memory.  Pass B: one thread per queued row decodes the remaining probe keys
@@ -350,7 +350,7 @@ void launch_dict_match(const PageTask* tasks, const int32_t* dict_task, int nfil
   NDS_CUDA(cudaGetLastError());
 }
 
-// One CTA per (page of the first key column, part): the page's 4096-row chunks c = part, part + split, ...  The views and
+// One CTA per (page of the first key column, part): the page's 2048-row chunks c = part, part + split, ...  The views and
 // the file's match bits are set up once; pass A queues rows chunk after chunk and pass B runs when the queue may not hold
 // another chunk (an unselective join) or after the last chunk (the usual case: one pass B with all warps busy).
 __global__ void __launch_bounds__(kFusedThreads)

@@ -140,7 +140,7 @@ void launch_join_probe_chain(const ProbeChain& chain, RowCount n, uint32_t* out_
 // fused_scan.cu: page decode -> join-chain probe in one kernel over directly addressable pages, then the payload
 // columns of the surviving rows only (late materialisation).
 constexpr int kFusedThreads = 256;
-constexpr int kFusedChunk = 4096;          // rows of one page a CTA of scan_probe_kernel handles
+constexpr int kFusedChunk = 2048;          // rows of one page a CTA of scan_probe_kernel handles
 struct FusedChunk {
   uint32_t page;                           // index into every key column's task array (the key columns are aligned page for page)
   uint32_t row0;                           // first row of the chunk inside the page (multiple of kFusedChunk)
@@ -211,7 +211,7 @@ void launch_scan_probe(const FusedScanArgs& args, int nchunks, cudaStream_t s);
 // dense join table -> existence filter (bloom_words pre-zeroed words)
 void launch_bloom_from_dense(const uint32_t* dense, uint32_t range, uint32_t shift, uint32_t* bloom, cudaStream_t s);
 // One (column, selected file) pair of a fused scan: expand_tasks_kernel copies the file's page templates, patches them
-// and lists the pages (def kernel) and their 4096-row chunks (probe kernel) - the host only places whole files.
+// and lists the pages (def kernel) and their 2048-row chunks (probe kernel) - the host only places whole files.
 struct FileJob {
   const PageTask* tmpl;                    // the column's templates (device), indexed from page 0 of the table
   const uint2* page_aux;

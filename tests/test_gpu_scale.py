@@ -83,7 +83,7 @@ def test_six_query_stream_at_sf1_matches_oracle(sf1, pi):
             assert rows_equal(got.to_pylist(), exp.to_pylist()), (query, source, got.to_pylist()[:3], exp.to_pylist()[:3])
             ops = [o['op'] for o in eng.last_stats()['ops']]
             assert 'scan_probe' in ops and not any(o.startswith('decode:store_sales') for o in ops), (query, ops)   # the fused fact scan ran
-        # the first join tested per dictionary entry and file (dict_match_kernel; on by itself from 2048 chunks = 8 M rows)
+        # the first join tested per dictionary entry and file (dict_match_kernel; on by itself from 4096 chunks = 8 M rows)
         got = pa.Table.from_batches([eng.execute(planner.plan_sql(sql), options={'dict_match_chunks': 1})])
         assert rows_equal(got.to_pylist(), exp.to_pylist()), query
         assert 'dict_match' in [o['op'] for o in eng.last_stats()['ops']], query
