@@ -2664,6 +2664,58 @@ struct Exec {
   // ---------------------------------------------------------------- sort / top-k
   Batch sort(const Json& node, std::vector<RuntimeFilter>& filters) {
     Batch in = exec(node.at("child"), filters);
+    return sort_batch(node, in);
+  }
+
+  // rank() / row_number() / dense_rank() OVER (PARTITION BY p ORDER BY o) (Spark: WindowExec over a sort):
+  // the child's rows sorted by (p, o) - the node's `keys`, the first `npart` of them the partition keys - plus one int64 column
+  // per function.  Partition and tie-group starts come from comparing neighbouring rows and a max-scan (ops.cu, launch_rank).
+  Batch rank(const Json& node, std::vector<RuntimeFilter>& filters) {
+    Batch in = exec(node.at("child"), filters);
+    Batch out = sort_batch(node, in);
+    size_t st = begin_stat("rank");
+    const Json& jkeys = node.at("keys");
+    const int nkeys = (int)jkeys.a.size(), npart = (int)node.int_or("npart", 0);
+    if (npart < 0 || npart > nkeys || nkeys > 16) fail("plan: rank node with bad key counts");
+    const int64_t n = out.rc().host;
+    const Json& jf = node.at("funcs");
+    int64_t* cols3[3] = {nullptr, nullptr, nullptr};
+    std::vector<std::pair<std::string, int>> names;
+    for (const Json& f : jf.a) {
+      const std::string& fn = f.str("fn");
+      const int which = fn == "rank" ? 0 : (fn == "row_number" ? 1 : (fn == "dense_rank" ? 2 : -1));
+      if (which < 0) fail("plan: unsupported ranking function '" + fn + "'");
+      if (!cols3[which]) cols3[which] = ar.alloc_n<int64_t>(std::max<int64_t>(n, 1));
+      names.emplace_back(f.str("name"), which);
+    }
+    if (n > 0) {
+      Blob bb;
+      for (const Json& k : jkeys.a) {
+        std::vector<Instr> code;
+        LType t = compile(k.at("expr"), out, bb, code);
+        bb.add_prog(code, t);
+      }
+      Blob::Dev dev = bb.upload(ar, s);
+      uint32_t* scratch = ar.alloc_n<uint32_t>(3 * n);
+      launch_rank(dev.progs, nkeys, npart, dev.ctx, out.rc(), scratch, scratch + n, scratch + 2 * n, cols3[0], cols3[1], cols3[2], s);
+      launches += 3;
+    }
+    const int64_t vwords = (std::max<int64_t>(n, 1) + 31) / 32 + 1;
+    uint32_t* ones = ar.alloc_n<uint32_t>(vwords);
+    NDS_CUDA(cudaMemsetAsync(ones, 0xFF, (size_t)vwords * 4, s));
+    for (const auto& nm : names) {
+      Column c;
+      c.name = nm.first;
+      c.lt.kind = LType::INT;
+      c.data = cols3[nm.second];
+      c.valid = ones;
+      out.cols.push_back(c);
+    }
+    end_stat(st, n * 16, n);
+    return out;
+  }
+
+  Batch sort_batch(const Json& node, Batch& in) {
     const int64_t limit = node.int_or("limit", -1);
     size_t st = begin_stat("sort");
     // compile the keys first: the string keys' maximum lengths are measured on the device with the row count still
@@ -2854,6 +2906,7 @@ struct Exec {
     if (op == "aggregate") return aggregate(node, filters);
     if (op == "rollup") return rollup(node, filters);
     if (op == "window") return window(node, filters);
+    if (op == "rank") return rank(node, filters);
     if (op == "sort") return sort(node, filters);
     if (op == "exchange") return exchange(node, filters);
     fail("plan: unsupported plan node '" + op + "' (no CPU fallback exists)");

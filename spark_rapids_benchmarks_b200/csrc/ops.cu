@@ -658,6 +658,80 @@ void launch_win_gather(const Prog* progs, int nkeys, const AggSpec* aggs, int na
   NDS_CUDA(cudaGetLastError());
 }
 
+// Ranking window functions over rows SORTED by (partition keys, order keys): row j starts a partition when a partition key
+// differs from row j - 1's, a tie group when an order key differs too (NULL equals NULL, as in GROUP BY).
+//   rank_flags_kernel  m1[j] = j if row j starts a partition else 0;  m2[j] = j if it starts a tie group else 0;  d[j] = 1 / 0
+//   rank_scan_kernel   in place: m1, m2 -> inclusive max (the row's partition / tie-group start), d -> inclusive sum
+//   rank_out_kernel    rank = tie start - partition start + 1, row_number = j - partition start + 1,
+//                      dense_rank = d[j] - d[partition start] + 1
+__global__ void __launch_bounds__(kThreads)
+rank_flags_kernel(const Prog* __restrict__ progs, int nkeys, int npart, OpCtx c, const int* n_dev, int64_t n_host,
+                  uint32_t* __restrict__ m1, uint32_t* __restrict__ m2, uint32_t* __restrict__ d) {
+  const int64_t n = row_count(n_dev, n_host);
+  for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+    bool newp = j == 0, newo = j == 0;
+    for (int k = 0; k < nkeys && !newp && j > 0; ++k) {
+      if (newo && k >= npart) break;
+      const Val a = eval_program(progs[k].code, progs[k].n, c.cols, c.lit, j);
+      const Val b = eval_program(progs[k].code, progs[k].n, c.cols, c.lit, j - 1);
+      if (!val_equal(a, b, progs[k].kind)) { if (k < npart) newp = true; else newo = true; }
+    }
+    newo = newo || newp;
+    m1[j] = newp ? (uint32_t)j : 0u;
+    m2[j] = newo ? (uint32_t)j : 0u;
+    d[j] = newo ? 1u : 0u;
+  }
+}
+constexpr int kRankScanThreads = 1024;
+__global__ void __launch_bounds__(kRankScanThreads)
+rank_scan_kernel(const int* n_dev, int64_t n_host, uint32_t* __restrict__ m1, uint32_t* __restrict__ m2, uint32_t* __restrict__ d) {
+  __shared__ uint32_t w1[32], w2[32], w3[32];
+  __shared__ uint32_t c1, c2, c3;
+  const int64_t n = row_count(n_dev, n_host);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) { c1 = 0; c2 = 0; c3 = 0; }
+  __syncthreads();
+  for (int64_t base = 0; base < n; base += kRankScanThreads) {
+    const int64_t j = base + tid;
+    uint32_t v1 = j < n ? m1[j] : 0u, v2 = j < n ? m2[j] : 0u, v3 = j < n ? d[j] : 0u;
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t a = __shfl_up_sync(0xFFFFFFFFu, v1, o), b = __shfl_up_sync(0xFFFFFFFFu, v2, o), e = __shfl_up_sync(0xFFFFFFFFu, v3, o);
+      if (lane >= o) { v1 = max(v1, a); v2 = max(v2, b); v3 += e; }
+    }
+    if (lane == 31) { w1[warp] = v1; w2[warp] = v2; w3[warp] = v3; }
+    __syncthreads();
+    uint32_t p1 = c1, p2 = c2, p3 = c3;
+    for (int q = 0; q < warp; ++q) { p1 = max(p1, w1[q]); p2 = max(p2, w2[q]); p3 += w3[q]; }
+    v1 = max(v1, p1);
+    v2 = max(v2, p2);
+    v3 += p3;
+    if (j < n) { m1[j] = v1; m2[j] = v2; d[j] = v3; }
+    __syncthreads();
+    if (tid == kRankScanThreads - 1) { c1 = v1; c2 = v2; c3 = v3; }     // (rows past n carry zeros / nothing new: harmless)
+    __syncthreads();
+  }
+}
+__global__ void __launch_bounds__(kThreads)
+rank_out_kernel(const int* n_dev, int64_t n_host, const uint32_t* __restrict__ m1, const uint32_t* __restrict__ m2,
+                const uint32_t* __restrict__ d, int64_t* __restrict__ out_rank, int64_t* __restrict__ out_rown, int64_t* __restrict__ out_dense) {
+  const int64_t n = row_count(n_dev, n_host);
+  for (int64_t j = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; j < n; j += (int64_t)gridDim.x * blockDim.x) {
+    const uint32_t ps = m1[j];
+    if (out_rank) out_rank[j] = (int64_t)m2[j] - ps + 1;
+    if (out_rown) out_rown[j] = j - ps + 1;
+    if (out_dense) out_dense[j] = (int64_t)d[j] - d[ps] + 1;
+  }
+}
+void launch_rank(const Prog* progs, int nkeys, int npart, OpCtx c, RowCount n, uint32_t* m1, uint32_t* m2, uint32_t* d, int64_t* out_rank,
+                 int64_t* out_rown, int64_t* out_dense, cudaStream_t s) {
+  rank_flags_kernel<<<grid_for(n.host), kThreads, 0, s>>>(progs, nkeys, npart, c, n.dev, n.host, m1, m2, d);
+  NDS_CUDA(cudaGetLastError());
+  rank_scan_kernel<<<1, kRankScanThreads, 0, s>>>(n.dev, n.host, m1, m2, d);
+  NDS_CUDA(cudaGetLastError());
+  rank_out_kernel<<<grid_for(n.host), kThreads, 0, s>>>(n.dev, n.host, m1, m2, d, out_rank, out_rown, out_dense);
+  NDS_CUDA(cudaGetLastError());
+}
+
 // A keyless aggregate (no GROUP BY) yields exactly one row, also over an empty input: COUNT = 0, everything else NULL.
 __global__ void agg_keyless_fix_kernel(const AggSpec* __restrict__ aggs, int naggs, int* ngroups, uint32_t* rep_out, int64_t* out_vals,
                                        uint32_t* out_valid, int64_t out_stride, int64_t valid_stride_words) {

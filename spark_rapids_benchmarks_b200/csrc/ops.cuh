@@ -249,6 +249,10 @@ void launch_agg_insert(const Prog* progs, int nkeys, const AggSpec* aggs, int na
 void launch_agg_finalize(const AggSpec* aggs, int naggs, const uint32_t* slots, uint32_t cap_max, RowCount n, const int64_t* acc,
                          const int64_t* cnt, uint32_t* rep_out, int64_t* out_vals, uint32_t* out_valid, int64_t out_stride,
                          int64_t valid_stride_words, int* ngroups, cudaStream_t s);
+// ranking window functions over rows sorted by (npart partition keys, then the order keys): three launches; m1 / m2 / d are
+// scratch of one word per row; an output pointer may be null
+void launch_rank(const Prog* progs, int nkeys, int npart, OpCtx c, RowCount n, uint32_t* m1, uint32_t* m2, uint32_t* d, int64_t* out_rank,
+                 int64_t* out_rown, int64_t* out_dense, cudaStream_t s);
 // window aggregates: the partition's finished state per input row (after launch_agg_init + launch_agg_insert)
 void launch_win_gather(const Prog* progs, int nkeys, const AggSpec* aggs, int naggs, OpCtx c, RowCount n, const uint32_t* slots,
                        uint32_t cap_max, const int64_t* acc, const int64_t* cnt, int64_t* out_vals, uint32_t* out_valid, int64_t out_stride,

@@ -315,12 +315,30 @@ class Planner:
     def win_ref(self, ast, agg_map, key_map):
         """The argument and the partition keys are expressions over the rows the window sees: the groups of an aggregating
         query (sum(sum(x)) over (partition by k): the inner sum is an ordinary aggregate), else the joined rows."""
-        fname, args, part = ast[1], ast[2], ast[3]
+        fname, args, part, order = ast[1], ast[2], ast[3], ast[4]
         wm = getattr(self, '_win', None)
         if wm is None:
             raise PlanError('window function %s() is not allowed here (select list only)' % fname)
+        if fname in ('rank', 'row_number', 'dense_rank'):
+            # ranking functions: the rows sorted by (partition keys, order keys), positions from neighbour comparisons
+            if args or not order:
+                raise PlanError('%s() takes no argument and needs OVER (... ORDER BY ...)' % fname)
+            self._win = None
+            try:
+                pirs = [self.expr(p, agg_map, key_map)[0] for p in part]
+                okeys = []
+                for e, desc, nf in order:
+                    k = {'expr': self.expr(e, agg_map, key_map)[0], 'desc': bool(desc)}
+                    if nf is not None:
+                        k['nulls_first'] = bool(nf)
+                    okeys.append(k)
+            finally:
+                self._win = wm
+            return _col(wm.add_rank(pirs, okeys, fname)), 'int64'
         if fname not in ('sum', 'avg', 'min', 'max', 'count'):
-            raise PlanError('window function %s() is not supported yet (sum / avg / min / max / count over PARTITION BY are)' % fname)
+            raise PlanError('window function %s() is not supported yet' % fname)
+        if order:
+            raise PlanError('aggregate window functions with ORDER BY (running totals) are not supported yet')
         if not part:
             raise PlanError('a window without PARTITION BY is not supported yet')
         self._win = None                     # no window inside a window's argument
@@ -682,7 +700,7 @@ class Planner:
                 node = agg_node
             if having_ir is not None:        # HAVING: a filter over the (merged) groups
                 node = {'op': 'filter', 'cond': having_ir, 'child': node}
-            if win_map.parts:                # window aggregates see the groups that are left
+            if win_map.parts or win_map.ranks:                # window functions see the groups that are left
                 if q.get('rollup'):
                     raise PlanError('window functions over GROUP BY ROLLUP are not supported yet')
                 node = win_map.wrap(node)
@@ -696,7 +714,7 @@ class Planner:
                     out_cols.append((name, ir, t))
             finally:
                 self._win = None
-            if win_map.parts:
+            if win_map.parts or win_map.ranks:
                 if distributed:
                     raise PlanError('window functions are not supported across GPUs yet')
                 node = win_map.wrap(node)
@@ -849,6 +867,7 @@ class _WinMap:
     """Window aggregates of a select list, grouped by their PARTITION BY list: one engine `window` node per list."""
     def __init__(self):
         self.parts = []          # [(partition irs, [agg specs])]
+        self.ranks = []          # [(partition irs, order keys, [{'name', 'fn'}])]
         self.names = {}
         self.count = 0
 
@@ -870,9 +889,26 @@ class _WinMap:
             self.parts.append((pirs, [spec]))
         return name
 
+    def add_rank(self, pirs, okeys, fn):
+        key = ('rank', repr(pirs), repr(okeys), fn)
+        if key in self.names:
+            return self.names[key]
+        name = '_win%d' % self.count
+        self.count += 1
+        self.names[key] = name
+        for p, o, funcs in self.ranks:
+            if repr(p) == repr(pirs) and repr(o) == repr(okeys):
+                funcs.append({'name': name, 'fn': fn})
+                break
+        else:
+            self.ranks.append((pirs, okeys, [{'name': name, 'fn': fn}]))
+        return name
+
     def wrap(self, node):
         for i, (pirs, specs) in enumerate(self.parts):
             node = {'op': 'window', 'keys': [{'name': '_wk%d_%d' % (i, j), 'expr': p} for j, p in enumerate(pirs)], 'aggs': specs, 'child': node}
+        for pirs, okeys, funcs in self.ranks:
+            node = {'op': 'rank', 'keys': [{'expr': p, 'desc': False} for p in pirs] + okeys, 'npart': len(pirs), 'funcs': funcs, 'child': node}
         return node
 
 
@@ -941,12 +977,17 @@ class _DerivedPlanner(Planner):
                 raise PlanError('WHERE condition is not boolean')
             node = {'op': 'filter', 'cond': cond, 'child': node}
         out_cols = []
-        for e, alias in q['select']:
-            if e == ('star',):
-                out_cols += [(o['name'], _col(o['name']), o['type']) for o in self.outputs]
-                continue
-            ir, t = self.expr(e)
-            out_cols.append((alias if alias else self.text(e), ir, t))
+        self._win = win_map = _WinMap()
+        try:
+            for e, alias in q['select']:
+                if e == ('star',):
+                    out_cols += [(o['name'], _col(o['name']), o['type']) for o in self.outputs]
+                    continue
+                ir, t = self.expr(e)
+                out_cols.append((alias if alias else self.text(e), ir, t))
+        finally:
+            self._win = None
+        node = win_map.wrap(node)
         names = [n for n, _, _ in out_cols]
         if len(set(names)) != len(names):
             raise PlanError('duplicate output column names over a derived table')
@@ -980,12 +1021,17 @@ def plan_sql(sql_text, distributed=False, sharded=None):
     except SqlError as e:
         raise PlanError(str(e))
     if len(ast['from']) == 1 and isinstance(ast['from'][0][0], tuple):
-        # select ... from (subquery) alias ...: the subquery is planned as a query of its own, the outer query over its output
         if distributed:
             raise PlanError('derived tables are not supported across GPUs yet')
-        (_, sub), alias = ast['from'][0]
-        if len(sub['from']) == 1 and isinstance(sub['from'][0][0], tuple):
-            raise PlanError('nested derived tables are not supported yet')
-        inner = Planner(sub).plan()
-        return _DerivedPlanner(ast, alias, inner['output']).plan_over(inner['root'])
+        return _plan_query(ast)
     return Planner(ast).plan(distributed=distributed, sharded=sharded)
+
+
+def _plan_query(ast):
+    """select ... from (subquery) alias ... (also nested, also written as WITH alias AS (subquery)): the subquery is planned as a
+    query of its own, the outer query over its output."""
+    if len(ast['from']) == 1 and isinstance(ast['from'][0][0], tuple):
+        (_, sub), alias = ast['from'][0]
+        inner = _plan_query(sub)
+        return _DerivedPlanner(ast, alias, inner['output']).plan_over(inner['root'])
+    return Planner(ast).plan()

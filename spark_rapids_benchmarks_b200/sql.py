@@ -12,7 +12,7 @@ with `[NOT] EXISTS (SELECT ... FROM t WHERE ...)` and `x [NOT] IN (SELECT c FROM
 
 Anything outside the subset raises SqlError - the statement is never silently approximated.
 The AST is plain tuples:  ('col', qualifier|None, name) | ('num', text) | ('str', value) | ('null',)
- | ('call', fname, [args], distinct) | ('wcall', fname, [args], [partition exprs]) | ('bin', op, l, r) | ('not', x) | ('neg', x)
+ | ('call', fname, [args], distinct) | ('wcall', fname, [args], [partition exprs], [(expr, desc, nulls_first)]) | ('bin', op, l, r) | ('not', x) | ('neg', x)
  | ('isnull', x, negated) | ('between', x, lo, hi, negated) | ('in', x, [items], negated)
  | ('case', [(cond, value)...], else|None) | ('cast', x, typename) | ('star',)
  | ('exists', query, negated) | ('in_sub', x, query, negated)
@@ -60,6 +60,7 @@ class Parser:
     def __init__(self, text):
         self.t = tokenize(text)
         self.i = 0
+        self.ctes = {}           # WITH name AS (...): name -> [ast, references]
 
     def peek(self, k=0):
         return self.t[self.i + k]
@@ -93,8 +94,20 @@ class Parser:
 
     # ---- statement -----------------------------------------------------------------------------
     def parse_query(self, sub=False):
-        if self.peek() == ('kw', 'with'):
-            raise SqlError('WITH (common table expressions) is not supported by the B200 planner yet')
+        if self.kw('with'):
+            # WITH name AS (subquery) [, ...]: a name that is referenced once is the same as a derived table with that alias
+            if sub:
+                raise SqlError('WITH inside a subquery is not supported')
+            while True:
+                name = self.expect('id')[1]
+                self.expect('kw', 'as')
+                self.expect('op', '(')
+                if self.peek() != ('kw', 'select'):
+                    raise SqlError('expected a subquery after WITH %s AS (' % name)
+                self.ctes[name] = [self.parse_query(sub=True), 0]
+                self.expect('op', ')')
+                if not self.accept('op', ','):
+                    break
         self.expect('kw', 'select')
         distinct = bool(self.kw('distinct'))
         select = [self.select_item()]
@@ -194,6 +207,12 @@ class Parser:
             alias = self.expect('id')[1]
         elif self.peek()[0] == 'id':
             alias = self.next()[1]
+        if name in self.ctes:
+            cte = self.ctes[name]
+            cte[1] += 1
+            if cte[1] > 1:
+                raise SqlError('common table expression %r is referenced more than once (not supported yet)' % name)
+            return (('subquery', cte[0]), alias or name)
         return (name, alias or name)
 
     def order_item(self):
@@ -361,10 +380,16 @@ class Parser:
                         part.append(self.expr())
                         while self.accept('op', ','):
                             part.append(self.expr())
+                    order = []
+                    if self.kw('order'):
+                        self.expect('kw', 'by')
+                        order.append(self.order_item())
+                        while self.accept('op', ','):
+                            order.append(self.order_item())
                     if self.peek() != ('op', ')'):
-                        raise SqlError('window ORDER BY / frames are not supported by the B200 planner yet')
+                        raise SqlError('window frames (ROWS / RANGE BETWEEN ...) are not supported by the B200 planner yet')
                     self.expect('op', ')')
-                    return ('wcall', tok[1], args, part)
+                    return ('wcall', tok[1], args, part, order)
                 return ('call', tok[1], args, distinct)
             if self.accept('op', '.'):
                 return ('col', tok[1], self.expect('id')[1])

@@ -260,3 +260,58 @@ def test_derived_table_with_window_filter(gpu_engine, warehouse):
     exp = sorted(rows, key=_key)[:100]
     assert _rows(got, ['avg_quarterly_sales', 'sum_sales', 'i_manufact_id']) == exp and len(exp) > 10
     assert got.schema.names == ['i_manufact_id', 'sum_sales', 'avg_quarterly_sales']
+
+
+def test_ranking_windows_and_nested_derived_tables(gpu_engine, warehouse):
+    """rank() / row_number() / dense_rank() OVER (PARTITION BY ... ORDER BY ...) over groups with many ties, filtered by an outer query
+    on the rank; the same over a star join; a CTE referenced once and nested derived tables."""
+    sql = ("select * from (select i_category, i_class, sum(i_current_price) s, count(*) n, "
+           "rank() over (partition by i_category order by count(*) desc) rk, "
+           "row_number() over (partition by i_category order by count(*) desc, i_class) rn, "
+           "dense_rank() over (partition by i_category order by count(*) desc) dr "
+           "from item group by i_category, i_class) t where rk <= 5 order by i_category, rn")
+    got = _Sess(gpu_engine).sql(sql).toArrow()
+    it = oq.read_dim(warehouse, 'item', ['i_category', 'i_class', 'i_current_price'])
+    g = it.group_by(['i_category', 'i_class']).aggregate([('i_current_price', 'sum'), ([], 'count_all')]).to_pylist()
+    cats = {}
+    for r in g:
+        cats.setdefault(r['i_category'], []).append(r)
+    exp = []
+    for cat, rows in cats.items():
+        ns = sorted({r['count_all'] for r in rows}, reverse=True)
+        order = sorted(rows, key=lambda r: (-r['count_all'], r['i_class'] is not None, r['i_class'] or ''))
+        for rn, r in enumerate(order, 1):
+            rk = 1 + sum(1 for x in rows if x['count_all'] > r['count_all'])
+            if rk <= 5:
+                exp.append((cat, r['i_class'], r['i_current_price_sum'], r['count_all'], rk, rn, 1 + ns.index(r['count_all'])))
+    exp.sort(key=lambda r: ((r[0] is not None, r[0] or ''), r[5]))
+    assert _rows(got, ['i_category', 'i_class', 's', 'n', 'rk', 'rn', 'dr']) == exp
+    assert len(exp) > 20 and any(r[4] != r[5] for r in exp) and any(r[4] != r[6] for r in exp)       # ties: rank, row_number and dense_rank differ
+    assert [o['op'] for o in gpu_engine.last_stats()['ops']].count('rank') == 2
+
+    sql = ("select * from (select i_category, d_dow, sum(ss_quantity) q, rank() over (partition by i_category order by sum(ss_quantity) desc) rk "
+           "from store_sales, item, date_dim where ss_item_sk = i_item_sk and ss_sold_date_sk = d_date_sk and d_year = 1998 "
+           "group by i_category, d_dow) t where rk <= 2 order by i_category, rk, d_dow")
+    got = _Sess(gpu_engine).sql(sql).toArrow()
+    ss = oq.read_fact(warehouse, 'store_sales', 'ss_sold_date_sk', ['ss_sold_date_sk', 'ss_item_sk', 'ss_quantity'])
+    dd = oq.read_dim(warehouse, 'date_dim', ['d_date_sk', 'd_year', 'd_dow'])
+    dd = dd.filter(pc.equal(dd['d_year'], 1998).fill_null(False)).select(['d_date_sk', 'd_dow'])
+    i2 = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_category'])
+    j = ss.join(dd, keys='ss_sold_date_sk', right_keys='d_date_sk', join_type='inner').join(i2, keys='ss_item_sk', right_keys='i_item_sk', join_type='inner')
+    g = j.group_by(['i_category', 'd_dow']).aggregate([('ss_quantity', 'sum')]).to_pylist()
+    exp = []
+    for r in g:
+        q = r['ss_quantity_sum']
+        # ORDER BY q DESC: NULL sums last; rank = 1 + the groups of the category that sort before
+        before = sum(1 for x in g if x['i_category'] == r['i_category'] and x['ss_quantity_sum'] is not None and (q is None or x['ss_quantity_sum'] > q))
+        if before + 1 <= 2:
+            exp.append((r['i_category'], r['d_dow'], q, before + 1))
+    exp.sort(key=lambda r: ((r[0] is not None, r[0] or ''), r[3], r[1]))
+    assert _rows(got, ['i_category', 'd_dow', 'q', 'rk']) == exp and len(exp) > 5
+
+    a = _Sess(gpu_engine).sql("with t as (select i_item_sk k, i_class c from item where i_manager_id < 30) "
+                              "select k from (select k, c from t where c > 'i_class_03') v where k < 5000 order by k").toArrow()
+    it = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_class', 'i_manager_id']).to_pylist()
+    want = sorted(r['i_item_sk'] for r in it if r['i_manager_id'] is not None and r['i_manager_id'] < 30 and r['i_class'] is not None
+                  and r['i_class'] > 'i_class_03' and r['i_item_sk'] < 5000)
+    assert a['k'].to_pylist() == want and len(want) > 3

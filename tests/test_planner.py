@@ -59,9 +59,11 @@ def test_distributed_plan_splits_at_the_aggregate():
     'select i_item_sk from item where i_item_sk not in (select ss_customer_sk from store_sales)',   # NOT IN over a nullable column
     'select i_item_sk from item where exists (select 1 from item where i_manager_id = 3)',          # uncorrelated / same table
     'select i_item_sk from item where i_item_sk = (select max(ss_item_sk) from store_sales)',      # scalar subquery
-    'select i_item_sk, rank() over (partition by i_brand order by i_item_sk) from item',
+    'select i_item_sk, sum(i_item_sk) over (partition by i_brand order by i_item_sk) from item',     # running total
+    'select i_item_sk, rank() over (partition by i_brand) from item',                               # ranking without ORDER BY
+    'select i_item_sk, sum(i_item_sk) over (partition by i_brand rows between 1 preceding and current row) from item',
     'select i_brand, count(distinct i_item_sk) from item group by rollup(i_brand)',
-    'with x as (select 1) select * from x',
+    'with x as (select i_item_sk from item) select a.i_item_sk from x a, x b',    # a CTE referenced twice
     'select i_item_sk from item, store',                                     # cross join
     'select ss_item_sk from store_sales, store_returns where ss_item_sk = sr_item_sk',   # fact-fact join
     'select distinct i_brand, count(*) from item group by i_brand',
@@ -316,7 +318,7 @@ def test_window_plan_shape():
     assert w['op'] == 'window' and {a['fn'] for a in w['aggs']} == {'sum', 'count'} and w['child']['op'] == 'filter'
     for bad in ('select i_item_sk, sum(i_item_sk) over () from item',
                 'select i_item_sk, sum(i_item_sk) over (partition by i_class order by i_item_sk) from item',
-                'select i_item_sk, row_number() over (partition by i_class) from item',
+                'select i_item_sk, ntile(4) over (partition by i_class order by i_item_sk) from item',
                 'select i_item_sk from item where sum(i_item_sk) over (partition by i_class) > 3'):
         with pytest.raises(planner.PlanError):
             planner.plan_sql(bad)
@@ -341,3 +343,35 @@ def test_derived_table_plan_shape():
     assert case['args'][1]['fn'] == 'div' and case['args'][1]['args'][0]['fn'] == 'if'      # abs()
     p = planner.plan_sql('select t.i_item_sk k, i_class from (select i_item_sk, i_class from item where i_manager_id = 1) as t order by k')
     assert [o['name'] for o in p['output']] == ['k', 'i_class']
+    # a CTE that is referenced once is a derived table; derived tables nest
+    a = planner.plan_sql('with t as (select i_item_sk, i_class from item where i_manager_id = 1) select t.i_item_sk k, i_class from t order by k')
+    assert a == p
+    n = planner.plan_sql('select k from (select i_item_sk k, c from (select i_item_sk, i_class c from item) u where c > \'m\') v where k < 10 order by k')
+    ops = []
+    node = n['root']
+    while 'child' in node:
+        ops.append(node['op'])
+        node = node['child']
+    assert ops == ['sort', 'project', 'filter', 'project', 'filter', 'project'] and node['op'] == 'scan'
+
+
+def test_ranking_window_plan_shape():
+    """rank() / row_number() / dense_rank() OVER (PARTITION BY p ORDER BY o): a `rank` node whose keys are the partition keys followed
+    by the order keys; functions over the same window share it; in a derived table the outer query can filter on the rank."""
+    p = planner.plan_sql('select * from (select i_category, i_class, sum(i_current_price) s, '
+                         'rank() over (partition by i_category order by sum(i_current_price) desc) rk, '
+                         'row_number() over (partition by i_category order by sum(i_current_price) desc) rn, '
+                         'dense_rank() over (order by i_class) dr from item group by i_category, i_class) t where rk <= 3 '
+                         'order by i_category, rk, i_class')
+    node = p['root']
+    ranks = []
+    while 'child' in node:
+        if node['op'] == 'rank':
+            ranks.append(node)
+        node = node['child']
+    assert len(ranks) == 2
+    by_np = {r['npart']: r for r in ranks}
+    assert [f['fn'] for f in by_np[1]['funcs']] == ['rank', 'row_number']
+    assert by_np[1]['keys'] == [{'expr': {'col': 'i_category'}, 'desc': False}, {'expr': {'col': '_agg0'}, 'desc': True}]
+    assert by_np[0]['keys'] == [{'expr': {'col': 'i_class'}, 'desc': False}] and by_np[0]['funcs'][0]['fn'] == 'dense_rank'
+    assert [o['name'] for o in p['output']] == ['i_category', 'i_class', 's', 'rk', 'rn', 'dr']
