@@ -92,7 +92,7 @@ def test_unsupported_statement_is_reported_failed(gpu_engine, tmp_path):
     sess.register_table = lambda *a: None
     stream = tmp_path / 'q.sql'
     stream.write_text('-- start query 1 in stream 0 using template query98.tpl\n'
-                      'select i_item_id, rank() over (partition by i_class order by i_item_id) from item\n;\n'
+                      'select i_item_id, sum(i_item_sk) over (partition by i_class order by i_item_id) from item\n;\n'
                       '-- end query 1 in stream 0 using template query98.tpl\n')
     qd = nds_power.gen_sql_from_stream(str(stream))
     with contextlib.redirect_stdout(io.StringIO()):
