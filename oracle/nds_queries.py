@@ -321,7 +321,44 @@ def q7(sql, warehouse, shard=None, partial=False):
     return _to_table(order_rows(rows, names, [('i_item_id', False)], 100), schema)
 
 
-QUERIES = {'query3': q3, 'query7': q7, 'query19': q19, 'query42': q42, 'query52': q52, 'query55': q55}
+def q98(sql, warehouse, shard=None, partial=False):
+    """TPC-DS query98 (Spark dialect of the NDS templates): item revenue over 31 days and its share of the class's revenue -
+    sum(sum(x)) over (partition by i_class) restated as a second pass over the groups.  The ratio is a double (the engine's
+    `/`; Spark would give a decimal), compared with a relative tolerance by the tests."""
+    import datetime
+    cats = re.search(r"i_category\s+in\s*\(\s*'([^']*)'\s*,\s*'([^']*)'\s*,\s*'([^']*)'\s*\)", sql).groups()
+    d0 = datetime.date.fromisoformat(_str(sql, r"cast\('([^']*)'\s+as\s+date\)"))
+    days = _int(sql, r'interval\s+(\d+)\s+days')
+    d1 = d0 + datetime.timedelta(days=days)
+    dd = read_dim(warehouse, 'date_dim', ['d_date_sk', 'd_date'])
+    dd = dd.filter(pc.and_(pc.greater_equal(dd['d_date'], pa.scalar(d0, type=dd.schema.field('d_date').type)),
+                           pc.less_equal(dd['d_date'], pa.scalar(d1, type=dd.schema.field('d_date').type))).fill_null(False))
+    dd = dd.select(['d_date_sk'])
+    it = read_dim(warehouse, 'item', ['i_item_sk', 'i_item_id', 'i_item_desc', 'i_category', 'i_class', 'i_current_price'])
+    it = it.filter(pc.is_in(it['i_category'], value_set=pa.array(list(cats))).fill_null(False))
+    t = _star(warehouse, ['ss_sold_date_sk', 'ss_item_sk', 'ss_ext_sales_price'], [('ss_item_sk', it, 'i_item_sk')], dd, shard)
+    keys = ['i_item_id', 'i_item_desc', 'i_category', 'i_class', 'i_current_price']
+    groups = _group_sum(t, keys)
+    total = {}
+    for r in groups:
+        if r['_sum'] is not None:
+            total[r['i_class']] = total.get(r['i_class'], 0) + r['_sum']
+    rows = []
+    for r in groups:
+        s, tot = r['_sum'], total.get(r['i_class'])
+        ratio = (float(s * 100) / float(tot)) if (s is not None and tot) else None
+        row = {k: r[k] for k in keys}
+        row['itemrevenue'] = s
+        row['revenueratio'] = ratio
+        rows.append(row)
+    names = keys + ['itemrevenue', 'revenueratio']
+    schema = pa.schema([('i_item_id', pa.string()), ('i_item_desc', pa.string()), ('i_category', pa.string()), ('i_class', pa.string()),
+                        ('i_current_price', pa.decimal128(7, 2)), ('itemrevenue', DEC172), ('revenueratio', pa.float64())])
+    order = [('i_category', False), ('i_class', False), ('i_item_id', False), ('i_item_desc', False), ('revenueratio', False)]
+    return _to_table(order_rows(rows, names, order, None), schema)
+
+
+QUERIES = {'query3': q3, 'query7': q7, 'query19': q19, 'query42': q42, 'query52': q52, 'query55': q55, 'query98': q98}
 
 
 def run_query(name, sql, warehouse, shard=None):

@@ -215,6 +215,12 @@ class Planner:
                 l, _ = self.expr(ast[2], agg_map, key_map)
                 r, _ = self.expr(ast[3], agg_map, key_map)
                 return _fn(op, l, r), 'bool'
+            if op in ('add', 'sub') and isinstance(ast[3], tuple) and ast[3][0] == 'interval':
+                # date literal +/- INTERVAL n DAYS: folded (the NDS templates only add intervals to constants)
+                l, tl = self.expr(ast[2], agg_map, key_map)
+                if tl != 'date' or 'lit' not in l or l['lit'] is None:
+                    raise PlanError('INTERVAL arithmetic is only supported on date constants')
+                return {'lit': l['lit'] + (ast[3][1] if op == 'add' else -ast[3][1]), 'type': 'date'}, 'date'
             l, tl = self.expr(ast[2], agg_map, key_map)
             r, tr = self.expr(ast[3], agg_map, key_map)
             if op in ('eq', 'ne', 'lt', 'le', 'gt', 'ge'):
@@ -238,6 +244,8 @@ class Planner:
             if op == 'div':
                 return _fn('div', l, r), 'double'
             raise PlanError('operator %r' % op)
+        if kind == 'interval':
+            raise PlanError('INTERVAL is only supported as date constant +/- INTERVAL n DAYS')
         if kind == 'wcall':
             return self.win_ref(ast, agg_map, key_map)
         if kind == 'call':

@@ -14,7 +14,7 @@ Anything outside the subset raises SqlError - the statement is never silently ap
 The AST is plain tuples:  ('col', qualifier|None, name) | ('num', text) | ('str', value) | ('null',)
  | ('call', fname, [args], distinct) | ('wcall', fname, [args], [partition exprs], [(expr, desc, nulls_first)]) | ('bin', op, l, r) | ('not', x) | ('neg', x)
  | ('isnull', x, negated) | ('between', x, lo, hi, negated) | ('in', x, [items], negated)
- | ('case', [(cond, value)...], else|None) | ('cast', x, typename) | ('star',)
+ | ('interval', n, 'day') | ('case', [(cond, value)...], else|None) | ('cast', x, typename) | ('star',)
  | ('exists', query, negated) | ('in_sub', x, query, negated)
 A query is {'select', 'from', 'where', 'group', 'having', 'order', 'limit', 'distinct', 'left_joins': [(alias, on_expr)],
 'rollup': GROUP BY ROLLUP(...)}.
@@ -328,6 +328,17 @@ class Parser:
             return ('str', tok[1])
         if tok == ('kw', 'null'):
             return ('null',)
+        if tok == ('kw', 'interval'):
+            # INTERVAL n DAY[S] (Spark's form in the NDS templates: cast('1999-02-22' as date) + interval 30 days)
+            n = self.next()
+            if n[0] == 'str':
+                n = ('num', n[1].strip())
+            if n[0] != 'num' or not n[1].isdigit():
+                raise SqlError('INTERVAL needs an integer count')
+            unit = self.next()
+            if unit[0] != 'id' or unit[1].lower() not in ('day', 'days'):
+                raise SqlError('only INTERVAL n DAYS is supported')
+            return ('interval', int(n[1]), 'day')
         if tok == ('op', '('):
             if self.peek() == ('kw', 'select'):
                 raise SqlError('scalar subqueries are not supported by the B200 planner yet')

@@ -29,6 +29,8 @@ def _params(seed, stream):
         'GEN': ['M', 'F'][int(r.integers(0, 2))],
         'MS': datagen.MARITAL[int(r.integers(0, 5))],
         'ES': datagen.EDUCATION[int(r.integers(0, 7))],
+        # query98 (drawn after the six-query stream's parameters, so those keep their values)
+        'CAT1': 'Sports', 'CAT2': 'Books', 'CAT3': 'Home', 'SDATE': '1998-01-05',
     }
 
 
@@ -106,6 +108,20 @@ TEMPLATES = {
  order by ext_price desc, i_brand_id
  LIMIT 100""",
 }
+
+
+# Statements beyond the six-query bench stream that the planner and the engine also run (tests; not part of the metric)
+EXTRA = ['query98']
+TEMPLATES['query98'] = """select i_item_id, i_item_desc, i_category, i_class, i_current_price,
+       sum(ss_ext_sales_price) as itemrevenue,
+       sum(ss_ext_sales_price)*100/sum(sum(ss_ext_sales_price)) over (partition by i_class) as revenueratio
+ from store_sales, item, date_dim
+ where ss_item_sk = i_item_sk
+   and i_category in ('{CAT1}', '{CAT2}', '{CAT3}')
+   and ss_sold_date_sk = d_date_sk
+   and d_date between cast('{SDATE}' as date) and (cast('{SDATE}' as date) + interval 30 days)
+ group by i_item_id, i_item_desc, i_category, i_class, i_current_price
+ order by i_category, i_class, i_item_id, i_item_desc, revenueratio"""
 
 
 def render(template_name, seed=datagen.SEED, stream=0, overrides=None):

@@ -47,6 +47,21 @@ def rows_equal(got, exp):
     return True
 
 
+def test_query98_matches_the_oracle(gpu_engine, warehouse):
+    """A seventh NDS statement beyond the bench stream: query98 as the Spark-dialect template has it (date constant + INTERVAL,
+    five group keys incl. the 200-character item description, sum(sum(x)) OVER (PARTITION BY i_class), ORDER BY without LIMIT)."""
+    sql = streams.render('query98')
+    exp = oq.run_query('query98', sql, warehouse)
+    assert exp.num_rows > 20
+    for source in ('hbm', 'host'):
+        got = _Sess(gpu_engine, source).sql(sql).toArrow()
+        assert got.schema.names == exp.schema.names
+        assert [str(t) for t in got.schema.types] == [str(t) for t in exp.schema.types], (got.schema, exp.schema)
+        assert rows_equal(got.to_pylist(), exp.to_pylist()), (source, got.to_pylist()[:2], exp.to_pylist()[:2])
+        ops = [o['op'] for o in gpu_engine.last_stats()['ops']]
+        assert 'scan_probe' in ops and 'window' in ops, ops
+
+
 @pytest.mark.parametrize('query', streams.SUBSET)
 @pytest.mark.parametrize('pi', range(len(PARAMS)))
 def test_query_matches_oracle(gpu_engine, warehouse, query, pi):

@@ -375,3 +375,22 @@ def test_ranking_window_plan_shape():
     assert by_np[1]['keys'] == [{'expr': {'col': 'i_category'}, 'desc': False}, {'expr': {'col': '_agg0'}, 'desc': True}]
     assert by_np[0]['keys'] == [{'expr': {'col': 'i_class'}, 'desc': False}] and by_np[0]['funcs'][0]['fn'] == 'dense_rank'
     assert [o['name'] for o in p['output']] == ['i_category', 'i_class', 's', 'rk', 'rn', 'dr']
+
+
+def test_query98_template_plans():
+    """query98 of the NDS templates: `cast('..' as date) + interval 30 days` folds to a date constant; the window sits between
+    the aggregate and the projection; no LIMIT."""
+    from spark_rapids_benchmarks_b200 import streams
+    p = planner.plan_sql(streams.render('query98'))
+    assert p['root']['op'] == 'sort' and p['root']['limit'] == -1
+    ops = []
+    node = p['root']
+    while 'child' in node:
+        ops.append(node['op'])
+        node = node['child']
+    assert ops == ['sort', 'project', 'window', 'aggregate'] and node['op'] == 'join'
+    dates = node['build']['cond']['args']
+    assert dates[0]['args'][1] == {'lit': 10231, 'type': 'date'} and dates[1]['args'][1] == {'lit': 10261, 'type': 'date'}
+    assert [o['type'] for o in p['output']][-2:] == ['decimal(17,2)', 'double']
+    with pytest.raises(planner.PlanError):
+        planner.plan_sql('select d_date_sk from date_dim where d_date + interval 3 days > cast(\'1998-01-01\' as date)')
