@@ -244,6 +244,18 @@ class Planner:
             if op == 'div':
                 return _fn('div', l, r), 'double'
             raise PlanError('operator %r' % op)
+        if kind == 'like':
+            # x LIKE 'abc%' (a prefix) = substr(x, 1, 3) = 'abc'; x LIKE 'abc' (no wildcard) = equality.  Other patterns raise.
+            x, t = self.expr(ast[1], agg_map, key_map)
+            pat = ast[2]
+            if t != 'string':
+                raise PlanError('LIKE over a non-string')
+            body = pat[:-1] if pat.endswith('%') else pat
+            if '%' in body or '_' in body or '\\' in body or not body:
+                raise PlanError('LIKE pattern %r is not supported yet (a literal prefix followed by %% is)' % pat)
+            lhs = _fn('substr', x, start=1, len=len(body)) if pat.endswith('%') else x
+            r = _fn('eq', lhs, {'lit': body, 'type': 'string'})
+            return (_fn('not', r) if ast[3] else r), 'bool'
         if kind == 'interval':
             raise PlanError('INTERVAL is only supported as date constant +/- INTERVAL n DAYS')
         if kind == 'wcall':
@@ -261,6 +273,19 @@ class Planner:
                 start = self.const_int(ast[2][1])
                 ln = self.const_int(ast[2][2]) if len(ast[2]) > 2 else (1 << 30)
                 return _fn('substr', x, start=start, len=ln), 'string'
+            if fname == 'coalesce' and len(ast[2]) >= 2:
+                # coalesce(a, b, ...) = if(a is not null, a, coalesce(b, ...)); the arguments must be of one type family
+                parts = [self.expr(a, agg_map, key_map) for a in ast[2]]
+                if any(tv == 'string' for _, tv in parts):
+                    raise PlanError('coalesce() over strings is not supported yet (a projected string must come from one column)')
+                res, t = parts[-1]
+                for v, tv in reversed(parts[:-1]):
+                    if (tv == 'string') != (t == 'string') or (tv == 'double') != (t == 'double'):
+                        raise PlanError('coalesce() over different types')
+                    if 'lit' in res and res['lit'] is None:
+                        res = {'lit': None, 'type': tv}
+                    res, t = _fn('if', _fn('isnotnull', v), v, res), tv
+                return res, t
             if fname == 'abs' and len(ast[2]) == 1:
                 x, t = self.expr(ast[2][0], agg_map, key_map)
                 if not _is_num(t) and t != 'double':

@@ -14,7 +14,7 @@ Anything outside the subset raises SqlError - the statement is never silently ap
 The AST is plain tuples:  ('col', qualifier|None, name) | ('num', text) | ('str', value) | ('null',)
  | ('call', fname, [args], distinct) | ('wcall', fname, [args], [partition exprs], [(expr, desc, nulls_first)]) | ('bin', op, l, r) | ('not', x) | ('neg', x)
  | ('isnull', x, negated) | ('between', x, lo, hi, negated) | ('in', x, [items], negated)
- | ('interval', n, 'day') | ('case', [(cond, value)...], else|None) | ('cast', x, typename) | ('star',)
+ | ('interval', n, 'day') | ('like', x, pattern, negated) | ('case', [(cond, value)...], else|None) | ('cast', x, typename) | ('star',)
  | ('exists', query, negated) | ('in_sub', x, query, negated)
 A query is {'select', 'from', 'where', 'group', 'having', 'order', 'limit', 'distinct', 'left_joins': [(alias, on_expr)],
 'rollup': GROUP BY ROLLUP(...)}.
@@ -290,7 +290,10 @@ class Parser:
             self.expect('op', ')')
             return ('in', e, items, neg)
         if self.kw('like'):
-            raise SqlError('LIKE is not supported by the B200 planner yet')
+            pat = self.next()
+            if pat[0] != 'str':
+                raise SqlError('LIKE needs a string literal pattern')
+            return ('like', e, pat[1], neg)
         return e
 
     def additive(self):

@@ -315,3 +315,16 @@ def test_ranking_windows_and_nested_derived_tables(gpu_engine, warehouse):
     want = sorted(r['i_item_sk'] for r in it if r['i_manager_id'] is not None and r['i_manager_id'] < 30 and r['i_class'] is not None
                   and r['i_class'] > 'i_class_03' and r['i_item_sk'] < 5000)
     assert a['k'].to_pylist() == want and len(want) > 3
+
+
+def test_like_prefix_and_coalesce(gpu_engine, warehouse):
+    sql = ("select i_item_sk, coalesce(i_current_price, 0) p, coalesce(i_manager_id, i_manufact_id, -1) m from item "
+           "where i_category like 'S%' and i_category not like 'Sports' order by i_item_sk")
+    got = _Sess(gpu_engine).sql(sql).toArrow().to_pylist()
+    it = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_category', 'i_current_price', 'i_manager_id', 'i_manufact_id']).to_pylist()
+    exp = []
+    for r in sorted(it, key=lambda r: r['i_item_sk']):
+        if r['i_category'] is not None and r['i_category'].startswith('S') and r['i_category'] != 'Sports':
+            m = r['i_manager_id'] if r['i_manager_id'] is not None else (r['i_manufact_id'] if r['i_manufact_id'] is not None else -1)
+            exp.append({'i_item_sk': r['i_item_sk'], 'p': r['i_current_price'] if r['i_current_price'] is not None else decimal.Decimal('0.00'), 'm': m})
+    assert got == exp and len(exp) > 5 and any(r['i_current_price'] is None for r in it)

@@ -69,7 +69,8 @@ def test_distributed_plan_splits_at_the_aggregate():
     'select distinct i_brand, count(*) from item group by i_brand',
     'select i_brand from item having count(*) > 1 and i_brand > \'a\'',       # HAVING over a non-grouped column
     'select i_brand from item left join promotion on p_item_sk = i_item_sk left join store on s_store_sk = p_promo_sk',   # chained outer joins
-    'select i_brand from item where i_brand like \'a%\'',
+    'select i_brand from item where i_brand like \'%a\'',                      # only a literal prefix + % is supported
+    'select i_brand from item where i_brand like \'a_c%\'',
     'select i_brand, sum(distinct i_item_sk) from item group by i_brand',
     'select i_brand, count(distinct i_item_sk), count(distinct i_class) from item group by i_brand',
     'select nope from item',
@@ -394,3 +395,14 @@ def test_query98_template_plans():
     assert [o['type'] for o in p['output']][-2:] == ['decimal(17,2)', 'double']
     with pytest.raises(planner.PlanError):
         planner.plan_sql('select d_date_sk from date_dim where d_date + interval 3 days > cast(\'1998-01-01\' as date)')
+
+
+def test_like_prefix_and_coalesce():
+    p = planner.plan_sql("select i_item_sk, coalesce(i_current_price, 0) p from item where i_brand like 'amalgam%' and i_class not like 'x' order by i_item_sk")
+    f = p['root']['child']['child']
+    assert f['op'] == 'filter'
+    a, b = f['cond']['args']
+    assert a == {'fn': 'eq', 'args': [{'fn': 'substr', 'args': [{'col': 'i_brand'}], 'start': 1, 'len': 7}, {'lit': 'amalgam', 'type': 'string'}]}
+    assert b == {'fn': 'not', 'args': [{'fn': 'eq', 'args': [{'col': 'i_class'}, {'lit': 'x', 'type': 'string'}]}]}
+    e = p['root']['child']['exprs'][1]['expr']
+    assert e['fn'] == 'if' and e['args'][0] == {'fn': 'isnotnull', 'args': [{'col': 'i_current_price'}]} and p['output'][1]['type'] == 'decimal(7,2)'
