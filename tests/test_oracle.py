@@ -67,3 +67,38 @@ def test_stream_generator_roundtrip(tmp_path):
     assert list(d.keys()) == names == streams.SUBSET
     for k, v in d.items():
         assert v.startswith('-- start query') and (k + '.tpl') in v
+
+
+def test_query98_oracle_against_plain_python(warehouse):
+    """The Acero restatement of query98 against dict / Decimal loops over the same files (an independent second path, like
+    run_query_slow for the six bench statements): same groups, same revenue, same share of the class's revenue, same order."""
+    import datetime
+    import decimal
+    sql = streams.render('query98')
+    a = oq.run_query('query98', sql, warehouse).to_pylist()
+    d0 = datetime.date(1998, 1, 5)
+    days = {r['d_date_sk'] for r in oq.read_dim(warehouse, 'date_dim', ['d_date_sk', 'd_date']).to_pylist()
+            if r['d_date'] is not None and d0 <= r['d_date'] <= d0 + datetime.timedelta(days=30)}
+    items = {r['i_item_sk']: r for r in oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_item_id', 'i_item_desc', 'i_category', 'i_class',
+                                                                       'i_current_price']).to_pylist()
+             if r['i_category'] in ('Sports', 'Books', 'Home')}
+    groups = {}
+    for r in oq.read_fact(warehouse, 'store_sales', 'ss_sold_date_sk', ['ss_sold_date_sk', 'ss_item_sk', 'ss_ext_sales_price']).to_pylist():
+        if r['ss_sold_date_sk'] in days and r['ss_item_sk'] in items:
+            it = items[r['ss_item_sk']]
+            k = (it['i_item_id'], it['i_item_desc'], it['i_category'], it['i_class'], it['i_current_price'])
+            s = groups.setdefault(k, [None])
+            if r['ss_ext_sales_price'] is not None:
+                s[0] = r['ss_ext_sales_price'] if s[0] is None else s[0] + r['ss_ext_sales_price']
+    total = {}
+    for k, (s,) in groups.items():
+        if s is not None:
+            total[k[3]] = total.get(k[3], decimal.Decimal(0)) + s
+    b = {k: (s, (float(s * 100) / float(total[k[3]])) if s is not None and total.get(k[3]) else None) for k, (s,) in groups.items()}
+    assert len(a) == len(b) > 20
+    for r in a:
+        k = (r['i_item_id'], r['i_item_desc'], r['i_category'], r['i_class'], r['i_current_price'])
+        assert b[k][0] == r['itemrevenue'] and (b[k][1] == r['revenueratio'] or abs(b[k][1] - r['revenueratio']) < 1e-9 * abs(b[k][1]))
+    keys = [(r['i_category'], r['i_class'], r['i_item_id']) for r in a]
+    none_first = lambda t: tuple((v is not None, v or '') for v in t)
+    assert keys == sorted(keys, key=none_first)
