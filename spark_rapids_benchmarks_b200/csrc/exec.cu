@@ -637,11 +637,18 @@ struct Exec {
     } else if (fn == "if") {
       LType tc = compile(arg(0), b, bb, code);
       if (tc.kind != LType::BOOL) fail("plan: if() condition must be boolean");
-      LType tt = compile(arg(1), b, bb, code), te = compile(arg(2), b, bb, code);
+      int o1 = -1, o2 = -1;
+      LType tt = compile(arg(1), b, bb, code, &o1), te = compile(arg(2), b, bb, code, &o2);
       if ((tt.kind == LType::STR) != (te.kind == LType::STR) || (tt.kind == LType::F64) != (te.kind == LType::F64))
         fail("plan: if() branches of different type families");
       code.push_back(Instr{OP_IF, 0, 0});
-      if (str_origin) *str_origin = -2;
+      if (str_origin) {
+        // a string result points into ONE column's bytes: both branches from that column, or the other branch a NULL
+        // (CASE WHEN c THEN col END); anything else (a literal beside a column, two columns) is mixed
+        const bool n1 = arg(1).has("lit") && arg(1).at("lit").kind == Json::Null;
+        const bool n2 = arg(2).has("lit") && arg(2).at("lit").kind == Json::Null;
+        *str_origin = n1 ? o2 : (n2 ? o1 : (o1 == o2 ? o1 : -2));
+      }
       out = tt;
       out.is32 = false;
       out.maxlen = (tt.maxlen > 0 && te.maxlen > 0) ? std::max(tt.maxlen, te.maxlen) : 0;

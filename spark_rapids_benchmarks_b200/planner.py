@@ -431,6 +431,19 @@ class Planner:
         and marked 'replicated': every rank computes the whole result and nothing is exchanged - summing the ranks'
         identical partial states would multiply every SUM and COUNT by the world size."""
         q = self.q
+        # ORDER BY expressions may use select aliases (Spark resolves them against the select list first): an alias INSIDE an
+        # expression is replaced by the select expression it names; a bare alias stays a reference to the output column
+        alias_ast = {a: e for e, a in q['select'] if a and self.col_table.get(a) not in self.tables}
+
+        def subst(a):
+            if not isinstance(a, tuple):
+                return a
+            if a[0] == 'col' and a[1] is None and a[2] in alias_ast:
+                return alias_ast[a[2]]
+            return tuple([subst(y) if isinstance(y, tuple) else y for y in x] if isinstance(x, list) else subst(x) for x in a)
+        if alias_ast:
+            q = dict(q, order=[((e if (e[0] == 'col' and e[1] is None) else subst(e)), d, nf) for e, d, nf in q['order']])
+            self.q = q
         conj = []
 
         def split(e):
@@ -753,21 +766,26 @@ class Planner:
                 node = win_map.wrap(node)
             order_extra = [None if (e[0] == 'col' and e[1] is None and e[2] in select_aliases) else self.expr(e)
                            for e, _, _ in q['order']]
-        node = {'op': 'project', 'exprs': [{'name': n, 'expr': ir} for n, ir, _ in out_cols], 'child': node}
-
         # ---- order by / limit
+        hidden = []                # ORDER BY expressions that are no output column: computed beside the outputs, dropped after the sort
+        order_names = []
+        for (e, desc, nf), extra in zip(q['order'], order_extra):
+            if extra is None:
+                order_names.append(e[2])
+                continue
+            ir, t = extra
+            match = [n for n, oir, _ in out_cols if oir == ir] + [n for n, oir, _ in hidden if oir == ir]
+            if not match:
+                if q.get('distinct'):
+                    raise PlanError('ORDER BY expression %s is not in the select list of SELECT DISTINCT' % self.text(e))
+                match = ['_ord%d' % len(hidden)]
+                hidden.append((match[0], ir, t))
+            order_names.append(match[0])
+        node = {'op': 'project', 'exprs': [{'name': n, 'expr': ir} for n, ir, _ in out_cols + hidden], 'child': node}
         if q['order'] or q['limit'] is not None:
             keys = []
             used_names = []
-            for (e, desc, nf), extra in zip(q['order'], order_extra):
-                if extra is None:
-                    name = e[2]
-                else:
-                    ir, _ = extra
-                    match = [n for n, oir, _ in out_cols if oir == ir]
-                    if not match:
-                        raise PlanError('ORDER BY expression %s is not in the select list (not supported yet)' % self.text(e))
-                    name = match[0]
+            for (e, desc, nf), name in zip(q['order'], order_names):
                 k = {'expr': _col(name), 'desc': bool(desc)}
                 if nf is not None:
                     k['nulls_first'] = bool(nf)
@@ -785,6 +803,10 @@ class Planner:
                 if n not in used_names and not total:
                     keys.append({'expr': _col(n), 'desc': False})
             node = {'op': 'sort', 'keys': keys, 'limit': -1 if q['limit'] is None else q['limit'], 'child': node}
+        if hidden:
+            if distributed:
+                raise PlanError('ORDER BY expressions outside the select list are not supported across GPUs yet')
+            node = {'op': 'project', 'exprs': [{'name': n, 'expr': _col(n)} for n, _, _ in out_cols], 'child': node}
         out = {'root': node, 'output': [{'name': n, 'type': t} for n, _, t in out_cols]}
         if replicated_root:
             out['replicated'] = True

@@ -328,3 +328,32 @@ def test_like_prefix_and_coalesce(gpu_engine, warehouse):
             m = r['i_manager_id'] if r['i_manager_id'] is not None else (r['i_manufact_id'] if r['i_manufact_id'] is not None else -1)
             exp.append({'i_item_sk': r['i_item_sk'], 'p': r['i_current_price'] if r['i_current_price'] is not None else decimal.Decimal('0.00'), 'm': m})
     assert got == exp and len(exp) > 5 and any(r['i_current_price'] is None for r in it)
+
+
+def test_order_by_outside_the_select_list(gpu_engine, warehouse):
+    """ORDER BY a column / an aggregate / an expression over a select alias that is not an output column: computed beside the
+    outputs, sorted on, dropped (project -> sort -> project)."""
+    it = oq.read_dim(warehouse, 'item', ['i_item_sk', 'i_class', 'i_category', 'i_current_price', 'i_manager_id']).to_pylist()
+    got = _Sess(gpu_engine).sql("select i_item_sk k, i_current_price p from item where i_manager_id < 40 "
+                                "order by i_class desc, k limit 50").toArrow()
+    rows = [r for r in it if r['i_manager_id'] is not None and r['i_manager_id'] < 40]
+    rows.sort(key=lambda r: r['i_item_sk'])
+    rows.sort(key=lambda r: (r['i_class'] is not None, (r['i_class'] or '').encode()), reverse=True)      # DESC: NULLS LAST, stable
+    assert got.schema.names == ['k', 'p']
+    assert _rows(got, ['k', 'p']) == [(r['i_item_sk'], r['i_current_price']) for r in rows[:50]]
+
+    got = _Sess(gpu_engine).sql("select i_category c, sum(i_current_price) s from item group by i_category "
+                                "order by count(*) desc, case when s > 0 then c end limit 100").toArrow()
+    groups = {}
+    for r in it:
+        g = groups.setdefault(r['i_category'], [0, None])
+        g[0] += 1
+        if r['i_current_price'] is not None:
+            g[1] = r['i_current_price'] if g[1] is None else g[1] + r['i_current_price']
+    exp = [(c, s, n) for c, (n, s) in groups.items()]
+    exp.sort(key=lambda t: (t[0] is not None, (t[0] or '').encode(), t[1] is not None, t[1] or 0))     # tie-break: the outputs, ascending, NULLS FIRST
+    exp.sort(key=lambda t: ((t[0] if (t[1] is not None and t[1] > 0) else None) is not None,
+                            ((t[0] if (t[1] is not None and t[1] > 0) else None) or '').encode()))
+    exp.sort(key=lambda t: -t[2])
+    assert got.schema.names == ['c', 's']
+    assert _rows(got, ['c', 's']) == [(c, s) for c, s, _ in exp]
