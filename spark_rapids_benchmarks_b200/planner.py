@@ -820,7 +820,8 @@ class Planner:
             # the partial states are hash-partitioned by the group keys (all-to-all), every rank merges and ranks ITS groups
             # only, and the per-rank results (at most LIMIT rows each) are gathered and ranked once more
             gkeys = [k['name'] for k in final_partial['keys']]
-            if gkeys:
+            # (not with window functions: a partition's groups would be spread over the ranks - the gather form has them all)
+            if gkeys and not (win_map.parts or win_map.ranks):
                 local = _replace_partial_scan(node, {'op': 'exchange', 'mode': 'hash', 'keys': gkeys, 'child': final_partial})
                 top = {'op': 'exchange', 'child': local}
                 if node['op'] == 'sort':

@@ -63,3 +63,13 @@ def test_sql_shapes_of_the_gpu_suite_on_the_interpreter(warehouse):
     assert len(names) >= 12
     for n in names:
         getattr(m, n)(eng, warehouse)
+
+
+def test_distributed_window_statement_keeps_the_gather_form(warehouse):
+    """query98 across GPUs: partial aggregate -> exchange (gather) -> merge -> window -> ...; the hash form, where every rank
+    would only see its own groups of a partition, is not offered."""
+    sql = streams.render('query98')
+    plan = planner.plan_sql(sql, distributed=True)
+    assert 'fused' in plan and 'fused_hash' not in plan
+    rb, _ = plan_interp.execute({'root': plan['fused']}, warehouse)
+    assert _rows_equal(rb.to_pylist(), oq.run_query('query98', sql, warehouse).to_pylist())
