@@ -116,11 +116,16 @@ class Batch:
         return out
 
 
-def _scan_table(warehouse, table, columns):
+def _stable_hash(key):
+    import zlib
+    return zlib.crc32(repr(key).encode())
+
+
+def _scan_table(warehouse, table, columns, shard=None):
     from spark_rapids_benchmarks_b200 import nds_schema
     part = nds_schema.TABLE_PARTITIONING.get(table)
     if part and os.path.isdir(os.path.join(warehouse, table)) and any('=' in e for e in os.listdir(os.path.join(warehouse, table))):
-        t = oq.read_fact(warehouse, table, part, list(columns))
+        t = oq.read_fact(warehouse, table, part, list(columns), None, shard)
     else:
         t = oq.read_dim(warehouse, table, list(columns))
     b = Batch()
@@ -310,8 +315,12 @@ def _out_val(t, v):
 
 # ---------------------------------------------------------------- operators
 class Interp:
-    def __init__(self, warehouse):
+    """rank / world: one rank of `world` - a hive-partitioned table is read as this rank's shard (every world-th file, like the
+    engine), an `exchange` runs its child for every rank and gathers the rows (mode hash: keeps the rows whose keys hash to
+    this rank), so that the distributed plan forms can be checked on the CPU."""
+    def __init__(self, warehouse, rank=0, world=1):
         self.wh = warehouse
+        self.rank, self.world = rank, world
         self.ops = []
 
     def run(self, node):
@@ -319,10 +328,21 @@ class Interp:
         return getattr(self, 'op_' + op)(node)
 
     def op_scan(self, node):
-        return _scan_table(self.wh, node['table'], node['columns'])
+        return _scan_table(self.wh, node['table'], node['columns'], (self.rank, self.world) if self.world > 1 else None)
 
     def op_exchange(self, node):
-        return self.run(node['child'])
+        if self.world <= 1:
+            return self.run(node['child'])
+        parts = [Interp(self.wh, r, self.world).run(node['child']) for r in range(self.world)]
+        out = Batch()
+        out._n = sum(p.n for p in parts)
+        for c, name in enumerate(parts[0].names):
+            out.add(name, parts[0].types[c], [v for p in parts for v in p.cols[c]])
+        if node.get('mode', 'gather') == 'hash':
+            kc = [out.cols[out.find(k)] for k in node['keys']]
+            mine = [i for i in range(out.n) if _stable_hash(tuple(col[i] for col in kc)) % self.world == self.rank]
+            out = out.take(mine)
+        return out
 
     def op_filter(self, node):
         b = self.run(node['child'])
@@ -573,9 +593,9 @@ def to_arrow(b):
     return pa.RecordBatch.from_arrays(arrays, schema=pa.schema(fields))
 
 
-def execute(plan, warehouse):
+def execute(plan, warehouse, rank=0, world=1):
     """plan: {'root': node} or a node. Returns (pyarrow.RecordBatch, [operator names the tests look for])."""
-    it = Interp(warehouse)
+    it = Interp(warehouse, rank, world)
     b = it.run(plan['root'] if 'root' in plan else plan)
     return to_arrow(b), it.ops
 

@@ -73,3 +73,22 @@ def test_distributed_window_statement_keeps_the_gather_form(warehouse):
     assert 'fused' in plan and 'fused_hash' not in plan
     rb, _ = plan_interp.execute({'root': plan['fused']}, warehouse)
     assert _rows_equal(rb.to_pylist(), oq.run_query('query98', sql, warehouse).to_pylist())
+
+
+@pytest.mark.parametrize('world', [2, 3])
+@pytest.mark.parametrize('query', streams.SUBSET + streams.EXTRA)
+def test_distributed_plan_forms_over_emulated_ranks(warehouse, query, world):
+    """Every rank of `world` runs the one-plan form over its shard of the fact files (every world-th file), the exchange gathers
+    (or hash-partitions) the partial states of all ranks: every rank must end with the single-GPU answer."""
+    sql = streams.render(query, overrides=PARAMS[0])
+    exp = oq.run_query(query, sql, warehouse).to_pylist()
+    plan = planner.plan_sql(sql, distributed=True)
+    for form in ('fused', 'fused_hash'):
+        if form not in plan:
+            continue
+        for rank in range(world):
+            rb, _ = plan_interp.execute({'root': plan[form]}, warehouse, rank, world)
+            assert _rows_equal(rb.to_pylist(), exp), (form, rank)
+    # a statement whose root table is replicated is planned without an exchange: every rank computes it alone
+    rep = planner.plan_sql('select i_category, count(*) n from item group by i_category order by i_category', distributed=True)
+    assert rep.get('replicated') and 'fused' not in rep
